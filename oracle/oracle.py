@@ -1,0 +1,298 @@
+"""CPU oracle for the LUT-VQ hot path -- TEST INFRASTRUCTURE ONLY.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this module.  The product path
+(``rvv-lut-vq_b200/`` + ``liblutvq.so``) never touches ``oracle/``.
+
+Two layers, both restating the reference (paths relative to /root/reference):
+
+* numpy restatements (``np_*``) that follow the reference line by line and are small-case
+  checkers: ``vq_dataflow_sim/vq.py:269-307`` and
+  ``benchmark/AQLM/inference_lib/src/aqlm/{utils.py:24-70, inference_kernels/numba_kernel.py:38-48}``;
+* ctypes bindings (``c_*``) to ``liblutvq_oracle.so`` (``lutvq_oracle.c``), the fast C restatement
+  used at full sizes and as the timed CPU baseline.
+
+Parity: PINNED -- ``oracle/gen_golden.py`` ran the reference's own Python in the build container
+and froze its outputs under ``tests/golden/``; ``tests/test_oracle_golden.py`` replays them.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liblutvq_oracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile the C oracle (and, when /root/reference exists, oracle/_ref). Idempotent."""
+    if force or not os.path.exists(_LIB_PATH) or any(
+        os.path.exists(os.path.join(_HERE, s)) and os.path.getmtime(os.path.join(_HERE, s)) > os.path.getmtime(_LIB_PATH)
+        for s in ("lutvq_oracle.c", "tmac_oracle.c")
+    ):
+        subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
+    if os.path.isdir("/root/reference") and os.path.exists(os.path.join(_HERE, "ref_wrap_tmac.cc")):
+        subprocess.call(["make", "-C", _HERE, "ref"], stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.orc_num_threads.restype = ctypes.c_int
+        P, I, U64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint64
+        sigs = {
+            "orc_lut_build_vqpy": [P, P, I, I, I, I, I, P],
+            "orc_lut_build_f32": [P, P, I, I, I, I, P],
+            "orc_lut_gemv_f64": [P, P, I, I, I, I, P],
+            "orc_dequantize": [P, I, P, P, I, I, I, I, I, I, P],
+            "orc_dense_gemv_f64": [P, P, I, I, I, P],
+            "orc_dense_gemm_f64": [P, P, I, I, I, I, P],
+            "orc_aqlm_gemv_f64": [P, P, P, I, I, I, I, I, P],
+            "orc_aqlm_gemv_f32": [P, P, P, P, P, I, I, I, I, P, P],
+            "orc_aqlm_gemv_rowmajor": [P, P, P, P, P, I, I, I, I, I, P, P],
+            "orc_scale_bias_epilogue": [P, P, P, I, I, I],
+            "orc_unpack_codes": [P, ctypes.c_size_t, P],
+            "orc_simd_lut_scalar": [P, P, P, I, U64, U64],
+        }
+        for name, args in sigs.items():
+            fn = getattr(_lib, name)
+            fn.argtypes, fn.restype = args, None
+    return _lib
+
+
+def _p(a: Optional[np.ndarray]):
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"], "oracle expects C-contiguous arrays"
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def num_threads() -> int:
+    return int(lib().orc_num_threads())
+
+
+# --------------------------------------------------------------------------------------------
+# helpers: dtype views.  fp16 lives in numpy natively; bf16 is carried as uint16 bit patterns.
+# --------------------------------------------------------------------------------------------
+def f32_to_bf16_bits(a: np.ndarray) -> np.ndarray:
+    u = np.ascontiguousarray(a, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    r = (u + 0x7FFF + ((u >> 16) & 1)) >> 16
+    return r.astype(np.uint16)
+
+
+def bf16_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    return (b.astype(np.uint32) << 16).view(np.float32)
+
+
+def to_bits(a: np.ndarray, dtype: int) -> np.ndarray:
+    """storage bits (uint16) of an array given as float: dtype 0 = fp16, 1 = bf16"""
+    if a.dtype == np.uint16:
+        return np.ascontiguousarray(a)
+    if dtype == 0:
+        return np.ascontiguousarray(a.astype(np.float16)).view(np.uint16)
+    return f32_to_bf16_bits(a.astype(np.float32))
+
+
+def from_bits(b: np.ndarray, dtype: int) -> np.ndarray:
+    return b.view(np.float16).astype(np.float32) if dtype == 0 else bf16_bits_to_f32(b)
+
+
+# --------------------------------------------------------------------------------------------
+# numpy restatements (small cases; line-by-line with the reference)
+# --------------------------------------------------------------------------------------------
+def np_unpack_int_data(codes: np.ndarray, nbits: int = 8) -> np.ndarray:
+    """utils.py:29-31: data.to(int64) % 2**nbits"""
+    return codes.astype(np.int64) % (2**nbits)
+
+
+def np_pack_int_data(idx: np.ndarray, nbits: int = 8) -> np.ndarray:
+    """utils.py:24-26 (without mutating the input): values >= 2^(nbits-1) wrap negative, stored in int8"""
+    d = idx.astype(np.int64).copy()
+    d[d >= 2 ** (nbits - 1)] -= 2**nbits
+    return d.astype(np.int8 if nbits <= 8 else np.int16)
+
+
+def np_compute_lut(x: np.ndarray, codebook: np.ndarray) -> np.ndarray:
+    """vq.py:280-285.  x (D,) ; codebook (M,N,K,d) fp16 -> lut (M,N,K) fp16 (numpy fp16 semantics)."""
+    M, N, K, d = codebook.shape
+    xr = x.reshape(M, 1, 1, d).astype(np.float16)
+    return (codebook * xr).sum(axis=-1)
+
+
+def np_compute_lut_gemm(x: np.ndarray, codebook: np.ndarray, codeword: np.ndarray) -> np.ndarray:
+    """vq.py:287-302 vectorised: out[i,j] = sum_{m,n} lut_i[m,n,code[j,m,n]] in float64."""
+    M, N, K, d = codebook.shape
+    out = np.zeros((x.shape[0], codeword.shape[0]))
+    mi = np.arange(M)[None, :, None]
+    ni = np.arange(N)[None, None, :]
+    for i in range(x.shape[0]):
+        lut = np_compute_lut(x[i], codebook)
+        out[i] = lut[mi, ni, codeword].astype(np.float64).sum(axis=(1, 2))
+    return out
+
+
+def np_dequantize(codebook: np.ndarray, codeword: np.ndarray) -> np.ndarray:
+    """vq.py:269-278: weight[j,m,:] = sum_n codebook[m,n,code[j,m,n],:] (float64) -> fp16 (d_out, D)."""
+    M, N, K, d = codebook.shape
+    d_out = codeword.shape[0]
+    w = np.zeros((d_out, M, d))
+    mi = np.arange(M)[None, :]
+    for n in range(N):
+        w += codebook[mi, n, codeword[:, :, n], :]
+    return w.reshape(d_out, M * d).astype(np.float16)
+
+
+def np_aqlm_dequantize_weight(codes_idx: np.ndarray, codebooks: np.ndarray, scales: Optional[np.ndarray]) -> np.ndarray:
+    """utils.py:43-70 for out_group_size=1: W[o, g*d:(g+1)*d] = (sum_n codebooks[n, idx[o,g,n], 0, :]) * scales[o].
+    Computed in float32 from the given arrays (embedding_bag accumulates in the storage dtype; callers
+    compare by tolerance except for N=2 where a single add is exact in both)."""
+    O, G, N = codes_idx.shape
+    d = codebooks.shape[-1]
+    w = np.zeros((O, G, d), dtype=np.float32)
+    for n in range(N):
+        w += codebooks[n, codes_idx[:, :, n], 0, :].astype(np.float32)
+    if scales is not None:
+        w = w * scales.reshape(O, 1, 1).astype(np.float32)
+    return w.reshape(O, G * d)
+
+
+def np_numba_gemv_lut(x: np.ndarray, codebooks: np.ndarray, codes_alt: np.ndarray, scales: np.ndarray) -> np.ndarray:
+    """numba_kernel.py:38-48 restated with numpy (fp32).  codes_alt uint8 [G, O, N]."""
+    N, K, _, d = codebooks.shape
+    G, O, _ = codes_alt.shape
+    lut = x.reshape(-1, d).astype(np.float32) @ codebooks.reshape(-1, d).astype(np.float32).T
+    lut = lut.reshape(G, N, K)
+    gi = np.arange(G)[:, None, None]
+    ci = np.arange(N)[None, None, :]
+    out = lut[gi, ci, codes_alt].sum(axis=(0, 2), dtype=np.float32)
+    return out * scales.reshape(-1).astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------------
+# ctypes bindings to the C restatement
+# --------------------------------------------------------------------------------------------
+def c_lut_build_vqpy(x_f16: np.ndarray, codebook_f16: np.ndarray, M: int) -> np.ndarray:
+    """codebook (M,N,K,d) or shared (N,K,d).  returns lut fp16 (M,N,K)"""
+    shared = codebook_f16.ndim == 3
+    N, K, d = codebook_f16.shape[-3:]
+    x = np.ascontiguousarray(x_f16, dtype=np.float16)
+    cb = np.ascontiguousarray(codebook_f16, dtype=np.float16)
+    lut = np.empty((M, N, K), dtype=np.float16)
+    lib().orc_lut_build_vqpy(_p(x), _p(cb), int(shared), M, N, K, d, _p(lut))
+    return lut
+
+
+def c_lut_gemv_f64(lut_f16: np.ndarray, codeword_u8: np.ndarray) -> np.ndarray:
+    M, N, K = lut_f16.shape
+    d_out = codeword_u8.shape[0]
+    out = np.empty(d_out, dtype=np.float64)
+    lib().orc_lut_gemv_f64(_p(np.ascontiguousarray(lut_f16)), _p(np.ascontiguousarray(codeword_u8)), d_out, M, N, K, _p(out))
+    return out
+
+
+def c_dequantize(codebook_bits: np.ndarray, codeword_u8: np.ndarray, scales_bits: Optional[np.ndarray], M: int, dtype: int = 0) -> np.ndarray:
+    """returns W storage bits uint16 (d_out, M*d).  codebook (M,N,K,d) or shared (N,K,d), uint16 bits or fp16."""
+    cb = codebook_bits.view(np.uint16) if codebook_bits.dtype != np.uint16 else codebook_bits
+    cb = np.ascontiguousarray(cb)
+    shared = cb.ndim == 3
+    N, K, d = cb.shape[-3:]
+    cw = np.ascontiguousarray(codeword_u8, dtype=np.uint8)
+    d_out = cw.shape[0]
+    sc = None
+    if scales_bits is not None:
+        sc = np.ascontiguousarray(scales_bits.view(np.uint16) if scales_bits.dtype != np.uint16 else scales_bits).reshape(-1)
+    W = np.empty((d_out, M * d), dtype=np.uint16)
+    lib().orc_dequantize(_p(cb), int(shared), _p(cw), _p(sc), d_out, M, N, K, d, dtype, _p(W))
+    return W
+
+
+def c_dense_gemv_f64(x_bits: np.ndarray, W_bits: np.ndarray, dtype: int = 0) -> np.ndarray:
+    d_out, D = W_bits.shape
+    out = np.empty(d_out, dtype=np.float64)
+    lib().orc_dense_gemv_f64(_p(np.ascontiguousarray(x_bits.view(np.uint16))), _p(np.ascontiguousarray(W_bits.view(np.uint16))), d_out, D, dtype, _p(out))
+    return out
+
+
+def c_dense_gemm_f64(x_bits: np.ndarray, W_bits: np.ndarray, dtype: int = 0) -> np.ndarray:
+    B, I = x_bits.shape
+    O = W_bits.shape[0]
+    out = np.empty((B, O), dtype=np.float64)
+    lib().orc_dense_gemm_f64(_p(np.ascontiguousarray(x_bits.view(np.uint16))), _p(np.ascontiguousarray(W_bits.view(np.uint16))), B, O, I, dtype, _p(out))
+    return out
+
+
+def c_aqlm_gemv_f64(x_bits: np.ndarray, codes_i8: np.ndarray, codebooks_bits: np.ndarray, dtype: int = 0) -> np.ndarray:
+    """exact y64 from raw operands.  codes int8 [O,G,N]; codebooks [N,256,1,d] or [N,256,d] storage bits."""
+    O, G, N = codes_i8.shape
+    d = codebooks_bits.shape[-1]
+    out = np.empty(O, dtype=np.float64)
+    lib().orc_aqlm_gemv_f64(
+        _p(np.ascontiguousarray(x_bits.view(np.uint16)).reshape(-1)),
+        _p(np.ascontiguousarray(codes_i8.view(np.int8))),
+        _p(np.ascontiguousarray(codebooks_bits.view(np.uint16))),
+        O, G, N, d, dtype, _p(out))
+    return out
+
+
+def c_aqlm_gemv_f32(x_f32: np.ndarray, codes_alt_u8: np.ndarray, codebooks_f32: np.ndarray, scales_f32: np.ndarray,
+                    bias_f32: Optional[np.ndarray] = None) -> np.ndarray:
+    """numba_gemv_lut_ port.  codes_alt uint8 [G,O,N]"""
+    G, O, N = codes_alt_u8.shape
+    d = codebooks_f32.shape[-1]
+    lut = np.empty((G, N, 256), dtype=np.float32)
+    out = np.empty(O, dtype=np.float32)
+    lib().orc_aqlm_gemv_f32(
+        _p(np.ascontiguousarray(x_f32, dtype=np.float32).reshape(-1)),
+        _p(np.ascontiguousarray(codes_alt_u8.view(np.uint8))),
+        _p(np.ascontiguousarray(codebooks_f32, dtype=np.float32)),
+        _p(np.ascontiguousarray(scales_f32, dtype=np.float32).reshape(-1)),
+        _p(None if bias_f32 is None else np.ascontiguousarray(bias_f32, dtype=np.float32)),
+        O, G, N, d, _p(lut), _p(out))
+    return out
+
+
+class RowMajorGemv:
+    """The timed CPU baseline: preallocates scratch so repeated calls time only the math."""
+
+    def __init__(self, O: int, G: int, N: int = 2, d: int = 8, dtype: int = 0):
+        self.O, self.G, self.N, self.d, self.dtype = O, G, N, d, dtype
+        self.lut = np.empty((G, N, 256), dtype=np.float32)
+        self.y = np.empty(O, dtype=np.uint16)
+        self._fn = lib().orc_aqlm_gemv_rowmajor
+
+    def __call__(self, x_bits, codes_i8, codebooks_bits, scales_bits=None, bias_bits=None) -> np.ndarray:
+        self._fn(_p(x_bits), _p(codes_i8), _p(codebooks_bits), _p(scales_bits), _p(bias_bits),
+                 self.O, self.G, self.N, self.d, self.dtype, _p(self.lut), _p(self.y))
+        return self.y
+
+
+def c_aqlm_gemv_rowmajor(x_bits, codes_i8, codebooks_bits, scales_bits=None, bias_bits=None, dtype: int = 0) -> np.ndarray:
+    O, G, N = codes_i8.shape
+    d = codebooks_bits.shape[-1]
+    f = RowMajorGemv(O, G, N, d, dtype)
+    u16 = lambda a: None if a is None else np.ascontiguousarray(a.view(np.uint16)).reshape(-1)
+    return f(u16(x_bits), np.ascontiguousarray(codes_i8.view(np.int8)), u16(codebooks_bits), u16(scales_bits), u16(bias_bits)).copy()
+
+
+def c_scale_bias_epilogue(y_bits: np.ndarray, scales_bits, bias_bits, dtype: int = 0) -> np.ndarray:
+    y = np.ascontiguousarray(y_bits.view(np.uint16)).copy()
+    B, O = y.reshape(-1, y.shape[-1]).shape
+    u16 = lambda a: None if a is None else np.ascontiguousarray(a.view(np.uint16)).reshape(-1)
+    lib().orc_scale_bias_epilogue(_p(y), _p(u16(scales_bits)), _p(u16(bias_bits)), B, O, dtype)
+    return y
+
+
+def c_simd_lut_scalar(idx_u8: np.ndarray, lut_i8: np.ndarray, n_runs: int) -> np.ndarray:
+    """bench_avx_lut.cpp:98-107 scalar semantics.  idx [n_lut_per_run, CB] uint8; returns int16[CB]."""
+    n_lut, cb = idx_u8.shape
+    out = np.zeros(cb, dtype=np.int16)
+    lib().orc_simd_lut_scalar(_p(np.ascontiguousarray(idx_u8)), _p(np.ascontiguousarray(lut_i8)), _p(out), cb, n_runs, n_lut)
+    return out
