@@ -1,0 +1,361 @@
+#!/usr/bin/env python
+"""bench.py -- LUT-VQ GEMV throughput on B200 (BASELINE.json metric: "LUT-VQ GEMV us & HBM GB/s (AQLM 2x8,
+4096x11008)"), one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (N=1, BASELINE configs[1]): Llama-2-7B gate_proj shape 4096->11008, AQLM 2x8 codes, batch 1.
+One STEP = one LUT-GEMV over each of NBUF distinct layers (random codes/codebooks/scales), whose code
+matrices total > 2x the 126 MB L2, so every launch streams its codes from HBM (L2-cold by construction).
+  value   whole-job GB/s on the algorithmic byte stream (O*(I/8)*2 + 8192 + 2I + 4O per GEMV),
+          inputs resident in HBM, the NBUF launches replayed as one CUDA graph, timed with CUDA events;
+  e2e     the same metric through the reference-facing op (ops.code2x8_matmat) with HOST buffers: per GEMV the
+          activation row is copied from pinned host memory and the output row copied back, inside the timed region;
+  roofline / cpu_baseline / clocks / sweep: see DESIGN.md "Measurement".
+N>1 (torchrun, one rank per GPU): the layer is sharded by OUTPUT CHANNEL (each rank owns an 11008-row shard of
+an N*11008-row layer) and every GEMV is followed by the all-gather of output slices (weak scaling).
+--impl reference: the reference's CPU LUT-GEMV (oracle port of numba_gemv_lut_, all host threads) on the same config.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+IN_F, OUT_F = 4096, 11008           # headline shape (gate_proj), BASELINE.json metric
+NBUF = 24                           # 24 x 11.27 MB = 270 MB of codes per step (> 2x L2)
+METRIC = "lutvq_gemv_hbm_gbps"
+UNIT = "GB/s"
+
+
+def algorithmic_bytes(i: int, o: int) -> int:
+    return o * (i // 8) * 2 + 2 * 256 * 8 * 2 + 2 * i + 4 * o
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons while the timed region runs"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's CPU implementation of the path (numba_gemv_lut_ semantics, aqlm numba_kernel.py:38-48),
+    timed as the oracle port on all host threads; each step = CPU_BUFS GEMVs of the headline shape."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as orc
+    CPU_BUFS = 4
+    rng = np.random.default_rng(0)
+    G = IN_F // 8
+    layers = [(rng.integers(0, 256, size=(OUT_F, G, 2), dtype=np.uint8).view(np.int8),
+               rng.standard_normal((2, 256, 8)).astype(np.float16).view(np.uint16),
+               np.ones(OUT_F, dtype=np.float16).view(np.uint16)) for _ in range(CPU_BUFS)]
+    x = rng.standard_normal(IN_F).astype(np.float16).view(np.uint16)
+    f = orc.RowMajorGemv(OUT_F, G)
+    orc.calibrate_threads(lambda: f(x, *layers[0]))
+    step = lambda: [f(x, c, cb, sc) for (c, cb, sc) in layers]
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    ms = dt / args.steps * 1e3
+    val = CPU_BUFS * algorithmic_bytes(IN_F, OUT_F) / (ms * 1e-3) / 1e9
+    cores = orc.num_threads()
+    sample = f"{args.steps} steps x {CPU_BUFS} GEMVs of {IN_F}x{OUT_F} (distinct code matrices), {cores} OpenMP threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj), CPU LUT path", "gemvs_per_step": CPU_BUFS},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "us_per_gemv": ms * 1e3 / CPU_BUFS,
+    }))
+
+
+def cpu_baseline(seconds: float = 12.0):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as orc
+    rng = np.random.default_rng(0)
+    G = IN_F // 8
+    bufs = 4
+    layers = [(rng.integers(0, 256, size=(OUT_F, G, 2), dtype=np.uint8).view(np.int8),
+               rng.standard_normal((2, 256, 8)).astype(np.float16).view(np.uint16)) for _ in range(bufs)]
+    x = rng.standard_normal(IN_F).astype(np.float16).view(np.uint16)
+    f = orc.RowMajorGemv(OUT_F, G)
+    orc.calibrate_threads(lambda: f(x, *layers[0]))
+    for c, cb in layers:
+        f(x, c, cb)
+    n, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds:
+        c, cb = layers[n % bufs]
+        f(x, c, cb)
+        n += 1
+    dt = time.perf_counter() - t0
+    cores = orc.num_threads()
+    return {"value": n * algorithmic_bytes(IN_F, OUT_F) / dt / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+            "us_per_gemv": dt / n * 1e6,
+            "sample": f"{n} GEMVs of {IN_F}x{OUT_F} over {bufs} distinct code matrices in {dt:.1f} s, {cores} OpenMP threads "
+                      "(oracle/lutvq_oracle.c orc_aqlm_gemv_rowmajor = numba_gemv_lut_ restated, race-free over rows)"}
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=100)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--tuning", default="", help="nw,pf,ctas_per_sm override for the GEMV kernel (experiments)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import rvv_lut_vq_b200 as pkg
+    from rvv_lut_vq_b200 import ops, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = pkg.lib()
+    if args.tuning:
+        nw, pf, cps = [int(v) for v in args.tuning.split(",")]
+        lib.lutvq_debug_set_gemv_tuning(nw, pf, cps)
+
+    # ---- synthetic layers: NBUF distinct code matrices (per rank: its own output-channel shard) ----
+    layers = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=1000 * rank + i, scales="ones") for i in range(NBUF)]
+    xs = torch.randn((NBUF, 1, IN_F), device=dev, dtype=torch.float16)
+    ys = torch.empty((NBUF, 1, OUT_F), device=dev, dtype=torch.float16)
+    gathered = torch.empty((NBUF, world * OUT_F), device=dev, dtype=torch.float16) if world > 1 else None
+    stream = torch.cuda.Stream(dev)
+
+    import ctypes
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+
+    def step_body():
+        ws = ops.workspace(dev, OUT_F, IN_F)
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for i, L in enumerate(layers):
+            pkg._lib.check(lib.lutvq_code2x8_matmat(P(xs[i]), P(L["codes"]), P(L["codebooks"]), P(L["scales"]), None,
+                                                    P(ys[i]), 1, OUT_F, IN_F, 0, P(ws), ws.numel(), st))
+            if world > 1:
+                dist.all_gather_into_tensor(gathered[i], ys[i, 0])
+
+    with torch.cuda.stream(stream):
+        step_body()
+        torch.cuda.synchronize()
+        graph = None
+        if world == 1:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream):
+                step_body()
+
+        def run_step():
+            if graph is not None:
+                graph.replay()
+            else:
+                step_body()
+
+        def timed(n_steps):
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(n_steps):
+                run_step()
+            e1.record(stream)
+            if world > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            if world > 1:
+                t = torch.tensor([ms], device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            return ms
+
+        for _ in range(args.warmup):
+            run_step()
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        ms_total = timed(args.steps)
+        # keep the GPU under the same load a little longer so the 100 ms sampler sees it
+        t_end = time.time() + 0.5
+        while rank == 0 and world == 1 and time.time() < t_end:
+            run_step()
+        torch.cuda.synchronize()
+        clocks = sampler.stop() if rank == 0 else None
+        ms_per_step = ms_total / args.steps
+        bytes_per_gemv = algorithmic_bytes(IN_F, OUT_F)
+        value = world * NBUF * bytes_per_gemv / (ms_per_step * 1e-3) / 1e9
+        us_per_gemv = ms_per_step * 1e3 / NBUF
+
+        # ---- e2e: host buffers through the reference-facing op ----
+        x_host = torch.randn((NBUF, 1, IN_F), dtype=torch.float16).pin_memory()
+        y_host = torch.empty((NBUF, 1, OUT_F), dtype=torch.float16).pin_memory()
+
+        def e2e_step():
+            for i, L in enumerate(layers):
+                xd = x_host[i].to(dev, non_blocking=True)
+                yd = ops.code2x8_matmat(xd, L["codes"], L["codebooks"], L["scales"], None)
+                if world > 1:
+                    dist.all_gather_into_tensor(gathered[i], yd[0])
+                y_host[i].copy_(yd, non_blocking=True)
+
+        e2e_steps = max(3, args.steps // 10)
+        for _ in range(3):
+            e2e_step()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        e2e_ms = e0.elapsed_time(e1) / e2e_steps
+        if world > 1:
+            t = torch.tensor([e2e_ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+        e2e_val = world * NBUF * bytes_per_gemv / (e2e_ms * 1e-3) / 1e9
+
+        # ---- the other shapes of the configs[1] sweep (not part of the timed region above) ----
+        sweep = []
+        if rank == 0 and world == 1 and not args.no_sweep:
+            peak, _ = measured_peak()
+            for (i_f, o_f) in synth.SWEEP_7B:
+                nb = max(8, int(280e6 // (o_f * i_f // 4)))
+                Ls = [synth.make_layer_torch(i_f, o_f, dev, seed=77 + k, scales="ones") for k in range(nb)]
+                xv = torch.randn((nb, 1, i_f), device=dev, dtype=torch.float16)
+                yv = torch.empty((nb, 1, o_f), device=dev, dtype=torch.float16)
+
+                def body():
+                    ws = ops.workspace(dev, o_f, i_f)
+                    st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+                    for k, L in enumerate(Ls):
+                        pkg._lib.check(lib.lutvq_code2x8_matmat(P(xv[k]), P(L["codes"]), P(L["codebooks"]), P(L["scales"]), None,
+                                                                P(yv[k]), 1, o_f, i_f, 0, P(ws), ws.numel(), st))
+                body()
+                torch.cuda.synchronize()
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    body()
+                for _ in range(5):
+                    g.replay()
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                reps = 50
+                a.record(stream)
+                for _ in range(reps):
+                    g.replay()
+                b.record(stream)
+                torch.cuda.synchronize()
+                us = a.elapsed_time(b) * 1e3 / (reps * nb)
+                gbps = algorithmic_bytes(i_f, o_f) / (us * 1e-6) / 1e9
+                sweep.append({"shape": f"{i_f}->{o_f}", "us": round(us, 3), "gbps": round(gbps, 1), "frac_of_measured_peak": round(gbps / peak, 4), "layers_in_ring": nb})
+                del Ls, g
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak()
+    achieved = bytes_per_gemv / (us_per_gemv * 1e-6) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get("lut_gemv_2x8_kernel_4096x11008_dram_bytes_per_launch")
+    except Exception:
+        pass
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj, BASELINE configs[1] headline shape)",
+                   "gemvs_per_step": NBUF, "cache": f"inputs larger than L2: {NBUF} distinct code matrices = {NBUF * OUT_F * IN_F // 4 / 1e6:.0f} MB per step",
+                   "launch": "one CUDA graph per step, programmatic dependent launch between GEMVs" if world == 1 else "eager launches + NCCL all_gather of output slices per GEMV",
+                   "sharding": "none" if world == 1 else f"output channels, {world} x {OUT_F} rows"},
+        "us_per_gemv": us_per_gemv,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * OUT_F * 2,
+                "us_per_gemv": e2e_ms * 1e3 / NBUF},
+        "gpu_launches": args.steps * NBUF,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "kernel": "lut_gemv_2x8_kernel", "algorithmic_bytes_per_launch": bytes_per_gemv, "peak_source": peak_src,
+                     "frac_of_nominal_8TBs": achieved / 8000.0},
+        "clocks": clocks,
+        "sweep": sweep,
+    }
+    if not args.no_cpu_baseline and world == 1:
+        out["cpu_baseline"] = cpu_baseline()
+    elif world == 1:
+        out["cpu_baseline"] = None
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,114 @@
+/*
+ * lutvq.h -- C-ABI of liblutvq.so: the B200-native (sm_100a) LUT vector-quantization hot path.
+ *
+ * Drop-in boundary for the reference's kernel entry points (paths relative to the reference tree
+ * wh-xu/RVV-LUT-VQ; "aqlm/" = benchmark/AQLM/inference_lib/src/aqlm/inference_kernels/):
+ *
+ *   lutvq_code2x8_matvec          <- code2x8_matvec_cuda<bf16>(A,B,C,codebook,prob_m,prob_k)   aqlm/cuda_kernel.cu:555-563
+ *                                    + code2x8_matvec(A,B,C,codebook,use_bfloat16)             aqlm/cuda_kernel.cpp:356-385
+ *   lutvq_code2x8_matmat          <- code2x8_matmat(input,codes,codebooks,scales,bias)         aqlm/cuda_kernel.cpp:387-421
+ *                                    + scale_bias_unflatten_output                             aqlm/cuda_kernel.cpp:95-111
+ *   lutvq_code2x8_dequant         <- code2x8_dequant_cuda(A,C,codebook,prob_m,prob_k,bf16)     aqlm/cuda_kernel.cu:622-629
+ *                                    + code2x8_dequant(codes,codebooks,scales)                 aqlm/cuda_kernel.cpp:423-448
+ *   lutvq_code2x8_matmat_dequant  <- code2x8_matmat_dequant(input,codes,codebooks,scales,bias) aqlm/cuda_kernel.cpp:450-484
+ *   lutvq_lut_build               <- VQ.compute_lut                                            vq_dataflow_sim/vq.py:280-285
+ *                                    (and the LUT line of numba_gemv_lut_, aqlm/numba_kernel.py:39-40)
+ *   lutvq_lut_gemv                <- VQ.compute_lut_gemm inner loops                           vq_dataflow_sim/vq.py:293-298
+ *                                    (and numba_gemv_lut_ gather loop, aqlm/numba_kernel.py:43-46)
+ *   lutvq_vq_dequantize           <- VQ.dequantize (per-subvector codebooks)                   vq_dataflow_sim/vq.py:269-278
+ *
+ * Conventions (differences from the reference launchers are deliberate and listed in INTEGRATION.md):
+ *   - every entry point is extern "C", takes plain device pointers + sizes, an explicit CUDA stream
+ *     (cudaStream_t passed as void*), never allocates, never synchronises the host, and runs on the
+ *     CURRENT device of the calling thread (the reference queries device 0, cuda_kernel.cu:486,497);
+ *   - returns 0 on success, a negative LUTVQ_E* code otherwise; lutvq_last_error() gives a thread-local
+ *     message.  There is no CPU fallback: without a CUDA device every compute call fails with LUTVQ_ECUDA;
+ *   - scratch memory is passed in (ws, ws_bytes); size it with lutvq_workspace_bytes().  A workspace must
+ *     be zero-filled once before first use (cudaMemset) and may then be reused by calls ON THE SAME STREAM;
+ *   - dtype is the storage/arithmetic type of x, codebooks, scales, bias, y (fp16 or bf16, the two types
+ *     cuda_kernel.cpp:9-25 accepts).  Codes are int8 holding unsigned 8-bit indices
+ *     (aqlm/../utils.py:24-31), layout [prob_m][prob_k/8][num_codebooks] exactly as QuantizedLinear.codes.
+ */
+#ifndef LUTVQ_H_
+#define LUTVQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LUTVQ_OK            0
+#define LUTVQ_EINVAL       (-1)   /* bad pointer / shape / alignment / workspace too small */
+#define LUTVQ_EUNSUPPORTED (-2)   /* valid request this build does not implement (e.g. dtype, codebook count) */
+#define LUTVQ_ECUDA        (-3)   /* CUDA runtime error (message carries cudaGetErrorString) */
+
+typedef enum { LUTVQ_F16 = 0, LUTVQ_BF16 = 1 } lutvq_dtype_t;
+
+/* flags for the *_ex entry points */
+#define LUTVQ_FLAG_LUT_FP16   1u  /* round LUT entries to fp16 (vq.py:285 semantics) before accumulation */
+#define LUTVQ_FLAG_NO_PDL     2u  /* do not use programmatic dependent launch for this call */
+
+/* lutvq_lut_build lut_mode */
+#define LUTVQ_LUT_VQPY_FP16   0   /* bit-exact vq.py: fp16 products, numpy pairwise fp32 sum, fp16 entries */
+#define LUTVQ_LUT_FP32        1   /* fp32 products and sum (numba semantics), fp32 entries */
+/* lutvq_lut_gemv acc_mode */
+#define LUTVQ_ACC_F64         0   /* float64 accumulate, float64 out (vq.py:297; exact for fp16 entries) */
+#define LUTVQ_ACC_F32         1   /* float32 accumulate, float32 out (numba_kernel.py:46) */
+
+const char* lutvq_last_error(void);
+int         lutvq_version(void);                     /* 10000*major + 100*minor + patch */
+/* fills what the launch heuristics see; any pointer may be NULL */
+int         lutvq_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin_bytes);
+
+/* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch). */
+size_t lutvq_workspace_bytes(int prob_m, int prob_k);
+
+/* y[prob_m] = W(codes, codebook) . x[prob_k]            (no scale, like Code2x8MatVec)
+ * codes    int8  [prob_m][prob_k/8][2]   (16-byte aligned rows: prob_k % 64 == 0, as the reference requires)
+ * x        dtype [prob_k]
+ * y        dtype [prob_m]
+ * codebook dtype [2][256][8]
+ * Arithmetic: fp32 LUT built with tensor-core MMAs, fp32 gather-accumulate, one rounding to dtype. */
+int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* codebook,
+                         int prob_m, int prob_k, int dtype, void* ws, size_t ws_bytes, void* stream);
+
+/* y[b][o] = round(round(acc) * scales[o]) + bias[o]   for b < batch  (reference epilogue order, fused)
+ * x dtype [batch][prob_k]; scales dtype [prob_m] (NULL = no scaling); bias dtype [prob_m] or NULL; y dtype [batch][prob_m]. */
+int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales,
+                         const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
+                         void* ws, size_t ws_bytes, void* stream);
+int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebooks, const void* scales,
+                            const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
+                            unsigned flags, void* ws, size_t ws_bytes, void* stream);
+
+/* W[o][8g+j] = codebook[0][c0(o,g)][j] + codebook[1][c1(o,g)][j]   (one RN add in dtype; bit-exact class)
+ * then, if scales != NULL, W[o][:] = round(W[o][:] * scales[o])     (cuda_kernel.cpp:445)
+ * W dtype [prob_m][prob_k] row-major. */
+int lutvq_code2x8_dequant(const void* codes, void* W, const void* codebook, const void* scales,
+                          int prob_m, int prob_k, int dtype, void* stream);
+
+/* Prefill path: y = x . W^T with W dequantized on the fly into shared memory and contracted on the
+ * tcgen05 tensor cores (fp32 accumulation in TMEM), then the matmat epilogue.  Same arguments as matmat. */
+int lutvq_code2x8_matmat_dequant(const void* x, const void* codes, const void* codebooks, const void* scales,
+                                 const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
+                                 void* ws, size_t ws_bytes, void* stream);
+
+/* Golden-model pair (vq.py layouts; unfused; used by the parity tests and for ncu of the two halves):
+ * lutvq_lut_build:  x dtype-fp16 [M*d]; codebook fp16 [M][N][K][d] or, if cb_shared, [N][K][d];
+ *                   lut [M][N][K] fp16 (LUTVQ_LUT_VQPY_FP16) or fp32 (LUTVQ_LUT_FP32).   d <= 32, K <= 65536.
+ * lutvq_lut_gemv:   codeword uint8 [d_out][M][N]; lut as above (lut_is_fp32 selects);
+ *                   out float64[d_out] (LUTVQ_ACC_F64) or float32[d_out] (LUTVQ_ACC_F32). */
+int lutvq_lut_build(const void* x, const void* codebook, void* lut, int M, int N, int K, int d,
+                    int cb_shared, int lut_mode, void* stream);
+int lutvq_lut_gemv(const void* codeword, const void* lut, void* out, int d_out, int M, int N, int K,
+                   int lut_is_fp32, int acc_mode, void* stream);
+/* W fp16 [d_out][M*d] = fp16( sum_n codebook[m][n][code[j][m][n]][:] ) with the sum in float64 (vq.py:276-278) */
+int lutvq_vq_dequantize(const void* codebook, const void* codeword, void* W, int d_out, int M, int N, int K,
+                        int d, int cb_shared, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LUTVQ_H_ */

@@ -58,6 +58,14 @@ int orc_num_threads(void) {
 #endif
 }
 
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* numpy's HALF_pairwise_sum for n <= 128 (numpy/_core/src/umath/loops_utils.h.src), which is
  * what `lut.sum(axis=-1)` in vq.py:285 runs per LUT entry: fp16 inputs widened to fp32,
  * 8 running lanes, then the fixed tree ((r0+r1)+(r2+r3))+((r4+r5)+(r6+r7)). */

@@ -61,6 +61,7 @@ def lib() -> ctypes.CDLL:
             "orc_scale_bias_epilogue": [P, P, P, I, I, I],
             "orc_unpack_codes": [P, ctypes.c_size_t, P],
             "orc_simd_lut_scalar": [P, P, P, I, U64, U64],
+            "orc_set_num_threads": [I],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)
@@ -77,6 +78,33 @@ def _p(a: Optional[np.ndarray]):
 
 def num_threads() -> int:
     return int(lib().orc_num_threads())
+
+
+def set_num_threads(n: int) -> None:
+    lib().orc_set_num_threads(int(n))
+
+
+def calibrate_threads(fn, max_threads: int = 0) -> int:
+    """Pick the OpenMP thread count (1, 2, 4, ... host cores) at which `fn()` runs fastest and leave it set.
+    (On oversubscribed VMs more threads can be slower; the baseline should be the best the host can do.)"""
+    import time
+    hi = max_threads or (os.cpu_count() or 1)
+    cands, t = [], 1
+    while t < hi:
+        cands.append(t)
+        t *= 2
+    cands.append(hi)
+    best, best_t = 1, float("inf")
+    for n in cands:
+        set_num_threads(n)
+        fn()
+        t0 = time.perf_counter()
+        fn(); fn()
+        dt = (time.perf_counter() - t0) / 2
+        if dt < best_t:
+            best, best_t = n, dt
+    set_num_threads(best)
+    return best
 
 
 # --------------------------------------------------------------------------------------------

@@ -1,0 +1,75 @@
+"""Loader for liblutvq.so (the C-ABI in include/lutvq.h).  There is NO fallback: if the library is missing
+or a call fails the error is raised -- nothing here can compute on the CPU."""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(CSRC, "liblutvq.so")
+
+LUTVQ_OK, LUTVQ_EINVAL, LUTVQ_EUNSUPPORTED, LUTVQ_ECUDA = 0, -1, -2, -3
+LUTVQ_F16, LUTVQ_BF16 = 0, 1
+FLAG_LUT_FP16, FLAG_NO_PDL = 1, 2
+LUT_VQPY_FP16, LUT_FP32 = 0, 1
+ACC_F64, ACC_F32 = 0, 1
+
+P, I, U, SZ = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/lutvq.h declares (tests/test_abi.py checks)
+SIGNATURES = {
+    "lutvq_last_error": (ctypes.c_char_p, []),
+    "lutvq_version": (I, []),
+    "lutvq_device_info": (I, [P, P, P, P]),
+    "lutvq_workspace_bytes": (SZ, [I, I]),
+    "lutvq_code2x8_matvec": (I, [P, P, P, P, I, I, I, P, SZ, P]),
+    "lutvq_code2x8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
+    "lutvq_code2x8_matmat_ex": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),
+    "lutvq_code2x8_dequant": (I, [P, P, P, P, I, I, I, P]),
+    "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
+    "lutvq_lut_build": (I, [P, P, P, I, I, I, I, I, I, P]),
+    "lutvq_lut_gemv": (I, [P, P, P, I, I, I, I, I, I, P]),
+    "lutvq_vq_dequantize": (I, [P, P, P, I, I, I, I, I, I, P]),
+}
+DEBUG_SIGNATURES = {
+    "lutvq_debug_set_gemv_tuning": (None, [I, I, I]),
+    "lutvq_debug_get_gemv_plan": (None, [I, I, P, P, P]),
+}
+
+
+class LutvqError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"liblutvq error {code}: {msg}")
+        self.code = code
+
+
+def build(force: bool = False) -> str:
+    """Compile liblutvq.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    cmd = ["make", "-C", CSRC, "-j8"] + (["-B"] if force else [])
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)")
+        _lib = ctypes.CDLL(LIB_PATH)
+        for table in (SIGNATURES, DEBUG_SIGNATURES):
+            for name, (res, args) in table.items():
+                fn = getattr(_lib, name)
+                fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise LutvqError(rc, lib().lutvq_last_error().decode())

@@ -1,0 +1,185 @@
+// api.cu -- the extern "C" surface of liblutvq.so (include/lutvq.h): argument validation, error strings,
+// device-info cache, dispatch to the kernel launchers.  No torch types, no allocation, no host sync.
+#include "common.cuh"
+
+#include <mutex>
+#include <string.h>
+
+namespace lutvq {
+
+// launchers (gemv_lut.cu, dequant.cu, vq_golden.cu, gemm_tc.cu)
+int gemv_2x8_launch(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
+                    const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
+                    cudaStream_t stream);
+size_t gemv_workspace_bytes(int O, int G);
+void gemv_set_tuning(int nw, int pf, int ctas_per_sm);
+void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk);
+int code2x8_dequant_launch(const void* codes, void* W, const void* codebook, const void* scales, int O, int I,
+                           int dtype, cudaStream_t stream);
+int lut_build_launch(const void* x, const void* codebook, void* lut, int M, int N, int K, int d, int cb_shared,
+                     int lut_mode, cudaStream_t stream);
+int lut_gemv_launch(const void* codeword, const void* lut, void* out, int d_out, int M, int N, int K,
+                    int lut_is_fp32, int acc_mode, cudaStream_t stream);
+int vq_dequantize_launch(const void* codebook, const void* codeword, void* W, int d_out, int M, int N, int K, int d,
+                         int cb_shared, cudaStream_t stream);
+int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codebooks, const void* scales,
+                           const void* bias, void* y, int batch, int O, int I, int dtype, void* ws, size_t ws_bytes,
+                           cudaStream_t stream);
+size_t gemm_workspace_bytes(int O, int I);
+
+char* err_buf() {
+    static thread_local char buf[512] = "";
+    return buf;
+}
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err_buf(), 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int get_device_info(DeviceInfo* out) {
+    static std::mutex mu;
+    static DeviceInfo cache[64];
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return fail(LUTVQ_ECUDA, "no usable CUDA device (%s); liblutvq has no CPU fallback", cudaGetErrorString(e));
+    if (dev < 0 || dev >= 64) return fail(LUTVQ_ECUDA, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    DeviceInfo& c = cache[dev];
+    if (c.device != dev) {
+        int v = 0;
+        LUTVQ_CUDA_OK(cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, dev));
+        LUTVQ_CUDA_OK(cudaDeviceGetAttribute(&c.cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+        LUTVQ_CUDA_OK(cudaDeviceGetAttribute(&c.cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+        LUTVQ_CUDA_OK(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        c.smem_optin = (size_t)v;
+        if (c.cc_major != 10)
+            return fail(LUTVQ_EUNSUPPORTED, "liblutvq is built for sm_100a only; device %d is sm_%d%d", dev, c.cc_major, c.cc_minor);
+        c.device = dev;
+    }
+    *out = c;
+    return LUTVQ_OK;
+}
+
+static int check_2x8_common(const void* codes, const void* codebook, int prob_m, int prob_k, int dtype) {
+    LUTVQ_REQUIRE(codes && codebook, "null codes/codebook pointer");
+    LUTVQ_REQUIRE(prob_m > 0 && prob_k > 0, "bad shape prob_m=%d prob_k=%d", prob_m, prob_k);
+    LUTVQ_REQUIRE(prob_k % 64 == 0, "prob_k=%d must be a multiple of 64 (16-byte code rows, as cuda_kernel.cu:154 assumes)", prob_k);
+    LUTVQ_REQUIRE(aligned16(codes) && aligned16(codebook), "codes and codebook must be 16-byte aligned");
+    if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16)
+        return fail(LUTVQ_EUNSUPPORTED, "AQLM kernels only support float16 (0) and bfloat16 (1); got dtype %d", dtype);
+    return LUTVQ_OK;
+}
+
+}  // namespace lutvq
+
+using namespace lutvq;
+
+extern "C" {
+
+const char* lutvq_last_error(void) { return err_buf(); }
+int lutvq_version(void) { return 10000 * 0 + 100 * 1 + 0; }
+
+int lutvq_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin_bytes) {
+    DeviceInfo di;
+    if (int rc = get_device_info(&di)) return rc;
+    if (sm_count) *sm_count = di.sm_count;
+    if (cc_major) *cc_major = di.cc_major;
+    if (cc_minor) *cc_minor = di.cc_minor;
+    if (smem_optin_bytes) *smem_optin_bytes = di.smem_optin;
+    return LUTVQ_OK;
+}
+
+size_t lutvq_workspace_bytes(int prob_m, int prob_k) {
+    if (prob_m <= 0 || prob_k <= 0) return 0;
+    size_t a = gemv_workspace_bytes(prob_m, prob_k / 8);
+    size_t b = gemm_workspace_bytes(prob_m, prob_k);
+    return a > b ? a : b;
+}
+
+int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* codebook, int prob_m, int prob_k,
+                         int dtype, void* ws, size_t ws_bytes, void* stream) {
+    if (int rc = check_2x8_common(codes, codebook, prob_m, prob_k, dtype)) return rc;
+    LUTVQ_REQUIRE(x && y, "null x/y pointer");
+    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
+    return gemv_2x8_launch(codes, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, 0u, ws, ws_bytes,
+                           static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebooks, const void* scales,
+                            const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, unsigned flags,
+                            void* ws, size_t ws_bytes, void* stream) {
+    if (int rc = check_2x8_common(codes, codebooks, prob_m, prob_k, dtype)) return rc;
+    LUTVQ_REQUIRE(x && y, "null x/y pointer");
+    LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
+    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
+    // cuda_kernel.cpp:404-414 loops the matvec over the flattened batch rows; so do we (one fused launch per row,
+    // scale/bias folded into the kernel's epilogue instead of three extra elementwise kernels).
+    const size_t esz = 2;
+    for (int b = 0; b < batch; ++b) {
+        const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * esz;
+        void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * esz;
+        if (int rc = gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, flags, ws, ws_bytes,
+                                     static_cast<cudaStream_t>(stream)))
+            return rc;
+    }
+    return LUTVQ_OK;
+}
+
+int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,
+                         void* y, int batch, int prob_m, int prob_k, int dtype, void* ws, size_t ws_bytes, void* stream) {
+    return lutvq_code2x8_matmat_ex(x, codes, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, 0u, ws, ws_bytes, stream);
+}
+
+int lutvq_code2x8_dequant(const void* codes, void* W, const void* codebook, const void* scales, int prob_m, int prob_k,
+                          int dtype, void* stream) {
+    if (int rc = check_2x8_common(codes, codebook, prob_m, prob_k, dtype)) return rc;
+    LUTVQ_REQUIRE(W && aligned16(W), "W must be non-null and 16-byte aligned");
+    return code2x8_dequant_launch(codes, W, codebook, scales, prob_m, prob_k, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_code2x8_matmat_dequant(const void* x, const void* codes, const void* codebooks, const void* scales,
+                                 const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, void* ws,
+                                 size_t ws_bytes, void* stream) {
+    if (int rc = check_2x8_common(codes, codebooks, prob_m, prob_k, dtype)) return rc;
+    LUTVQ_REQUIRE(x && y, "null x/y pointer");
+    LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
+    LUTVQ_REQUIRE(aligned16(x) && aligned16(y), "x and y must be 16-byte aligned");
+    if (batch == 0) return LUTVQ_OK;
+    return gemm_dequant_tc_launch(x, codes, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, ws, ws_bytes,
+                                  static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_lut_build(const void* x, const void* codebook, void* lut, int M, int N, int K, int d, int cb_shared,
+                    int lut_mode, void* stream) {
+    LUTVQ_REQUIRE(x && codebook && lut, "null pointer");
+    LUTVQ_REQUIRE(M > 0 && N > 0 && K > 0 && d > 0 && d <= 32 && K <= 65536, "bad shape M=%d N=%d K=%d d=%d", M, N, K, d);
+    LUTVQ_REQUIRE(lut_mode == LUTVQ_LUT_VQPY_FP16 || lut_mode == LUTVQ_LUT_FP32, "bad lut_mode %d", lut_mode);
+    return lut_build_launch(x, codebook, lut, M, N, K, d, cb_shared, lut_mode, static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_lut_gemv(const void* codeword, const void* lut, void* out, int d_out, int M, int N, int K, int lut_is_fp32,
+                   int acc_mode, void* stream) {
+    LUTVQ_REQUIRE(codeword && lut && out, "null pointer");
+    LUTVQ_REQUIRE(d_out > 0 && M > 0 && N > 0 && K > 0 && K <= 256, "bad shape d_out=%d M=%d N=%d K=%d (uint8 codes: K<=256)", d_out, M, N, K);
+    LUTVQ_REQUIRE(acc_mode == LUTVQ_ACC_F64 || acc_mode == LUTVQ_ACC_F32, "bad acc_mode %d", acc_mode);
+    return lut_gemv_launch(codeword, lut, out, d_out, M, N, K, lut_is_fp32, acc_mode, static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_vq_dequantize(const void* codebook, const void* codeword, void* W, int d_out, int M, int N, int K, int d,
+                        int cb_shared, void* stream) {
+    LUTVQ_REQUIRE(codebook && codeword && W, "null pointer");
+    LUTVQ_REQUIRE(d_out > 0 && M > 0 && N > 0 && K > 0 && K <= 256 && d > 0, "bad shape");
+    return vq_dequantize_launch(codebook, codeword, W, d_out, M, N, K, d, cb_shared, static_cast<cudaStream_t>(stream));
+}
+
+// ---- not part of the public header: tuning hooks used by bench.py's sweep and the tests ----
+void lutvq_debug_set_gemv_tuning(int nw, int pf, int ctas_per_sm) { gemv_set_tuning(nw, pf, ctas_per_sm); }
+void lutvq_debug_get_gemv_plan(int prob_m, int prob_k, int* n_k, int* n_chunks, int* rows_per_chunk) {
+    gemv_get_plan(prob_m, prob_k, n_k, n_chunks, rows_per_chunk);
+}
+
+}  // extern "C"

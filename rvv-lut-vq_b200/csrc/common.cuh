@@ -1,0 +1,97 @@
+// common.cuh -- shared helpers for liblutvq.so (error reporting, dtype traits, small PTX wrappers)
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+
+#include "../../include/lutvq.h"
+
+namespace lutvq {
+
+// ---- thread-local error string (lutvq_last_error) ----
+char* err_buf();
+int   fail(int code, const char* fmt, ...);
+
+#define LUTVQ_CUDA_OK(expr)                                                                     \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess)                                                                  \
+            return ::lutvq::fail(LUTVQ_ECUDA, "%s failed: %s (%s:%d)", #expr,                   \
+                                 cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+    } while (0)
+
+#define LUTVQ_REQUIRE(cond, ...)                                                                \
+    do {                                                                                        \
+        if (!(cond)) return ::lutvq::fail(LUTVQ_EINVAL, __VA_ARGS__);                           \
+    } while (0)
+
+struct DeviceInfo {
+    int device = -1, sm_count = 0, cc_major = 0, cc_minor = 0;
+    size_t smem_optin = 0;
+};
+// Cached per device; queries the CURRENT device (not device 0 as cuda_kernel.cu:486,497 does).
+int get_device_info(DeviceInfo* out);
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- dtype traits: storage type <-> float, one RN op in the storage type ----
+template <int DT> struct Dtype;
+template <> struct Dtype<LUTVQ_F16> {
+    using T = __half;
+    using T2 = __half2;
+    static __device__ __forceinline__ float to_f(T v) { return __half2float(v); }
+    static __device__ __forceinline__ T from_f(float v) { return __float2half_rn(v); }
+    static __device__ __forceinline__ T mul(T a, T b) { return __hmul(a, b); }
+    static __device__ __forceinline__ T add(T a, T b) { return __hadd(a, b); }
+    static __device__ __forceinline__ T2 add2(T2 a, T2 b) { return __hadd2(a, b); }
+    static __device__ __forceinline__ T2 mul2(T2 a, T2 b) { return __hmul2(a, b); }
+    static __device__ __forceinline__ T2 dup(T a) { return __half2half2(a); }
+};
+template <> struct Dtype<LUTVQ_BF16> {
+    using T = __nv_bfloat16;
+    using T2 = __nv_bfloat162;
+    static __device__ __forceinline__ float to_f(T v) { return __bfloat162float(v); }
+    static __device__ __forceinline__ T from_f(float v) { return __float2bfloat16_rn(v); }
+    static __device__ __forceinline__ T mul(T a, T b) { return __hmul(a, b); }
+    static __device__ __forceinline__ T add(T a, T b) { return __hadd(a, b); }
+    static __device__ __forceinline__ T2 add2(T2 a, T2 b) { return __hadd2(a, b); }
+    static __device__ __forceinline__ T2 mul2(T2 a, T2 b) { return __hmul2(a, b); }
+    static __device__ __forceinline__ T2 dup(T a) { return __bfloat162bfloat162(a); }
+};
+
+// ---- PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+// streaming 64-bit global load that does not allocate in L1 (codes are read exactly once)
+__device__ __forceinline__ uint2 ldg_stream_u64(const void* p) {
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint4 ldg_stream_u128(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// L2-coherent load (bypasses L1): for data written by other CTAs of the same grid
+__device__ __forceinline__ float ldcg_f32(const float* p) {
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldcg_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+// programmatic dependent launch (no-ops when the launch did not opt in)
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+}  // namespace lutvq

@@ -1,0 +1,162 @@
+"""Torch-tensor front end of liblutvq.so with the reference's operator names, argument order and error
+behaviour (reference: benchmark/AQLM/inference_lib/src/aqlm/inference_kernels/cuda_kernel.cpp:356-484 and
+the torch.library schema `(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, Tensor bias) -> Tensor`
+in cuda_kernel.py:13-132).  Torch is plumbing only: tensors supply device pointers and the current stream;
+every op is one or more launches of our own sm_100a kernels through the C-ABI.  No CPU path exists."""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import check, lib
+
+_DT = {torch.float16: _lib.LUTVQ_F16, torch.bfloat16: _lib.LUTVQ_BF16}
+_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def check_use_bfloat16(t: torch.Tensor) -> int:
+    """cuda_kernel.cpp:9-25: only fp16 / bf16; anything else is NotImplementedError."""
+    if t.dtype not in _DT:
+        raise NotImplementedError(
+            f"AQLM CUDA kernels only support float16 and bfloat16. Got {t.dtype}. "
+            "Please specify the correct `torch_dtype` when loading the model.")
+    return _DT[t.dtype]
+
+
+def _require_cuda(*tensors: Optional[torch.Tensor]) -> torch.device:
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("lutvq ops run on CUDA tensors only (there is no CPU fallback)")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError(f"tensors on different devices: {dev} vs {t.device}")
+    return dev
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream(dev: torch.device) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def workspace(dev: torch.device, prob_m: int, prob_k: int) -> torch.Tensor:
+    """Zero-initialised scratch, cached per (device, stream) as include/lutvq.h requires."""
+    need = int(lib().lutvq_workspace_bytes(prob_m, prob_k))
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    return ws
+
+
+def _flat_scales(scales: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    return None if scales is None else scales.reshape(-1).contiguous()
+
+
+def code2x8_matvec(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, codebook: torch.Tensor, use_bfloat16: bool) -> None:
+    """cuda_kernel.cpp:356-385: C[prob_m] = W(A) . B[prob_k], written into the caller's C."""
+    dev = _require_cuda(A, B, C, codebook)
+    prob_m, prob_k = C.size(0), B.size(0)
+    with torch.cuda.device(dev):
+        ws = workspace(dev, prob_m, prob_k)
+        check(lib().lutvq_code2x8_matvec(_ptr(A), _ptr(B), _ptr(C), _ptr(codebook), prob_m, prob_k,
+                                         _lib.LUTVQ_BF16 if use_bfloat16 else _lib.LUTVQ_F16,
+                                         _ptr(ws), ws.numel(), _stream(dev)))
+
+
+def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional[int] = None) -> torch.Tensor:
+    dtype = check_use_bfloat16(input)
+    dev = _require_cuda(input, codes, codebooks, scales, bias)
+    out_features = codes.size(0) * codebooks.size(2)
+    in_features = input.size(-1)
+    flat_input = input.reshape(-1, in_features).contiguous()
+    batch = flat_input.size(0)
+    flat_output = torch.empty((batch, out_features), dtype=input.dtype, device=dev)
+    codes_c, cb_c = codes.contiguous(), codebooks.contiguous()
+    sc, bi = _flat_scales(scales), (None if bias is None else bias.contiguous())
+    with torch.cuda.device(dev):
+        ws = workspace(dev, out_features, in_features)
+        fn = getattr(lib(), fn_name)
+        if flags is None:
+            rc = fn(_ptr(flat_input), _ptr(codes_c), _ptr(cb_c), _ptr(sc), _ptr(bi), _ptr(flat_output), batch,
+                    out_features, in_features, dtype, _ptr(ws), ws.numel(), _stream(dev))
+        else:
+            rc = fn(_ptr(flat_input), _ptr(codes_c), _ptr(cb_c), _ptr(sc), _ptr(bi), _ptr(flat_output), batch,
+                    out_features, in_features, dtype, flags, _ptr(ws), ws.numel(), _stream(dev))
+        check(rc)
+    return flat_output.reshape(tuple(input.shape[:-1]) + (out_features,))
+
+
+def code2x8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False) -> torch.Tensor:
+    """cuda_kernel.cpp:387-421 (+ epilogue :95-111): the decode / small-batch path (fused LUT-GEMV per row)."""
+    if lut_fp16:
+        return _matmat("lutvq_code2x8_matmat_ex", input, codes, codebooks, scales, bias, _lib.FLAG_LUT_FP16)
+    return _matmat("lutvq_code2x8_matmat", input, codes, codebooks, scales, bias)
+
+
+def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                           bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """cuda_kernel.cpp:450-484: the prefill path (dequant fused into a tcgen05 GEMM instead of dequant + cuBLAS)."""
+    return _matmat("lutvq_code2x8_matmat_dequant", input, codes, codebooks, scales, bias)
+
+
+def code2x8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:
+    """cuda_kernel.cpp:423-448: W[out, in] = (cb0[c0] + cb1[c1]) * scales, storage dtype of the codebooks."""
+    dtype = check_use_bfloat16(codebooks)
+    dev = _require_cuda(codes, codebooks, scales)
+    in_features = codes.size(1) * 8
+    out_features = codes.size(0)
+    weight = torch.empty((out_features, in_features), dtype=codebooks.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code2x8_dequant(_ptr(codes.contiguous()), _ptr(weight), _ptr(codebooks.contiguous()),
+                                          _ptr(_flat_scales(scales)), out_features, in_features, dtype, _stream(dev)))
+    return weight
+
+
+# ---- golden-model pair (vq.py layouts) ----
+def lut_build(x: torch.Tensor, codebook: torch.Tensor, M: int, lut_mode: int = _lib.LUT_VQPY_FP16) -> torch.Tensor:
+    """VQ.compute_lut (vq.py:280-285).  x fp16 [M*d]; codebook fp16 (M,N,K,d) or shared (N,K,d) -> lut (M,N,K)."""
+    dev = _require_cuda(x, codebook)
+    shared = codebook.dim() == 3
+    N, K, d = codebook.shape[-3:]
+    lut = torch.empty((M, N, K), dtype=torch.float16 if lut_mode == _lib.LUT_VQPY_FP16 else torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_lut_build(_ptr(x.contiguous()), _ptr(codebook.contiguous()), _ptr(lut), M, N, K, d,
+                                    int(shared), lut_mode, _stream(dev)))
+    return lut
+
+
+def lut_gemv(codeword: torch.Tensor, lut: torch.Tensor, acc_mode: int = _lib.ACC_F64) -> torch.Tensor:
+    """VQ.compute_lut_gemm inner loops (vq.py:293-298).  codeword uint8 (d_out,M,N); lut (M,N,K) fp16|fp32."""
+    dev = _require_cuda(codeword, lut)
+    d_out, M, N = codeword.shape
+    K = lut.shape[-1]
+    out = torch.empty(d_out, dtype=torch.float64 if acc_mode == _lib.ACC_F64 else torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_lut_gemv(_ptr(codeword.contiguous()), _ptr(lut.contiguous()), _ptr(out), d_out, M, N, K,
+                                   int(lut.dtype == torch.float32), acc_mode, _stream(dev)))
+    return out
+
+
+def vq_dequantize(codebook: torch.Tensor, codeword: torch.Tensor, M: int) -> torch.Tensor:
+    """VQ.dequantize (vq.py:269-278) -> fp16 (d_out, M*d)."""
+    dev = _require_cuda(codebook, codeword)
+    shared = codebook.dim() == 3
+    N, K, d = codebook.shape[-3:]
+    d_out = codeword.shape[0]
+    W = torch.empty((d_out, M * d), dtype=torch.float16, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_vq_dequantize(_ptr(codebook.contiguous()), _ptr(codeword.contiguous()), _ptr(W), d_out, M, N,
+                                        K, d, int(shared), _stream(dev)))
+    return W

@@ -1,0 +1,297 @@
+"""GPU parity: the CUDA path (through the C-ABI / the reference-mirroring ops) against the CPU oracle and
+the committed golden vectors.  Bit-exact for index / dequantize / golden-model LUT work; stated tolerances
+for fp16/fp32 accumulation (max|y - y64| / max|y64| <= 1e-3)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+TOL_GEMV = 1e-3          # north_star: max rel err 1e-3 vs the exact (float64) evaluation
+VQ_CASES = ["vq_d128_m16_n2_k256", "vq_d64_m8_n1_k256", "vq_d64_m8_n4_k256", "vq_d96_m6_n2_k256_d16"]
+AQLM_2X8 = ["aqlm_2x8_i256_o96", "aqlm_2x8_i1024_o64"]
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import rvv_lut_vq_b200 as r
+    assert os.path.exists(r._lib.LIB_PATH), "liblutvq.so must be prebuilt in-tree (no fallback)"
+    assert torch.cuda.is_available()
+    return r
+
+
+@pytest.fixture(scope="module")
+def ops(pkg):
+    from rvv_lut_vq_b200 import ops
+    return ops
+
+
+def cu(a, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    return t if dtype is None else t.to(dtype)
+
+
+def bits(t: torch.Tensor) -> np.ndarray:
+    return t.detach().cpu().contiguous().view(torch.int16).numpy().view(np.uint16)
+
+
+def _load(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name + ".npz")))
+
+
+def expected_epilogue(orc, acc64, scales16, bias16, dtype=0):
+    """reference rounding order on the exact accumulator: round -> *scale -> +bias (cuda_kernel.cpp:95-111)"""
+    y = orc.to_bits(acc64.astype(np.float32), dtype)
+    return orc.c_scale_bias_epilogue(y.reshape(1, -1), scales16, bias16, dtype).reshape(-1)
+
+
+def rel_err(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    return np.abs(got - want).max() / max(np.abs(want).max(), 1e-30)
+
+
+# ------------------------------------------------------------------ golden model (vq.py), bit-exact
+@pytest.mark.parametrize("name", VQ_CASES)
+def test_vqpy_golden_bit_exact(pkg, ops, golden_dir, name):
+    g = _load(golden_dir, name)
+    D, M, N, K, d_out, B, _ = [int(v) for v in g["cfg"]]
+    cb, cw = cu(g["codebook"]), cu(g["codeword"])
+    outs = []
+    for b in range(B):
+        lut = ops.lut_build(cu(g["x"][b]), cb, M)                       # VQ.compute_lut
+        outs.append(ops.lut_gemv(cw, lut).cpu().numpy())                # VQ.compute_lut_gemm (float64)
+    assert np.array_equal(bits(lut), g["lut_last"].view(np.uint16)), "LUT entries differ from vq.py"
+    assert np.array_equal(np.stack(outs), g["out_lut_gemm"]), "LUT-GEMV differs from vq.py"
+    W = ops.vq_dequantize(cb, cw, M)                                    # VQ.dequantize
+    assert np.array_equal(bits(W), g["weight_mat"].view(np.uint16)), "dequantized weights differ from vq.py"
+
+
+def test_vqpy_shared_codebook_matches_oracle(pkg, ops, orc):
+    """AQLM is vq.py with the codebook broadcast over subvectors: config-1 shape, seeded."""
+    rng = np.random.default_rng(42)
+    M, N, K, d, d_out = 512, 2, 256, 8, 256
+    cb = rng.standard_normal((N, K, d)).astype(np.float16)
+    cw = rng.integers(0, K, size=(d_out, M, N), dtype=np.uint8)
+    x = rng.standard_normal(M * d).astype(np.float16)
+    lut = ops.lut_build(cu(x), cu(cb), M)
+    want_lut = orc.c_lut_build_vqpy(x, cb, M)
+    assert np.array_equal(bits(lut), want_lut.view(np.uint16))
+    out = ops.lut_gemv(cu(cw), lut).cpu().numpy()
+    assert np.array_equal(out, orc.c_lut_gemv_f64(want_lut, cw))
+    W = ops.vq_dequantize(cu(cb), cu(cw), M)
+    assert np.array_equal(bits(W), orc.c_dequantize(cb, cw, None, M))
+
+
+# ------------------------------------------------------------------ AQLM goldens (numba / _dequantize_weight)
+@pytest.mark.parametrize("name", AQLM_2X8)
+def test_aqlm_golden_dequant_bit_exact(pkg, ops, golden_dir, name):
+    g = _load(golden_dir, name)
+    codes, cb, sc = cu(g["codes"]), cu(g["codebooks"], torch.float16), cu(g["scales"], torch.float16)
+    W = ops.code2x8_dequant(codes, cb, None)
+    assert np.array_equal(bits(W), g["weight_f16_noscale"].astype(np.float16).view(np.uint16))
+    Ws = ops.code2x8_dequant(codes, cb, sc)
+    assert np.array_equal(bits(Ws), g["weight_f16_scaled"].astype(np.float16).view(np.uint16))
+
+
+@pytest.mark.parametrize("name", AQLM_2X8)
+def test_aqlm_golden_matmat(pkg, ops, golden_dir, name):
+    g = _load(golden_dir, name)
+    wb = int(g["cfg"][5])
+    x = cu(g["x"], torch.float16)
+    codes, cb, sc = cu(g["codes"]), cu(g["codebooks"], torch.float16), cu(g["scales"], torch.float16)
+    bias = cu(g["bias"], torch.float16) if wb else None
+    y = ops.code2x8_matmat(x, codes, cb, sc, bias).float().cpu().numpy()
+    assert y.shape == g["y_numba"].shape
+    assert rel_err(y, g["y_numba"]) <= TOL_GEMV                       # vs numba_gemm_lut (fp32) run by the reference
+    # unfused pair in numba's own arithmetic: fp32 LUT, fp32 sequential gather -> tight agreement
+    from rvv_lut_vq_b200 import _lib
+    G = g["codes"].shape[1]
+    lut = ops.lut_build(x[0], cb.reshape(2, 256, 8), G, lut_mode=_lib.LUT_FP32)
+    acc = ops.lut_gemv(codes.view(torch.uint8), lut, acc_mode=_lib.ACC_F32).cpu().numpy()
+    want = (g["y_numba"][0] - (g["bias"] if wb else 0)) / g["scales"].reshape(-1)
+    assert rel_err(acc, want) <= 5e-6
+
+
+# ------------------------------------------------------------------ seeded cases vs the oracle
+CASES = [
+    # (in, out, scales, bias, batch)        what it covers
+    (64, 32, "randn", False, 1),            # single partial k-slice (8 groups), one row set
+    (256, 96, "randn", True, 2),            # n_k == 1 direct-epilogue path
+    (512, 40, "ones", False, 1),            # out not a multiple of 8: clamped rows
+    (2048, 1000, "randn", True, 1),         # out not a multiple of 32, split-k reduce
+    (4096, 4096, "randn", False, 1),        # BASELINE configs[0] shape
+    (11008, 256, "randn", True, 3),         # 43 k-slices
+    (1088, 300, "randn", False, 1),         # G = 136: last k-slice is partial (8 of 32 groups)
+]
+
+
+@pytest.mark.parametrize("I,O,scales,bias,batch", CASES)
+def test_matmat_vs_oracle(pkg, ops, orc, I, O, scales, bias, batch):
+    from rvv_lut_vq_b200 import synth
+    L = synth.make_layer_np(I, O, seed=I + O, scales=scales, bias=bias, batch=batch)
+    y = ops.code2x8_matmat(cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]),
+                           None if L["bias"] is None else cu(L["bias"]))
+    assert y.shape == (batch, O) and y.dtype == torch.float16
+    for b in range(batch):
+        y64 = orc.c_aqlm_gemv_f64(L["x"][b], L["codes"], L["codebooks"])
+        s64 = L["scales"].reshape(-1).astype(np.float64)
+        want64 = y64 * s64 + (0 if L["bias"] is None else L["bias"].astype(np.float64))
+        got = y[b].float().cpu().numpy()
+        assert rel_err(got, want64) <= TOL_GEMV
+        # and against the fp32-accumulate port with the reference's epilogue rounding: at most 1 fp16 ulp apart
+        port = orc.c_aqlm_gemv_rowmajor(L["x"][b], L["codes"], L["codebooks"], L["scales"], L["bias"])
+        ulp = np.abs(bits(y[b]).astype(np.int64) - port.astype(np.int64))
+        ulp = np.minimum(ulp, np.abs(ulp - 0x8000))                   # +-0 crossing
+        assert (ulp <= 2).mean() > 0.999, f"fp16 outputs differ by more than 2 ulp in {(ulp > 2).mean():.4%} of rows"
+
+
+def test_matmat_bf16(pkg, ops, orc):
+    from rvv_lut_vq_b200 import synth
+    I, O = 1024, 512
+    L = synth.make_layer_np(I, O, seed=5, scales="randn", bias=True)
+    tb = lambda a: cu(a.astype(np.float32)).to(torch.bfloat16)
+    x, cb, sc, bi = tb(L["x"]), tb(L["codebooks"]), tb(L["scales"]), tb(L["bias"])
+    y = ops.code2x8_matmat(x, cu(L["codes"]), cb, sc, bi)
+    assert y.dtype == torch.bfloat16
+    y64 = orc.c_aqlm_gemv_f64(bits(x[0]), L["codes"], bits(cb), dtype=1)
+    want = y64 * sc.float().cpu().numpy().reshape(-1) + bi.float().cpu().numpy()
+    assert rel_err(y[0].float().cpu().numpy(), want) <= 8e-3          # bf16 output rounding: 2^-8
+    W = ops.code2x8_dequant(cu(L["codes"]), cb, sc)
+    assert np.array_equal(bits(W), orc.c_dequantize(bits(cb).reshape(2, 256, 8), L["idx"], bits(sc), I // 8, dtype=1))
+
+
+def test_lut_fp16_flag_matches_vqpy_semantics(pkg, ops, orc):
+    """LUTVQ_FLAG_LUT_FP16: fused GEMV with LUT entries rounded to fp16 == vq.py's LUT-GEMV within tolerance."""
+    from rvv_lut_vq_b200 import synth
+    I, O = 4096, 512
+    L = synth.make_layer_np(I, O, seed=9, scales="ones")
+    y = ops.code2x8_matmat(cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]), None, lut_fp16=True)
+    lut = orc.c_lut_build_vqpy(L["x"][0], L["codebooks"].reshape(2, 256, 8), I // 8)
+    want = orc.c_lut_gemv_f64(lut, L["idx"])
+    assert rel_err(y[0].float().cpu().numpy(), want) <= TOL_GEMV
+
+
+# ------------------------------------------------------------------ full BASELINE sizes
+@pytest.mark.parametrize("I,O", [(4096, 4096), (4096, 11008), (11008, 4096)])
+def test_full_size_sweep(pkg, ops, orc, I, O):
+    """BASELINE configs[1]: the three Llama-2-7B shapes, checked directly against the oracle (it is fast enough)
+    plus size-independent properties: determinism, row-permutation equivariance, dequant round trip, zero input."""
+    from rvv_lut_vq_b200 import synth
+    L = synth.make_layer_np(I, O, seed=1, scales="randn", bias=False)
+    x, codes, cb, sc = cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"])
+    y = ops.code2x8_matmat(x, codes, cb, sc, None)
+    y64 = orc.c_aqlm_gemv_f64(L["x"][0], L["codes"], L["codebooks"]) * L["scales"].reshape(-1).astype(np.float64)
+    assert rel_err(y[0].float().cpu().numpy(), y64) <= TOL_GEMV
+    # deterministic: fixed-order split-k reduction
+    y2 = ops.code2x8_matmat(x, codes, cb, sc, None)
+    assert torch.equal(y, y2)
+    # permuting output rows of (codes, scales) permutes y bit-for-bit
+    perm = torch.randperm(O, device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+    yp = ops.code2x8_matmat(x, codes[perm].contiguous(), cb, sc[perm].contiguous(), None)
+    assert torch.equal(yp[0], y[0][perm])
+    # dequantize (bit-exact vs oracle on a row sample) and the dense check of benchmark_rq_gemm_gpu.py:99-109
+    W = ops.code2x8_dequant(codes, cb, sc)
+    rows = np.linspace(0, O - 1, 64).astype(int)
+    Wref = orc.c_dequantize(L["codebooks"].reshape(2, 256, 8), L["idx"][rows], L["scales"].reshape(-1)[rows], I // 8)
+    assert np.array_equal(bits(W[torch.from_numpy(rows).cuda()]), Wref)
+    dense = (x.double() @ W.double().T)[0].cpu().numpy()
+    assert rel_err(y[0].double().cpu().numpy(), dense) <= 2e-3        # W carries the extra scale rounding
+    # zero activations -> exactly zero
+    y0 = ops.code2x8_matmat(torch.zeros_like(x), codes, cb, sc, None)
+    assert torch.count_nonzero(y0) == 0
+
+
+def test_dequant_full_matrix_checksum(pkg, ops, orc):
+    """whole 4096x11008 dequant against the oracle via a checksum of row checksums (bit-exact class)"""
+    from rvv_lut_vq_b200 import synth
+    I, O = 4096, 11008
+    L = synth.make_layer_np(I, O, seed=3, scales="randn")
+    W = ops.code2x8_dequant(cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]))
+    Wref = orc.c_dequantize(L["codebooks"].reshape(2, 256, 8), L["idx"], L["scales"], I // 8)
+    got = bits(W).astype(np.uint64)
+    weights = (np.arange(I, dtype=np.uint64) * 2654435761 + 12345) % 1000003
+    assert np.array_equal((got * weights).sum(axis=1), (Wref.astype(np.uint64) * weights).sum(axis=1))
+
+
+# ------------------------------------------------------------------ edge cases / API behaviour
+def test_empty_batch_and_shapes(pkg, ops):
+    from rvv_lut_vq_b200 import synth
+    L = synth.make_layer_np(256, 64, seed=0)
+    codes, cb, sc = cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"])
+    y = ops.code2x8_matmat(torch.zeros((0, 256), dtype=torch.float16, device="cuda"), codes, cb, sc, None)
+    assert y.shape == (0, 64)
+    y = ops.code2x8_matmat(torch.randn((2, 3, 256), dtype=torch.float16, device="cuda"), codes, cb, sc, None)
+    assert y.shape == (2, 3, 64)                                      # input.shape[:-1] + (out,)  (cuda_kernel.cpp:105-110)
+    with pytest.raises(NotImplementedError):
+        ops.code2x8_matmat(torch.zeros((1, 256), dtype=torch.float32, device="cuda"), codes, cb, sc, None)
+
+
+def test_c_abi_direct_and_errors(pkg):
+    """call the C-ABI with raw pointers (no torch in the signature); workspace-too-small is EINVAL, not a crash"""
+    from rvv_lut_vq_b200 import synth
+    lib = pkg.lib()
+    L = synth.make_layer_np(1024, 128, seed=2)
+    codes, cb, x = cu(L["codes"]), cu(L["codebooks"]), cu(L["x"][0])
+    y = torch.empty(128, dtype=torch.float16, device="cuda")
+    need = lib.lutvq_workspace_bytes(128, 1024)
+    ws = torch.zeros(need, dtype=torch.uint8, device="cuda")
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert lib.lutvq_code2x8_matvec(P(codes), P(x), P(y), P(cb), 128, 1024, 0, P(ws), need, st) == 0
+    torch.cuda.synchronize()
+    assert lib.lutvq_code2x8_matvec(P(codes), P(x), P(y), P(cb), 128, 1024, 0, P(ws), 16, st) == pkg._lib.LUTVQ_EINVAL
+    assert b"workspace" in lib.lutvq_last_error()
+    sm = ctypes.c_int()
+    assert lib.lutvq_device_info(ctypes.byref(sm), None, None, None) == 0 and sm.value > 0
+
+
+def test_cuda_graph_and_pdl(pkg, ops, orc):
+    """capture a chain of dependent GEMVs (y feeds the next x) in one CUDA graph; replay must equal eager,
+    with and without programmatic dependent launch"""
+    from rvv_lut_vq_b200 import synth, _lib
+    I = O = 1024
+    Ls = [synth.make_layer_np(I, O, seed=20 + i, scales="randn") for i in range(4)]
+    dev = [{k: cu(v) for k, v in L.items() if v is not None and k != "idx"} for L in Ls]
+    for d in dev:
+        d["scales"] = d["scales"] * 0.05                              # keep the chain in fp16 range
+    x0 = cu(Ls[0]["x"])
+
+    def chain(flags=None):
+        h = x0
+        for d in dev:
+            if flags is None:
+                h = ops.code2x8_matmat(h, d["codes"], d["codebooks"], d["scales"], None)
+            else:
+                h = ops._matmat("lutvq_code2x8_matmat_ex", h, d["codes"], d["codebooks"], d["scales"], None, flags)
+        return h
+
+    eager = chain()
+    nopdl = chain(_lib.FLAG_NO_PDL)
+    assert torch.equal(eager, nopdl)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        chain()                                                       # allocate workspace for this stream
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            out = chain()
+    for _ in range(3):
+        graph.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(out, eager)
+
+
+def test_quantized_linear_module(pkg, orc):
+    from rvv_lut_vq_b200 import QuantizedLinear, synth
+    I, O = 512, 192
+    L = synth.make_layer_np(I, O, seed=11, scales="randn", bias=True, batch=4)
+    m = QuantizedLinear(I, O, 8, 1, 2, 8, bias=True, device="cuda", dtype=torch.float16)
+    m.load_state_dict({"codes": cu(L["codes"]), "codebooks": cu(L["codebooks"]), "scales": cu(L["scales"]), "bias": cu(L["bias"])})
+    y = m(cu(L["x"]))                                                 # batch 4 <= 6 -> gemv op
+    assert y.shape == (4, O)
+    for b in range(4):
+        want = orc.c_aqlm_gemv_f64(L["x"][b], L["codes"], L["codebooks"]) * L["scales"].reshape(-1).astype(np.float64) + L["bias"]
+        assert rel_err(y[b].float().cpu().numpy(), want) <= TOL_GEMV

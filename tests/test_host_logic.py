@@ -1,0 +1,126 @@
+"""CPU: host-side logic -- layout proof, C-ABI surface, loud failure without a GPU, reference-mirroring API."""
+import ctypes
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    import rvv_lut_vq_b200 as r
+    r.build()
+    return r
+
+
+def test_layout_proof(tmp_path):
+    """tests/layout_check.cpp: PRMT addressing, bank-conflict freedom, build<->lookup agreement, warp reduction."""
+    exe = tmp_path / "layout_check"
+    cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.check_call([cxx, "-O1", "-std=c++17", "-o", str(exe), os.path.join(ROOT, "tests", "layout_check.cpp")])
+    out = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert out.returncode == 0 and "layout OK" in out.stdout, out.stdout + out.stderr
+
+
+def test_abi_exports_every_declared_symbol(pkg):
+    hdr = open(os.path.join(ROOT, "include", "lutvq.h")).read()
+    declared = set(re.findall(r"\b(lutvq_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    lib = ctypes.CDLL(pkg._lib.LIB_PATH)
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"liblutvq.so does not export {name}"
+    assert declared == set(pkg._lib.SIGNATURES), "python signature table out of sync with include/lutvq.h"
+
+
+def test_abi_is_plain_c(pkg):
+    """exported lutvq_* symbols are unmangled and the library does not link torch"""
+    nm = subprocess.run(["nm", "-D", "--defined-only", pkg._lib.LIB_PATH], capture_output=True, text=True).stdout
+    syms = [l.split()[-1] for l in nm.splitlines() if " T " in l]
+    assert "lutvq_code2x8_matvec" in syms
+    ldd = subprocess.run(["ldd", pkg._lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "torch" not in ldd and "c10" not in ldd
+
+
+def test_version_and_workspace(pkg):
+    lib = pkg.lib()
+    assert lib.lutvq_version() >= 100
+    # n_k = ceil(2G/64) partial planes of O floats + tickets
+    for O, I in [(4096, 4096), (11008, 4096), (4096, 11008), (96, 256)]:
+        need = lib.lutvq_workspace_bytes(O, I)
+        n_k = -(-(I // 8 * 2) // 64)
+        assert need >= n_k * O * 4
+        assert need < n_k * O * 4 + O + 4096
+    assert lib.lutvq_workspace_bytes(0, 64) == 0
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_fails_loudly_without_gpu(pkg):
+    lib = pkg.lib()
+    buf = np.zeros(1 << 16, dtype=np.uint8)
+    p = ctypes.c_void_p(buf.ctypes.data - buf.ctypes.data % 16 + 16)
+    rc = lib.lutvq_code2x8_matvec(p, p, p, p, 64, 64, 0, p, 1 << 15, None)
+    assert rc == pkg._lib.LUTVQ_ECUDA
+    assert b"no CPU fallback" in lib.lutvq_last_error()
+    from rvv_lut_vq_b200 import ops
+    x = torch.zeros(1, 64, dtype=torch.float16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.code2x8_matmat(x, torch.zeros(8, 8, 2, dtype=torch.int8), torch.zeros(2, 256, 1, 8, dtype=torch.float16),
+                           torch.ones(8, 1, 1, 1, dtype=torch.float16), None)
+
+
+def test_argument_validation(pkg):
+    lib = pkg.lib()
+    buf = np.zeros(1 << 12, dtype=np.uint8)
+    a = buf.ctypes.data - buf.ctypes.data % 16 + 16
+    p = ctypes.c_void_p(a)
+    E = pkg._lib.LUTVQ_EINVAL
+    assert lib.lutvq_code2x8_matvec(None, p, p, p, 64, 64, 0, p, 64, None) == E
+    assert lib.lutvq_code2x8_matvec(p, p, p, p, 64, 72, 0, p, 64, None) == E           # prob_k % 64
+    assert b"multiple of 64" in lib.lutvq_last_error()
+    assert lib.lutvq_code2x8_matvec(ctypes.c_void_p(a + 4), p, p, p, 64, 64, 0, p, 64, None) == E   # alignment
+    assert lib.lutvq_code2x8_matvec(p, p, p, p, 64, 64, 7, p, 64, None) == pkg._lib.LUTVQ_EUNSUPPORTED
+    assert b"float16" in lib.lutvq_last_error()
+    assert lib.lutvq_code2x8_dequant(p, None, p, None, 64, 64, 0, None) == E
+    assert lib.lutvq_lut_build(p, p, p, 4, 2, 256, 64, 0, 0, None) == E                # d too large
+    assert lib.lutvq_lut_gemv(p, p, p, 4, 2, 2, 256, 0, 9, None) == E                  # bad acc mode
+
+
+def test_reference_mirroring_api():
+    """names / signatures / parameter layout a user of the reference expects (inference.py:11-61, utils.py:11-31)"""
+    from rvv_lut_vq_b200 import QuantizedLinear, ops, utils
+    for name in ("code2x8_matmat", "code2x8_matvec", "code2x8_dequant", "code2x8_matmat_dequant"):
+        assert callable(getattr(ops, name))
+    m = QuantizedLinear(256, 96, in_group_size=8, out_group_size=1, num_codebooks=2, nbits_per_codebook=8, bias=True,
+                        dtype=torch.float16)
+    sd = {k: (tuple(v.shape), v.dtype) for k, v in m.state_dict().items()}
+    assert sd == {
+        "codebooks": ((2, 256, 1, 8), torch.float16),
+        "codes": ((96, 32, 2), torch.int8),
+        "scales": ((96, 1, 1, 1), torch.float16),
+        "bias": ((96,), torch.float16),
+    }
+    assert m.use_gemv_rule(torch.zeros(1, 6, 256)) and not m.use_gemv_rule(torch.zeros(1, 7, 256))
+    with pytest.raises(NotImplementedError):
+        m(torch.zeros(1, 256, dtype=torch.float16))          # CPU tensor: no CPU path
+    m16 = QuantizedLinear(256, 96, 8, 1, 1, 16, bias=False, dtype=torch.float16, device="meta")
+    assert m16.codes.dtype == torch.int16 and m16.codebook_size == 65536
+    # pack/unpack round trip incl. the reference's in-place wrap
+    idx = torch.randint(256, (5, 7, 2))
+    keep = idx.clone()
+    packed = utils.pack_int_data(idx, 8)
+    assert packed.dtype == torch.int8 and torch.equal(utils.unpack_int_data(packed, 8), keep)
+    with pytest.raises(NotImplementedError):
+        ops.check_use_bfloat16(torch.zeros(1, dtype=torch.float32))
+
+
+def test_algorithmic_bytes_table():
+    """SURVEY 8 table / BASELINE.md section 2"""
+    from rvv_lut_vq_b200 import synth
+    assert synth.gemv_algorithmic_bytes(4096, 4096) == 4227072
+    assert synth.gemv_algorithmic_bytes(4096, 11008) == 11332608
+    assert synth.gemv_algorithmic_bytes(11008, 4096) == 11318784
