@@ -83,6 +83,17 @@ int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebo
                             const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
                             unsigned flags, void* ws, size_t ws_bytes, void* stream);
 
+/* Optional load-time re-layout of the codes for the GEMV (the reference does the same kind of one-off permutation
+ * for its CPU kernel in QuantizedLinear.prepare_matmul_op, aqlm/../inference.py:78-83).  The packed image holds the
+ * same code bytes, ordered [k-slice of 64 code bytes][32-row set][8-row tile][lane] x 16 B so that every warp load
+ * is 512 contiguous bytes; rows / k-slices are zero-padded to whole sets (lutvq_code2x8_packed_bytes >= prob_m*prob_k/4).
+ * lutvq_code2x8_matmat_packed == lutvq_code2x8_matmat_ex on the packed image (bit-identical results). */
+size_t lutvq_code2x8_packed_bytes(int prob_m, int prob_k);
+int lutvq_code2x8_prepack(const void* codes, void* packed, int prob_m, int prob_k, void* stream);
+int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* codebooks, const void* scales,
+                                const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
+                                unsigned flags, void* ws, size_t ws_bytes, void* stream);
+
 /* W[o][8g+j] = codebook[0][c0(o,g)][j] + codebook[1][c1(o,g)][j]   (one RN add in dtype; bit-exact class)
  * then, if scales != NULL, W[o][:] = round(W[o][:] * scales[o])     (cuda_kernel.cpp:445)
  * W dtype [prob_m][prob_k] row-major. */

@@ -27,6 +27,9 @@ SIGNATURES = {
     "lutvq_code2x8_matvec": (I, [P, P, P, P, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat_ex": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),
+    "lutvq_code2x8_packed_bytes": (SZ, [I, I]),
+    "lutvq_code2x8_prepack": (I, [P, P, I, I, P]),
+    "lutvq_code2x8_matmat_packed": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),
     "lutvq_code2x8_dequant": (I, [P, P, P, P, I, I, I, P]),
     "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_lut_build": (I, [P, P, P, I, I, I, I, I, I, P]),

@@ -8,10 +8,12 @@
 namespace lutvq {
 
 // launchers (gemv_lut.cu, dequant.cu, vq_golden.cu, gemm_tc.cu)
-int gemv_2x8_launch(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
+int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream);
 size_t gemv_workspace_bytes(int O, int G);
+size_t gemv_packed_bytes(int O, int G);
+int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);
 void gemv_set_tuning(int nw, int pf, int ctas_per_sm);
 void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk);
 int code2x8_dequant_launch(const void* codes, void* W, const void* codebook, const void* scales, int O, int I,
@@ -105,13 +107,13 @@ int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* 
     if (int rc = check_2x8_common(codes, codebook, prob_m, prob_k, dtype)) return rc;
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
     LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
-    return gemv_2x8_launch(codes, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, 0u, ws, ws_bytes,
+    return gemv_2x8_launch(codes, 0, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, 0u, ws, ws_bytes,
                            static_cast<cudaStream_t>(stream));
 }
 
-int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebooks, const void* scales,
-                            const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, unsigned flags,
-                            void* ws, size_t ws_bytes, void* stream) {
+static int matmat_rows(const void* x, const void* codes, int packed, const void* codebooks, const void* scales,
+                       const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, unsigned flags,
+                       void* ws, size_t ws_bytes, void* stream) {
     if (int rc = check_2x8_common(codes, codebooks, prob_m, prob_k, dtype)) return rc;
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
     LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
@@ -122,11 +124,37 @@ int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebo
     for (int b = 0; b < batch; ++b) {
         const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * esz;
         void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * esz;
-        if (int rc = gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, flags, ws, ws_bytes,
-                                     static_cast<cudaStream_t>(stream)))
+        if (int rc = gemv_2x8_launch(codes, packed, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, flags, ws,
+                                     ws_bytes, static_cast<cudaStream_t>(stream)))
             return rc;
     }
     return LUTVQ_OK;
+}
+
+int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebooks, const void* scales,
+                            const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, unsigned flags,
+                            void* ws, size_t ws_bytes, void* stream) {
+    return matmat_rows(x, codes, 0, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, flags, ws, ws_bytes, stream);
+}
+
+size_t lutvq_code2x8_packed_bytes(int prob_m, int prob_k) {
+    if (prob_m <= 0 || prob_k <= 0) return 0;
+    return gemv_packed_bytes(prob_m, prob_k / 8);
+}
+
+int lutvq_code2x8_prepack(const void* codes, void* packed, int prob_m, int prob_k, void* stream) {
+    LUTVQ_REQUIRE(codes && packed, "null codes/packed pointer");
+    LUTVQ_REQUIRE(prob_m > 0 && prob_k > 0 && prob_k % 64 == 0, "bad shape prob_m=%d prob_k=%d (prob_k %% 64 == 0)", prob_m, prob_k);
+    LUTVQ_REQUIRE(aligned16(codes) && aligned16(packed), "codes and packed must be 16-byte aligned");
+    DeviceInfo di;
+    if (int rc = get_device_info(&di)) return rc;
+    return gemv_prepack_launch(codes, packed, prob_m, prob_k, static_cast<cudaStream_t>(stream));
+}
+
+int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* codebooks, const void* scales,
+                                const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
+                                unsigned flags, void* ws, size_t ws_bytes, void* stream) {
+    return matmat_rows(x, packed, 1, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, flags, ws, ws_bytes, stream);
 }
 
 int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,

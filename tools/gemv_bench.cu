@@ -1,0 +1,187 @@
+// gemv_bench.cu -- stand-alone microbenchmark of liblutvq's AQLM 2x8 LUT-GEMV through the C-ABI (no Python).
+//
+//   gemv_bench [--shapes 4096x11008,4096x4096,11008x4096] [--packed 0|1|2] [--tuning nw,pf] [--nopdl] [--reps R]
+//              [--check] [--ncu]
+//
+// Per shape: a ring of distinct layers whose codes total > 2x the 126 MB L2 (so every launch streams its codes
+// from HBM), captured as ONE CUDA graph of back-to-back GEMVs, replayed R times between CUDA events.
+// --check compares layer 0's output with a naive fp32 dequant-dot kernel (max |err| / max |ref|).
+// --ncu   runs only a handful of eager launches (for use under ncu).
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include <algorithm>
+#include <cmath>
+#include "../include/lutvq.h"
+
+extern "C" void lutvq_debug_set_gemv_tuning(int nw, int pf, int ctas_per_sm);
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(2); } } while (0)
+#define LK(x) do { int rc_ = (x); if (rc_ != 0) { fprintf(stderr, "lutvq error %d: %s at %s:%d\n", rc_, lutvq_last_error(), __FILE__, __LINE__); exit(3); } } while (0)
+
+__device__ __forceinline__ uint32_t hash32(uint32_t v) {
+    v ^= v >> 16; v *= 0x7feb352dU; v ^= v >> 15; v *= 0x846ca68bU; v ^= v >> 16;
+    return v;
+}
+__global__ void fill_codes(uint32_t* p, size_t n_words, uint32_t seed) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = hash32((uint32_t)i * 2654435761U + seed);
+}
+__global__ void fill_half(__half* p, size_t n, uint32_t seed, float scale) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        // sum of 4 uniforms ~ roughly normal, unit-ish variance
+        uint32_t h = hash32((uint32_t)i + seed);
+        float u = ((h & 0xFF) + ((h >> 8) & 0xFF) + ((h >> 16) & 0xFF) + (h >> 24)) / 255.f - 2.f;
+        p[i] = __float2half_rn(u * 1.7f * scale);
+    }
+}
+// naive reference: y[o] = sum_g sum_j (cb0[c0][j] + cb1[c1][j]) * x[8g+j] in fp32 (weights as one fp16 add, like the reference)
+__global__ void ref_gemv(const uint8_t* codes, const __half* x, const __half* cb, float* y, int O, int G) {
+    const int o = blockIdx.x;
+    float acc = 0.f;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) {
+        const int c0 = codes[((size_t)o * G + g) * 2], c1 = codes[((size_t)o * G + g) * 2 + 1];
+        for (int j = 0; j < 8; ++j) {
+            const float w = __half2float(cb[c0 * 8 + j]) + __half2float(cb[(256 + c1) * 8 + j]);
+            acc += w * __half2float(x[g * 8 + j]);
+        }
+    }
+    __shared__ float red[256];
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = blockDim.x / 2; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+    if (threadIdx.x == 0) y[o] = red[0];
+}
+
+struct Layer { void* codes; void* packed; __half* cb; __half* scales; __half* x; __half* y; };
+
+int main(int argc, char** argv) {
+    std::string shapes = "4096x4096,4096x11008,11008x4096";
+    int packed = 2, reps = 40, nw = 0, pf = 0;
+    bool nopdl = false, check = false, ncu = false;
+    double peak = 6536.7;
+    for (int i = 1; i < argc; ++i) {
+        std::string a = argv[i];
+        auto next = [&]() { return std::string(i + 1 < argc ? argv[++i] : ""); };
+        if (a == "--shapes") shapes = next();
+        else if (a == "--packed") packed = atoi(next().c_str());
+        else if (a == "--reps") reps = atoi(next().c_str());
+        else if (a == "--tuning") { std::string t = next(); sscanf(t.c_str(), "%d,%d", &nw, &pf); }
+        else if (a == "--nopdl") nopdl = true;
+        else if (a == "--check") check = true;
+        else if (a == "--ncu") ncu = true;
+        else if (a == "--peak") peak = atof(next().c_str());
+    }
+    if (nw) lutvq_debug_set_gemv_tuning(nw, pf, 0);
+    int sms = 0;
+    LK(lutvq_device_info(&sms, nullptr, nullptr, nullptr));
+    cudaStream_t st;
+    CK(cudaStreamCreate(&st));
+    const unsigned flags = nopdl ? LUTVQ_FLAG_NO_PDL : 0u;
+
+    size_t pos = 0;
+    while (pos < shapes.size()) {
+        size_t comma = shapes.find(',', pos);
+        std::string sh = shapes.substr(pos, comma == std::string::npos ? std::string::npos : comma - pos);
+        pos = comma == std::string::npos ? shapes.size() : comma + 1;
+        int I = 0, O = 0;
+        if (sscanf(sh.c_str(), "%dx%d", &I, &O) != 2) { fprintf(stderr, "bad shape %s\n", sh.c_str()); return 1; }
+        const int G = I / 8;
+        const size_t code_bytes = (size_t)O * G * 2;
+        int nbuf = (int)std::max<size_t>(8, (size_t)(280e6 / code_bytes) + 1);
+        if (ncu) nbuf = 4;
+        const size_t pk_bytes = lutvq_code2x8_packed_bytes(O, I);
+        const size_t ws_bytes = lutvq_workspace_bytes(O, I);
+        void* ws;
+        CK(cudaMalloc(&ws, ws_bytes));
+        CK(cudaMemset(ws, 0, ws_bytes));
+        std::vector<Layer> L(nbuf);
+        for (int b = 0; b < nbuf; ++b) {
+            CK(cudaMalloc(&L[b].codes, code_bytes));
+            CK(cudaMalloc(&L[b].packed, pk_bytes));
+            CK(cudaMalloc(&L[b].cb, 2 * 256 * 8 * 2));
+            CK(cudaMalloc(&L[b].scales, (size_t)O * 2));
+            CK(cudaMalloc(&L[b].x, (size_t)I * 2));
+            CK(cudaMalloc(&L[b].y, (size_t)O * 2));
+            fill_codes<<<592, 256, 0, st>>>((uint32_t*)L[b].codes, code_bytes / 4, 1000u * b + 7u);
+            fill_half<<<16, 256, 0, st>>>(L[b].cb, 2 * 256 * 8, 31u * b + 1u, 1.f);
+            fill_half<<<16, 256, 0, st>>>(L[b].x, I, 77u * b + 5u, 1.f);
+            fill_half<<<16, 256, 0, st>>>(L[b].scales, O, 13u * b + 3u, 0.f);   // zeros, then set to 1 below
+            LK(lutvq_code2x8_prepack(L[b].codes, L[b].packed, O, I, st));
+        }
+        CK(cudaStreamSynchronize(st));
+        {   // scales = 1 like benchmark_rq_gemm_gpu.py:97
+            std::vector<__half> ones(O, __float2half(1.f));
+            for (int b = 0; b < nbuf; ++b) CK(cudaMemcpy(L[b].scales, ones.data(), (size_t)O * 2, cudaMemcpyHostToDevice));
+        }
+        const double alg_bytes = (double)code_bytes + 8192 + 2.0 * I + 4.0 * O;
+
+        for (int mode = 0; mode < 2; ++mode) {
+            if (packed != 2 && packed != mode) continue;
+            auto launch = [&](int b) {
+                if (mode) LK(lutvq_code2x8_matmat_packed(L[b].x, L[b].packed, L[b].cb, L[b].scales, nullptr, L[b].y, 1, O, I, LUTVQ_F16, flags, ws, ws_bytes, st));
+                else      LK(lutvq_code2x8_matmat_ex(L[b].x, L[b].codes, L[b].cb, L[b].scales, nullptr, L[b].y, 1, O, I, LUTVQ_F16, flags, ws, ws_bytes, st));
+            };
+            if (check) {
+                float* yref;
+                CK(cudaMalloc(&yref, (size_t)O * 4));
+                ref_gemv<<<O, 256, 0, st>>>((const uint8_t*)L[0].codes, L[0].x, L[0].cb, yref, O, G);
+                CK(cudaMemsetAsync(L[0].y, 0xFF, (size_t)O * 2, st));
+                launch(0);
+                launch(0);      // twice: exercises the epoch hand-over
+                CK(cudaStreamSynchronize(st));
+                std::vector<float> r(O);
+                std::vector<__half> y(O);
+                CK(cudaMemcpy(r.data(), yref, (size_t)O * 4, cudaMemcpyDeviceToHost));
+                CK(cudaMemcpy(y.data(), L[0].y, (size_t)O * 2, cudaMemcpyDeviceToHost));
+                double maxref = 0, maxerr = 0;
+                int bad = -1;
+                for (int o = 0; o < O; ++o) {
+                    maxref = std::max(maxref, (double)fabsf(r[o]));
+                    double e = fabs((double)__half2float(y[o]) - r[o]);
+                    if (!(e <= maxerr)) { maxerr = e; bad = o; }
+                }
+                printf("check %s mode=%s: max|err|/max|ref| = %.3e (row %d: got %f want %f)\n", sh.c_str(), mode ? "packed" : "reference-layout",
+                       maxerr / maxref, bad, bad >= 0 ? __half2float(y[bad]) : 0.f, bad >= 0 ? r[bad] : 0.f);
+                CK(cudaFree(yref));
+            }
+            if (ncu) {
+                for (int b = 0; b < nbuf; ++b) launch(b);
+                CK(cudaStreamSynchronize(st));
+                continue;
+            }
+            cudaGraph_t graph;
+            cudaGraphExec_t exec;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeGlobal));
+            for (int b = 0; b < nbuf; ++b) launch(b);
+            CK(cudaStreamEndCapture(st, &graph));
+            CK(cudaGraphInstantiate(&exec, graph, 0));
+            for (int i = 0; i < 5; ++i) CK(cudaGraphLaunch(exec, st));
+            CK(cudaStreamSynchronize(st));
+            cudaEvent_t e0, e1;
+            CK(cudaEventCreate(&e0));
+            CK(cudaEventCreate(&e1));
+            CK(cudaEventRecord(e0, st));
+            for (int i = 0; i < reps; ++i) CK(cudaGraphLaunch(exec, st));
+            CK(cudaEventRecord(e1, st));
+            CK(cudaStreamSynchronize(st));
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            const double us = ms * 1e3 / ((double)reps * nbuf);
+            const double gbps = alg_bytes / (us * 1e-6) / 1e9;
+            printf("{\"shape\": \"%s\", \"layout\": \"%s\", \"pdl\": %d, \"us\": %.3f, \"gbps\": %.1f, \"frac\": %.4f, \"ring\": %d, \"sms\": %d}\n",
+                   sh.c_str(), mode ? "packed" : "reference", nopdl ? 0 : 1, us, gbps, gbps / peak, nbuf, sms);
+            CK(cudaGraphExecDestroy(exec));
+            CK(cudaGraphDestroy(graph));
+        }
+        for (int b = 0; b < nbuf; ++b) {
+            cudaFree(L[b].codes); cudaFree(L[b].packed); cudaFree(L[b].cb); cudaFree(L[b].scales); cudaFree(L[b].x); cudaFree(L[b].y);
+        }
+        cudaFree(ws);
+    }
+    return 0;
+}
