@@ -49,6 +49,10 @@ typedef enum { LUTVQ_F16 = 0, LUTVQ_BF16 = 1 } lutvq_dtype_t;
 /* flags for the *_ex entry points */
 #define LUTVQ_FLAG_LUT_FP16   1u  /* round LUT entries to fp16 (vq.py:285 semantics) before accumulation */
 #define LUTVQ_FLAG_NO_PDL     2u  /* do not use programmatic dependent launch for this call */
+#define LUTVQ_FLAG_X_READY    4u  /* caller's promise: x, scales and bias were NOT written by the kernel(s) immediately
+                                     preceding this call in the stream (e.g. the k/v projections after q, up after gate,
+                                     or a microbenchmark loop over one input).  The LUT build and the gather then overlap
+                                     the previous kernel; the workspace traffic and the y stores stay stream-ordered. */
 
 /* lutvq_lut_build lut_mode */
 #define LUTVQ_LUT_VQPY_FP16   0   /* bit-exact vq.py: fp16 products, numpy pairwise fp32 sum, fp16 entries */

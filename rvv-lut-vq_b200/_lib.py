@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(CSRC, "liblutvq.so")
 
 LUTVQ_OK, LUTVQ_EINVAL, LUTVQ_EUNSUPPORTED, LUTVQ_ECUDA = 0, -1, -2, -3
 LUTVQ_F16, LUTVQ_BF16 = 0, 1
-FLAG_LUT_FP16, FLAG_NO_PDL = 1, 2
+FLAG_LUT_FP16, FLAG_NO_PDL, FLAG_X_READY = 1, 2, 4
 LUT_VQPY_FP16, LUT_FP32 = 0, 1
 ACC_F64, ACC_F32 = 0, 1
 

@@ -10,16 +10,32 @@
 //                                                     one PRMT + one LDS + one FADD per code byte,
 //                                                     conflict-free for any index pattern (lut_layout.h)
 //
-// Grid = (row chunks, k-slices), at most one CTA per SM so that the whole grid is co-resident.  The split-k
-// partial sums travel through L2 as 8-byte {value, epoch} words (flag-in-data, no fence / no atomic on the
-// critical path); the 32-row sets of a row chunk are dealt round-robin to the (k-slice CTA, warp) pairs of
-// that chunk, which poll the n_k partials of a set, add them IN FIXED k ORDER (deterministic) and apply the
-// reference epilogue order (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111).
+// Work decomposition.  The work items of one GEMV are (k-slice, 32-row set) pairs, linearised slice-major.
+// The grid is EXACTLY one CTA per SM (a "worker"); worker w owns a contiguous range of items:
+//   aligned  (n_k <= #SMs): the workers are dealt to the slices (floor or ceil(#SMs/n_k) each) and split that
+//            slice's row sets evenly -> one LUT build per worker;
+//   linear   (otherwise, or when cheaper): range w*T/W .. (w+1)*T/W, which may straddle slices (<= 2 builds
+//            when T/W >= n_sets, more for very long K).
+// One CTA per SM per launch matters under programmatic dependent launch: consecutive launches then pair up
+// 1:1 on every SM (occupancy 2), instead of a 144-CTA grid doubling up on the 4 idle SMs and straggling.
+//
+// Cross-CTA split-k reduction: partial sums travel through L2 as 8-byte {value, epoch} words (flag-in-data,
+// no fence / no atomic on the critical path); the 32-row sets are dealt round-robin to all warps of the grid,
+// which poll the n_k partials of a set, add them IN FIXED k ORDER (deterministic) and apply the reference
+// epilogue order (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111).  All CTAs of a launch are
+// co-resident (grid <= #SMs, >= 1 slot per SM), which the polling relies on.
+//
+// Stream overlap (programmatic dependent launch).  Weights (codes, codebooks) never depend on the previous
+// kernel, so the first tile sets are requested into registers and the rest of the worker's share is pushed
+// HBM -> L2 BEFORE griddepcontrol.wait.  With LUTVQ_FLAG_X_READY the caller additionally promises that x /
+// scales / bias were not written by the kernel(s) immediately preceding this call in the stream; then the LUT
+// build and the whole gather also run before the wait (row sums parked in shared memory) and only the
+// workspace traffic, the reduction and the y stores are ordered behind the previous kernel.
 //
 // Two code layouts feed the same gather loop:
 //   reference  int8 [O][G][2] exactly as QuantizedLinear.codes: a warp's 128-bit load touches 8 rows x 64 B;
 //   packed     lutvq_code2x8_prepack(): [k-slice][32-row set][8-row tile][lane] x 16 B, the lane's register
-//              image, so a warp's load is 512 contiguous bytes and a CTA's whole share is one contiguous range.
+//              image, so a warp's load is 512 contiguous bytes and a worker's share is one contiguous range.
 //
 // Algorithmic HBM bytes per launch: O*(I/8)*2 codes + 8192 codebooks + 2I x + 2O scales + 2O y.
 #include "common.cuh"
@@ -27,11 +43,8 @@
 
 namespace lutvq {
 
-struct WsHeader {               // first 256 bytes of the workspace
-    unsigned int epoch;         // bumped once per launch by the last CTA to finish; partial tags are epoch + 1
-    unsigned int done;          // CTAs finished in the current launch
-};
-constexpr size_t kWsHeaderBytes = 256;
+constexpr size_t kWsHeaderBytes = 256;        // reserved
+constexpr uint32_t kTagFull = 0x600DF00Du;    // tag of a partial that has been written and not yet consumed
 
 struct GemvParams {
     const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
@@ -40,11 +53,25 @@ struct GemvParams {
     void* y;                  // [O]
     const void* scales;       // [O] or null
     const void* bias;         // [O] or null
-    WsHeader* hdr;
-    uint2* partial;           // [n_k][O_pad] {value bits, tag}
-    int O, O_pad, G, n_k, sets_per_chunk, n_sets_total;
+    uint2* partial;           // [n_k][O_pad] {value bits, tag}; tag == 0 between launches
+    int O, O_pad, G, n_k, n_sets;
+    int aligned;              // 1: aligned plan (q, r below), 0: linear plan
+    int q, r;                 // aligned plan: W = q*n_k + r; slices < r have q+1 workers
+    unsigned magic_q, magic_q1;                 // ceil(2^20 / q), ceil(2^20 / (q+1))
+    int base_q, rem_q, base_q1, rem_q1;         // n_sets = base_q*q + rem_q = base_q1*(q+1) + rem_q1
     unsigned flags;
+    unsigned long long* tl;   // debug timeline [256 CTAs][16] of %globaltimer stamps for this launch, or null
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TL_STAMP(i)                                                                                              \
+    do {                                                                                                         \
+        if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + (i)] = globaltimer_ns();          \
+    } while (0)
 
 template <int DT> struct MmaK8;
 template <> struct MmaK8<LUTVQ_F16> {
@@ -60,26 +87,30 @@ template <> struct MmaK8<LUTVQ_BF16> {
     }
 };
 
-__device__ __forceinline__ float lds_f32(uint32_t addr) {
-    float v;
-    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-    return v;
-}
 __device__ __forceinline__ void sts_v4(uint32_t addr, float a, float b, float c, float d) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-// flag-in-data partial sums: one 8-byte word is written / read as a unit
+// flag-in-data partial sums: one naturally aligned 64-bit word {value bits, tag} is written / read as a unit.
+// Both sides use L1-bypassing (.cg) accesses, so L2 is the meeting point.  They are deliberately NOT .relaxed.gpu /
+// .volatile: measured on B200, a warp's strong loads are not pipelined (16 polls = 16 serial L2 round trips,
+// 2.4 us), whereas 16 .cg loads overlap (one round trip).  An aligned 8-byte access is a single transaction, so
+// value and tag always travel together.
 __device__ __forceinline__ void st_partial(uint2* p, float v, uint32_t tag) {
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(__float_as_uint(v)), "r"(tag) : "memory");
+    const unsigned long long w = ((unsigned long long)tag << 32) | __float_as_uint(v);
+    asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p), "l"(w) : "memory");
 }
 __device__ __forceinline__ uint2 ld_partial(const uint2* p) {
-    uint2 r;
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p) : "memory");
-    return r;
+    unsigned long long w;
+    asm volatile("ld.global.cg.b64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+    return make_uint2((uint32_t)w, (uint32_t)(w >> 32));
 }
 // asynchronous HBM -> L2 prefetch of a contiguous range (no registers, no shared memory)
 __device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+// per-thread (non-uniform address) L2 prefetch of the line holding p
+__device__ __forceinline__ void l2_prefetch_line(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
 }
 
 template <int DT>
@@ -95,18 +126,43 @@ __device__ __forceinline__ void epilogue_store(void* y, const void* scales, cons
 // One warp tile set = 32 rows x 64 bytes: 4 tiles of 8 rows; per lane 4 x 16 bytes.
 struct CodeRegs { uint32_t w[4][4]; };
 
+// worker -> linear item range [begin, end) over (slice, set) pairs, slice-major.  The aligned plan is division-free:
+// slices < r have q+1 workers, the others q; a slice's n_sets sets are dealt base (+1 for the first rem) per worker.
+__device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
+    if (p.aligned) {
+        const int big = p.r * (p.q + 1);
+        const bool hi_part = w >= big;
+        const int nw = hi_part ? p.q : p.q + 1;
+        const int w2 = hi_part ? w - big : w;
+        const int s2 = (int)(((unsigned)w2 * (hi_part ? p.magic_q : p.magic_q1)) >> 20);     // w2 / nw  (exact for w2, nw <= 1024)
+        const int j = w2 - s2 * nw;
+        const int s = (hi_part ? p.r : 0) + s2;
+        const int base = hi_part ? p.base_q : p.base_q1, rem = hi_part ? p.rem_q : p.rem_q1;  // n_sets = base*nw + rem
+        begin = s * p.n_sets + j * base + min(j, rem);
+        end   = begin + base + (j < rem ? 1 : 0);
+    } else {
+        const long long T = (long long)p.n_k * p.n_sets;
+        begin = (int)((T * w) / W);
+        end   = (int)((T * (w + 1)) / W);
+    }
+}
+
 template <int DT, bool PACKED, int NW, int PF>
-__global__ void __launch_bounds__(NW * 32, 2)
+__global__ void __launch_bounds__(NW * 32, (NW <= 4 ? 3 : 2))
 lut_gemv_2x8_kernel(const GemvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t lut_base = smem_u32(smem_raw);
 
+    TL_STAMP(0);
+    if (p.tl != nullptr && threadIdx.x == 0) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.tl[(size_t)blockIdx.x * 16 + 15] = smid + 1;
+    }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int chunk = blockIdx.x;
-    const int my = blockIdx.y, ny = gridDim.y;            // this CTA owns k-slices my, my+ny, ... (ny == n_k unless n_k > #SMs)
-    const int set0 = chunk * p.sets_per_chunk;            // first 32-row set of this row chunk
-    const int n_sets = min(p.sets_per_chunk, p.n_sets_total - set0);
-    const int row0 = set0 * kSetRows;
+    const int W = gridDim.x;
+    int begin, end;
+    worker_range(p, blockIdx.x, W, begin, end);
     const size_t row_bytes = (size_t)p.G * 2;
     const int last_row = p.O - 1;
 
@@ -115,10 +171,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     // and lanes whose 16-byte chunk lies past the end of the row (last, partial k-slice) re-read chunk 0 --
     // their tables were built from x = 0, so whatever index they fetch contributes exactly 0.
     const int e = stream_first_half(lane);
-    auto load_set = [&](CodeRegs& r, int ks, int s) {
+    auto load_set = [&](CodeRegs& r, int ks, int set) {
         if (PACKED) {
-            const uint4* base = reinterpret_cast<const uint4*>(p.codes) +
-                                (((size_t)ks * p.n_sets_total + (set0 + s)) * 4) * 32 + lane;
+            const uint4* base = reinterpret_cast<const uint4*>(p.codes) + (((size_t)ks * p.n_sets + set) * 4) * 32 + lane;
             #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const uint4 v = ldg_stream_u128(base + t * 32);
@@ -128,7 +183,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             const int slice_byte0 = ks * kSliceTables;
             const bool chunk_valid = (size_t)(slice_byte0 + 16 * stream_chunk(lane)) < row_bytes;
             const uint8_t* lane_base = p.codes + slice_byte0 + (chunk_valid ? 16 * stream_chunk(lane) : 0);
-            const int rbase = row0 + s * kSetRows + stream_row_in_tile(lane);
+            const int rbase = set * kSetRows + stream_row_in_tile(lane);
             #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const uint32_t row = (uint32_t)min(rbase + t * kTileRows, last_row);
@@ -140,28 +195,47 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         }
     };
 
+    TL_STAMP(8);
+    // first segment of this worker's range: slice ks, sets [lo, hi)
+    int pos = begin;
+    int ks = (begin < end) ? (int)((unsigned)begin / (unsigned)p.n_sets) : 0;
+    int lo = begin - ks * p.n_sets;
+    int hi = min(p.n_sets, lo + (end - begin));
+
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
     // Codes and codebooks are weights.  (1) the first PF tile sets are requested into registers, (2) the rest
-    // of this CTA's share is pushed HBM -> L2 by bulk prefetches, (3) the codebook MMA fragments are loaded --
-    // all BEFORE the programmatic-dependency wait, i.e. while the previous kernel is still running.
+    // of this worker's share is pushed HBM -> L2, (3) x / the workspace header are pulled into L2 (L2 is the
+    // coherence point, so this is safe even while the previous kernel is still writing them), (4) the codebook
+    // MMA fragments are loaded -- all BEFORE the programmatic-dependency wait.
     CodeRegs buf[PF];
     #pragma unroll
     for (int i = 0; i < PF; ++i)
-        if (warp + i * NW < n_sets) load_set(buf[i], my, warp + i * NW);
+        if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + warp + i * NW);
+    TL_STAMP(9);
     if (PACKED) {
-        for (int ks = my; ks < p.n_k; ks += ny) {
-            const uint8_t* base = p.codes + ((size_t)ks * p.n_sets_total + set0) * 2048;
-            for (int s = threadIdx.x; s < n_sets; s += NW * 32) l2_prefetch_bulk(base + (size_t)s * 2048, 2048);
+        // the worker's whole share is ONE contiguous range of the packed image (linear item index * 2048 B)
+        if (lane == 0) {
+            const uint8_t* base = p.codes + (size_t)begin * 2048;
+            const int n = end - begin;
+            for (int c = warp * 4 + PF * NW; c < n; c += NW * 4)
+                l2_prefetch_bulk(base + (size_t)c * 2048, (uint32_t)min(4, n - c) * 2048u);
         }
     } else {
-        const int rows_here = min(n_sets * kSetRows, p.O - row0);
-        for (int ks = my; ks < p.n_k; ks += ny) {
-            const size_t off = (size_t)ks * kSliceTables;
-            const uint32_t seg = (uint32_t)min((size_t)kSliceTables, row_bytes - off);
-            for (int r = threadIdx.x; r < rows_here; r += NW * 32)
-                l2_prefetch_bulk(p.codes + (size_t)(row0 + r) * row_bytes + off, seg);
+        int ppos = begin;
+        while (ppos < end) {
+            const int s = ppos / p.n_sets, l = ppos - s * p.n_sets, h = min(p.n_sets, l + (end - ppos));
+            const size_t off = (size_t)s * kSliceTables;
+            const int r1 = min(h * kSetRows, p.O);
+            for (int r = l * kSetRows + threadIdx.x; r < r1; r += NW * 32)
+                l2_prefetch_line(p.codes + (size_t)r * row_bytes + off);
+            ppos += h - l;
         }
     }
+    if (warp == NW - 1) {
+        if (lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
+            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * 512 + lane * 128);
+    }
+    TL_STAMP(10);
     const int r = lane >> 2, q = lane & 3;
     constexpr int MB_PER_WARP = 16 / NW;                                   // 16 idx blocks of 16 per codebook
     uint32_t afrag[MB_PER_WARP][2][2];
@@ -178,9 +252,15 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             }
         }
     }
+    TL_STAMP(1);
     pdl_launch_dependents();    // the next kernel may start ITS weight prefetch now (it still waits for us below)
-    pdl_wait();                 // x and the workspace belong to the previous kernel until here
-    const uint32_t tag = ldcg_u32(&p.hdr->epoch) + 1u;
+    // X_READY: x is not the previous kernel's output and the workspace is exclusively ours (include/lutvq.h), so
+    // nothing but the final y stores has to be ordered behind the previous kernel.
+    const bool xready = (p.flags & LUTVQ_FLAG_X_READY) != 0;
+    bool waited = !xready;
+    if (!xready) pdl_wait();    // x and the workspace belong to the previous kernel until here
+    constexpr uint32_t tag = kTagFull;
+    TL_STAMP(2);
 
     // PRMT operands (lut_layout.h): byte0 <- lm, byte1 <- code byte, bytes 2,3 <- 0.  The slice base and the
     // (c&1)*128 half-select are compile-time constants for ptxas and ride in the LDS immediate.
@@ -194,9 +274,10 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     const bool b3 = (lane >> 3) & 1, b4 = (lane >> 4) & 1;
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
+    bool first_seg = true;
 
-    for (int ks = my; ks < p.n_k; ks += ny) {
-        // ---------------- K1: build this CTA's 64 KiB LUT slice ----------------
+    while (pos < end) {
+        // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
         {
             // B fragments: column r of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
             const uint32_t* x32 = static_cast<const uint32_t*>(p.x);              // 4 words per group
@@ -204,7 +285,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int g = ks * 32 + build_group_of_col(j, r);
-                bfrag[j] = (g < p.G) ? ldcg_u32(x32 + g * 4 + q) : 0u;   // L2-coherent: x is the previous kernel's output
+                bfrag[j] = (g < p.G) ? ldcg_u32(x32 + g * 4 + q) : 0u;   // L2-coherent: x may be the previous kernel's output
             }
             #pragma unroll
             for (int mi = 0; mi < MB_PER_WARP; ++mi) {
@@ -250,15 +331,23 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             }
         }
         __syncthreads();
+        if (first_seg) TL_STAMP(3);
+        first_seg = false;
 
         // ---------------- K2: stream codes, gather-accumulate ----------------
-        const int ks_next = ks + ny;
-        for (int it = 0; it * NW + warp < n_sets; it += PF) {
+        for (int it = 0; lo + it * NW + warp < hi; it += PF) {
             #pragma unroll
             for (int st = 0; st < PF; ++st) {
-                const int s = (it + st) * NW + warp;
-                if (s < n_sets) {                                   // warp-uniform
+                const int set = lo + (it + st) * NW + warp;
+                if (set < hi) {                                     // warp-uniform
                     float acc[4][2];
+                    if (p.flags & 0x100u) {                         // DEBUG: no lookups (pure code streaming)
+                        #pragma unroll
+                        for (int t = 0; t < 4; ++t) {
+                            acc[t][0] = __uint_as_float((buf[st].w[t][0] ^ buf[st].w[t][1]) & 0x3fffffffu);
+                            acc[t][1] = __uint_as_float((buf[st].w[t][2] ^ buf[st].w[t][3]) & 0x3fffffffu);
+                        }
+                    } else {
                     #pragma unroll
                     for (int c = 0; c < 4; ++c)
                         #pragma unroll
@@ -266,12 +355,19 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                             #pragma unroll
                             for (int t = 0; t < 4; ++t) {
                                 const uint32_t ad = __byte_perm(buf[st].w[t][c], lm[c >> 1][d], sel[d]);
-                                const float v = lds_f32(lut_base + ad + stream_imm(c));
+                                
+#ifdef LUTVQ_VOLATILE_LDS
+                                float v;
+                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(lut_base + ad + stream_imm(c)));
+#else
+                                const float v = *reinterpret_cast<const float*>(smem_raw + ad + stream_imm(c));
+#endif
                                 if (c == 0 && d < 2) acc[t][d] = v;
                                 else                 acc[t][d & 1] += v;
                             }
+                    }
                     // refill this stage with the set PF iterations ahead before the (short) reduction
-                    if (s + PF * NW < n_sets) load_set(buf[st], ks, s + PF * NW);
+                    if (set + PF * NW < hi && !(p.flags & 0x200u)) load_set(buf[st], ks, set + PF * NW);   // 0x200 DEBUG: no streaming
                     float a0 = acc[0][0] + acc[0][1], a1 = acc[1][0] + acc[1][1];
                     float a2 = acc[2][0] + acc[2][1], a3 = acc[3][0] + acc[3][1];
                     // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
@@ -281,55 +377,89 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                     k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
                     float keep = b3 ? k1 : k0, give = b3 ? k0 : k1;
                     keep += __shfl_xor_sync(0xffffffffu, give, 8);
-                    const int row = row0 + s * kSetRows + lane;
-                    if (p.n_k == 1) { if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep); }
-                    else            st_partial(p.partial + (size_t)ks * p.O_pad + row, keep, tag);
+                    const int row = set * kSetRows + lane;
+                    if (p.n_k == 1) {
+                        if (!waited) { pdl_wait(); waited = true; }
+                        if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
+                    } else {
+                        if (p.flags & 0x400u) {                     // DEBUG: weak store
+                            const unsigned long long wv = ((unsigned long long)tag << 32) | __float_as_uint(keep);
+                            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p.partial + (size_t)ks * p.O_pad + row), "l"(wv) : "memory");
+                        } else if (p.flags & 0x800u) {              // DEBUG: no store at all (results wrong)
+                        } else
+                        st_partial(p.partial + (size_t)ks * p.O_pad + row, keep, tag);
+                    }
+                    if (p.tl != nullptr && threadIdx.x == 0 && it + st < 2) p.tl[(size_t)blockIdx.x * 16 + 11 + it + st] = globaltimer_ns();
                 }
             }
         }
-        if (ks_next < p.n_k) {                                     // only when n_k exceeds the SM count
+        pos += hi - lo;
+        if (pos < end) {                                           // next segment (linear plan only)
+            ks = pos / p.n_sets;
+            lo = pos - ks * p.n_sets;
+            hi = min(p.n_sets, lo + (end - pos));
             #pragma unroll
             for (int i = 0; i < PF; ++i)
-                if (warp + i * NW < n_sets) load_set(buf[i], ks_next, warp + i * NW);
+                if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + warp + i * NW);
             __syncthreads();                                       // everyone is done reading this slice's LUT
         }
     }
+    TL_STAMP(4);
 
     if (p.n_k > 1) {
-        // ---------------- deterministic split-k reduction, dealt over the (k-slice CTA, warp) pairs of the chunk ----------------
-        for (int j = my + ny * warp; j < n_sets; j += ny * NW) {
-            const int row = row0 + j * kSetRows + lane;
+        // ---------------- deterministic split-k reduction, row sets dealt over all warps of the grid ----------------
+        using D = Dtype<DT>;
+        using T = typename D::T;
+        for (int j = warp * W + blockIdx.x; j < p.n_sets; j += W * NW) {
+            const int row = j * kSetRows + lane;
+            const bool live = row < p.O;
+            // epilogue operands are weights: request them before the (long) poll
+            T sc = D::from_f(1.f), bi = D::from_f(0.f);
+            if (p.scales && live) sc = static_cast<const T*>(p.scales)[row];
+            if (p.bias && live)   bi = static_cast<const T*>(p.bias)[row];
             const uint2* src = p.partial + row;
             float acc = 0.f;
-            for (int k0 = 0; k0 < p.n_k; k0 += 8) {
-                uint2 v[8];
+            for (int k0 = 0; k0 < p.n_k; k0 += 16) {              // 16 partials in flight per poll
+                uint2 v[16];
                 bool ok;
+                unsigned rounds = 0;
+                if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + 13] = globaltimer_ns();
                 do {
                     ok = true;
+                    ++rounds;
                     #pragma unroll
-                    for (int i = 0; i < 8; ++i)
+                    for (int i = 0; i < 16; ++i)
                         if (k0 + i < p.n_k) {
                             v[i] = ld_partial(src + (size_t)(k0 + i) * p.O_pad);
                             ok = ok && (v[i].y == tag);
                         }
+                    if (p.tl != nullptr && threadIdx.x == 0 && rounds == 1) p.tl[(size_t)blockIdx.x * 16 + 14] = globaltimer_ns();
                 } while (!__all_sync(0xffffffffu, ok));
+                if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + 7] = rounds;
                 #pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    if (k0 + i < p.n_k) acc += __uint_as_float(v[i].x);
+                for (int i = 0; i < 16; ++i)
+                    if (k0 + i < p.n_k) {
+                        acc += __uint_as_float(v[i].x);
+#if defined(LUTVQ_NO_RESET)
+#elif defined(LUTVQ_WEAK_RESET)
+                        const_cast<uint2*>(src)[(size_t)(k0 + i) * p.O_pad] = make_uint2(0u, 0u);
+#else
+                        st_partial(const_cast<uint2*>(src) + (size_t)(k0 + i) * p.O_pad, 0.f, 0u);   // consumed: hand the slot back
+#endif
+                    }
             }
-            if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, acc);
+            if (!waited) { pdl_wait(); waited = true; }        // y stores are ordered behind the previous kernel
+            if (live) {
+                T rr = D::from_f(acc);                                     // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
+                if (p.scales) rr = D::mul(rr, sc);                         // flat_output *= scales             (cuda_kernel.cpp:101)
+                if (p.bias)   rr = D::add(rr, bi);                         // flat_output += bias               (cuda_kernel.cpp:103)
+                static_cast<T*>(p.y)[row] = rr;
+            }
         }
     }
-    // ---------------- last CTA out bumps the epoch (every CTA has read it by then) ----------------
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned total = gridDim.x * gridDim.y;
-        const unsigned prev = atomicAdd(&p.hdr->done, 1u);
-        if (prev == total - 1) {
-            p.hdr->done = 0u;
-            p.hdr->epoch = tag;
-        }
-    }
+    TL_STAMP(5);
+    if (!waited) pdl_wait();                                       // completion stays stream-ordered
+    TL_STAMP(6);
 }
 
 // [k-slice][set][tile][lane] x 16 B register images from reference-layout codes (see file header)
@@ -355,18 +485,34 @@ __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __r
 // ---------------------------------------------------------------------------------------------------
 struct GemvTuning { int nw = 8, pf = 2, ctas_per_sm = 1; };
 static GemvTuning g_tuning;
+static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][8] stamps
+static unsigned g_timeline_seq = 0;
+void gemv_set_timeline(void* buf) { g_timeline = static_cast<unsigned long long*>(buf); g_timeline_seq = 0; }
 
-struct GemvPlan { int n_k, ny, n_chunks, sets_per_chunk, n_sets_total; };
+struct GemvPlan { int n_k, n_sets, W, aligned, q, r, max_range; };
 
+// One worker (CTA) per SM.  Cost model in units of one 32-row set of gather work; a LUT build costs about 10.
 static GemvPlan plan_gemv(int O, int G, int sm_count) {
     GemvPlan pl;
     pl.n_k = ceil_div(G * 2, kSliceTables);
-    pl.ny = pl.n_k < sm_count ? pl.n_k : sm_count;      // whole grid co-resident: the split-k reducers poll their peers
-    pl.n_sets_total = ceil_div(O, kSetRows);
-    int n_r = sm_count / pl.ny;
-    if (n_r < 1) n_r = 1;
-    pl.sets_per_chunk = ceil_div(pl.n_sets_total, n_r);
-    pl.n_chunks = ceil_div(pl.n_sets_total, pl.sets_per_chunk);
+    pl.n_sets = ceil_div(O, kSetRows);
+    const long long T = (long long)pl.n_k * pl.n_sets;
+    pl.W = (int)(T < sm_count ? T : sm_count);
+    if (pl.W > 1024) pl.W = 1024;                                  // worker_range's magic division is exact up to 1024
+    const int kBuildCost = 10;
+    const long long per = (T + pl.W - 1) / pl.W;
+    const long long lin_builds = 1 + (per + pl.n_sets - 1) / pl.n_sets;            // a range of `per` items touches at most this many slices
+    const long long cost_linear = per + kBuildCost * (lin_builds > pl.n_k ? pl.n_k : lin_builds);
+    pl.aligned = 0; pl.q = 0; pl.r = 0;
+    pl.max_range = (int)per;
+    if (pl.n_k <= pl.W) {
+        const int q = pl.W / pl.n_k;
+        const long long cost_aligned = (pl.n_sets + q - 1) / q + kBuildCost;
+        if (cost_aligned <= cost_linear) {
+            pl.aligned = 1; pl.q = q; pl.r = pl.W % pl.n_k;
+            pl.max_range = (pl.n_sets + q - 1) / q;
+        }
+    }
     return pl;
 }
 
@@ -393,7 +539,7 @@ int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStrea
 }
 
 template <int DT, bool PACKED, int NW, int PF>
-static int launch_variant(const GemvParams& p, dim3 grid, cudaStream_t stream, bool pdl) {
+static int launch_variant(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
     auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF>;
     static thread_local int attr_device = -1;
     int dev = 0;
@@ -403,9 +549,9 @@ static int launch_variant(const GemvParams& p, dim3 grid, cudaStream_t stream, b
         attr_device = dev;
     }
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = grid;
+    cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(NW * 32);
-    cfg.dynamicSmemBytes = kSliceBytes;
+    cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -417,15 +563,15 @@ static int launch_variant(const GemvParams& p, dim3 grid, cudaStream_t stream, b
 }
 
 template <int DT, bool PACKED>
-static int launch_tuned(const GemvParams& p, dim3 grid, cudaStream_t stream, bool pdl) {
+static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
     const GemvTuning t = g_tuning;
-    if (t.nw == 8 && t.pf == 2)  return launch_variant<DT, PACKED, 8, 2>(p, grid, stream, pdl);
-    if (t.nw == 8 && t.pf == 3)  return launch_variant<DT, PACKED, 8, 3>(p, grid, stream, pdl);
-    if (t.nw == 8 && t.pf == 1)  return launch_variant<DT, PACKED, 8, 1>(p, grid, stream, pdl);
-    if (t.nw == 16 && t.pf == 1) return launch_variant<DT, PACKED, 16, 1>(p, grid, stream, pdl);
-    if (t.nw == 16 && t.pf == 2) return launch_variant<DT, PACKED, 16, 2>(p, grid, stream, pdl);
-    if (t.nw == 4 && t.pf == 2)  return launch_variant<DT, PACKED, 4, 2>(p, grid, stream, pdl);
-    if (t.nw == 4 && t.pf == 4)  return launch_variant<DT, PACKED, 4, 4>(p, grid, stream, pdl);
+    if (t.nw == 8 && t.pf == 2)  return launch_variant<DT, PACKED, 8, 2>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 3)  return launch_variant<DT, PACKED, 8, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1)  return launch_variant<DT, PACKED, 8, 1>(p, grid, smem, stream, pdl);
+    if (t.nw == 16 && t.pf == 1) return launch_variant<DT, PACKED, 16, 1>(p, grid, smem, stream, pdl);
+    if (t.nw == 4 && t.pf == 4)  return launch_variant<DT, PACKED, 4, 4>(p, grid, smem, stream, pdl);
+    if (t.nw == 4 && t.pf == 3)  return launch_variant<DT, PACKED, 4, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 4 && t.pf == 2)  return launch_variant<DT, PACKED, 4, 2>(p, grid, smem, stream, pdl);
     return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d", t.nw, t.pf);
 }
 
@@ -443,14 +589,21 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
     GemvParams p;
     p.codes = static_cast<const uint8_t*>(codes);
     p.x = x; p.codebook = codebook; p.y = y; p.scales = scales; p.bias = bias;
-    p.hdr = static_cast<WsHeader*>(ws);
     p.partial = reinterpret_cast<uint2*>(static_cast<uint8_t*>(ws) + kWsHeaderBytes);
-    p.O = O; p.O_pad = pl.n_sets_total * kSetRows; p.G = G; p.n_k = pl.n_k;
-    p.sets_per_chunk = pl.sets_per_chunk; p.n_sets_total = pl.n_sets_total; p.flags = flags;
-    const dim3 grid(pl.n_chunks, pl.ny);
+    p.O = O; p.O_pad = pl.n_sets * kSetRows; p.G = G; p.n_k = pl.n_k; p.n_sets = pl.n_sets;
+    p.aligned = pl.aligned; p.q = pl.q; p.r = pl.r;
+    p.magic_q = p.magic_q1 = 0; p.base_q = p.rem_q = p.base_q1 = p.rem_q1 = 0;
+    if (pl.aligned) {
+        p.magic_q = ((1u << 20) + pl.q - 1) / pl.q;   p.magic_q1 = ((1u << 20) + pl.q) / (pl.q + 1);
+        p.base_q = pl.n_sets / pl.q;                  p.rem_q = pl.n_sets % pl.q;
+        p.base_q1 = pl.n_sets / (pl.q + 1);           p.rem_q1 = pl.n_sets % (pl.q + 1);
+    }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
-    if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, grid, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, grid, stream, pdl);
-    if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, grid, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, grid, stream, pdl);
+    p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
+    p.tl = g_timeline ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
+    const size_t smem = kSliceBytes;
+    if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, pl.W, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, pl.W, smem, stream, pdl);
+    if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, pl.W, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, pl.W, smem, stream, pdl);
     return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
 }
 
@@ -465,8 +618,8 @@ void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk) {
     if (get_device_info(&di) == 0) sm = di.sm_count;
     GemvPlan pl = plan_gemv(O, I / 8, sm);
     if (n_k) *n_k = pl.n_k;
-    if (n_chunks) *n_chunks = pl.n_chunks;
-    if (rows_per_chunk) *rows_per_chunk = pl.sets_per_chunk * kSetRows;
+    if (n_chunks) *n_chunks = pl.W;
+    if (rows_per_chunk) *rows_per_chunk = pl.max_range * kSetRows;
 }
 
 }  // namespace lutvq
