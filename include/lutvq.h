@@ -24,7 +24,8 @@
  *   - returns 0 on success, a negative LUTVQ_E* code otherwise; lutvq_last_error() gives a thread-local
  *     message.  There is no CPU fallback: without a CUDA device every compute call fails with LUTVQ_ECUDA;
  *   - scratch memory is passed in (ws, ws_bytes); size it with lutvq_workspace_bytes().  A workspace must
- *     be zero-filled once before first use (cudaMemset) and may then be reused by calls ON THE SAME STREAM;
+ *     be zero-filled once before first use (cudaMemset); every call leaves it all-zero again, so it may be reused
+ *     by any later call ON THE SAME STREAM (any shape);
  *   - dtype is the storage/arithmetic type of x, codebooks, scales, bias, y (fp16 or bf16, the two types
  *     cuda_kernel.cpp:9-25 accepts).  Codes are int8 holding unsigned 8-bit indices
  *     (aqlm/../utils.py:24-31), layout [prob_m][prob_k/8][num_codebooks] exactly as QuantizedLinear.codes.
@@ -49,10 +50,13 @@ typedef enum { LUTVQ_F16 = 0, LUTVQ_BF16 = 1 } lutvq_dtype_t;
 /* flags for the *_ex entry points */
 #define LUTVQ_FLAG_LUT_FP16   1u  /* round LUT entries to fp16 (vq.py:285 semantics) before accumulation */
 #define LUTVQ_FLAG_NO_PDL     2u  /* do not use programmatic dependent launch for this call */
-#define LUTVQ_FLAG_X_READY    4u  /* caller's promise: x, scales and bias were NOT written by the kernel(s) immediately
-                                     preceding this call in the stream (e.g. the k/v projections after q, up after gate,
-                                     or a microbenchmark loop over one input).  The LUT build and the gather then overlap
-                                     the previous kernel; the workspace traffic and the y stores stay stream-ordered. */
+#define LUTVQ_FLAG_X_READY    4u  /* caller's promise: (1) x was NOT written by the kernel(s) immediately preceding this call
+                                     in the stream (e.g. the k/v projections after q, up after gate, or a microbenchmark
+                                     loop over resident inputs), and (2) ws is not used by any of the LUTVQ_XREADY_WS_RING - 1
+                                     calls before or after this one in the stream (rotate through a ring of workspaces).
+                                     The LUT build, the gather and the split-k reduction then overlap the previous kernel;
+                                     the y stores and the completion of the call stay stream-ordered. */
+#define LUTVQ_XREADY_WS_RING  8
 
 /* lutvq_lut_build lut_mode */
 #define LUTVQ_LUT_VQPY_FP16   0   /* bit-exact vq.py: fp16 products, numpy pairwise fp32 sum, fp16 entries */

@@ -116,8 +116,9 @@ static int matmat_rows(const void* x, const void* codes, int packed, const void*
                        const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, unsigned flags,
                        void* ws, size_t ws_bytes, void* stream) {
     if (int rc = check_2x8_common(codes, codebooks, prob_m, prob_k, dtype)) return rc;
-    LUTVQ_REQUIRE(x && y, "null x/y pointer");
     LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
+    if (batch == 0) return LUTVQ_OK;                                  // empty input: nothing to launch (pointers may be null)
+    LUTVQ_REQUIRE(x && y, "null x/y pointer");
     LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
     // cuda_kernel.cpp:404-414 loops the matvec over the flattened batch rows; so do we (one fused launch per row,
     // scale/bias folded into the kernel's epilogue instead of three extra elementwise kernels).
@@ -174,10 +175,10 @@ int lutvq_code2x8_matmat_dequant(const void* x, const void* codes, const void* c
                                  const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype, void* ws,
                                  size_t ws_bytes, void* stream) {
     if (int rc = check_2x8_common(codes, codebooks, prob_m, prob_k, dtype)) return rc;
-    LUTVQ_REQUIRE(x && y, "null x/y pointer");
     LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
-    LUTVQ_REQUIRE(aligned16(x) && aligned16(y), "x and y must be 16-byte aligned");
     if (batch == 0) return LUTVQ_OK;
+    LUTVQ_REQUIRE(x && y, "null x/y pointer");
+    LUTVQ_REQUIRE(aligned16(x) && aligned16(y), "x and y must be 16-byte aligned");
     return gemm_dequant_tc_launch(x, codes, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, ws, ws_bytes,
                                   static_cast<cudaStream_t>(stream));
 }

@@ -19,18 +19,23 @@
 // One CTA per SM per launch matters under programmatic dependent launch: consecutive launches then pair up
 // 1:1 on every SM (occupancy 2), instead of a 144-CTA grid doubling up on the 4 idle SMs and straggling.
 //
-// Cross-CTA split-k reduction: partial sums travel through L2 as 8-byte {value, epoch} words (flag-in-data,
-// no fence / no atomic on the critical path); the 32-row sets are dealt round-robin to all warps of the grid,
-// which poll the n_k partials of a set, add them IN FIXED k ORDER (deterministic) and apply the reference
-// epilogue order (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111).  All CTAs of a launch are
-// co-resident (grid <= #SMs, >= 1 slot per SM), which the polling relies on.
+// Cross-CTA split-k reduction: one 64-bit accumulator word per output row, (fixed-point sum << 8) | arrivals.  Each
+// (row, k-slice) partial is ONE integer atomic add executed at the row's L2 home slice; the atomic's return value
+// tells the contributor whether it was the last of the n_k, in which case it holds the complete sum, applies the
+// reference epilogue order (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111), writes y and zeroes the word.
+// Integer addition commutes => the result is bit-identical whatever the arrival order; nothing polls, nothing
+// needs the CTAs of a launch to be co-resident, and the workspace is self-cleaning (all zero between launches).
+// The return value is examined PF sets after the atomic was issued, so its L2 round trip hides behind lookups;
+// workers of different k-slices walk their rows in rotated order so the n_k atomics of a row do not collide.
+// (Measured alternatives on B200, 4096x11008: {value, tag} words polled through L2 cost 1.7-2.7 us per launch
+// after the last store -- one poll round of 16 loads took 2.4 us -- against ~1 us for the atomic scheme.)
 //
-// Stream overlap (programmatic dependent launch).  Weights (codes, codebooks) never depend on the previous
-// kernel, so the first tile sets are requested into registers and the rest of the worker's share is pushed
-// HBM -> L2 BEFORE griddepcontrol.wait.  With LUTVQ_FLAG_X_READY the caller additionally promises that x /
-// scales / bias were not written by the kernel(s) immediately preceding this call in the stream; then the LUT
-// build and the whole gather also run before the wait (row sums parked in shared memory) and only the
-// workspace traffic, the reduction and the y stores are ordered behind the previous kernel.
+// Stream overlap (programmatic dependent launch).  Weights (codes, codebooks, scales, bias) never depend on the
+// previous kernel, so the first tile sets are requested into registers and the rest of the worker's share is pushed
+// HBM -> L2 BEFORE griddepcontrol.wait.  With LUTVQ_FLAG_X_READY the caller additionally promises that x was not
+// written by the kernel(s) immediately preceding this call in the stream and that the workspace is not shared with
+// them (include/lutvq.h); then the LUT build, the gather and the split-k atomics all run before the wait and only
+// the y stores (and this kernel's completion) are ordered behind the previous kernel.
 //
 // Two code layouts feed the same gather loop:
 //   reference  int8 [O][G][2] exactly as QuantizedLinear.codes: a warp's 128-bit load touches 8 rows x 64 B;
@@ -44,7 +49,6 @@
 namespace lutvq {
 
 constexpr size_t kWsHeaderBytes = 256;        // reserved
-constexpr uint32_t kTagFull = 0x600DF00Du;    // tag of a partial that has been written and not yet consumed
 
 struct GemvParams {
     const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
@@ -53,7 +57,7 @@ struct GemvParams {
     void* y;                  // [O]
     const void* scales;       // [O] or null
     const void* bias;         // [O] or null
-    uint2* partial;           // [n_k][O_pad] {value bits, tag}; tag == 0 between launches
+    unsigned long long* acc;  // [O_pad] split-k accumulator words, zero between launches
     int O, O_pad, G, n_k, n_sets;
     int aligned;              // 1: aligned plan (q, r below), 0: linear plan
     int q, r;                 // aligned plan: W = q*n_k + r; slices < r have q+1 workers
@@ -90,19 +94,33 @@ template <> struct MmaK8<LUTVQ_BF16> {
 __device__ __forceinline__ void sts_v4(uint32_t addr, float a, float b, float c, float d) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
-// flag-in-data partial sums: one naturally aligned 64-bit word {value bits, tag} is written / read as a unit.
-// Both sides use L1-bypassing (.cg) accesses, so L2 is the meeting point.  They are deliberately NOT .relaxed.gpu /
-// .volatile: measured on B200, a warp's strong loads are not pipelined (16 polls = 16 serial L2 round trips,
-// 2.4 us), whereas 16 .cg loads overlap (one round trip).  An aligned 8-byte access is a single transaction, so
-// value and tag always travel together.
-__device__ __forceinline__ void st_partial(uint2* p, float v, uint32_t tag) {
-    const unsigned long long w = ((unsigned long long)tag << 32) | __float_as_uint(v);
-    asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p), "l"(w) : "memory");
+// Split-k accumulator word (one per output row, zero between launches):  (fixed-point sum << 8) | arrivals.
+// Every (row, k-slice) partial is ONE 64-bit integer atomic add performed at the row's L2 home slice; integer
+// addition commutes, so the result is bit-identical whatever the arrival order.  The atomic returns the old word:
+// the contributor that sees arrivals == n_k - 1 holds the complete sum (old + its own), writes y and zeroes the word.
+// Fixed point: 2^-kFxBits per unit in a 56-bit signed field.  fp16 (|y| <= 65504): 2^-30 -> +-3.4e7 of range with
+// 9.3e-10 resolution (below half an ulp of every normal fp16 output).  bf16: 2^-20 -> +-3.4e10.  Partials are
+// saturated to the field (a non-finite partial saturates too: the output becomes +-inf in fp16, not NaN).
+template <int DT> struct Fx;
+template <> struct Fx<LUTVQ_F16>  { static constexpr float scale = 1073741824.f, inv = 1.f / 1073741824.f; };   // 2^30
+template <> struct Fx<LUTVQ_BF16> { static constexpr float scale = 1048576.f,    inv = 1.f / 1048576.f; };      // 2^20
+
+template <int DT>
+__device__ __forceinline__ unsigned long long fx_contribution(float v) {
+    // clamp so that the sum of n_k <= 255 contributions cannot leave the signed 56-bit field: |fx| < 2^47
+    float sv = v * Fx<DT>::scale;
+    sv = fminf(fmaxf(sv, -1.4e14f), 1.4e14f);                   // NaN -> -1.4e14 (fmaxf/fminf drop NaN), 1.4e14 < 2^47
+    const long long fx = __float2ll_rn(sv);
+    return ((unsigned long long)fx << 8) + 1ull;
 }
-__device__ __forceinline__ uint2 ld_partial(const uint2* p) {
-    unsigned long long w;
-    asm volatile("ld.global.cg.b64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
-    return make_uint2((uint32_t)w, (uint32_t)(w >> 32));
+__device__ __forceinline__ unsigned long long atom_add_u64(unsigned long long* p, unsigned long long v) {
+    unsigned long long old;
+    asm volatile("atom.relaxed.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
+    return old;
+}
+template <int DT>
+__device__ __forceinline__ float fx_total(unsigned long long word) {
+    return (float)((long long)word >> 8) * Fx<DT>::inv;          // arithmetic shift drops the arrival count
 }
 // asynchronous HBM -> L2 prefetch of a contiguous range (no registers, no shared memory)
 __device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
@@ -196,6 +214,14 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     };
 
     TL_STAMP(8);
+    // The workers of different k-slices walk the same rows; each starts at a slice-dependent rotation of its own
+    // range so that the n_k atomics of one row are spread over the whole gather instead of colliding at one instant.
+    auto set_of = [&](int i, int ks_, int lo_, int hi_) {
+        const int n = hi_ - lo_;
+        int v = i + (int)(((unsigned)ks_ * (unsigned)n) / (unsigned)p.n_k);
+        if (v >= n) v -= n;
+        return lo_ + v;
+    };
     // first segment of this worker's range: slice ks, sets [lo, hi)
     int pos = begin;
     int ks = (begin < end) ? (int)((unsigned)begin / (unsigned)p.n_sets) : 0;
@@ -210,7 +236,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     CodeRegs buf[PF];
     #pragma unroll
     for (int i = 0; i < PF; ++i)
-        if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + warp + i * NW);
+        if (lo + warp + i * NW < hi) load_set(buf[i], ks, set_of(warp + i * NW, ks, lo, hi));
     TL_STAMP(9);
     if (PACKED) {
         // the worker's whole share is ONE contiguous range of the packed image (linear item index * 2048 B)
@@ -229,6 +255,17 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             for (int r = l * kSetRows + threadIdx.x; r < r1; r += NW * 32)
                 l2_prefetch_line(p.codes + (size_t)r * row_bytes + off);
             ppos += h - l;
+        }
+    }
+    if (p.n_k > 1 && begin < end) {
+        // scale / bias of this worker's first-segment rows: 64 B per set each, pulled into L2 for the in-loop fetch
+        const int nl = (hi - lo + 1) / 2;                             // 128-byte lines
+        if ((int)threadIdx.x < nl) {
+            const size_t off = (size_t)lo * 64 + (size_t)threadIdx.x * 128;
+            if (off < (size_t)p.O * 2) {
+                if (p.scales) l2_prefetch_line(static_cast<const uint8_t*>(p.scales) + off);
+                if (p.bias)   l2_prefetch_line(static_cast<const uint8_t*>(p.bias) + off);
+            }
         }
     }
     if (warp == NW - 1) {
@@ -259,7 +296,6 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     const bool xready = (p.flags & LUTVQ_FLAG_X_READY) != 0;
     bool waited = !xready;
     if (!xready) pdl_wait();    // x and the workspace belong to the previous kernel until here
-    constexpr uint32_t tag = kTagFull;
     TL_STAMP(2);
 
     // PRMT operands (lut_layout.h): byte0 <- lm, byte1 <- code byte, bytes 2,3 <- 0.  The slice base and the
@@ -275,6 +311,34 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
     bool first_seg = true;
+
+    // ---- split-k completion: see the accumulator word comment above ----
+    using D = Dtype<DT>;
+    using T = typename D::T;
+    // A contribution's atomic is issued at the end of its set and its return value is examined PF sets later, so the
+    // L2 round trip hides behind lookups.  Pending state per slot: the returned word, the partial, the row and the
+    // (scale, bias) pair -- both weights, fetched with the atomic so that the last arriver has them at hand.
+    unsigned long long pend_old[PF];
+    float pend_keep[PF];
+    int pend_row[PF];
+    unsigned short pend_sc[PF], pend_bi[PF];
+    bool pend_valid[PF];
+    #pragma unroll
+    for (int i = 0; i < PF; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_sc[i] = pend_bi[i] = 0; pend_valid[i] = false; }
+    const unsigned last_count = (unsigned)p.n_k - 1u;
+    auto finish_row = [&](unsigned long long old, float keep, int row, unsigned short scb, unsigned short bib) {
+        if ((unsigned)(old & 255ull) == last_count) {              // this lane delivered the last partial of `row`
+            if (!waited) { pdl_wait(); waited = true; }            // y stores are ordered behind the previous kernel
+            const float total = fx_total<DT>(old + fx_contribution<DT>(keep));
+            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p.acc + row), "l"(0ull) : "memory");   // hand the word back
+            if (row < p.O) {
+                T rr = D::from_f(total);                                               // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
+                if (p.scales) rr = D::mul(rr, *reinterpret_cast<const T*>(&scb));      // flat_output *= scales             (cuda_kernel.cpp:101)
+                if (p.bias)   rr = D::add(rr, *reinterpret_cast<const T*>(&bib));      // flat_output += bias               (cuda_kernel.cpp:103)
+                static_cast<T*>(p.y)[row] = rr;
+            }
+        }
+    };
 
     while (pos < end) {
         // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
@@ -338,8 +402,16 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         for (int it = 0; lo + it * NW + warp < hi; it += PF) {
             #pragma unroll
             for (int st = 0; st < PF; ++st) {
-                const int set = lo + (it + st) * NW + warp;
-                if (set < hi) {                                     // warp-uniform
+                const int li = (it + st) * NW + warp;               // local index in this segment
+                if (lo + li < hi) {                                 // warp-uniform
+                    const int set = set_of(li, ks, lo, hi);
+                    const int row = set * kSetRows + lane;
+                    // epilogue operands are weights: fetch them now, a whole set of lookups before they are needed
+                    unsigned short sc_raw = 0, bi_raw = 0;
+                    if (p.n_k > 1 && row < p.O) {
+                        if (p.scales) sc_raw = static_cast<const unsigned short*>(p.scales)[row];
+                        if (p.bias)   bi_raw = static_cast<const unsigned short*>(p.bias)[row];
+                    }
                     float acc[4][2];
                     if (p.flags & 0x100u) {                         // DEBUG: no lookups (pure code streaming)
                         #pragma unroll
@@ -356,18 +428,13 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                             for (int t = 0; t < 4; ++t) {
                                 const uint32_t ad = __byte_perm(buf[st].w[t][c], lm[c >> 1][d], sel[d]);
                                 
-#ifdef LUTVQ_VOLATILE_LDS
-                                float v;
-                                asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(lut_base + ad + stream_imm(c)));
-#else
                                 const float v = *reinterpret_cast<const float*>(smem_raw + ad + stream_imm(c));
-#endif
                                 if (c == 0 && d < 2) acc[t][d] = v;
                                 else                 acc[t][d & 1] += v;
                             }
                     }
                     // refill this stage with the set PF iterations ahead before the (short) reduction
-                    if (set + PF * NW < hi && !(p.flags & 0x200u)) load_set(buf[st], ks, set + PF * NW);   // 0x200 DEBUG: no streaming
+                    if (lo + li + PF * NW < hi && !(p.flags & 0x200u)) load_set(buf[st], ks, set_of(li + PF * NW, ks, lo, hi));   // 0x200 DEBUG: no streaming
                     float a0 = acc[0][0] + acc[0][1], a1 = acc[1][0] + acc[1][1];
                     float a2 = acc[2][0] + acc[2][1], a3 = acc[3][0] + acc[3][1];
                     // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
@@ -377,19 +444,16 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                     k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
                     float keep = b3 ? k1 : k0, give = b3 ? k0 : k1;
                     keep += __shfl_xor_sync(0xffffffffu, give, 8);
-                    const int row = set * kSetRows + lane;
                     if (p.n_k == 1) {
                         if (!waited) { pdl_wait(); waited = true; }
                         if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
                     } else {
-                        if (p.flags & 0x400u) {                     // DEBUG: weak store
-                            const unsigned long long wv = ((unsigned long long)tag << 32) | __float_as_uint(keep);
-                            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p.partial + (size_t)ks * p.O_pad + row), "l"(wv) : "memory");
-                        } else if (p.flags & 0x800u) {              // DEBUG: no store at all (results wrong)
-                        } else
-                        st_partial(p.partial + (size_t)ks * p.O_pad + row, keep, tag);
+                        // finish the atomic this slot issued PF sets ago, then issue this set's
+                        if (pend_valid[st]) finish_row(pend_old[st], pend_keep[st], pend_row[st], pend_sc[st], pend_bi[st]);
+                        pend_row[st] = row; pend_valid[st] = true; pend_keep[st] = keep;
+                        pend_sc[st] = sc_raw; pend_bi[st] = bi_raw;
+                        pend_old[st] = atom_add_u64(p.acc + row, fx_contribution<DT>(keep));
                     }
-                    if (p.tl != nullptr && threadIdx.x == 0 && it + st < 2) p.tl[(size_t)blockIdx.x * 16 + 11 + it + st] = globaltimer_ns();
                 }
             }
         }
@@ -400,63 +464,15 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             hi = min(p.n_sets, lo + (end - pos));
             #pragma unroll
             for (int i = 0; i < PF; ++i)
-                if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + warp + i * NW);
+                if (lo + warp + i * NW < hi) load_set(buf[i], ks, set_of(warp + i * NW, ks, lo, hi));
             __syncthreads();                                       // everyone is done reading this slice's LUT
         }
     }
     TL_STAMP(4);
 
-    if (p.n_k > 1) {
-        // ---------------- deterministic split-k reduction, row sets dealt over all warps of the grid ----------------
-        using D = Dtype<DT>;
-        using T = typename D::T;
-        for (int j = warp * W + blockIdx.x; j < p.n_sets; j += W * NW) {
-            const int row = j * kSetRows + lane;
-            const bool live = row < p.O;
-            // epilogue operands are weights: request them before the (long) poll
-            T sc = D::from_f(1.f), bi = D::from_f(0.f);
-            if (p.scales && live) sc = static_cast<const T*>(p.scales)[row];
-            if (p.bias && live)   bi = static_cast<const T*>(p.bias)[row];
-            const uint2* src = p.partial + row;
-            float acc = 0.f;
-            for (int k0 = 0; k0 < p.n_k; k0 += 16) {              // 16 partials in flight per poll
-                uint2 v[16];
-                bool ok;
-                unsigned rounds = 0;
-                if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + 13] = globaltimer_ns();
-                do {
-                    ok = true;
-                    ++rounds;
-                    #pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (k0 + i < p.n_k) {
-                            v[i] = ld_partial(src + (size_t)(k0 + i) * p.O_pad);
-                            ok = ok && (v[i].y == tag);
-                        }
-                    if (p.tl != nullptr && threadIdx.x == 0 && rounds == 1) p.tl[(size_t)blockIdx.x * 16 + 14] = globaltimer_ns();
-                } while (!__all_sync(0xffffffffu, ok));
-                if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + 7] = rounds;
-                #pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (k0 + i < p.n_k) {
-                        acc += __uint_as_float(v[i].x);
-#if defined(LUTVQ_NO_RESET)
-#elif defined(LUTVQ_WEAK_RESET)
-                        const_cast<uint2*>(src)[(size_t)(k0 + i) * p.O_pad] = make_uint2(0u, 0u);
-#else
-                        st_partial(const_cast<uint2*>(src) + (size_t)(k0 + i) * p.O_pad, 0.f, 0u);   // consumed: hand the slot back
-#endif
-                    }
-            }
-            if (!waited) { pdl_wait(); waited = true; }        // y stores are ordered behind the previous kernel
-            if (live) {
-                T rr = D::from_f(acc);                                     // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
-                if (p.scales) rr = D::mul(rr, sc);                         // flat_output *= scales             (cuda_kernel.cpp:101)
-                if (p.bias)   rr = D::add(rr, bi);                         // flat_output += bias               (cuda_kernel.cpp:103)
-                static_cast<T*>(p.y)[row] = rr;
-            }
-        }
-    }
+    #pragma unroll
+    for (int i = 0; i < PF; ++i)
+        if (pend_valid[i]) finish_row(pend_old[i], pend_keep[i], pend_row[i], pend_sc[i], pend_bi[i]);
     TL_STAMP(5);
     if (!waited) pdl_wait();                                       // completion stays stream-ordered
     TL_STAMP(6);
@@ -517,9 +533,9 @@ static GemvPlan plan_gemv(int O, int G, int sm_count) {
 }
 
 size_t gemv_workspace_bytes(int O, int G) {
-    const int n_k = ceil_div(G * 2, kSliceTables);
+    (void)G;
     const size_t O_pad = (size_t)ceil_div(O, kSetRows) * kSetRows;
-    return kWsHeaderBytes + (size_t)n_k * O_pad * sizeof(uint2);
+    return kWsHeaderBytes + O_pad * sizeof(unsigned long long);
 }
 
 size_t gemv_packed_bytes(int O, int G) {
@@ -586,10 +602,11 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
     const size_t need = gemv_workspace_bytes(O, G);
     LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= need, "workspace too small: need %zu bytes, got %zu", need, ws_bytes);
     LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
+    if (pl.n_k > 255) return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds 255 (prob_k <= 65280)", I, pl.n_k);
     GemvParams p;
     p.codes = static_cast<const uint8_t*>(codes);
     p.x = x; p.codebook = codebook; p.y = y; p.scales = scales; p.bias = bias;
-    p.partial = reinterpret_cast<uint2*>(static_cast<uint8_t*>(ws) + kWsHeaderBytes);
+    p.acc = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ws) + kWsHeaderBytes);
     p.O = O; p.O_pad = pl.n_sets * kSetRows; p.G = G; p.n_k = pl.n_k; p.n_sets = pl.n_sets;
     p.aligned = pl.aligned; p.q = pl.q; p.r = pl.r;
     p.magic_q = p.magic_q1 = 0; p.base_q = p.rem_q = p.base_q1 = p.rem_q1 = 0;

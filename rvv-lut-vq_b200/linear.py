@@ -44,6 +44,8 @@ class QuantizedLinear(nn.Module):
             self.bias = nn.Parameter(torch.empty(out_features, **factory_kwargs), requires_grad=False)
         else:
             self.register_parameter("bias", None)
+        self._packed = None          # GEMV code image, built on first use (prepare_matmul_op analogue, inference.py:74-83)
+        self.x_ready = False         # set True when this layer's input is never the output of the kernel right before it
 
     def _check_format(self, input: torch.Tensor) -> None:
         fmt = (self.num_codebooks, self.codebook_size, self.out_group_size, self.in_group_size)
@@ -60,5 +62,8 @@ class QuantizedLinear(nn.Module):
     def forward(self, input: torch.Tensor) -> torch.Tensor:
         self._check_format(input)
         if self.use_gemv_rule(input):
-            return ops.code2x8_matmat(input, self.codes, self.codebooks, self.scales, self.bias)
+            if self._packed is None or self._packed.device != input.device:
+                self._packed = ops.code2x8_prepack(self.codes)
+            return ops.code2x8_matmat_packed(input, self._packed, self.out_features, self.codebooks, self.scales,
+                                             self.bias, x_ready=self.x_ready)
         return ops.code2x8_matmat_dequant(input, self.codes, self.codebooks, self.scales, self.bias)

@@ -48,15 +48,27 @@ def _stream(dev: torch.device) -> ctypes.c_void_p:
     return ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
 
 
-def workspace(dev: torch.device, prob_m: int, prob_k: int) -> torch.Tensor:
-    """Zero-initialised scratch, cached per (device, stream) as include/lutvq.h requires."""
-    need = int(lib().lutvq_workspace_bytes(prob_m, prob_k))
+XREADY_WS_RING = 8          # include/lutvq.h LUTVQ_XREADY_WS_RING
+_ws_ring_pos: Dict[Tuple[int, int], int] = {}
+
+
+def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False) -> torch.Tensor:
+    """Zero-initialised scratch, cached per (device, stream) as include/lutvq.h requires.  The cache holds a ring of
+    XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True`` (LUTVQ_FLAG_X_READY calls) steps through
+    the ring so that overlapping launches never share a region.  (Inside a CUDA graph the region is baked at capture:
+    keep the number of X_READY calls per graph a multiple of XREADY_WS_RING.)"""
+    need = (int(lib().lutvq_workspace_bytes(prob_m, prob_k)) + 255) // 256 * 256
     key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
     ws = _workspaces.get(key)
-    if ws is None or ws.numel() < need:
-        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+    if ws is None or ws.numel() < need * XREADY_WS_RING:
+        ws = torch.zeros(max(need, 1 << 17) * XREADY_WS_RING, dtype=torch.uint8, device=dev)
         _workspaces[key] = ws
-    return ws
+    slot = ws.numel() // XREADY_WS_RING
+    i = 0
+    if rotate:
+        i = _ws_ring_pos.get(key, 0)
+        _ws_ring_pos[key] = (i + 1) % XREADY_WS_RING
+    return ws[i * slot:(i + 1) * slot]
 
 
 def _flat_scales(scales: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -85,7 +97,7 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
     codes_c, cb_c = codes.contiguous(), codebooks.contiguous()
     sc, bi = _flat_scales(scales), (None if bias is None else bias.contiguous())
     with torch.cuda.device(dev):
-        ws = workspace(dev, out_features, in_features)
+        ws = workspace(dev, out_features, in_features, rotate=bool(flags and flags & _lib.FLAG_X_READY))
         fn = getattr(lib(), fn_name)
         if flags is None:
             rc = fn(_ptr(flat_input), _ptr(codes_c), _ptr(cb_c), _ptr(sc), _ptr(bi), _ptr(flat_output), batch,
@@ -98,11 +110,44 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
 
 
 def code2x8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
-                   bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False) -> torch.Tensor:
-    """cuda_kernel.cpp:387-421 (+ epilogue :95-111): the decode / small-batch path (fused LUT-GEMV per row)."""
-    if lut_fp16:
-        return _matmat("lutvq_code2x8_matmat_ex", input, codes, codebooks, scales, bias, _lib.FLAG_LUT_FP16)
+                   bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False, x_ready: bool = False) -> torch.Tensor:
+    """cuda_kernel.cpp:387-421 (+ epilogue :95-111): the decode / small-batch path (fused LUT-GEMV per row).
+    ``x_ready``: LUTVQ_FLAG_X_READY (input not produced by the kernel just before this call on the stream)."""
+    flags = (_lib.FLAG_LUT_FP16 if lut_fp16 else 0) | (_lib.FLAG_X_READY if x_ready else 0)
+    if flags:
+        return _matmat("lutvq_code2x8_matmat_ex", input, codes, codebooks, scales, bias, flags)
     return _matmat("lutvq_code2x8_matmat", input, codes, codebooks, scales, bias)
+
+
+def code2x8_prepack(codes: torch.Tensor) -> torch.Tensor:
+    """One-off re-layout of QuantizedLinear.codes for the GEMV (the counterpart of the CPU permutation in
+    inference.py:78-83); returns an opaque uint8 image for code2x8_matmat_packed."""
+    dev = _require_cuda(codes)
+    prob_m, prob_k = codes.size(0), codes.size(1) * 8
+    packed = torch.empty(int(lib().lutvq_code2x8_packed_bytes(prob_m, prob_k)), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code2x8_prepack(_ptr(codes.contiguous()), _ptr(packed), prob_m, prob_k, _stream(dev)))
+    return packed
+
+
+def code2x8_matmat_packed(input: torch.Tensor, packed: torch.Tensor, out_features: int, codebooks: torch.Tensor,
+                          scales: torch.Tensor, bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False,
+                          x_ready: bool = False) -> torch.Tensor:
+    """code2x8_matmat on a prepacked code image (bit-identical results)."""
+    dtype = check_use_bfloat16(input)
+    dev = _require_cuda(input, packed, codebooks, scales, bias)
+    in_features = input.size(-1)
+    flat_input = input.reshape(-1, in_features).contiguous()
+    batch = flat_input.size(0)
+    flat_output = torch.empty((batch, out_features), dtype=input.dtype, device=dev)
+    flags = (_lib.FLAG_LUT_FP16 if lut_fp16 else 0) | (_lib.FLAG_X_READY if x_ready else 0)
+    sc, bi = _flat_scales(scales), (None if bias is None else bias.contiguous())
+    with torch.cuda.device(dev):
+        ws = workspace(dev, out_features, in_features, rotate=x_ready)
+        check(lib().lutvq_code2x8_matmat_packed(_ptr(flat_input), _ptr(packed), _ptr(codebooks.contiguous()), _ptr(sc), _ptr(bi),
+                                                _ptr(flat_output), batch, out_features, in_features, dtype, flags,
+                                                _ptr(ws), ws.numel(), _stream(dev)))
+    return flat_output.reshape(tuple(input.shape[:-1]) + (out_features,))
 
 
 def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,

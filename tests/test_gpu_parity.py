@@ -188,10 +188,19 @@ def test_full_size_sweep(pkg, ops, orc, I, O):
     # deterministic: fixed-order split-k reduction
     y2 = ops.code2x8_matmat(x, codes, cb, sc, None)
     assert torch.equal(y, y2)
-    # permuting output rows of (codes, scales) permutes y bit-for-bit
-    perm = torch.randperm(O, device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+    # permuting output rows IN BLOCKS OF 32 (the kernel's row set; a row's fp32 summation order depends only on
+    # its position inside the set) permutes y bit-for-bit: the split-k reduction is integer and order-free
+    nblk = O // 32
+    bperm = torch.randperm(nblk, device="cuda", generator=torch.Generator(device="cuda").manual_seed(0))
+    perm = (bperm[:, None] * 32 + torch.arange(32, device="cuda")[None, :]).reshape(-1)
     yp = ops.code2x8_matmat(x, codes[perm].contiguous(), cb, sc[perm].contiguous(), None)
     assert torch.equal(yp[0], y[0][perm])
+    # the prepacked code image and the X_READY overlap mode give bit-identical results
+    packed = ops.code2x8_prepack(codes)
+    assert torch.equal(ops.code2x8_matmat_packed(x, packed, O, cb, sc, None), y)
+    for _ in range(3):
+        assert torch.equal(ops.code2x8_matmat_packed(x, packed, O, cb, sc, None, x_ready=True), y)
+        assert torch.equal(ops.code2x8_matmat(x, codes, cb, sc, None, x_ready=True), y)
     # dequantize (bit-exact vs oracle on a row sample) and the dense check of benchmark_rq_gemm_gpu.py:99-109
     W = ops.code2x8_dequant(codes, cb, sc)
     rows = np.linspace(0, O - 1, 64).astype(int)
@@ -282,6 +291,26 @@ def test_cuda_graph_and_pdl(pkg, ops, orc):
         graph.replay()
     torch.cuda.synchronize()
     assert torch.equal(out, eager)
+
+
+def test_x_ready_overlapping_launches(pkg, ops, orc):
+    """LUTVQ_FLAG_X_READY: a burst of independent GEMVs (resident inputs, rotating workspaces) overlaps on the GPU;
+    every output must still equal the stream-ordered result, and the workspace must come back all-zero."""
+    from rvv_lut_vq_b200 import synth
+    I, O = 4096, 1536
+    Ls = [synth.make_layer_np(I, O, seed=40 + i, scales="randn") for i in range(6)]
+    dev = [{k: cu(v) for k, v in L.items() if v is not None and k != "idx"} for L in Ls]
+    packed = [ops.code2x8_prepack(d["codes"]) for d in dev]
+    ref = [ops.code2x8_matmat(d["x"], d["codes"], d["codebooks"], d["scales"], None) for d in dev]
+    torch.cuda.synchronize()
+    for rep in range(4):
+        outs = [ops.code2x8_matmat_packed(d["x"], pk, O, d["codebooks"], d["scales"], None, x_ready=True)
+                for d, pk in zip(dev, packed)]
+        for o, r in zip(outs, ref):
+            assert torch.equal(o, r)
+    torch.cuda.synchronize()
+    for ws in ops._workspaces.values():
+        assert torch.count_nonzero(ws) == 0, "split-k accumulator words must be handed back zeroed"
 
 
 def test_quantized_linear_module(pkg, orc):

@@ -49,12 +49,11 @@ def test_abi_is_plain_c(pkg):
 def test_version_and_workspace(pkg):
     lib = pkg.lib()
     assert lib.lutvq_version() >= 100
-    # n_k = ceil(2G/64) partial planes of O_pad {value, epoch tag} 8-byte words + a 256-byte header
+    # one 64-bit split-k accumulator word per (padded) output row + a 256-byte reserved header
     for O, I in [(4096, 4096), (11008, 4096), (4096, 11008), (96, 256)]:
         need = lib.lutvq_workspace_bytes(O, I)
-        n_k = -(-(I // 8 * 2) // 64)
         O_pad = -(-O // 32) * 32
-        assert need == 256 + n_k * O_pad * 8
+        assert need == 256 + O_pad * 8
     assert lib.lutvq_workspace_bytes(0, 64) == 0
 
 
