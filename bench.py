@@ -190,12 +190,20 @@ def main():
     import ctypes
     P = lambda t: ctypes.c_void_p(t.data_ptr())
 
-    def step_body():
-        ws = ops.workspace(dev, OUT_F, IN_F)
+    # prepacked code images (what QuantizedLinear builds on first use) and a ring of workspaces: the NBUF GEMVs of a
+    # step are independent (resident inputs), so they are issued with LUTVQ_FLAG_X_READY and overlap on the GPU
+    packed = [ops.code2x8_prepack(L["codes"]) for L in layers]
+    ws_need = (int(lib.lutvq_workspace_bytes(OUT_F, IN_F)) + 255) // 256 * 256
+    ws_ring = torch.zeros(ops.XREADY_WS_RING * ws_need, dtype=torch.uint8, device=dev)
+    assert NBUF % ops.XREADY_WS_RING == 0
+    FLAGS = {"x_ready": pkg._lib.FLAG_X_READY, "dependent": 0}
+
+    def step_body(mode="x_ready"):
         st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         for i, L in enumerate(layers):
-            pkg._lib.check(lib.lutvq_code2x8_matmat(P(xs[i]), P(L["codes"]), P(L["codebooks"]), P(L["scales"]), None,
-                                                    P(ys[i]), 1, OUT_F, IN_F, 0, P(ws), ws.numel(), st))
+            ws = ws_ring[(i % ops.XREADY_WS_RING) * ws_need:]
+            pkg._lib.check(lib.lutvq_code2x8_matmat_packed(P(xs[i]), P(packed[i]), P(L["codebooks"]), P(L["scales"]), None,
+                                                           P(ys[i]), 1, OUT_F, IN_F, 0, FLAGS[mode], P(ws), ws_need, st))
             if world > 1:
                 dist.all_gather_into_tensor(gathered[i], ys[i, 0])
 
@@ -247,6 +255,23 @@ def main():
         clocks = sampler.stop() if rank == 0 else None
         ms_per_step = ms_total / args.steps
         bytes_per_gemv = algorithmic_bytes(IN_F, OUT_F)
+        # the same ring issued WITHOUT the X_READY promise: every GEMV waits for the previous one (decode-like chain)
+        dep_us = None
+        if world == 1:
+            gdep = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gdep, stream=stream):
+                step_body("dependent")
+            for _ in range(5):
+                gdep.replay()
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = max(20, min(args.steps, 200))
+            a.record(stream)
+            for _ in range(reps):
+                gdep.replay()
+            b.record(stream)
+            torch.cuda.synchronize()
+            dep_us = a.elapsed_time(b) * 1e3 / (reps * NBUF)
         value = world * NBUF * bytes_per_gemv / (ms_per_step * 1e-3) / 1e9
         us_per_gemv = ms_per_step * 1e3 / NBUF
 
@@ -255,12 +280,11 @@ def main():
         y_host = torch.empty((NBUF, 1, OUT_F), dtype=torch.float16).pin_memory()
 
         def e2e_step():
-            for i, L in enumerate(layers):
-                xd = x_host[i].to(dev, non_blocking=True)
-                yd = ops.code2x8_matmat(xd, L["codes"], L["codebooks"], L["scales"], None)
-                if world > 1:
-                    dist.all_gather_into_tensor(gathered[i], yd[0])
-                y_host[i].copy_(yd, non_blocking=True)
+            # one step end to end: the step's activations come from pinned host memory, the C-ABI GEMVs run (as the
+            # captured graph for 1 GPU, eagerly + all-gather otherwise), the step's outputs are read back to the host
+            xs.copy_(x_host, non_blocking=True)
+            run_step()
+            y_host.copy_(ys, non_blocking=True)
 
         e2e_steps = max(3, args.steps // 10)
         for _ in range(3):
@@ -280,42 +304,62 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_ms = float(t.item())
         e2e_val = world * NBUF * bytes_per_gemv / (e2e_ms * 1e-3) / 1e9
+        # per-call cost of the torch-facing op (QuantizedLinear's path): H2D of one row, one op call, D2H of one row
+        xd1 = x_host[0].to(dev)
+        for _ in range(5):
+            ops.code2x8_matmat_packed(xd1, packed[0], OUT_F, layers[0]["codebooks"], layers[0]["scales"], None)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n_calls = 200
+        for i in range(n_calls):
+            xd = x_host[i % NBUF].to(dev, non_blocking=True)
+            yd = ops.code2x8_matmat_packed(xd, packed[i % NBUF], OUT_F, layers[i % NBUF]["codebooks"], layers[i % NBUF]["scales"], None)
+            y_host[i % NBUF].copy_(yd, non_blocking=True)
+        torch.cuda.synchronize()
+        eager_call_us = (time.perf_counter() - t0) / n_calls * 1e6
 
         # ---- the other shapes of the configs[1] sweep (not part of the timed region above) ----
         sweep = []
         if rank == 0 and world == 1 and not args.no_sweep:
             peak, _ = measured_peak()
             for (i_f, o_f) in synth.SWEEP_7B:
-                nb = max(8, int(280e6 // (o_f * i_f // 4)))
+                nb = -(-max(8, int(280e6 // (o_f * i_f // 4))) // ops.XREADY_WS_RING) * ops.XREADY_WS_RING
                 Ls = [synth.make_layer_torch(i_f, o_f, dev, seed=77 + k, scales="ones") for k in range(nb)]
                 xv = torch.randn((nb, 1, i_f), device=dev, dtype=torch.float16)
                 yv = torch.empty((nb, 1, o_f), device=dev, dtype=torch.float16)
 
-                def body():
-                    ws = ops.workspace(dev, o_f, i_f)
+                pk = [ops.code2x8_prepack(L["codes"]) for L in Ls]
+                need = (int(lib.lutvq_workspace_bytes(o_f, i_f)) + 255) // 256 * 256
+                ring = torch.zeros(ops.XREADY_WS_RING * need, dtype=torch.uint8, device=dev)
+
+                def body(flags):
                     st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
                     for k, L in enumerate(Ls):
-                        pkg._lib.check(lib.lutvq_code2x8_matmat(P(xv[k]), P(L["codes"]), P(L["codebooks"]), P(L["scales"]), None,
-                                                                P(yv[k]), 1, o_f, i_f, 0, P(ws), ws.numel(), st))
-                body()
-                torch.cuda.synchronize()
-                g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=stream):
-                    body()
-                for _ in range(5):
-                    g.replay()
-                torch.cuda.synchronize()
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                reps = 50
-                a.record(stream)
-                for _ in range(reps):
-                    g.replay()
-                b.record(stream)
-                torch.cuda.synchronize()
-                us = a.elapsed_time(b) * 1e3 / (reps * nb)
-                gbps = algorithmic_bytes(i_f, o_f) / (us * 1e-6) / 1e9
-                sweep.append({"shape": f"{i_f}->{o_f}", "us": round(us, 3), "gbps": round(gbps, 1), "frac_of_measured_peak": round(gbps / peak, 4), "layers_in_ring": nb})
-                del Ls, g
+                        pkg._lib.check(lib.lutvq_code2x8_matmat_packed(P(xv[k]), P(pk[k]), P(L["codebooks"]), P(L["scales"]), None,
+                                                                       P(yv[k]), 1, o_f, i_f, 0, flags, P(ring[(k % ops.XREADY_WS_RING) * need:]), need, st))
+                row = {"shape": f"{i_f}->{o_f}", "layers_in_ring": nb}
+                for name, flags in (("x_ready", pkg._lib.FLAG_X_READY), ("dependent", 0)):
+                    body(flags)
+                    torch.cuda.synchronize()
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g, stream=stream):
+                        body(flags)
+                    for _ in range(5):
+                        g.replay()
+                    torch.cuda.synchronize()
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    reps = 50
+                    a.record(stream)
+                    for _ in range(reps):
+                        g.replay()
+                    b.record(stream)
+                    torch.cuda.synchronize()
+                    us = a.elapsed_time(b) * 1e3 / (reps * nb)
+                    gbps = algorithmic_bytes(i_f, o_f) / (us * 1e-6) / 1e9
+                    row[name] = {"us": round(us, 3), "gbps": round(gbps, 1), "frac_of_measured_peak": round(gbps / peak, 4)}
+                    del g
+                sweep.append(row)
+                del Ls, pk
 
     if rank != 0:
         if world > 1:
@@ -336,11 +380,15 @@ def main():
         "data": "synthetic",
         "config": {"workload": f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj, BASELINE configs[1] headline shape)",
                    "gemvs_per_step": NBUF, "cache": f"inputs larger than L2: {NBUF} distinct code matrices = {NBUF * OUT_F * IN_F // 4 / 1e6:.0f} MB per step",
-                   "launch": "one CUDA graph per step, programmatic dependent launch between GEMVs" if world == 1 else "eager launches + NCCL all_gather of output slices per GEMV",
+                   "launch": ("one CUDA graph per step; the GEMVs of a step are independent (resident inputs), issued with LUTVQ_FLAG_X_READY on "
+                              "prepacked codes + a ring of 8 workspaces, so consecutive launches overlap under programmatic dependent launch; "
+                              "dependent_chain_us_per_gemv is the same ring without the promise") if world == 1 else "eager launches + NCCL all_gather of output slices per GEMV",
                    "sharding": "none" if world == 1 else f"output channels, {world} x {OUT_F} rows"},
         "us_per_gemv": us_per_gemv,
+        "dependent_chain_us_per_gemv": dep_us,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * OUT_F * 2,
-                "us_per_gemv": e2e_ms * 1e3 / NBUF},
+                "us_per_gemv": e2e_ms * 1e3 / NBUF, "eager_torch_op_call_us": eager_call_us,
+                "how": "per step: one H2D copy of the step's NBUF activation rows from pinned host memory, the step's C-ABI GEMVs, one D2H copy of the NBUF output rows"},
         "gpu_launches": args.steps * NBUF,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "lut_gemv_2x8_kernel", "algorithmic_bytes_per_launch": bytes_per_gemv, "peak_source": peak_src,

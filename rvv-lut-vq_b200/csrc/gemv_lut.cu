@@ -316,25 +316,24 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     using D = Dtype<DT>;
     using T = typename D::T;
     // A contribution's atomic is issued at the end of its set and its return value is examined PF sets later, so the
-    // L2 round trip hides behind lookups.  Pending state per slot: the returned word, the partial, the row and the
-    // (scale, bias) pair -- both weights, fetched with the atomic so that the last arriver has them at hand.
+    // L2 round trip hides behind lookups.  Pending state per slot: the returned word, the partial and the row.
     unsigned long long pend_old[PF];
     float pend_keep[PF];
     int pend_row[PF];
-    unsigned short pend_sc[PF], pend_bi[PF];
     bool pend_valid[PF];
     #pragma unroll
-    for (int i = 0; i < PF; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_sc[i] = pend_bi[i] = 0; pend_valid[i] = false; }
+    for (int i = 0; i < PF; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_valid[i] = false; }
     const unsigned last_count = (unsigned)p.n_k - 1u;
-    auto finish_row = [&](unsigned long long old, float keep, int row, unsigned short scb, unsigned short bib) {
+    auto finish_row = [&](unsigned long long old, float keep, int row) {
         if ((unsigned)(old & 255ull) == last_count) {              // this lane delivered the last partial of `row`
             if (!waited) { pdl_wait(); waited = true; }            // y stores are ordered behind the previous kernel
             const float total = fx_total<DT>(old + fx_contribution<DT>(keep));
             asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p.acc + row), "l"(0ull) : "memory");   // hand the word back
             if (row < p.O) {
                 T rr = D::from_f(total);                                               // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
-                if (p.scales) rr = D::mul(rr, *reinterpret_cast<const T*>(&scb));      // flat_output *= scales             (cuda_kernel.cpp:101)
-                if (p.bias)   rr = D::add(rr, *reinterpret_cast<const T*>(&bib));      // flat_output += bias               (cuda_kernel.cpp:103)
+                // scale / bias were pulled into L2 by the prologue; only the last arriver (1 in n_k) pays this round trip
+                if (p.scales) rr = D::mul(rr, static_cast<const T*>(p.scales)[row]);   // flat_output *= scales             (cuda_kernel.cpp:101)
+                if (p.bias)   rr = D::add(rr, static_cast<const T*>(p.bias)[row]);     // flat_output += bias               (cuda_kernel.cpp:103)
                 static_cast<T*>(p.y)[row] = rr;
             }
         }
@@ -406,12 +405,6 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                 if (lo + li < hi) {                                 // warp-uniform
                     const int set = set_of(li, ks, lo, hi);
                     const int row = set * kSetRows + lane;
-                    // epilogue operands are weights: fetch them now, a whole set of lookups before they are needed
-                    unsigned short sc_raw = 0, bi_raw = 0;
-                    if (p.n_k > 1 && row < p.O) {
-                        if (p.scales) sc_raw = static_cast<const unsigned short*>(p.scales)[row];
-                        if (p.bias)   bi_raw = static_cast<const unsigned short*>(p.bias)[row];
-                    }
                     float acc[4][2];
                     if (p.flags & 0x100u) {                         // DEBUG: no lookups (pure code streaming)
                         #pragma unroll
@@ -449,9 +442,8 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                         if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
                     } else {
                         // finish the atomic this slot issued PF sets ago, then issue this set's
-                        if (pend_valid[st]) finish_row(pend_old[st], pend_keep[st], pend_row[st], pend_sc[st], pend_bi[st]);
+                        if (pend_valid[st]) finish_row(pend_old[st], pend_keep[st], pend_row[st]);
                         pend_row[st] = row; pend_valid[st] = true; pend_keep[st] = keep;
-                        pend_sc[st] = sc_raw; pend_bi[st] = bi_raw;
                         pend_old[st] = atom_add_u64(p.acc + row, fx_contribution<DT>(keep));
                     }
                 }
@@ -472,7 +464,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
 
     #pragma unroll
     for (int i = 0; i < PF; ++i)
-        if (pend_valid[i]) finish_row(pend_old[i], pend_keep[i], pend_row[i], pend_sc[i], pend_bi[i]);
+        if (pend_valid[i]) finish_row(pend_old[i], pend_keep[i], pend_row[i]);
     TL_STAMP(5);
     if (!waited) pdl_wait();                                       // completion stays stream-ordered
     TL_STAMP(6);
