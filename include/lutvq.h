@@ -72,6 +72,8 @@ int         lutvq_device_info(int* sm_count, int* cc_major, int* cc_minor, size_
 
 /* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch). */
 size_t lutvq_workspace_bytes(int prob_m, int prob_k);
+/* Same, when the caller knows its largest batch: batch <= 6 only ever needs the (small) GEMV scratch. */
+size_t lutvq_workspace_bytes_ex(int prob_m, int prob_k, int max_batch);
 
 /* y[prob_m] = W(codes, codebook) . x[prob_k]            (no scale, like Code2x8MatVec)
  * codes    int8  [prob_m][prob_k/8][2]   (16-byte aligned rows: prob_k % 64 == 0, as the reference requires)

@@ -24,6 +24,7 @@ SIGNATURES = {
     "lutvq_version": (I, []),
     "lutvq_device_info": (I, [P, P, P, P]),
     "lutvq_workspace_bytes": (SZ, [I, I]),
+    "lutvq_workspace_bytes_ex": (SZ, [I, I, I]),
     "lutvq_code2x8_matvec": (I, [P, P, P, P, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat_ex": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),

@@ -29,6 +29,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
                            const void* bias, void* y, int batch, int O, int I, int dtype, void* ws, size_t ws_bytes,
                            cudaStream_t stream);
 size_t gemm_workspace_bytes(int O, int I);
+size_t gemm_workspace_bytes_for(int O, int I, int max_batch);
 
 char* err_buf() {
     static thread_local char buf[512] = "";
@@ -100,6 +101,13 @@ size_t lutvq_workspace_bytes(int prob_m, int prob_k) {
     if (prob_m <= 0 || prob_k <= 0) return 0;
     size_t a = gemv_workspace_bytes(prob_m, prob_k / 8);
     size_t b = gemm_workspace_bytes(prob_m, prob_k);
+    return a > b ? a : b;
+}
+
+size_t lutvq_workspace_bytes_ex(int prob_m, int prob_k, int max_batch) {
+    if (prob_m <= 0 || prob_k <= 0) return 0;
+    size_t a = gemv_workspace_bytes(prob_m, prob_k / 8);
+    size_t b = max_batch > 6 ? gemm_workspace_bytes_for(prob_m, prob_k, max_batch) : 0;   // batch <= 6 never takes the GEMM path
     return a > b ? a : b;
 }
 

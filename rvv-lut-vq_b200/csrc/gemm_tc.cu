@@ -1,9 +1,374 @@
-// gemm_tc.cu -- placeholder until the tcgen05 prefill kernel lands.
+// gemm_tc.cu -- prefill path: y[b][o] = epilogue( sum_k x[b][k] * W[o][k] ) with W dequantized ON THE FLY into shared
+// memory and contracted on the 5th-generation tensor cores (tcgen05.mma, fp32 accumulators in TMEM).
+//
+// Replaces code2x8_matmat_dequant (reference benchmark/AQLM/inference_lib/src/aqlm/inference_kernels/
+// cuda_kernel.cpp:450-484): Code2x8Dequant writes the whole fp16 W to HBM (2*O*I bytes), cuBLAS F.linear reads it
+// back, three elementwise kernels apply scale / bias.  Here W never exists in HBM: the only weight traffic is the
+// code stream (O*I/4 bytes), and the epilogue (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111) is fused.
+//
+// One CTA = one 128-row tile of output channels x the whole (padded) batch, over a k-range of the split:
+//   D[128 x N] (TMEM, fp32)  +=  A[128 x 64] (smem, dequantized weights, K-major)  *  B[N x 64]^T (smem, activations)
+//   warps 0-3  producers: each thread owns one output row: a 16-byte code load = 8 groups per 64-wide k block; per
+//              group two conflict-free 128-bit reads of the 8x replicated codebooks, one HADD2 x4 (the SAME single
+//              RN add as Code2x8Dequant, cuda_kernel.cu:283-289), one 128-bit store -- exactly one "core matrix row"
+//              of the no-swizzle K-major UMMA layout  addr = kchunk * (rows*16) + row*16.
+//              The activation tile is brought in by cp.async in the same layout.  Afterwards the same warps run the
+//              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
+//   warp 4     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
+//              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
+//   mbarrier pipeline of kStages smem stages (full: 128 producer arrivals, empty: tcgen05.commit).
+//
+// Split-k (few row tiles, e.g. 4096 outputs = 32 tiles on 148 SMs): partial accumulators go to the workspace in
+// fp32, a per-tile arrival counter elects the last CTA, which adds the partials IN FIXED ORDER (deterministic) and
+// runs the epilogue; it resets the counter, so the workspace is all-zero again between launches.
+//
+// Bound: tensor pipe only at large batch; below ~128 columns the producers' shared-memory traffic (48 B per group)
+// is the limiter.  Algorithmic flops 2*batch*I*O; algorithmic HBM bytes as the GEMV + 2*batch*(I+O).
 #include "common.cuh"
+
 namespace lutvq {
-size_t gemm_workspace_bytes(int, int) { return 0; }
-int gemm_dequant_tc_launch(const void*, const void*, const void*, const void*, const void*, void*, int, int, int, int,
-                           void*, size_t, cudaStream_t) {
-    return fail(LUTVQ_EUNSUPPORTED, "tcgen05 prefill GEMM not built yet");
+
+constexpr int kBM = 128;                 // output channels per CTA (UMMA M)
+constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 code bytes per row
+constexpr int kProducerThreads = 128;
+constexpr int kGemmThreads = 160;
+constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
+constexpr int kAStageBytes = kBM * kBK * 2;        // 16 KiB
+
+struct GemmParams {
+    const uint8_t* codes;   // [O][G][2]
+    const void* x;          // [batch][I]
+    const uint4* codebook;  // [2][256] x 16 B
+    const void* scales;     // [O] or null
+    const void* bias;       // [O] or null
+    void* y;                // [batch][O]
+    unsigned int* counters; // [n_tiles] split-k arrival counters (zero between launches)
+    float* partial;         // [ksplit][n_pad][O_pad] fp32 partial accumulators (ksplit > 1)
+    int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, tmem_cols;
+};
+
+// ---- PTX wrappers (forms as in CUTLASS cute/arch/{copy_sm100,mma_sm100_umma,tmem_allocator_sm100}.hpp) ----
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}"
+        :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+// K-major, no-swizzle UMMA shared-memory descriptor (cute::UMMA::SmemDescriptor): 8-row x 16-byte core matrices,
+// rows 16 B apart; SBO = distance between 8-row groups, LBO = distance between the two k core matrices of one MMA.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);   // version 1 (Blackwell), layout_type 0 = SWIZZLE_NONE
+}
+// cute::UMMA::InstrDescriptor for kind::f16: D = F32, A/B = F16 or BF16, both K-major, dense
+__device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
+    return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <int DT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_dequant_tc_kernel(const GemmParams p) {
+    using D = Dtype<DT>;
+    using T = typename D::T;
+    using T2 = typename D::T2;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    uint4* sh_cb = reinterpret_cast<uint4*>(smem);
+    const int S = p.stages;
+    const uint32_t sA = sbase + kCbSmemBytes;
+    const uint32_t bstage = (uint32_t)p.n_pad * 128u;
+    const uint32_t sB = sA + (uint32_t)S * kAStageBytes;
+    const uint32_t bars = sB + (uint32_t)S * bstage;
+    auto full_bar  = [&](int i) { return bars + 8u * (uint32_t)i; };
+    auto empty_bar = [&](int i) { return bars + 8u * (uint32_t)(S + i); };
+    const uint32_t accum_bar = bars + 16u * (uint32_t)S;
+    const uint32_t tmem_slot = accum_bar + 8u;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
+    volatile uint32_t* last_flag_ptr = tmem_slot_ptr + 1;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tile = blockIdx.x, z = blockIdx.y;
+    const int row0 = tile * kBM;
+    const int kb0 = (int)(((long long)z * p.nkb) / p.ksplit), kb1 = (int)(((long long)(z + 1) * p.nkb) / p.ksplit);
+
+    // ---------------- one-time setup ----------------
+    if (tid == kProducerThreads) {
+        for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads); mbar_init(empty_bar(i), 1); }
+        mbar_init(accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)p.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+        for (int i = tid; i < 2 * 256 * 8; i += kProducerThreads) sh_cb[i] = __ldg(p.codebook + (i >> 3));
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp < 4) {
+        // =============================== producers: dequantize A, copy B ===============================
+        const int row = min(row0 + tid, p.O - 1);                       // rows past the end recompute the last row; never stored
+        const uint8_t* codes_row = p.codes + (size_t)row * (size_t)(p.I / 4);
+        const uint4* cb0 = sh_cb + (lane & 7);
+        const uint4* cb1 = sh_cb + 256 * 8 + (lane & 7);
+        const uint8_t* xb = static_cast<const uint8_t*>(p.x);
+        auto issue_B = [&](int kb, int s) {
+            for (int n = tid; n < p.n_pad; n += kProducerThreads) {
+                const uint32_t dst = sB + (uint32_t)s * bstage + (uint32_t)n * 16u;
+                if (n < p.batch) {
+                    const uint8_t* src = xb + ((size_t)n * p.I + (size_t)kb * kBK) * 2;
+                    #pragma unroll
+                    for (int j = 0; j < 8; ++j) cp_async16(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u), src + j * 16);
+                } else {
+                    #pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" :: "r"(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u)), "r"(0u) : "memory");
+                }
+            }
+            cp_async_commit();
+        };
+        uint4 c_cur = ldg_stream_u128(codes_row + (size_t)kb0 * 16);
+        uint4 c_nxt = (kb0 + 1 < kb1) ? ldg_stream_u128(codes_row + (size_t)(kb0 + 1) * 16) : make_uint4(0, 0, 0, 0);
+        issue_B(kb0, 0);
+        for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+            const int s = it % S;
+            if (kb + 1 < kb1) {                                          // next stage's activations fly while we dequantize
+                const int it1 = it + 1, s1 = it1 % S;
+                mbar_wait(empty_bar(s1), (uint32_t)(((it1 / S) & 1) ^ 1));
+                issue_B(kb + 1, s1);
+            } else {
+                cp_async_commit();
+            }
+            const uint4 cc = c_cur;
+            c_cur = c_nxt;
+            if (kb + 2 < kb1) c_nxt = ldg_stream_u128(codes_row + (size_t)(kb + 2) * 16);
+            const uint32_t w[4] = {cc.x, cc.y, cc.z, cc.w};
+            const uint32_t a_dst = sA + (uint32_t)s * kAStageBytes + (uint32_t)tid * 16u;
+            #pragma unroll
+            for (int g = 0; g < 8; ++g) {
+                const uint32_t code = (w[g >> 1] >> (16 * (g & 1))) & 0xFFFFu;   // byte 0 = codebook-0 index, byte 1 = codebook-1 index
+                const uint4 a = cb0[(code & 0xFFu) * 8];
+                const uint4 b = cb1[(code >> 8) * 8];
+                uint4 r;
+                const T2* a2 = reinterpret_cast<const T2*>(&a);
+                const T2* b2 = reinterpret_cast<const T2*>(&b);
+                T2* r2 = reinterpret_cast<T2*>(&r);
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) r2[j] = D::add2(a2[j], b2[j]);
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_dst + (uint32_t)g * (kBM * 16u)), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
+            }
+            cp_async_wait<1>();                                          // this stage's activations have landed
+            fence_proxy_async_smem();                                    // generic-proxy writes -> visible to the tensor core
+            mbar_arrive(full_bar(s));
+        }
+
+        // =============================== epilogue ===============================
+        mbar_wait(accum_bar, 0u);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
+        const int o = row0 + tid;
+        const bool live = o < p.O;
+        T sc = D::from_f(1.f), bi = D::from_f(0.f);
+        if (live && p.scales) sc = static_cast<const T*>(p.scales)[o];
+        if (live && p.bias)   bi = static_cast<const T*>(p.bias)[o];
+        auto finish = [&](float acc, int b) {
+            T rr = D::from_f(acc);                                       // round(acc)              (Code2x8MatVec / F.linear output dtype)
+            if (p.scales) rr = D::mul(rr, sc);                           // flat_output *= scales   (cuda_kernel.cpp:101)
+            if (p.bias)   rr = D::add(rr, bi);                           // flat_output += bias     (cuda_kernel.cpp:103)
+            static_cast<T*>(p.y)[(size_t)b * p.O + o] = rr;
+        };
+        if (p.ksplit == 1) {
+            for (int c0 = 0; c0 < p.n_pad; c0 += 16) {
+                uint32_t v[16];
+                tc_ld16(taddr + (uint32_t)c0, v);
+                #pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (live && c0 + j < p.batch) finish(__uint_as_float(v[j]), c0 + j);
+            }
+        } else {
+            float* mine = p.partial + ((size_t)z * p.n_pad) * p.O_pad + o;
+            for (int c0 = 0; c0 < p.n_pad; c0 += 16) {
+                uint32_t v[16];
+                tc_ld16(taddr + (uint32_t)c0, v);
+                #pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (c0 + j < p.batch) __stcg(mine + (size_t)(c0 + j) * p.O_pad, __uint_as_float(v[j]));
+            }
+            __threadfence();
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (tid == 0) *last_flag_ptr = (atomicAdd(p.counters + tile, 1u) == (unsigned)p.ksplit - 1u) ? 1u : 0u;
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (*last_flag_ptr) {                                        // last CTA of this tile: fixed-order sum of the partials
+                __threadfence();
+                if (live)
+                    for (int b = 0; b < p.batch; ++b) {
+                        float acc = 0.f;
+                        for (int zz = 0; zz < p.ksplit; ++zz)
+                            acc += __ldcg(p.partial + ((size_t)zz * p.n_pad + b) * p.O_pad + o);
+                        finish(acc, b);
+                    }
+                if (tid == 0) p.counters[tile] = 0u;                     // hand the counter back
+            }
+        }
+    } else {
+        // =============================== MMA issuer (warp 4) ===============================
+        const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
+        for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+            const int s = it % S;
+            mbar_wait(full_bar(s), (uint32_t)((it / S) & 1));
+            tc_fence_after();
+            if (lane == 0) {
+                #pragma unroll
+                for (int k = 0; k < kBK / 16; ++k) {
+                    const uint64_t adesc = umma_desc(sA + (uint32_t)s * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
+                    const uint64_t bdesc = umma_desc(sB + (uint32_t)s * bstage + (uint32_t)k * (2u * (uint32_t)p.n_pad * 16u), (uint32_t)p.n_pad * 16u, 128u);
+                    tc_mma_f16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
+            }
+            __syncwarp();
+        }
+        if (lane == 0) tc_commit(accum_bar);                             // accumulator complete
+        __syncwarp();
+    }
+
+    // ---------------- teardown ----------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+struct GemmPlan { int n_tiles, O_pad, nkb, ksplit; };
+
+static GemmPlan plan_gemm(int O, int I, int sm_count) {
+    GemmPlan pl;
+    pl.n_tiles = ceil_div(O, kBM);
+    pl.O_pad = pl.n_tiles * kBM;
+    pl.nkb = I / kBK;
+    int ks = sm_count / pl.n_tiles;                       // fill the SMs when there are few row tiles
+    if (ks > pl.nkb / 4) ks = pl.nkb / 4;                 // at least 4 k blocks per CTA
+    if (ks > 16) ks = 16;
+    if (ks < 1) ks = 1;
+    pl.ksplit = ks;
+    return pl;
+}
+
+constexpr int kGemmMaxBatch = 256;                        // UMMA N <= 256; larger batches are chunked by the launcher
+
+static size_t gemv_acc_bytes(int O) { return ((size_t)ceil_div(O, 32) * 32 * 8 + 255) / 256 * 256; }
+
+// workspace = [256 B header][GEMV accumulator words, also the GEMM tile counters][GEMM split-k partials]
+size_t gemm_workspace_bytes_for(int O, int I, int max_batch) {
+    int sm = 148;
+    DeviceInfo di;
+    if (get_device_info(&di) == 0) sm = di.sm_count;
+    const GemmPlan pl = plan_gemm(O, I, sm);
+    if (max_batch <= 0) return 0;
+    int nb = max_batch < kGemmMaxBatch ? max_batch : kGemmMaxBatch;
+    nb = ceil_div(nb, 16) * 16;
+    const size_t partial = pl.ksplit > 1 ? (size_t)pl.ksplit * nb * pl.O_pad * sizeof(float) : 0;
+    return 256 + gemv_acc_bytes(O) + partial;
+}
+size_t gemm_workspace_bytes(int O, int I) { return gemm_workspace_bytes_for(O, I, kGemmMaxBatch); }
+
+template <int DT>
+static int launch_gemm(const GemmParams& p, dim3 grid, size_t smem, cudaStream_t stream) {
+    auto kern = gemm_dequant_tc_kernel<DT>;
+    static thread_local int attr_device = -1;
+    int dev = 0;
+    LUTVQ_CUDA_OK(cudaGetDevice(&dev));
+    if (attr_device != dev) {
+        LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_device = dev;
+    }
+    kern<<<grid, kGemmThreads, smem, stream>>>(p);
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codebooks, const void* scales,
+                           const void* bias, void* y, int batch, int O, int I, int dtype, void* ws, size_t ws_bytes,
+                           cudaStream_t stream) {
+    DeviceInfo di;
+    if (int rc = get_device_info(&di)) return rc;
+    if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+    const GemmPlan pl = plan_gemm(O, I, di.sm_count);
+    for (int b0 = 0; b0 < batch; b0 += kGemmMaxBatch) {
+        const int nb = batch - b0 < kGemmMaxBatch ? batch - b0 : kGemmMaxBatch;
+        GemmParams p;
+        p.codes = static_cast<const uint8_t*>(codes);
+        p.x = static_cast<const uint8_t*>(x) + (size_t)b0 * I * 2;
+        p.codebook = static_cast<const uint4*>(codebooks);
+        p.scales = scales; p.bias = bias;
+        p.y = static_cast<uint8_t*>(y) + (size_t)b0 * O * 2;
+        p.O = O; p.O_pad = pl.O_pad; p.I = I; p.batch = nb;
+        p.n_pad = ceil_div(nb, 16) * 16;
+        p.nkb = pl.nkb; p.ksplit = pl.ksplit;
+        p.tmem_cols = 32;
+        while (p.tmem_cols < p.n_pad) p.tmem_cols *= 2;
+        const size_t stage_bytes = (size_t)kAStageBytes + (size_t)p.n_pad * 128;
+        const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - 1024;
+        int S = (int)(budget / stage_bytes);
+        if (S > 4) S = 4;
+        if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
+        p.stages = S;
+        const size_t smem = kCbSmemBytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
+        p.counters = nullptr; p.partial = nullptr;
+        if (pl.ksplit > 1) {
+            const size_t need = gemm_workspace_bytes_for(O, I, nb);
+            LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= need, "workspace too small: need %zu bytes, got %zu", need, ws_bytes);
+            LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
+            p.counters = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(ws) + 256);
+            p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256 + gemv_acc_bytes(O));
+        }
+        const dim3 grid(pl.n_tiles, pl.ksplit);
+        const int rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16>(p, grid, smem, stream);
+        if (rc) return rc;
+    }
+    return LUTVQ_OK;
+}
+
 }  // namespace lutvq

@@ -52,12 +52,26 @@ XREADY_WS_RING = 8          # include/lutvq.h LUTVQ_XREADY_WS_RING
 _ws_ring_pos: Dict[Tuple[int, int], int] = {}
 
 
+_gemm_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def gemm_workspace(dev: torch.device, prob_m: int, prob_k: int, batch: int) -> torch.Tensor:
+    """Scratch of the prefill GEMM (split-k partial accumulators; can be tens of MB), cached per (device, stream)."""
+    need = int(lib().lutvq_workspace_bytes_ex(prob_m, prob_k, batch))
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    ws = _gemm_workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=dev)
+        _gemm_workspaces[key] = ws
+    return ws
+
+
 def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False) -> torch.Tensor:
     """Zero-initialised scratch, cached per (device, stream) as include/lutvq.h requires.  The cache holds a ring of
     XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True`` (LUTVQ_FLAG_X_READY calls) steps through
     the ring so that overlapping launches never share a region.  (Inside a CUDA graph the region is baked at capture:
     keep the number of X_READY calls per graph a multiple of XREADY_WS_RING.)"""
-    need = (int(lib().lutvq_workspace_bytes(prob_m, prob_k)) + 255) // 256 * 256
+    need = (int(lib().lutvq_workspace_bytes_ex(prob_m, prob_k, 6)) + 255) // 256 * 256
     key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < need * XREADY_WS_RING:
@@ -97,7 +111,10 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
     codes_c, cb_c = codes.contiguous(), codebooks.contiguous()
     sc, bi = _flat_scales(scales), (None if bias is None else bias.contiguous())
     with torch.cuda.device(dev):
-        ws = workspace(dev, out_features, in_features, rotate=bool(flags and flags & _lib.FLAG_X_READY))
+        if fn_name == "lutvq_code2x8_matmat_dequant":
+            ws = gemm_workspace(dev, out_features, in_features, batch)
+        else:
+            ws = workspace(dev, out_features, in_features, rotate=bool(flags and flags & _lib.FLAG_X_READY))
         fn = getattr(lib(), fn_name)
         if flags is None:
             rc = fn(_ptr(flat_input), _ptr(codes_c), _ptr(cb_c), _ptr(sc), _ptr(bi), _ptr(flat_output), batch,

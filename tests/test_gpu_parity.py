@@ -225,6 +225,62 @@ def test_dequant_full_matrix_checksum(pkg, ops, orc):
     assert np.array_equal((got * weights).sum(axis=1), (Wref.astype(np.uint64) * weights).sum(axis=1))
 
 
+# ------------------------------------------------------------------ prefill: dequant -> smem -> tcgen05 GEMM
+GEMM_CASES = [
+    # (in, out, batch, dtype, bias)
+    (256, 128, 16, "f16", False),          # one row tile, 4 k blocks, no split
+    (1024, 1000, 17, "f16", True),         # ragged rows (1000 = 7 tiles + 104) and ragged batch (17 -> 32 columns)
+    (4096, 4096, 64, "f16", True),         # 32 row tiles -> split-k 4 through the workspace
+    (4096, 11008, 256, "f16", False),      # BASELINE configs[2] top batch: 86 tiles, no split, 3 stages
+    (11008, 4096, 128, "f16", False),      # long k (172 blocks), split-k
+    (2048, 512, 300, "f16", True),         # batch > 256: chunked launches
+    (1024, 768, 48, "bf16", True),
+]
+
+
+@pytest.mark.parametrize("I,O,batch,dt,bias", GEMM_CASES)
+def test_matmat_dequant_tensor_core(pkg, ops, orc, I, O, batch, dt, bias):
+    """code2x8_matmat_dequant: exact products of the bit-exact dequantized weights, fp32 accumulation in TMEM.
+    Checked against float64 of the same operands (tolerance 1e-3 of max |y|, north star) and, tighter, against the
+    reference's own recipe (dequant -> F.linear in fp32 -> round -> *scale -> +bias, cuda_kernel.cpp:463-477,95-111)."""
+    from rvv_lut_vq_b200 import synth
+    tdt = torch.float16 if dt == "f16" else torch.bfloat16
+    L = synth.make_layer_np(I, O, seed=7 * I + O + batch, scales="randn", bias=bias, batch=batch)
+    conv = (lambda a: cu(a)) if dt == "f16" else (lambda a: cu(a.astype(np.float32)).to(torch.bfloat16))
+    x, cb, sc = conv(L["x"]), conv(L["codebooks"]), conv(L["scales"])
+    bi = conv(L["bias"]) if bias else None
+    codes = cu(L["codes"])
+    y = ops.code2x8_matmat_dequant(x, codes, cb, sc, bi)
+    assert y.shape == (batch, O) and y.dtype == tdt
+    W = ops.code2x8_dequant(codes, cb, None)                          # bit-exact vs the oracle (tests above)
+    acc64 = x.double() @ W.double().T
+    want64 = acc64 * sc.reshape(-1).double() + (bi.double() if bias else 0)
+    tol = 1e-3 if dt == "f16" else 8e-3
+    assert rel_err(y.double().cpu().numpy(), want64.cpu().numpy()) <= tol
+    ref = (x.float() @ W.float().T).to(tdt) * sc.reshape(-1)
+    if bias:
+        ref = ref + bi
+    ulp = (y.view(torch.int16).int() - ref.view(torch.int16).int()).abs()
+    assert (ulp <= 2).float().mean() > 0.995
+    # deterministic (fixed-order split-k) and leaves its workspace clean
+    assert torch.equal(ops.code2x8_matmat_dequant(x, codes, cb, sc, bi), y)
+    for ws in ops._gemm_workspaces.values():
+        assert torch.count_nonzero(ws[:256 + 4 * ((O + 127) // 128)]) == 0     # header + tile counters (partials need no cleaning)
+
+
+def test_quantized_linear_prefill_dispatch(pkg, orc):
+    """batch > 6 -> gemm op (inference.py:95-96); must agree with the gemv op row by row within fp16 rounding"""
+    from rvv_lut_vq_b200 import QuantizedLinear, synth
+    I, O = 1024, 640
+    L = synth.make_layer_np(I, O, seed=77, scales="randn", bias=True, batch=40)
+    m = QuantizedLinear(I, O, 8, 1, 2, 8, bias=True, device="cuda", dtype=torch.float16)
+    m.load_state_dict({"codes": cu(L["codes"]), "codebooks": cu(L["codebooks"]), "scales": cu(L["scales"]), "bias": cu(L["bias"])})
+    x = cu(L["x"])
+    y_gemm = m(x)
+    y_gemv = torch.cat([m(x[i:i + 4]) for i in range(0, 40, 4)])
+    assert rel_err(y_gemm.float().cpu().numpy(), y_gemv.float().cpu().numpy()) <= 1e-3
+
+
 # ------------------------------------------------------------------ edge cases / API behaviour
 def test_empty_batch_and_shapes(pkg, ops):
     from rvv_lut_vq_b200 import synth

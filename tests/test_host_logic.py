@@ -51,7 +51,8 @@ def test_version_and_workspace(pkg):
     assert lib.lutvq_version() >= 100
     # one 64-bit split-k accumulator word per (padded) output row + a 256-byte reserved header
     for O, I in [(4096, 4096), (11008, 4096), (4096, 11008), (96, 256)]:
-        need = lib.lutvq_workspace_bytes(O, I)
+        need = lib.lutvq_workspace_bytes_ex(O, I, 6)                     # decode-only scratch
+        assert lib.lutvq_workspace_bytes(O, I) >= need                 # any-batch scratch also covers the prefill split-k partials
         O_pad = -(-O // 32) * 32
         assert need == 256 + O_pad * 8
     assert lib.lutvq_workspace_bytes(0, 64) == 0
