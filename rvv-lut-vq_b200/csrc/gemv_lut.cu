@@ -46,9 +46,20 @@
 #include "common.cuh"
 #include "lut_layout.h"
 
+#ifndef LUTVQ_DBG
+#define LUTVQ_DBG 0          // 1: compile the experiment knobs (flags 0x100 no lookups, 0x200 no streaming, 0x400 no atomics)
+#endif
+#if LUTVQ_DBG
+#define LUTVQ_DBG_AND(x) && (x)
+#else
+#define LUTVQ_DBG_AND(x)
+#endif
+
 namespace lutvq {
 
 constexpr size_t kWsHeaderBytes = 256;        // reserved
+
+constexpr int kRangeTable = 160;              // workers whose item ranges ride in the kernel parameters (B200: 148)
 
 struct GemvParams {
     const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
@@ -64,6 +75,9 @@ struct GemvParams {
     unsigned magic_q, magic_q1;                 // ceil(2^20 / q), ceil(2^20 / (q+1))
     int base_q, rem_q, base_q1, rem_q1;         // n_sets = base_q*q + rem_q = base_q1*(q+1) + rem_q1
     unsigned flags;
+    int has_table;                              // 1: the host tabulated every worker's range (W <= kRangeTable)
+    int tab_begin[kRangeTable + 1];             // worker w owns linear items [tab_begin[w], tab_begin[w+1])
+    unsigned short tab_ks[kRangeTable];         // k-slice of item tab_begin[w]
     unsigned long long* tl;   // debug timeline [256 CTAs][16] of %globaltimer stamps for this launch, or null
 };
 
@@ -72,10 +86,14 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+#if LUTVQ_DBG
 #define TL_STAMP(i)                                                                                              \
     do {                                                                                                         \
         if (p.tl != nullptr && threadIdx.x == 0) p.tl[(size_t)blockIdx.x * 16 + (i)] = globaltimer_ns();          \
     } while (0)
+#else
+#define TL_STAMP(i) do { } while (0)
+#endif
 
 template <int DT> struct MmaK8;
 template <> struct MmaK8<LUTVQ_F16> {
@@ -141,12 +159,39 @@ __device__ __forceinline__ void epilogue_store(void* y, const void* scales, cons
     static_cast<T*>(y)[row] = r;
 }
 
+// ---- fixed-point LUT entries --------------------------------------------------------------------------------
+// The LUT holds INTEGERS: entry = round(L * 2^e) with one exponent e per (CTA, k-slice), chosen from the bound
+// |L| <= 8 * max|codebook| * max|x_slice| so that |entry| <= 2^22 (the whole signed range of the magic-number trick).  The conversion is free: the build adds the
+// magic constant 1.5 * 2^23 with the scaling FMA, which leaves 0x4B400000 + entry in the float's bits, and the
+// gather adds those words as plain 32-bit integers (one IADD3 per TWO lookups instead of one FADD per lookup); the
+// 64 magic offsets of a row partial (64 tables) are removed once, mod 2^32.  Integer sums are exact and order-free;
+// resolution is 2^-22 of the slice bound, i.e. >= 2^11 times finer than the fp16 LUT of the golden model (vq.py:285).
+constexpr float    kFxMagic     = 12582912.f;                       // 1.5 * 2^23
+constexpr uint32_t kFxMagicBits = 0x4B400000u;
+constexpr uint32_t kFxMagic64   = (uint32_t)(64ull * kFxMagicBits); // 64 lookups per row partial, mod 2^32
+
+// |v| bits of the two halves of a packed fp16x2 / bf16x2 word, as an integer that orders like |v| (NaN highest)
+__device__ __forceinline__ uint32_t absmax_halves(uint32_t w) { return max(w & 0x7FFFu, (w >> 16) & 0x7FFFu); }
+template <int DT> __device__ __forceinline__ float abs_half_bits_to_float(uint32_t h);
+template <> __device__ __forceinline__ float abs_half_bits_to_float<LUTVQ_F16>(uint32_t h)  { return __half2float(__ushort_as_half((unsigned short)h)); }
+template <> __device__ __forceinline__ float abs_half_bits_to_float<LUTVQ_BF16>(uint32_t h) { return __uint_as_float(h << 16); }
+// scale 2^e and its inverse for a slice whose entries are bounded by `bound` (>= 0): |L * 2^e| <= 2^22, so a row
+// partial (64 entries) stays below 2^28.
+// Degenerate bounds: < 2^-107 -> inverse flushes to 0 (outputs 0); inf/NaN -> inverse NaN (the partial saturates).
+__device__ __forceinline__ void fx_scales(float bound, float& scale, float& inv) {
+    uint32_t ex = (__float_as_uint(bound) >> 23) & 0xFFu;            // bound < 2^(ex - 126)
+    const bool bad = ex == 255u;
+    ex = max(ex, 21u);
+    scale = __uint_as_float((275u - ex) << 23);                      // 2^(148 - ex): bound * scale < 2^22
+    inv   = bad ? __uint_as_float(0x7FC00000u) : __uint_as_float((ex - 21u) << 23);
+}
+
 // One warp tile set = 32 rows x 64 bytes: 4 tiles of 8 rows; per lane 4 x 16 bytes.
 struct CodeRegs { uint32_t w[4][4]; };
 
 // worker -> linear item range [begin, end) over (slice, set) pairs, slice-major.  The aligned plan is division-free:
 // slices < r have q+1 workers, the others q; a slice's n_sets sets are dealt base (+1 for the first rem) per worker.
-__device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
+__host__ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
     if (p.aligned) {
         const int big = p.r * (p.q + 1);
         const bool hi_part = w >= big;
@@ -156,7 +201,7 @@ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, 
         const int j = w2 - s2 * nw;
         const int s = (hi_part ? p.r : 0) + s2;
         const int base = hi_part ? p.base_q : p.base_q1, rem = hi_part ? p.rem_q : p.rem_q1;  // n_sets = base*nw + rem
-        begin = s * p.n_sets + j * base + min(j, rem);
+        begin = s * p.n_sets + j * base + (j < rem ? j : rem);
         end   = begin + base + (j < rem ? 1 : 0);
     } else {
         const long long T = (long long)p.n_k * p.n_sets;
@@ -165,22 +210,25 @@ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, 
     }
 }
 
-template <int DT, bool PACKED, int NW, int PF>
-__global__ void __launch_bounds__(NW * 32, (NW <= 4 ? 3 : 2))
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB)
 lut_gemv_2x8_kernel(const GemvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t lut_base = smem_u32(smem_raw);
 
     TL_STAMP(0);
+#if LUTVQ_DBG
     if (p.tl != nullptr && threadIdx.x == 0) {
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
         p.tl[(size_t)blockIdx.x * 16 + 15] = smid + 1;
     }
+#endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int W = gridDim.x;
     int begin, end;
-    worker_range(p, blockIdx.x, W, begin, end);
+    if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_begin[blockIdx.x + 1]; }     // two constant-bank loads
+    else worker_range(p, blockIdx.x, W, begin, end);
     const size_t row_bytes = (size_t)p.G * 2;
     const int last_row = p.O - 1;
 
@@ -216,18 +264,15 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     TL_STAMP(8);
     // The workers of different k-slices walk the same rows; each starts at a slice-dependent rotation of its own
     // range so that the n_k atomics of one row are spread over the whole gather instead of colliding at one instant.
-    auto set_of = [&](int i, int ks_, int lo_, int hi_) {
-        const int n = hi_ - lo_;
-        int v = i + (int)(((unsigned)ks_ * (unsigned)n) / (unsigned)p.n_k);
-        if (v >= n) v -= n;
-        return lo_ + v;
-    };
+    auto rot_of = [&](int ks_, int n) { return (int)(((unsigned)ks_ * (unsigned)n) / (unsigned)p.n_k); };
+    auto wrap = [](int v, int n) { while (v >= n) v -= n; return v; };
     // first segment of this worker's range: slice ks, sets [lo, hi)
     int pos = begin;
-    int ks = (begin < end) ? (int)((unsigned)begin / (unsigned)p.n_sets) : 0;
+    int ks = p.has_table ? (int)p.tab_ks[blockIdx.x] : (begin < end) ? (int)((unsigned)begin / (unsigned)p.n_sets) : 0;
     int lo = begin - ks * p.n_sets;
     int hi = min(p.n_sets, lo + (end - begin));
 
+    int seg_rot = rot_of(ks, hi - lo);
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
     // Codes and codebooks are weights.  (1) the first PF tile sets are requested into registers, (2) the rest
     // of this worker's share is pushed HBM -> L2, (3) x / the workspace header are pulled into L2 (L2 is the
@@ -236,7 +281,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     CodeRegs buf[PF];
     #pragma unroll
     for (int i = 0; i < PF; ++i)
-        if (lo + warp + i * NW < hi) load_set(buf[i], ks, set_of(warp + i * NW, ks, lo, hi));
+        if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + wrap(warp + i * NW + seg_rot, hi - lo));
     TL_STAMP(9);
     if (PACKED) {
         // the worker's whole share is ONE contiguous range of the packed image (linear item index * 2048 B)
@@ -289,8 +334,21 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             }
         }
     }
+    // max |codebook| over the CTA (every warp holds 1/NW of it in its A fragments): one REDUX + one smem word per warp
+    __shared__ uint32_t cmax_red[NW];
+    {
+        uint32_t m = 0;
+        #pragma unroll
+        for (int mi = 0; mi < MB_PER_WARP; ++mi)
+            #pragma unroll
+            for (int n = 0; n < 2; ++n) m = max(m, max(absmax_halves(afrag[mi][n][0]), absmax_halves(afrag[mi][n][1])));
+        m = __reduce_max_sync(0xffffffffu, m);
+        if (lane == 0) cmax_red[warp] = m;
+    }
     TL_STAMP(1);
-    pdl_launch_dependents();    // the next kernel may start ITS weight prefetch now (it still waits for us below)
+    // The next launch may become resident now that OUR weight requests are in flight (it still waits for us below).
+    // Measured on B200 (4096x11008, 3 CTAs/SM): triggering at kernel entry instead costs 5.4 us per launch vs 4.0 us.
+    pdl_launch_dependents();
     // X_READY: x is not the previous kernel's output and the workspace is exclusively ours (include/lutvq.h), so
     // nothing but the final y stores has to be ordered behind the previous kernel.
     const bool xready = (p.flags & LUTVQ_FLAG_X_READY) != 0;
@@ -307,22 +365,32 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         lm[0][d] = stream_lm(lane, 0, d);
         lm[1][d] = stream_lm(lane, 1, d);
     }
+    __syncthreads();
+    float cmax8;
+    {
+        uint32_t m = 0;
+        #pragma unroll
+        for (int i = 0; i < NW; ++i) m = max(m, cmax_red[i]);
+        cmax8 = 8.f * abs_half_bits_to_float<DT>(m);
+    }
     const bool b3 = (lane >> 3) & 1, b4 = (lane >> 4) & 1;
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
     bool first_seg = true;
+    float fx_scale = 1.f, fx_inv = 1.f;                                  // this segment's 2^e and 2^-e
 
     // ---- split-k completion: see the accumulator word comment above ----
     using D = Dtype<DT>;
     using T = typename D::T;
     // A contribution's atomic is issued at the end of its set and its return value is examined PF sets later, so the
     // L2 round trip hides behind lookups.  Pending state per slot: the returned word, the partial and the row.
-    unsigned long long pend_old[PF];
-    float pend_keep[PF];
-    int pend_row[PF];
-    bool pend_valid[PF];
+    static_assert(PA % PF == 0, "the pending-atomic ring must be a whole number of code rings");
+    unsigned long long pend_old[PA];
+    float pend_keep[PA];
+    int pend_row[PA];
+    bool pend_valid[PA];
     #pragma unroll
-    for (int i = 0; i < PF; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_valid[i] = false; }
+    for (int i = 0; i < PA; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_valid[i] = false; }
     const unsigned last_count = (unsigned)p.n_k - 1u;
     auto finish_row = [&](unsigned long long old, float keep, int row) {
         if ((unsigned)(old & 255ull) == last_count) {              // this lane delivered the last partial of `row`
@@ -350,6 +418,11 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                 const int g = ks * 32 + build_group_of_col(j, r);
                 bfrag[j] = (g < p.G) ? ldcg_u32(x32 + g * 4 + q) : 0u;   // L2-coherent: x may be the previous kernel's output
             }
+            {   // the warp's 32 lanes x 4 words are exactly the slice's 256 activations
+                uint32_t m = max(max(absmax_halves(bfrag[0]), absmax_halves(bfrag[1])), max(absmax_halves(bfrag[2]), absmax_halves(bfrag[3])));
+                m = __reduce_max_sync(0xffffffffu, m);
+                fx_scales(cmax8 * abs_half_bits_to_float<DT>(m), fx_scale, fx_inv);
+            }
             #pragma unroll
             for (int mi = 0; mi < MB_PER_WARP; ++mi) {
                 const int m = warp * MB_PER_WARP + mi;
@@ -361,14 +434,16 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                         c[n][j][0] = c[n][j][1] = c[n][j][2] = c[n][j][3] = 0.f;
                         MmaK8<DT>::run(c[n][j], afrag[mi][n][0], afrag[mi][n][1], bfrag[j]);
                     }
-                if (round16) {
+                #pragma unroll
+                for (int n = 0; n < 2; ++n)
                     #pragma unroll
-                    for (int n = 0; n < 2; ++n)
+                    for (int j = 0; j < 4; ++j)
                         #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            #pragma unroll
-                            for (int i = 0; i < 4; ++i) c[n][j][i] = __half2float(__float2half_rn(c[n][j][i]));
-                }
+                        for (int i = 0; i < 4; ++i) {
+                            float v = c[n][j][i];
+                            if (round16) v = __half2float(__float2half_rn(v));
+                            c[n][j][i] = fmaf(v, fx_scale, kFxMagic);      // float bits = 0x4B400000 + round(v * 2^e)
+                        }
                 // c[n][j][2h+u]: idx = 16m + r + 8h, table bytes beta = 2u+n of (chunk q, word w_j)
                 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -398,53 +473,68 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         first_seg = false;
 
         // ---------------- K2: stream codes, gather-accumulate ----------------
-        for (int it = 0; lo + it * NW + warp < hi; it += PF) {
+        {
+            const int n_seg = hi - lo;
+            int v = warp + seg_rot;                                  // rotated local index of this warp's next set
+            if (v >= n_seg) v -= n_seg;
+            int vnext = v;                                           // ... and of the set PF iterations ahead
             #pragma unroll
-            for (int st = 0; st < PF; ++st) {
-                const int li = (it + st) * NW + warp;               // local index in this segment
-                if (lo + li < hi) {                                 // warp-uniform
-                    const int set = set_of(li, ks, lo, hi);
-                    const int row = set * kSetRows + lane;
-                    float acc[4][2];
-                    if (p.flags & 0x100u) {                         // DEBUG: no lookups (pure code streaming)
-                        #pragma unroll
-                        for (int t = 0; t < 4; ++t) {
-                            acc[t][0] = __uint_as_float((buf[st].w[t][0] ^ buf[st].w[t][1]) & 0x3fffffffu);
-                            acc[t][1] = __uint_as_float((buf[st].w[t][2] ^ buf[st].w[t][3]) & 0x3fffffffu);
-                        }
-                    } else {
-                    #pragma unroll
-                    for (int c = 0; c < 4; ++c)
-                        #pragma unroll
-                        for (int d = 0; d < 4; ++d)
+            for (int i = 0; i < PF; ++i) { vnext += NW; if (vnext >= n_seg) vnext -= n_seg; }
+            for (int li = warp; li < n_seg; li += PA * NW) {
+                #pragma unroll
+                for (int sa = 0; sa < PA; ++sa) {
+                    constexpr int kDummy = 0; (void)kDummy;
+                    const int st = sa % PF;                          // code-ring slot (compile-time after unrolling)
+                    if (li + sa * NW < n_seg) {                      // warp-uniform
+                        const int row = (lo + v) * kSetRows + lane;
+                        uint32_t acc[4];
+#if LUTVQ_DBG
+                        if (p.flags & 0x100u) {                      // DEBUG: no lookups (pure code streaming)
                             #pragma unroll
-                            for (int t = 0; t < 4; ++t) {
-                                const uint32_t ad = __byte_perm(buf[st].w[t][c], lm[c >> 1][d], sel[d]);
-                                
-                                const float v = *reinterpret_cast<const float*>(smem_raw + ad + stream_imm(c));
-                                if (c == 0 && d < 2) acc[t][d] = v;
-                                else                 acc[t][d & 1] += v;
-                            }
-                    }
-                    // refill this stage with the set PF iterations ahead before the (short) reduction
-                    if (lo + li + PF * NW < hi && !(p.flags & 0x200u)) load_set(buf[st], ks, set_of(li + PF * NW, ks, lo, hi));   // 0x200 DEBUG: no streaming
-                    float a0 = acc[0][0] + acc[0][1], a1 = acc[1][0] + acc[1][1];
-                    float a2 = acc[2][0] + acc[2][1], a3 = acc[3][0] + acc[3][1];
-                    // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
-                    float k0 = b4 ? a2 : a0, k1 = b4 ? a3 : a1;
-                    float g0 = b4 ? a0 : a2, g1 = b4 ? a1 : a3;
-                    k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
-                    k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
-                    float keep = b3 ? k1 : k0, give = b3 ? k0 : k1;
-                    keep += __shfl_xor_sync(0xffffffffu, give, 8);
-                    if (p.n_k == 1) {
-                        if (!waited) { pdl_wait(); waited = true; }
-                        if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
-                    } else {
-                        // finish the atomic this slot issued PF sets ago, then issue this set's
-                        if (pend_valid[st]) finish_row(pend_old[st], pend_keep[st], pend_row[st]);
-                        pend_row[st] = row; pend_valid[st] = true; pend_keep[st] = keep;
-                        pend_old[st] = atom_add_u64(p.acc + row, fx_contribution<DT>(keep));
+                            for (int t = 0; t < 4; ++t) acc[t] = buf[st].w[t][0] ^ buf[st].w[t][1] ^ buf[st].w[t][2] ^ buf[st].w[t][3];
+                        } else
+#endif
+                        {
+                            #pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                                #pragma unroll
+                                for (int d = 0; d < 4; d += 2)
+                                    #pragma unroll
+                                    for (int t = 0; t < 4; ++t) {
+                                        const uint32_t ad0 = __byte_perm(buf[st].w[t][c], lm[c >> 1][d], sel[d]);
+                                        const uint32_t ad1 = __byte_perm(buf[st].w[t][c], lm[c >> 1][d + 1], sel[d + 1]);
+                                        const uint32_t v0 = *reinterpret_cast<const uint32_t*>(smem_raw + ad0 + stream_imm(c));
+                                        const uint32_t v1 = *reinterpret_cast<const uint32_t*>(smem_raw + ad1 + stream_imm(c));
+                                        if (c == 0 && d == 0) acc[t] = v0 + v1;
+                                        else                  acc[t] = acc[t] + v0 + v1;       // IADD3
+                                    }
+                        }
+                        // refill this stage with the set PF iterations ahead before the (short) reduction
+                        if (li + (sa + PF) * NW < n_seg LUTVQ_DBG_AND(!(p.flags & 0x200u))) load_set(buf[st], ks, lo + vnext);
+                        // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
+                        uint32_t k0 = b4 ? acc[2] : acc[0], k1 = b4 ? acc[3] : acc[1];
+                        uint32_t g0 = b4 ? acc[0] : acc[2], g1 = b4 ? acc[1] : acc[3];
+                        k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
+                        k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
+                        uint32_t keep_u = b3 ? k1 : k0, give = b3 ? k0 : k1;
+                        keep_u += __shfl_xor_sync(0xffffffffu, give, 8);
+                        const float keep = (float)(int)(keep_u - kFxMagic64) * fx_inv;     // 64 lookups' magic offsets, mod 2^32
+                        if (p.n_k == 1) {
+                            if (!waited) { pdl_wait(); waited = true; }
+                            if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
+                        } else {
+                            // finish the atomic this slot issued PA sets ago (its L2 round trip, ~1.3 us under load, has
+                            // long completed), then issue this set's
+                            if (pend_valid[sa]) finish_row(pend_old[sa], pend_keep[sa], pend_row[sa]);
+                            pend_row[sa] = row; pend_valid[sa] = true; pend_keep[sa] = keep;
+#if LUTVQ_DBG
+                            if (p.flags & 0x400u) { pend_old[sa] = 0; if (row < p.O) static_cast<T*>(p.y)[row] = D::from_f(keep); }   // DEBUG: no atomics
+                            else
+#endif
+                            pend_old[sa] = atom_add_u64(p.acc + row, fx_contribution<DT>(keep));
+                        }
+                        v += NW;     if (v >= n_seg) v -= n_seg;
+                        vnext += NW; if (vnext >= n_seg) vnext -= n_seg;
                     }
                 }
             }
@@ -454,16 +544,17 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             ks = pos / p.n_sets;
             lo = pos - ks * p.n_sets;
             hi = min(p.n_sets, lo + (end - pos));
+            seg_rot = rot_of(ks, hi - lo);
             #pragma unroll
             for (int i = 0; i < PF; ++i)
-                if (lo + warp + i * NW < hi) load_set(buf[i], ks, set_of(warp + i * NW, ks, lo, hi));
+                if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + wrap(warp + i * NW + seg_rot, hi - lo));
             __syncthreads();                                       // everyone is done reading this slice's LUT
         }
     }
     TL_STAMP(4);
 
     #pragma unroll
-    for (int i = 0; i < PF; ++i)
+    for (int i = 0; i < PA; ++i)
         if (pend_valid[i]) finish_row(pend_old[i], pend_keep[i], pend_row[i]);
     TL_STAMP(5);
     if (!waited) pdl_wait();                                       // completion stays stream-ordered
@@ -491,7 +582,7 @@ __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __r
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
-struct GemvTuning { int nw = 8, pf = 2, ctas_per_sm = 1; };
+struct GemvTuning { int nw = 0, pf = 0, pa = 0; };   // 0 = choose per shape (launch_tuned)
 static GemvTuning g_tuning;
 static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][8] stamps
 static unsigned g_timeline_seq = 0;
@@ -546,9 +637,9 @@ int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStrea
     return LUTVQ_OK;
 }
 
-template <int DT, bool PACKED, int NW, int PF>
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB = 2>
 static int launch_variant(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
-    auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF>;
+    auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF, PA, MINB>;
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -572,15 +663,27 @@ static int launch_variant(const GemvParams& p, int grid, size_t smem, cudaStream
 
 template <int DT, bool PACKED>
 static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
-    const GemvTuning t = g_tuning;
-    if (t.nw == 8 && t.pf == 2)  return launch_variant<DT, PACKED, 8, 2>(p, grid, smem, stream, pdl);
-    if (t.nw == 8 && t.pf == 3)  return launch_variant<DT, PACKED, 8, 3>(p, grid, smem, stream, pdl);
-    if (t.nw == 8 && t.pf == 1)  return launch_variant<DT, PACKED, 8, 1>(p, grid, smem, stream, pdl);
-    if (t.nw == 16 && t.pf == 1) return launch_variant<DT, PACKED, 16, 1>(p, grid, smem, stream, pdl);
-    if (t.nw == 4 && t.pf == 4)  return launch_variant<DT, PACKED, 4, 4>(p, grid, smem, stream, pdl);
-    if (t.nw == 4 && t.pf == 3)  return launch_variant<DT, PACKED, 4, 3>(p, grid, smem, stream, pdl);
-    if (t.nw == 4 && t.pf == 2)  return launch_variant<DT, PACKED, 4, 2>(p, grid, smem, stream, pdl);
-    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d", t.nw, t.pf);
+    GemvTuning t = g_tuning;
+    if (t.nw == 0) {
+        // Measured on B200 (X_READY ring, packed codes): 3 CTAs/SM with a 1-deep code ring wins while a row has few
+        // split-k arrivals (4096x11008: 3.75 vs 4.39 us; 4096x4096: 2.39 vs 2.51 us); with many k-slices the exposed
+        // atomic round trip of the shallow ring loses to 2 CTAs/SM with 2-deep rings (11008x4096: 6.08 vs 5.07 us).
+        t.nw = 8;
+        if (p.n_k <= 24) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
+    }
+    if (t.nw == 8 && t.pf == 1 && t.pa == 1)  return launch_variant<DT, PACKED, 8, 1, 1, 3>(p, grid, smem, stream, pdl);   // 3 CTAs / SM
+    if (t.nw == 8 && t.pf == 2 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 2, 2, 2>(p, grid, smem, stream, pdl);   // 2 CTAs / SM, deeper ring
+#if LUTVQ_DBG
+    if (t.nw == 8 && t.pf == 2 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 2, 4>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 2 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 2, 6>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 1, 4>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 1, 6>(p, grid, smem, stream, pdl);
+    if (t.nw == 16 && t.pf == 1 && t.pa == 3) return launch_variant<DT, PACKED, 16, 1, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 4 && t.pf == 2 && t.pa == 8)  return launch_variant<DT, PACKED, 4, 2, 8, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 1, 2, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 2 && t.pa == 8)  return launch_variant<DT, PACKED, 8, 2, 2, 3>(p, grid, smem, stream, pdl);   // "8,2,8" = (8,2,2) at 3 CTAs/SM
+#endif
+    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d pa=%d", t.nw, t.pf, t.pa);
 }
 
 // One GEMV: y = epilogue(W(codes) . x).  Validation is done by the caller (api.cu).
@@ -607,6 +710,16 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
         p.base_q = pl.n_sets / pl.q;                  p.rem_q = pl.n_sets % pl.q;
         p.base_q1 = pl.n_sets / (pl.q + 1);           p.rem_q1 = pl.n_sets % (pl.q + 1);
     }
+    p.has_table = 0;
+    if (pl.W <= kRangeTable LUTVQ_DBG_AND(!(flags & 0x1000u))) {
+        for (int w = 0; w < pl.W; ++w) {
+            int b, e;
+            worker_range(p, w, pl.W, b, e);
+            p.tab_begin[w] = b; p.tab_begin[w + 1] = e;                 // ranges are contiguous: end(w) == begin(w+1)
+            p.tab_ks[w] = (unsigned short)(b < e ? b / pl.n_sets : 0);
+        }
+        p.has_table = 1;
+    }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
     p.tl = g_timeline ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
@@ -616,10 +729,10 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
     return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
 }
 
-void gemv_set_tuning(int nw, int pf, int ctas_per_sm) {
+void gemv_set_tuning(int nw, int pf, int pa) {
     if (nw > 0) g_tuning.nw = nw;
     if (pf > 0) g_tuning.pf = pf;
-    if (ctas_per_sm > 0) g_tuning.ctas_per_sm = ctas_per_sm;
+    if (pa > 0) g_tuning.pa = pa;
 }
 void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk) {
     DeviceInfo di;

@@ -141,11 +141,20 @@ def test_matmat_vs_oracle(pkg, ops, orc, I, O, scales, bias, batch):
         want64 = y64 * s64 + (0 if L["bias"] is None else L["bias"].astype(np.float64))
         got = y[b].float().cpu().numpy()
         assert rel_err(got, want64) <= TOL_GEMV
-        # and against the fp32-accumulate port with the reference's epilogue rounding: at most 1 fp16 ulp apart
+        # and against the fp32-accumulate port with the reference's epilogue rounding: at most 2 fp16 ulp apart, an ulp
+        # being that of the largest operand of the epilogue (round(acc)*s, bias, result) -- the bias add can cancel,
+        # and one ulp of the product is then many ulps of the (small) sum
         port = orc.c_aqlm_gemv_rowmajor(L["x"][b], L["codes"], L["codebooks"], L["scales"], L["bias"])
-        ulp = np.abs(bits(y[b]).astype(np.int64) - port.astype(np.int64))
-        ulp = np.minimum(ulp, np.abs(ulp - 0x8000))                   # +-0 crossing
-        assert (ulp <= 2).mean() > 0.999, f"fp16 outputs differ by more than 2 ulp in {(ulp > 2).mean():.4%} of rows"
+        portf = port.view(np.float16).astype(np.float64)
+        mag = np.maximum(np.abs(portf), np.abs(y64 * s64))
+        if L["bias"] is not None:
+            mag = np.maximum(mag, np.abs(L["bias"].astype(np.float64)))
+        ulp_size = 2.0 ** (np.floor(np.log2(np.maximum(mag, 2.0 ** -14))) - 10)
+        # the LUT is fixed point (gemv_lut.cu): absolute resolution 2^-22 of the slice bound 8*max|C|*max|x| per entry,
+        # which for a row that cancels to ~0 can exceed the (tiny) ulp of that row -- allow 4e-6 of the layer's range
+        floor_abs = 4e-6 * np.abs(y64 * s64).max()
+        off = np.maximum(np.abs(got.astype(np.float64) - portf) - floor_abs, 0) / ulp_size
+        assert (off <= 2).mean() > 0.999, f"fp16 outputs differ by more than 2 ulp in {(off > 2).mean():.4%} of rows"
 
 
 def test_matmat_bf16(pkg, ops, orc):

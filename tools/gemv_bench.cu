@@ -62,7 +62,7 @@ struct Layer { void* codes; void* packed; __half* cb; __half* scales; __half* x;
 
 int main(int argc, char** argv) {
     std::string shapes = "4096x4096,4096x11008,11008x4096";
-    int packed = 2, reps = 40, nw = 0, pf = 0;
+    int packed = 2, reps = 40, nw = 0, pf = 0, pa = 0;
     bool nopdl = false, check = false, ncu = false, timeline = false, xready = false;
     bool noscales = false;
     int wsring = 8;   // workspaces rotate through a ring of this many regions of ONE allocation (0: one allocation per layer)
@@ -74,7 +74,7 @@ int main(int argc, char** argv) {
         if (a == "--shapes") shapes = next();
         else if (a == "--packed") packed = atoi(next().c_str());
         else if (a == "--reps") reps = atoi(next().c_str());
-        else if (a == "--tuning") { std::string t = next(); sscanf(t.c_str(), "%d,%d", &nw, &pf); }
+        else if (a == "--tuning") { std::string t = next(); sscanf(t.c_str(), "%d,%d,%d", &nw, &pf, &pa); }
         else if (a == "--nopdl") nopdl = true;
         else if (a == "--xready") xready = true;
         else if (a == "--noscales") noscales = true;
@@ -85,7 +85,7 @@ int main(int argc, char** argv) {
         else if (a == "--timeline") timeline = true;
         else if (a == "--peak") peak = atof(next().c_str());
     }
-    if (nw) lutvq_debug_set_gemv_tuning(nw, pf, 0);
+    if (nw) lutvq_debug_set_gemv_tuning(nw, pf, pa);
     int sms = 0;
     LK(lutvq_device_info(&sms, nullptr, nullptr, nullptr));
     cudaStream_t st;
@@ -248,8 +248,8 @@ int main(int argc, char** argv) {
             CK(cudaEventElapsedTime(&ms, e0, e1));
             const double us = ms * 1e3 / ((double)reps * nbuf);
             const double gbps = alg_bytes / (us * 1e-6) / 1e9;
-            printf("{\"shape\": \"%s\", \"layout\": \"%s\", \"pdl\": %d, \"xready\": %d, \"dbg\": %u, \"tuning\": \"%d,%d\", \"us\": %.3f, \"gbps\": %.1f, \"frac\": %.4f, \"ring\": %d, \"sms\": %d}\n",
-                   sh.c_str(), mode ? "packed" : "reference", nopdl ? 0 : 1, xready ? 1 : 0, dbg, nw, pf, us, gbps, gbps / peak, nbuf, sms);
+            printf("{\"shape\": \"%s\", \"layout\": \"%s\", \"pdl\": %d, \"xready\": %d, \"dbg\": %u, \"tuning\": \"%d,%d,%d\", \"us\": %.3f, \"gbps\": %.1f, \"frac\": %.4f, \"ring\": %d, \"sms\": %d}\n",
+                   sh.c_str(), mode ? "packed" : "reference", nopdl ? 0 : 1, xready ? 1 : 0, dbg, nw, pf, pa, us, gbps, gbps / peak, nbuf, sms);
             CK(cudaGraphExecDestroy(exec));
             CK(cudaGraphDestroy(graph));
         }
