@@ -129,6 +129,38 @@ int lutvq_lut_gemv(const void* codeword, const void* lut, void* out, int d_out, 
 int lutvq_vq_dequantize(const void* codebook, const void* codeword, void* W, int d_out, int M, int N, int K,
                         int d, int cb_shared, void* stream);
 
+
+/* ---- output-channel-sharded decode over the GPUs of one NVSwitch domain (one process per GPU) --------------------
+ * Replaces nothing in the reference (its kernels are single-GPU; cuda_kernel.cu:486,497 even queries device 0): this
+ * is the multi-GPU row of the hot path (BASELINE.json north_star: "weight codes sharded by output channel across 2, 4
+ * and 8 GPUs ... all-gather of output slices over NVLink").  Rank r of P owns rows [r*O/P, (r+1)*O/P) of a layer.
+ * lutvq_sharded_matmat_packed runs the fused LUT-GEMV on the local rows and, in the SAME kernel, stores every finished
+ * row into the gather slot of every peer over NVLink and publishes the slot's epoch; lutvq_shard_wait (stream-ordered,
+ * graph-capturable, bounded spin) returns once all P slices of the slot have landed in the LOCAL slot, which then holds
+ * the whole y.  The NCCL all-gather variant of the same step lives in the host plumbing (rvv-lut-vq_b200/sharded.py).
+ *
+ *   create (cudaMalloc of {flags | n_slots x slot_bytes}) -> export (64-byte CUDA IPC handle) -> exchange the handles
+ *   with any host transport -> attach (maps the peers) -> [sharded_matmat_packed -> wait -> read lutvq_shard_slot()]* -> destroy
+ * A slot may be pushed again once every rank has consumed its previous epoch; rotate through >= 2 slots. */
+typedef struct lutvq_shard lutvq_shard_t;
+#define LUTVQ_SHARD_HANDLE_BYTES 64
+int    lutvq_shard_create(lutvq_shard_t** out, int nranks, int rank, int n_slots, size_t slot_bytes);
+int    lutvq_shard_export(lutvq_shard_t* s, void* handle64);
+int    lutvq_shard_attach(lutvq_shard_t* s, const void* handles /* nranks x 64 bytes, indexed by rank */);
+/* same-process alternative to export/attach: bases[r] = lutvq_shard_base() of rank r's object (peer access enabled) */
+int    lutvq_shard_attach_ptrs(lutvq_shard_t* s, void* const* bases);
+void*  lutvq_shard_base(lutvq_shard_t* s);
+void*  lutvq_shard_slot(lutvq_shard_t* s, int slot);              /* local device pointer of a gather slot */
+size_t lutvq_shard_slot_bytes(lutvq_shard_t* s);
+/* y_slot[row_offset + i] (on EVERY rank) = epilogue(W_local(packed) . x)[i], i < rows_local; batch 1.
+ * packed = lutvq_code2x8_prepack image of the LOCAL rows; other arguments as lutvq_code2x8_matmat_packed. */
+int    lutvq_sharded_matmat_packed(lutvq_shard_t* s, int slot, size_t row_offset, const void* x, const void* packed,
+                                   const void* codebooks, const void* scales, const void* bias, int rows_local,
+                                   int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
+int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
+int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
+int    lutvq_shard_destroy(lutvq_shard_t* s);
+
 #ifdef __cplusplus
 }
 #endif

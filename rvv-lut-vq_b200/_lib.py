@@ -36,6 +36,17 @@ SIGNATURES = {
     "lutvq_lut_build": (I, [P, P, P, I, I, I, I, I, I, P]),
     "lutvq_lut_gemv": (I, [P, P, P, I, I, I, I, I, I, P]),
     "lutvq_vq_dequantize": (I, [P, P, P, I, I, I, I, I, I, P]),
+    "lutvq_shard_create": (I, [P, I, I, I, SZ]),
+    "lutvq_shard_export": (I, [P, P]),
+    "lutvq_shard_attach": (I, [P, P]),
+    "lutvq_shard_attach_ptrs": (I, [P, P]),
+    "lutvq_shard_base": (P, [P]),
+    "lutvq_shard_slot": (P, [P, I]),
+    "lutvq_shard_slot_bytes": (SZ, [P]),
+    "lutvq_sharded_matmat_packed": (I, [P, I, SZ, P, P, P, P, P, I, I, I, U, P, SZ, P]),
+    "lutvq_shard_wait": (I, [P, I, P]),
+    "lutvq_shard_error": (I, [P, P]),
+    "lutvq_shard_destroy": (I, [P]),
 }
 DEBUG_SIGNATURES = {
     "lutvq_debug_set_gemv_tuning": (None, [I, I, I]),

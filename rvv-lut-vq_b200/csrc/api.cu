@@ -10,7 +10,7 @@ namespace lutvq {
 // launchers (gemv_lut.cu, dequant.cu, vq_golden.cu, gemm_tc.cu)
 int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
-                    cudaStream_t stream);
+                    cudaStream_t stream, const GemvPush* push = nullptr);
 size_t gemv_workspace_bytes(int O, int G);
 size_t gemv_packed_bytes(int O, int G);
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);

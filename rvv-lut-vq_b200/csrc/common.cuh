@@ -35,6 +35,16 @@ struct DeviceInfo {
 // Cached per device; queries the CURRENT device (not device 0 as cuda_kernel.cu:486,497 does).
 int get_device_info(DeviceInfo* out);
 
+// Peer targets of a sharded GEMV (shard.cu -> gemv_lut.cu): where each finished output element is ALSO stored, and
+// which flags the launch's last CTA publishes.  Pointers are device addresses valid on the launching GPU (local or
+// peer memory mapped through CUDA IPC / peer access).
+struct GemvPush {
+    int n = 0;
+    void* y[8] = {};             // peer r's gather buffer, already offset to this rank's first row
+    unsigned* flag[8] = {};      // peer r's epoch flag for (slot, this rank)
+    unsigned* sent = nullptr;    // local pushes-completed counter of the slot
+};
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

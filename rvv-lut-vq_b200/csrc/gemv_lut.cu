@@ -59,6 +59,7 @@ namespace lutvq {
 
 constexpr size_t kWsHeaderBytes = 256;        // reserved
 
+constexpr int kMaxPeers = 8;                  // one NVSwitch domain
 constexpr int kRangeTable = 160;              // workers whose item ranges ride in the kernel parameters (B200: 148)
 
 struct GemvParams {
@@ -75,6 +76,14 @@ struct GemvParams {
     unsigned magic_q, magic_q1;                 // ceil(2^20 / q), ceil(2^20 / (q+1))
     int base_q, rem_q, base_q1, rem_q1;         // n_sets = base_q*q + rem_q = base_q1*(q+1) + rem_q1
     unsigned flags;
+    // ---- output-channel-sharded decode (shard.cu): besides y, every finished row is stored into each peer's gather
+    // buffer over NVLink (peer pointers already offset to this rank's row range), and the LAST CTA of the launch to
+    // finish publishes the slot's epoch to every peer.  n_push == 0: plain single-GPU GEMV, none of this is touched.
+    int n_push;
+    void* push_y[kMaxPeers];                    // peer r's gather buffer + this rank's row offset
+    unsigned* push_flag[kMaxPeers];             // peer r's epoch flag for (slot, this rank)
+    unsigned* push_sent;                        // local: pushes completed on this slot so far (epoch counter)
+    unsigned* cta_arrivals;                     // local: workspace header word counting finished CTAs (self-resetting)
     int has_table;                              // 1: the host tabulated every worker's range (W <= kRangeTable)
     int tab_begin[kRangeTable + 1];             // worker w owns linear items [tab_begin[w], tab_begin[w+1])
     unsigned short tab_ks[kRangeTable];         // k-slice of item tab_begin[w]
@@ -184,6 +193,14 @@ __device__ __forceinline__ void fx_scales(float bound, float& scale, float& inv)
     ex = max(ex, 21u);
     scale = __uint_as_float((275u - ex) << 23);                      // 2^(148 - ex): bound * scale < 2^22
     inv   = bad ? __uint_as_float(0x7FC00000u) : __uint_as_float((ex - 21u) << 23);
+}
+
+// store one finished output element locally and into every peer's gather buffer (sharded decode)
+template <int DT>
+__device__ __forceinline__ void store_y(const GemvParams& p, int row, typename Dtype<DT>::T v) {
+    using T = typename Dtype<DT>::T;
+    static_cast<T*>(p.y)[row] = v;
+    for (int r = 0; r < p.n_push; ++r) static_cast<T*>(p.push_y[r])[row] = v;       // NVLink stores (peer memory)
 }
 
 // One warp tile set = 32 rows x 64 bytes: 4 tiles of 8 rows; per lane 4 x 16 bytes.
@@ -402,7 +419,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                 // scale / bias were pulled into L2 by the prologue; only the last arriver (1 in n_k) pays this round trip
                 if (p.scales) rr = D::mul(rr, static_cast<const T*>(p.scales)[row]);   // flat_output *= scales             (cuda_kernel.cpp:101)
                 if (p.bias)   rr = D::add(rr, static_cast<const T*>(p.bias)[row]);     // flat_output += bias               (cuda_kernel.cpp:103)
-                static_cast<T*>(p.y)[row] = rr;
+                store_y<DT>(p, row, rr);
             }
         }
     };
@@ -521,7 +538,12 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                         const float keep = (float)(int)(keep_u - kFxMagic64) * fx_inv;     // 64 lookups' magic offsets, mod 2^32
                         if (p.n_k == 1) {
                             if (!waited) { pdl_wait(); waited = true; }
-                            if (row < p.O) epilogue_store<DT>(p.y, p.scales, p.bias, row, keep);
+                            if (row < p.O) {
+                                T rr = D::from_f(keep);
+                                if (p.scales) rr = D::mul(rr, static_cast<const T*>(p.scales)[row]);
+                                if (p.bias)   rr = D::add(rr, static_cast<const T*>(p.bias)[row]);
+                                store_y<DT>(p, row, rr);
+                            }
                         } else {
                             // finish the atomic this slot issued PA sets ago (its L2 round trip, ~1.3 us under load, has
                             // long completed), then issue this set's
@@ -559,6 +581,27 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     TL_STAMP(5);
     if (!waited) pdl_wait();                                       // completion stays stream-ordered
     TL_STAMP(6);
+    if (p.n_push > 0) {
+        // All of this CTA's y / peer stores are issued; make them visible system-wide, then count the CTA in.  The CTA
+        // that completes the count has (by fence cumulativity) every CTA's stores ordered before its own flag writes.
+        __syncthreads();
+        __shared__ unsigned last_flag;
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            const unsigned prev = atomicAdd(p.cta_arrivals, 1u);
+            last_flag = (prev == gridDim.x - 1) ? 1u : 0u;
+        }
+        __syncthreads();
+        if (last_flag) {
+            if (threadIdx.x == 0) *p.cta_arrivals = 0u;                               // self-cleaning, like the accumulators
+            __threadfence_system();
+            const unsigned epoch = *p.push_sent + 1u;
+            if ((int)threadIdx.x < p.n_push)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p.push_flag[threadIdx.x]), "r"(epoch) : "memory");
+            __syncthreads();
+            if (threadIdx.x == 0) *p.push_sent = epoch;
+        }
+    }
 }
 
 // [k-slice][set][tile][lane] x 16 B register images from reference-layout codes (see file header)
@@ -689,7 +732,7 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
 // One GEMV: y = epilogue(W(codes) . x).  Validation is done by the caller (api.cu).
 int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
-                    cudaStream_t stream) {
+                    cudaStream_t stream, const GemvPush* push) {
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
     const int G = I / 8;
@@ -709,6 +752,14 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
         p.magic_q = ((1u << 20) + pl.q - 1) / pl.q;   p.magic_q1 = ((1u << 20) + pl.q) / (pl.q + 1);
         p.base_q = pl.n_sets / pl.q;                  p.rem_q = pl.n_sets % pl.q;
         p.base_q1 = pl.n_sets / (pl.q + 1);           p.rem_q1 = pl.n_sets % (pl.q + 1);
+    }
+    p.n_push = 0; p.push_sent = nullptr;
+    p.cta_arrivals = reinterpret_cast<unsigned*>(ws);                // first word of the reserved workspace header
+    for (int r = 0; r < kMaxPeers; ++r) { p.push_y[r] = nullptr; p.push_flag[r] = nullptr; }
+    if (push != nullptr && push->n > 0) {
+        LUTVQ_REQUIRE(push->n <= kMaxPeers, "at most %d push targets", kMaxPeers);
+        p.n_push = push->n; p.push_sent = push->sent;
+        for (int r = 0; r < push->n; ++r) { p.push_y[r] = push->y[r]; p.push_flag[r] = push->flag[r]; }
     }
     p.has_table = 0;
     if (pl.W <= kRangeTable LUTVQ_DBG_AND(!(flags & 0x1000u))) {

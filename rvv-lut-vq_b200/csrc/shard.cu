@@ -1,0 +1,221 @@
+// shard.cu -- output-channel-sharded decode across the GPUs of one NVSwitch domain.
+//
+// Rank r of P holds codes[r*O/P : (r+1)*O/P] and computes that slice of y with the SAME fused LUT-GEMV kernel
+// (prob_m = O/P).  The exchange step of the path -- every rank needs the whole y as the next layer's input -- is fused
+// into the kernel's epilogue instead of a separate collective: the lane that finishes a row stores it into every peer's
+// gather buffer over NVLink (plain peer stores, 2 bytes x P per row), and the last CTA of the launch publishes the
+// slot's epoch to every peer with one st.release.sys each.  A consumer waits (lutvq_shard_wait: one warp spinning on
+// ITS OWN memory with ld.acquire.sys) until all P epochs of the slot have arrived.  No NCCL call, no extra copy,
+// no host involvement; everything is graph-capturable because the epochs live in device memory.
+//
+// One process per GPU: each rank cudaMalloc's one symmetric buffer {flags | gather slots}, exports it as a CUDA IPC
+// handle, the handles are exchanged by the host plumbing (torch.distributed in rvv-lut-vq_b200/sharded.py) and every
+// rank maps its peers' buffers (lutvq_shard_attach).  lutvq_shard_attach_ptrs takes raw device pointers instead, for a
+// single process that drives several GPUs with peer access enabled (and for the one-GPU protocol test).
+//
+// Slot reuse: a slot may be pushed again once every rank has consumed its previous epoch.  In a decode chain that is
+// implied with >= 2 slots (a rank can only be one gather ahead of the slowest peer); the python
+// layer rotates through all slots.
+#include "common.cuh"
+
+#include <new>
+#include <string.h>
+
+namespace lutvq {
+
+int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
+                    const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
+                    cudaStream_t stream, const GemvPush* push);
+
+constexpr int    kShardMaxRanks  = 8;
+constexpr int    kShardMaxSlots  = 16;
+constexpr size_t kShardFlagBytes = 4096;       // [slot][rank] uint32 epochs written by peers, then local counters
+constexpr size_t kLocalOff       = 2048;       // local-only area inside the flag page: sent[slot], consumed[slot], error
+
+struct Shard {
+    int nranks = 0, rank = 0, n_slots = 0, device = -1;
+    size_t slot_bytes = 0, total_bytes = 0;
+    uint8_t* local = nullptr;                   // this rank's symmetric buffer
+    uint8_t* peer[kShardMaxRanks] = {};         // peer[r] = rank r's buffer as mapped here (peer[rank] == local)
+    bool ipc_opened[kShardMaxRanks] = {};
+    bool attached = false;
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// One warp.  Lane r < nranks spins on flag[slot][r] (local memory, written remotely) until it reaches the slot's next
+// expected epoch.  Bounded: after `timeout_ns` the kernel records an error word and returns instead of hanging the GPU.
+__global__ void shard_wait_kernel(const unsigned* flags, unsigned* consumed, unsigned* error, int nranks,
+                                  unsigned long long timeout_ns) {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const unsigned want = *consumed + 1u;
+    const int lane = threadIdx.x;
+    bool ok = true;
+    if (lane < nranks) {
+        unsigned long long t0, t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int)(ld_acquire_sys(flags + lane) - want) < 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) { ok = false; break; }
+            __nanosleep(64);
+        }
+    }
+    const unsigned all_ok = __all_sync(0xffffffffu, ok);
+    __threadfence_system();
+    if (lane == 0) {
+        *consumed = want;
+        if (!all_ok) *error = want;
+    }
+}
+
+}  // namespace lutvq
+
+using namespace lutvq;
+
+extern "C" {
+
+int lutvq_shard_create(lutvq_shard_t** out, int nranks, int rank, int n_slots, size_t slot_bytes) {
+    LUTVQ_REQUIRE(out != nullptr, "null out pointer");
+    LUTVQ_REQUIRE(nranks >= 1 && nranks <= kShardMaxRanks && rank >= 0 && rank < nranks, "bad nranks=%d rank=%d (<= %d ranks)", nranks, rank, kShardMaxRanks);
+    LUTVQ_REQUIRE(n_slots >= 1 && n_slots <= kShardMaxSlots, "n_slots=%d must be in 1..%d", n_slots, kShardMaxSlots);
+    LUTVQ_REQUIRE(slot_bytes > 0, "slot_bytes must be positive");
+    DeviceInfo di;
+    if (int rc = get_device_info(&di)) return rc;
+    Shard* s = new (std::nothrow) Shard();
+    LUTVQ_REQUIRE(s != nullptr, "out of host memory");
+    s->nranks = nranks; s->rank = rank; s->n_slots = n_slots; s->device = di.device;
+    s->slot_bytes = (slot_bytes + 255) / 256 * 256;
+    s->total_bytes = kShardFlagBytes + s->slot_bytes * n_slots;
+    cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&s->local), s->total_bytes);
+    if (e != cudaSuccess) { delete s; return fail(LUTVQ_ECUDA, "cudaMalloc(%zu) failed: %s", s->total_bytes, cudaGetErrorString(e)); }
+    e = cudaMemset(s->local, 0, s->total_bytes);
+    if (e != cudaSuccess) { cudaFree(s->local); delete s; return fail(LUTVQ_ECUDA, "cudaMemset failed: %s", cudaGetErrorString(e)); }
+    s->peer[rank] = s->local;
+    s->attached = (nranks == 1);
+    *out = reinterpret_cast<lutvq_shard_t*>(s);
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_export(lutvq_shard_t* h, void* handle64) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s && handle64, "null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == LUTVQ_SHARD_HANDLE_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t ih;
+    LUTVQ_CUDA_OK(cudaIpcGetMemHandle(&ih, s->local));
+    memcpy(handle64, &ih, sizeof(ih));
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_attach(lutvq_shard_t* h, const void* handles) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s && handles, "null pointer");
+    for (int r = 0; r < s->nranks; ++r) {
+        if (r == s->rank || s->peer[r] != nullptr) continue;
+        cudaIpcMemHandle_t ih;
+        memcpy(&ih, static_cast<const uint8_t*>(handles) + (size_t)r * LUTVQ_SHARD_HANDLE_BYTES, sizeof(ih));
+        void* p = nullptr;
+        LUTVQ_CUDA_OK(cudaIpcOpenMemHandle(&p, ih, cudaIpcMemLazyEnablePeerAccess));
+        s->peer[r] = static_cast<uint8_t*>(p);
+        s->ipc_opened[r] = true;
+    }
+    s->attached = true;
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_attach_ptrs(lutvq_shard_t* h, void* const* bases) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s && bases, "null pointer");
+    for (int r = 0; r < s->nranks; ++r) {
+        if (r == s->rank) continue;
+        LUTVQ_REQUIRE(bases[r] != nullptr, "null base pointer for rank %d", r);
+        s->peer[r] = static_cast<uint8_t*>(bases[r]);
+    }
+    s->attached = true;
+    return LUTVQ_OK;
+}
+
+void* lutvq_shard_base(lutvq_shard_t* h) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    return s ? s->local : nullptr;
+}
+
+void* lutvq_shard_slot(lutvq_shard_t* h, int slot) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    if (!s || slot < 0 || slot >= s->n_slots) return nullptr;
+    return s->local + kShardFlagBytes + s->slot_bytes * slot;
+}
+
+size_t lutvq_shard_slot_bytes(lutvq_shard_t* h) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    return s ? s->slot_bytes : 0;
+}
+
+int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, const void* x, const void* packed,
+                                const void* codebooks, const void* scales, const void* bias, int rows_local,
+                                int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr, "null shard handle");
+    LUTVQ_REQUIRE(s->attached, "lutvq_shard_attach has not been called");
+    LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
+    LUTVQ_REQUIRE(rows_local > 0 && prob_k > 0 && prob_k % 64 == 0, "bad shape rows_local=%d prob_k=%d", rows_local, prob_k);
+    LUTVQ_REQUIRE((row_offset + (size_t)rows_local) * 2 <= s->slot_bytes, "rows [%zu, %zu) do not fit a %zu-byte slot", row_offset, row_offset + rows_local, s->slot_bytes);
+    LUTVQ_REQUIRE(x && packed && codebooks, "null pointer");
+    if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+    const size_t slot_off = kShardFlagBytes + s->slot_bytes * slot + row_offset * 2;
+    GemvPush push;
+    push.n = 0;
+    for (int r = 0; r < s->nranks; ++r) {
+        if (r == s->rank) continue;                                  // the local copy is the kernel's ordinary y store
+        push.y[push.n] = s->peer[r] + slot_off;
+        push.flag[push.n] = reinterpret_cast<unsigned*>(s->peer[r]) + (size_t)slot * kShardMaxRanks + s->rank;
+        ++push.n;
+    }
+    // the local flag goes through the same mechanism (own buffer is "peer" rank): keeps one code path for P == 1
+    push.y[push.n] = s->local + slot_off;                            // harmless duplicate of the y store
+    push.flag[push.n] = reinterpret_cast<unsigned*>(s->local) + (size_t)slot * kShardMaxRanks + s->rank;
+    ++push.n;
+    push.sent = reinterpret_cast<unsigned*>(s->local + kLocalOff) + slot;
+    void* y_local = s->local + slot_off;
+    return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
+                           static_cast<cudaStream_t>(stream), &push);
+}
+
+int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range", slot);
+    const unsigned* flags = reinterpret_cast<const unsigned*>(s->local) + (size_t)slot * kShardMaxRanks;
+    unsigned* local = reinterpret_cast<unsigned*>(s->local + kLocalOff);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(32); cfg.dynamicSmemBytes = 0; cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_wait_kernel, flags, local + kShardMaxSlots + slot, local + 2 * kShardMaxSlots,
+                                     s->nranks, 2000000000ull));
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_error(lutvq_shard_t* h, unsigned* out) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s && out, "null pointer");
+    LUTVQ_CUDA_OK(cudaMemcpy(out, s->local + kLocalOff + 2 * kShardMaxSlots * sizeof(unsigned), sizeof(unsigned), cudaMemcpyDeviceToHost));
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_destroy(lutvq_shard_t* h) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    if (!s) return LUTVQ_OK;
+    for (int r = 0; r < s->nranks; ++r)
+        if (s->ipc_opened[r] && s->peer[r]) cudaIpcCloseMemHandle(s->peer[r]);
+    if (s->local) cudaFree(s->local);
+    delete s;
+    return LUTVQ_OK;
+}
+
+}  // extern "C"
