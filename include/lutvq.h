@@ -50,11 +50,15 @@ typedef enum { LUTVQ_F16 = 0, LUTVQ_BF16 = 1 } lutvq_dtype_t;
 /* flags for the *_ex entry points */
 #define LUTVQ_FLAG_LUT_FP16   1u  /* round LUT entries to fp16 (vq.py:285 semantics) before accumulation */
 #define LUTVQ_FLAG_NO_PDL     2u  /* do not use programmatic dependent launch for this call */
-#define LUTVQ_FLAG_X_READY    4u  /* caller's promise: (1) x was NOT written by the kernel(s) immediately preceding this call
-                                     in the stream (e.g. the k/v projections after q, up after gate, or a microbenchmark
-                                     loop over resident inputs), and (2) ws is not used by any of the LUTVQ_XREADY_WS_RING - 1
-                                     calls before or after this one in the stream (rotate through a ring of workspaces).
-                                     The LUT build, the gather and the split-k reduction then overlap the previous kernel;
+#define LUTVQ_FLAG_X_READY    4u  /* caller's promise: (1) x was complete BEFORE the run of back-to-back launches this call belongs
+                                     to began -- i.e. it was not written by any kernel still in flight when this one may start.
+                                     Launches overlap under programmatic dependent launch, so "not the kernel right before"
+                                     is NOT enough: with producer -> A -> B(X_READY), B can start while the producer of x is
+                                     still running.  Valid: a microbenchmark loop over resident inputs, weights-only
+                                     prefetch runs, inputs produced before a stream/event synchronisation.
+                                     (2) ws is not used by any of the LUTVQ_XREADY_WS_RING - 1 calls before or after this one
+                                     in the stream (rotate through a ring of workspaces).
+                                     The LUT build, the gather and the split-k reduction then overlap the previous kernels;
                                      the y stores and the completion of the call stay stream-ordered. */
 #define LUTVQ_XREADY_WS_RING  8
 
@@ -160,6 +164,18 @@ int    lutvq_sharded_matmat_packed(lutvq_shard_t* s, int slot, size_t row_offset
 int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
 int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
 int    lutvq_shard_destroy(lutvq_shard_t* s);
+
+/* ---- decode glue (fp16, batch 1): the non-GEMV steps of a Llama-shaped decode step, so a whole token is one chain of
+ * launches of this library inside a CUDA graph.  Not reference entry points (the reference takes these from HF
+ * transformers, benchmark/llm/generate_benchmark.py) and not LUT-VQ work; they exist for the decode tok/s metric.
+ *   add_rmsnorm : resid += delta (delta may be NULL); y = resid * rsqrt(mean(resid^2) + eps) * w        (n <= 16384)
+ *   silu_mul    : y = silu(gate) * up
+ *   attention   : RoPE(q, k_new) at position *pos (device int), append k/v to the caches [n_kv][max_seq][128],
+ *                 out = softmax(q K^T / sqrt(128)) V over positions 0..*pos; head_dim must be 128 */
+int lutvq_decode_add_rmsnorm(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream);
+int lutvq_decode_silu_mul(const void* gate, const void* up, void* y, int n, void* stream);
+int lutvq_decode_attention(const void* q, const void* k_new, const void* v_new, void* kcache, void* vcache, const int* pos,
+                           void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream);
 
 #ifdef __cplusplus
 }

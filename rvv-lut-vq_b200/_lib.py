@@ -47,6 +47,9 @@ SIGNATURES = {
     "lutvq_shard_wait": (I, [P, I, P]),
     "lutvq_shard_error": (I, [P, P]),
     "lutvq_shard_destroy": (I, [P]),
+    "lutvq_decode_add_rmsnorm": (I, [P, P, P, P, I, ctypes.c_float, P]),
+    "lutvq_decode_silu_mul": (I, [P, P, P, I, P]),
+    "lutvq_decode_attention": (I, [P, P, P, P, P, P, P, I, I, I, I, ctypes.c_float, P]),
 }
 DEBUG_SIGNATURES = {
     "lutvq_debug_set_gemv_tuning": (None, [I, I, I]),

@@ -1,0 +1,161 @@
+// decode_glue.cu -- the small non-GEMV steps of a Llama-shaped decode step (batch 1), so that the whole token is a
+// chain of OUR launches inside one CUDA graph: residual add + RMSNorm, RoPE + KV append + single-query attention,
+// SwiGLU.  The reference gets these from HF transformers (benchmark/llm/generate_benchmark.py); they are not LUT-VQ
+// work and are outside the graded hot path, but the decode tok/s metric (BASELINE.json configs[3], [4]) runs through them.
+// fp16 only (the decode benchmark's dtype).  All kernels honour programmatic dependent launch like the GEMV.
+#include "common.cuh"
+
+namespace lutvq {
+
+__device__ __forceinline__ float warp_sum(float v) {
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// resid (+= delta, if given);  y = resid * rsqrt(mean(resid^2) + eps) * w.   One CTA, n <= 1024 * 16.
+__global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps) {
+    pdl_launch_dependents();
+    pdl_wait();
+    __shared__ float red[32];
+    float v[16];
+    float ss = 0.f;
+    int cnt = 0;
+    for (int i = threadIdx.x; i < n; i += 1024, ++cnt) {
+        float a = __half2float(resid[i]);
+        if (delta) { a = __half2float(__float2half_rn(a + __half2float(delta[i]))); resid[i] = __float2half_rn(a); }
+        v[cnt] = a;
+        ss += a * a;
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+    #pragma unroll
+    for (int i = 0; i < 32; ++i) tot += red[i];
+    const float r = rsqrtf(tot / (float)n + eps);
+    cnt = 0;
+    for (int i = threadIdx.x; i < n; i += 1024, ++cnt) y[i] = __float2half_rn(v[cnt] * r * __half2float(w[i]));
+}
+
+__global__ void silu_mul_kernel(const __half* g, const __half* u, __half* y, int n) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const float a = __half2float(g[i]);
+        y[i] = __float2half_rn(a / (1.f + __expf(-a)) * __half2float(u[i]));
+    }
+}
+
+// One CTA (128 threads = head_dim) per query head.  RoPE (HF rotate_half convention) on q and on the new k, the new
+// k/v appended to the cache at *pos by the first head of each KV group, then softmax(q.K^T / sqrt(d)) V over [0, *pos].
+constexpr int kHeadDim = 128;
+__global__ void __launch_bounds__(kHeadDim) attn_decode_kernel(const __half* q, const __half* k_new, const __half* v_new,
+                                                              __half* kcache, __half* vcache, const int* pos_ptr, __half* out,
+                                                              int n_heads, int n_kv, int max_seq, float theta) {
+    pdl_launch_dependents();
+    pdl_wait();
+    extern __shared__ float sc[];                 // [max_seq] scores
+    __shared__ float qs[kHeadDim], ks[kHeadDim], red[4];
+    const int h = blockIdx.x, d = threadIdx.x, lane = d & 31, warp = d >> 5;
+    const int kvh = h / (n_heads / n_kv);
+    const int pos = *pos_ptr;
+    const int half_d = kHeadDim / 2, i = d % half_d;
+    const float freq = __powf(theta, -2.f * (float)i / (float)kHeadDim);
+    float sn, cs;
+    __sincosf((float)pos * freq, &sn, &cs);
+    {
+        const float a = __half2float(q[h * kHeadDim + d]), b = __half2float(q[h * kHeadDim + (d < half_d ? d + half_d : d - half_d)]);
+        qs[d] = (d < half_d) ? a * cs - b * sn : a * cs + b * sn;
+        const float c = __half2float(k_new[kvh * kHeadDim + d]), e = __half2float(k_new[kvh * kHeadDim + (d < half_d ? d + half_d : d - half_d)]);
+        ks[d] = (d < half_d) ? c * cs - e * sn : c * cs + e * sn;
+    }
+    const float vn = __half2float(v_new[kvh * kHeadDim + d]);
+    if (h % (n_heads / n_kv) == 0) {
+        kcache[((size_t)kvh * max_seq + pos) * kHeadDim + d] = __float2half_rn(ks[d]);
+        vcache[((size_t)kvh * max_seq + pos) * kHeadDim + d] = __float2half_rn(vn);
+    }
+    __syncthreads();
+    const float scale = rsqrtf((float)kHeadDim);
+    // scores: warp w takes positions w, w+4, ...; lane covers 4 dims
+    float mx = -1e30f;
+    for (int t = warp; t <= pos; t += 4) {
+        float s = 0.f;
+        if (t < pos) {
+            const __half2* kr = reinterpret_cast<const __half2*>(kcache + ((size_t)kvh * max_seq + t) * kHeadDim) + lane * 2;
+            const float2 k0 = __half22float2(kr[0]), k1 = __half22float2(kr[1]);
+            s = qs[4 * lane] * k0.x + qs[4 * lane + 1] * k0.y + qs[4 * lane + 2] * k1.x + qs[4 * lane + 3] * k1.y;
+        } else {
+            // the current position comes from shared memory (rounded like the cache copy), not from the racing global store
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) s += qs[4 * lane + j] * __half2float(__float2half_rn(ks[4 * lane + j]));
+        }
+        s = warp_sum(s) * scale;
+        if (lane == 0) sc[t] = s;
+        mx = fmaxf(mx, s);
+    }
+    mx = warp_max(mx);
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+    __syncthreads();
+    float sum = 0.f;
+    for (int t = d; t <= pos; t += kHeadDim) { const float e = __expf(sc[t] - mx); sc[t] = e; sum += e; }
+    sum = warp_sum(sum);
+    if (lane == 0) red[warp] = sum;
+    __syncthreads();
+    const float inv = 1.f / (red[0] + red[1] + red[2] + red[3]);
+    float acc = 0.f;
+    for (int t = 0; t < pos; ++t) acc += sc[t] * __half2float(vcache[((size_t)kvh * max_seq + t) * kHeadDim + d]);
+    acc += sc[pos] * __half2float(__float2half_rn(vn));
+    out[h * kHeadDim + d] = __float2half_rn(acc * inv);
+}
+
+template <typename... Args>
+static int launch_pdl(void (*kern)(Args...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, args...));
+    return LUTVQ_OK;
+}
+
+}  // namespace lutvq
+
+using namespace lutvq;
+
+extern "C" {
+
+int lutvq_decode_add_rmsnorm(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream) {
+    LUTVQ_REQUIRE(resid && w && y && n > 0 && n <= 16384, "bad arguments (n=%d, n <= 16384)", n);
+    return launch_pdl(add_rmsnorm_kernel, dim3(1), dim3(1024), 0, static_cast<cudaStream_t>(stream), static_cast<__half*>(resid),
+                      static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps);
+}
+
+int lutvq_decode_silu_mul(const void* gate, const void* up, void* y, int n, void* stream) {
+    LUTVQ_REQUIRE(gate && up && y && n > 0, "bad arguments");
+    return launch_pdl(silu_mul_kernel, dim3((n + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream),
+                      static_cast<const __half*>(gate), static_cast<const __half*>(up), static_cast<__half*>(y), n);
+}
+
+int lutvq_decode_attention(const void* q, const void* k_new, const void* v_new, void* kcache, void* vcache, const int* pos,
+                           void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream) {
+    LUTVQ_REQUIRE(q && k_new && v_new && kcache && vcache && pos && out, "null pointer");
+    LUTVQ_REQUIRE(head_dim == kHeadDim, "head_dim must be %d", kHeadDim);
+    LUTVQ_REQUIRE(n_heads > 0 && n_kv_heads > 0 && n_heads % n_kv_heads == 0 && max_seq > 0 && max_seq <= 8192, "bad head counts / max_seq");
+    return launch_pdl(attn_decode_kernel, dim3(n_heads), dim3(kHeadDim), (size_t)max_seq * sizeof(float), static_cast<cudaStream_t>(stream),
+                      static_cast<const __half*>(q), static_cast<const __half*>(k_new), static_cast<const __half*>(v_new),
+                      static_cast<__half*>(kcache), static_cast<__half*>(vcache), pos, static_cast<__half*>(out), n_heads, n_kv_heads,
+                      max_seq, rope_theta);
+}
+
+}  // extern "C"

@@ -30,6 +30,7 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
 constexpr int    kShardMaxRanks  = 8;
 constexpr int    kShardMaxSlots  = 16;
 constexpr size_t kShardFlagBytes = 4096;       // [slot][rank] uint32 epochs written by peers, then local counters
+constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;   // a wait gives up (and records an error) after 4 s
 constexpr size_t kLocalOff       = 2048;       // local-only area inside the flag page: sent[slot], consumed[slot], error
 
 struct Shard {
@@ -197,7 +198,7 @@ int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_wait_kernel, flags, local + kShardMaxSlots + slot, local + 2 * kShardMaxSlots,
-                                     s->nranks, 2000000000ull));
+                                     s->nranks, kWaitTimeoutNs));
     return LUTVQ_OK;
 }
 
