@@ -157,6 +157,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--force-shard", action="store_true", help="experiment: take the sharded (push) path even at N=1")
     ap.add_argument("--tuning", default="", help="nw,pf,ctas_per_sm override for the GEMV kernel (experiments)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -184,7 +185,6 @@ def main():
     layers = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=1000 * rank + i, scales="ones") for i in range(NBUF)]
     xs = torch.randn((NBUF, 1, IN_F), device=dev, dtype=torch.float16)
     ys = torch.empty((NBUF, 1, OUT_F), device=dev, dtype=torch.float16)
-    gathered = torch.empty((NBUF, world * OUT_F), device=dev, dtype=torch.float16) if world > 1 else None
     stream = torch.cuda.Stream(dev)
 
     import ctypes
@@ -198,29 +198,55 @@ def main():
     assert NBUF % ops.XREADY_WS_RING == 0
     FLAGS = {"x_ready": pkg._lib.FLAG_X_READY, "dependent": 0}
 
-    def step_body(mode="x_ready"):
+    # N > 1: each rank owns an OUT_F-row shard of an (N * OUT_F)-row layer; the GEMV kernel itself pushes its rows into
+    # every peer's gather slot over NVLink (lutvq_sharded_matmat_packed) and one wait kernel per group of GROUP GEMVs
+    # confirms that all N slices of those slots have landed locally.
+    GROUP = 6
+    group = None
+    sharded = world > 1 or args.force_shard
+    if sharded:
+        from rvv_lut_vq_b200.sharded import ShardGroup
+        group = ShardGroup.from_process_group(world * OUT_F, n_slots=NBUF) if world > 1 else ShardGroup(1, 0, OUT_F, n_slots=NBUF)
+        slot_views = [group.slot_tensor(sl, world * OUT_F, torch.float16) for sl in range(NBUF)]
+
+    def step_body(mode="x_ready", first=0, count=NBUF):
         st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        for i, L in enumerate(layers):
+        mask = 0
+        for i in range(first, first + count):
+            L = layers[i]
             ws = ws_ring[(i % ops.XREADY_WS_RING) * ws_need:]
-            pkg._lib.check(lib.lutvq_code2x8_matmat_packed(P(xs[i]), P(packed[i]), P(L["codebooks"]), P(L["scales"]), None,
-                                                           P(ys[i]), 1, OUT_F, IN_F, 0, FLAGS[mode], P(ws), ws_need, st))
-            if world > 1:
-                dist.all_gather_into_tensor(gathered[i], ys[i, 0])
+            if not sharded:
+                pkg._lib.check(lib.lutvq_code2x8_matmat_packed(P(xs[i]), P(packed[i]), P(L["codebooks"]), P(L["scales"]), None,
+                                                               P(ys[i]), 1, OUT_F, IN_F, 0, FLAGS[mode], P(ws), ws_need, st))
+            else:
+                slot = i                                            # one gather slot per GEMV of the step: reused only after the step-end wait
+                pkg._lib.check(lib.lutvq_sharded_matmat_packed(group._h, slot, rank * OUT_F, P(xs[i]), P(packed[i]), P(L["codebooks"]),
+                                                               P(L["scales"]), None, OUT_F, IN_F, 0, FLAGS[mode], P(ws), ws_need, st))
+                mask |= 1 << slot
+                if i % GROUP == GROUP - 1:
+                    # the exchange of the group runs on a side stream (a parallel branch of the captured graph), so the
+                    # GEMV launch chain on the main stream is never queued behind it
+                    main = torch.cuda.current_stream(dev)
+                    side.wait_stream(main)
+                    with torch.cuda.stream(side):
+                        pkg._lib.check(lib.lutvq_shard_wait_mask(group._h, mask, ctypes.c_void_p(side.cuda_stream)))
+                    mask = 0
+        if sharded:
+            torch.cuda.current_stream(dev).wait_stream(side)            # end of the (partial) step: every slice confirmed
+
+    side = torch.cuda.Stream(dev) if sharded else None
 
     with torch.cuda.stream(stream):
         step_body()
         torch.cuda.synchronize()
-        graph = None
-        if world == 1:
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=stream):
-                step_body()
+        if world > 1:
+            dist.barrier()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            step_body()
 
         def run_step():
-            if graph is not None:
-                graph.replay()
-            else:
-                step_body()
+            graph.replay()
 
         def timed(n_steps):
             if world > 1:
@@ -278,13 +304,18 @@ def main():
         # ---- e2e: host buffers through the reference-facing op ----
         x_host = torch.randn((NBUF, 1, IN_F), dtype=torch.float16).pin_memory()
         y_host = torch.empty((NBUF, 1, OUT_F), dtype=torch.float16).pin_memory()
+        yg_host = torch.empty((NBUF, world * OUT_F), dtype=torch.float16).pin_memory() if sharded else None
 
         def e2e_step():
             # one step end to end: the step's activations come from pinned host memory, the C-ABI GEMVs run (as the
             # captured graph for 1 GPU, eagerly + all-gather otherwise), the step's outputs are read back to the host
             xs.copy_(x_host, non_blocking=True)
             run_step()
-            y_host.copy_(ys, non_blocking=True)
+            if not sharded:
+                y_host.copy_(ys, non_blocking=True)
+            else:
+                for j in range(NBUF):                                   # the gathered outputs live in the slot ring
+                    yg_host[j].copy_(slot_views[j], non_blocking=True)
 
         e2e_steps = max(3, args.steps // 10)
         for _ in range(3):
@@ -382,14 +413,15 @@ def main():
                    "gemvs_per_step": NBUF, "cache": f"inputs larger than L2: {NBUF} distinct code matrices = {NBUF * OUT_F * IN_F // 4 / 1e6:.0f} MB per step",
                    "launch": ("one CUDA graph per step; the GEMVs of a step are independent (resident inputs), issued with LUTVQ_FLAG_X_READY on "
                               "prepacked codes + a ring of 8 workspaces, so consecutive launches overlap under programmatic dependent launch; "
-                              "dependent_chain_us_per_gemv is the same ring without the promise") if world == 1 else "eager launches + NCCL all_gather of output slices per GEMV",
+                              "dependent_chain_us_per_gemv is the same ring without the promise") if world == 1 else ("one CUDA graph per step; every GEMV (lutvq_sharded_matmat_packed, X_READY ring) stores its rows into all peers' gather slots over NVLink "
+                              "inside the kernel; per group of 6 GEMVs one exchange launch on a side stream (parallel graph branch) forwards the finished slices to the peers and confirms the group's all-gather locally (lutvq_shard_wait_mask); the step ends with every slice confirmed; no NCCL on the data path"),
                    "sharding": "none" if world == 1 else f"output channels, {world} x {OUT_F} rows"},
         "us_per_gemv": us_per_gemv,
         "dependent_chain_us_per_gemv": dep_us,
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * OUT_F * 2,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * world * OUT_F * 2,
                 "us_per_gemv": e2e_ms * 1e3 / NBUF, "eager_torch_op_call_us": eager_call_us,
                 "how": "per step: one H2D copy of the step's NBUF activation rows from pinned host memory, the step's C-ABI GEMVs, one D2H copy of the NBUF output rows"},
-        "gpu_launches": args.steps * NBUF,
+        "gpu_launches": args.steps * (NBUF + (NBUF // GROUP if world > 1 else 0)),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "kernel": "lut_gemv_2x8_kernel", "algorithmic_bytes_per_launch": bytes_per_gemv, "peak_source": peak_src,
                      "frac_of_nominal_8TBs": achieved / 8000.0},

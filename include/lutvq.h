@@ -60,6 +60,8 @@ typedef enum { LUTVQ_F16 = 0, LUTVQ_BF16 = 1 } lutvq_dtype_t;
                                      in the stream (rotate through a ring of workspaces).
                                      The LUT build, the gather and the split-k reduction then overlap the previous kernels;
                                      the y stores and the completion of the call stay stream-ordered. */
+#define LUTVQ_FLAG_PUSH_EPILOGUE 8u /* lutvq_sharded_matmat_packed only: push the rows to the peers from the GEMV's own epilogue
+                                     (fused variant) instead of from the exchange kernel behind lutvq_shard_wait */
 #define LUTVQ_XREADY_WS_RING  8
 
 /* lutvq_lut_build lut_mode */
@@ -162,6 +164,9 @@ int    lutvq_sharded_matmat_packed(lutvq_shard_t* s, int slot, size_t row_offset
                                    const void* codebooks, const void* scales, const void* bias, int rows_local,
                                    int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
 int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
+int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);   /* all slots of the mask, one launch */
+/* software pipelining: forward + publish the slots now (non-blocking), lutvq_shard_wait[_mask] on them later only waits */
+int    lutvq_shard_push_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);
 int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
 int    lutvq_shard_destroy(lutvq_shard_t* s);
 

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(CSRC, "liblutvq.so")
 
 LUTVQ_OK, LUTVQ_EINVAL, LUTVQ_EUNSUPPORTED, LUTVQ_ECUDA = 0, -1, -2, -3
 LUTVQ_F16, LUTVQ_BF16 = 0, 1
-FLAG_LUT_FP16, FLAG_NO_PDL, FLAG_X_READY = 1, 2, 4
+FLAG_LUT_FP16, FLAG_NO_PDL, FLAG_X_READY, FLAG_PUSH_EPILOGUE = 1, 2, 4, 8
 LUT_VQPY_FP16, LUT_FP32 = 0, 1
 ACC_F64, ACC_F32 = 0, 1
 
@@ -45,6 +45,8 @@ SIGNATURES = {
     "lutvq_shard_slot_bytes": (SZ, [P]),
     "lutvq_sharded_matmat_packed": (I, [P, I, SZ, P, P, P, P, P, I, I, I, U, P, SZ, P]),
     "lutvq_shard_wait": (I, [P, I, P]),
+    "lutvq_shard_wait_mask": (I, [P, U, P]),
+    "lutvq_shard_push_mask": (I, [P, U, P]),
     "lutvq_shard_error": (I, [P, P]),
     "lutvq_shard_destroy": (I, [P]),
     "lutvq_decode_add_rmsnorm": (I, [P, P, P, P, I, ctypes.c_float, P]),

@@ -28,7 +28,7 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
                     cudaStream_t stream, const GemvPush* push);
 
 constexpr int    kShardMaxRanks  = 8;
-constexpr int    kShardMaxSlots  = 16;
+constexpr int    kShardMaxSlots  = 24;
 constexpr size_t kShardFlagBytes = 4096;       // [slot][rank] uint32 epochs written by peers, then local counters
 constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;   // a wait gives up (and records an error) after 4 s
 constexpr size_t kLocalOff       = 2048;       // local-only area inside the flag page: sent[slot], consumed[slot], error
@@ -40,6 +40,8 @@ struct Shard {
     uint8_t* peer[kShardMaxRanks] = {};         // peer[r] = rank r's buffer as mapped here (peer[rank] == local)
     bool ipc_opened[kShardMaxRanks] = {};
     bool attached = false;
+    // what the last lutvq_sharded_matmat_packed on each slot produced (host state; baked into the exchange launch)
+    struct Pending { unsigned row_off = 0, rows = 0; int fused = 0, pushed = 0; } pending[kShardMaxSlots];
 };
 
 __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
@@ -52,6 +54,7 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 // expected epoch.  Bounded: after `timeout_ns` the kernel records an error word and returns instead of hanging the GPU.
 __global__ void shard_wait_kernel(const unsigned* flags, unsigned* consumed, unsigned* error, int nranks,
                                   unsigned long long timeout_ns) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the next launch may prefetch its weights while we spin
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const unsigned want = *consumed + 1u;
     const int lane = threadIdx.x;
@@ -71,6 +74,128 @@ __global__ void shard_wait_kernel(const unsigned* flags, unsigned* consumed, uns
         *consumed = want;
         if (!all_ok) *error = want;
     }
+}
+
+// Several slots at once: thread t = 8 * slot + rank (blockDim = 8 * kShardMaxSlots); slots outside `mask` are skipped.
+__global__ void shard_wait_mask_kernel(const unsigned* flags, unsigned* consumed, unsigned* error, int nranks, unsigned mask,
+                                       unsigned long long timeout_ns) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int slot = threadIdx.x >> 3, r = threadIdx.x & 7;
+    const bool active = ((mask >> slot) & 1u) != 0 && r < nranks;
+    bool ok = true;
+    unsigned want = 0;
+    if (active) {
+        want = consumed[slot] + 1u;
+        unsigned long long t0, t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while ((int)(ld_acquire_sys(flags + slot * kShardMaxRanks + r) - want) < 0) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > timeout_ns) { ok = false; break; }
+            __nanosleep(64);
+        }
+    }
+    const int all_ok = __syncthreads_and(ok ? 1 : 0);
+    __threadfence_system();
+    if (active && r == 0) consumed[slot] = want;
+    if (threadIdx.x == 0 && !all_ok) *error = 0xFFFFFFFFu;
+}
+
+// ---- exchange kernel: push + wait of up to kShardMaxSlots slots in ONE launch (the default exchange) -------------------
+// grid = nranks CTAs.  CTA c != rank forwards this rank's finished slice of every listed slot into peer c's gather slot
+// (coalesced 128-bit NVLink stores from L2-resident data), fences once, and publishes the epochs to peer c.  CTA
+// c == rank publishes the local epochs and then spins (bounded) until every rank's epoch of every listed slot has arrived.
+// The GEMV launches themselves stay untouched: no fences, no arrival counting on their critical path.  Measured on
+// 2 x B200 (4096x11008 ring): fused epilogue push (LUTVQ_FLAG_PUSH_EPILOGUE) 12.8 us per GEMV -- the per-CTA
+// system-scope fence dominates, it is the same 13.5 us on ONE GPU with no peer at all -- vs this kernel: see DESIGN.md 4.5.
+struct ExchangeList { int n; int slot[kShardMaxSlots]; unsigned row_off[kShardMaxSlots]; unsigned rows[kShardMaxSlots]; };
+struct PeerBases { uint8_t* base[kShardMaxRanks]; };
+
+// grid = (nranks, listed slots).  CTA (c, e): c != rank forwards slice e to peer c and publishes its epoch there;
+// c == rank publishes the local epoch and (do_wait) spins, bounded, until all ranks' epochs of slot e have arrived.
+// Epochs live in device memory (graph replays need no host state): sent[slot] counts pushes, consumed[slot] waits.
+// Launch-queue note: three resident GEMV CTAs hold 61K of an SM's 64K registers, so an exchange CTA only becomes resident
+// when a GEMV CTA exits, and everything queued behind it in the SAME stream waits with it.  Measured (4096x11008 X_READY
+// ring, 2 x B200): exchange launches in the GEMV stream 8.2 us per GEMV; on a side stream (parallel graph branch) 5.5 us.
+// Throughput callers therefore issue the exchange from a side stream; a decode chain is dependent anyway.
+constexpr int kExThreads = 256;
+__global__ void __launch_bounds__(kExThreads) shard_exchange_kernel(uint8_t* local, PeerBases peers, int nranks, int rank, size_t slot_bytes,
+                                                            ExchangeList ex, int do_push, int do_wait, unsigned long long timeout_ns) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");                 // the GEMVs that filled the local slices are complete
+    unsigned* lflags = reinterpret_cast<unsigned*>(local);
+    unsigned* lstate = reinterpret_cast<unsigned*>(local + kLocalOff);
+    unsigned* sent = lstate;
+    unsigned* consumed = lstate + kShardMaxSlots;
+    unsigned* error = lstate + 2 * kShardMaxSlots;
+    unsigned* arrive = lstate + 2 * kShardMaxSlots + 1;                // CTAs of this launch that have finished pushing
+    const int c = blockIdx.x, e = blockIdx.y, slot = ex.slot[e];
+    const unsigned epoch_push = sent[slot] + 1u;                        // read by every CTA before any CTA can arrive below
+    if (do_push) {
+        if (c != rank) {
+            uint8_t* pb = peers.base[c];
+            const size_t off = kShardFlagBytes + slot_bytes * slot + (size_t)ex.row_off[e] * 2;
+            const uint4* src = reinterpret_cast<const uint4*>(local + off);
+            uint4* dst = reinterpret_cast<uint4*>(pb + off);
+            const int n16 = (int)(ex.rows[e] * 2 / 16);
+            #pragma unroll 8
+            for (int i = threadIdx.x; i < n16; i += kExThreads) dst[i] = __ldcg(src + i);      // L2-coherent reads, coalesced NVLink stores
+            const unsigned short* s2 = reinterpret_cast<const unsigned short*>(local + off);
+            unsigned short* d2 = reinterpret_cast<unsigned short*>(pb + off);
+            for (int i = n16 * 8 + threadIdx.x; i < (int)ex.rows[e]; i += kExThreads) d2[i] = __ldcg(s2 + i);
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                unsigned* f = reinterpret_cast<unsigned*>(pb) + (size_t)slot * kShardMaxRanks + rank;
+                asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(f), "r"(epoch_push) : "memory");
+            }
+        } else if (threadIdx.x == 0) {
+            asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(lflags + (size_t)slot * kShardMaxRanks + rank), "r"(epoch_push) : "memory");
+        }
+    }
+    if (do_wait && c == rank) {
+        const unsigned want = consumed[slot] + 1u;
+        bool ok = true;
+        if ((int)threadIdx.x < nranks) {
+            const unsigned* f = lflags + (size_t)slot * kShardMaxRanks + threadIdx.x;
+            unsigned long long t0, t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while ((int)(ld_acquire_sys(f) - want) < 0) {
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t - t0 > timeout_ns) { ok = false; break; }
+                __nanosleep(32);
+            }
+        }
+        const int all_ok = __syncthreads_and(ok ? 1 : 0);
+        __threadfence_system();
+        if (threadIdx.x == 0) {
+            consumed[slot] = want;
+            if (!all_ok) *error = 0xFFFFFFFEu;
+        }
+    }
+    if (do_push && threadIdx.x == 0) {
+        // the last CTA of the launch advances the push epochs (every CTA has read its epoch by the time it arrives here)
+        const unsigned total = gridDim.x * gridDim.y;
+        __threadfence();
+        if (atomicAdd(arrive, 1u) == total - 1) {
+            for (int k = 0; k < ex.n; ++k) sent[ex.slot[k]] += 1u;
+            __threadfence();
+            *arrive = 0u;
+        }
+    }
+}
+
+static int launch_exchange(Shard* s, const ExchangeList& ex, cudaStream_t stream, int do_push = 1, int do_wait = 1) {
+    PeerBases pb;
+    for (int r = 0; r < kShardMaxRanks; ++r) pb.base[r] = r < s->nranks ? s->peer[r] : nullptr;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(s->nranks, ex.n); cfg.blockDim = dim3(kExThreads); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_exchange_kernel, s->local, pb, s->nranks, s->rank, s->slot_bytes, ex, do_push, do_wait, kWaitTimeoutNs));
+    return LUTVQ_OK;
 }
 
 }  // namespace lutvq
@@ -167,6 +292,15 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     LUTVQ_REQUIRE(x && packed && codebooks, "null pointer");
     if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
     const size_t slot_off = kShardFlagBytes + s->slot_bytes * slot + row_offset * 2;
+    void* y_local = s->local + slot_off;
+    s->pending[slot].row_off = (unsigned)row_offset;
+    s->pending[slot].rows = (unsigned)rows_local;
+    s->pending[slot].fused = (flags & LUTVQ_FLAG_PUSH_EPILOGUE) ? 1 : 0;
+    s->pending[slot].pushed = 0;
+    if (!(flags & LUTVQ_FLAG_PUSH_EPILOGUE))
+        // default: the GEMV fills the local slice; lutvq_shard_wait[_mask] forwards it to the peers and waits (one kernel)
+        return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
+                               static_cast<cudaStream_t>(stream), nullptr);
     GemvPush push;
     push.n = 0;
     for (int r = 0; r < s->nranks; ++r) {
@@ -180,7 +314,6 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     push.flag[push.n] = reinterpret_cast<unsigned*>(s->local) + (size_t)slot * kShardMaxRanks + s->rank;
     ++push.n;
     push.sent = reinterpret_cast<unsigned*>(s->local + kLocalOff) + slot;
-    void* y_local = s->local + slot_off;
     return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
                            static_cast<cudaStream_t>(stream), &push);
 }
@@ -189,6 +322,13 @@ int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {
     Shard* s = reinterpret_cast<Shard*>(h);
     LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
     LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range", slot);
+    if (!s->pending[slot].fused) {
+        ExchangeList ex{};
+        ex.n = 1; ex.slot[0] = slot; ex.row_off[0] = s->pending[slot].row_off; ex.rows[0] = s->pending[slot].rows;
+        const int pushed = s->pending[slot].pushed;
+        s->pending[slot].pushed = 0;
+        return launch_exchange(s, ex, static_cast<cudaStream_t>(stream), pushed ? 0 : 1, 1);
+    }
     const unsigned* flags = reinterpret_cast<const unsigned*>(s->local) + (size_t)slot * kShardMaxRanks;
     unsigned* local = reinterpret_cast<unsigned*>(s->local + kLocalOff);
     cudaLaunchConfig_t cfg{};
@@ -200,6 +340,53 @@ int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {
     LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_wait_kernel, flags, local + kShardMaxSlots + slot, local + 2 * kShardMaxSlots,
                                      s->nranks, kWaitTimeoutNs));
     return LUTVQ_OK;
+}
+
+int lutvq_shard_wait_mask(lutvq_shard_t* h, unsigned slot_mask, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(slot_mask != 0 && (slot_mask >> s->n_slots) == 0, "slot mask 0x%x names slots outside 0..%d", slot_mask, s->n_slots - 1);
+    {
+        ExchangeList ex{};
+        int fused = 0, pushed = 0;
+        for (int sl = 0; sl < s->n_slots; ++sl)
+            if ((slot_mask >> sl) & 1u) {
+                fused += s->pending[sl].fused;
+                pushed += s->pending[sl].pushed;
+                s->pending[sl].pushed = 0;
+                ex.slot[ex.n] = sl; ex.row_off[ex.n] = s->pending[sl].row_off; ex.rows[ex.n] = s->pending[sl].rows;
+                ++ex.n;
+            }
+        LUTVQ_REQUIRE(fused == 0 || fused == ex.n, "slot mask 0x%x mixes fused-epilogue and exchange-kernel slots", slot_mask);
+        LUTVQ_REQUIRE(pushed == 0 || pushed == ex.n, "slot mask 0x%x mixes already-pushed and unpushed slots", slot_mask);
+        if (fused == 0) return launch_exchange(s, ex, static_cast<cudaStream_t>(stream), pushed ? 0 : 1, 1);
+    }
+    const unsigned* flags = reinterpret_cast<const unsigned*>(s->local);
+    unsigned* local = reinterpret_cast<unsigned*>(s->local + kLocalOff);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(8 * kShardMaxSlots); cfg.dynamicSmemBytes = 0; cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_wait_mask_kernel, flags, local + kShardMaxSlots, local + 2 * kShardMaxSlots, s->nranks,
+                                     slot_mask, kWaitTimeoutNs));
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_push_mask(lutvq_shard_t* h, unsigned slot_mask, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(slot_mask != 0 && (slot_mask >> s->n_slots) == 0, "slot mask 0x%x names slots outside 0..%d", slot_mask, s->n_slots - 1);
+    ExchangeList ex{};
+    for (int sl = 0; sl < s->n_slots; ++sl)
+        if ((slot_mask >> sl) & 1u) {
+            LUTVQ_REQUIRE(!s->pending[sl].fused && !s->pending[sl].pushed, "slot %d was already pushed", sl);
+            ex.slot[ex.n] = sl; ex.row_off[ex.n] = s->pending[sl].row_off; ex.rows[ex.n] = s->pending[sl].rows;
+            s->pending[sl].pushed = 1;
+            ++ex.n;
+        }
+    return launch_exchange(s, ex, static_cast<cudaStream_t>(stream), 1, 0);
 }
 
 int lutvq_shard_error(lutvq_shard_t* h, unsigned* out) {

@@ -4,8 +4,10 @@ One process per GPU (torch.distributed is the plumbing).  Rank r of P owns rows 
 layer's codes / scales / bias; x and the 8 KiB codebooks are replicated.  Two exchange modes for the step that turns
 the P output slices back into the whole y every rank needs as the next input:
 
-  ``push``  (product) the GEMV kernel itself stores each finished row into every peer's gather slot over NVLink and
-            publishes an epoch; ``ShardGroup.wait`` is one warp spinning on local memory (include/lutvq.h lutvq_shard_*).
+  ``push``  (product) the GEMV fills this rank's slice of a symmetric gather slot; ONE exchange kernel
+            (``ShardGroup.wait`` / ``wait_mask``) forwards the slice to every peer with coalesced NVLink stores, publishes
+            the slot's epoch and spins (bounded) on local memory until all P slices have landed -- no NCCL, graph-capturable.
+            ``fused_epilogue=True`` pushes from the GEMV's own epilogue instead (measured slower: DESIGN.md 4.5).
   ``nccl``  (baseline) local GEMV, then ``dist.all_gather_into_tensor`` of the slices.
 
 The pure-host parts (row partition, handle exchange, slot rotation) are exercised on CPU with gloo in
@@ -115,13 +117,14 @@ class ShardGroup:
             self._views[key] = v
         return v
 
-    def matmat(self, slot: int, row_offset: int, x, packed, codebooks, scales, bias, rows_local: int, *, x_ready: bool = False) -> None:
+    def matmat(self, slot: int, row_offset: int, x, packed, codebooks, scales, bias, rows_local: int, *, x_ready: bool = False,
+               fused_epilogue: bool = False) -> None:
         import torch
         from . import ops, _lib
         dtype = ops.check_use_bfloat16(x)
         in_features = x.size(-1)
         assert x.numel() == in_features, "sharded decode is batch 1"
-        flags = _lib.FLAG_X_READY if x_ready else 0
+        flags = (_lib.FLAG_X_READY if x_ready else 0) | (_lib.FLAG_PUSH_EPILOGUE if fused_epilogue else 0)
         with torch.cuda.device(self.device):
             ws = ops.workspace(self.device, rows_local, in_features, rotate=x_ready)
             self._check(self._lib.lutvq_sharded_matmat_packed(
@@ -133,6 +136,12 @@ class ShardGroup:
         from . import ops
         with torch.cuda.device(self.device):
             self._check(self._lib.lutvq_shard_wait(self._h, slot, ops._stream(self.device)))
+
+    def wait_mask(self, mask: int) -> None:
+        import torch
+        from . import ops
+        with torch.cuda.device(self.device):
+            self._check(self._lib.lutvq_shard_wait_mask(self._h, mask, ops._stream(self.device)))
 
     def error(self) -> int:
         e = ctypes.c_uint(0)

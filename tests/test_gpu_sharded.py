@@ -18,8 +18,9 @@ def cu(a, dev="cuda:0"):
     return torch.from_numpy(np.ascontiguousarray(a)).to(dev)
 
 
+@pytest.mark.parametrize("fused", [False, True])
 @pytest.mark.parametrize("world,I,O", [(1, 512, 256), (2, 1024, 1000), (4, 4096, 4096), (8, 2048, 1024)])
-def test_push_protocol_one_gpu(world, I, O):
+def test_push_protocol_one_gpu(world, I, O, fused):
     from rvv_lut_vq_b200 import ops, synth
     from rvv_lut_vq_b200.sharded import ShardGroup, ShardedQuantizedLinear, shard_rows
     L = synth.make_layer_np(I, O, seed=world * 7 + 1, scales="randn", bias=True)
@@ -41,7 +42,7 @@ def test_push_protocol_one_gpu(world, I, O):
             with torch.cuda.stream(streams[r]):
                 g = groups[r]
                 lay = layers[r]
-                g.matmat(slot, lay.begin, x, lay.packed, lay.codebooks, lay.scales, lay.bias, lay.rows)
+                g.matmat(slot, lay.begin, x, lay.packed, lay.codebooks, lay.scales, lay.bias, lay.rows, fused_epilogue=fused)
         outs = []
         for r in range(world):
             with torch.cuda.stream(streams[r]):
