@@ -110,6 +110,15 @@ int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* c
                                 const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
                                 unsigned flags, void* ws, size_t ws_bytes, void* stream);
 
+/* Grouped launch: n <= 3 linears that read the SAME x (q/k/v, gate/up of a decoder layer; each with its own packed codes,
+ * codebooks, scales, bias, output) in ONE kernel launch, batch 1.  Results are bit-identical to n separate
+ * lutvq_code2x8_matmat_packed calls; a dependent decode chain saves n-1 launch latencies.  ws: at least
+ * lutvq_group_workspace_bytes(n, prob_m, prob_k), zero-filled once, left all-zero. */
+size_t lutvq_group_workspace_bytes(int n, const int* prob_m, int prob_k);
+int lutvq_code2x8_matmat_group_packed(const void* x, int n, const void* const* packed, const void* const* codebooks,
+                                      const void* const* scales, const void* const* bias, void* const* y, const int* prob_m,
+                                      int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
+
 /* W[o][8g+j] = codebook[0][c0(o,g)][j] + codebook[1][c1(o,g)][j]   (one RN add in dtype; bit-exact class)
  * then, if scales != NULL, W[o][:] = round(W[o][:] * scales[o])     (cuda_kernel.cpp:445)
  * W dtype [prob_m][prob_k] row-major. */
@@ -163,6 +172,11 @@ size_t lutvq_shard_slot_bytes(lutvq_shard_t* s);
 int    lutvq_sharded_matmat_packed(lutvq_shard_t* s, int slot, size_t row_offset, const void* x, const void* packed,
                                    const void* codebooks, const void* scales, const void* bias, int rows_local,
                                    int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
+/* grouped form (see lutvq_code2x8_matmat_group_packed): linear i fills rows [row_offsets[i], +rows_local[i]) of slots[i] */
+int    lutvq_sharded_matmat_group_packed(lutvq_shard_t* s, int n, const int* slots, const size_t* row_offsets, const void* x,
+                                         const void* const* packed, const void* const* codebooks, const void* const* scales,
+                                         const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                                         void* ws, size_t ws_bytes, void* stream);
 int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
 int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);   /* all slots of the mask, one launch */
 /* software pipelining: forward + publish the slots now (non-blocking), lutvq_shard_wait[_mask] on them later only waits */

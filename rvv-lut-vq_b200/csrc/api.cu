@@ -12,6 +12,9 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push = nullptr);
 size_t gemv_workspace_bytes(int O, int G);
+size_t gemv_group_workspace_bytes(int n, const int* O);
+int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 size_t gemv_packed_bytes(int O, int G);
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);
 void gemv_set_tuning(int nw, int pf, int pa);
@@ -165,6 +168,26 @@ int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* c
                                 const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
                                 unsigned flags, void* ws, size_t ws_bytes, void* stream) {
     return matmat_rows(x, packed, 1, codebooks, scales, bias, y, batch, prob_m, prob_k, dtype, flags, ws, ws_bytes, stream);
+}
+
+size_t lutvq_group_workspace_bytes(int n, const int* prob_m, int prob_k) {
+    if (n < 1 || n > 3 || !prob_m || prob_k <= 0) return 0;
+    return gemv_group_workspace_bytes(n, prob_m);
+}
+
+int lutvq_code2x8_matmat_group_packed(const void* x, int n, const void* const* packed, const void* const* codebooks,
+                                      const void* const* scales, const void* const* bias, void* const* y, const int* prob_m,
+                                      int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
+    LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
+    LUTVQ_REQUIRE(x && packed && codebooks && y && prob_m, "null pointer");
+    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
+    GemvItem items[3];
+    for (int i = 0; i < n; ++i) {
+        if (int rc = check_2x8_common(packed[i], codebooks[i], prob_m[i], prob_k, dtype)) return rc;
+        LUTVQ_REQUIRE(y[i] != nullptr, "null y pointer of linear %d", i);
+        items[i] = GemvItem{packed[i], codebooks[i], y[i], scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, prob_m[i]};
+    }
+    return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,

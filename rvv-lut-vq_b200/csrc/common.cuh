@@ -45,6 +45,9 @@ struct GemvPush {
     unsigned* sent = nullptr;    // local pushes-completed counter of the slot
 };
 
+// one linear of a grouped GEMV launch (gemv_lut.cu gemv_2x8_launch_group)
+struct GemvItem { const void* codes; const void* codebook; void* y; const void* scales; const void* bias; int O; };
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -62,19 +62,24 @@ constexpr size_t kWsHeaderBytes = 256;        // reserved
 constexpr int kMaxPeers = 8;                  // one NVSwitch domain
 constexpr int kRangeTable = 160;              // workers whose item ranges ride in the kernel parameters (B200: 148)
 
-struct GemvParams {
+constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
+
+// One linear layer of a (possibly grouped) launch.  Every worker (CTA) belongs to exactly one problem.
+struct GemvProblem {
     const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
-    const void* x;            // [I]
     const void* codebook;     // [2][256][8]
     void* y;                  // [O]
     const void* scales;       // [O] or null
     const void* bias;         // [O] or null
     unsigned long long* acc;  // [O_pad] split-k accumulator words, zero between launches
-    int O, O_pad, G, n_k, n_sets;
-    int aligned;              // 1: aligned plan (q, r below), 0: linear plan
-    int q, r;                 // aligned plan: W = q*n_k + r; slices < r have q+1 workers
-    unsigned magic_q, magic_q1;                 // ceil(2^20 / q), ceil(2^20 / (q+1))
-    int base_q, rem_q, base_q1, rem_q1;         // n_sets = base_q*q + rem_q = base_q1*(q+1) + rem_q1
+    int O, n_sets;
+};
+
+struct GemvParams {
+    GemvProblem prob[kMaxProblems];
+    int n_prob;
+    const void* x;            // [I], shared by the problems of a group
+    int G, n_k;
     unsigned flags;
     // ---- output-channel-sharded decode (shard.cu): besides y, every finished row is stored into each peer's gather
     // buffer over NVLink (peer pointers already offset to this rank's row range), and the LAST CTA of the launch to
@@ -85,8 +90,10 @@ struct GemvParams {
     unsigned* push_sent;                        // local: pushes completed on this slot so far (epoch counter)
     unsigned* cta_arrivals;                     // local: workspace header word counting finished CTAs (self-resetting)
     int has_table;                              // 1: the host tabulated every worker's range (W <= kRangeTable)
-    int tab_begin[kRangeTable + 1];             // worker w owns linear items [tab_begin[w], tab_begin[w+1])
+    int tab_begin[kRangeTable];                 // worker w owns linear items [tab_begin[w], tab_end[w]) of ITS problem
+    int tab_end[kRangeTable];
     unsigned short tab_ks[kRangeTable];         // k-slice of item tab_begin[w]
+    unsigned char tab_prob[kRangeTable];        // problem of worker w (ranges are per problem)
     unsigned long long* tl;   // debug timeline [256 CTAs][16] of %globaltimer stamps for this launch, or null
 };
 
@@ -197,34 +204,20 @@ __device__ __forceinline__ void fx_scales(float bound, float& scale, float& inv)
 
 // store one finished output element locally and into every peer's gather buffer (sharded decode)
 template <int DT>
-__device__ __forceinline__ void store_y(const GemvParams& p, int row, typename Dtype<DT>::T v) {
+__device__ __forceinline__ void store_y(const GemvParams& p, const GemvProblem& PB, int row, typename Dtype<DT>::T v) {
     using T = typename Dtype<DT>::T;
-    static_cast<T*>(p.y)[row] = v;
+    static_cast<T*>(PB.y)[row] = v;
     for (int r = 0; r < p.n_push; ++r) static_cast<T*>(p.push_y[r])[row] = v;       // NVLink stores (peer memory)
 }
 
 // One warp tile set = 32 rows x 64 bytes: 4 tiles of 8 rows; per lane 4 x 16 bytes.
 struct CodeRegs { uint32_t w[4][4]; };
 
-// worker -> linear item range [begin, end) over (slice, set) pairs, slice-major.  The aligned plan is division-free:
-// slices < r have q+1 workers, the others q; a slice's n_sets sets are dealt base (+1 for the first rem) per worker.
-__host__ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
-    if (p.aligned) {
-        const int big = p.r * (p.q + 1);
-        const bool hi_part = w >= big;
-        const int nw = hi_part ? p.q : p.q + 1;
-        const int w2 = hi_part ? w - big : w;
-        const int s2 = (int)(((unsigned)w2 * (hi_part ? p.magic_q : p.magic_q1)) >> 20);     // w2 / nw  (exact for w2, nw <= 1024)
-        const int j = w2 - s2 * nw;
-        const int s = (hi_part ? p.r : 0) + s2;
-        const int base = hi_part ? p.base_q : p.base_q1, rem = hi_part ? p.rem_q : p.rem_q1;  // n_sets = base*nw + rem
-        begin = s * p.n_sets + j * base + (j < rem ? j : rem);
-        end   = begin + base + (j < rem ? 1 : 0);
-    } else {
-        const long long T = (long long)p.n_k * p.n_sets;
-        begin = (int)((T * w) / W);
-        end   = (int)((T * (w + 1)) / W);
-    }
+// Fallback when the grid is larger than the tabulated ranges (never on a 148-SM B200): the linear plan, one problem.
+__device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
+    const long long T = (long long)p.n_k * p.prob[0].n_sets;
+    begin = (int)((T * w) / W);
+    end   = (int)((T * (w + 1)) / W);
 }
 
 template <int DT, bool PACKED, int NW, int PF, int PA, int MINB>
@@ -232,6 +225,7 @@ __global__ void __launch_bounds__(NW * 32, MINB)
 lut_gemv_2x8_kernel(const GemvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t lut_base = smem_u32(smem_raw);
+    const GemvProblem& PB = p.prob[p.n_prob > 1 ? (int)p.tab_prob[blockIdx.x] : 0];       // indexed constant-bank loads
 
     TL_STAMP(0);
 #if LUTVQ_DBG
@@ -244,10 +238,10 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int W = gridDim.x;
     int begin, end;
-    if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_begin[blockIdx.x + 1]; }     // two constant-bank loads
+    if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_end[blockIdx.x]; }          // two constant-bank loads
     else worker_range(p, blockIdx.x, W, begin, end);
     const size_t row_bytes = (size_t)p.G * 2;
-    const int last_row = p.O - 1;
+    const int last_row = PB.O - 1;
 
     // ---------------- streaming-side lane constants ----------------
     // Reference layout: no predicated loads.  Rows past the end are clamped to the last row (result discarded)
@@ -256,7 +250,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     const int e = stream_first_half(lane);
     auto load_set = [&](CodeRegs& r, int ks, int set) {
         if (PACKED) {
-            const uint4* base = reinterpret_cast<const uint4*>(p.codes) + (((size_t)ks * p.n_sets + set) * 4) * 32 + lane;
+            const uint4* base = reinterpret_cast<const uint4*>(PB.codes) + (((size_t)ks * PB.n_sets + set) * 4) * 32 + lane;
             #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const uint4 v = ldg_stream_u128(base + t * 32);
@@ -265,7 +259,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         } else {
             const int slice_byte0 = ks * kSliceTables;
             const bool chunk_valid = (size_t)(slice_byte0 + 16 * stream_chunk(lane)) < row_bytes;
-            const uint8_t* lane_base = p.codes + slice_byte0 + (chunk_valid ? 16 * stream_chunk(lane) : 0);
+            const uint8_t* lane_base = PB.codes + slice_byte0 + (chunk_valid ? 16 * stream_chunk(lane) : 0);
             const int rbase = set * kSetRows + stream_row_in_tile(lane);
             #pragma unroll
             for (int t = 0; t < 4; ++t) {
@@ -285,9 +279,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     auto wrap = [](int v, int n) { while (v >= n) v -= n; return v; };
     // first segment of this worker's range: slice ks, sets [lo, hi)
     int pos = begin;
-    int ks = p.has_table ? (int)p.tab_ks[blockIdx.x] : (begin < end) ? (int)((unsigned)begin / (unsigned)p.n_sets) : 0;
-    int lo = begin - ks * p.n_sets;
-    int hi = min(p.n_sets, lo + (end - begin));
+    int ks = p.has_table ? (int)p.tab_ks[blockIdx.x] : (begin < end) ? (int)((unsigned)begin / (unsigned)PB.n_sets) : 0;
+    int lo = begin - ks * PB.n_sets;
+    int hi = min(PB.n_sets, lo + (end - begin));
 
     int seg_rot = rot_of(ks, hi - lo);
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
@@ -303,7 +297,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     if (PACKED) {
         // the worker's whole share is ONE contiguous range of the packed image (linear item index * 2048 B)
         if (lane == 0) {
-            const uint8_t* base = p.codes + (size_t)begin * 2048;
+            const uint8_t* base = PB.codes + (size_t)begin * 2048;
             const int n = end - begin;
             for (int c = warp * 4 + PF * NW; c < n; c += NW * 4)
                 l2_prefetch_bulk(base + (size_t)c * 2048, (uint32_t)min(4, n - c) * 2048u);
@@ -311,11 +305,11 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     } else {
         int ppos = begin;
         while (ppos < end) {
-            const int s = ppos / p.n_sets, l = ppos - s * p.n_sets, h = min(p.n_sets, l + (end - ppos));
+            const int s = ppos / PB.n_sets, l = ppos - s * PB.n_sets, h = min(PB.n_sets, l + (end - ppos));
             const size_t off = (size_t)s * kSliceTables;
-            const int r1 = min(h * kSetRows, p.O);
+            const int r1 = min(h * kSetRows, PB.O);
             for (int r = l * kSetRows + threadIdx.x; r < r1; r += NW * 32)
-                l2_prefetch_line(p.codes + (size_t)r * row_bytes + off);
+                l2_prefetch_line(PB.codes + (size_t)r * row_bytes + off);
             ppos += h - l;
         }
     }
@@ -324,9 +318,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         const int nl = (hi - lo + 1) / 2;                             // 128-byte lines
         if ((int)threadIdx.x < nl) {
             const size_t off = (size_t)lo * 64 + (size_t)threadIdx.x * 128;
-            if (off < (size_t)p.O * 2) {
-                if (p.scales) l2_prefetch_line(static_cast<const uint8_t*>(p.scales) + off);
-                if (p.bias)   l2_prefetch_line(static_cast<const uint8_t*>(p.bias) + off);
+            if (off < (size_t)PB.O * 2) {
+                if (PB.scales) l2_prefetch_line(static_cast<const uint8_t*>(PB.scales) + off);
+                if (PB.bias)   l2_prefetch_line(static_cast<const uint8_t*>(PB.bias) + off);
             }
         }
     }
@@ -339,7 +333,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     constexpr int MB_PER_WARP = 16 / NW;                                   // 16 idx blocks of 16 per codebook
     uint32_t afrag[MB_PER_WARP][2][2];
     {
-        const uint32_t* cb32 = static_cast<const uint32_t*>(p.codebook);  // [2][256][4] words (2 values each)
+        const uint32_t* cb32 = static_cast<const uint32_t*>(PB.codebook);  // [2][256][4] words (2 values each)
         // A fragments for this warp's idx blocks: rows 16m + r and 16m + r + 8, k = 2q, 2q+1
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi) {
@@ -413,13 +407,13 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         if ((unsigned)(old & 255ull) == last_count) {              // this lane delivered the last partial of `row`
             if (!waited) { pdl_wait(); waited = true; }            // y stores are ordered behind the previous kernel
             const float total = fx_total<DT>(old + fx_contribution<DT>(keep));
-            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(p.acc + row), "l"(0ull) : "memory");   // hand the word back
-            if (row < p.O) {
+            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(PB.acc + row), "l"(0ull) : "memory");   // hand the word back
+            if (row < PB.O) {
                 T rr = D::from_f(total);                                               // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
                 // scale / bias were pulled into L2 by the prologue; only the last arriver (1 in n_k) pays this round trip
-                if (p.scales) rr = D::mul(rr, static_cast<const T*>(p.scales)[row]);   // flat_output *= scales             (cuda_kernel.cpp:101)
-                if (p.bias)   rr = D::add(rr, static_cast<const T*>(p.bias)[row]);     // flat_output += bias               (cuda_kernel.cpp:103)
-                store_y<DT>(p, row, rr);
+                if (PB.scales) rr = D::mul(rr, static_cast<const T*>(PB.scales)[row]);   // flat_output *= scales             (cuda_kernel.cpp:101)
+                if (PB.bias)   rr = D::add(rr, static_cast<const T*>(PB.bias)[row]);     // flat_output += bias               (cuda_kernel.cpp:103)
+                store_y<DT>(p, PB, row, rr);
             }
         }
     };
@@ -538,11 +532,11 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                         const float keep = (float)(int)(keep_u - kFxMagic64) * fx_inv;     // 64 lookups' magic offsets, mod 2^32
                         if (p.n_k == 1) {
                             if (!waited) { pdl_wait(); waited = true; }
-                            if (row < p.O) {
+                            if (row < PB.O) {
                                 T rr = D::from_f(keep);
-                                if (p.scales) rr = D::mul(rr, static_cast<const T*>(p.scales)[row]);
-                                if (p.bias)   rr = D::add(rr, static_cast<const T*>(p.bias)[row]);
-                                store_y<DT>(p, row, rr);
+                                if (PB.scales) rr = D::mul(rr, static_cast<const T*>(PB.scales)[row]);
+                                if (PB.bias)   rr = D::add(rr, static_cast<const T*>(PB.bias)[row]);
+                                store_y<DT>(p, PB, row, rr);
                             }
                         } else {
                             // finish the atomic this slot issued PA sets ago (its L2 round trip, ~1.3 us under load, has
@@ -550,10 +544,10 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                             if (pend_valid[sa]) finish_row(pend_old[sa], pend_keep[sa], pend_row[sa]);
                             pend_row[sa] = row; pend_valid[sa] = true; pend_keep[sa] = keep;
 #if LUTVQ_DBG
-                            if (p.flags & 0x400u) { pend_old[sa] = 0; if (row < p.O) static_cast<T*>(p.y)[row] = D::from_f(keep); }   // DEBUG: no atomics
+                            if (p.flags & 0x400u) { pend_old[sa] = 0; if (row < PB.O) static_cast<T*>(PB.y)[row] = D::from_f(keep); }   // DEBUG: no atomics
                             else
 #endif
-                            pend_old[sa] = atom_add_u64(p.acc + row, fx_contribution<DT>(keep));
+                            pend_old[sa] = atom_add_u64(PB.acc + row, fx_contribution<DT>(keep));
                         }
                         v += NW;     if (v >= n_seg) v -= n_seg;
                         vnext += NW; if (vnext >= n_seg) vnext -= n_seg;
@@ -563,9 +557,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         }
         pos += hi - lo;
         if (pos < end) {                                           // next segment (linear plan only)
-            ks = pos / p.n_sets;
-            lo = pos - ks * p.n_sets;
-            hi = min(p.n_sets, lo + (end - pos));
+            ks = pos / PB.n_sets;
+            lo = pos - ks * PB.n_sets;
+            hi = min(PB.n_sets, lo + (end - pos));
             seg_rot = rot_of(ks, hi - lo);
             #pragma unroll
             for (int i = 0; i < PF; ++i)
@@ -729,29 +723,85 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
     return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d pa=%d", t.nw, t.pf, t.pa);
 }
 
-// One GEMV: y = epilogue(W(codes) . x).  Validation is done by the caller (api.cu).
-int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
-                    const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
-                    cudaStream_t stream, const GemvPush* push) {
+// worker w of a problem planned as `pl` -> its item range [begin, end) over (slice, set) pairs, slice-major.
+// Aligned plan: slices < r have q+1 workers, the others q; a slice's n_sets sets are dealt base (+1 for the first rem).
+static void host_worker_range(const GemvPlan& pl, int w, int& begin, int& end) {
+    if (pl.aligned) {
+        const int big = pl.r * (pl.q + 1);
+        const bool hi_part = w >= big;
+        const int nw = hi_part ? pl.q : pl.q + 1;
+        const int w2 = hi_part ? w - big : w;
+        const int s2 = w2 / nw, j = w2 - s2 * nw;
+        const int s = (hi_part ? pl.r : 0) + s2;
+        const int base = pl.n_sets / nw, rem = pl.n_sets % nw;
+        begin = s * pl.n_sets + j * base + (j < rem ? j : rem);
+        end   = begin + base + (j < rem ? 1 : 0);
+    } else {
+        const long long T = (long long)pl.n_k * pl.n_sets;
+        begin = (int)((T * w) / pl.W);
+        end   = (int)((T * (w + 1)) / pl.W);
+    }
+}
+
+size_t gemv_group_workspace_bytes(int n, const int* O) {
+    size_t b = kWsHeaderBytes;
+    for (int i = 0; i < n; ++i) b += (size_t)ceil_div(O[i], kSetRows) * kSetRows * sizeof(unsigned long long);
+    return b;
+}
+
+// n linears that share x (and prob_k) in ONE launch: y_i = epilogue_i(W_i(codes_i) . x).  The workers (one CTA per SM)
+// are dealt to the problems in proportion to their rows; each problem is then planned exactly like a single GEMV on
+// its share of the SMs.  Validation is done by the caller (api.cu / shard.cu).
+int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
+    LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
+    LUTVQ_REQUIRE(n == 1 || di.sm_count <= kRangeTable, "grouped launches need the tabulated plan (<= %d SMs)", kRangeTable);
+    LUTVQ_REQUIRE(n == 1 || push == nullptr, "the fused push epilogue takes one linear per launch");
     const int G = I / 8;
-    const GemvPlan pl = plan_gemv(O, G, di.sm_count);
-    const size_t need = gemv_workspace_bytes(O, G);
+    int Os[kMaxProblems];
+    long long sets_total = 0;
+    for (int i = 0; i < n; ++i) { Os[i] = items[i].O; sets_total += ceil_div(items[i].O, kSetRows); }
+    const size_t need = gemv_group_workspace_bytes(n, Os);
     LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= need, "workspace too small: need %zu bytes, got %zu", need, ws_bytes);
     LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
-    if (pl.n_k > 255) return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds 255 (prob_k <= 65280)", I, pl.n_k);
     GemvParams p;
-    p.codes = static_cast<const uint8_t*>(codes);
-    p.x = x; p.codebook = codebook; p.y = y; p.scales = scales; p.bias = bias;
-    p.acc = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(ws) + kWsHeaderBytes);
-    p.O = O; p.O_pad = pl.n_sets * kSetRows; p.G = G; p.n_k = pl.n_k; p.n_sets = pl.n_sets;
-    p.aligned = pl.aligned; p.q = pl.q; p.r = pl.r;
-    p.magic_q = p.magic_q1 = 0; p.base_q = p.rem_q = p.base_q1 = p.rem_q1 = 0;
-    if (pl.aligned) {
-        p.magic_q = ((1u << 20) + pl.q - 1) / pl.q;   p.magic_q1 = ((1u << 20) + pl.q) / (pl.q + 1);
-        p.base_q = pl.n_sets / pl.q;                  p.rem_q = pl.n_sets % pl.q;
-        p.base_q1 = pl.n_sets / (pl.q + 1);           p.rem_q1 = pl.n_sets % (pl.q + 1);
+    p.n_prob = n; p.x = x; p.G = G;
+    p.has_table = 0;
+    int W_total = 0, left = di.sm_count;
+    uint8_t* accp = static_cast<uint8_t*>(ws) + kWsHeaderBytes;
+    for (int i = 0; i < kMaxProblems; ++i) p.prob[i] = GemvProblem{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+    for (int i = 0; i < n; ++i) {
+        // SM share of problem i: proportional to its row sets, at least one, the last problem takes the remainder
+        const int n_sets_i = ceil_div(items[i].O, kSetRows);
+        int share = (i == n - 1) ? left : (int)((long long)di.sm_count * n_sets_i / sets_total);
+        if (share < 1) share = 1;
+        if (share > left - (n - 1 - i)) share = left - (n - 1 - i);
+        left -= share;
+        GemvPlan pl = plan_gemv(items[i].O, G, share);
+        if (pl.n_k > 255) return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds 255 (prob_k <= 65280)", I, pl.n_k);
+        p.n_k = pl.n_k;
+        GemvProblem& pb = p.prob[i];
+        pb.codes = static_cast<const uint8_t*>(items[i].codes); pb.codebook = items[i].codebook; pb.y = items[i].y;
+        pb.scales = items[i].scales; pb.bias = items[i].bias;
+        pb.acc = reinterpret_cast<unsigned long long*>(accp);
+        pb.O = items[i].O; pb.n_sets = pl.n_sets;
+        accp += (size_t)pl.n_sets * kSetRows * sizeof(unsigned long long);
+        if (W_total + pl.W <= kRangeTable LUTVQ_DBG_AND(!(flags & 0x1000u))) {
+            for (int w = 0; w < pl.W; ++w) {
+                int b, e;
+                host_worker_range(pl, w, b, e);
+                p.tab_begin[W_total + w] = b; p.tab_end[W_total + w] = e;
+                p.tab_ks[W_total + w] = (unsigned short)(b < e ? b / pl.n_sets : 0);
+                p.tab_prob[W_total + w] = (unsigned char)i;
+            }
+            p.has_table = 1;
+        } else {
+            LUTVQ_REQUIRE(n == 1, "grouped launches need the tabulated plan");
+            p.has_table = 0;                                        // device fallback: linear plan over W CTAs
+        }
+        W_total += pl.W;
     }
     p.n_push = 0; p.push_sent = nullptr;
     p.cta_arrivals = reinterpret_cast<unsigned*>(ws);                // first word of the reserved workspace header
@@ -761,23 +811,21 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
         p.n_push = push->n; p.push_sent = push->sent;
         for (int r = 0; r < push->n; ++r) { p.push_y[r] = push->y[r]; p.push_flag[r] = push->flag[r]; }
     }
-    p.has_table = 0;
-    if (pl.W <= kRangeTable LUTVQ_DBG_AND(!(flags & 0x1000u))) {
-        for (int w = 0; w < pl.W; ++w) {
-            int b, e;
-            worker_range(p, w, pl.W, b, e);
-            p.tab_begin[w] = b; p.tab_begin[w + 1] = e;                 // ranges are contiguous: end(w) == begin(w+1)
-            p.tab_ks[w] = (unsigned short)(b < e ? b / pl.n_sets : 0);
-        }
-        p.has_table = 1;
-    }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
     p.tl = g_timeline ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
     const size_t smem = kSliceBytes;
-    if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, pl.W, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, pl.W, smem, stream, pdl);
-    if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, pl.W, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, pl.W, smem, stream, pdl);
+    if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, W_total, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, W_total, smem, stream, pdl);
+    if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, W_total, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, W_total, smem, stream, pdl);
     return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+}
+
+// One GEMV: y = epilogue(W(codes) . x).
+int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
+                    const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
+                    cudaStream_t stream, const GemvPush* push) {
+    const GemvItem it{codes, codebook, y, scales, bias, O};
+    return gemv_2x8_launch_group(1, &it, packed, x, I, dtype, flags, ws, ws_bytes, stream, push);
 }
 
 void gemv_set_tuning(int nw, int pf, int pa) {

@@ -27,6 +27,9 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push);
 
+int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
+
 constexpr int    kShardMaxRanks  = 8;
 constexpr int    kShardMaxSlots  = 24;
 constexpr size_t kShardFlagBytes = 4096;       // [slot][rank] uint32 epochs written by peers, then local counters
@@ -316,6 +319,34 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     push.sent = reinterpret_cast<unsigned*>(s->local + kLocalOff) + slot;
     return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
                            static_cast<cudaStream_t>(stream), &push);
+}
+
+int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* x,
+                                      const void* const* packed, const void* const* codebooks, const void* const* scales,
+                                      const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                                      void* ws, size_t ws_bytes, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
+    LUTVQ_REQUIRE(slots && row_offsets && x && packed && codebooks && rows_local, "null pointer");
+    LUTVQ_REQUIRE(prob_k > 0 && prob_k % 64 == 0, "bad prob_k=%d", prob_k);
+    LUTVQ_REQUIRE(!(flags & LUTVQ_FLAG_PUSH_EPILOGUE), "the fused push epilogue takes one linear per launch");
+    if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+    GemvItem items[3];
+    for (int i = 0; i < n; ++i) {
+        const int slot = slots[i];
+        LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
+        for (int j = 0; j < i; ++j) LUTVQ_REQUIRE(slots[j] != slot, "the linears of a group need distinct slots");
+        LUTVQ_REQUIRE(rows_local[i] > 0 && (row_offsets[i] + (size_t)rows_local[i]) * 2 <= s->slot_bytes, "rows of linear %d do not fit a slot", i);
+        LUTVQ_REQUIRE(packed[i] && codebooks[i], "null pointer in linear %d", i);
+        void* y_local = s->local + kShardFlagBytes + s->slot_bytes * slot + row_offsets[i] * 2;
+        items[i] = GemvItem{packed[i], codebooks[i], y_local, scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, rows_local[i]};
+        s->pending[slot].row_off = (unsigned)row_offsets[i];
+        s->pending[slot].rows = (unsigned)rows_local[i];
+        s->pending[slot].fused = 0;
+        s->pending[slot].pushed = 0;
+    }
+    return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {

@@ -70,9 +70,9 @@ class _Linear:
 
 class Decoder:
     def __init__(self, cfg: DecoderConfig, device, world: int = 1, rank: int = 0, group: Optional[ShardGroup] = None,
-                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False):
+                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True):
         self.cfg, self.dev, self.world, self.rank, self.group, self.max_seq = cfg, torch.device(device), world, rank, group, max_seq
-        self.exchange, self.pg = exchange, pg
+        self.exchange, self.pg, self.grouped = exchange, pg, grouped
         if world > 1 and exchange == "push":
             assert group is not None
         self.lib = _lib.lib()
@@ -104,7 +104,7 @@ class Decoder:
         self.pos = torch.zeros(1, dtype=torch.int32, device=dev)
         # workspace ring: every GEMV takes the next region (include/lutvq.h X_READY contract)
         max_rows = max(l.rows for l in self.layers[0].values() if isinstance(l, _Linear))
-        self.ws_need = (int(self.lib.lutvq_workspace_bytes_ex(max_rows, max(i for i, _ in shapes.values()), 6)) + 255) // 256 * 256
+        self.ws_need = (3 * int(self.lib.lutvq_workspace_bytes_ex(max_rows, max(i for i, _ in shapes.values()), 6)) + 255) // 256 * 256   # a group of <= 3
         self.ws = torch.zeros(ops.XREADY_WS_RING * self.ws_need, dtype=torch.uint8, device=dev)
         self._ws_i = 0
         if world > 1 and exchange == "nccl":
@@ -158,19 +158,45 @@ class Decoder:
             self.launches_per_token += 1
 
     def _group_gemv(self, L, names, x):
-        """the linears that share an input; all launched before any wait.  None of them may use LUTVQ_FLAG_X_READY: under
-        programmatic dependent launch the kernel after an X_READY kernel can start before the kernel that PRODUCED x
-        (two launches back) has finished, so the promise only holds for inputs that were complete before the whole
-        overlapped run of launches began (include/lutvq.h)."""
-        outs, slots = [], []
-        for j, n in enumerate(names):
-            slot = self.group.next_slot() if (self.world > 1 and self.exchange == "push") else None
-            o, s = self._gemv(L[n], x, n, x_ready=False, slot=slot)
-            outs.append(o)
-            slots.append(s)
-        for s in slots:
-            self._wait(s)
-        return outs
+        """the linears that share an input go out as ONE grouped launch (lutvq_*_matmat_group_packed) and, when sharded,
+        ONE exchange launch.  None of this may use LUTVQ_FLAG_X_READY: under programmatic dependent launch the kernel
+        after an X_READY kernel can start before the kernel that PRODUCED x (two launches back) has finished, so the
+        promise only holds for inputs that were complete before the whole overlapped run began (include/lutvq.h)."""
+        n = len(names)
+        lins = [L[k] for k in names]
+        if self.world > 1 and self.exchange == "nccl" or not self.grouped:
+            outs, slots = [], []
+            for k in names:
+                slot = self.group.next_slot() if (self.world > 1 and self.exchange == "push") else None
+                o, s = self._gemv(L[k], x, k, x_ready=False, slot=slot)
+                outs.append(o)
+                slots.append(s)
+            for s in slots:
+                self._wait(s)
+            return outs
+        arr = lambda ts: (ctypes.c_void_p * n)(*[None if t is None else t.data_ptr() for t in ts])
+        P = lambda t: ctypes.c_void_p(t.data_ptr())
+        self.launches_per_token += 1
+        if self.world == 1:
+            outs = [self.bufs[k] for k in names]
+            pm = (ctypes.c_int * n)(*[l.out_f for l in lins])
+            _lib.check(self.lib.lutvq_code2x8_matmat_group_packed(P(x), n, arr([l.packed for l in lins]), arr([l.codebooks for l in lins]),
+                                                                  arr([l.scales for l in lins]), arr([None] * n), arr(outs), pm, lins[0].in_f, 0, 0,
+                                                                  self._next_ws(), self.ws_need, self._st()))
+            return outs
+        slots = [self.group.next_slot() for _ in names]
+        sl = (ctypes.c_int * n)(*slots)
+        ro = (ctypes.c_size_t * n)(*[l.begin for l in lins])
+        rl = (ctypes.c_int * n)(*[l.rows for l in lins])
+        _lib.check(self.lib.lutvq_sharded_matmat_group_packed(self.group._h, n, sl, ro, P(x), arr([l.packed for l in lins]),
+                                                              arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n), rl,
+                                                              lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st()))
+        mask = 0
+        for s_ in slots:
+            mask |= 1 << s_
+        _lib.check(self.lib.lutvq_shard_wait_mask(self.group._h, mask, self._st()))
+        self.launches_per_token += 1
+        return [self.group.slot_tensor(s_, l.out_f, torch.float16) for s_, l in zip(slots, lins)]
 
     def step(self):
         """one token: reads self.token / self.pos, writes self.logits and the next token"""

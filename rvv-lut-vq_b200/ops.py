@@ -6,7 +6,7 @@ every op is one or more launches of our own sm_100a kernels through the C-ABI.  
 from __future__ import annotations
 
 import ctypes
-from typing import Dict, Optional, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import torch
 
@@ -222,3 +222,32 @@ def vq_dequantize(codebook: torch.Tensor, codeword: torch.Tensor, M: int) -> tor
         check(lib().lutvq_vq_dequantize(_ptr(codebook.contiguous()), _ptr(codeword.contiguous()), _ptr(W), d_out, M, N,
                                         K, d, int(shared), _stream(dev)))
     return W
+
+
+def code2x8_matmat_group_packed(input: torch.Tensor, packed: List[torch.Tensor], out_features: List[int], codebooks: List[torch.Tensor],
+                                scales: List[Optional[torch.Tensor]], bias: Optional[List[Optional[torch.Tensor]]] = None,
+                                out: Optional[List[torch.Tensor]] = None) -> List[torch.Tensor]:
+    """n <= 3 linears that read the same input row (q/k/v, gate/up) in ONE launch (lutvq_code2x8_matmat_group_packed);
+    bit-identical to n code2x8_matmat_packed calls."""
+    dtype = check_use_bfloat16(input)
+    n = len(packed)
+    dev = _require_cuda(input, *packed, *codebooks)
+    in_features = input.size(-1)
+    assert input.numel() == in_features, "grouped launches are batch 1"
+    x = input.reshape(-1).contiguous()
+    ys = out if out is not None else [torch.empty(o, dtype=input.dtype, device=dev) for o in out_features]
+    sc = [_flat_scales(s) for s in scales]
+    bi = [None] * n if bias is None else [None if b is None else b.contiguous() for b in bias]
+    cbs = [c.contiguous() for c in codebooks]
+    arr = lambda ts: (ctypes.c_void_p * n)(*[None if t is None else t.data_ptr() for t in ts])
+    pm = (ctypes.c_int * n)(*out_features)
+    need = int(lib().lutvq_group_workspace_bytes(n, pm, in_features))
+    key = ("group", dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1 << 18), dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code2x8_matmat_group_packed(_ptr(x), n, arr(packed), arr(cbs), arr(sc), arr(bi), arr(ys), pm, in_features, dtype, 0,
+                                                      _ptr(ws), ws.numel(), _stream(dev)))
+    return ys

@@ -389,3 +389,21 @@ def test_quantized_linear_module(pkg, orc):
     for b in range(4):
         want = orc.c_aqlm_gemv_f64(L["x"][b], L["codes"], L["codebooks"]) * L["scales"].reshape(-1).astype(np.float64) + L["bias"]
         assert rel_err(y[b].float().cpu().numpy(), want) <= TOL_GEMV
+
+
+@pytest.mark.parametrize("I,Os", [(4096, [4096, 4096, 4096]), (4096, [11008, 11008]), (8192, [8192, 1024, 1024]), (1024, [96, 1000]), (11008, [4096])])
+def test_grouped_launch_is_bit_identical(pkg, ops, I, Os):
+    """lutvq_code2x8_matmat_group_packed: n linears sharing x in one launch == n separate launches, bit for bit"""
+    from rvv_lut_vq_b200 import synth
+    Ls = [synth.make_layer_np(I, O, seed=100 + i, scales="randn", bias=(i % 2 == 0)) for i, O in enumerate(Os)]
+    x = cu(Ls[0]["x"])
+    packed = [ops.code2x8_prepack(cu(L["codes"])) for L in Ls]
+    cbs = [cu(L["codebooks"]) for L in Ls]
+    scs = [cu(L["scales"]) for L in Ls]
+    bis = [None if L["bias"] is None else cu(L["bias"]) for L in Ls]
+    want = [ops.code2x8_matmat_packed(x, packed[i], Os[i], cbs[i], scs[i], bis[i])[0] for i in range(len(Os))]
+    for rep in range(3):                                                   # the workspace must come back all-zero
+        got = ops.code2x8_matmat_group_packed(x, packed, Os, cbs, scs, bis)
+        torch.cuda.synchronize()
+        for i in range(len(Os)):
+            assert torch.equal(got[i].view(torch.int16), want[i].view(torch.int16)), f"linear {i} of the group differs (rep {rep})"
