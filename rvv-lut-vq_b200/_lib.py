@@ -35,6 +35,9 @@ SIGNATURES = {
     "lutvq_code2x8_matmat_group_packed": (I, [P, I, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_code2x8_dequant": (I, [P, P, P, P, I, I, I, P]),
     "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
+    "lutvq_codeKx8_workspace_bytes": (SZ, [I, I, I]),
+    "lutvq_codeKx8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, I, P, SZ, P]),
+    "lutvq_codeKx8_dequant": (I, [P, P, P, P, I, I, I, I, P]),
     "lutvq_lut_build": (I, [P, P, P, I, I, I, I, I, I, P]),
     "lutvq_lut_gemv": (I, [P, P, P, I, I, I, I, I, I, P]),
     "lutvq_vq_dequantize": (I, [P, P, P, I, I, I, I, I, I, P]),

@@ -251,3 +251,33 @@ def code2x8_matmat_group_packed(input: torch.Tensor, packed: List[torch.Tensor],
         check(lib().lutvq_code2x8_matmat_group_packed(_ptr(x), n, arr(packed), arr(cbs), arr(sc), arr(bi), arr(ys), pm, in_features, dtype, 0,
                                                       _ptr(ws), ws.numel(), _stream(dev)))
     return ys
+
+
+def codeKx8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """codeKx8_matmat / code1x8_matmat (cuda_kernel.cpp:521-684): any number of 256-entry codebooks, groups of 8, fp16."""
+    dtype = check_use_bfloat16(input)
+    dev = _require_cuda(input, codes, codebooks, scales, bias)
+    N = codes.size(-1)
+    in_features, out_features = input.size(-1), codes.size(0)
+    flat = input.reshape(-1, in_features).contiguous()
+    y = torch.empty((flat.size(0), out_features), dtype=input.dtype, device=dev)
+    need = int(lib().lutvq_codeKx8_workspace_bytes(out_features, in_features, N))
+    ws = torch.empty(need, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_codeKx8_matmat(_ptr(flat), _ptr(codes.contiguous()), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)),
+                                         _ptr(None if bias is None else bias.contiguous()), _ptr(y), flat.size(0), out_features, in_features, N,
+                                         dtype, _ptr(ws), need, _stream(dev)))
+    return y.reshape(tuple(input.shape[:-1]) + (out_features,))
+
+
+def codeKx8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:
+    """CodeKx8Dequant (cuda_kernel.cu:392-468): W = ((cb0 + cb1) + cb2) + ... in fp16, then * scales."""
+    dtype = check_use_bfloat16(codebooks)
+    dev = _require_cuda(codes, codebooks, scales)
+    O, G, N = codes.shape
+    W = torch.empty((O, G * 8), dtype=codebooks.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_codeKx8_dequant(_ptr(codes.contiguous()), _ptr(W), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)), O, G * 8, N,
+                                          dtype, _stream(dev)))
+    return W

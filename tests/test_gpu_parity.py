@@ -407,3 +407,42 @@ def test_grouped_launch_is_bit_identical(pkg, ops, I, Os):
         torch.cuda.synchronize()
         for i in range(len(Os)):
             assert torch.equal(got[i].view(torch.int16), want[i].view(torch.int16)), f"linear {i} of the group differs (rep {rep})"
+
+
+# ------------------------------------------------------------------ Kx8 generalisation (N = 1, 2, 4 codebooks)
+@pytest.mark.parametrize("name", ["aqlm_1x8_i128_o32", "aqlm_4x8_i128_o48", "aqlm_2x8_i256_o96"])
+def test_codeKx8_vs_golden(pkg, ops, orc, golden_dir, name):
+    """lutvq_codeKx8_matmat / _dequant against the fixtures generated from the reference's own numba_gemm_lut and
+    _dequantize_weight (oracle/gen_golden.py), and bit-exact against the sequential-fp16-add restatement of CodeKx8Dequant."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    I, O, N, B, _, wb = [int(v) for v in g["cfg"]]
+    x16 = g["x"].astype(np.float16)
+    cb16 = g["codebooks"].astype(np.float16)
+    sc16 = g["scales"].astype(np.float16)
+    bias = g["bias"].astype(np.float16) if wb else None
+    y = ops.codeKx8_matmat(cu(x16), cu(g["codes"]), cu(cb16), cu(sc16), None if bias is None else cu(bias))
+    assert y.shape == (B, O)
+    # float64 evaluation of the same fp16 operands: north-star tolerance 1e-3 of the layer's range
+    Wd = np.zeros((O, I), dtype=np.float64)
+    for n in range(N):
+        Wd += cb16[n, g["idx"][:, :, n].astype(np.int64), 0, :].astype(np.float64).reshape(O, I)
+    want = (x16.astype(np.float64) @ Wd.T) * sc16.reshape(-1).astype(np.float64) + (0 if bias is None else bias.astype(np.float64))
+    got = y.float().cpu().numpy().astype(np.float64)
+    assert np.abs(got - want).max() / np.abs(want).max() <= TOL_GEMV
+    # the reference's fp32 numba result (fp32 operands) agrees to fp16-operand precision
+    assert np.abs(got - g["y_numba"]).max() / np.abs(g["y_numba"]).max() <= 5e-3
+    # dequantize: sequential fp16 adds in codebook order (cuda_kernel.cu:437-453), one more RN multiply for the scale
+    W = ops.codeKx8_dequant(cu(g["codes"]), cu(cb16), None)
+    seq = cb16[0, g["idx"][:, :, 0].astype(np.int64), 0, :]
+    for n in range(1, N):
+        seq = (seq + cb16[n, g["idx"][:, :, n].astype(np.int64), 0, :]).astype(np.float16)
+    assert np.array_equal(bits(W), seq.reshape(O, I).view(np.uint16)), "CodeKx8Dequant semantics: not bit-exact"
+    Ws = ops.codeKx8_dequant(cu(g["codes"]), cu(cb16), cu(sc16))
+    seqs = (seq.reshape(O, I) * sc16.reshape(-1, 1)).astype(np.float16)
+    assert np.array_equal(bits(Ws), seqs.view(np.uint16))
+    ref = g["weight_f16_noscale"].astype(np.float16)
+    if N <= 2:
+        assert np.array_equal(bits(W), ref.view(np.uint16))              # one IEEE add: identical to _dequantize_weight
+        assert torch.equal(W, ops.code2x8_dequant(cu(g["codes"]), cu(cb16), None)) if N == 2 else True
+    else:
+        np.testing.assert_allclose(W.float().cpu().numpy(), ref.astype(np.float32), rtol=2e-3, atol=2e-3)

@@ -29,7 +29,7 @@ def test_layout_proof(tmp_path):
 
 def test_abi_exports_every_declared_symbol(pkg):
     hdr = open(os.path.join(ROOT, "include", "lutvq.h")).read()
-    declared = set(re.findall(r"\b(lutvq_[a-z0-9_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(lutvq_[A-Za-z0-9_]+)\s*\(", hdr))
     assert declared, "no declarations parsed"
     lib = ctypes.CDLL(pkg._lib.LIB_PATH)
     for name in sorted(declared):
