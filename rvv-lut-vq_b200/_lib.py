@@ -62,6 +62,7 @@ SIGNATURES = {
 DEBUG_SIGNATURES = {
     "lutvq_debug_set_gemv_tuning": (None, [I, I, I]),
     "lutvq_debug_get_gemv_plan": (None, [I, I, P, P, P]),
+    "lutvq_debug_set_gemm_mode": (None, [I]),
 }
 
 

@@ -19,6 +19,7 @@ size_t gemv_packed_bytes(int O, int G);
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);
 void gemv_set_tuning(int nw, int pf, int pa);
 void gemv_set_timeline(void* buf);
+void gemm_set_debug_mode(int m);
 void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk);
 int code2x8_dequant_launch(const void* codes, void* W, const void* codebook, const void* scales, int O, int I,
                            int dtype, cudaStream_t stream);
@@ -240,6 +241,7 @@ int lutvq_vq_dequantize(const void* codebook, const void* codeword, void* W, int
 // ---- not part of the public header: tuning hooks used by bench.py's sweep and the tests ----
 void lutvq_debug_set_gemv_tuning(int nw, int pf, int pa) { gemv_set_tuning(nw, pf, pa); }
 void lutvq_debug_set_timeline(void* buf) { gemv_set_timeline(buf); }
+void lutvq_debug_set_gemm_mode(int m) { gemm_set_debug_mode(m); }
 void lutvq_debug_get_gemv_plan(int prob_m, int prob_k, int* n_k, int* n_chunks, int* rows_per_chunk) {
     gemv_get_plan(prob_m, prob_k, n_k, n_chunks, rows_per_chunk);
 }

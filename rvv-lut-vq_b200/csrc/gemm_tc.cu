@@ -16,7 +16,7 @@
 //              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
 //   warp 4     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
 //              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
-//   mbarrier pipeline of kStages smem stages (full: 128 producer arrivals, empty: tcgen05.commit).
+//   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp, empty: tcgen05.commit).
 //
 // Split-k (few row tiles, e.g. 4096 outputs = 32 tiles on 148 SMs): partial accumulators go to the workspace in
 // fp32, a per-tile arrival counter elects the last CTA, which adds the partials IN FIXED ORDER (deterministic) and
@@ -45,6 +45,8 @@ struct GemmParams {
     unsigned int* counters; // [n_tiles] split-k arrival counters (zero between launches)
     float* partial;         // [ksplit][n_pad][O_pad] fp32 partial accumulators (ksplit > 1)
     int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, tmem_cols;
+    int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
+    int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
 };
 
 // ---- PTX wrappers (forms as in CUTLASS cute/arch/{copy_sm100,mma_sm100_umma,tmem_allocator_sm100}.hpp) ----
@@ -90,6 +92,20 @@ __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
 
+__device__ __forceinline__ uint4 lds128(uint32_t a) {       // read-only data (the codebook copies): free to be scheduled
+    uint4 v;
+    asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint4 lds128_sync(uint32_t a) {  // data another thread wrote before a barrier
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // K-major, no-swizzle UMMA shared-memory descriptor (cute::UMMA::SmemDescriptor): 8-row x 16-byte core matrices,
 // rows 16 B apart; SBO = distance between 8-row groups, LBO = distance between the two k core matrices of one MMA.
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -101,7 +117,7 @@ __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
     return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-template <int DT>
+template <int DT, int P>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_dequant_tc_kernel(const GemmParams p) {
     using D = Dtype<DT>;
@@ -111,7 +127,8 @@ gemm_dequant_tc_kernel(const GemmParams p) {
     const uint32_t sbase = smem_u32(smem);
     uint4* sh_cb = reinterpret_cast<uint4*>(smem);
     const int S = p.stages;
-    const uint32_t sA = sbase + kCbSmemBytes;
+    const uint32_t sC = sbase + kCbSmemBytes;                               // 2 code-chunk buffers of 128 rows x chunk x 16 B
+    const uint32_t sA = sC + 2u * (uint32_t)kBM * (uint32_t)P * 16u;
     const uint32_t bstage = (uint32_t)p.n_pad * 128u;
     const uint32_t sB = sA + (uint32_t)S * kAStageBytes;
     const uint32_t bars = sB + (uint32_t)S * bstage;
@@ -129,7 +146,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
 
     // ---------------- one-time setup ----------------
     if (tid == kProducerThreads) {
-        for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads); mbar_init(empty_bar(i), 1); }
+        for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads / 32); mbar_init(empty_bar(i), 1); }
         mbar_init(accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -137,6 +154,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)p.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else {
+        #pragma unroll 8
         for (int i = tid; i < 2 * 256 * 8; i += kProducerThreads) sh_cb[i] = __ldg(p.codebook + (i >> 3));
     }
     tc_fence_before();
@@ -146,12 +164,11 @@ gemm_dequant_tc_kernel(const GemmParams p) {
 
     if (warp < 4) {
         // =============================== producers: dequantize A, copy B ===============================
-        const int row = min(row0 + tid, p.O - 1);                       // rows past the end recompute the last row; never stored
-        const uint8_t* codes_row = p.codes + (size_t)row * (size_t)(p.I / 4);
-        const uint4* cb0 = sh_cb + (lane & 7);
-        const uint4* cb1 = sh_cb + 256 * 8 + (lane & 7);
+        const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
+        const uint32_t cbB = cbA + 256u * 8u * 16u;
         const uint8_t* xb = static_cast<const uint8_t*>(p.x);
         auto issue_B = [&](int kb, int s) {
+            if (p.dbg & 4) { cp_async_commit(); return; }
             for (int n = tid; n < p.n_pad; n += kProducerThreads) {
                 const uint32_t dst = sB + (uint32_t)s * bstage + (uint32_t)n * 16u;
                 if (n < p.batch) {
@@ -160,45 +177,99 @@ gemm_dequant_tc_kernel(const GemmParams p) {
                     for (int j = 0; j < 8; ++j) cp_async16(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u), src + j * 16);
                 } else {
                     #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        asm volatile("st.shared.v4.u32 [%0], {%1, %1, %1, %1};" :: "r"(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u)), "r"(0u) : "memory");
+                    for (int j = 0; j < 8; ++j) sts128(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u), make_uint4(0u, 0u, 0u, 0u));
                 }
             }
             cp_async_commit();
         };
-        uint4 c_cur = ldg_stream_u128(codes_row + (size_t)kb0 * 16);
-        uint4 c_nxt = (kb0 + 1 < kb1) ? ldg_stream_u128(codes_row + (size_t)(kb0 + 1) * 16) : make_uint4(0, 0, 0, 0);
-        issue_B(kb0, 0);
-        for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
-            const int s = it % S;
+        // The loop is bound by instruction issue (one producer warp per scheduler), so everything that is not a codebook
+        // read, an add or a store is kept out of it: stage indices and parities are carried, not divided; the code
+        // stream is staged per CHUNK of P k blocks.  A chunk = P*16 bytes of every row: each thread loads P 16-byte
+        // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead), stores them
+        // XOR-swizzled into one of two shared buffers, and after one producer barrier reads its own row's P code words
+        // back with conflict-free 128-bit loads.
+        constexpr int lgP = P == 8 ? 3 : 2;
+        constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
+        auto swz = [](int r, int c) { return P == 8 ? (c ^ (r & 7)) : (c ^ ((r >> 1) & 3)); };
+        uint4 pre[P], cur[P];
+        auto load_chunk = [&](int c) {
+            const int kbase = kb0 + c * P;
+            #pragma unroll
+            for (int i = 0; i < P; ++i) {
+                const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
+                const int grow = min(row0 + r, p.O - 1);                 // rows past the end recompute the last row; never stored
+                pre[i] = kb < kb1 ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
+            }
+        };
+        auto store_chunk = [&](int c) {
+            const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
+            #pragma unroll
+            for (int i = 0; i < P; ++i) {
+                const int q = i * kProducerThreads + tid, r = q >> lgP;
+                sts128(buf + (uint32_t)((r << lgP) + swz(r, q & (P - 1))) * 16u, pre[i]);
+            }
+        };
+        auto read_chunk = [&](int c) {
+            const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
+            #pragma unroll
+            for (int j = 0; j < P; ++j) cur[j] = lds128_sync(buf + (uint32_t)((tid << lgP) + swz(tid, j)) * 16u);
+        };
+        int s = 0, s1 = 1;                                               // stage of this k block / of the next (S >= 2)
+        uint32_t par1 = 1u;                                              // parity to wait for on empty[s1]
+        auto do_block = [&](int kb, const uint4 cc) {
             if (kb + 1 < kb1) {                                          // next stage's activations fly while we dequantize
-                const int it1 = it + 1, s1 = it1 % S;
-                mbar_wait(empty_bar(s1), (uint32_t)(((it1 / S) & 1) ^ 1));
+                mbar_wait(empty_bar(s1), par1);
                 issue_B(kb + 1, s1);
             } else {
                 cp_async_commit();
             }
-            const uint4 cc = c_cur;
-            c_cur = c_nxt;
-            if (kb + 2 < kb1) c_nxt = ldg_stream_u128(codes_row + (size_t)(kb + 2) * 16);
             const uint32_t w[4] = {cc.x, cc.y, cc.z, cc.w};
             const uint32_t a_dst = sA + (uint32_t)s * kAStageBytes + (uint32_t)tid * 16u;
-            #pragma unroll
-            for (int g = 0; g < 8; ++g) {
-                const uint32_t code = (w[g >> 1] >> (16 * (g & 1))) & 0xFFFFu;   // byte 0 = codebook-0 index, byte 1 = codebook-1 index
-                const uint4 a = cb0[(code & 0xFFu) * 8];
-                const uint4 b = cb1[(code >> 8) * 8];
-                uint4 r;
-                const T2* a2 = reinterpret_cast<const T2*>(&a);
-                const T2* b2 = reinterpret_cast<const T2*>(&b);
-                T2* r2 = reinterpret_cast<T2*>(&r);
+            if (!(p.dbg & 2)) {
                 #pragma unroll
-                for (int j = 0; j < 4; ++j) r2[j] = D::add2(a2[j], b2[j]);
-                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a_dst + (uint32_t)g * (kBM * 16u)), "r"(r.x), "r"(r.y), "r"(r.z), "r"(r.w) : "memory");
+                for (int h = 0; h < 2; ++h) {                            // 4 groups at a time: 8 reads in flight, then adds and stores
+                    uint4 a[4], b[4];
+                    #pragma unroll
+                    for (int g = 0; g < 4; ++g) {                        // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
+                        const uint32_t wg = w[2 * h + (g >> 1)];
+                        a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
+                        b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
+                    }
+                    #pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint4 r;
+                        const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
+                        const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
+                        T2* r2 = reinterpret_cast<T2*>(&r);
+                        #pragma unroll
+                        for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
+                        sts128(a_dst + (uint32_t)(4 * h + g) * (kBM * 16u), r);
+                    }
+                }
             }
             cp_async_wait<1>();                                          // this stage's activations have landed
             fence_proxy_async_smem();                                    // generic-proxy writes -> visible to the tensor core
-            mbar_arrive(full_bar(s));
+            __syncwarp();
+            if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
+            s = s1;
+            if (++s1 == S) { s1 = 0; par1 ^= 1u; }
+        };
+        load_chunk(0);
+        store_chunk(0);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        read_chunk(0);
+        if (kb0 + P < kb1) load_chunk(1);
+        issue_B(kb0, 0);
+        for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
+            #pragma unroll
+            for (int j = 0; j < P; ++j)
+                if (kbc + j < kb1) do_block(kbc + j, cur[j]);
+            if (kbc + P < kb1) {
+                store_chunk(c + 1);
+                asm volatile("bar.sync 1, 128;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
+                read_chunk(c + 1);
+                if (kbc + 2 * P < kb1) load_chunk(c + 2);
+            }
         }
 
         // =============================== epilogue ===============================
@@ -252,20 +323,22 @@ gemm_dequant_tc_kernel(const GemmParams p) {
     } else {
         // =============================== MMA issuer (warp 4) ===============================
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
+        int s = 0;
+        uint32_t par = 0u;
         for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
-            const int s = it % S;
-            mbar_wait(full_bar(s), (uint32_t)((it / S) & 1));
+            mbar_wait(full_bar(s), par);
             tc_fence_after();
             if (lane == 0) {
                 #pragma unroll
                 for (int k = 0; k < kBK / 16; ++k) {
                     const uint64_t adesc = umma_desc(sA + (uint32_t)s * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
                     const uint64_t bdesc = umma_desc(sB + (uint32_t)s * bstage + (uint32_t)k * (2u * (uint32_t)p.n_pad * 16u), (uint32_t)p.n_pad * 16u, 128u);
-                    tc_mma_f16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    if (!(p.dbg & 1)) tc_mma_f16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
                 tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
             }
             __syncwarp();
+            if (++s == S) { s = 0; par ^= 1u; }
         }
         if (lane == 0) tc_commit(accum_bar);                             // accumulator complete
         __syncwarp();
@@ -281,6 +354,9 @@ gemm_dequant_tc_kernel(const GemmParams p) {
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
+static int g_gemm_dbg = 0;
+void gemm_set_debug_mode(int m) { g_gemm_dbg = m; }
+
 struct GemmPlan { int n_tiles, O_pad, nkb, ksplit; };
 
 static GemmPlan plan_gemm(int O, int I, int sm_count) {
@@ -314,9 +390,9 @@ size_t gemm_workspace_bytes_for(int O, int I, int max_batch) {
 }
 size_t gemm_workspace_bytes(int O, int I) { return gemm_workspace_bytes_for(O, I, kGemmMaxBatch); }
 
-template <int DT>
+template <int DT, int P>
 static int launch_gemm(const GemmParams& p, dim3 grid, size_t smem, cudaStream_t stream) {
-    auto kern = gemm_dequant_tc_kernel<DT>;
+    auto kern = gemm_dequant_tc_kernel<DT, P>;
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -347,15 +423,18 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.O = O; p.O_pad = pl.O_pad; p.I = I; p.batch = nb;
         p.n_pad = ceil_div(nb, 16) * 16;
         p.nkb = pl.nkb; p.ksplit = pl.ksplit;
+        p.dbg = g_gemm_dbg;
         p.tmem_cols = 32;
         while (p.tmem_cols < p.n_pad) p.tmem_cols *= 2;
         const size_t stage_bytes = (size_t)kAStageBytes + (size_t)p.n_pad * 128;
-        const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - 1024;
+        p.chunk = p.n_pad <= 128 ? 8 : 4;
+        const size_t code_bytes = 2 * (size_t)kBM * p.chunk * 16;
+        const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - code_bytes - 1024;
         int S = (int)(budget / stage_bytes);
-        if (S > 4) S = 4;
+        if (S > 8) S = 8;
         if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
         p.stages = S;
-        const size_t smem = kCbSmemBytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
+        const size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
         p.counters = nullptr; p.partial = nullptr;
         if (pl.ksplit > 1) {
             const size_t need = gemm_workspace_bytes_for(O, I, nb);
@@ -365,7 +444,8 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
             p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256 + gemv_acc_bytes(O));
         }
         const dim3 grid(pl.n_tiles, pl.ksplit);
-        const int rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16>(p, grid, smem, stream);
+        const int rc = p.chunk == 8 ? (dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8>(p, grid, smem, stream))
+                                    : (dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4>(p, grid, smem, stream));
         if (rc) return rc;
     }
     return LUTVQ_OK;

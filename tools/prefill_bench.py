@@ -12,16 +12,25 @@ from rvv_lut_vq_b200 import ops, synth  # noqa: E402
 
 
 def timed(fn, reps):
-    for _ in range(3):
-        fn()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(reps):
-        fn()
-    b.record()
-    torch.cuda.synchronize()
-    return a.elapsed_time(b) * 1e3 / reps
+    """reps calls captured in ONE CUDA graph (the Python wrapper costs more host time per call than the kernel runs)"""
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            fn()
+        st.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=st):
+            for _ in range(reps):
+                fn()
+        g.replay()
+        st.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(st)
+        for _ in range(3):
+            g.replay()
+        b.record(st)
+        st.synchronize()
+    return a.elapsed_time(b) * 1e3 / (3 * reps)
 
 
 def main():
