@@ -8,13 +8,13 @@
 //
 // One CTA = one 128-row tile of output channels x the whole (padded) batch, over a k-range of the split:
 //   D[128 x N] (TMEM, fp32)  +=  A[128 x 64] (smem, dequantized weights, K-major)  *  B[N x 64]^T (smem, activations)
-//   warps 0-3  producers: each thread owns one output row: a 16-byte code load = 8 groups per 64-wide k block; per
+//   warps 0-7  producers: each thread owns one output row and one half of every 64-wide k block (4 groups = 8 code bytes); per
 //              group two conflict-free 128-bit reads of the 8x replicated codebooks, one HADD2 x4 (the SAME single
 //              RN add as Code2x8Dequant, cuda_kernel.cu:283-289), one 128-bit store -- exactly one "core matrix row"
 //              of the no-swizzle K-major UMMA layout  addr = kchunk * (rows*16) + row*16.
 //              The activation tile is brought in by cp.async in the same layout.  Afterwards the same warps run the
 //              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
-//   warp 4     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
+//   warp 8     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
 //              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
 //   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp, empty: tcgen05.commit).
 //
@@ -30,8 +30,8 @@ namespace lutvq {
 
 constexpr int kBM = 128;                 // output channels per CTA (UMMA M)
 constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 code bytes per row
-constexpr int kProducerThreads = 128;
-constexpr int kGemmThreads = 160;
+constexpr int kProducerThreads = 256;      // 8 warps: thread = (output row, half of the k block); two warps per scheduler hide the LDS latency
+constexpr int kGemmThreads = 288;          // + the MMA warp
 constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
 constexpr int kAStageBytes = kBM * kBK * 2;        // 16 KiB
 
@@ -45,6 +45,8 @@ struct GemmParams {
     unsigned int* counters; // [n_tiles] split-k arrival counters (zero between launches)
     float* partial;         // [ksplit][n_pad][O_pad] fp32 partial accumulators (ksplit > 1)
     int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, tmem_cols;
+    int rpc;                // output rows this CTA owns (<= 128, multiple of 8): rows of the M=128 tile past it are never dequantized or stored
+    int lookahead;          // k blocks the activation copies run ahead (1..3, < stages)
     int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
     int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
 };
@@ -102,6 +104,11 @@ __device__ __forceinline__ uint4 lds128_sync(uint32_t a) {  // data another thre
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
     return v;
 }
+__device__ __forceinline__ uint2 lds64_sync(uint32_t a) {
+    uint2 v;
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+    return v;
+}
 __device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -111,6 +118,11 @@ __device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
            ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);   // version 1 (Blackwell), layout_type 0 = SWIZZLE_NONE
+}
+// K-major SWIZZLE_128B descriptor: rows of 128 bytes, 8-row atoms 1024 bytes apart (SBO), LBO unused (1), layout_type 2;
+// the atom base must be 1024-byte aligned; a K=16 step inside the 128-byte span advances the start address by 32 bytes.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 // cute::UMMA::InstrDescriptor for kind::f16: D = F32, A/B = F16 or BF16, both K-major, dense
 __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
@@ -141,7 +153,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tile = blockIdx.x, z = blockIdx.y;
-    const int row0 = tile * kBM;
+    const int row0 = tile * p.rpc;
     const int kb0 = (int)(((long long)z * p.nkb) / p.ksplit), kb1 = (int)(((long long)(z + 1) * p.nkb) / p.ksplit);
 
     // ---------------- one-time setup ----------------
@@ -150,7 +162,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         mbar_init(accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {
+    if (warp == kProducerThreads / 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)p.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else {
@@ -162,23 +174,23 @@ gemm_dequant_tc_kernel(const GemmParams p) {
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
-    if (warp < 4) {
+    if (warp < kProducerThreads / 32) {
+        const int row = tid & (kBM - 1), hk = tid >> 7;                  // this thread's row of the tile and half (4 groups) of every k block
         // =============================== producers: dequantize A, copy B ===============================
         const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
         const uint32_t cbB = cbA + 256u * 8u * 16u;
         const uint8_t* xb = static_cast<const uint8_t*>(p.x);
+        // Activation tile: SWIZZLE_128B K-major -- batch row n = 128 contiguous bytes (64 k), its 16-byte pieces XOR-permuted
+        // by n & 7.  Eight lanes copy one row: 128 contiguous bytes in global AND in shared memory, i.e. one wavefront
+        // per row (the no-swizzle layout scattered every 16-byte piece to its own wavefront: 2048 per k block at batch
+        // 256).  Padding rows n >= batch are left as they are: D column n depends on B row n only and is never read.
         auto issue_B = [&](int kb, int s) {
             if (p.dbg & 4) { cp_async_commit(); return; }
-            for (int n = tid; n < p.n_pad; n += kProducerThreads) {
-                const uint32_t dst = sB + (uint32_t)s * bstage + (uint32_t)n * 16u;
-                if (n < p.batch) {
-                    const uint8_t* src = xb + ((size_t)n * p.I + (size_t)kb * kBK) * 2;
-                    #pragma unroll
-                    for (int j = 0; j < 8; ++j) cp_async16(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u), src + j * 16);
-                } else {
-                    #pragma unroll
-                    for (int j = 0; j < 8; ++j) sts128(dst + (uint32_t)j * ((uint32_t)p.n_pad * 16u), make_uint4(0u, 0u, 0u, 0u));
-                }
+            const uint32_t base = sB + (uint32_t)s * bstage;
+            const uint8_t* src0 = xb + (size_t)kb * (kBK * 2);
+            for (int q = tid; q < p.batch * 8; q += kProducerThreads) {
+                const int n = q >> 3, j = q & 7;
+                cp_async16(base + (uint32_t)n * 128u + (uint32_t)((j ^ (n & 7)) * 16), src0 + (size_t)n * p.I * 2 + j * 16);
             }
             cp_async_commit();
         };
@@ -191,20 +203,21 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         constexpr int lgP = P == 8 ? 3 : 2;
         constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
         auto swz = [](int r, int c) { return P == 8 ? (c ^ (r & 7)) : (c ^ ((r >> 1) & 3)); };
-        uint4 pre[P], cur[P];
+        uint4 pre[P / 2];
+        uint2 cur[P];
         auto load_chunk = [&](int c) {
             const int kbase = kb0 + c * P;
             #pragma unroll
-            for (int i = 0; i < P; ++i) {
+            for (int i = 0; i < P / 2; ++i) {
                 const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
                 const int grow = min(row0 + r, p.O - 1);                 // rows past the end recompute the last row; never stored
-                pre[i] = kb < kb1 ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
+                pre[i] = (kb < kb1 && r < p.rpc) ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
             }
         };
         auto store_chunk = [&](int c) {
             const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
             #pragma unroll
-            for (int i = 0; i < P; ++i) {
+            for (int i = 0; i < P / 2; ++i) {
                 const int q = i * kProducerThreads + tid, r = q >> lgP;
                 sts128(buf + (uint32_t)((r << lgP) + swz(r, q & (P - 1))) * 16u, pre[i]);
             }
@@ -212,61 +225,63 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         auto read_chunk = [&](int c) {
             const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
             #pragma unroll
-            for (int j = 0; j < P; ++j) cur[j] = lds128_sync(buf + (uint32_t)((tid << lgP) + swz(tid, j)) * 16u);
+            for (int j = 0; j < P; ++j) cur[j] = lds64_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 8u);
         };
-        int s = 0, s1 = 1;                                               // stage of this k block / of the next (S >= 2)
-        uint32_t par1 = 1u;                                              // parity to wait for on empty[s1]
-        auto do_block = [&](int kb, const uint4 cc) {
-            if (kb + 1 < kb1) {                                          // next stage's activations fly while we dequantize
-                mbar_wait(empty_bar(s1), par1);
-                issue_B(kb + 1, s1);
+        // Activations are issued D k blocks ahead (D = min(3, S - 2) >= 1): one block ahead left every block waiting for
+        // most of an L2 round trip in cp.async.wait_group.
+        const int LA = p.lookahead;
+        int s = 0, sD = LA;                                              // stage of this k block / of block +D  (D < S)
+        uint32_t parD = 1u;                                              // parity to wait for on empty[sD]
+        auto do_block = [&](int kb, const uint2 cc) {
+            if (kb + LA < kb1) {
+                mbar_wait(empty_bar(sD), parD);
+                issue_B(kb + LA, sD);
             } else {
                 cp_async_commit();
             }
-            const uint32_t w[4] = {cc.x, cc.y, cc.z, cc.w};
-            const uint32_t a_dst = sA + (uint32_t)s * kAStageBytes + (uint32_t)tid * 16u;
-            if (!(p.dbg & 2)) {
+            const uint32_t w[2] = {cc.x, cc.y};
+            const uint32_t a_dst = sA + (uint32_t)s * kAStageBytes + (uint32_t)row * 16u + (uint32_t)hk * (4u * kBM * 16u);
+            if (!(p.dbg & 2) && row < p.rpc) {                           // 4 groups: 8 reads in flight, then adds and stores
+                uint4 a[4], b[4];
                 #pragma unroll
-                for (int h = 0; h < 2; ++h) {                            // 4 groups at a time: 8 reads in flight, then adds and stores
-                    uint4 a[4], b[4];
+                for (int g = 0; g < 4; ++g) {                            // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
+                    const uint32_t wg = w[g >> 1];
+                    a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
+                    b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
+                }
+                #pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    uint4 r;
+                    const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
+                    const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
+                    T2* r2 = reinterpret_cast<T2*>(&r);
                     #pragma unroll
-                    for (int g = 0; g < 4; ++g) {                        // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
-                        const uint32_t wg = w[2 * h + (g >> 1)];
-                        a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
-                        b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
-                    }
-                    #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        uint4 r;
-                        const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
-                        const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
-                        T2* r2 = reinterpret_cast<T2*>(&r);
-                        #pragma unroll
-                        for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
-                        sts128(a_dst + (uint32_t)(4 * h + g) * (kBM * 16u), r);
-                    }
+                    for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
+                    sts128(a_dst + (uint32_t)g * (kBM * 16u), r);
                 }
             }
-            cp_async_wait<1>();                                          // this stage's activations have landed
+            if (LA == 3) cp_async_wait<3>(); else if (LA == 2) cp_async_wait<2>(); else cp_async_wait<1>();   // this stage's activations have landed
             fence_proxy_async_smem();                                    // generic-proxy writes -> visible to the tensor core
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
-            s = s1;
-            if (++s1 == S) { s1 = 0; par1 ^= 1u; }
+            if (++s == S) s = 0;
+            if (++sD == S) { sD = 0; parD ^= 1u; }
         };
         load_chunk(0);
         store_chunk(0);
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
         read_chunk(0);
         if (kb0 + P < kb1) load_chunk(1);
-        issue_B(kb0, 0);
+        for (int d = 0; d < LA; ++d) {
+            if (kb0 + d < kb1) issue_B(kb0 + d, d); else cp_async_commit();
+        }
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
             #pragma unroll
             for (int j = 0; j < P; ++j)
                 if (kbc + j < kb1) do_block(kbc + j, cur[j]);
             if (kbc + P < kb1) {
                 store_chunk(c + 1);
-                asm volatile("bar.sync 1, 128;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
+                asm volatile("bar.sync 1, 256;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
                 read_chunk(c + 1);
                 if (kbc + 2 * P < kb1) load_chunk(c + 2);
             }
@@ -275,9 +290,9 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         // =============================== epilogue ===============================
         mbar_wait(accum_bar, 0u);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16);
-        const int o = row0 + tid;
-        const bool live = o < p.O;
+        const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);   // a warp reaches TMEM lanes 32*(warp%4)..+31
+        const int o = row0 + row;
+        const bool live = row < p.rpc && o < p.O;                        // the two warps of a row split the batch columns
         T sc = D::from_f(1.f), bi = D::from_f(0.f);
         if (live && p.scales) sc = static_cast<const T*>(p.scales)[o];
         if (live && p.bias)   bi = static_cast<const T*>(p.bias)[o];
@@ -288,7 +303,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
             static_cast<T*>(p.y)[(size_t)b * p.O + o] = rr;
         };
         if (p.ksplit == 1) {
-            for (int c0 = 0; c0 < p.n_pad; c0 += 16) {
+            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 32) {
                 uint32_t v[16];
                 tc_ld16(taddr + (uint32_t)c0, v);
                 #pragma unroll
@@ -297,21 +312,21 @@ gemm_dequant_tc_kernel(const GemmParams p) {
             }
         } else {
             float* mine = p.partial + ((size_t)z * p.n_pad) * p.O_pad + o;
-            for (int c0 = 0; c0 < p.n_pad; c0 += 16) {
+            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 32) {
                 uint32_t v[16];
                 tc_ld16(taddr + (uint32_t)c0, v);
                 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                    if (c0 + j < p.batch) __stcg(mine + (size_t)(c0 + j) * p.O_pad, __uint_as_float(v[j]));
+                    if (live && c0 + j < p.batch) __stcg(mine + (size_t)(c0 + j) * p.O_pad, __uint_as_float(v[j]));
             }
             __threadfence();
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (tid == 0) *last_flag_ptr = (atomicAdd(p.counters + tile, 1u) == (unsigned)p.ksplit - 1u) ? 1u : 0u;
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             if (*last_flag_ptr) {                                        // last CTA of this tile: fixed-order sum of the partials
                 __threadfence();
                 if (live)
-                    for (int b = 0; b < p.batch; ++b) {
+                    for (int b = hk; b < p.batch; b += 2) {
                         float acc = 0.f;
                         for (int zz = 0; zz < p.ksplit; ++zz)
                             acc += __ldcg(p.partial + ((size_t)zz * p.n_pad + b) * p.O_pad + o);
@@ -321,7 +336,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
             }
         }
     } else {
-        // =============================== MMA issuer (warp 4) ===============================
+        // =============================== MMA issuer (warp 8) ===============================
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
         int s = 0;
         uint32_t par = 0u;
@@ -332,7 +347,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
                 #pragma unroll
                 for (int k = 0; k < kBK / 16; ++k) {
                     const uint64_t adesc = umma_desc(sA + (uint32_t)s * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
-                    const uint64_t bdesc = umma_desc(sB + (uint32_t)s * bstage + (uint32_t)k * (2u * (uint32_t)p.n_pad * 16u), (uint32_t)p.n_pad * 16u, 128u);
+                    const uint64_t bdesc = umma_desc_sw128(sB + (uint32_t)s * bstage + (uint32_t)k * 32u);
                     if (!(p.dbg & 1)) tc_mma_f16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
                 }
                 tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
@@ -347,22 +362,32 @@ gemm_dequant_tc_kernel(const GemmParams p) {
     // ---------------- teardown ----------------
     tc_fence_before();
     __syncthreads();
-    if (warp == 4)
+    if (warp == kProducerThreads / 32)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
+
 static int g_gemm_dbg = 0;
 void gemm_set_debug_mode(int m) { g_gemm_dbg = m; }
 
-struct GemmPlan { int n_tiles, O_pad, nkb, ksplit; };
+struct GemmPlan { int n_tiles, rpc, O_pad, nkb, ksplit; };
 
 static GemmPlan plan_gemm(int O, int I, int sm_count) {
     GemmPlan pl;
-    pl.n_tiles = ceil_div(O, kBM);
-    pl.O_pad = pl.n_tiles * kBM;
+    // The producers' shared-memory traffic (per ROW) bounds the kernel, the M=128 MMA is nearly free: when 128-row tiles
+    // would leave SMs idle (11008 rows = 86 tiles on 148 SMs) every CTA takes fewer rows of its tile instead.
+    pl.rpc = kBM;
+    const int tiles128 = ceil_div(O, kBM);
+    if (tiles128 * 2 > sm_count && !(g_gemm_dbg & 8)) {
+        const int waves = ceil_div(tiles128, sm_count);
+        pl.rpc = ceil_div(ceil_div(O, waves * sm_count), 8) * 8;
+        if (pl.rpc > kBM) pl.rpc = kBM;
+    }
+    pl.n_tiles = ceil_div(O, pl.rpc);
+    pl.O_pad = pl.n_tiles * pl.rpc;
     pl.nkb = I / kBK;
     int ks = sm_count / pl.n_tiles;                       // fill the SMs when there are few row tiles
     if (ks > pl.nkb / 4) ks = pl.nkb / 4;                 // at least 4 k blocks per CTA
@@ -420,7 +445,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.codebook = static_cast<const uint4*>(codebooks);
         p.scales = scales; p.bias = bias;
         p.y = static_cast<uint8_t*>(y) + (size_t)b0 * O * 2;
-        p.O = O; p.O_pad = pl.O_pad; p.I = I; p.batch = nb;
+        p.O = O; p.O_pad = pl.O_pad; p.I = I; p.batch = nb; p.rpc = pl.rpc;
         p.n_pad = ceil_div(nb, 16) * 16;
         p.nkb = pl.nkb; p.ksplit = pl.ksplit;
         p.dbg = g_gemm_dbg;
@@ -434,6 +459,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         if (S > 8) S = 8;
         if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
         p.stages = S;
+        p.lookahead = S - 2 < 1 ? 1 : (S - 2 > 3 ? 3 : S - 2);
         const size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
         p.counters = nullptr; p.partial = nullptr;
         if (pl.ksplit > 1) {
