@@ -129,7 +129,7 @@ __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
     return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-template <int DT, int P>
+template <int DT, int P, int BPS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_dequant_tc_kernel(const GemmParams p) {
     using D = Dtype<DT>;
@@ -141,8 +141,10 @@ gemm_dequant_tc_kernel(const GemmParams p) {
     const int S = p.stages;
     const uint32_t sC = sbase + kCbSmemBytes;                               // 2 code-chunk buffers of 128 rows x chunk x 16 B
     const uint32_t sA = sC + 2u * (uint32_t)kBM * (uint32_t)P * 16u;
-    const uint32_t bstage = (uint32_t)p.n_pad * 128u;
-    const uint32_t sB = sA + (uint32_t)S * kAStageBytes;
+    // a pipeline stage = BPS k blocks (every mbarrier round trip costs ~150 cycles per warp: small batches take 2 per stage)
+    constexpr uint32_t astage = (uint32_t)BPS * kAStageBytes;
+    const uint32_t bblock = (uint32_t)p.n_pad * 128u, bstage = (uint32_t)BPS * bblock;
+    const uint32_t sB = sA + (uint32_t)S * astage;
     const uint32_t bars = sB + (uint32_t)S * bstage;
     auto full_bar  = [&](int i) { return bars + 8u * (uint32_t)i; };
     auto empty_bar = [&](int i) { return bars + 8u * (uint32_t)(S + i); };
@@ -184,13 +186,17 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         // by n & 7.  Eight lanes copy one row: 128 contiguous bytes in global AND in shared memory, i.e. one wavefront
         // per row (the no-swizzle layout scattered every 16-byte piece to its own wavefront: 2048 per k block at batch
         // 256).  Padding rows n >= batch are left as they are: D column n depends on B row n only and is never read.
-        auto issue_B = [&](int kb, int s) {
+        auto issue_B = [&](int kb, int s) {                              // the BPS k blocks of one stage, first one = kb
             if (p.dbg & 4) { cp_async_commit(); return; }
-            const uint32_t base = sB + (uint32_t)s * bstage;
-            const uint8_t* src0 = xb + (size_t)kb * (kBK * 2);
-            for (int q = tid; q < p.batch * 8; q += kProducerThreads) {
-                const int n = q >> 3, j = q & 7;
-                cp_async16(base + (uint32_t)n * 128u + (uint32_t)((j ^ (n & 7)) * 16), src0 + (size_t)n * p.I * 2 + j * 16);
+            #pragma unroll
+            for (int b = 0; b < BPS; ++b) {
+                if (kb + b >= kb1) break;
+                const uint32_t base = sB + (uint32_t)s * bstage + (uint32_t)b * bblock;
+                const uint8_t* src0 = xb + (size_t)(kb + b) * (kBK * 2);
+                for (int q = tid; q < p.batch * 8; q += kProducerThreads) {
+                    const int n = q >> 3, j = q & 7;
+                    cp_async16(base + (uint32_t)n * 128u + (uint32_t)((j ^ (n & 7)) * 16), src0 + (size_t)n * p.I * 2 + j * 16);
+                }
             }
             cp_async_commit();
         };
@@ -232,36 +238,40 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         const int LA = p.lookahead;
         int s = 0, sD = LA;                                              // stage of this k block / of block +D  (D < S)
         uint32_t parD = 1u;                                              // parity to wait for on empty[sD]
-        auto do_block = [&](int kb, const uint2 cc) {
-            if (kb + LA < kb1) {
+        auto do_stage = [&](int kb, const uint2 c0, const uint2 c1) {    // k blocks kb .. kb+BPS-1 (c1 unused when BPS == 1)
+            if (kb + LA * BPS < kb1) {
                 mbar_wait(empty_bar(sD), parD);
-                issue_B(kb + LA, sD);
+                issue_B(kb + LA * BPS, sD);
             } else {
                 cp_async_commit();
             }
-            const uint32_t w[2] = {cc.x, cc.y};
-            const uint32_t a_dst = sA + (uint32_t)s * kAStageBytes + (uint32_t)row * 16u + (uint32_t)hk * (4u * kBM * 16u);
-            if (!(p.dbg & 2) && row < p.rpc) {                           // 4 groups: 8 reads in flight, then adds and stores
-                uint4 a[4], b[4];
-                #pragma unroll
-                for (int g = 0; g < 4; ++g) {                            // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
-                    const uint32_t wg = w[g >> 1];
-                    a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
-                    b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
-                }
-                #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    uint4 r;
-                    const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
-                    const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
-                    T2* r2 = reinterpret_cast<T2*>(&r);
+            #pragma unroll
+            for (int sb = 0; sb < BPS; ++sb) {
+                if (kb + sb >= kb1) break;
+                const uint32_t w[2] = {sb ? c1.x : c0.x, sb ? c1.y : c0.y};
+                const uint32_t a_dst = sA + (uint32_t)s * astage + (uint32_t)sb * kAStageBytes + (uint32_t)row * 16u + (uint32_t)hk * (4u * kBM * 16u);
+                if (!(p.dbg & 2) && row < p.rpc) {                       // 4 groups: 8 reads in flight, then adds and stores
+                    uint4 a[4], b[4];
                     #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
-                    sts128(a_dst + (uint32_t)g * (kBM * 16u), r);
+                    for (int g = 0; g < 4; ++g) {                        // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
+                        const uint32_t wg = w[g >> 1];
+                        a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
+                        b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
+                    }
+                    #pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint4 r;
+                        const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
+                        const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
+                        T2* r2 = reinterpret_cast<T2*>(&r);
+                        #pragma unroll
+                        for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
+                        sts128(a_dst + (uint32_t)g * (kBM * 16u), r);
+                    }
                 }
             }
             if (LA == 3) cp_async_wait<3>(); else if (LA == 2) cp_async_wait<2>(); else cp_async_wait<1>();   // this stage's activations have landed
-            fence_proxy_async_smem();                                    // generic-proxy writes -> visible to the tensor core
+            if (!(p.dbg & 16)) fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
             if (++s == S) s = 0;
@@ -273,13 +283,13 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         read_chunk(0);
         if (kb0 + P < kb1) load_chunk(1);
         for (int d = 0; d < LA; ++d) {
-            if (kb0 + d < kb1) issue_B(kb0 + d, d); else cp_async_commit();
+            if (kb0 + d * BPS < kb1) issue_B(kb0 + d * BPS, d); else cp_async_commit();
         }
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
             #pragma unroll
-            for (int j = 0; j < P; ++j)
-                if (kbc + j < kb1) do_block(kbc + j, cur[j]);
-            if (kbc + P < kb1) {
+            for (int j = 0; j < P; j += BPS)
+                if (kbc + j < kb1) do_stage(kbc + j, cur[j], cur[j + BPS - 1]);
+            if (kbc + P < kb1 && !(p.dbg & 32)) {
                 store_chunk(c + 1);
                 asm volatile("bar.sync 1, 256;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
                 read_chunk(c + 1);
@@ -340,15 +350,19 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
         int s = 0;
         uint32_t par = 0u;
-        for (int kb = kb0, it = 0; kb < kb1; ++kb, ++it) {
+        for (int kb = kb0; kb < kb1; kb += BPS) {
             mbar_wait(full_bar(s), par);
             tc_fence_after();
             if (lane == 0) {
                 #pragma unroll
-                for (int k = 0; k < kBK / 16; ++k) {
-                    const uint64_t adesc = umma_desc(sA + (uint32_t)s * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
-                    const uint64_t bdesc = umma_desc_sw128(sB + (uint32_t)s * bstage + (uint32_t)k * 32u);
-                    if (!(p.dbg & 1)) tc_mma_f16(tmem_base, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                for (int sb = 0; sb < BPS; ++sb) {
+                    if (kb + sb >= kb1) break;
+                    #pragma unroll
+                    for (int k = 0; k < kBK / 16; ++k) {
+                        const uint64_t adesc = umma_desc(sA + (uint32_t)s * astage + (uint32_t)sb * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
+                        const uint64_t bdesc = umma_desc_sw128(sB + (uint32_t)s * bstage + (uint32_t)sb * bblock + (uint32_t)k * 32u);
+                        if (!(p.dbg & 1)) tc_mma_f16(tmem_base, adesc, bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
+                    }
                 }
                 tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
             }
@@ -415,9 +429,9 @@ size_t gemm_workspace_bytes_for(int O, int I, int max_batch) {
 }
 size_t gemm_workspace_bytes(int O, int I) { return gemm_workspace_bytes_for(O, I, kGemmMaxBatch); }
 
-template <int DT, int P>
+template <int DT, int P, int BPS>
 static int launch_gemm(const GemmParams& p, dim3 grid, size_t smem, cudaStream_t stream) {
-    auto kern = gemm_dequant_tc_kernel<DT, P>;
+    auto kern = gemm_dequant_tc_kernel<DT, P, BPS>;
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -451,8 +465,9 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.dbg = g_gemm_dbg;
         p.tmem_cols = 32;
         while (p.tmem_cols < p.n_pad) p.tmem_cols *= 2;
-        const size_t stage_bytes = (size_t)kAStageBytes + (size_t)p.n_pad * 128;
-        p.chunk = p.n_pad <= 128 ? 8 : 4;
+        const int bps = (p.n_pad <= 64 && !(g_gemm_dbg & 128)) ? 2 : 1;   // k blocks per pipeline stage
+        const size_t stage_bytes = (size_t)bps * ((size_t)kAStageBytes + (size_t)p.n_pad * 128);
+        p.chunk = (p.n_pad <= 128 && bps == 1) ? 8 : 4;
         const size_t code_bytes = 2 * (size_t)kBM * p.chunk * 16;
         const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - code_bytes - 1024;
         int S = (int)(budget / stage_bytes);
@@ -470,8 +485,10 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
             p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256 + gemv_acc_bytes(O));
         }
         const dim3 grid(pl.n_tiles, pl.ksplit);
-        const int rc = p.chunk == 8 ? (dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8>(p, grid, smem, stream))
-                                    : (dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4>(p, grid, smem, stream));
+        int rc;
+        if (bps == 2)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, grid, smem, stream);
+        else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, grid, smem, stream);
+        else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, grid, smem, stream);
         if (rc) return rc;
     }
     return LUTVQ_OK;

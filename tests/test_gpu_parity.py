@@ -240,10 +240,13 @@ GEMM_CASES = [
     (256, 128, 16, "f16", False),          # one row tile, 4 k blocks, no split
     (1024, 1000, 17, "f16", True),         # ragged rows (1000 = 7 tiles + 104) and ragged batch (17 -> 32 columns)
     (4096, 4096, 64, "f16", True),         # 32 row tiles -> split-k 4 through the workspace
-    (4096, 11008, 256, "f16", False),      # BASELINE configs[2] top batch: 86 tiles, no split, 3 stages
+    (4096, 11008, 256, "f16", False),      # BASELINE configs[2] top batch: 138 CTAs x 80 rows, no split, 3 stages
     (11008, 4096, 128, "f16", False),      # long k (172 blocks), split-k
     (2048, 512, 300, "f16", True),         # batch > 256: chunked launches
     (1024, 768, 48, "bf16", True),
+    (4096, 11008, 16, "f16", True),        # 138 CTAs x 80 rows (rows-per-CTA plan), 2 k blocks per pipeline stage
+    (11008, 4096, 32, "f16", True),        # split-k 4 x 43 k blocks: odd tail stage with 2 k blocks per stage
+    (320, 200, 8, "bf16", False),          # 5 k blocks, ragged rows, one chunk
 ]
 
 

@@ -4,12 +4,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from rvv_lut_vq_b200 import ops, synth, _lib
 from prefill_bench import timed
 dev = torch.device('cuda', 0)
-for I in (1024, 4096):
+for I in (2048, 8192):
     nl = max(4, min(24, (300 << 20) // (11008 * I // 4)))
     Ls = [synth.make_layer_torch(I, 11008, dev, seed=k, scales="ones") for k in range(nl)]
     x = torch.randn((16, I), device=dev, dtype=torch.float16)
     out = []
-    for mode in (0, 2, 7):
+    for mode in (55, 119, 71):
         _lib.lib().lutvq_debug_set_gemm_mode(mode)
         k = [0]
         def f():
