@@ -186,17 +186,20 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         // by n & 7.  Eight lanes copy one row: 128 contiguous bytes in global AND in shared memory, i.e. one wavefront
         // per row (the no-swizzle layout scattered every 16-byte piece to its own wavefront: 2048 per k block at batch
         // 256).  Padding rows n >= batch are left as they are: D column n depends on B row n only and is never read.
+        // thread -> (row n0 = tid / 8 (+32 per step: same n & 7), piece j = tid % 8): pointer bumps only in the copy loop
+        const int bn0 = tid >> 3, bj = tid & 7;
+        const uint8_t* const bsrc = xb + (size_t)bn0 * p.I * 2 + bj * 16;
+        const uint32_t bdst = (uint32_t)bn0 * 128u + (uint32_t)((bj ^ (bn0 & 7)) * 16);
+        const size_t bsrc_step = (size_t)(kProducerThreads / 8) * p.I * 2;
         auto issue_B = [&](int kb, int s) {                              // the BPS k blocks of one stage, first one = kb
             if (p.dbg & 4) { cp_async_commit(); return; }
             #pragma unroll
             for (int b = 0; b < BPS; ++b) {
                 if (kb + b >= kb1) break;
-                const uint32_t base = sB + (uint32_t)s * bstage + (uint32_t)b * bblock;
-                const uint8_t* src0 = xb + (size_t)(kb + b) * (kBK * 2);
-                for (int q = tid; q < p.batch * 8; q += kProducerThreads) {
-                    const int n = q >> 3, j = q & 7;
-                    cp_async16(base + (uint32_t)n * 128u + (uint32_t)((j ^ (n & 7)) * 16), src0 + (size_t)n * p.I * 2 + j * 16);
-                }
+                uint32_t dst = sB + (uint32_t)s * bstage + (uint32_t)b * bblock + bdst;
+                const uint8_t* src = bsrc + (size_t)(kb + b) * (kBK * 2);
+                for (int n = bn0; n < p.batch; n += kProducerThreads / 8, dst += (kProducerThreads / 8) * 128u, src += bsrc_step)
+                    cp_async16(dst, src);
             }
             cp_async_commit();
         };

@@ -6,9 +6,9 @@ from rvv_lut_vq_b200 import ops, synth, _lib
 from prefill_bench import timed
 dev = torch.device('cuda', 0)
 Ls = [synth.make_layer_torch(4096, 11008, dev, seed=k, scales="ones") for k in range(24)]
-for batch in (16, 32, 64):
+for batch in (16, 64, 128, 256):
     x = torch.randn((batch, 4096), device=dev, dtype=torch.float16)
-    for mode in (0, 128):
+    for mode in (0,):
         _lib.lib().lutvq_debug_set_gemm_mode(mode)
         k = [0]
         def f():
