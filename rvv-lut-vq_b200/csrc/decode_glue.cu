@@ -43,6 +43,54 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const 
     for (int i = threadIdx.x; i < n; i += 1024, ++cnt) y[i] = __float2half_rn(v[cnt] * r * __half2float(w[i]));
 }
 
+// The same for n % 8 == 0, n <= 8192 (every Llama hidden size): one 16-byte load per operand and thread, all of them
+// in flight at once (the norm weights before griddepcontrol.wait: no kernel of the chain writes them), values kept
+// in registers -- the generic kernel above pays three dependent L2 round trips and a local-memory array.
+__global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps) {
+    pdl_launch_dependents();
+    __shared__ float red[32];
+    const int i0 = threadIdx.x * 8;
+    const bool act = i0 < n;
+    uint4 wv = make_uint4(0u, 0u, 0u, 0u), rv = wv, dv = wv;
+    if (act) wv = __ldg(reinterpret_cast<const uint4*>(w + i0));
+    pdl_wait();
+    if (act) {
+        rv = __ldcg(reinterpret_cast<const uint4*>(resid + i0));
+        if (delta) dv = __ldcg(reinterpret_cast<const uint4*>(delta + i0));
+    }
+    const __half* rh = reinterpret_cast<const __half*>(&rv);
+    const __half* dh = reinterpret_cast<const __half*>(&dv);
+    const __half* wh = reinterpret_cast<const __half*>(&wv);
+    float a[8], ss = 0.f;
+    #pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        a[j] = __half2float(rh[j]);
+        if (delta) a[j] = __half2float(__float2half_rn(a[j] + __half2float(dh[j])));
+        ss += a[j] * a[j];
+    }
+    if (act && delta) {
+        uint4 o;
+        __half* oh = reinterpret_cast<__half*>(&o);
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) oh[j] = __float2half_rn(a[j]);
+        *reinterpret_cast<uint4*>(resid + i0) = o;
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    float tot = 0.f;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; ++i) tot += red[i];
+    const float r = rsqrtf(tot / (float)n + eps);
+    if (act) {
+        uint4 o;
+        __half* oh = reinterpret_cast<__half*>(&o);
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) oh[j] = __float2half_rn(a[j] * r * __half2float(wh[j]));
+        *reinterpret_cast<uint4*>(y + i0) = o;
+    }
+}
+
 __global__ void silu_mul_kernel(const __half* g, const __half* u, __half* y, int n) {
     pdl_launch_dependents();
     pdl_wait();
@@ -137,6 +185,10 @@ extern "C" {
 
 int lutvq_decode_add_rmsnorm(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream) {
     LUTVQ_REQUIRE(resid && w && y && n > 0 && n <= 16384, "bad arguments (n=%d, n <= 16384)", n);
+    const bool vec8 = n % 8 == 0 && n <= 8192 && aligned16(resid) && aligned16(w) && aligned16(y) && (!delta || aligned16(delta));
+    if (vec8)
+        return launch_pdl(add_rmsnorm_vec8_kernel, dim3(1), dim3((n / 8 + 31) / 32 * 32), 0, static_cast<cudaStream_t>(stream), static_cast<__half*>(resid),
+                          static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps);
     return launch_pdl(add_rmsnorm_kernel, dim3(1), dim3(1024), 0, static_cast<cudaStream_t>(stream), static_cast<__half*>(resid),
                       static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps);
 }
