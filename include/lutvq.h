@@ -119,6 +119,17 @@ int lutvq_code2x8_matmat_group_packed(const void* x, int n, const void* const* p
                                       const void* const* scales, const void* const* bias, void* const* y, const int* prob_m,
                                       int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
 
+/* Grouped launch whose activations are computed on the fly: x[i] = fp16( silu(gate[i]) * up[i] ), the MLP activation of a
+ * Llama-shaped decoder (down_proj input), evaluated inside the kernel's x load with the arithmetic of
+ * lutvq_decode_silu_mul -- results are bit-identical to lutvq_decode_silu_mul followed by
+ * lutvq_code2x8_matmat_group_packed, one launch and one [prob_k] round trip fewer in a dependent decode chain.
+ * fp16 only; LUTVQ_FLAG_X_READY is rejected.  Not a reference entry point (the reference gets SwiGLU from HF
+ * transformers' LlamaMLP); used by the decode loop (BASELINE configs[3], [4]). */
+int lutvq_code2x8_matmat_group_packed_swiglu(const void* gate, const void* up, int n, const void* const* packed,
+                                             const void* const* codebooks, const void* const* scales,
+                                             const void* const* bias, void* const* y, const int* prob_m, int prob_k,
+                                             int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream);
+
 /* W[o][8g+j] = codebook[0][c0(o,g)][j] + codebook[1][c1(o,g)][j]   (one RN add in dtype; bit-exact class)
  * then, if scales != NULL, W[o][:] = round(W[o][:] * scales[o])     (cuda_kernel.cpp:445)
  * W dtype [prob_m][prob_k] row-major. */
@@ -188,6 +199,13 @@ int    lutvq_sharded_matmat_group_packed(lutvq_shard_t* s, int n, const int* slo
                                          const void* const* packed, const void* const* codebooks, const void* const* scales,
                                          const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
                                          void* ws, size_t ws_bytes, void* stream);
+/* the same with the SwiGLU fused into the activation load: x[i] = silu(gate[i]) * up[i] (see
+ * lutvq_code2x8_matmat_group_packed_swiglu) */
+int    lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* s, int n, const int* slots, const size_t* row_offsets,
+                                                const void* gate, const void* up, const void* const* packed,
+                                                const void* const* codebooks, const void* const* scales, const void* const* bias,
+                                                const int* rows_local, int prob_k, int dtype, unsigned flags, void* ws,
+                                                size_t ws_bytes, void* stream);
 int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
 int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);   /* all slots of the mask, one launch */
 /* software pipelining: forward + publish the slots now (non-blocking), lutvq_shard_wait[_mask] on them later only waits */

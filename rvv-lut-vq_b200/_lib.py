@@ -33,6 +33,7 @@ SIGNATURES = {
     "lutvq_code2x8_matmat_packed": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),
     "lutvq_group_workspace_bytes": (SZ, [I, P, I]),
     "lutvq_code2x8_matmat_group_packed": (I, [P, I, P, P, P, P, P, P, I, I, U, P, SZ, P]),
+    "lutvq_code2x8_matmat_group_packed_swiglu": (I, [P, P, I, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_code2x8_dequant": (I, [P, P, P, P, I, I, I, P]),
     "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_codeKx8_workspace_bytes": (SZ, [I, I, I]),
@@ -50,6 +51,7 @@ SIGNATURES = {
     "lutvq_shard_slot_bytes": (SZ, [P]),
     "lutvq_sharded_matmat_packed": (I, [P, I, SZ, P, P, P, P, P, I, I, I, U, P, SZ, P]),
     "lutvq_sharded_matmat_group_packed": (I, [P, I, P, P, P, P, P, P, P, P, I, I, U, P, SZ, P]),
+    "lutvq_sharded_matmat_group_packed_swiglu": (I, [P, I, P, P, P, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_shard_wait": (I, [P, I, P]),
     "lutvq_shard_wait_mask": (I, [P, U, P]),
     "lutvq_shard_push_mask": (I, [P, U, P]),

@@ -13,6 +13,7 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
                     cudaStream_t stream, const GemvPush* push = nullptr);
 size_t gemv_workspace_bytes(int O, int G);
 size_t gemv_group_workspace_bytes(int n, const int* O);
+void gemv_set_x_gate(const void* gate);
 int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 size_t gemv_packed_bytes(int O, int G);
@@ -189,6 +190,19 @@ int lutvq_code2x8_matmat_group_packed(const void* x, int n, const void* const* p
         items[i] = GemvItem{packed[i], codebooks[i], y[i], scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, prob_m[i]};
     }
     return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+int lutvq_code2x8_matmat_group_packed_swiglu(const void* gate, const void* up, int n, const void* const* packed,
+                                             const void* const* codebooks, const void* const* scales, const void* const* bias,
+                                             void* const* y, const int* prob_m, int prob_k, int dtype, unsigned flags, void* ws,
+                                             size_t ws_bytes, void* stream) {
+    LUTVQ_REQUIRE(gate && up, "null gate/up pointer");
+    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(gate) & 3u) == 0, "gate must be 4-byte aligned");
+    LUTVQ_REQUIRE(dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only (dtype %d)", dtype);
+    gemv_set_x_gate(gate);
+    const int rc = lutvq_code2x8_matmat_group_packed(up, n, packed, codebooks, scales, bias, y, prob_m, prob_k, dtype, flags, ws, ws_bytes, stream);
+    gemv_set_x_gate(nullptr);
+    return rc;
 }
 
 int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,

@@ -65,6 +65,16 @@ constexpr int kRangeTable = 160;              // workers whose item ranges ride 
 constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
 
 // One linear layer of a (possibly grouped) launch.  Every worker (CTA) belongs to exactly one problem.
+// two fp16 lanes of silu(g) * u, rounded once: the arithmetic of decode_glue.cu silu_mul_kernel, bit for bit
+__device__ __forceinline__ uint32_t silu_mul_halves(uint32_t g, uint32_t u) {
+    const __half2 gh = *reinterpret_cast<const __half2*>(&g), uh = *reinterpret_cast<const __half2*>(&u);
+    const float a0 = __low2float(gh), a1 = __high2float(gh);
+    const __half r0 = __float2half_rn(a0 / (1.f + __expf(-a0)) * __low2float(uh));
+    const __half r1 = __float2half_rn(a1 / (1.f + __expf(-a1)) * __high2float(uh));
+    const __half2 r = __halves2half2(r0, r1);
+    return *reinterpret_cast<const uint32_t*>(&r);
+}
+
 struct GemvProblem {
     const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
     const void* codebook;     // [2][256][8]
@@ -79,6 +89,7 @@ struct GemvParams {
     GemvProblem prob[kMaxProblems];
     int n_prob;
     const void* x;            // [I], shared by the problems of a group
+    const void* x_gate;       // fp16 only, or null: the activations are silu(x_gate[i]) * x[i] (SwiGLU fused into the x load)
     int G, n_k;
     unsigned flags;
     // ---- output-channel-sharded decode (shard.cu): besides y, every finished row is stored into each peer's gather
@@ -326,7 +337,10 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     }
     if (warp == NW - 1) {
         if (lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
+        {
             l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * 512 + lane * 128);
+            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * 512 + lane * 128);
+        }
     }
     TL_STAMP(10);
     const int r = lane >> 2, q = lane & 3;
@@ -428,6 +442,8 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             for (int j = 0; j < 4; ++j) {
                 const int g = ks * 32 + build_group_of_col(j, r);
                 bfrag[j] = (g < p.G) ? ldcg_u32(x32 + g * 4 + q) : 0u;   // L2-coherent: x may be the previous kernel's output
+                if (DT == LUTVQ_F16 && p.x_gate != nullptr && g < p.G)
+                    bfrag[j] = silu_mul_halves(ldcg_u32(static_cast<const uint32_t*>(p.x_gate) + g * 4 + q), bfrag[j]);
             }
             {   // the warp's 32 lanes x 4 words are exactly the slice's 256 activations
                 uint32_t m = max(max(absmax_halves(bfrag[0]), absmax_halves(bfrag[1])), max(absmax_halves(bfrag[2]), absmax_halves(bfrag[3])));
@@ -749,6 +765,11 @@ size_t gemv_group_workspace_bytes(int n, const int* O) {
     return b;
 }
 
+// The next launch of this thread reads its activations as silu(gate) * x (fp16): set by the *_swiglu entry points right
+// before they call the ordinary launch path, consumed (and cleared) by gemv_2x8_launch_group.
+static thread_local const void* t_x_gate = nullptr;
+void gemv_set_x_gate(const void* gate) { t_x_gate = gate; }
+
 // n linears that share x (and prob_k) in ONE launch: y_i = epilogue_i(W_i(codes_i) . x).  The workers (one CTA per SM)
 // are dealt to the problems in proportion to their rows; each problem is then planned exactly like a single GEMV on
 // its share of the SMs.  Validation is done by the caller (api.cu / shard.cu).
@@ -768,6 +789,8 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* 
     LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
     GemvParams p;
     p.n_prob = n; p.x = x; p.G = G;
+    p.x_gate = t_x_gate; t_x_gate = nullptr;
+    LUTVQ_REQUIRE(p.x_gate == nullptr || (dtype == LUTVQ_F16 && !(flags & LUTVQ_FLAG_X_READY)), "the fused SwiGLU input is fp16 only and never X_READY");
     p.has_table = 0;
     int W_total = 0, left = di.sm_count;
     uint8_t* accp = static_cast<uint8_t*>(ws) + kWsHeaderBytes;

@@ -27,6 +27,7 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push);
 
+void gemv_set_x_gate(const void* gate);
 int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 
@@ -347,6 +348,20 @@ int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots,
         s->pending[slot].pushed = 0;
     }
     return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+int lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* gate,
+                                             const void* up, const void* const* packed, const void* const* codebooks,
+                                             const void* const* scales, const void* const* bias, const int* rows_local, int prob_k,
+                                             int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
+    LUTVQ_REQUIRE(gate && up, "null gate/up pointer");
+    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(gate) & 3u) == 0, "gate must be 4-byte aligned");
+    LUTVQ_REQUIRE(dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only (dtype %d)", dtype);
+    gemv_set_x_gate(gate);
+    const int rc = lutvq_sharded_matmat_group_packed(h, n, slots, row_offsets, up, packed, codebooks, scales, bias, rows_local, prob_k,
+                                                     dtype, flags, ws, ws_bytes, stream);
+    gemv_set_x_gate(nullptr);
+    return rc;
 }
 
 int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {

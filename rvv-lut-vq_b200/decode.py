@@ -70,9 +70,10 @@ class _Linear:
 
 class Decoder:
     def __init__(self, cfg: DecoderConfig, device, world: int = 1, rank: int = 0, group: Optional[ShardGroup] = None,
-                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True):
+                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True, fuse_swiglu: bool = True):
         self.cfg, self.dev, self.world, self.rank, self.group, self.max_seq = cfg, torch.device(device), world, rank, group, max_seq
         self.exchange, self.pg, self.grouped = exchange, pg, grouped
+        self.fuse_swiglu = fuse_swiglu and grouped and not (world > 1 and exchange == "nccl")
         if world > 1 and exchange == "push":
             assert group is not None
         self.lib = _lib.lib()
@@ -157,7 +158,7 @@ class Decoder:
             _lib.check(self.lib.lutvq_shard_wait(self.group._h, slot, self._st()))
             self.launches_per_token += 1
 
-    def _group_gemv(self, L, names, x):
+    def _group_gemv(self, L, names, x, gate=None):
         """the linears that share an input go out as ONE grouped launch (lutvq_*_matmat_group_packed) and, when sharded,
         ONE exchange launch.  None of this may use LUTVQ_FLAG_X_READY: under programmatic dependent launch the kernel
         after an X_READY kernel can start before the kernel that PRODUCED x (two launches back) has finished, so the
@@ -180,17 +181,23 @@ class Decoder:
         if self.world == 1:
             outs = [self.bufs[k] for k in names]
             pm = (ctypes.c_int * n)(*[l.out_f for l in lins])
-            _lib.check(self.lib.lutvq_code2x8_matmat_group_packed(P(x), n, arr([l.packed for l in lins]), arr([l.codebooks for l in lins]),
-                                                                  arr([l.scales for l in lins]), arr([None] * n), arr(outs), pm, lins[0].in_f, 0, 0,
-                                                                  self._next_ws(), self.ws_need, self._st()))
+            tail = (n, arr([l.packed for l in lins]), arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n),
+                    arr(outs), pm, lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st())
+            if gate is None:
+                _lib.check(self.lib.lutvq_code2x8_matmat_group_packed(P(x), *tail))
+            else:                                             # x = silu(gate) * up inside the kernel's activation load
+                _lib.check(self.lib.lutvq_code2x8_matmat_group_packed_swiglu(P(gate), P(x), *tail))
             return outs
         slots = [self.group.next_slot() for _ in names]
         sl = (ctypes.c_int * n)(*slots)
         ro = (ctypes.c_size_t * n)(*[l.begin for l in lins])
         rl = (ctypes.c_int * n)(*[l.rows for l in lins])
-        _lib.check(self.lib.lutvq_sharded_matmat_group_packed(self.group._h, n, sl, ro, P(x), arr([l.packed for l in lins]),
-                                                              arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n), rl,
-                                                              lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st()))
+        tail = (arr([l.packed for l in lins]), arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n), rl,
+                lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st())
+        if gate is None:
+            _lib.check(self.lib.lutvq_sharded_matmat_group_packed(self.group._h, n, sl, ro, P(x), *tail))
+        else:
+            _lib.check(self.lib.lutvq_sharded_matmat_group_packed_swiglu(self.group._h, n, sl, ro, P(gate), P(x), *tail))
         mask = 0
         for s_ in slots:
             mask |= 1 << s_
@@ -212,9 +219,13 @@ class Decoder:
             (o,) = self._group_gemv(L, ["o"], self.attn_out)
             _lib.check(lib.lutvq_decode_add_rmsnorm(P(self.resid), P(o), P(L["norm2"]), P(self.normed), cfg.hidden, cfg.eps, st()))
             gate, up = self._group_gemv(L, ["gate", "up"], self.normed)
-            _lib.check(lib.lutvq_decode_silu_mul(P(gate), P(up), P(self.act), cfg.intermediate, st()))
-            (delta,) = self._group_gemv(L, ["down"], self.act)
-            self.launches_per_token += 4
+            if self.fuse_swiglu:                              # SwiGLU inside down_proj's activation load: one launch fewer
+                (delta,) = self._group_gemv(L, ["down"], up, gate=gate)
+                self.launches_per_token += 3
+            else:
+                _lib.check(lib.lutvq_decode_silu_mul(P(gate), P(up), P(self.act), cfg.intermediate, st()))
+                (delta,) = self._group_gemv(L, ["down"], self.act)
+                self.launches_per_token += 4
         _lib.check(lib.lutvq_decode_add_rmsnorm(P(self.resid), P(delta), P(self.final_norm), P(self.normed), cfg.hidden, cfg.eps, st()))
         torch.mv(self.lm_head, self.normed, out=self.logits)
         self.token.copy_(torch.argmax(self.logits).reshape(1))

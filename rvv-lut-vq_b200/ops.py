@@ -226,9 +226,10 @@ def vq_dequantize(codebook: torch.Tensor, codeword: torch.Tensor, M: int) -> tor
 
 def code2x8_matmat_group_packed(input: torch.Tensor, packed: List[torch.Tensor], out_features: List[int], codebooks: List[torch.Tensor],
                                 scales: List[Optional[torch.Tensor]], bias: Optional[List[Optional[torch.Tensor]]] = None,
-                                out: Optional[List[torch.Tensor]] = None) -> List[torch.Tensor]:
+                                out: Optional[List[torch.Tensor]] = None, gate: Optional[torch.Tensor] = None) -> List[torch.Tensor]:
     """n <= 3 linears that read the same input row (q/k/v, gate/up) in ONE launch (lutvq_code2x8_matmat_group_packed);
-    bit-identical to n code2x8_matmat_packed calls."""
+    bit-identical to n code2x8_matmat_packed calls.  With `gate` the activations are silu(gate) * input, evaluated in
+    the kernel's activation load (lutvq_code2x8_matmat_group_packed_swiglu; fp16)."""
     dtype = check_use_bfloat16(input)
     n = len(packed)
     dev = _require_cuda(input, *packed, *codebooks)
@@ -248,8 +249,13 @@ def code2x8_matmat_group_packed(input: torch.Tensor, packed: List[torch.Tensor],
         ws = torch.zeros(max(need, 1 << 18), dtype=torch.uint8, device=dev)
         _workspaces[key] = ws
     with torch.cuda.device(dev):
-        check(lib().lutvq_code2x8_matmat_group_packed(_ptr(x), n, arr(packed), arr(cbs), arr(sc), arr(bi), arr(ys), pm, in_features, dtype, 0,
-                                                      _ptr(ws), ws.numel(), _stream(dev)))
+        tail = (n, arr(packed), arr(cbs), arr(sc), arr(bi), arr(ys), pm, in_features, dtype, 0, _ptr(ws), ws.numel(), _stream(dev))
+        if gate is None:
+            check(lib().lutvq_code2x8_matmat_group_packed(_ptr(x), *tail))
+        else:
+            g = gate.reshape(-1).contiguous()
+            assert g.numel() == in_features and g.dtype == input.dtype and g.device == x.device
+            check(lib().lutvq_code2x8_matmat_group_packed_swiglu(_ptr(g), _ptr(x), *tail))
     return ys
 
 

@@ -413,6 +413,29 @@ def test_grouped_launch_is_bit_identical(pkg, ops, I, Os):
 
 
 # ------------------------------------------------------------------ Kx8 generalisation (N = 1, 2, 4 codebooks)
+@pytest.mark.parametrize("I,O", [(11008, 4096), (1024, 96), (28672, 8192)])
+def test_fused_swiglu_input_is_bit_identical(pkg, ops, I, O):
+    """lutvq_code2x8_matmat_group_packed_swiglu == lutvq_decode_silu_mul followed by the plain grouped launch, bit for bit;
+    the activation itself against torch (fp32 silu * up, one rounding)."""
+    import ctypes
+    from rvv_lut_vq_b200 import synth, _lib
+    L = synth.make_layer_np(I, O, seed=I + O, scales="randn", bias=True)
+    codes, cb, sc, bi = cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]), cu(L["bias"])
+    packed = ops.code2x8_prepack(codes)
+    g = torch.Generator(device="cuda").manual_seed(5)
+    gate = (torch.randn(I, device="cuda", generator=g) * 2).half()
+    up = torch.randn(I, device="cuda", generator=g).half()
+    act = torch.empty_like(up)
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    _lib.check(_lib.lib().lutvq_decode_silu_mul(P(gate), P(up), P(act), I, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    ref_act = (torch.nn.functional.silu(gate.float()) * up.float())
+    assert (act.float() - ref_act).abs().max() <= 2e-3 * ref_act.abs().max()
+    want = ops.code2x8_matmat_group_packed(act, [packed], [O], [cb], [sc], [bi])[0]
+    got = ops.code2x8_matmat_group_packed(up, [packed], [O], [cb], [sc], [bi], gate=gate)[0]
+    torch.cuda.synchronize()
+    assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+
+
 @pytest.mark.parametrize("name", ["aqlm_1x8_i128_o32", "aqlm_4x8_i128_o48", "aqlm_2x8_i256_o96"])
 def test_codeKx8_vs_golden(pkg, ops, orc, golden_dir, name):
     """lutvq_codeKx8_matmat / _dequant against the fixtures generated from the reference's own numba_gemm_lut and

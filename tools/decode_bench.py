@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--tokens", type=int, default=128)
     ap.add_argument("--exchange", default="push", choices=["push", "nccl"])
     ap.add_argument("--ungrouped", action="store_true", help="one launch per linear instead of grouped q/k/v and gate/up launches")
+    ap.add_argument("--unfused-swiglu", action="store_true", help="separate silu*up launch instead of the fused down_proj activation load")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (memory-bounded experiments)")
     args = ap.parse_args()
     import torch.distributed as dist
@@ -36,7 +37,7 @@ def main():
         import dataclasses
         cfg = dataclasses.replace(cfg, n_layers=args.layers)
     group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if (world > 1 and args.exchange == "push") else None
-    dec = Decoder(cfg, dev, world, rank, group, max_seq=args.tokens + 16, exchange=args.exchange, grouped=not args.ungrouped)
+    dec = Decoder(cfg, dev, world, rank, group, max_seq=args.tokens + 16, exchange=args.exchange, grouped=not args.ungrouped, fuse_swiglu=not args.unfused_swiglu)
     st = torch.cuda.Stream()
     dec.reset(1)
     dec.capture(st)
@@ -67,7 +68,7 @@ def main():
             peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
         except Exception:
             pass
-        print(json.dumps({"metric": "decode_tok_per_s", "model": cfg.name, "layers": cfg.n_layers, "n_gpus": world, "exchange": args.exchange if world > 1 else None, "grouped_launches": not args.ungrouped,
+        print(json.dumps({"metric": "decode_tok_per_s", "model": cfg.name, "layers": cfg.n_layers, "n_gpus": world, "exchange": args.exchange if world > 1 else None, "grouped_launches": not args.ungrouped, "fused_swiglu": dec.fuse_swiglu,
                           "value": 1e6 / us_tok, "unit": "tok/s", "us_per_token": us_tok, "tokens": args.tokens, "batch": 1,
                           "launches_per_token": dec.launches_per_token, "graph": dec.graph is not None,
                           "gemv_code_stream_bytes_per_token": gemv_bytes,
