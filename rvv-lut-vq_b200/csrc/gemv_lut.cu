@@ -721,8 +721,12 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
         // Measured on B200 (X_READY ring, packed codes): 3 CTAs/SM with a 1-deep code ring wins while a row has few
         // split-k arrivals (4096x11008: 3.75 vs 4.39 us; 4096x4096: 2.39 vs 2.51 us); with many k-slices the exposed
         // atomic round trip of the shallow ring loses to 2 CTAs/SM with 2-deep rings (11008x4096: 6.08 vs 5.07 us).
+        // That is the INDEPENDENT (X_READY) ring.  A dependent chain (decode) runs one launch at a time: there the third
+        // resident CTA buys nothing, the deeper ring wins on every shape, and alternating between the two variants
+        // (different register / occupancy footprints) costs the PDL overlap: Llama-2-7B layer, 4 GEMV launches chained:
+        // 51.7 us mixed, 36.6 all 3-CTA, 31.0 all 2-CTA (tools/decode_parts.py).
         t.nw = 8;
-        if (p.n_k <= 24) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
+        if (p.n_k <= 24 && (p.flags & LUTVQ_FLAG_X_READY)) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
     }
     if (t.nw == 8 && t.pf == 1 && t.pa == 1)  return launch_variant<DT, PACKED, 8, 1, 1, 3>(p, grid, smem, stream, pdl);   // 3 CTAs / SM
     if (t.nw == 8 && t.pf == 2 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 2, 2, 2>(p, grid, smem, stream, pdl);   // 2 CTAs / SM, deeper ring
