@@ -112,13 +112,26 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __ha
                                                                      __half* kcache, __half* vcache, const int* pos_ptr, __half* out,
                                                                      int n_heads, int n_kv, int max_seq, float theta) {
     pdl_launch_dependents();
-    pdl_wait();
     extern __shared__ float sc[];                 // [max_seq] scores, then [kAttnWarps][kHeadDim] partial outputs
     float* part = sc + max_seq;
     __shared__ float qs[kHeadDim], ks[kHeadDim], vs[kHeadDim], red[kAttnWarps];
     const int h = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int kvh = h / (n_heads / n_kv);
+    // *pos and the cache rows below it were written by earlier TOKENS (complete before this token's first launch), not
+    // by a kernel this launch may overlap with: the first kPre positions of every warp are fetched before
+    // griddepcontrol.wait, i.e. while the q/k/v GEMV is still running.
     const int pos = *pos_ptr;
+    const uint2* kbase = reinterpret_cast<const uint2*>(kcache + (size_t)kvh * max_seq * kHeadDim) + lane;   // + t * 32
+    const uint2* vbase = reinterpret_cast<const uint2*>(vcache + (size_t)kvh * max_seq * kHeadDim) + lane;
+    constexpr int kPre = 16;                      // positions per warp held in registers (covers pos <= 128)
+    uint2 kpre[kPre], vpre[kPre];
+    #pragma unroll
+    for (int u = 0; u < kPre; ++u) {
+        const int t = warp + u * kAttnWarps;
+        kpre[u] = t < pos ? __ldcg(kbase + (size_t)t * 32) : make_uint2(0u, 0u);
+        vpre[u] = t < pos ? __ldcg(vbase + (size_t)t * 32) : make_uint2(0u, 0u);
+    }
+    pdl_wait();
     if (tid < kHeadDim) {
         const int d = tid, half_d = kHeadDim / 2, i = d % half_d;
         const float freq = __powf(theta, -2.f * (float)i / (float)kHeadDim);
@@ -139,14 +152,21 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __ha
     __syncthreads();
     const float scale = rsqrtf((float)kHeadDim);
     const float q0 = qs[4 * lane], q1 = qs[4 * lane + 1], q2 = qs[4 * lane + 2], q3 = qs[4 * lane + 3];
-    const uint2* kbase = reinterpret_cast<const uint2*>(kcache + (size_t)kvh * max_seq * kHeadDim) + lane;   // + t * 32
-    const uint2* vbase = reinterpret_cast<const uint2*>(vcache + (size_t)kvh * max_seq * kHeadDim) + lane;
     auto dot4 = [&](const uint2 k) {
         const float2 k0 = __half22float2(*reinterpret_cast<const __half2*>(&k.x)), k1 = __half22float2(*reinterpret_cast<const __half2*>(&k.y));
         return q0 * k0.x + q1 * k0.y + q2 * k1.x + q3 * k1.y;
     };
     float mx = -1e30f;
-    for (int t0 = warp; t0 < pos; t0 += 4 * kAttnWarps) {
+    #pragma unroll
+    for (int u = 0; u < kPre; ++u) {
+        const int t = warp + u * kAttnWarps;
+        if (t < pos) {                            // warp-uniform
+            const float s_ = warp_sum(dot4(kpre[u])) * scale;
+            if (lane == 0) sc[t] = s_;
+            mx = fmaxf(mx, s_);
+        }
+    }
+    for (int t0 = warp + kPre * kAttnWarps; t0 < pos; t0 += 4 * kAttnWarps) {
         uint2 kv[4];
         #pragma unroll
         for (int u = 0; u < 4; ++u) { const int t = t0 + u * kAttnWarps; kv[u] = t < pos ? __ldcg(kbase + (size_t)t * 32) : make_uint2(0u, 0u); }
@@ -182,7 +202,12 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __ha
         const float2 v0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x)), v1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
         acc[0] += p_ * v0.x; acc[1] += p_ * v0.y; acc[2] += p_ * v1.x; acc[3] += p_ * v1.y;
     };
-    for (int t0 = warp; t0 < pos; t0 += 4 * kAttnWarps) {
+    #pragma unroll
+    for (int u = 0; u < kPre; ++u) {
+        const int t = warp + u * kAttnWarps;
+        if (t < pos) fma4(sc[t], vpre[u]);
+    }
+    for (int t0 = warp + kPre * kAttnWarps; t0 < pos; t0 += 4 * kAttnWarps) {
         uint2 vv[4];
         #pragma unroll
         for (int u = 0; u < 4; ++u) { const int t = t0 + u * kAttnWarps; vv[u] = t < pos ? __ldcg(vbase + (size_t)t * 32) : make_uint2(0u, 0u); }

@@ -18,17 +18,17 @@ dec.reset(1)
 dec.pos.fill_(96)
 
 
-def chain(gemv=True, glue=True, which=("qkv", "o", "gu", "down")):
+def chain(gemv=True, glue=True, which=("qkv", "o", "gu", "down"), parts=("rms1", "attn", "rms2")):
     delta = None
     for L in dec.layers:
-        if glue:
+        if glue and "rms1" in parts:
             _lib.check(lib.lutvq_decode_add_rmsnorm(P(dec.resid), None if delta is None else P(delta), P(L["norm1"]), P(dec.normed), cfg.hidden, cfg.eps, sp()))
         q, k, v = dec._group_gemv(L, ["q", "k", "v"], dec.normed) if gemv and "qkv" in which else (dec.bufs["q"], dec.bufs["k"], dec.bufs["v"])
-        if glue:
+        if glue and "attn" in parts:
             _lib.check(lib.lutvq_decode_attention(P(q), P(k), P(v), P(L["kcache"]), P(L["vcache"]), P(dec.pos), P(dec.attn_out), cfg.n_heads,
                                                   cfg.n_kv_heads, cfg.head_dim, dec.max_seq, cfg.rope_theta, sp()))
         (o,) = dec._group_gemv(L, ["o"], dec.attn_out) if gemv and "o" in which else (dec.bufs["o"],)
-        if glue:
+        if glue and "rms2" in parts:
             _lib.check(lib.lutvq_decode_add_rmsnorm(P(dec.resid), P(o), P(L["norm2"]), P(dec.normed), cfg.hidden, cfg.eps, sp()))
         gate, up = dec._group_gemv(L, ["gate", "up"], dec.normed) if gemv and "gu" in which else (dec.bufs["gate"], dec.bufs["up"])
         (delta,) = dec._group_gemv(L, ["down"], up, gate=gate) if gemv and "down" in which else (dec.bufs["down"],)
@@ -57,6 +57,8 @@ out = {"model": cfg.name, "pos": 96, "unit": "us per layer",
        "full": timed(), "gemv_only": timed(glue=False), "glue_only": timed(gemv=False)}
 for w in ("qkv", "o", "gu", "down"):
     out["gemv_only_" + w] = timed(glue=False, which=(w,))
+for pp in ("rms1", "attn", "rms2"):
+    out["full_without_" + pp] = timed(parts=tuple(x for x in ("rms1", "attn", "rms2") if x != pp))
 for name, t in (("all_3cta", (8, 1, 1)), ("all_2cta", (8, 2, 2))):
     lib.lutvq_debug_set_gemv_tuning(*t)
     out["gemv_only_" + name] = timed(glue=False)
