@@ -192,3 +192,66 @@ def test_decode_loop_matches_torch_reference():
                 assert (top2[0] - top2[1]) / ref_logits[i].abs().max() < 3e-2
                 dec.token.fill_(ref_tokens[i])
     assert sum(a == b for a, b in zip(got_tokens, ref_tokens)) >= n - 2
+
+
+@pytest.mark.parametrize("pos", [0, 5, 127, 128, 129, 300])
+@pytest.mark.parametrize("n_heads,n_kv", [(8, 8), (8, 2)])
+def test_decode_attention_vs_torch(pos, n_heads, n_kv):
+    """lutvq_decode_attention (RoPE + KV append + softmax(qK^T)V) against fp32 torch at positions on both sides of the
+    128-position register prefetch window; the cache rows below pos are random, the new row must land at pos."""
+    import ctypes
+    from rvv_lut_vq_b200 import _lib
+    lib = _lib.lib()
+    hd, max_seq, theta = 128, 512, 10000.0
+    g = torch.Generator(device="cuda").manual_seed(pos * 31 + n_kv)
+    rn = lambda *s: torch.randn(*s, device="cuda", generator=g)
+    q, k, v = rn(n_heads, hd).half(), rn(n_kv, hd).half(), rn(n_kv, hd).half()
+    kc, vc = rn(n_kv, max_seq, hd).half(), rn(n_kv, max_seq, hd).half()
+    kc0, vc0 = kc.clone(), vc.clone()
+    out = torch.zeros(n_heads * hd, dtype=torch.float16, device="cuda")
+    pos_t = torch.tensor([pos], dtype=torch.int32, device="cuda")
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    torch.cuda.synchronize()
+    _lib.check(lib.lutvq_decode_attention(P(q), P(k), P(v), P(kc), P(vc), P(pos_t), P(out), n_heads, n_kv, hd, max_seq, theta,
+                                          ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    half = hd // 2
+    inv = theta ** (-2.0 * torch.arange(half, device="cuda", dtype=torch.float32) / hd)
+    c, s = torch.cos(pos * inv), torch.sin(pos * inv)
+    def rope(x):
+        a, b = x[:, :half].float(), x[:, half:].float()
+        return torch.cat([a * c - b * s, b * c + a * s], dim=1)
+    qr, kr = rope(q), rope(k).half()
+    # cache: row pos written (k rotated, v as is), every other row untouched
+    assert torch.equal(vc[:, pos], v) and (kc[:, pos].float() - kr.float()).abs().max() < 4e-3
+    keep = torch.ones(max_seq, dtype=torch.bool, device="cuda"); keep[pos] = False
+    assert torch.equal(kc[:, keep], kc0[:, keep]) and torch.equal(vc[:, keep], vc0[:, keep])
+    rep = n_heads // n_kv
+    K = kc[:, :pos + 1].float().repeat_interleave(rep, 0)               # [heads, t, hd]
+    V = vc[:, :pos + 1].float().repeat_interleave(rep, 0)
+    p = torch.softmax(torch.einsum("hd,htd->ht", qr, K) / hd ** 0.5, dim=-1)
+    want = torch.einsum("ht,htd->hd", p, V).reshape(-1)
+    err = (out.float() - want).abs().max() / want.abs().max()
+    assert err < 5e-3, f"attention off by {err:.2e} at pos {pos}"
+
+
+@pytest.mark.parametrize("n", [256, 1000, 4096, 8192, 8200])
+@pytest.mark.parametrize("with_delta", [False, True])
+def test_decode_add_rmsnorm_vs_torch(n, with_delta):
+    """lutvq_decode_add_rmsnorm: the 16-byte-per-thread kernel (n % 8 == 0, n <= 8192) and the generic one (1000, 8200)"""
+    import ctypes
+    from rvv_lut_vq_b200 import _lib
+    g = torch.Generator(device="cuda").manual_seed(n + with_delta)
+    resid = torch.randn(n, device="cuda", generator=g).half()
+    delta = torch.randn(n, device="cuda", generator=g).half() if with_delta else None
+    w = (1 + 0.1 * torch.randn(n, device="cuda", generator=g)).half()
+    y = torch.zeros(n, dtype=torch.float16, device="cuda")
+    r0 = resid.clone()
+    P = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    _lib.check(_lib.lib().lutvq_decode_add_rmsnorm(P(resid), P(delta), P(w), P(y), n, 1e-5, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    want_resid = (r0.float() + delta.float()).half() if with_delta else r0
+    assert torch.equal(resid, want_resid)                               # one rounding of the sum, in place
+    x = want_resid.float()
+    want = x * torch.rsqrt((x * x).mean() + 1e-5) * w.float()
+    assert (y.float() - want).abs().max() <= 2e-3 * want.abs().max()
