@@ -32,7 +32,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 IN_F, OUT_F = 4096, 11008           # headline shape (gate_proj), BASELINE.json metric
-NBUF = 24                           # 24 x 11.27 MB = 270 MB of codes per step (> 2x L2)
+# GEMVs per step.  One GPU: 64 = the gate_proj + up_proj launches of one Llama-2-7B decode token (32 layers x 2, all of the
+# headline shape), 64 x 11.27 MB = 721 MB of codes per step.  Sharded (N > 1): 24 (the gather-slot ring holds 24 slots),
+# 270 MB per rank and step.  Both are > 2x L2.  The step is one CUDA graph; a graph boundary costs one programmatic-
+# dependent-launch overlap (~7 us): 8 % of a 24-launch step, 3 % of a 64-launch step (measured 2835 / 2989 / 3033 GB/s
+# at 24 / 72 / 144 launches per step), so `value` is the steady-state stream plus that stated share of boundary cost.
+NBUF = int(os.environ.get("LUTVQ_BENCH_NBUF", "0")) or (64 if int(os.environ.get("WORLD_SIZE", "1")) == 1 else 24)
 METRIC = "lutvq_gemv_hbm_gbps"
 UNIT = "GB/s"
 
@@ -204,6 +209,8 @@ def main():
     GROUP = 6
     group = None
     sharded = world > 1 or args.force_shard
+    if sharded and NBUF > 24:
+        raise SystemExit("the sharded path has 24 gather slots: run --force-shard with LUTVQ_BENCH_NBUF=24")
     if sharded:
         from rvv_lut_vq_b200.sharded import ShardGroup
         group = ShardGroup.from_process_group(world * OUT_F, n_slots=NBUF) if world > 1 else ShardGroup(1, 0, OUT_F, n_slots=NBUF)
