@@ -213,6 +213,19 @@ int    lutvq_shard_push_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream)
 int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
 int    lutvq_shard_destroy(lutvq_shard_t* s);
 
+/* ---- integer LUT: lookup-and-add ----
+ * Replaces lookup_and_add_simd of benchmark/kernel/simd_lut/bench_avx_lut.cpp:26-138 with the _SCALAR_ build's semantics
+ * (:98-107):  for run < n_runs, j < n_lut_per_run, k < cb_size:  output[k] += lut[idx[j*cb_size + k]]  with int16
+ * wraparound (additions modulo 2^16: split over all SMs, any order, same bits).  idx: uint8 [n_lut_per_run][cb_size]
+ * (4-byte aligned, values < n_entries), lut: int8 [n_entries <= 256], output: int16 [cb_size] (accumulated in place),
+ * cb_size 16 / 32 / 64 (any multiple of 4 dividing 1024).  ws: lutvq_simd_lut_workspace_bytes() bytes, zero on first
+ * use, handed back zeroed.  The reference's AVX builds use SATURATING adds and differ from its own scalar build; the
+ * scalar build is the oracle (oracle/lutvq_oracle.c orc_simd_lut_scalar). */
+size_t lutvq_simd_lut_workspace_bytes(int cb_size);
+int    lutvq_simd_lut_lookup_add(const void* idx, const void* lut, void* output, int cb_size, int n_entries,
+                                 unsigned long long n_runs, unsigned long long n_lut_per_run, void* ws, size_t ws_bytes,
+                                 void* stream);
+
 /* ---- decode glue (fp16, batch 1): the non-GEMV steps of a Llama-shaped decode step, so a whole token is one chain of
  * launches of this library inside a CUDA graph.  Not reference entry points (the reference takes these from HF
  * transformers, benchmark/llm/generate_benchmark.py) and not LUT-VQ work; they exist for the decode tok/s metric.

@@ -17,6 +17,7 @@ LUT_VQPY_FP16, LUT_FP32 = 0, 1
 ACC_F64, ACC_F32 = 0, 1
 
 P, I, U, SZ = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t
+U64 = ctypes.c_ulonglong
 
 # name -> (restype, argtypes); must list every symbol include/lutvq.h declares (tests/test_abi.py checks)
 SIGNATURES = {
@@ -36,6 +37,8 @@ SIGNATURES = {
     "lutvq_code2x8_matmat_group_packed_swiglu": (I, [P, P, I, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_code2x8_dequant": (I, [P, P, P, P, I, I, I, P]),
     "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
+    "lutvq_simd_lut_workspace_bytes": (SZ, [I]),
+    "lutvq_simd_lut_lookup_add": (I, [P, P, P, I, I, U64, U64, P, SZ, P]),
     "lutvq_codeKx8_workspace_bytes": (SZ, [I, I, I]),
     "lutvq_codeKx8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, I, P, SZ, P]),
     "lutvq_codeKx8_dequant": (I, [P, P, P, P, I, I, I, I, P]),

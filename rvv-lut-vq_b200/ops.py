@@ -287,3 +287,23 @@ def codeKx8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Option
         check(lib().lutvq_codeKx8_dequant(_ptr(codes.contiguous()), _ptr(W), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)), O, G * 8, N,
                                           dtype, _stream(dev)))
     return W
+
+
+def simd_lut_lookup_add(idx: torch.Tensor, lut: torch.Tensor, output: torch.Tensor, n_runs: int) -> torch.Tensor:
+    """lookup_and_add_simd, _SCALAR_ semantics (benchmark/kernel/simd_lut/bench_avx_lut.cpp:26-138, :98-107):
+    output[k] += lut[idx[j, k]] for every row j, repeated n_runs times, int16 wraparound.  idx uint8 [n_lut_per_run, CB],
+    lut int8 [n_entries], output int16 [CB] (updated in place and returned)."""
+    dev = _require_cuda(idx, lut, output)
+    assert idx.dtype == torch.uint8 and lut.dtype == torch.int8 and output.dtype == torch.int16
+    assert idx.dim() == 2 and idx.is_contiguous() and output.is_contiguous() and output.numel() == idx.size(1)
+    cb = idx.size(1)
+    need = int(lib().lutvq_simd_lut_workspace_bytes(cb))
+    key = ("simd_lut", dev.index if dev.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(max(need, 1024), dtype=torch.uint8, device=dev)
+        _workspaces[key] = ws
+    with torch.cuda.device(dev):
+        check(lib().lutvq_simd_lut_lookup_add(_ptr(idx), _ptr(lut.contiguous()), _ptr(output), cb, lut.numel(), int(n_runs), idx.size(0),
+                                              _ptr(ws), ws.numel(), _stream(dev)))
+    return output

@@ -472,3 +472,32 @@ def test_codeKx8_vs_golden(pkg, ops, orc, golden_dir, name):
         assert torch.equal(W, ops.code2x8_dequant(cu(g["codes"]), cu(cb16), None)) if N == 2 else True
     else:
         np.testing.assert_allclose(W.float().cpu().numpy(), ref.astype(np.float32), rtol=2e-3, atol=2e-3)
+
+
+# ------------------------------------------------------------------------------------------------ integer LUT (a13)
+@pytest.mark.parametrize("cb,n_entries,n_lut,n_runs", [(16, 16, 1000, 37), (32, 16, 777, 5), (64, 64, 1000, 300), (16, 256, 10, 1)])
+def test_simd_lut_lookup_add_vs_oracle(pkg, ops, orc, cb, n_entries, n_lut, n_runs):
+    """bit-exact int16 wraparound sums against the scalar restatement (bench_avx_lut.cpp:98-107), non-zero start values"""
+    rng = np.random.default_rng(cb * n_lut + n_runs)
+    idx = rng.integers(0, n_entries, size=(n_lut, cb), dtype=np.uint8)
+    lut = ((np.arange(n_entries) * 10 + 100) & 0xFF).astype(np.uint8).view(np.int8)     # the reference's table, wrapped to int8
+    out0 = rng.integers(-30000, 30000, size=cb).astype(np.int16)
+    base = orc.c_simd_lut_scalar(idx, lut, n_runs=n_runs)                               # starts from zero
+    want = (out0.view(np.uint16).astype(np.uint32) + base.view(np.uint16).astype(np.uint32)).astype(np.uint16).view(np.int16)
+    got = ops.simd_lut_lookup_add(cu(idx), cu(lut), cu(out0.copy()), n_runs)
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), want)
+    again = ops.simd_lut_lookup_add(cu(idx), cu(lut), cu(out0.copy()), n_runs)           # workspace came back zeroed
+    assert np.array_equal(again.cpu().numpy(), want)
+
+
+def test_simd_lut_full_size_is_n_runs_times_one_run(pkg, ops, orc):
+    """the reference's own size (CB 16, 10 000 rows, 100 000 runs = 1.6e10 lookups): equals n_runs x (one oracle run) mod 2^16"""
+    rng = np.random.default_rng(3)
+    idx = rng.integers(0, 16, size=(10000, 16), dtype=np.uint8)
+    lut = ((np.arange(16) * 10 + 100) & 0xFF).astype(np.uint8).view(np.int8)
+    one = orc.c_simd_lut_scalar(idx, lut, n_runs=1).view(np.uint16).astype(np.uint64)
+    want = ((one * 100000) & 0xFFFF).astype(np.uint16).view(np.int16)
+    got = ops.simd_lut_lookup_add(cu(idx), cu(lut), torch.zeros(16, dtype=torch.int16, device="cuda"), 100000)
+    torch.cuda.synchronize()
+    assert np.array_equal(got.cpu().numpy(), want)
