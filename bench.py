@@ -206,7 +206,7 @@ def main():
     # N > 1: each rank owns an OUT_F-row shard of an (N * OUT_F)-row layer; the GEMV kernel itself pushes its rows into
     # every peer's gather slot over NVLink (lutvq_sharded_matmat_packed) and one wait kernel per group of GROUP GEMVs
     # confirms that all N slices of those slots have landed locally.
-    GROUP = 6
+    GROUP = int(os.environ.get("LUTVQ_BENCH_GROUP", "24"))      # 24 = one exchange per step (N=2: 3574 / 3791 / 4472 GB/s at 6 / 12 / 24)
     group = None
     sharded = world > 1 or args.force_shard
     if sharded and NBUF > 24:
