@@ -25,13 +25,31 @@ __global__ void __launch_bounds__(kSimdLutThreads) simd_lut_kernel(const uint32_
     unsigned a0 = 0u, a1 = 0u, a2 = 0u, a3 = 0u;
     if (r0 < rstep)                                                  // threads past the last whole row group idle
         for (unsigned long long run = blockIdx.x; run < n_runs; run += gridDim.x)
-            for (unsigned long long j = r0; j < n_rows; j += rstep) {
-                const uint32_t v = __ldg(idx32 + j * wpr + w);
+        {
+            // 4 rows per trip: the index loads of a trip are issued together, then their 16 table reads
+            const uint32_t* pidx = idx32 + w;
+            const unsigned n = (unsigned)n_rows, step = (unsigned)rstep;
+            unsigned j = (unsigned)r0;
+            for (; j + 3u * step < n; j += 4u * step) {
+                uint32_t v[4];
+                #pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = __ldg(pidx + (size_t)(j + u * step) * wpr);
+                #pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    a0 += (unsigned)s_lut[v[u] & 0xFFu];
+                    a1 += (unsigned)s_lut[(v[u] >> 8) & 0xFFu];
+                    a2 += (unsigned)s_lut[(v[u] >> 16) & 0xFFu];
+                    a3 += (unsigned)s_lut[v[u] >> 24];
+                }
+            }
+            for (; j < n; j += step) {
+                const uint32_t v = __ldg(pidx + (size_t)j * wpr);
                 a0 += (unsigned)s_lut[v & 0xFFu];
                 a1 += (unsigned)s_lut[(v >> 8) & 0xFFu];
                 a2 += (unsigned)s_lut[(v >> 16) & 0xFFu];
                 a3 += (unsigned)s_lut[v >> 24];
             }
+        }
     atomicAdd(&s_acc[4 * w + 0], a0); atomicAdd(&s_acc[4 * w + 1], a1);
     atomicAdd(&s_acc[4 * w + 2], a2); atomicAdd(&s_acc[4 * w + 3], a3);
     __syncthreads();
@@ -60,6 +78,7 @@ int lutvq_simd_lut_lookup_add(const void* idx, const void* lut, void* output, in
     LUTVQ_REQUIRE(cb_size > 0 && cb_size <= 256 && cb_size % 4 == 0 && kSimdLutThreads % (cb_size / 4) == 0,
                   "cb_size=%d must be a multiple of 4 that divides 1024 (16 / 32 / 64 in the reference)", cb_size);
     LUTVQ_REQUIRE(n_entries > 0 && n_entries <= 256, "n_entries=%d must be in 1..256", n_entries);
+    LUTVQ_REQUIRE(n_lut_per_run < (1ull << 31), "n_lut_per_run must be below 2^31");
     LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(idx) & 3u) == 0, "idx must be 4-byte aligned");
     LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= lutvq_simd_lut_workspace_bytes(cb_size) && (reinterpret_cast<uintptr_t>(ws) & 3u) == 0,
                   "workspace too small or misaligned (zero-initialised, %zu bytes)", lutvq_simd_lut_workspace_bytes(cb_size));
