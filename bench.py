@@ -5,15 +5,17 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 Workload (N=1, BASELINE configs[1]): Llama-2-7B gate_proj shape 4096->11008, AQLM 2x8 codes, batch 1.
-One STEP = one LUT-GEMV over each of NBUF distinct layers (random codes/codebooks/scales), whose code
-matrices total > 2x the 126 MB L2, so every launch streams its codes from HBM (L2-cold by construction).
+One STEP = one LUT-GEMV over each of NBUF distinct layers (random codes/codebooks/scales; NBUF = 64 on one GPU = the
+gate/up projections of one Llama-2-7B token, 24 per rank when sharded), whose code matrices total > 2x the 126 MB L2,
+so every launch streams its codes from HBM (L2-cold by construction).
   value   whole-job GB/s on the algorithmic byte stream (O*(I/8)*2 + 8192 + 2I + 4O per GEMV),
           inputs resident in HBM, the NBUF launches replayed as one CUDA graph, timed with CUDA events;
   e2e     the same metric through the reference-facing op (ops.code2x8_matmat) with HOST buffers: per GEMV the
           activation row is copied from pinned host memory and the output row copied back, inside the timed region;
   roofline / cpu_baseline / clocks / sweep: see DESIGN.md "Measurement".
 N>1 (torchrun, one rank per GPU): the layer is sharded by OUTPUT CHANNEL (each rank owns an 11008-row shard of
-an N*11008-row layer) and every GEMV is followed by the all-gather of output slices (weak scaling).
+an N*11008-row layer), every GEMV's output slice is all-gathered into every rank's gather slot by the push exchange
+(one exchange launch per step of 24 independent GEMVs by default, LUTVQ_BENCH_GROUP; weak scaling).
 --impl reference: the reference's CPU LUT-GEMV (oracle port of numba_gemv_lut_, all host threads) on the same config.
 """
 from __future__ import annotations
