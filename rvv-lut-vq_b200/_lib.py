@@ -66,6 +66,7 @@ SIGNATURES = {
 }
 DEBUG_SIGNATURES = {
     "lutvq_debug_set_gemv_tuning": (None, [I, I, I]),
+    "lutvq_debug_set_dependent_workers": (None, [I]),
     "lutvq_debug_get_gemv_plan": (None, [I, I, P, P, P]),
     "lutvq_debug_set_gemm_mode": (None, [I]),
 }
@@ -99,6 +100,8 @@ def lib() -> ctypes.CDLL:
             for name, (res, args) in table.items():
                 fn = getattr(_lib, name)
                 fn.restype, fn.argtypes = res, args
+        if os.environ.get("LUTVQ_DEP_WORKERS"):          # experiment switch: workers per SM of a dependent GEMV launch
+            _lib.lutvq_debug_set_dependent_workers(int(os.environ["LUTVQ_DEP_WORKERS"]))
     return _lib
 
 

@@ -14,6 +14,7 @@ int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const
 size_t gemv_workspace_bytes(int O, int G);
 size_t gemv_group_workspace_bytes(int n, const int* O);
 void gemv_set_x_gate(const void* gate);
+void gemv_set_dependent_workers(int m);
 int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 size_t gemv_packed_bytes(int O, int G);
@@ -255,6 +256,7 @@ int lutvq_vq_dequantize(const void* codebook, const void* codeword, void* W, int
 // ---- not part of the public header: tuning hooks used by bench.py's sweep and the tests ----
 void lutvq_debug_set_gemv_tuning(int nw, int pf, int pa) { gemv_set_tuning(nw, pf, pa); }
 void lutvq_debug_set_timeline(void* buf) { gemv_set_timeline(buf); }
+void lutvq_debug_set_dependent_workers(int per_sm) { gemv_set_dependent_workers(per_sm); }
 void lutvq_debug_set_gemm_mode(int m) { gemm_set_debug_mode(m); }
 void lutvq_debug_get_gemv_plan(int prob_m, int prob_k, int* n_k, int* n_chunks, int* rows_per_chunk) {
     gemv_get_plan(prob_m, prob_k, n_k, n_chunks, rows_per_chunk);

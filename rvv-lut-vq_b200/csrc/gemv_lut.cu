@@ -60,7 +60,7 @@ namespace lutvq {
 constexpr size_t kWsHeaderBytes = 256;        // reserved
 
 constexpr int kMaxPeers = 8;                  // one NVSwitch domain
-constexpr int kRangeTable = 160;              // workers whose item ranges ride in the kernel parameters (B200: 148)
+constexpr int kRangeTable = 320;              // workers whose item ranges ride in the kernel parameters (B200: 148 or 2 x 148)
 
 constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
 
@@ -637,6 +637,8 @@ __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __r
 // ---------------------------------------------------------------------------------------------------
 struct GemvTuning { int nw = 0, pf = 0, pa = 0; };   // 0 = choose per shape (launch_tuned)
 static GemvTuning g_tuning;
+static int g_dep_workers_per_sm = 2;   // workers (CTAs) per SM of a DEPENDENT launch, see gemv_2x8_launch_group
+void gemv_set_dependent_workers(int m) { g_dep_workers_per_sm = m < 1 ? 1 : (m > 2 ? 2 : m); }
 static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][8] stamps
 static unsigned g_timeline_seq = 0;
 void gemv_set_timeline(void* buf) { g_timeline = static_cast<unsigned long long*>(buf); g_timeline_seq = 0; }
@@ -782,7 +784,10 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* 
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
     LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
-    LUTVQ_REQUIRE(n == 1 || di.sm_count <= kRangeTable, "grouped launches need the tabulated plan (<= %d SMs)", kRangeTable);
+    // An independent (X_READY) ring fills the SMs by overlapping consecutive launches, one worker per SM each.  A dependent
+    // launch runs alone: it may be planned over g_dep_workers_per_sm workers per SM (2 fit with the 2-CTA variant).
+    const int workers = di.sm_count * ((flags & LUTVQ_FLAG_X_READY) ? 1 : g_dep_workers_per_sm);
+    LUTVQ_REQUIRE(n == 1 || workers <= kRangeTable, "grouped launches need the tabulated plan (<= %d workers)", kRangeTable);
     LUTVQ_REQUIRE(n == 1 || push == nullptr, "the fused push epilogue takes one linear per launch");
     const int G = I / 8;
     int Os[kMaxProblems];
@@ -796,13 +801,13 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* 
     p.x_gate = t_x_gate; t_x_gate = nullptr;
     LUTVQ_REQUIRE(p.x_gate == nullptr || (dtype == LUTVQ_F16 && !(flags & LUTVQ_FLAG_X_READY)), "the fused SwiGLU input is fp16 only and never X_READY");
     p.has_table = 0;
-    int W_total = 0, left = di.sm_count;
+    int W_total = 0, left = workers;
     uint8_t* accp = static_cast<uint8_t*>(ws) + kWsHeaderBytes;
     for (int i = 0; i < kMaxProblems; ++i) p.prob[i] = GemvProblem{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
     for (int i = 0; i < n; ++i) {
         // SM share of problem i: proportional to its row sets, at least one, the last problem takes the remainder
         const int n_sets_i = ceil_div(items[i].O, kSetRows);
-        int share = (i == n - 1) ? left : (int)((long long)di.sm_count * n_sets_i / sets_total);
+        int share = (i == n - 1) ? left : (int)((long long)workers * n_sets_i / sets_total);
         if (share < 1) share = 1;
         if (share > left - (n - 1 - i)) share = left - (n - 1 - i);
         left -= share;
@@ -840,7 +845,7 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* 
     }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
-    p.tl = g_timeline ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
+    p.tl = (g_timeline && W_total <= 256) ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
     const size_t smem = kSliceBytes;
     if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, W_total, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, W_total, smem, stream, pdl);
     if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, W_total, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, W_total, smem, stream, pdl);
