@@ -200,7 +200,7 @@ def main():
     # prepacked code images (what QuantizedLinear builds on first use) and a ring of workspaces: the NBUF GEMVs of a
     # step are independent (resident inputs), so they are issued with LUTVQ_FLAG_X_READY and overlap on the GPU
     packed = [ops.code2x8_prepack(L["codes"]) for L in layers]
-    ws_need = (int(lib.lutvq_workspace_bytes(OUT_F, IN_F)) + 255) // 256 * 256
+    ws_need = (int(lib.lutvq_packed_workspace_bytes(OUT_F, IN_F)) + 255) // 256 * 256
     ws_ring = torch.zeros(ops.XREADY_WS_RING * ws_need, dtype=torch.uint8, device=dev)
     assert NBUF % ops.XREADY_WS_RING == 0
     FLAGS = {"x_ready": pkg._lib.FLAG_X_READY, "dependent": 0}
@@ -369,7 +369,7 @@ def main():
                 yv = torch.empty((nb, 1, o_f), device=dev, dtype=torch.float16)
 
                 pk = [ops.code2x8_prepack(L["codes"]) for L in Ls]
-                need = (int(lib.lutvq_workspace_bytes(o_f, i_f)) + 255) // 256 * 256
+                need = (int(lib.lutvq_packed_workspace_bytes(o_f, i_f)) + 255) // 256 * 256
                 ring = torch.zeros(ops.XREADY_WS_RING * need, dtype=torch.uint8, device=dev)
 
                 def body(flags):

@@ -24,8 +24,10 @@
  *   - returns 0 on success, a negative LUTVQ_E* code otherwise; lutvq_last_error() gives a thread-local
  *     message.  There is no CPU fallback: without a CUDA device every compute call fails with LUTVQ_ECUDA;
  *   - scratch memory is passed in (ws, ws_bytes); size it with lutvq_workspace_bytes().  A workspace must
- *     be zero-filled once before first use (cudaMemset); every call leaves it all-zero again, so it may be reused
- *     by any later call ON THE SAME STREAM (any shape);
+ *     be zero-filled once before first use (cudaMemset); every call leaves its first lutvq_packed_workspace_bytes()
+ *     bytes (the split-k words) all-zero again, so it may be reused by any later call ON THE SAME STREAM (any shape).
+ *     The rest is a staging area that only the reference-layout entry points use (they re-lay the codes into the
+ *     packed image first; callers that prepack once at load time never touch it and may pass the small size);
  *   - dtype is the storage/arithmetic type of x, codebooks, scales, bias, y (fp16 or bf16, the two types
  *     cuda_kernel.cpp:9-25 accepts).  Codes are int8 holding unsigned 8-bit indices
  *     (aqlm/../utils.py:24-31), layout [prob_m][prob_k/8][num_codebooks] exactly as QuantizedLinear.codes.
@@ -76,17 +78,24 @@ int         lutvq_version(void);                     /* 10000*major + 100*minor 
 /* fills what the launch heuristics see; any pointer may be NULL */
 int         lutvq_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin_bytes);
 
-/* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch). */
+/* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch), including the staging
+ * area of the reference-layout entry points (about prob_m * prob_k / 4 bytes). */
 size_t lutvq_workspace_bytes(int prob_m, int prob_k);
+/* Scratch needed by the *_packed / group / sharded entry points: the split-k words only (8 bytes per output row + 256). */
+size_t lutvq_packed_workspace_bytes(int prob_m, int prob_k);
 /* Same, when the caller knows its largest batch: batch <= 6 only ever needs the (small) GEMV scratch. */
 size_t lutvq_workspace_bytes_ex(int prob_m, int prob_k, int max_batch);
 
 /* y[prob_m] = W(codes, codebook) . x[prob_k]            (no scale, like Code2x8MatVec)
  * codes    int8  [prob_m][prob_k/8][2]   (16-byte aligned rows: prob_k % 64 == 0, as the reference requires)
- * x        dtype [prob_k]
+ * x        dtype [prob_k]                 (16-byte aligned: Code2x8MatVec reads it as int4 too, cuda_kernel.cu:147)
  * y        dtype [prob_m]
  * codebook dtype [2][256][8]
- * Arithmetic: fp32 LUT built with tensor-core MMAs, fp32 gather-accumulate, one rounding to dtype. */
+ * Arithmetic: LUT entries L = C . x_group from tensor-core MMAs (fp32 accumulate), stored as 16-bit fixed point with ONE
+ * scale per GEMV (step = max_k|C_k|_2 * max_g|x_g|_2 / 32704, finer than the fp16 LUT of vq.py:285); the gather adds
+ * integers (exact, order-free => bit-reproducible); one rounding to dtype.  Tolerance (tests): max|y - y64| <= 1e-3 *
+ * max|y64| against the float64 evaluation of the same operands.  prob_k <= 32256 (63 k-slices of 512 activations).
+ * Non-finite activations or codebooks make EVERY output NaN (the reference propagates them row by row). */
 int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* codebook,
                          int prob_m, int prob_k, int dtype, void* ws, size_t ws_bytes, void* stream);
 
@@ -101,9 +110,11 @@ int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebo
 
 /* Optional load-time re-layout of the codes for the GEMV (the reference does the same kind of one-off permutation
  * for its CPU kernel in QuantizedLinear.prepare_matmul_op, aqlm/../inference.py:78-83).  The packed image holds the
- * same code bytes, ordered [k-slice of 64 code bytes][32-row set][8-row tile][lane] x 16 B so that every warp load
- * is 512 contiguous bytes; rows / k-slices are zero-padded to whole sets (lutvq_code2x8_packed_bytes >= prob_m*prob_k/4).
- * lutvq_code2x8_matmat_packed == lutvq_code2x8_matmat_ex on the packed image (bit-identical results). */
+ * same code bytes, ordered [k-slice of 128 code bytes][32-row set][8-row tile][half][lane] x 16 B in the order each lane
+ * walks them (rvv-lut-vq_b200/csrc/lut_layout.h), so that a worker's share is ONE contiguous range streamed by 1-D bulk
+ * async copies; rows / k-slices are zero-padded to whole sets (lutvq_code2x8_packed_bytes >= prob_m*prob_k/4).
+ * lutvq_code2x8_matmat_packed == lutvq_code2x8_matmat_ex on the packed image (bit-identical results; the reference-layout
+ * entry points run this very re-layout into the workspace's staging area on every call). */
 size_t lutvq_code2x8_packed_bytes(int prob_m, int prob_k);
 int lutvq_code2x8_prepack(const void* codes, void* packed, int prob_m, int prob_k, void* stream);
 int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* codebooks, const void* scales,

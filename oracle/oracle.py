@@ -62,6 +62,12 @@ def lib() -> ctypes.CDLL:
             "orc_unpack_codes": [P, ctypes.c_size_t, P],
             "orc_simd_lut_scalar": [P, P, P, I, U64, U64],
             "orc_set_num_threads": [I],
+            "orc_tbl_g4_int8_int32_update": [I, P, P, P, I],
+            "orc_tbl_g4_int8_float_update": [I, P, P, P, P, P, P, I, I, I, I, I],
+            "orc_partial_max_g4_int8_k8": [P, P],
+            "orc_lut_ctor_g4_int8": [I, P, P, P, P],
+            "orc_tmac_preprocessor_int8": [I, P, P, P, P],
+            "orc_tmac_qgemm_lut_int8": [I, I, I, I, P, P, P, P, P, P],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)
@@ -318,9 +324,72 @@ def c_scale_bias_epilogue(y_bits: np.ndarray, scales_bits, bias_bits, dtype: int
     return y
 
 
-def c_simd_lut_scalar(idx_u8: np.ndarray, lut_i8: np.ndarray, n_runs: int) -> np.ndarray:
-    """bench_avx_lut.cpp:98-107 scalar semantics.  idx [n_lut_per_run, CB] uint8; returns int16[CB]."""
+def c_simd_lut_scalar(idx_u8: np.ndarray, lut_i8: np.ndarray, n_runs: int, out0: Optional[np.ndarray] = None) -> np.ndarray:
+    """bench_avx_lut.cpp:98-107 scalar semantics.  idx [n_lut_per_run, CB] uint8; returns int16[CB] (accumulated onto out0)."""
     n_lut, cb = idx_u8.shape
-    out = np.zeros(cb, dtype=np.int16)
+    out = np.zeros(cb, dtype=np.int16) if out0 is None else np.ascontiguousarray(out0, dtype=np.int16).copy()
     lib().orc_simd_lut_scalar(_p(np.ascontiguousarray(idx_u8)), _p(np.ascontiguousarray(lut_i8)), _p(out), cb, n_runs, n_lut)
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# T-MAC bit-serial integer-LUT kernels (tmac_oracle.c; reference benchmark/kernel/bs_lut_gemm/{tbl,lut_ctor}.cc)
+# --------------------------------------------------------------------------------------------
+def c_tbl_g4_int8_int32_update(m: int, c_i32: np.ndarray, lut_i8: np.ndarray, a_u8: np.ndarray, K: int) -> np.ndarray:
+    """tbl.cc:586-627; returns the updated copy of c"""
+    c = np.ascontiguousarray(c_i32, dtype=np.int32).copy()
+    lib().orc_tbl_g4_int8_int32_update(m, _p(c), _p(np.ascontiguousarray(lut_i8, dtype=np.int8)), _p(np.ascontiguousarray(a_u8, dtype=np.uint8)), K)
+    return c
+
+
+def c_tbl_g4_int8_float_update(m, c_f32, lut_i8, a_u8, scales, lut_scales, lut_biases, K, bits, act_k, fast_aggregation=False, zero_point=False):
+    """tbl.cc:433-520; returns the updated copy of c"""
+    c = np.ascontiguousarray(c_f32, dtype=np.float32).copy()
+    f = lambda v: np.ascontiguousarray(v, dtype=np.float32)
+    lib().orc_tbl_g4_int8_float_update(m, _p(c), _p(np.ascontiguousarray(lut_i8, dtype=np.int8)), _p(np.ascontiguousarray(a_u8, dtype=np.uint8)),
+                                       _p(f(scales)), _p(f(lut_scales)), _p(f(lut_biases)), K, bits, act_k, int(fast_aggregation), int(zero_point))
+    return c
+
+
+def c_partial_max_g4_int8_k8(lut_scale: float, b_f32: np.ndarray) -> float:
+    """lut_ctor.cc:232-259"""
+    s = np.array([lut_scale], dtype=np.float32)
+    lib().orc_partial_max_g4_int8_k8(_p(s), _p(np.ascontiguousarray(b_f32, dtype=np.float32)))
+    return float(s[0])
+
+
+def c_lut_ctor_g4_int8(act_k: int, b_f32: np.ndarray, lut_scale: float):
+    """lut_ctor.cc:120-216 -> (qlut int8 [act_k/32 * 8][16], lut_scales, lut_biases)"""
+    qlut = np.zeros((act_k // 32 * 8, 16), dtype=np.int8)
+    s, bi = np.array([lut_scale], dtype=np.float32), np.zeros(1, dtype=np.float32)
+    lib().orc_lut_ctor_g4_int8(act_k, _p(qlut), _p(np.ascontiguousarray(b_f32, dtype=np.float32)), _p(s), _p(bi))
+    return qlut, float(s[0]), float(bi[0])
+
+
+def c_tmac_preprocessor_int8(B_f32: np.ndarray):
+    """T-MAC deploy/tuned/kernels.cc:1002-1037 -> (qlut int8 [K/4][16], lut_scales [K/32], lut_biases [K/32])"""
+    K = B_f32.shape[0]
+    qlut = np.zeros((K // 4, 16), dtype=np.int8)
+    ls, lb = np.zeros(K // 32, dtype=np.float32), np.zeros(K // 32, dtype=np.float32)
+    lib().orc_tmac_preprocessor_int8(K, _p(np.ascontiguousarray(B_f32, dtype=np.float32)), _p(ls), _p(lb), _p(qlut))
+    return qlut, ls, lb
+
+
+def c_tmac_qgemm_lut_int8(M: int, K: int, bits: int, bm: int, A_u8, qlut_i8, scales, lut_scales, lut_biases) -> np.ndarray:
+    """T-MAC deploy/tuned/kernels.cc:827-960 (float_type = float), all m tiles"""
+    C = np.zeros(M, dtype=np.float32)
+    f = lambda v: np.ascontiguousarray(v, dtype=np.float32)
+    lib().orc_tmac_qgemm_lut_int8(M, K, bits, bm, _p(np.ascontiguousarray(A_u8, dtype=np.uint8)), _p(np.ascontiguousarray(qlut_i8, dtype=np.int8)),
+                                  _p(f(scales)), _p(f(lut_scales)), _p(f(lut_biases)), _p(C))
+    return C
+
+
+# ---- the reference's own compiled kernels (oracle/_ref, built by `make -C oracle ref` where /root/reference exists) ----
+def ref_tmac():
+    path = os.path.join(_HERE, "_ref", "libtmac_ref.so")
+    return ctypes.CDLL(path) if os.path.exists(path) else None
+
+
+def ref_simd_lut():
+    path = os.path.join(_HERE, "_ref", "libsimdlut_ref.so")
+    return ctypes.CDLL(path) if os.path.exists(path) else None

@@ -19,13 +19,14 @@ ACC_F64, ACC_F32 = 0, 1
 P, I, U, SZ = ctypes.c_void_p, ctypes.c_int, ctypes.c_uint, ctypes.c_size_t
 U64 = ctypes.c_ulonglong
 
-# name -> (restype, argtypes); must list every symbol include/lutvq.h declares (tests/test_abi.py checks)
+# name -> (restype, argtypes); must list every symbol include/lutvq.h declares (tests/test_host_logic.py checks)
 SIGNATURES = {
     "lutvq_last_error": (ctypes.c_char_p, []),
     "lutvq_version": (I, []),
     "lutvq_device_info": (I, [P, P, P, P]),
     "lutvq_workspace_bytes": (SZ, [I, I]),
     "lutvq_workspace_bytes_ex": (SZ, [I, I, I]),
+    "lutvq_packed_workspace_bytes": (SZ, [I, I]),
     "lutvq_code2x8_matvec": (I, [P, P, P, P, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_code2x8_matmat_ex": (I, [P, P, P, P, P, P, I, I, I, I, U, P, SZ, P]),

@@ -8,14 +8,15 @@
 namespace lutvq {
 
 // launchers (gemv_lut.cu, dequant.cu, vq_golden.cu, gemm_tc.cu)
-int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
+int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push = nullptr);
+int gemv_stage_codes(const void* codes, int O, int I, void* ws, size_t ws_bytes, cudaStream_t stream, const void** staged, size_t* small_bytes);
 size_t gemv_workspace_bytes(int O, int G);
+size_t gemv_packed_workspace_bytes(int O, int G);
 size_t gemv_group_workspace_bytes(int n, const int* O);
-void gemv_set_x_gate(const void* gate);
 void gemv_set_dependent_workers(int m);
-int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
+int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 size_t gemv_packed_bytes(int O, int G);
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);
@@ -110,6 +111,11 @@ size_t lutvq_workspace_bytes(int prob_m, int prob_k) {
     return a > b ? a : b;
 }
 
+size_t lutvq_packed_workspace_bytes(int prob_m, int prob_k) {
+    if (prob_m <= 0 || prob_k <= 0) return 0;
+    return gemv_packed_workspace_bytes(prob_m, prob_k / 8);
+}
+
 size_t lutvq_workspace_bytes_ex(int prob_m, int prob_k, int max_batch) {
     if (prob_m <= 0 || prob_k <= 0) return 0;
     size_t a = gemv_workspace_bytes(prob_m, prob_k / 8);
@@ -121,8 +127,10 @@ int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* 
                          int dtype, void* ws, size_t ws_bytes, void* stream) {
     if (int rc = check_2x8_common(codes, codebook, prob_m, prob_k, dtype)) return rc;
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
-    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
-    return gemv_2x8_launch(codes, 0, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, 0u, ws, ws_bytes,
+    const void* staged = nullptr;
+    size_t small = 0;
+    if (int rc = gemv_stage_codes(codes, prob_m, prob_k, ws, ws_bytes, static_cast<cudaStream_t>(stream), &staged, &small)) return rc;
+    return gemv_2x8_launch(staged, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, LUTVQ_FLAG_NO_PDL, ws, small,
                            static_cast<cudaStream_t>(stream));
 }
 
@@ -133,15 +141,36 @@ static int matmat_rows(const void* x, const void* codes, int packed, const void*
     LUTVQ_REQUIRE(batch >= 0, "bad batch %d", batch);
     if (batch == 0) return LUTVQ_OK;                                  // empty input: nothing to launch (pointers may be null)
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
-    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    size_t region = ws_bytes;
+    if (!packed) {
+        // reference layout: one re-layout pass into the staging area, then the packed kernel (gemv_stage_codes)
+        const void* staged = nullptr;
+        if (int rc = gemv_stage_codes(codes, prob_m, prob_k, ws, ws_bytes, st, &staged, &region)) return rc;
+        codes = staged;
+        flags &= ~LUTVQ_FLAG_X_READY;                                 // the staged image is not a resident weight
+    }
     // cuda_kernel.cpp:404-414 loops the matvec over the flattened batch rows; so do we (one fused launch per row,
     // scale/bias folded into the kernel's epilogue instead of three extra elementwise kernels).
+    // X_READY launches overlap under programmatic dependent launch, so consecutive rows must not share split-k words:
+    // row b takes workspace region b % LUTVQ_XREADY_WS_RING when the caller's workspace holds that many regions,
+    // otherwise the promise is dropped for the rows after the first.
+    const size_t need = (gemv_packed_workspace_bytes(prob_m, prob_k / 8) + 255) / 256 * 256;
+    int regions = 1;
+    if (packed && batch > 1 && (flags & LUTVQ_FLAG_X_READY)) {
+        const int want = batch < LUTVQ_XREADY_WS_RING ? batch : LUTVQ_XREADY_WS_RING;
+        if (ws_bytes >= need * (size_t)want) regions = want;
+    }
     const size_t esz = 2;
     for (int b = 0; b < batch; ++b) {
         const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * esz;
         void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * esz;
-        if (int rc = gemv_2x8_launch(codes, packed, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, flags, ws,
-                                     ws_bytes, static_cast<cudaStream_t>(stream)))
+        unsigned f = flags;
+        if (!packed && b == 0) f |= LUTVQ_FLAG_NO_PDL;                // must not start before the prepack kernel has finished
+        if (b > 0 && regions == 1) f &= ~LUTVQ_FLAG_X_READY;
+        void* wsb = regions > 1 ? static_cast<uint8_t*>(ws) + (size_t)(b % regions) * need : ws;
+        if (int rc = gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb,
+                                     regions > 1 ? need : region, st))
             return rc;
     }
     return LUTVQ_OK;
@@ -183,14 +212,13 @@ int lutvq_code2x8_matmat_group_packed(const void* x, int n, const void* const* p
                                       int prob_k, int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
     LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
     LUTVQ_REQUIRE(x && packed && codebooks && y && prob_m, "null pointer");
-    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(x) & 3u) == 0, "x must be 4-byte aligned");
     GemvItem items[3];
     for (int i = 0; i < n; ++i) {
         if (int rc = check_2x8_common(packed[i], codebooks[i], prob_m[i], prob_k, dtype)) return rc;
         LUTVQ_REQUIRE(y[i] != nullptr, "null y pointer of linear %d", i);
         items[i] = GemvItem{packed[i], codebooks[i], y[i], scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, prob_m[i]};
     }
-    return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
+    return gemv_2x8_launch_group(n, items, x, nullptr, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 int lutvq_code2x8_matmat_group_packed_swiglu(const void* gate, const void* up, int n, const void* const* packed,
@@ -198,12 +226,16 @@ int lutvq_code2x8_matmat_group_packed_swiglu(const void* gate, const void* up, i
                                              void* const* y, const int* prob_m, int prob_k, int dtype, unsigned flags, void* ws,
                                              size_t ws_bytes, void* stream) {
     LUTVQ_REQUIRE(gate && up, "null gate/up pointer");
-    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(gate) & 3u) == 0, "gate must be 4-byte aligned");
     LUTVQ_REQUIRE(dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only (dtype %d)", dtype);
-    gemv_set_x_gate(gate);
-    const int rc = lutvq_code2x8_matmat_group_packed(up, n, packed, codebooks, scales, bias, y, prob_m, prob_k, dtype, flags, ws, ws_bytes, stream);
-    gemv_set_x_gate(nullptr);
-    return rc;
+    LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
+    LUTVQ_REQUIRE(packed && codebooks && y && prob_m, "null pointer");
+    GemvItem items[3];
+    for (int i = 0; i < n; ++i) {
+        if (int rc = check_2x8_common(packed[i], codebooks[i], prob_m[i], prob_k, dtype)) return rc;
+        LUTVQ_REQUIRE(y[i] != nullptr, "null y pointer of linear %d", i);
+        items[i] = GemvItem{packed[i], codebooks[i], y[i], scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, prob_m[i]};
+    }
+    return gemv_2x8_launch_group(n, items, up, gate, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,

@@ -23,12 +23,11 @@
 
 namespace lutvq {
 
-int gemv_2x8_launch(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales,
+int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push);
 
-void gemv_set_x_gate(const void* gate);
-int gemv_2x8_launch_group(int n, const GemvItem* items, int packed, const void* x, int I, int dtype, unsigned flags,
+int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 
 constexpr int    kShardMaxRanks  = 8;
@@ -293,6 +292,7 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
     LUTVQ_REQUIRE(rows_local > 0 && prob_k > 0 && prob_k % 64 == 0, "bad shape rows_local=%d prob_k=%d", rows_local, prob_k);
     LUTVQ_REQUIRE((row_offset + (size_t)rows_local) * 2 <= s->slot_bytes, "rows [%zu, %zu) do not fit a %zu-byte slot", row_offset, row_offset + rows_local, s->slot_bytes);
+    LUTVQ_REQUIRE(row_offset % 8 == 0, "row_offset %zu must be a multiple of 8 (the exchange moves 16-byte pieces)", row_offset);
     LUTVQ_REQUIRE(x && packed && codebooks, "null pointer");
     if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
     const size_t slot_off = kShardFlagBytes + s->slot_bytes * slot + row_offset * 2;
@@ -303,7 +303,7 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     s->pending[slot].pushed = 0;
     if (!(flags & LUTVQ_FLAG_PUSH_EPILOGUE))
         // default: the GEMV fills the local slice; lutvq_shard_wait[_mask] forwards it to the peers and waits (one kernel)
-        return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
+        return gemv_2x8_launch(packed, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
                                static_cast<cudaStream_t>(stream), nullptr);
     GemvPush push;
     push.n = 0;
@@ -318,14 +318,14 @@ int lutvq_sharded_matmat_packed(lutvq_shard_t* h, int slot, size_t row_offset, c
     push.flag[push.n] = reinterpret_cast<unsigned*>(s->local) + (size_t)slot * kShardMaxRanks + s->rank;
     ++push.n;
     push.sent = reinterpret_cast<unsigned*>(s->local + kLocalOff) + slot;
-    return gemv_2x8_launch(packed, 1, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
+    return gemv_2x8_launch(packed, x, y_local, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes,
                            static_cast<cudaStream_t>(stream), &push);
 }
 
-int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* x,
-                                      const void* const* packed, const void* const* codebooks, const void* const* scales,
-                                      const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
-                                      void* ws, size_t ws_bytes, void* stream) {
+static int sharded_group_impl(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* x, const void* gate,
+                              const void* const* packed, const void* const* codebooks, const void* const* scales,
+                              const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                              void* ws, size_t ws_bytes, void* stream) {
     Shard* s = reinterpret_cast<Shard*>(h);
     LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
     LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
@@ -339,6 +339,7 @@ int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots,
         LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
         for (int j = 0; j < i; ++j) LUTVQ_REQUIRE(slots[j] != slot, "the linears of a group need distinct slots");
         LUTVQ_REQUIRE(rows_local[i] > 0 && (row_offsets[i] + (size_t)rows_local[i]) * 2 <= s->slot_bytes, "rows of linear %d do not fit a slot", i);
+        LUTVQ_REQUIRE(row_offsets[i] % 8 == 0, "row offset of linear %d must be a multiple of 8", i);
         LUTVQ_REQUIRE(packed[i] && codebooks[i], "null pointer in linear %d", i);
         void* y_local = s->local + kShardFlagBytes + s->slot_bytes * slot + row_offsets[i] * 2;
         items[i] = GemvItem{packed[i], codebooks[i], y_local, scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, rows_local[i]};
@@ -347,7 +348,14 @@ int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots,
         s->pending[slot].fused = 0;
         s->pending[slot].pushed = 0;
     }
-    return gemv_2x8_launch_group(n, items, 1, x, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
+    return gemv_2x8_launch_group(n, items, x, gate, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr);
+}
+
+int lutvq_sharded_matmat_group_packed(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* x,
+                                      const void* const* packed, const void* const* codebooks, const void* const* scales,
+                                      const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                                      void* ws, size_t ws_bytes, void* stream) {
+    return sharded_group_impl(h, n, slots, row_offsets, x, nullptr, packed, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes, stream);
 }
 
 int lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* h, int n, const int* slots, const size_t* row_offsets, const void* gate,
@@ -355,13 +363,8 @@ int lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* h, int n, const int*
                                              const void* const* scales, const void* const* bias, const int* rows_local, int prob_k,
                                              int dtype, unsigned flags, void* ws, size_t ws_bytes, void* stream) {
     LUTVQ_REQUIRE(gate && up, "null gate/up pointer");
-    LUTVQ_REQUIRE((reinterpret_cast<uintptr_t>(gate) & 3u) == 0, "gate must be 4-byte aligned");
     LUTVQ_REQUIRE(dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only (dtype %d)", dtype);
-    gemv_set_x_gate(gate);
-    const int rc = lutvq_sharded_matmat_group_packed(h, n, slots, row_offsets, up, packed, codebooks, scales, bias, rows_local, prob_k,
-                                                     dtype, flags, ws, ws_bytes, stream);
-    gemv_set_x_gate(nullptr);
-    return rc;
+    return sharded_group_impl(h, n, slots, row_offsets, up, gate, packed, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes, stream);
 }
 
 int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {

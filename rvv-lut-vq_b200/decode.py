@@ -105,7 +105,7 @@ class Decoder:
         self.pos = torch.zeros(1, dtype=torch.int32, device=dev)
         # workspace ring: every GEMV takes the next region (include/lutvq.h X_READY contract)
         max_rows = max(l.rows for l in self.layers[0].values() if isinstance(l, _Linear))
-        self.ws_need = (3 * int(self.lib.lutvq_workspace_bytes_ex(max_rows, max(i for i, _ in shapes.values()), 6)) + 255) // 256 * 256   # a group of <= 3
+        self.ws_need = (3 * int(self.lib.lutvq_packed_workspace_bytes(max_rows, max(i for i, _ in shapes.values()))) + 255) // 256 * 256   # a group of <= 3
         self.ws = torch.zeros(ops.XREADY_WS_RING * self.ws_need, dtype=torch.uint8, device=dev)
         self._ws_i = 0
         if world > 1 and exchange == "nccl":

@@ -53,12 +53,17 @@ _ws_ring_pos: Dict[Tuple[int, int], int] = {}
 
 
 _gemm_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+_stage_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+
+
+def _key(dev: torch.device) -> Tuple[int, int]:
+    return (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
 
 
 def gemm_workspace(dev: torch.device, prob_m: int, prob_k: int, batch: int) -> torch.Tensor:
     """Scratch of the prefill GEMM (split-k partial accumulators; can be tens of MB), cached per (device, stream)."""
     need = int(lib().lutvq_workspace_bytes_ex(prob_m, prob_k, batch))
-    key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    key = _key(dev)
     ws = _gemm_workspaces.get(key)
     if ws is None or ws.numel() < need:
         ws = torch.zeros(max(need, 1 << 20), dtype=torch.uint8, device=dev)
@@ -66,13 +71,25 @@ def gemm_workspace(dev: torch.device, prob_m: int, prob_k: int, batch: int) -> t
     return ws
 
 
+def stage_workspace(dev: torch.device, prob_m: int, prob_k: int) -> torch.Tensor:
+    """Scratch of the reference-layout GEMV entry points: split-k words + the staging area for the re-laid codes
+    (lutvq_workspace_bytes), cached per (device, stream).  Callers that prepack once never need it."""
+    need = int(lib().lutvq_workspace_bytes(prob_m, prob_k))
+    key = _key(dev)
+    ws = _stage_workspaces.get(key)
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, dtype=torch.uint8, device=dev)
+        _stage_workspaces[key] = ws
+    return ws
+
+
 def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False) -> torch.Tensor:
-    """Zero-initialised scratch, cached per (device, stream) as include/lutvq.h requires.  The cache holds a ring of
-    XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True`` (LUTVQ_FLAG_X_READY calls) steps through
-    the ring so that overlapping launches never share a region.  (Inside a CUDA graph the region is baked at capture:
-    keep the number of X_READY calls per graph a multiple of XREADY_WS_RING.)"""
-    need = (int(lib().lutvq_workspace_bytes_ex(prob_m, prob_k, 6)) + 255) // 256 * 256
-    key = (dev.index if dev.index is not None else torch.cuda.current_device(), torch.cuda.current_stream(dev).cuda_stream)
+    """Zero-initialised split-k words for the packed entry points, cached per (device, stream) as include/lutvq.h
+    requires.  The cache holds a ring of XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True``
+    (LUTVQ_FLAG_X_READY calls) steps through regions 1.. so that overlapping launches never share a region and never
+    collide with a plain call's region 0.  (Inside a CUDA graph the region is baked at capture.)"""
+    need = (8 * ((prob_m + 31) // 32 * 32) + 256 + 255) // 256 * 256          # lutvq_packed_workspace_bytes, rounded
+    key = _key(dev)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < need * XREADY_WS_RING:
         ws = torch.zeros(max(need, 1 << 17) * XREADY_WS_RING, dtype=torch.uint8, device=dev)
@@ -80,8 +97,8 @@ def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False)
     slot = ws.numel() // XREADY_WS_RING
     i = 0
     if rotate:
-        i = _ws_ring_pos.get(key, 0)
-        _ws_ring_pos[key] = (i + 1) % XREADY_WS_RING
+        i = _ws_ring_pos.get(key, 0) % (XREADY_WS_RING - 1) + 1
+        _ws_ring_pos[key] = i
     return ws[i * slot:(i + 1) * slot]
 
 
@@ -94,7 +111,7 @@ def code2x8_matvec(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, codebook: 
     dev = _require_cuda(A, B, C, codebook)
     prob_m, prob_k = C.size(0), B.size(0)
     with torch.cuda.device(dev):
-        ws = workspace(dev, prob_m, prob_k)
+        ws = stage_workspace(dev, prob_m, prob_k)
         check(lib().lutvq_code2x8_matvec(_ptr(A), _ptr(B), _ptr(C), _ptr(codebook), prob_m, prob_k,
                                          _lib.LUTVQ_BF16 if use_bfloat16 else _lib.LUTVQ_F16,
                                          _ptr(ws), ws.numel(), _stream(dev)))
@@ -114,7 +131,7 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
         if fn_name == "lutvq_code2x8_matmat_dequant":
             ws = gemm_workspace(dev, out_features, in_features, batch)
         else:
-            ws = workspace(dev, out_features, in_features, rotate=bool(flags and flags & _lib.FLAG_X_READY))
+            ws = stage_workspace(dev, out_features, in_features)
         fn = getattr(lib(), fn_name)
         if flags is None:
             rc = fn(_ptr(flat_input), _ptr(codes_c), _ptr(cb_c), _ptr(sc), _ptr(bi), _ptr(flat_output), batch,

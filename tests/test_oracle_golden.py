@@ -111,3 +111,92 @@ def test_simd_lut_scalar_wraparound(orc):
     want = (37 * lut8.astype(np.int64)[idx].sum(axis=0)).astype(np.int64)
     want = ((want + 2**15) % 2**16 - 2**15).astype(np.int16)
     assert np.array_equal(got, want)
+
+
+def test_simd_lut_scalar_matches_reference_build(orc, golden_dir):
+    """a13 pinned by the reference itself: fixture produced by bench_avx_lut.cpp -D_SCALAR_ (oracle/_ref/libsimdlut_ref.so,
+    oracle/gen_golden_tmac.py): non-zero start values, 300 runs over 500 rows of CB_SIZE 16."""
+    g = _load(golden_dir, "simd_lut_ref")
+    got = orc.c_simd_lut_scalar(g["idx"], g["lut"], n_runs=int(g["n_runs"][0]), out0=g["out_in"])
+    assert np.array_equal(got, g["out"])
+
+
+# ------------------------------------------------------------------ T-MAC integer-LUT kernels (a14)
+def test_tmac_lut_ctor_known_answer_and_fixtures(orc, golden_dir):
+    """lut_ctor.cc:38-266 via tmac_oracle.c vs fixtures produced by the reference's compiled code, incl. the known answer
+    of its own test_lut_ctor.cc (b[i] = i -> lut_scales 0.929134, lut_biases -496)."""
+    g = _load(golden_dir, "tmac_lut_ctor")
+    for name in ("kat", "rand32", "rand256", "sat"):
+        b = g[f"{name}__b"]
+        n = b.shape[0] // 32
+        scales = np.array([orc.c_partial_max_g4_int8_k8(0.0, b[32 * k:32 * k + 32]) for k in range(n)], dtype=np.float32)
+        assert np.array_equal(scales.view(np.uint32), g[f"{name}__scales"].view(np.uint32))
+        for k in range(n):
+            qlut, ls, lb = orc.c_lut_ctor_g4_int8(32, b[32 * k:32 * k + 32], scales[k])
+            assert np.array_equal(qlut, g[f"{name}__qlut"][8 * k:8 * k + 8])
+            assert np.float32(ls).view(np.uint32) == g[f"{name}__lut_scales"][k].view(np.uint32)
+            assert np.float32(lb).view(np.uint32) == g[f"{name}__lut_biases"][k].view(np.uint32)
+        qs, ls, lb = orc.c_lut_ctor_g4_int8(b.shape[0], b, float(g[f"{name}__scale_single"][0]))
+        assert np.array_equal(qs, g[f"{name}__qlut_single"]) and np.float32(lb).view(np.uint32) == g[f"{name}__bias_single"][0].view(np.uint32)
+        # the fused preprocessor protocol (kernels.cc:1002-1037)
+        q2, s2, b2 = orc.c_tmac_preprocessor_int8(b)
+        assert np.array_equal(q2, g[f"{name}__qlut"]) and np.array_equal(s2, g[f"{name}__lut_scales"]) and np.array_equal(b2, g[f"{name}__lut_biases"])
+    kat_q = g["kat__qlut"]
+    assert kat_q[0].tolist() == [-6, -6, -4, -4, -2, -2, 0, 0, 0, 0, 2, 2, 4, 4, 6, 6]
+    assert kat_q[7].tolist() == [-127, -67, -65, -4, -62, -2, 0, 60, -60, 0, 2, 62, 4, 65, 67, 127]
+    assert abs(float(g["kat__scales"][0]) - 0.929134) < 1e-6 and float(g["kat__lut_biases"][0]) == -496.0
+
+
+def test_tmac_tbl_updates_bit_exact(orc, golden_dir):
+    """tbl.cc:536-630 (int32) and :323-532 (float: plain, ZeroPoint, FastAggregation) vs the reference's compiled output"""
+    g = _load(golden_dir, "tmac_tbl")
+    for K, bits in ((16, 2), (8, 4)):
+        t = f"i32_k{K}_b{bits}"
+        got = orc.c_tbl_g4_int8_int32_update(256, g[f"{t}__c_in"], g[f"{t}__lut"], g[f"{t}__a"], K)
+        assert np.array_equal(got, g[f"{t}__c_out"])
+    for t in ("f_k16_b2", "f_k8_b4", "f_k16_b4_zp", "f_k16_b2_fa"):
+        K, bits, ak, fa, zp = [int(v) for v in g[f"{t}__cfg"]]
+        args = (g[f"{t}__lut"], g[f"{t}__a"], g[f"{t}__scales"], g[f"{t}__lut_scales"], g[f"{t}__lut_biases"], K, bits, ak, fa, zp)
+        c1 = orc.c_tbl_g4_int8_float_update(256, g[f"{t}__c_in"], *args)
+        assert np.array_equal(c1.view(np.uint32), g[f"{t}__c_out"].view(np.uint32)), t
+        c2 = orc.c_tbl_g4_int8_float_update(256, c1, *args)
+        assert np.array_equal(c2.view(np.uint32), g[f"{t}__c_out2"].view(np.uint32)), t
+
+
+def test_tmac_qgemm_bit_exact(orc, golden_dir):
+    """whole bit-serial GEMV in the generated kernels' call structure (T-MAC deploy/tuned/kernels.cc:827-960)"""
+    g = _load(golden_dir, "tmac_qgemm")
+    M, K, bits, bm = [int(v) for v in g["cfg"]]
+    q, ls, lb = orc.c_tmac_preprocessor_int8(g["B"])
+    assert np.array_equal(q, g["qlut"]) and np.array_equal(ls, g["lut_scales"]) and np.array_equal(lb, g["lut_biases"])
+    C = orc.c_tmac_qgemm_lut_int8(M, K, bits, bm, g["A"], q, g["scales"], ls, lb)
+    assert np.array_equal(C.view(np.uint32), g["C"].view(np.uint32))
+
+
+def test_tmac_oracle_vs_reference_build_random(orc):
+    """when oracle/_ref exists (build container): fresh random cases straight against the reference's compiled code"""
+    import ctypes
+    ref = orc.ref_tmac()
+    if ref is None:
+        pytest.skip("oracle/_ref/libtmac_ref.so not built (no /root/reference here)")
+    rng = np.random.default_rng(7)
+    P = lambda a: a.ctypes.data_as(ctypes.c_void_p)
+    for trial in range(20):
+        lut = rng.integers(-128, 128, size=(8, 16), dtype=np.int8)
+        a = rng.integers(0, 256, size=(128 * 8,), dtype=np.uint8)
+        sc = rng.standard_normal(64).astype(np.float32)
+        ls, lb = rng.standard_normal(1).astype(np.float32), rng.standard_normal(1).astype(np.float32)
+        c = rng.standard_normal(256).astype(np.float32)
+        want = c.copy()
+        ref.tbl_g4_int8_float_update_strue_k8_b4_ak8_fafalse_zfalse_osfalse(256, P(want), P(lut), P(a), P(sc), P(ls), P(lb))
+        got = orc.c_tbl_g4_int8_float_update(256, c, lut, a, sc, ls, lb, 8, 4, 8)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        b = (rng.standard_normal(32) * 10 ** rng.uniform(-3, 3)).astype(np.float32)
+        s = np.zeros(1, dtype=np.float32)
+        ref.partial_max_g4_int8_k8(P(s), P(b))
+        assert np.float32(orc.c_partial_max_g4_int8_k8(0.0, b)).view(np.uint32) == s.view(np.uint32)[0]
+        q = np.zeros((8, 16), dtype=np.int8)
+        s2, b2 = s.copy(), np.zeros(1, dtype=np.float32)
+        ref.lut_ctor_g4_int8_k0_b4(32, P(q), P(b), P(s2), P(b2))
+        gq, gs, gb = orc.c_lut_ctor_g4_int8(32, b, float(s[0]))
+        assert np.array_equal(gq, q) and np.float32(gb).view(np.uint32) == b2.view(np.uint32)[0]
