@@ -237,6 +237,62 @@ int    lutvq_simd_lut_lookup_add(const void* idx, const void* lut, void* output,
                                  unsigned long long n_runs, unsigned long long n_lut_per_run, void* ws, size_t ws_bytes,
                                  void* stream);
 
+/* ---- AQLM 1x16 (one codebook of 65536 vectors, 16-bit codes) ----
+ * Replaces code1x16_matvec_cuda<bf16, group_size> / code1x16_dequant_cuda<group_size> (cuda_kernel.cu:470-553 launching
+ * Code1x16MatVec :7-95 / Code1x16Dequant :98-142) and the host wrappers code1x16_matvec / code1x16_matmat /
+ * code1x16_dequant (cuda_kernel.cpp:113-209).  codes int16 [prob_m][prob_k / group_size] (unsigned index in two's
+ * complement, utils.py:24-31), codebook [65536][group_size] fp16/bf16, group_size 8 or 16 (anything else:
+ * LUTVQ_EUNSUPPORTED, the reference's NotImplementedError cuda_kernel.cpp:136-145), prob_k a multiple of 8 * group_size.
+ *   matvec : y[prob_m] = round(W x)                          (the raw launcher, no scale)
+ *   matmat : y[batch][prob_m] = round(W x) * scales + bias   (the reference's rounding order, cuda_kernel.cpp:95-111;
+ *            up to 4 batch rows share each fetched codebook row instead of one launch per row)
+ *   dequant: W[prob_m][prob_k] = codebook[code] (* scales[row] when scales != NULL: `weight *= scales`, one RN multiply); bit-exact.
+ * Not LUT-able (G x 65536 entries per activation vector): a dequantize-and-FMA GEMV, fp32 accumulation, bound by the
+ * L2 gather of one codebook row per code.  No workspace. */
+int lutvq_code1x16_matvec(const void* codes, const void* x, void* y, const void* codebook, int prob_m, int prob_k, int group_size,
+                          int dtype, void* stream);
+int lutvq_code1x16_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias, void* y,
+                          int batch, int prob_m, int prob_k, int group_size, int dtype, void* stream);
+int lutvq_code1x16_dequant(const void* codes, void* W, const void* codebook, const void* scales, int prob_m, int prob_k, int group_size,
+                           int dtype, void* stream);
+
+/* ---- T-MAC bit-serial integer LUT ----
+ * The entry points of benchmark/kernel/bs_lut_gemm/tbl.cc and lut_ctor.cc with the reference's argument lists (x86
+ * semantics: float_type = float, tbl.cc:10-15) plus a stream; the template parameters the reference bakes into the
+ * symbol name (tbl.cc:673-691 `tbl_g4_int8_float_update_s{s}_k{K}_b{bits}_ak{act_k}_fa{fa}_z{z}_os{os}`, lut_ctor.cc:223-226
+ * `lut_ctor_g4_int8_k{fak}_b{bits}`) are trailing arguments.  All pointers are device pointers.  Integer results are exact,
+ * fp32 results reproduce the reference's AVX2 build bit for bit (oracle/tmac_oracle.c, pinned by oracle/_ref/libtmac_ref.so).
+ *   tbl_g4_int8_int32_update (tbl.cc:536-630): block i of 32 outputs: c[2i+l] += sum_k lut[k][a[iK+16k+l] & 15],
+ *       c[2i+16+l] += sum_k lut[k][a[iK+16k+l] >> 4], k-sum in wrapping int16.  c int32[m], lut int8[K][16] (16-byte
+ *       aligned), a uint8[m/2 * K]; m % 32 == 0.
+ *   tbl_g4_int8_float_update (tbl.cc:323-532): same sums per act_k block, * lut_scales[kk] (+ lut_biases[kk] on bit plane 0),
+ *       then c = fma(sum, scales[...], c); fast_aggregation = the halving adder (tbl.cc:169-215), zero_point = tbl.cc:493-507.
+ *       (has_scale and one_scale are not consulted on the x86 path and have no argument.)
+ *   tbl_{int8,int16,int32,float}_reset (tbl.cc:697-715), partial_max_g4_int8_k8 / partial_max_reset (lut_ctor.cc:232-266):
+ *       *lut_scales = max(*lut_scales, max_j(|b[4j]|+|b[4j+1]|+|b[4j+2]|+|b[4j+3]|) / 127) over 32 activations.
+ *   lut_ctor_g4_int8 (lut_ctor.cc:38-221): qlut int8[act_k/4][16] = sat(round(entry / *lut_scales)), *lut_biases = sum of
+ *       the all-minus entries; *lut_scales is read (and written back unchanged).
+ *   tmac_preprocessor_int8 / tmac_qgemm_lut_int8: the call structure T-MAC's generated kernels wrap around the above
+ *       (deploy/tuned/kernels.cc:1002-1037 / 827-960; TMACGeMMWrapper calls them): per 32 activations reset + partial_max +
+ *       lut_ctor(32); per tile of bm bit-plane rows tbl_float_reset, K/32 x tbl_g4_int8_float_update(k8, ak8), then
+ *       C = ((c0 * 0.5 + c1) + c2 * 2) + c3 * 4 over the bit planes.  A uint8[M*bits/bm][K/32][bm/2 * 8],
+ *       scales float[M*bits/bm][K/32][bm/bits], C float[M].  Shapes without a kernel return LUTVQ_EUNSUPPORTED (the
+ *       reference's generated dispatcher returns -1). */
+int lutvq_tbl_g4_int8_int32_update(int m, void* c, const void* lut, const void* a, int K, void* stream);
+int lutvq_tbl_g4_int8_float_update(int m, void* c, const void* lut, const void* a, const void* scales, const void* lut_scales,
+                                   const void* lut_biases, int K, int bits, int act_k, int fast_aggregation, int zero_point,
+                                   void* stream);
+int lutvq_tbl_int8_reset(int m, void* c, void* stream);
+int lutvq_tbl_int16_reset(int m, void* c, void* stream);
+int lutvq_tbl_int32_reset(int m, void* c, void* stream);
+int lutvq_tbl_float_reset(int m, void* c, void* stream);
+int lutvq_partial_max_g4_int8_k8(void* lut_scales, const void* b, void* stream);
+int lutvq_partial_max_reset(void* lut_scales, void* stream);
+int lutvq_lut_ctor_g4_int8(int act_k, void* qlut, const void* b, void* lut_scales, void* lut_biases, void* stream);
+int lutvq_tmac_preprocessor_int8(int K, const void* B, void* lut_scales, void* lut_biases, void* qlut, void* stream);
+int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, const void* qlut, const void* scales,
+                              const void* lut_scales, const void* lut_biases, void* C, void* stream);
+
 /* ---- decode glue (fp16, batch 1): the non-GEMV steps of a Llama-shaped decode step, so a whole token is one chain of
  * launches of this library inside a CUDA graph.  Not reference entry points (the reference takes these from HF
  * transformers, benchmark/llm/generate_benchmark.py) and not LUT-VQ work; they exist for the decode tok/s metric.

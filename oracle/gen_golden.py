@@ -103,11 +103,50 @@ def gen_aqlm():
         print(f"[aqlm] {name}: numba-vs-dense rel {rel:.2e}")
 
 
+def codebook_1x16(seed: int, gs: int) -> np.ndarray:
+    """The 65536-entry codebook of a 1x16 fixture, regenerated from its seed (PCG64 stream: stable across numpy versions;
+    the fixture stores a checksum) instead of committing 1-2 MiB of random halves per case."""
+    return np.random.default_rng(seed).standard_normal((1, 65536, 1, gs)).astype(np.float16)
+
+
+def gen_aqlm_1x16():
+    """AQLM 1x16 (one 65536-entry codebook, int16 codes; inference.py:39-61) through the reference's own
+    pack_int_data / unpack_int_data / _dequantize_weight (aqlm/utils.py:11-70)."""
+    sys.path.insert(0, os.path.join(REF, "benchmark/AQLM/inference_lib/src"))
+    import torch
+    from aqlm.utils import _dequantize_weight, pack_int_data, unpack_int_data
+    torch.set_num_threads(1)
+    cases = {"aqlm_1x16_g8_i256_o48": (256, 48, 8, 3, 21, True), "aqlm_1x16_g16_i512_o40": (512, 40, 16, 2, 22, False)}
+    for name, (I, O, gs, B, seed, with_bias) in cases.items():
+        torch.manual_seed(seed)
+        x = torch.randn((B, I)).half()
+        idx = torch.randint(65536, (O, I // gs, 1))
+        idx[0, 0, 0], idx[1, 0, 0] = 65535, 32768                              # exercise the sign wrap of pack_int_data
+        codes = pack_int_data(idx.clone(), 16)                                 # int16 [O, G, 1]
+        assert codes.dtype == torch.int16 and torch.equal(unpack_int_data(codes, 16), idx)
+        cb = torch.from_numpy(codebook_1x16(seed, gs))
+        scales = torch.randn((O, 1, 1, 1)).half()
+        bias = torch.randn(O).half() if with_bias else None
+        w16_noscale = _dequantize_weight(unpack_int_data(codes, 16), cb, None).contiguous()
+        w16_scaled = _dequantize_weight(unpack_int_data(codes, 16), cb, scales).contiguous()
+        w32 = _dequantize_weight(unpack_int_data(codes, 16), cb.float(), scales.float()).contiguous()
+        y_dense = torch.nn.functional.linear(x.float(), w32, None if bias is None else bias.float())
+        np.savez_compressed(
+            os.path.join(OUT, name + ".npz"),
+            cfg=np.array([I, O, gs, B, seed, int(with_bias)]),
+            x=x.numpy(), codes=codes.numpy(), idx=idx.numpy().astype(np.uint16), codebook_checksum=np.array([int(cb.numpy().view(np.uint16).astype(np.uint64).sum())]),
+            scales=scales.numpy(), bias=(bias.numpy() if bias is not None else np.zeros(0, np.float16)),
+            weight_f16_noscale=w16_noscale.numpy(), weight_f16_scaled=w16_scaled.numpy(), y_dense=y_dense.numpy(),
+        )
+        print(f"[aqlm 1x16] {name}: W {tuple(w16_scaled.shape)}")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     vq = import_vq()
     gen_vqpy(vq)
     gen_aqlm()
+    gen_aqlm_1x16()
     try:
         from gen_golden_tmac import gen_tmac
         gen_tmac(OUT)

@@ -198,6 +198,23 @@ def np_aqlm_dequantize_weight(codes_idx: np.ndarray, codebooks: np.ndarray, scal
     return w.reshape(O, G * d)
 
 
+def np_aqlm_1x16_dequantize(codes_i16: np.ndarray, codebook_f16: np.ndarray, scales_f16: Optional[np.ndarray]) -> np.ndarray:
+    """AQLM 1x16 through utils.py:29-31 (unpack) and :43-70 (_dequantize_weight, one codebook: a pure gather, then
+    `* scales` = one fp16 RN multiply) = Code1x16Dequant (cuda_kernel.cu:98-142) + `weight *= scales` (cuda_kernel.cpp:206).
+    codes int16 [O, G, 1] or [O, G]; codebook fp16 [1, 65536, 1, gs]; -> fp16 [O, G * gs], bit-exact."""
+    idx = np_unpack_int_data(codes_i16.reshape(codes_i16.shape[0], -1), 16)
+    cb = codebook_f16.reshape(65536, -1)
+    w = cb[idx]                                                    # [O, G, gs]
+    if scales_f16 is not None:
+        w = (w.astype(np.float32) * scales_f16.reshape(-1, 1, 1).astype(np.float32)).astype(np.float16)   # exact product, one rounding
+    return np.ascontiguousarray(w.reshape(w.shape[0], -1))
+
+
+def codebook_1x16(seed: int, gs: int) -> np.ndarray:
+    """the 65536-entry codebook of a 1x16 fixture, regenerated from its seed (same code as oracle/gen_golden.py)"""
+    return np.random.default_rng(seed).standard_normal((1, 65536, 1, gs)).astype(np.float16)
+
+
 def np_numba_gemv_lut(x: np.ndarray, codebooks: np.ndarray, codes_alt: np.ndarray, scales: np.ndarray) -> np.ndarray:
     """numba_kernel.py:38-48 restated with numpy (fp32).  codes_alt uint8 [G, O, N]."""
     N, K, _, d = codebooks.shape

@@ -40,6 +40,20 @@ SIGNATURES = {
     "lutvq_code2x8_matmat_dequant": (I, [P, P, P, P, P, P, I, I, I, I, P, SZ, P]),
     "lutvq_simd_lut_workspace_bytes": (SZ, [I]),
     "lutvq_simd_lut_lookup_add": (I, [P, P, P, I, I, U64, U64, P, SZ, P]),
+    "lutvq_code1x16_matvec": (I, [P, P, P, P, I, I, I, I, P]),
+    "lutvq_code1x16_matmat": (I, [P, P, P, P, P, P, I, I, I, I, I, P]),
+    "lutvq_code1x16_dequant": (I, [P, P, P, P, I, I, I, I, P]),
+    "lutvq_tbl_g4_int8_int32_update": (I, [I, P, P, P, I, P]),
+    "lutvq_tbl_g4_int8_float_update": (I, [I, P, P, P, P, P, P, I, I, I, I, I, P]),
+    "lutvq_tbl_int8_reset": (I, [I, P, P]),
+    "lutvq_tbl_int16_reset": (I, [I, P, P]),
+    "lutvq_tbl_int32_reset": (I, [I, P, P]),
+    "lutvq_tbl_float_reset": (I, [I, P, P]),
+    "lutvq_partial_max_g4_int8_k8": (I, [P, P, P]),
+    "lutvq_partial_max_reset": (I, [P, P]),
+    "lutvq_lut_ctor_g4_int8": (I, [I, P, P, P, P, P]),
+    "lutvq_tmac_preprocessor_int8": (I, [I, P, P, P, P, P]),
+    "lutvq_tmac_qgemm_lut_int8": (I, [I, I, I, I, P, P, P, P, P, P, P]),
     "lutvq_codeKx8_workspace_bytes": (SZ, [I, I, I]),
     "lutvq_codeKx8_matmat": (I, [P, P, P, P, P, P, I, I, I, I, I, P, SZ, P]),
     "lutvq_codeKx8_dequant": (I, [P, P, P, P, I, I, I, I, P]),

@@ -1,0 +1,321 @@
+// tmac.cu -- SURVEY 8a row a14 / 8f rank 1: the T-MAC bit-serial integer-LUT entry points of the reference's
+// benchmark/kernel/bs_lut_gemm/{tbl.cc, lut_ctor.cc} on the GPU, x86 semantics (float_type = float, tbl.cc:10-15):
+//
+//   tbl_g4_int8_int32_update_impl  (tbl.cc:536-630)   c[2i + l] += sum_k lut[k][a[iK + 16k + l] & 15]   (int16 wraparound k-sum)
+//                                                     c[2i + 16 + l] += sum_k lut[k][a[iK + 16k + l] >> 4]
+//   tbl_g4_int8_float_update_impl  (tbl.cc:323-532)   the same sums, scaled per act_k block by lut_scales / lut_biases and per
+//                                                     output by `scales`, accumulated in fp32 in the reference's own order
+//   tbl_*_reset                    (tbl.cc:697-715)
+//   partial_max_g4_int8_k8 / partial_max_reset        (lut_ctor.cc:232-266)
+//   lut_ctor_g4_int8_impl          (lut_ctor.cc:38-221)  16 signed sums +-b0+-b1+-b2+-b3 per group of 4 activations, int8
+//   preprocessor_int8 / qgemm_lut_int8                (T-MAC deploy/tuned/kernels.cc:1002-1037, 827-960: the call structure
+//                                                     the generated kernels wrap around the functions above)
+//
+// Integer results are exact; the fp32 results reproduce the reference BIT FOR BIT, so every floating-point operation is
+// written with an explicit rounding intrinsic (__fadd_rn / __fmul_rn / __fdiv_rn: never contracted) and fmaf appears
+// exactly where the reference writes _mm256_fmadd_ps.  A 16-entry table is ONE 128-bit register quad per thread: the
+// lookup is a byte extract (PRMT) from the quad selected by the nibble, no shared-memory traffic at all.
+//
+// Work split: a thread owns one byte lane (block of 32 outputs, l) = two outputs (low nibble, high nibble); the k loop
+// stays sequential inside the thread because the reference's int16 wraparound and fp32 order are order-dependent.
+#include "common.cuh"
+
+namespace lutvq {
+
+// one lookup in the 16-entry int8 table held as 4 words: entry n = byte (n & 3) of word (n >> 2)
+__device__ __forceinline__ int lut16(const uint4& t, unsigned n) {
+    const uint32_t lo = (n & 4u) ? t.y : t.x, hi = (n & 4u) ? t.w : t.z;
+    const uint32_t w = (n & 8u) ? hi : lo;
+    return (int)(int8_t)__byte_perm(w, 0u, n & 3u);
+}
+__device__ __forceinline__ uint4 ld_table(const int8_t* lut, int k) { return __ldg(reinterpret_cast<const uint4*>(lut) + k); }
+
+// int16-wraparound sums of K lookups for one byte lane (SignedWideningAdder, tbl.cc:216-235: _mm256_add_epi16 wraps)
+__device__ __forceinline__ void lane_sums_i16(const int8_t* lut, const uint8_t* a, int k0, int nk, int& bot, int& top) {
+    int b = 0, t = 0;
+    for (int k = 0; k < nk; ++k) {
+        const uint4 tab = ld_table(lut, k0 + k);
+        const unsigned v = a[(size_t)(k0 + k) * 16];
+        b += lut16(tab, v & 15u);
+        t += lut16(tab, v >> 4);
+    }
+    bot = (int)(int16_t)b;                       // a wrapped int16 sum equals the exact sum reduced modulo 2^16
+    top = (int)(int16_t)t;
+}
+
+// tbl.cc:586-627
+__global__ void tbl_int32_update_kernel(int m, int32_t* __restrict__ c, const int8_t* __restrict__ lut,
+                                        const uint8_t* __restrict__ a, int K) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;             // byte lane: block t / 16, l = t % 16
+    if (t >= m / 2) return;
+    const int i = (t >> 4) << 4, l = t & 15;
+    int bot, top;
+    lane_sums_i16(lut, a + (size_t)i * K + l, 0, K, bot, top);
+    c[i * 2 + l] += bot;
+    c[i * 2 + 16 + l] += top;
+}
+
+__device__ __forceinline__ int get_bias_scale(int bits) { return bits == 4 ? 15 : bits == 3 ? 7 : bits == 2 ? 3 : bits == 1 ? 1 : 0; }   // tbl.cc:300-317
+__device__ __forceinline__ int mylog2(int k) { int r = -1; while (k) { ++r; k >>= 1; } return r; }                                         // tbl.cc:239-250
+
+// SignedHalvingAdder (tbl.cc:169-215): a binary tree of _mm256_avg_epu8 = UNSIGNED rounding averages of the raw bytes
+__device__ __forceinline__ void lane_sums_halving(const int8_t* lut, const uint8_t* a, int k0, int act_k, int& bot, int& top) {
+    uint8_t bb[64], tt[64];
+    for (int k = 0; k < act_k; ++k) {
+        const uint4 tab = ld_table(lut, k0 + k);
+        const unsigned v = a[(size_t)(k0 + k) * 16];
+        bb[k] = (uint8_t)lut16(tab, v & 15u);
+        tt[k] = (uint8_t)lut16(tab, v >> 4);
+    }
+    for (int n = act_k; n > 1; n >>= 1)
+        for (int j = 0; j < n / 2; ++j) {
+            bb[j] = (uint8_t)(((unsigned)bb[2 * j] + (unsigned)bb[2 * j + 1] + 1u) >> 1);
+            tt[j] = (uint8_t)(((unsigned)tt[2 * j] + (unsigned)tt[2 * j + 1] + 1u) >> 1);
+        }
+    bot = (int)(int8_t)bb[0];
+    top = (int)(int8_t)tt[0];
+}
+
+// One byte lane of tbl_g4_int8_float_update_impl (tbl.cc:433-520): returns the two finished outputs.
+// Lane (block i/16, l): low nibble -> sub-block s = l / 8, high nibble -> s = 2 + l / 8, element e = l % 8; ib = i/4 + s.
+struct TblFloatCfg { int K, bits, act_k, fast_aggregation, zero_point; };
+__device__ __forceinline__ void tbl_float_lane(const TblFloatCfg& g, int i, int l, float c_bot, float c_top, const int8_t* lut,
+                                               const uint8_t* a_lane, const float* scales, const float* lut_scales,
+                                               const float* lut_biases, float& out_bot, float& out_top) {
+    const int e = l & 7, ib_bot = i / 4 + (l >> 3), ib_top = ib_bot + 2;
+    float vb = 0.f, vt = 0.f;
+    float partial_sum = -0.0f;
+    for (int kk = 0; kk < g.K; kk += g.act_k) {
+        int bot, top;
+        if (g.fast_aggregation) lane_sums_halving(lut, a_lane, kk, g.act_k, bot, top);
+        else lane_sums_i16(lut, a_lane, kk, g.act_k, bot, top);
+        float lut_s = __ldg(lut_scales + kk / g.act_k);
+        float lut_b = __ldg(lut_biases + kk / g.act_k);
+        partial_sum = __fadd_rn(partial_sum, lut_b);
+        if (g.fast_aggregation) {
+            lut_s = __fmul_rn(lut_s, (float)g.act_k);
+            lut_b = __fsub_rn(lut_b, __fmul_rn(lut_s, (float)(mylog2(g.act_k) / 4 * get_bias_scale(g.bits))));
+        }
+        const float fb = (float)bot, ft = (float)top;
+        const float xb = (ib_bot % g.bits) ? __fmul_rn(fb, lut_s) : fmaf(fb, lut_s, lut_b);
+        const float xt = (ib_top % g.bits) ? __fmul_rn(ft, lut_s) : fmaf(ft, lut_s, lut_b);
+        vb = (kk == 0) ? xb : __fadd_rn(vb, xb);
+        vt = (kk == 0) ? xt : __fadd_rn(vt, xt);
+    }
+    if (g.zero_point) {
+        partial_sum = __fmul_rn(partial_sum, 2.f);
+        const float* sb = scales + (ib_bot / g.bits) * 16;
+        const float* st = scales + (ib_top / g.bits) * 16;
+        const float tb = fmaf(vb, __ldg(sb + e), c_bot), tt = fmaf(vt, __ldg(st + e), c_top);
+        out_bot = (ib_bot % g.bits) ? tb : fmaf(__ldg(sb + 8 + e), partial_sum, tb);
+        out_top = (ib_top % g.bits) ? tt : fmaf(__ldg(st + 8 + e), partial_sum, tt);
+    } else {
+        out_bot = fmaf(vb, __ldg(scales + (ib_bot / g.bits) * 8 + e), c_bot);
+        out_top = fmaf(vt, __ldg(scales + (ib_top / g.bits) * 8 + e), c_top);
+    }
+}
+
+__global__ void tbl_float_update_kernel(int m, float* __restrict__ c, const int8_t* __restrict__ lut, const uint8_t* __restrict__ a,
+                                        const float* __restrict__ scales, const float* __restrict__ lut_scales,
+                                        const float* __restrict__ lut_biases, TblFloatCfg g) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= m / 2) return;
+    const int i = (t >> 4) << 4, l = t & 15;
+    float ob, ot;
+    tbl_float_lane(g, i, l, c[i * 2 + l], c[i * 2 + 16 + l], lut, a + (size_t)i * g.K + l, scales, lut_scales, lut_biases, ob, ot);
+    c[i * 2 + l] = ob;
+    c[i * 2 + 16 + l] = ot;
+}
+
+// ---- lut_ctor.cc ----
+// abs-sum maximum of 8 groups of 4 activations / 127 (lut_ctor.cc:241-259); std::max(*lut_scales, scales) = (a < b) ? b : a
+__device__ __forceinline__ float partial_max32(const float* b) {
+    float mx = -INFINITY;
+    for (int j = 0; j < 8; ++j) {
+        const float s = __fadd_rn(__fadd_rn(fabsf(b[4 * j]), fabsf(b[4 * j + 1])), __fadd_rn(fabsf(b[4 * j + 2]), fabsf(b[4 * j + 3])));
+        mx = fmaxf(mx, s);                      // _mm_max_ps on non-NaN data
+    }
+    return __fdiv_rn(mx, 127.f);
+}
+__global__ void partial_max_kernel(float* lut_scales, const float* __restrict__ b) {
+    const float s = partial_max32(b);
+    if (*lut_scales < s) *lut_scales = s;
+}
+
+// One CTA of 128 threads per independent (scale, bias) segment of act_k activations; thread = (group j, entry g).
+// preprocess != 0: the segment's scale is first recomputed as partial_max_reset + partial_max (act_k must be 32).
+__global__ void __launch_bounds__(128) lut_ctor_kernel(int act_k, int8_t* __restrict__ qlut, const float* __restrict__ b,
+                                                       float* __restrict__ lut_scales, float* __restrict__ lut_biases, int preprocess) {
+    const int seg = blockIdx.x, j = threadIdx.x >> 4, g = threadIdx.x & 15;
+    b += (size_t)seg * act_k;
+    qlut += (size_t)seg * act_k * 4;
+    __shared__ float e0[8];
+    __shared__ float s_scale;
+    if (threadIdx.x == 0) {
+        float s = lut_scales[seg];
+        if (preprocess) { const float p = partial_max32(b); s = (0.0f < p) ? p : 0.0f; }
+        s_scale = s;
+    }
+    __syncthreads();
+    const float scales = s_scale;
+    const float t_scales = scales ? __fdiv_rn(1.0f, scales) : 0.0f;
+    float biases = 0.0f;
+    for (int k = 0; k < act_k / 32; ++k) {
+        const float* bj = b + k * 32 + 4 * j;
+        // odd g: ((b0 +- b1) +- b2) +- b3 with + where bit 1 / 2 / 3 of g is set; even g: -(entry 15 - g)   (lut_ctor.cc:133-176)
+        const int go = (g & 1) ? g : 15 - g;
+        float v = bj[0];
+        v = (go & 2) ? __fadd_rn(v, bj[1]) : __fsub_rn(v, bj[1]);
+        v = (go & 4) ? __fadd_rn(v, bj[2]) : __fsub_rn(v, bj[2]);
+        v = (go & 8) ? __fadd_rn(v, bj[3]) : __fsub_rn(v, bj[3]);
+        if (!(g & 1)) v = -v;
+        if (g == 0) e0[j] = v;
+        float r = rintf(__fmul_rn(v, t_scales));            // _mm256_round_ps(NEAREST) -> cvtps_epi32 -> packs (saturating)
+        r = fminf(fmaxf(r, -128.f), 127.f);
+        qlut[k * 128 + j * 16 + g] = (int8_t)(int)r;
+        __syncthreads();
+        // _mm256_addv_ps order (lut_ctor.cc:26-32): ((v0+v4) + (v2+v6)) + ((v1+v5) + (v3+v7))
+        if (threadIdx.x == 0)
+            biases = __fadd_rn(biases, __fadd_rn(__fadd_rn(__fadd_rn(e0[0], e0[4]), __fadd_rn(e0[2], e0[6])),
+                                                 __fadd_rn(__fadd_rn(e0[1], e0[5]), __fadd_rn(e0[3], e0[7]))));
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { lut_scales[seg] = scales; lut_biases[seg] = biases; }
+}
+
+// qgemm_lut_t1_int8_m{bm}_k{K}_n1_b{bits} (kernels.cc:827-960), one CTA per tile of bm bit-plane rows, a thread per byte
+// lane: CBits stays in registers over the K/32 sequential tbl_g4_int8_float_update(k8, ak8) calls, then goes through
+// shared memory for the bit-plane combination C = ((c0 * 0.5 + c1) + c2 * 2) + c3 * 4.
+__global__ void tmac_qgemm_kernel(int K, int bits, int bm, const uint8_t* __restrict__ A, const int8_t* __restrict__ qlut,
+                                  const float* __restrict__ scales, const float* __restrict__ lut_scales,
+                                  const float* __restrict__ lut_biases, float* __restrict__ C) {
+    extern __shared__ float cbits[];
+    const int tile = blockIdx.x, kt_n = K / 32, lanes = bm / 2;
+    const TblFloatCfg g{8, bits, 8, 0, 0};
+    for (int t = threadIdx.x; t < lanes; t += blockDim.x) {
+        const int i = (t >> 4) << 4, l = t & 15;
+        float cb = 0.f, ct = 0.f;                                    // tbl_float_reset
+        for (int kt = 0; kt < kt_n; ++kt) {
+            const size_t blk = (size_t)tile * kt_n + kt;
+            float ob, ot;
+            tbl_float_lane(g, i, l, cb, ct, qlut + (size_t)kt * 128, A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8 + l,
+                           scales + blk * (size_t)(bm / bits), lut_scales + kt, lut_biases + kt, ob, ot);
+            cb = ob; ct = ot;
+        }
+        cbits[i * 2 + l] = cb;
+        cbits[i * 2 + 16 + l] = ct;
+    }
+    __syncthreads();
+    const float alphas[4] = {0.5f, 1.f, 2.f, 4.f};
+    const int n_out = bm / bits;
+    for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
+        const int j = o >> 3, e = o & 7;
+        float acc = __fmul_rn(cbits[8 * bits * j + e], alphas[0]);
+        for (int bp = 1; bp < bits; ++bp) acc = __fadd_rn(acc, __fmul_rn(cbits[8 * bits * j + 8 * bp + e], alphas[bp]));
+        C[(size_t)tile * n_out + o] = acc;
+    }
+}
+
+static int need_device() {
+    DeviceInfo di;
+    return get_device_info(&di);                     // no device: LUTVQ_ECUDA, there is no CPU fallback
+}
+
+}  // namespace lutvq
+
+using namespace lutvq;
+
+extern "C" {
+
+int lutvq_tbl_g4_int8_int32_update(int m, void* c, const void* lut, const void* a, int K, void* stream) {
+    LUTVQ_REQUIRE(c && lut && a, "null pointer");
+    LUTVQ_REQUIRE(m > 0 && m % 32 == 0 && K > 0, "m=%d must be a positive multiple of 32 and K=%d positive (tbl.cc:586 walks blocks of 32 outputs)", m, K);
+    LUTVQ_REQUIRE(aligned16(lut), "lut must be 16-byte aligned (one table = one 128-bit load)");
+    if (int rc = need_device()) return rc;
+    const int lanes = m / 2;
+    tbl_int32_update_kernel<<<ceil_div(lanes, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        m, static_cast<int32_t*>(c), static_cast<const int8_t*>(lut), static_cast<const uint8_t*>(a), K);
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+int lutvq_tbl_g4_int8_float_update(int m, void* c, const void* lut, const void* a, const void* scales, const void* lut_scales,
+                                   const void* lut_biases, int K, int bits, int act_k, int fast_aggregation, int zero_point,
+                                   void* stream) {
+    LUTVQ_REQUIRE(c && lut && a && scales && lut_scales && lut_biases, "null pointer");
+    LUTVQ_REQUIRE(m > 0 && m % 32 == 0, "m=%d must be a positive multiple of 32", m);
+    LUTVQ_REQUIRE(bits >= 1 && bits <= 4, "bits=%d must be 1..4 (tbl.cc:300-317)", bits);
+    LUTVQ_REQUIRE(act_k > 0 && K > 0 && K % act_k == 0, "K=%d must be a positive multiple of act_k=%d", K, act_k);
+    LUTVQ_REQUIRE(!fast_aggregation || (act_k <= 64 && (act_k & (act_k - 1)) == 0), "fast aggregation needs a power-of-two act_k <= 64, got %d", act_k);
+    LUTVQ_REQUIRE(aligned16(lut), "lut must be 16-byte aligned (one table = one 128-bit load)");
+    if (int rc = need_device()) return rc;
+    const TblFloatCfg g{K, bits, act_k, fast_aggregation ? 1 : 0, zero_point ? 1 : 0};
+    tbl_float_update_kernel<<<ceil_div(m / 2, 128), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        m, static_cast<float*>(c), static_cast<const int8_t*>(lut), static_cast<const uint8_t*>(a), static_cast<const float*>(scales),
+        static_cast<const float*>(lut_scales), static_cast<const float*>(lut_biases), g);
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+static int reset_bytes(void* c, long long bytes, void* stream) {
+    LUTVQ_REQUIRE(c != nullptr && bytes >= 0, "null pointer or negative size");
+    if (int rc = need_device()) return rc;
+    LUTVQ_CUDA_OK(cudaMemsetAsync(c, 0, (size_t)bytes, static_cast<cudaStream_t>(stream)));
+    return LUTVQ_OK;
+}
+int lutvq_tbl_int8_reset(int m, void* c, void* stream)  { return reset_bytes(c, (long long)m, stream); }
+int lutvq_tbl_int16_reset(int m, void* c, void* stream) { return reset_bytes(c, (long long)m * 2, stream); }
+int lutvq_tbl_int32_reset(int m, void* c, void* stream) { return reset_bytes(c, (long long)m * 4, stream); }
+int lutvq_tbl_float_reset(int m, void* c, void* stream) { return reset_bytes(c, (long long)m * 4, stream); }
+int lutvq_partial_max_reset(void* lut_scales, void* stream) { return reset_bytes(lut_scales, 4, stream); }
+
+int lutvq_partial_max_g4_int8_k8(void* lut_scales, const void* b, void* stream) {
+    LUTVQ_REQUIRE(lut_scales && b, "null pointer");
+    if (int rc = need_device()) return rc;
+    partial_max_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<float*>(lut_scales), static_cast<const float*>(b));
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+int lutvq_lut_ctor_g4_int8(int act_k, void* qlut, const void* b, void* lut_scales, void* lut_biases, void* stream) {
+    LUTVQ_REQUIRE(qlut && b && lut_scales && lut_biases, "null pointer");
+    LUTVQ_REQUIRE(act_k > 0 && act_k % 32 == 0, "act_k=%d must be a positive multiple of 32 (lut_ctor.cc:127)", act_k);
+    if (int rc = need_device()) return rc;
+    lut_ctor_kernel<<<1, 128, 0, static_cast<cudaStream_t>(stream)>>>(act_k, static_cast<int8_t*>(qlut), static_cast<const float*>(b),
+                                                                     static_cast<float*>(lut_scales), static_cast<float*>(lut_biases), 0);
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+int lutvq_tmac_preprocessor_int8(int K, const void* B, void* lut_scales, void* lut_biases, void* qlut, void* stream) {
+    LUTVQ_REQUIRE(B && lut_scales && lut_biases && qlut, "null pointer");
+    LUTVQ_REQUIRE(K > 0 && K % 32 == 0, "K=%d must be a positive multiple of 32", K);
+    if (int rc = need_device()) return rc;
+    lut_ctor_kernel<<<K / 32, 128, 0, static_cast<cudaStream_t>(stream)>>>(32, static_cast<int8_t*>(qlut), static_cast<const float*>(B),
+                                                                          static_cast<float*>(lut_scales), static_cast<float*>(lut_biases), 1);
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, const void* qlut, const void* scales,
+                              const void* lut_scales, const void* lut_biases, void* C, void* stream) {
+    LUTVQ_REQUIRE(A && qlut && scales && lut_scales && lut_biases && C, "null pointer");
+    LUTVQ_REQUIRE(bits >= 1 && bits <= 4, "bits=%d must be 1..4", bits);
+    LUTVQ_REQUIRE(K > 0 && K % 32 == 0, "K=%d must be a positive multiple of 32", K);
+    // the reference returns -1 when no tuned kernel matches (deploy/tuned/kernels.h): here the shape rules are explicit
+    if (!(bm > 0 && bm % 32 == 0 && bm % (8 * bits) == 0 && bm <= 8192 && M > 0 && ((long long)M * bits) % bm == 0))
+        return fail(LUTVQ_EUNSUPPORTED, "no kernel for M=%d bits=%d bm=%d: bm must be a multiple of 32 and of 8*bits, <= 8192, and divide M*bits", M, bits, bm);
+    LUTVQ_REQUIRE(aligned16(qlut), "qlut must be 16-byte aligned");
+    if (int rc = need_device()) return rc;
+    const int tiles = (int)((long long)M * bits / bm);
+    int threads = bm / 2;
+    if (threads > 256) threads = 256;
+    threads = (threads + 31) / 32 * 32;
+    tmac_qgemm_kernel<<<tiles, threads, (size_t)bm * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
+        K, bits, bm, static_cast<const uint8_t*>(A), static_cast<const int8_t*>(qlut), static_cast<const float*>(scales),
+        static_cast<const float*>(lut_scales), static_cast<const float*>(lut_biases), static_cast<float*>(C));
+    LUTVQ_CUDA_OK(cudaGetLastError());
+    return LUTVQ_OK;
+}
+
+}  // extern "C"

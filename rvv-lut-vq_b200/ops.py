@@ -306,6 +306,82 @@ def codeKx8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Option
     return W
 
 
+def _check_1x16(codes: torch.Tensor, codebooks: torch.Tensor) -> int:
+    if codes.dtype != torch.int16:
+        raise TypeError(f"1x16 codes must be int16, got {codes.dtype}")
+    gs = codebooks.size(3)
+    if gs not in (8, 16):                                   # cuda_kernel.cpp:136-145
+        raise NotImplementedError(f"AQLM CUDA kernels only support codebooks with 8 or 16 features. Got {gs}.")
+    if codebooks.size(0) != 1 or codebooks.size(1) != 65536 or codebooks.size(2) != 1:
+        raise NotImplementedError(f"1x16 kernels take codebooks [1, 65536, 1, 8|16], got {tuple(codebooks.shape)}")
+    return gs
+
+
+def code1x16_matvec(A: torch.Tensor, B: torch.Tensor, C: torch.Tensor, codebook: torch.Tensor, use_bfloat16: bool) -> None:
+    """code1x16_matvec (cuda_kernel.cpp:113-146): C[prob_m] = round(W(A) . B), raw launcher semantics (no scale); A = codes.squeeze(2)."""
+    dev = _require_cuda(A, B, C, codebook)
+    gs = _check_1x16(A, codebook)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code1x16_matvec(_ptr(A.contiguous()), _ptr(B.contiguous()), _ptr(C), _ptr(codebook.contiguous()), C.size(0), B.size(0), gs,
+                                          _lib.LUTVQ_BF16 if use_bfloat16 else _lib.LUTVQ_F16, _stream(dev)))
+
+
+def code1x16_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                    bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x16_matmat (cuda_kernel.cpp:148-179): codes int16 [O, I/gs, 1], codebooks [1, 65536, 1, gs]."""
+    dtype = check_use_bfloat16(input)
+    dev = _require_cuda(input, codes, codebooks, scales, bias)
+    gs = _check_1x16(codes, codebooks)
+    in_features, out_features = input.size(-1), codes.size(0)
+    flat = input.reshape(-1, in_features).contiguous()
+    y = torch.empty((flat.size(0), out_features), dtype=input.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code1x16_matmat(_ptr(flat), _ptr(codes.contiguous()), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)),
+                                          _ptr(None if bias is None else bias.contiguous()), _ptr(y), flat.size(0), out_features, in_features, gs,
+                                          dtype, _stream(dev)))
+    return y.reshape(tuple(input.shape[:-1]) + (out_features,))
+
+
+def code1x16_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:
+    """code1x16_dequant (cuda_kernel.cpp:181-209): W fp16/bf16 [O, I] = codebook[code] * scales, bit-exact."""
+    dtype = check_use_bfloat16(codebooks)
+    dev = _require_cuda(codes, codebooks, scales)
+    gs = _check_1x16(codes, codebooks)
+    O, G = codes.size(0), codes.size(1)
+    W = torch.empty((O, G * gs), dtype=codebooks.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_code1x16_dequant(_ptr(codes.contiguous()), _ptr(W), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)), O, G * gs, gs,
+                                           dtype, _stream(dev)))
+    return W
+
+
+def _scale_bias_unflatten(flat_output: torch.Tensor, scales: torch.Tensor, bias: Optional[torch.Tensor], input_shape) -> torch.Tensor:
+    """scale_bias_unflatten_output (cuda_kernel.cpp:95-111)"""
+    flat_output = flat_output * scales.flatten().unsqueeze(0)
+    if bias is not None:
+        flat_output = flat_output + bias.unsqueeze(0)
+    return flat_output.reshape(tuple(input_shape[:-1]) + (flat_output.size(-1),)).clone()
+
+
+def code1x16_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x16_matmat_dequant (cuda_kernel.cpp:229-283): our dequantize kernel (no scale), then the plain library GEMM the
+    reference also calls (F.linear = cuBLAS), then the reference's epilogue."""
+    check_use_bfloat16(input)
+    W = code1x16_dequant(codes, codebooks, None)
+    flat = input.reshape(-1, input.size(-1))
+    return _scale_bias_unflatten(torch.nn.functional.linear(flat, W), scales, bias, input.shape)
+
+
+def code1x16_matmat_dequant_transposed(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                                       bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x16_matmat_dequant_transposed (cuda_kernel.cpp:285-354): (input * scales) @ W (the backward-pass product)."""
+    check_use_bfloat16(codebooks)
+    W = code1x16_dequant(codes, codebooks, None)
+    scaled = (input.reshape(-1, input.size(-1)) * scales.flatten().unsqueeze(0)).reshape(input.shape)
+    return torch.nn.functional.linear(scaled, W.transpose(0, 1), bias)
+
+
 def simd_lut_lookup_add(idx: torch.Tensor, lut: torch.Tensor, output: torch.Tensor, n_runs: int) -> torch.Tensor:
     """lookup_and_add_simd, _SCALAR_ semantics (benchmark/kernel/simd_lut/bench_avx_lut.cpp:26-138, :98-107):
     output[k] += lut[idx[j, k]] for every row j, repeated n_runs times, int16 wraparound.  idx uint8 [n_lut_per_run, CB],
@@ -324,3 +400,98 @@ def simd_lut_lookup_add(idx: torch.Tensor, lut: torch.Tensor, output: torch.Tens
         check(lib().lutvq_simd_lut_lookup_add(_ptr(idx), _ptr(lut.contiguous()), _ptr(output), cb, lut.numel(), int(n_runs), idx.size(0),
                                               _ptr(ws), ws.numel(), _stream(dev)))
     return output
+
+
+# ---- T-MAC bit-serial integer LUT (benchmark/kernel/bs_lut_gemm/tbl.cc, lut_ctor.cc; include/lutvq.h) ----
+def _tmac_check(t: torch.Tensor, dtype: torch.dtype, name: str) -> torch.Tensor:
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def tbl_g4_int8_int32_update(m: int, c: torch.Tensor, lut: torch.Tensor, a: torch.Tensor, K: int) -> torch.Tensor:
+    """tbl_g4_int8_int32_update_impl<K, Bits> (tbl.cc:536-630): c int32[m] accumulated in place and returned."""
+    dev = _require_cuda(c, lut, a)
+    assert c.is_contiguous() and c.dtype == torch.int32 and c.numel() >= m
+    with torch.cuda.device(dev):
+        check(lib().lutvq_tbl_g4_int8_int32_update(m, _ptr(c), _ptr(_tmac_check(lut, torch.int8, "lut")), _ptr(_tmac_check(a, torch.uint8, "a")),
+                                                   K, _stream(dev)))
+    return c
+
+
+def tbl_g4_int8_float_update(m: int, c: torch.Tensor, lut: torch.Tensor, a: torch.Tensor, scales: torch.Tensor, lut_scales: torch.Tensor,
+                             lut_biases: torch.Tensor, K: int, bits: int, act_k: int, fast_aggregation: bool = False,
+                             zero_point: bool = False) -> torch.Tensor:
+    """tbl_g4_int8_float_update_impl<has_scale, K, Bits, ActK, FastAggregation, ZeroPoint, OneScale> (tbl.cc:323-532), x86 path."""
+    dev = _require_cuda(c, lut, a, scales, lut_scales, lut_biases)
+    assert c.is_contiguous() and c.dtype == torch.float32 and c.numel() >= m
+    f32 = torch.float32
+    with torch.cuda.device(dev):
+        check(lib().lutvq_tbl_g4_int8_float_update(m, _ptr(c), _ptr(_tmac_check(lut, torch.int8, "lut")), _ptr(_tmac_check(a, torch.uint8, "a")),
+                                                   _ptr(_tmac_check(scales, f32, "scales")), _ptr(_tmac_check(lut_scales, f32, "lut_scales")),
+                                                   _ptr(_tmac_check(lut_biases, f32, "lut_biases")), K, bits, act_k, int(fast_aggregation),
+                                                   int(zero_point), _stream(dev)))
+    return c
+
+
+def tbl_reset(c: torch.Tensor) -> torch.Tensor:
+    """tbl_{int8,int16,int32,float}_reset (tbl.cc:697-715)."""
+    dev = _require_cuda(c)
+    fn = {torch.int8: "lutvq_tbl_int8_reset", torch.int16: "lutvq_tbl_int16_reset", torch.int32: "lutvq_tbl_int32_reset",
+          torch.float32: "lutvq_tbl_float_reset"}[c.dtype]
+    with torch.cuda.device(dev):
+        check(getattr(lib(), fn)(c.numel(), _ptr(c), _stream(dev)))
+    return c
+
+
+def partial_max_reset(lut_scales: torch.Tensor) -> torch.Tensor:
+    dev = _require_cuda(lut_scales)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_partial_max_reset(_ptr(lut_scales), _stream(dev)))
+    return lut_scales
+
+
+def partial_max_g4_int8_k8(lut_scales: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """partial_max_g4_int8_k8 (lut_ctor.cc:232-259) over the 32 activations at b; lut_scales: float32 view of ONE element."""
+    dev = _require_cuda(lut_scales, b)
+    assert lut_scales.dtype == torch.float32 and b.dtype == torch.float32 and b.is_contiguous() and b.numel() >= 32
+    with torch.cuda.device(dev):
+        check(lib().lutvq_partial_max_g4_int8_k8(_ptr(lut_scales), _ptr(b), _stream(dev)))
+    return lut_scales
+
+
+def lut_ctor_g4_int8(act_k: int, b: torch.Tensor, lut_scales: torch.Tensor):
+    """lut_ctor_g4_int8_impl (lut_ctor.cc:38-221) -> (qlut int8 [act_k/4, 16], lut_scales, lut_biases float32 [1])."""
+    dev = _require_cuda(b, lut_scales)
+    assert b.dtype == torch.float32 and b.is_contiguous() and b.numel() >= act_k and lut_scales.dtype == torch.float32
+    qlut = torch.empty((act_k // 4, 16), dtype=torch.int8, device=dev)
+    biases = torch.zeros(1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_lut_ctor_g4_int8(act_k, _ptr(qlut), _ptr(b), _ptr(lut_scales), _ptr(biases), _stream(dev)))
+    return qlut, lut_scales, biases
+
+
+def tmac_preprocessor_int8(B: torch.Tensor):
+    """preprocessor_t1_int8_* (T-MAC deploy/tuned/kernels.cc:1002-1037) -> (qlut int8 [K/4, 16], lut_scales [K/32], lut_biases [K/32])."""
+    dev = _require_cuda(B)
+    assert B.dtype == torch.float32 and B.dim() == 1 and B.is_contiguous()
+    K = B.numel()
+    qlut = torch.empty((K // 4, 16), dtype=torch.int8, device=dev)
+    ls = torch.empty(K // 32, dtype=torch.float32, device=dev)
+    lb = torch.empty(K // 32, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_tmac_preprocessor_int8(K, _ptr(B), _ptr(ls), _ptr(lb), _ptr(qlut), _stream(dev)))
+    return qlut, ls, lb
+
+
+def tmac_qgemm_lut_int8(M: int, K: int, bits: int, bm: int, A: torch.Tensor, qlut: torch.Tensor, scales: torch.Tensor,
+                        lut_scales: torch.Tensor, lut_biases: torch.Tensor) -> torch.Tensor:
+    """qgemm_lut_t1_int8_m{bm}_k{K}_n1_b{bits} (T-MAC deploy/tuned/kernels.cc:827-960) -> C float32 [M]."""
+    dev = _require_cuda(A, qlut, scales, lut_scales, lut_biases)
+    f32 = torch.float32
+    C = torch.empty(M, dtype=f32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().lutvq_tmac_qgemm_lut_int8(M, K, bits, bm, _ptr(_tmac_check(A, torch.uint8, "A")), _ptr(_tmac_check(qlut, torch.int8, "qlut")),
+                                              _ptr(_tmac_check(scales, f32, "scales")), _ptr(_tmac_check(lut_scales, f32, "lut_scales")),
+                                              _ptr(_tmac_check(lut_biases, f32, "lut_biases")), _ptr(C), _stream(dev)))
+    return C

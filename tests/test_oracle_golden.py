@@ -200,3 +200,23 @@ def test_tmac_oracle_vs_reference_build_random(orc):
         ref.lut_ctor_g4_int8_k0_b4(32, P(q), P(b), P(s2), P(b2))
         gq, gs, gb = orc.c_lut_ctor_g4_int8(32, b, float(s[0]))
         assert np.array_equal(gq, q) and np.float32(gb).view(np.uint32) == b2.view(np.uint32)[0]
+
+
+@pytest.mark.parametrize("name", ["aqlm_1x16_g8_i256_o48", "aqlm_1x16_g16_i512_o40"])
+def test_aqlm_1x16_dequantize_bit_exact(orc, golden_dir, name):
+    """1x16 (a12): the oracle's gather (* scale) vs the reference's unpack_int_data + _dequantize_weight outputs, bit for bit;
+    the float64 dense product of those weights vs the reference's F.linear check."""
+    g = _load(golden_dir, name)
+    I, O, gs, B, seed, wb = [int(v) for v in g["cfg"]]
+    cb = orc.codebook_1x16(seed, gs)
+    assert int(cb.view(np.uint16).astype(np.uint64).sum()) == int(g["codebook_checksum"][0]), "codebook regeneration drifted"
+    assert np.array_equal(orc.np_unpack_int_data(g["codes"], 16)[..., 0], g["idx"][..., 0].astype(np.int64))
+    assert np.array_equal(orc.np_pack_int_data(g["idx"].astype(np.int64), 16), g["codes"])
+    W = orc.np_aqlm_1x16_dequantize(g["codes"], cb, None)
+    Ws = orc.np_aqlm_1x16_dequantize(g["codes"], cb, g["scales"])
+    assert np.array_equal(W.view(np.uint16), g["weight_f16_noscale"].view(np.uint16))
+    assert np.array_equal(Ws.view(np.uint16), g["weight_f16_scaled"].view(np.uint16))
+    y64 = np.stack([orc.c_dense_gemv_f64(g["x"][b], W) for b in range(B)]) * g["scales"].reshape(1, -1).astype(np.float64)
+    if wb:
+        y64 = y64 + g["bias"].astype(np.float64)
+    assert np.abs(y64 - g["y_dense"]).max() / np.abs(g["y_dense"]).max() < 1e-5
