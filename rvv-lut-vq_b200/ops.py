@@ -382,6 +382,44 @@ def code1x16_matmat_dequant_transposed(input: torch.Tensor, codes: torch.Tensor,
     return torch.nn.functional.linear(scaled, W.transpose(0, 1), bias)
 
 
+def code2x8_matmat_dequant_transposed(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                                      bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code2x8_matmat_dequant_transposed (cuda_kernel.cpp:486-519): (input * scales) @ W -- the input-gradient product of the
+    reference's autograd op.  Our dequantize kernel (no scale) + the plain library GEMM the reference also calls."""
+    check_use_bfloat16(codebooks)
+    W = code2x8_dequant(codes, codebooks, None)
+    scaled = (input.reshape(-1, input.size(-1)) * scales.flatten().unsqueeze(0)).reshape(input.shape)
+    return torch.nn.functional.linear(scaled, W.transpose(0, 1), bias)
+
+
+def code1x8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x8_matmat (cuda_kernel.cpp:550-584): one 256-entry codebook; the N = 1 case of codeKx8_matmat."""
+    return codeKx8_matmat(input, codes, codebooks, scales, bias)
+
+
+def code1x8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:
+    """code1x8_dequant (cuda_kernel.cpp:586-611)."""
+    return codeKx8_dequant(codes, codebooks, scales)
+
+
+def code1x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                           bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x8_matmat_dequant (cuda_kernel.cpp:613-647): dequantize (our kernel) + library GEMM + the reference's epilogue."""
+    check_use_bfloat16(input)
+    W = codeKx8_dequant(codes, codebooks, None)
+    return _scale_bias_unflatten(torch.nn.functional.linear(input.reshape(-1, input.size(-1)), W), scales, bias, input.shape)
+
+
+def code1x8_matmat_dequant_transposed(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                                      bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """code1x8_matmat_dequant_transposed (cuda_kernel.cpp:649-684)."""
+    check_use_bfloat16(codebooks)
+    W = codeKx8_dequant(codes, codebooks, None)
+    scaled = (input.reshape(-1, input.size(-1)) * scales.flatten().unsqueeze(0)).reshape(input.shape)
+    return torch.nn.functional.linear(scaled, W.transpose(0, 1), bias)
+
+
 def simd_lut_lookup_add(idx: torch.Tensor, lut: torch.Tensor, output: torch.Tensor, n_runs: int) -> torch.Tensor:
     """lookup_and_add_simd, _SCALAR_ semantics (benchmark/kernel/simd_lut/bench_avx_lut.cpp:26-138, :98-107):
     output[k] += lut[idx[j, k]] for every row j, repeated n_runs times, int16 wraparound.  idx uint8 [n_lut_per_run, CB],

@@ -506,3 +506,77 @@ def test_simd_lut_full_size_is_n_runs_times_one_run(pkg, ops, orc):
     got = ops.simd_lut_lookup_add(cu(idx), cu(lut), torch.zeros(16, dtype=torch.int16, device="cuda"), 100000)
     torch.cuda.synchronize()
     assert np.array_equal(got.cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------ torch.ops.aqlm.* registration and module dispatch (a11)
+def test_torch_ops_aqlm_registered_and_equal(pkg, ops):
+    """the reference's op names (cuda_kernel.py:13-132) resolve to liblutvq and agree bit for bit with the python front end"""
+    from rvv_lut_vq_b200 import synth, torch_ops  # noqa: F401
+    L = synth.make_layer_np(512, 96, seed=3, scales="randn", bias=True, batch=3)
+    x, codes, cb, sc, bi = cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]), cu(L["bias"])
+    for name in ("code1x16_matmat", "code1x16_matmat_dequant", "code1x16_matmat_dequant_transposed", "code2x8_matmat", "code2x8_matmat_dequant",
+                 "code2x8_matmat_dequant_transposed", "code1x8_matmat", "code1x8_matmat_dequant", "code1x8_matmat_dequant_transposed"):
+        assert hasattr(torch.ops.aqlm, name), name
+    y_op = torch.ops.aqlm.code2x8_matmat(x, codes, cb, sc, bi)
+    assert torch.equal(y_op.view(torch.int16), ops.code2x8_matmat(x, codes, cb, sc, bi).view(torch.int16))
+    y_nb = torch.ops.aqlm.code2x8_matmat(x, codes, cb, sc, None)                      # bias-free layers pass None
+    assert torch.equal(y_nb.view(torch.int16), ops.code2x8_matmat(x, codes, cb, sc, None).view(torch.int16))
+    xb = torch.randn((16, 512), dtype=torch.float16, device="cuda")
+    assert torch.equal(torch.ops.aqlm.code2x8_matmat_dequant(xb, codes, cb, sc, bi).view(torch.int16),
+                       ops.code2x8_matmat_dequant(xb, codes, cb, sc, bi).view(torch.int16))
+    # transposed op = (g * scales) @ W   (cuda_kernel.cpp:486-519)
+    g = torch.randn((2, 96), dtype=torch.float16, device="cuda")
+    W = ops.code2x8_dequant(codes, cb, None)
+    want = (g.double() * sc.reshape(1, -1).double()) @ W.double()
+    got = torch.ops.aqlm.code2x8_matmat_dequant_transposed(g, codes, cb, sc, None)
+    assert rel_err(got.double().cpu().numpy(), want.cpu().numpy()) <= 4e-3
+    with pytest.raises((NotImplementedError, RuntimeError)):                            # no CPU implementation is registered
+        torch.ops.aqlm.code2x8_matmat(x.cpu(), codes.cpu(), cb.cpu(), sc.cpu(), None)
+
+
+@pytest.mark.parametrize("fmt", ["1x8", "4x8", "1x16g8", "1x16g16"])
+def test_quantized_linear_other_formats(pkg, ops, orc, fmt):
+    """QuantizedLinear dispatches on (num_codebooks, nbits, group) like kernel_selector.py:21-102; gemv op and gemm op agree with float64"""
+    from rvv_lut_vq_b200 import QuantizedLinear
+    I, O = 512, 160
+    N, nbits, gs = {"1x8": (1, 8, 8), "4x8": (4, 8, 8), "1x16g8": (1, 16, 8), "1x16g16": (1, 16, 16)}[fmt]
+    rng = np.random.default_rng(9)
+    idx = rng.integers(0, 2 ** nbits, size=(O, I // gs, N))
+    m = QuantizedLinear(I, O, gs, 1, N, nbits, bias=True, device="cuda", dtype=torch.float16)
+    cbk = torch.from_numpy(rng.standard_normal((N, 2 ** nbits, 1, gs)).astype(np.float16))
+    sc = torch.from_numpy(rng.standard_normal((O, 1, 1, 1)).astype(np.float16))
+    bi = torch.from_numpy(rng.standard_normal(O).astype(np.float16))
+    m.load_state_dict({"codes": cu(orc.np_pack_int_data(idx, nbits)), "codebooks": cbk.cuda(), "scales": sc.cuda(), "bias": bi.cuda()})
+    W64 = torch.zeros((O, I // gs, gs), dtype=torch.float64)
+    for n in range(N):
+        W64 += cbk[n, torch.from_numpy(idx[:, :, n]), 0, :].double()
+    W64 = W64.reshape(O, I)
+    for batch in (3, 12):                                                            # gemv op / gemm op (inference.py:95-96)
+        x = torch.from_numpy(rng.standard_normal((batch, I)).astype(np.float16))
+        y = m(x.cuda())
+        want = (x.double() @ W64.T) * sc.reshape(1, -1).double() + bi.double()
+        assert y.shape == (batch, O)
+        assert rel_err(y.double().cpu().numpy(), want.numpy()) <= 3e-3                 # 1e-3 on the accumulator + the epilogue's fp16 roundings
+
+
+def test_quantized_linear_repacks_after_reload_and_backward(pkg, ops):
+    """the cached GEMV image follows the codes (reload / in-place edit), and grad_input flows through the transposed op (inference.py:99-142)"""
+    from rvv_lut_vq_b200 import QuantizedLinear, synth
+    I, O = 256, 64
+    A, B = synth.make_layer_np(I, O, seed=1, scales="randn", bias=True), synth.make_layer_np(I, O, seed=2, scales="randn", bias=True)
+    m = QuantizedLinear(I, O, 8, 1, 2, 8, bias=True, device="cuda", dtype=torch.float16)
+    sd = lambda L: {"codes": cu(L["codes"]), "codebooks": cu(L["codebooks"]), "scales": cu(L["scales"]), "bias": cu(L["bias"])}
+    x = cu(A["x"])
+    m.load_state_dict(sd(A))
+    ya = m(x)
+    m.load_state_dict(sd(B))                                                         # same storage, new contents: _version changes
+    yb = m(x)
+    assert torch.equal(yb.view(torch.int16), ops.code2x8_matmat(x, cu(B["codes"]), cu(B["codebooks"]), cu(B["scales"]), cu(B["bias"])).view(torch.int16))
+    assert not torch.equal(ya, yb)
+    xg = x.clone().requires_grad_(True)
+    with torch.enable_grad():
+        y = m(xg)
+        y.float().sum().backward()
+    W = ops.code2x8_dequant(cu(B["codes"]), cu(B["codebooks"]), cu(B["scales"]))
+    want = W.double().sum(dim=0)
+    assert rel_err(xg.grad.double().cpu().numpy().reshape(-1), want.cpu().numpy()) <= 5e-3
