@@ -1,26 +1,33 @@
 #!/usr/bin/env python
-"""bench.py -- LUT-VQ GEMV throughput on B200 (BASELINE.json metric: "LUT-VQ GEMV us & HBM GB/s (AQLM 2x8,
-4096x11008)"), one JSON line on stdout.
+"""bench.py -- LUT-VQ GEMV throughput + Llama decode tok/s on B200 (BASELINE.json metric: "LUT-VQ GEMV us & HBM GB/s (AQLM 2x8,
+4096x11008); Llama-2-7B decode tok/s"), one JSON line on stdout.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-Workload (N=1, BASELINE configs[1]): Llama-2-7B gate_proj shape 4096->11008, AQLM 2x8 codes, batch 1.
-One STEP = one LUT-GEMV over each of NBUF distinct layers (random codes/codebooks/scales; NBUF = 64 on one GPU = the
-gate/up projections of one Llama-2-7B token, 24 per rank when sharded), whose code matrices total > 2x the 126 MB L2,
-so every launch streams its codes from HBM (L2-cold by construction).
-  value   whole-job GB/s on the algorithmic byte stream (O*(I/8)*2 + 8192 + 2I + 4O per GEMV),
-          inputs resident in HBM, the NBUF launches replayed as one CUDA graph, timed with CUDA events;
-  e2e     the same metric through the reference-facing op (ops.code2x8_matmat) with HOST buffers: per GEMV the
-          activation row is copied from pinned host memory and the output row copied back, inside the timed region;
+Workload (BASELINE configs[1] headline shape): Llama-2-7B gate_proj 4096->11008, AQLM 2x8 codes, batch 1.
+One STEP = one LUT-GEMV over each of 64 distinct layers per GPU (random codes/codebooks/scales = the gate/up projections of one
+Llama-2-7B token; 721 MB of codes per GPU and step, > 2x the 126 MB L2, so every launch streams its codes from HBM), replayed as
+ONE CUDA graph -- the same 64 launches per graph at every N.
+  value     whole-job GB/s on the algorithmic byte stream (O*(I/8)*2 + 8192 + 2I + 4O per GEMV), inputs resident in
+            HBM, timed with CUDA events on the launching stream, max over ranks;
+  e2e       the same step with HOST buffers: one H2D copy of the step's 64 activation rows from pinned memory, the step's
+            C-ABI GEMVs, one D2H copy of the 64 output rows, all inside the timed region;
+  dependent_chain_us_per_gemv   the same ring WITHOUT the X_READY promise: what a decoder issues;
+  decode    Llama-2-7B (N=1) and Llama-2-70B (every N: strong scaling, codes sharded by output channel) decode tok/s through
+            decode.Decoder, 128 new tokens, batch 1 (benchmark/AQLM/benchmark/generate_benchmark.py:95-106);
+  prefill / dequant / kernel_to_beat (N=1)   configs[2] batch 16..256, Code2x8Dequant, and the reference's own CUDA kernels
+            (baseline/_ref/aqlm_cuda, built unmodified by tools/vendor_ref_cuda.py) timed on the same GPU;
+  parity    N>1: before timing, every rank's gathered slot is compared bit for bit with the unsharded GEMV of the concatenated
+            layer; a mismatch exits non-zero;
   roofline / cpu_baseline / clocks / sweep: see DESIGN.md "Measurement".
-N>1 (torchrun, one rank per GPU): the layer is sharded by OUTPUT CHANNEL (each rank owns an 11008-row shard of
-an N*11008-row layer), every GEMV's output slice is all-gathered into every rank's gather slot by the push exchange
-(one exchange launch per step of 24 independent GEMVs by default, LUTVQ_BENCH_GROUP; weak scaling).
+N>1 (torchrun, one rank per GPU): weak scaling of the GEMV ring -- each rank owns an 11008-row shard of an N*11008-row layer and
+every output slice is all-gathered into every rank's gather slot by the push exchange over NVLink (no NCCL on the data path).
 --impl reference: the reference's CPU LUT-GEMV (oracle port of numba_gemv_lut_, all host threads) on the same config.
 """
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -34,26 +41,24 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 IN_F, OUT_F = 4096, 11008           # headline shape (gate_proj), BASELINE.json metric
-# GEMVs per step.  One GPU: 64 = the gate_proj + up_proj launches of one Llama-2-7B decode token (32 layers x 2, all of the
-# headline shape), 64 x 11.27 MB = 721 MB of codes per step.  Sharded (N > 1): 24 (the gather-slot ring holds 24 slots),
-# 270 MB per rank and step.  Both are > 2x L2.  The step is one CUDA graph; a graph boundary costs one programmatic-
-# dependent-launch overlap (~7 us): 8 % of a 24-launch step, 3 % of a 64-launch step (measured 2835 / 2989 / 3033 GB/s
-# at 24 / 72 / 144 launches per step), so `value` is the steady-state stream plus that stated share of boundary cost.
-NBUF = int(os.environ.get("LUTVQ_BENCH_NBUF", "0")) or (64 if int(os.environ.get("WORLD_SIZE", "1")) == 1 else 24)
+NBUF = int(os.environ.get("LUTVQ_BENCH_NBUF", "0")) or 64     # GEMVs per step and per GPU, at every N
 METRIC = "lutvq_gemv_hbm_gbps"
 UNIT = "GB/s"
+WORKLOAD = f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj, BASELINE configs[1] headline shape), {NBUF} distinct layers per step"
+DECODE_TOKENS = 128                 # generate_benchmark.py:95-106: 128 new tokens, batch 1
 
 
 def algorithmic_bytes(i: int, o: int) -> int:
     return o * (i // 8) * 2 + 2 * 256 * 8 * 2 + 2 * i + 4 * o
 
 
-def measured_peak():
+def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+            d = json.load(f)
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops", 1650.0)), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except Exception:
-        return 6650.0, "fallback (B200_PROFILING.md)"
+        return 6650.0, 1650.0, "fallback (B200_PROFILING.md)"
 
 
 class ClockSampler:
@@ -89,63 +94,67 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-# ------------------------------------------------------------------------------------------------ reference arm
+# ------------------------------------------------------------------------------------------------ reference arm / CPU baseline
+def _cpu_layers(n):
+    rng = np.random.default_rng(0)
+    G = IN_F // 8
+    layers = [(rng.integers(0, 256, size=(OUT_F, G, 2), dtype=np.uint8).view(np.int8),
+               rng.standard_normal((2, 256, 8)).astype(np.float16).view(np.uint16),
+               np.ones(OUT_F, dtype=np.float16).view(np.uint16)) for _ in range(n)]
+    x = rng.standard_normal(IN_F).astype(np.float16).view(np.uint16)
+    return layers, x
+
+
 def run_reference(args):
-    """The reference's CPU implementation of the path (numba_gemv_lut_ semantics, aqlm numba_kernel.py:38-48),
-    timed as the oracle port on all host threads; each step = CPU_BUFS GEMVs of the headline shape."""
+    """The reference's CPU implementation of the path (numba_gemv_lut_ semantics, aqlm numba_kernel.py:38-48), timed as the
+    oracle port on all host threads.  Same workload as our arm: one step = NBUF GEMVs of the headline shape; the host keeps
+    CPU_BUFS distinct code matrices (> the CPU's last-level cache) and walks them round-robin -- a bounded sample of the step's
+    NBUF matrices, stated in cpu_baseline.sample."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as orc
-    CPU_BUFS = 4
-    rng = np.random.default_rng(0)
-    G = IN_F // 8
-    layers = [(rng.integers(0, 256, size=(OUT_F, G, 2), dtype=np.uint8).view(np.int8),
-               rng.standard_normal((2, 256, 8)).astype(np.float16).view(np.uint16),
-               np.ones(OUT_F, dtype=np.float16).view(np.uint16)) for _ in range(CPU_BUFS)]
-    x = rng.standard_normal(IN_F).astype(np.float16).view(np.uint16)
-    f = orc.RowMajorGemv(OUT_F, G)
+    CPU_BUFS = 16
+    layers, x = _cpu_layers(CPU_BUFS)
+    f = orc.RowMajorGemv(OUT_F, IN_F // 8)
     orc.calibrate_threads(lambda: f(x, *layers[0]))
-    step = lambda: [f(x, c, cb, sc) for (c, cb, sc) in layers]
-    for _ in range(args.warmup):
+    step = lambda: [f(x, *layers[i % CPU_BUFS]) for i in range(NBUF)]
+    for _ in range(min(args.warmup, 3)):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     dt = time.perf_counter() - t0
     ms = dt / args.steps * 1e3
-    val = CPU_BUFS * algorithmic_bytes(IN_F, OUT_F) / (ms * 1e-3) / 1e9
+    val = NBUF * algorithmic_bytes(IN_F, OUT_F) / (ms * 1e-3) / 1e9
     cores = orc.num_threads()
-    sample = f"{args.steps} steps x {CPU_BUFS} GEMVs of {IN_F}x{OUT_F} (distinct code matrices), {cores} OpenMP threads"
+    sample = (f"{args.steps} steps x {NBUF} GEMVs of {IN_F}x{OUT_F} walking {CPU_BUFS} distinct code matrices (180 MB) round-robin, "
+              f"{cores} OpenMP threads (oracle/lutvq_oracle.c orc_aqlm_gemv_rowmajor = numba_gemv_lut_ restated, race-free over rows)")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj), CPU LUT path", "gemvs_per_step": CPU_BUFS},
+        "config": {"workload": WORKLOAD, "gemvs_per_step": NBUF},
+        "arm": {"path": "CPU LUT-GEMV (oracle port of the reference's numba kernel)", "distinct_code_matrices_resident": CPU_BUFS, "warmup_steps_run": min(args.warmup, 3)},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "us_per_gemv": ms * 1e3 / CPU_BUFS,
+        "us_per_gemv": ms * 1e3 / NBUF,
     }))
 
 
 def cpu_baseline(seconds: float = 12.0):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as orc
-    rng = np.random.default_rng(0)
-    G = IN_F // 8
     bufs = 4
-    layers = [(rng.integers(0, 256, size=(OUT_F, G, 2), dtype=np.uint8).view(np.int8),
-               rng.standard_normal((2, 256, 8)).astype(np.float16).view(np.uint16)) for _ in range(bufs)]
-    x = rng.standard_normal(IN_F).astype(np.float16).view(np.uint16)
-    f = orc.RowMajorGemv(OUT_F, G)
+    layers, x = _cpu_layers(bufs)
+    f = orc.RowMajorGemv(OUT_F, IN_F // 8)
     orc.calibrate_threads(lambda: f(x, *layers[0]))
-    for c, cb in layers:
-        f(x, c, cb)
+    for L in layers:
+        f(x, *L)
     n, t0 = 0, time.perf_counter()
     while time.perf_counter() - t0 < seconds:
-        c, cb = layers[n % bufs]
-        f(x, c, cb)
+        f(x, *layers[n % bufs])
         n += 1
     dt = time.perf_counter() - t0
     cores = orc.num_threads()
@@ -153,6 +162,117 @@ def cpu_baseline(seconds: float = 12.0):
             "us_per_gemv": dt / n * 1e6,
             "sample": f"{n} GEMVs of {IN_F}x{OUT_F} over {bufs} distinct code matrices in {dt:.1f} s, {cores} OpenMP threads "
                       "(oracle/lutvq_oracle.c orc_aqlm_gemv_rowmajor = numba_gemv_lut_ restated, race-free over rows)"}
+
+
+# ------------------------------------------------------------------------------------------------ secondary measurements
+def graph_time_us(torch, stream, body, reps, inner=1):
+    """us per `inner` unit: body() captured once as a CUDA graph on `stream`, replayed reps times between two events"""
+    with torch.cuda.stream(stream):
+        body()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            body()
+        for _ in range(3):
+            g.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(reps):
+            g.replay()
+        b.record(stream)
+        torch.cuda.synchronize()
+    return a.elapsed_time(b) * 1e3 / (reps * inner)
+
+
+def measure_decode(torch, dist, model: str, world: int, rank: int, dev, tokens: int = DECODE_TOKENS, exchange: str = "push"):
+    """decode tok/s of the Llama-shaped AQLM 2x8 decoder (decode.py): one CUDA graph per token, CUDA events, max over ranks"""
+    from rvv_lut_vq_b200.decode import LLAMA2_7B, LLAMA2_70B, Decoder
+    from rvv_lut_vq_b200.sharded import ShardGroup
+    cfg = {"7b": LLAMA2_7B, "70b": LLAMA2_70B}[model]
+    group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if world > 1 else None
+    dec = Decoder(cfg, dev, world, rank, group, max_seq=tokens + 16, exchange=exchange)
+    st = torch.cuda.Stream(dev)
+    dec.reset(1)
+    dec.capture(st)
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            dec.run_token()
+        dec.reset(1)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(tokens):
+            dec.run_token()
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    err = group.error() if group is not None else 0
+    last_token = int(dec.token.item())
+    us_tok = ms * 1e3 / tokens
+    gemv_bytes = cfg.gemv_bytes_per_token()
+    peak, _, _ = measured_peaks()
+    out = {"model": cfg.name, "tok_per_s": 1e6 / us_tok, "us_per_token": us_tok, "tokens": tokens, "batch": 1, "n_gpus": world,
+           "launches_per_token": dec.launches_per_token, "graph": dec.graph is not None,
+           "gemv_code_stream_bytes_per_token": gemv_bytes,
+           "frac_of_hbm_peak": gemv_bytes / world / (us_tok * 1e-6) / 1e9 / peak,
+           "exchange": None if world == 1 else f"{exchange}: output-channel shards all-gathered over NVLink peer memory, 4 exchanges per layer",
+           "wait_errors": err, "last_token": last_token}
+    del dec, group
+    torch.cuda.empty_cache()
+    return out
+
+
+def measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak):
+    """BASELINE configs[2]: dequantize-to-smem + tcgen05 GEMM at batch 16..256 on 4096x11008, and the stand-alone dequantize"""
+    from rvv_lut_vq_b200 import ops, synth
+    st = torch.cuda.Stream(dev)
+    NB = 24
+    Ls = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=900 + k, scales="ones") for k in range(NB)]
+    rows = []
+    for batch in (16, 32, 64, 128, 256):
+        x = torch.randn((batch, IN_F), device=dev, dtype=torch.float16)
+
+        def body():
+            for L in Ls:
+                ops.code2x8_matmat_dequant(x, L["codes"], L["codebooks"], L["scales"], None)
+        us = graph_time_us(torch, st, body, 5, NB)
+        flops = 2.0 * batch * IN_F * OUT_F
+        rows.append({"batch": batch, "us": round(us, 2), "tflops": round(flops / us / 1e6, 1), "frac_of_bf16_peak": round(flops / us / 1e6 / bf16_peak, 4),
+                     "code_stream_GBps": round(OUT_F * IN_F / 4 / us / 1e3, 1)})
+    W = [torch.empty((OUT_F, IN_F), dtype=torch.float16, device=dev) for _ in range(2)]
+    lib = __import__("rvv_lut_vq_b200").lib()
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+
+    def dq():
+        s = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for k, L in enumerate(Ls):
+            lib.lutvq_code2x8_dequant(P(L["codes"]), P(W[k % 2]), P(L["codebooks"]), P(L["scales"]), OUT_F, IN_F, 0, s)
+    us = graph_time_us(torch, st, dq, 5, NB)
+    nbytes = OUT_F * IN_F // 4 + 2 * OUT_F * IN_F + 8192 + 2 * OUT_F
+    dq_row = {"shape": f"{IN_F}x{OUT_F}", "us": round(us, 2), "GBps": round(nbytes / us / 1e3, 1), "frac_of_hbm_peak": round(nbytes / us / 1e3 / hbm_peak, 4),
+              "algorithmic_bytes": nbytes}
+    del Ls, W
+    torch.cuda.empty_cache()
+    return rows, dq_row
+
+
+def kernel_to_beat():
+    """the reference's own CUDA kernels on this GPU (baseline/_ref/aqlm_cuda, tools/ref_cuda_bench.py); never fatal"""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import contextlib
+        import ref_cuda_bench
+        with contextlib.redirect_stdout(sys.stderr):                 # stdout carries exactly one JSON line
+            return ref_cuda_bench.run(quick=True, batches=(16, 256))
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -164,8 +284,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip decode / prefill / dequant / kernel_to_beat (kernel experiments)")
     ap.add_argument("--force-shard", action="store_true", help="experiment: take the sharded (push) path even at N=1")
-    ap.add_argument("--tuning", default="", help="nw,pf,ctas_per_sm override for the GEMV kernel (experiments)")
+    ap.add_argument("--tuning", default="", help="nw,nslot override for the GEMV kernel (experiments)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -185,16 +306,19 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     lib = pkg.lib()
     if args.tuning:
-        nw, pf, cps = [int(v) for v in args.tuning.split(",")]
-        lib.lutvq_debug_set_gemv_tuning(nw, pf, cps)
+        t = [int(v) for v in args.tuning.split(",")] + [0, 0]
+        lib.lutvq_debug_set_gemv_tuning(t[0], t[1], t[2])
+    hbm_peak, bf16_peak, peak_src = measured_peaks()
 
     # ---- synthetic layers: NBUF distinct code matrices (per rank: its own output-channel shard) ----
     layers = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=1000 * rank + i, scales="ones") for i in range(NBUF)]
     xs = torch.randn((NBUF, 1, IN_F), device=dev, dtype=torch.float16)
+    if world > 1:
+        dist.broadcast(xs, 0)                                     # activations and codebooks are replicated; codes are per rank
+        for L in layers:
+            dist.broadcast(L["codebooks"], 0)
     ys = torch.empty((NBUF, 1, OUT_F), device=dev, dtype=torch.float16)
     stream = torch.cuda.Stream(dev)
-
-    import ctypes
     P = lambda t: ctypes.c_void_p(t.data_ptr())
 
     # prepacked code images (what QuantizedLinear builds on first use) and a ring of workspaces: the NBUF GEMVs of a
@@ -202,21 +326,21 @@ def main():
     packed = [ops.code2x8_prepack(L["codes"]) for L in layers]
     ws_need = (int(lib.lutvq_packed_workspace_bytes(OUT_F, IN_F)) + 255) // 256 * 256
     ws_ring = torch.zeros(ops.XREADY_WS_RING * ws_need, dtype=torch.uint8, device=dev)
-    assert NBUF % ops.XREADY_WS_RING == 0
+    assert NBUF % ops.XREADY_WS_RING == 0 and NBUF <= 64
     FLAGS = {"x_ready": pkg._lib.FLAG_X_READY, "dependent": 0}
 
-    # N > 1: each rank owns an OUT_F-row shard of an (N * OUT_F)-row layer; the GEMV kernel itself pushes its rows into
-    # every peer's gather slot over NVLink (lutvq_sharded_matmat_packed) and one wait kernel per group of GROUP GEMVs
-    # confirms that all N slices of those slots have landed locally.
-    GROUP = int(os.environ.get("LUTVQ_BENCH_GROUP", "24"))      # 24 = one exchange per step (N=2: 3574 / 3791 / 4472 GB/s at 6 / 12 / 24)
+    # N > 1: each rank owns an OUT_F-row shard of an (N * OUT_F)-row layer; every GEMV fills the rank's slice of its own
+    # gather slot, and ONE exchange launch per step (side stream = parallel graph branch) forwards all slices to the peers
+    # over NVLink and confirms that all N slices of every slot have landed locally.
+    GROUP = int(os.environ.get("LUTVQ_BENCH_GROUP", str(NBUF)))
     group = None
     sharded = world > 1 or args.force_shard
-    if sharded and NBUF > 24:
-        raise SystemExit("the sharded path has 24 gather slots: run --force-shard with LUTVQ_BENCH_NBUF=24")
+    parity = None
     if sharded:
         from rvv_lut_vq_b200.sharded import ShardGroup
         group = ShardGroup.from_process_group(world * OUT_F, n_slots=NBUF) if world > 1 else ShardGroup(1, 0, OUT_F, n_slots=NBUF)
         slot_views = [group.slot_tensor(sl, world * OUT_F, torch.float16) for sl in range(NBUF)]
+    side = torch.cuda.Stream(dev) if sharded else None
 
     def step_body(mode="x_ready", first=0, count=NBUF):
         st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
@@ -233,22 +357,40 @@ def main():
                                                                P(L["scales"]), None, OUT_F, IN_F, 0, FLAGS[mode], P(ws), ws_need, st))
                 mask |= 1 << slot
                 if i % GROUP == GROUP - 1:
-                    # the exchange of the group runs on a side stream (a parallel branch of the captured graph), so the
-                    # GEMV launch chain on the main stream is never queued behind it
-                    main = torch.cuda.current_stream(dev)
-                    side.wait_stream(main)
+                    main_s = torch.cuda.current_stream(dev)
+                    side.wait_stream(main_s)
                     with torch.cuda.stream(side):
                         pkg._lib.check(lib.lutvq_shard_wait_mask(group._h, mask, ctypes.c_void_p(side.cuda_stream)))
                     mask = 0
         if sharded:
             torch.cuda.current_stream(dev).wait_stream(side)            # end of the (partial) step: every slice confirmed
 
-    side = torch.cuda.Stream(dev) if sharded else None
-
     with torch.cuda.stream(stream):
         step_body()
         torch.cuda.synchronize()
         if world > 1:
+            # ---- parity of the multi-GPU data plane, before any timing: every gathered slot == the unsharded GEMV of the
+            # concatenated layer (same kernel, prob_m = N * OUT_F), bit for bit, on every rank
+            dist.barrier()
+            n_check = min(NBUF, int(os.environ.get("LUTVQ_BENCH_PARITY_SLOTS", "8")))
+            ok = True
+            for i in range(n_check):
+                parts = [torch.empty_like(layers[i]["codes"]) for _ in range(world)]
+                dist.all_gather(parts, layers[i]["codes"])
+                whole = torch.cat(parts)                                        # the concatenated layer: [N * OUT_F, G, 2]
+                want = ops.code2x8_matmat_packed(xs[i], ops.code2x8_prepack(whole), world * OUT_F, layers[i]["codebooks"],
+                                                 torch.ones(world * OUT_F, dtype=torch.float16, device=dev), None).reshape(-1)
+                ok = ok and bool(torch.equal(want.view(torch.int16), slot_views[i].view(torch.int16)))
+                del parts, whole
+            flag = torch.tensor([1 if ok else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            parity = {"gather_bit_identical": bool(flag.item() == 1), "slots_checked": n_check, "ranks": world,
+                      "how": "each rank's gathered slot vs lutvq_code2x8_matmat_packed on the concatenated layer (codes all-gathered by NCCL for the check only), bit for bit"}
+            if not parity["gather_bit_identical"]:
+                if rank == 0:
+                    print(json.dumps({"metric": METRIC, "parity": parity, "error": "gathered slots differ from the unsharded result"}))
+                dist.destroy_process_group()
+                sys.exit(3)
             dist.barrier()
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph, stream=stream):
@@ -276,7 +418,7 @@ def main():
                 ms = float(t.item())
             return ms
 
-        for _ in range(args.warmup):
+        for _ in range(max(args.warmup, 3)):
             run_step()
         sampler = ClockSampler(local_rank)
         if rank == 0:
@@ -293,31 +435,16 @@ def main():
         # the same ring issued WITHOUT the X_READY promise: every GEMV waits for the previous one (decode-like chain)
         dep_us = None
         if world == 1:
-            gdep = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(gdep, stream=stream):
-                step_body("dependent")
-            for _ in range(5):
-                gdep.replay()
-            torch.cuda.synchronize()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = max(20, min(args.steps, 200))
-            a.record(stream)
-            for _ in range(reps):
-                gdep.replay()
-            b.record(stream)
-            torch.cuda.synchronize()
-            dep_us = a.elapsed_time(b) * 1e3 / (reps * NBUF)
+            dep_us = graph_time_us(torch, stream, lambda: step_body("dependent"), max(20, min(args.steps, 100)), NBUF)
         value = world * NBUF * bytes_per_gemv / (ms_per_step * 1e-3) / 1e9
         us_per_gemv = ms_per_step * 1e3 / NBUF
 
-        # ---- e2e: host buffers through the reference-facing op ----
+        # ---- e2e: host buffers ----
         x_host = torch.randn((NBUF, 1, IN_F), dtype=torch.float16).pin_memory()
         y_host = torch.empty((NBUF, 1, OUT_F), dtype=torch.float16).pin_memory()
         yg_host = torch.empty((NBUF, world * OUT_F), dtype=torch.float16).pin_memory() if sharded else None
 
         def e2e_step():
-            # one step end to end: the step's activations come from pinned host memory, the C-ABI GEMVs run (as the
-            # captured graph for 1 GPU, eagerly + all-gather otherwise), the step's outputs are read back to the host
             xs.copy_(x_host, non_blocking=True)
             run_step()
             if not sharded:
@@ -361,13 +488,11 @@ def main():
         # ---- the other shapes of the configs[1] sweep (not part of the timed region above) ----
         sweep = []
         if rank == 0 and world == 1 and not args.no_sweep:
-            peak, _ = measured_peak()
             for (i_f, o_f) in synth.SWEEP_7B:
                 nb = -(-max(8, int(280e6 // (o_f * i_f // 4))) // ops.XREADY_WS_RING) * ops.XREADY_WS_RING
                 Ls = [synth.make_layer_torch(i_f, o_f, dev, seed=77 + k, scales="ones") for k in range(nb)]
                 xv = torch.randn((nb, 1, i_f), device=dev, dtype=torch.float16)
                 yv = torch.empty((nb, 1, o_f), device=dev, dtype=torch.float16)
-
                 pk = [ops.code2x8_prepack(L["codes"]) for L in Ls]
                 need = (int(lib.lutvq_packed_workspace_bytes(o_f, i_f)) + 255) // 256 * 256
                 ring = torch.zeros(ops.XREADY_WS_RING * need, dtype=torch.uint8, device=dev)
@@ -379,64 +504,80 @@ def main():
                                                                        P(yv[k]), 1, o_f, i_f, 0, flags, P(ring[(k % ops.XREADY_WS_RING) * need:]), need, st))
                 row = {"shape": f"{i_f}->{o_f}", "layers_in_ring": nb}
                 for name, flags in (("x_ready", pkg._lib.FLAG_X_READY), ("dependent", 0)):
-                    body(flags)
-                    torch.cuda.synchronize()
-                    g = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(g, stream=stream):
-                        body(flags)
-                    for _ in range(5):
-                        g.replay()
-                    torch.cuda.synchronize()
-                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                    reps = 50
-                    a.record(stream)
-                    for _ in range(reps):
-                        g.replay()
-                    b.record(stream)
-                    torch.cuda.synchronize()
-                    us = a.elapsed_time(b) * 1e3 / (reps * nb)
+                    us = graph_time_us(torch, stream, lambda: body(flags), 50, nb)
                     gbps = algorithmic_bytes(i_f, o_f) / (us * 1e-6) / 1e9
-                    row[name] = {"us": round(us, 3), "gbps": round(gbps, 1), "frac_of_measured_peak": round(gbps / peak, 4)}
-                    del g
+                    row[name] = {"us": round(us, 3), "gbps": round(gbps, 1), "frac_of_measured_peak": round(gbps / hbm_peak, 4)}
                 sweep.append(row)
                 del Ls, pk
+
+    # free the ring before the model-sized measurements
+    del layers, packed, graph
+    torch.cuda.empty_cache()
+
+    # ---- decode tok/s (the second half of BASELINE.json's metric) ----
+    decode = decode70 = prefill = dequant = ktb = None
+    if not args.no_extras:
+        if world == 1:
+            decode = measure_decode(torch, dist, "7b", 1, 0, dev)
+            decode70 = measure_decode(torch, dist, "70b", 1, 0, dev)
+            prefill, dequant = measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak)
+            ktb = kernel_to_beat()
+        else:
+            decode70 = measure_decode(torch, dist, "70b", world, rank, dev)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    peak, peak_src = measured_peak()
     achieved = bytes_per_gemv / (us_per_gemv * 1e-6) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("lut_gemv_2x8_kernel_4096x11008_dram_bytes_per_launch")
+            tj = json.load(f)
+        traffic = tj.get("lut_gemv_2x8_kernel_4096x11008_dram_bytes_per_launch")
+        traffic_src = f"profiles/traffic.json (ncu --set full capture, {tj.get('when', 'see file')}); a citation, not measured in this run"
     except Exception:
         pass
+    n_exch = (NBUF // GROUP) if sharded else 0
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"AQLM 2x8 LUT-GEMV {IN_F}x{OUT_F} batch 1 (Llama-2-7B gate_proj, BASELINE configs[1] headline shape)",
-                   "gemvs_per_step": NBUF, "cache": f"inputs larger than L2: {NBUF} distinct code matrices = {NBUF * OUT_F * IN_F // 4 / 1e6:.0f} MB per step",
+        "config": {"workload": WORKLOAD, "gemvs_per_step": NBUF,
+                   "cache": f"inputs larger than L2: {NBUF} distinct code matrices = {NBUF * OUT_F * IN_F // 4 / 1e6:.0f} MB per GPU and step",
                    "launch": ("one CUDA graph per step; the GEMVs of a step are independent (resident inputs), issued with LUTVQ_FLAG_X_READY on "
                               "prepacked codes + a ring of 8 workspaces, so consecutive launches overlap under programmatic dependent launch; "
-                              "dependent_chain_us_per_gemv is the same ring without the promise") if world == 1 else ("one CUDA graph per step; every GEMV (lutvq_sharded_matmat_packed, X_READY ring) stores its rows into all peers' gather slots over NVLink "
-                              "inside the kernel; per group of 6 GEMVs one exchange launch on a side stream (parallel graph branch) forwards the finished slices to the peers and confirms the group's all-gather locally (lutvq_shard_wait_mask); the step ends with every slice confirmed; no NCCL on the data path"),
+                              "dependent_chain_us_per_gemv is the same ring without the promise") if not sharded else
+                             (f"one CUDA graph per step of {NBUF} GEMVs per rank (lutvq_sharded_matmat_packed, X_READY ring): each fills the rank's slice of its "
+                              f"own gather slot; {n_exch} exchange launch(es) per step on a side stream (parallel graph branch) forward the finished slices to "
+                              "the peers with NVLink stores, publish the epochs and confirm all N slices of every slot locally (lutvq_shard_wait_mask); "
+                              "no NCCL on the data path"),
                    "sharding": "none" if world == 1 else f"output channels, {world} x {OUT_F} rows"},
         "us_per_gemv": us_per_gemv,
         "dependent_chain_us_per_gemv": dep_us,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * world * OUT_F * 2,
                 "us_per_gemv": e2e_ms * 1e3 / NBUF, "eager_torch_op_call_us": eager_call_us,
                 "how": "per step: one H2D copy of the step's NBUF activation rows from pinned host memory, the step's C-ABI GEMVs, one D2H copy of the NBUF output rows"},
-        "gpu_launches": args.steps * (NBUF + (NBUF // GROUP if world > 1 else 0)),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+        "gpu_launches": args.steps * (NBUF + n_exch),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                     "traffic_source": traffic_src,
                      "kernel": "lut_gemv_2x8_kernel", "algorithmic_bytes_per_launch": bytes_per_gemv, "peak_source": peak_src,
                      "frac_of_nominal_8TBs": achieved / 8000.0},
         "clocks": clocks,
         "sweep": sweep,
     }
+    if parity is not None:
+        out["parity"] = parity
+    if decode is not None:
+        out["decode"] = decode
+    if decode70 is not None:
+        out["decode_70b"] = decode70
+    if prefill is not None:
+        out["prefill"] = prefill
+        out["dequant"] = dequant
+    if ktb is not None:
+        out["kernel_to_beat"] = ktb
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline()
     elif world == 1:

@@ -218,9 +218,9 @@ int    lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* s, int n, const i
                                                 const int* rows_local, int prob_k, int dtype, unsigned flags, void* ws,
                                                 size_t ws_bytes, void* stream);
 int    lutvq_shard_wait(lutvq_shard_t* s, int slot, void* stream);
-int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);   /* all slots of the mask, one launch */
+int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned long long slot_mask, void* stream);   /* all slots of the mask, one launch */
 /* software pipelining: forward + publish the slots now (non-blocking), lutvq_shard_wait[_mask] on them later only waits */
-int    lutvq_shard_push_mask(lutvq_shard_t* s, unsigned slot_mask, void* stream);
+int    lutvq_shard_push_mask(lutvq_shard_t* s, unsigned long long slot_mask, void* stream);
 int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
 int    lutvq_shard_destroy(lutvq_shard_t* s);
 

@@ -71,8 +71,8 @@ SIGNATURES = {
     "lutvq_sharded_matmat_group_packed": (I, [P, I, P, P, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_sharded_matmat_group_packed_swiglu": (I, [P, I, P, P, P, P, P, P, P, P, P, I, I, U, P, SZ, P]),
     "lutvq_shard_wait": (I, [P, I, P]),
-    "lutvq_shard_wait_mask": (I, [P, U, P]),
-    "lutvq_shard_push_mask": (I, [P, U, P]),
+    "lutvq_shard_wait_mask": (I, [P, U64, P]),
+    "lutvq_shard_push_mask": (I, [P, U64, P]),
     "lutvq_shard_error": (I, [P, P]),
     "lutvq_shard_destroy": (I, [P]),
     "lutvq_decode_add_rmsnorm": (I, [P, P, P, P, I, ctypes.c_float, P]),

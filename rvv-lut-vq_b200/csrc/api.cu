@@ -19,7 +19,7 @@ void gemv_set_dependent_workers(int m);
 int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 size_t gemv_packed_bytes(int O, int G);
-int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream);
+int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream, void* zero, size_t zero_bytes);
 void gemv_set_tuning(int nw, int pf, int pa);
 void gemv_set_timeline(void* buf);
 void gemm_set_debug_mode(int m);
@@ -193,7 +193,7 @@ int lutvq_code2x8_prepack(const void* codes, void* packed, int prob_m, int prob_
     LUTVQ_REQUIRE(aligned16(codes) && aligned16(packed), "codes and packed must be 16-byte aligned");
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
-    return gemv_prepack_launch(codes, packed, prob_m, prob_k, static_cast<cudaStream_t>(stream));
+    return gemv_prepack_launch(codes, packed, prob_m, prob_k, static_cast<cudaStream_t>(stream), nullptr, 0);
 }
 
 int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* codebooks, const void* scales,

@@ -231,13 +231,12 @@ __device__ __forceinline__ uint32_t gather_tile(const uint8_t* lut, const uint4&
     return acc;
 }
 
-// dynamic shared memory: [LUT 64 KiB][ring NW*NSLOT KiB][mbarriers NW*NSLOT x 8 B]
-template <int NW, int NSLOT> constexpr size_t gemv_smem_bytes() { return (size_t)kSliceBytes + (size_t)NW * NSLOT * kTileBytes + (size_t)NW * NSLOT * 8; }
+// dynamic shared memory: [LUT 64 KiB][NW landing slots of one set = 4 KiB each][NW mbarriers x 8 B]
+template <int NW> constexpr size_t gemv_smem_bytes() { return (size_t)kSliceBytes + (size_t)NW * kSetBytes + (size_t)NW * 8; }
 
-template <int DT, int NW, int NSLOT>
+template <int DT, int NW>
 __global__ void __launch_bounds__(NW * 32, 2)
 lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
-    static_assert(NSLOT == 2 || NSLOT == 4, "ring of 2 or 4 tiles per warp");
     static_assert(16 % NW == 0, "NW divides the 16 idx blocks");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int NT = NW * 32;
@@ -257,9 +256,12 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_end[blockIdx.x]; }          // two constant-bank loads
     else worker_range(p, blockIdx.x, gridDim.x, begin, end);
 
-    // this warp's ring: NSLOT tile slots + their mbarriers
-    const uint32_t ring_base = lut_base + kSliceBytes + (uint32_t)(warp * NSLOT) * kTileBytes;
-    const uint32_t mbar_base = lut_base + kSliceBytes + (uint32_t)(NW * NSLOT) * kTileBytes + (uint32_t)(warp * NSLOT) * 8;
+    // this warp's landing slot (one 4 KiB set, filled by ONE bulk copy: small copies are bound by the per-SM issue rate of
+    // the copy engine, measured 2.4-3.3 TB/s chip-wide with 1 KiB copies) + its mbarrier.  A set is moved from the slot into
+    // registers as soon as it has landed and the slot is refilled at once, so the next set's L2/HBM round trip runs under
+    // this set's 128 lookups per lane.
+    const uint32_t slot_base = lut_base + kSliceBytes + (uint32_t)warp * kSetBytes;
+    const uint32_t mbar = lut_base + kSliceBytes + (uint32_t)NW * kSetBytes + (uint32_t)warp * 8;
 
     // The workers of different k-slices walk the same rows; each starts at a slice-dependent rotation of its own
     // range so that the n_k atomics of one row pair are spread over the whole gather instead of colliding at one instant.
@@ -283,20 +285,16 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         if (v >= n) v -= n;
         return (lo + v) * kSetRows;
     };
-    // first NSLOT tiles of a set into the ring (lane 0; the slots are free)
-    auto fill_first = [&](const uint8_t* sp) {
-        #pragma unroll
-        for (int s = 0; s < NSLOT; ++s) bulk_load(ring_base + s * kTileBytes, sp + s * kTileBytes, kTileBytes, mbar_base + s * 8);
-    };
+    // one set into this warp's landing slot (lane 0; the slot is free)
+    auto fill_slot = [&](const uint8_t* sp) { bulk_load(slot_base, sp, kSetBytes, mbar); };
 
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
     // (1) ring barriers + the first tiles of this warp's first set, (2) the rest of the worker's share pushed HBM -> L2,
     // (3) codebook MMA fragments + codebook row norms -- all BEFORE the programmatic-dependency wait.
     if (lane == 0) {
-        #pragma unroll
-        for (int s = 0; s < NSLOT; ++s) mbar_init(mbar_base + s * 8, 1);
+        mbar_init(mbar, 1);
         fence_mbar_init();
-        if (warp < hi - lo) fill_first(set_ptr(warp));
+        if (warp < hi - lo) fill_slot(set_ptr(warp));
         // this worker's share is ONE contiguous range of the packed image: warp w prefetches items w, w + NW, ...
         const uint8_t* base = PB.codes + (size_t)begin * kSetBytes;
         for (int c = warp; c < end - begin; c += NW) l2_prefetch_bulk(base + (size_t)c * kSetBytes, kSetBytes);
@@ -367,6 +365,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         m = __reduce_max_sync(0xffffffffu, m);
         if (lane == 0) red_x[warp] = m;
     }
+    TL_STAMP(10);
     // B fragments of slice ks: column (lane>>2) of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
     auto load_bfrag = [&](uint32_t (&bfrag)[8], int ks_) {
         const uint32_t* x32 = static_cast<const uint32_t*>(p.x);              // 4 words per group
@@ -396,6 +395,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         fx_scale = (bad || tiny) ? 0.f : __fdiv_rn(kFxTarget, bound);
         fx_inv   = (bad || tiny) ? 0.f : __fdiv_rn(bound, kFxTarget);
     }
+    TL_STAMP(11);
     const bool b3 = (lane >> 3) & 1, b4 = (lane >> 4) & 1;
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
@@ -429,13 +429,13 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     };
 
     bool first_seg = true;
-    uint32_t nfill = 0;                                            // sets this warp has started (all segments): ring phase for NSLOT == 4
+    uint32_t phase = 0;                                            // parity of this warp's slot barrier: flips with every consumed set
     while (pos < end) {
         const int n_seg = hi - lo;
         // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
         if (!first_seg) {
             __syncthreads();                                       // everyone is done reading the previous slice's LUT
-            if (lane == 0 && warp < n_seg) fill_first(set_ptr(warp));
+            if (lane == 0 && warp < n_seg) fill_slot(set_ptr(warp));
             load_bfrag(bfrag, ks);
         }
         #pragma unroll
@@ -476,6 +476,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
                 }
             }
         }
+        if (first_seg) TL_STAMP(12);
         __syncthreads();
         if (first_seg) TL_STAMP(3);
         first_seg = false;
@@ -483,34 +484,33 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         // ---------------- K2: gather-accumulate over this warp's sets of the segment ----------------
         for (int li = warp; li < n_seg; li += NW) {
             const bool has_next = li + NW < n_seg;
-            const uint8_t* cur = set_ptr(li);
-            const uint8_t* nxt = has_next ? set_ptr(li + NW) : cur;
+            uint4 w[4][2];
+#if LUTVQ_DBG
+            if (!(p.flags & 0x200u))                               // DEBUG 0x200: no code streaming at all (stale slot contents)
+#endif
+            mbar_wait(mbar, phase);
+            phase ^= 1u;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                w[t][0] = lds_v4(slot_base + t * kTileBytes + lane * 16);
+                w[t][1] = lds_v4(slot_base + t * kTileBytes + 512 + lane * 16);
+            }
             uint32_t acc[4];
             #pragma unroll
             for (int t = 0; t < 4; ++t) {
-                const int slot = t % NSLOT;
-                // NSLOT == 4: slot t is filled once per set -> parity = sets started so far; NSLOT == 2: twice per set -> (t >> 1)
-                const uint32_t parity = (NSLOT == 4) ? (nfill & 1u) : (uint32_t)((t >> 1) & 1);
-                mbar_wait(mbar_base + slot * 8, parity);
-                const uint4 w0 = lds_v4(ring_base + slot * kTileBytes + lane * 16);
-                const uint4 w1 = lds_v4(ring_base + slot * kTileBytes + 512 + lane * 16);
 #if LUTVQ_DBG
-                if (p.flags & 0x100u) acc[t] = w0.x ^ w0.y ^ w0.z ^ w0.w ^ w1.x ^ w1.y ^ w1.z ^ w1.w;   // DEBUG: no lookups
+                if (p.flags & 0x100u) acc[t] = w[t][0].x ^ w[t][0].y ^ w[t][0].z ^ w[t][0].w ^ w[t][1].x ^ w[t][1].y ^ w[t][1].z ^ w[t][1].w;   // DEBUG: no lookups
                 else
 #endif
-                acc[t] = gather_tile(smem_raw, w0, w1, lm);
-                // refill the slot with the tile NSLOT ahead in this warp's stream (every lane has consumed its 32 bytes)
-                __syncwarp();
-                if (lane == 0 LUTVQ_DBG_AND(!(p.flags & 0x200u))) {
-                    if (NSLOT == 4) {
-                        if (has_next) bulk_load(ring_base + slot * kTileBytes, nxt + t * kTileBytes, kTileBytes, mbar_base + slot * 8);
-                    } else {
-                        if (t < 2)         bulk_load(ring_base + slot * kTileBytes, cur + (t + 2) * kTileBytes, kTileBytes, mbar_base + slot * 8);
-                        else if (has_next) bulk_load(ring_base + slot * kTileBytes, nxt + (t - 2) * kTileBytes, kTileBytes, mbar_base + slot * 8);
-                    }
+                acc[t] = gather_tile(smem_raw, w[t][0], w[t][1], lm);
+                if (t == 0) {
+                    // Refill the slot with this warp's next set.  Every lane's 8 slot reads were issued before tile 0's
+                    // lookups consumed the first of them (in-order return), ~100 cycles ago; the copy lands >= an L2 round
+                    // trip from now.
+                    __syncwarp();
+                    if (lane == 0 && has_next LUTVQ_DBG_AND(!(p.flags & 0x200u))) fill_slot(set_ptr(li + NW));
                 }
             }
-            ++nfill;
             // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
             uint32_t k0 = b4 ? acc[2] : acc[0], k1 = b4 ? acc[3] : acc[1];
             uint32_t g0 = b4 ? acc[0] : acc[2], g1 = b4 ? acc[1] : acc[3];
@@ -571,7 +571,11 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
 
 // packed image from reference-layout codes: [k-slice][set][tile][half][lane] x 16 B in lane-walk order (lut_layout.h)
 __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __restrict__ packed, int O, int G,
-                                   int n_k, int n_sets_total) {
+                                   int n_k, int n_sets_total, uint4* __restrict__ zero, size_t zero16) {
+    // staging use (gemv_stage_codes): the split-k words in front of the staged image may hold a previous call's staged
+    // codes (another shape, same cached workspace): hand them over all-zero, as the GEMV kernel expects them
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < zero16; i += (size_t)gridDim.x * blockDim.x)
+        zero[i] = make_uint4(0u, 0u, 0u, 0u);
     const size_t total = (size_t)n_k * n_sets_total * (kSetBytes / 16);
     const size_t row_bytes = (size_t)G * 2;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -594,7 +598,7 @@ __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __r
 // ---------------------------------------------------------------------------------------------------
 struct GemvTuning { int nw = 0, nslot = 0; };   // 0 = choose per launch mode (launch_tuned)
 static GemvTuning g_tuning;
-static int g_dep_workers_per_sm = 1;   // workers (CTAs) per SM of a DEPENDENT launch, see gemv_2x8_launch_group
+static int g_dep_workers_per_sm = 2;   // workers (CTAs) per SM of a DEPENDENT launch, see gemv_2x8_launch_group
 void gemv_set_dependent_workers(int m) { g_dep_workers_per_sm = m < 1 ? 1 : (m > 2 ? 2 : m); }
 static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][16] stamps
 static unsigned g_timeline_seq = 0;
@@ -645,21 +649,22 @@ size_t gemv_packed_bytes(int O, int G) {
 // the reference-layout entry points stage a packed image behind the split-k words
 size_t gemv_workspace_bytes(int O, int G) { return align256(gemv_packed_workspace_bytes(O, G)) + gemv_packed_bytes(O, G); }
 
-int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream) {
+int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream, void* zero, size_t zero_bytes) {
     const int G = I / 8;
     const int n_k = ceil_div(G * 2, kSliceTables), n_sets_total = ceil_div(O, kSetRows);
     const size_t total = (size_t)n_k * n_sets_total * (kSetBytes / 16);
     int grid = (int)((total + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
-    prepack_2x8_kernel<<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(codes), static_cast<uint4*>(packed), O, G, n_k, n_sets_total);
+    prepack_2x8_kernel<<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(codes), static_cast<uint4*>(packed), O, G, n_k, n_sets_total,
+                                                 static_cast<uint4*>(zero), zero_bytes / 16);
     LUTVQ_CUDA_OK(cudaGetLastError());
     return LUTVQ_OK;
 }
 
-template <int DT, int NW, int NSLOT>
+template <int DT, int NW>
 static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
-    auto kern = lut_gemv_2x8_kernel<DT, NW, NSLOT>;
-    constexpr size_t smem = gemv_smem_bytes<NW, NSLOT>();
+    auto kern = lut_gemv_2x8_kernel<DT, NW>;
+    constexpr size_t smem = gemv_smem_bytes<NW>();
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -684,11 +689,10 @@ static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bo
 template <int DT>
 static int launch_tuned(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
     GemvTuning t = g_tuning;
-    if (t.nw == 0) { t.nw = 16; t.nslot = 2; }
-    if (t.nw == 16 && t.nslot == 2) return launch_variant<DT, 16, 2>(p, grid, stream, pdl);   // 2 CTAs / SM of 16 warps, 2 KiB ring per warp
-    if (t.nw == 8 && t.nslot == 4)  return launch_variant<DT, 8, 4>(p, grid, stream, pdl);    // 2 CTAs / SM of 8 warps, 4 KiB ring per warp
-    if (t.nw == 8 && t.nslot == 2)  return launch_variant<DT, 8, 2>(p, grid, stream, pdl);
-    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d nslot=%d", t.nw, t.nslot);
+    if (t.nw == 0) t.nw = 8;
+    if (t.nw == 8) return launch_variant<DT, 8>(p, grid, stream, pdl);      // 2 CTAs / SM: 64 KiB LUT + 32 KiB of landing slots each
+    if (t.nw == 4) return launch_variant<DT, 4>(p, grid, stream, pdl);      // 2-3 CTAs / SM of 4 warps
+    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d", t.nw);
 }
 
 // worker w of a problem planned as `pl` -> its item range [begin, end) over (slice, set) pairs, slice-major.
@@ -816,7 +820,7 @@ int gemv_stage_codes(const void* codes, int O, int I, void* ws, size_t ws_bytes,
     LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= need, "workspace too small: the reference-layout entry points need %zu bytes (lutvq_workspace_bytes), got %zu", need, ws_bytes);
     LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
     void* st = static_cast<uint8_t*>(ws) + small;
-    if (int rc = gemv_prepack_launch(codes, st, O, I, stream)) return rc;
+    if (int rc = gemv_prepack_launch(codes, st, O, I, stream, ws, small)) return rc;     // small is a multiple of 256
     *staged = st; *small_bytes = small;
     return LUTVQ_OK;
 }

@@ -31,7 +31,7 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const voi
                           void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
 
 constexpr int    kShardMaxRanks  = 8;
-constexpr int    kShardMaxSlots  = 24;
+constexpr int    kShardMaxSlots  = 64;      // = bits of a slot mask; [slot][rank] epochs fill exactly the first kLocalOff bytes
 constexpr size_t kShardFlagBytes = 4096;       // [slot][rank] uint32 epochs written by peers, then local counters
 constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;   // a wait gives up (and records an error) after 4 s
 constexpr size_t kLocalOff       = 2048;       // local-only area inside the flag page: sent[slot], consumed[slot], error
@@ -80,12 +80,12 @@ __global__ void shard_wait_kernel(const unsigned* flags, unsigned* consumed, uns
 }
 
 // Several slots at once: thread t = 8 * slot + rank (blockDim = 8 * kShardMaxSlots); slots outside `mask` are skipped.
-__global__ void shard_wait_mask_kernel(const unsigned* flags, unsigned* consumed, unsigned* error, int nranks, unsigned mask,
+__global__ void shard_wait_mask_kernel(const unsigned* flags, unsigned* consumed, unsigned* error, int nranks, unsigned long long mask,
                                        unsigned long long timeout_ns) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int slot = threadIdx.x >> 3, r = threadIdx.x & 7;
-    const bool active = ((mask >> slot) & 1u) != 0 && r < nranks;
+    const bool active = ((mask >> slot) & 1ull) != 0 && r < nranks;
     bool ok = true;
     unsigned want = 0;
     if (active) {
@@ -391,23 +391,23 @@ int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {
     return LUTVQ_OK;
 }
 
-int lutvq_shard_wait_mask(lutvq_shard_t* h, unsigned slot_mask, void* stream) {
+int lutvq_shard_wait_mask(lutvq_shard_t* h, unsigned long long slot_mask, void* stream) {
     Shard* s = reinterpret_cast<Shard*>(h);
     LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
-    LUTVQ_REQUIRE(slot_mask != 0 && (slot_mask >> s->n_slots) == 0, "slot mask 0x%x names slots outside 0..%d", slot_mask, s->n_slots - 1);
+    LUTVQ_REQUIRE(slot_mask != 0 && (s->n_slots == 64 || (slot_mask >> s->n_slots) == 0), "slot mask 0x%llx names slots outside 0..%d", slot_mask, s->n_slots - 1);
     {
         ExchangeList ex{};
         int fused = 0, pushed = 0;
         for (int sl = 0; sl < s->n_slots; ++sl)
-            if ((slot_mask >> sl) & 1u) {
+            if ((slot_mask >> sl) & 1ull) {
                 fused += s->pending[sl].fused;
                 pushed += s->pending[sl].pushed;
                 s->pending[sl].pushed = 0;
                 ex.slot[ex.n] = sl; ex.row_off[ex.n] = s->pending[sl].row_off; ex.rows[ex.n] = s->pending[sl].rows;
                 ++ex.n;
             }
-        LUTVQ_REQUIRE(fused == 0 || fused == ex.n, "slot mask 0x%x mixes fused-epilogue and exchange-kernel slots", slot_mask);
-        LUTVQ_REQUIRE(pushed == 0 || pushed == ex.n, "slot mask 0x%x mixes already-pushed and unpushed slots", slot_mask);
+        LUTVQ_REQUIRE(fused == 0 || fused == ex.n, "slot mask 0x%llx mixes fused-epilogue and exchange-kernel slots", slot_mask);
+        LUTVQ_REQUIRE(pushed == 0 || pushed == ex.n, "slot mask 0x%llx mixes already-pushed and unpushed slots", slot_mask);
         if (fused == 0) return launch_exchange(s, ex, static_cast<cudaStream_t>(stream), pushed ? 0 : 1, 1);
     }
     const unsigned* flags = reinterpret_cast<const unsigned*>(s->local);
@@ -423,13 +423,13 @@ int lutvq_shard_wait_mask(lutvq_shard_t* h, unsigned slot_mask, void* stream) {
     return LUTVQ_OK;
 }
 
-int lutvq_shard_push_mask(lutvq_shard_t* h, unsigned slot_mask, void* stream) {
+int lutvq_shard_push_mask(lutvq_shard_t* h, unsigned long long slot_mask, void* stream) {
     Shard* s = reinterpret_cast<Shard*>(h);
     LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
-    LUTVQ_REQUIRE(slot_mask != 0 && (slot_mask >> s->n_slots) == 0, "slot mask 0x%x names slots outside 0..%d", slot_mask, s->n_slots - 1);
+    LUTVQ_REQUIRE(slot_mask != 0 && (s->n_slots == 64 || (slot_mask >> s->n_slots) == 0), "slot mask 0x%llx names slots outside 0..%d", slot_mask, s->n_slots - 1);
     ExchangeList ex{};
     for (int sl = 0; sl < s->n_slots; ++sl)
-        if ((slot_mask >> sl) & 1u) {
+        if ((slot_mask >> sl) & 1ull) {
             LUTVQ_REQUIRE(!s->pending[sl].fused && !s->pending[sl].pushed, "slot %d was already pushed", sl);
             ex.slot[ex.n] = sl; ex.row_off[ex.n] = s->pending[sl].row_off; ex.rows[ex.n] = s->pending[sl].rows;
             s->pending[sl].pushed = 1;

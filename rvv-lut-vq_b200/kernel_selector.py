@@ -49,4 +49,8 @@ def get_backward_pass_kernel(codebooks: torch.Tensor, optimize_for_training: boo
     fmt = _format(codebooks)
     if fmt in ("code1x16", "code2x8", "code1x8"):
         return getattr(torch.ops.aqlm, fmt + "_matmat_dequant_transposed")
-    raise NotImplementedError(f"no lutvq backward kernel for codebooks of shape {tuple(codebooks.shape)}")
+    shape = tuple(codebooks.shape)
+
+    def _no_backward(*args, **kwargs):               # selected lazily like the reference's ops: only a backward CALL fails
+        raise NotImplementedError(f"no lutvq backward kernel for codebooks of shape {shape}")
+    return _no_backward

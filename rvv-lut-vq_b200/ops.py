@@ -83,23 +83,28 @@ def stage_workspace(dev: torch.device, prob_m: int, prob_k: int) -> torch.Tensor
     return ws
 
 
-def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False) -> torch.Tensor:
+def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False, stream: Optional[int] = None) -> torch.Tensor:
     """Zero-initialised split-k words for the packed entry points, cached per (device, stream) as include/lutvq.h
     requires.  The cache holds a ring of XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True``
     (LUTVQ_FLAG_X_READY calls) steps through regions 1.. so that overlapping launches never share a region and never
     collide with a plain call's region 0.  (Inside a CUDA graph the region is baked at capture.)"""
     need = (8 * ((prob_m + 31) // 32 * 32) + 256 + 255) // 256 * 256          # lutvq_packed_workspace_bytes, rounded
-    key = _key(dev)
-    ws = _workspaces.get(key)
-    if ws is None or ws.numel() < need * XREADY_WS_RING:
+    key = _key(dev) if stream is None else (dev.index, stream)
+    ent = _ws_regions.get(key)
+    if ent is None or ent[1] < need:
         ws = torch.zeros(max(need, 1 << 17) * XREADY_WS_RING, dtype=torch.uint8, device=dev)
         _workspaces[key] = ws
-    slot = ws.numel() // XREADY_WS_RING
-    i = 0
-    if rotate:
-        i = _ws_ring_pos.get(key, 0) % (XREADY_WS_RING - 1) + 1
-        _ws_ring_pos[key] = i
-    return ws[i * slot:(i + 1) * slot]
+        slot = ws.numel() // XREADY_WS_RING
+        ent = ([ws[i * slot:(i + 1) * slot] for i in range(XREADY_WS_RING)], slot)
+        _ws_regions[key] = ent
+    if not rotate:
+        return ent[0][0]
+    i = _ws_ring_pos.get(key, 0) % (XREADY_WS_RING - 1) + 1
+    _ws_ring_pos[key] = i
+    return ent[0][i]
+
+
+_ws_regions: Dict[Tuple[int, int], tuple] = {}
 
 
 def _flat_scales(scales: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
@@ -167,21 +172,51 @@ def code2x8_prepack(codes: torch.Tensor) -> torch.Tensor:
 def code2x8_matmat_packed(input: torch.Tensor, packed: torch.Tensor, out_features: int, codebooks: torch.Tensor,
                           scales: torch.Tensor, bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False,
                           x_ready: bool = False) -> torch.Tensor:
-    """code2x8_matmat on a prepacked code image (bit-identical results)."""
-    dtype = check_use_bfloat16(input)
-    dev = _require_cuda(input, packed, codebooks, scales, bias)
-    in_features = input.size(-1)
-    flat_input = input.reshape(-1, in_features).contiguous()
-    batch = flat_input.size(0)
+    """code2x8_matmat on a prepacked code image (bit-identical results).  This is QuantizedLinear's per-token call, so the
+    host side is kept lean: no device context switch when the tensors already live on the current device, raw integer
+    pointers into the ctypes call, one dict lookup for the cached workspace."""
+    dtype = _DT.get(input.dtype)
+    if dtype is None:
+        check_use_bfloat16(input)
+    if not (input.is_cuda and packed.is_cuda and codebooks.is_cuda):
+        raise RuntimeError("lutvq ops run on CUDA tensors only (there is no CPU fallback)")
+    dev = input.device
+    if packed.device != dev or codebooks.device != dev:
+        _require_cuda(input, packed, codebooks, scales, bias)
+    in_features = input.shape[-1]
+    flat_input = input if input.is_contiguous() else input.contiguous()
+    batch = flat_input.numel() // in_features
     flat_output = torch.empty((batch, out_features), dtype=input.dtype, device=dev)
     flags = (_lib.FLAG_LUT_FP16 if lut_fp16 else 0) | (_lib.FLAG_X_READY if x_ready else 0)
-    sc, bi = _flat_scales(scales), (None if bias is None else bias.contiguous())
-    with torch.cuda.device(dev):
-        ws = workspace(dev, out_features, in_features, rotate=x_ready)
-        check(lib().lutvq_code2x8_matmat_packed(_ptr(flat_input), _ptr(packed), _ptr(codebooks.contiguous()), _ptr(sc), _ptr(bi),
-                                                _ptr(flat_output), batch, out_features, in_features, dtype, flags,
-                                                _ptr(ws), ws.numel(), _stream(dev)))
+    sc = None if scales is None else (scales if scales.is_contiguous() else scales.contiguous())
+    bi = None if bias is None else (bias if bias.is_contiguous() else bias.contiguous())
+    cb = codebooks if codebooks.is_contiguous() else codebooks.contiguous()
+    switch = torch.cuda.current_device() != dev.index
+    if switch:
+        prev = torch.cuda.current_device()
+        torch.cuda.set_device(dev)
+    try:
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        ws = workspace(dev, out_features, in_features, rotate=x_ready, stream=stream)
+        rc = _fn_matmat_packed()(flat_input.data_ptr(), packed.data_ptr(), cb.data_ptr(), 0 if sc is None else sc.data_ptr(),
+                                 0 if bi is None else bi.data_ptr(), flat_output.data_ptr(), batch, out_features, in_features, dtype, flags,
+                                 ws.data_ptr(), ws.numel(), stream)
+        if rc != 0:
+            check(rc)
+    finally:
+        if switch:
+            torch.cuda.set_device(prev)
     return flat_output.reshape(tuple(input.shape[:-1]) + (out_features,))
+
+
+_matmat_packed_fn = None
+
+
+def _fn_matmat_packed():
+    global _matmat_packed_fn
+    if _matmat_packed_fn is None:
+        _matmat_packed_fn = lib().lutvq_code2x8_matmat_packed
+    return _matmat_packed_fn
 
 
 def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,

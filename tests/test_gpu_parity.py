@@ -269,8 +269,12 @@ def test_matmat_dequant_tensor_core(pkg, ops, orc, I, O, batch, dt, bias):
     codes = cu(L["codes"])
     y = ops.code2x8_matmat_dequant(x, codes, cb, sc, bi)
     assert y.shape == (batch, O) and y.dtype == tdt
-    W = ops.code2x8_dequant(codes, cb, None)                          # bit-exact vs the oracle (tests above)
-    acc64 = x.double() @ W.double().T
+    # the oracle's own chain: orc_dequantize (bit-exact weights) -> orc_dense_gemm_f64 (float64 contraction of the same operands)
+    dtn = 0 if dt == "f16" else 1
+    Wbits = orc.c_dequantize(bits(cb).reshape(2, 256, 8), L["idx"], None, I // 8, dtype=dtn)
+    W = ops.code2x8_dequant(codes, cb, None)
+    assert np.array_equal(bits(W), Wbits)
+    acc64 = torch.from_numpy(orc.c_dense_gemm_f64(bits(x), Wbits, dtn)).cuda()
     want64 = acc64 * sc.reshape(-1).double() + (bi.double() if bias else 0)
     tol = 1e-3 if dt == "f16" else 8e-3
     assert rel_err(y.double().cpu().numpy(), want64.cpu().numpy()) <= tol

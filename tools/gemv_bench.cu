@@ -20,6 +20,7 @@
 
 extern "C" void lutvq_debug_set_gemv_tuning(int nw, int pf, int ctas_per_sm);
 extern "C" void lutvq_debug_set_timeline(void* buf);
+extern "C" void lutvq_debug_set_dependent_workers(int m);
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { fprintf(stderr, "CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(2); } } while (0)
 #define LK(x) do { int rc_ = (x); if (rc_ != 0) { fprintf(stderr, "lutvq error %d: %s at %s:%d\n", rc_, lutvq_last_error(), __FILE__, __LINE__); exit(3); } } while (0)
@@ -84,6 +85,7 @@ int main(int argc, char** argv) {
         else if (a == "--ncu") ncu = true;
         else if (a == "--timeline") timeline = true;
         else if (a == "--peak") peak = atof(next().c_str());
+        else if (a == "--depworkers") lutvq_debug_set_dependent_workers(atoi(next().c_str()));
     }
     if (nw) lutvq_debug_set_gemv_tuning(nw, pf, pa);
     int sms = 0;
@@ -189,8 +191,8 @@ int main(int argc, char** argv) {
                 unsigned long long t00 = ~0ull;
                 for (int c = 0; c < 256; ++c) if (h[c * 16]) t00 = std::min(t00, h[c * 16]);
                 printf("timeline %s mode=%s (ns relative to first CTA entry of launch 0; per stamp min/median/max over CTAs)\n", sh.c_str(), mode ? "packed" : "reference");
-                const char* names[15] = {"entry", "prologue-issued", "pdl-wait-done", "lut-built", "stream-done", "reduce-done", "exit", "", "range-done", "loads-issued", "prefetch-issued", "set0-done", "set1-done", "poll-issue", "poll1-done"};
-                const int order[14] = {0, 8, 9, 10, 1, 2, 3, 11, 12, 4, 13, 14, 5, 6};
+                const char* names[15] = {"entry", "prologue-issued", "pdl-wait-done", "lut-built", "stream-done", "reduce-done", "exit", "", "range-done", "loads-issued", "xnorm-done", "scale-done", "mma-done", "poll-issue", "poll1-done"};
+                const int order[14] = {0, 8, 9, 1, 2, 10, 11, 12, 3, 4, 13, 14, 5, 6};
                 for (int l = 0; l < NL; ++l) {
                     for (int oi = 0; oi < 14; ++oi) {
                         const int s = order[oi];
