@@ -47,6 +47,7 @@
 namespace lutvq {
 
 constexpr size_t kWsHeaderBytes = 256;        // reserved
+constexpr unsigned kFlagL2Prefetch = 0x10000u; // internal: push the worker's share HBM -> L2 in the prologue (dependent launches)
 
 constexpr int kMaxPeers = 8;                  // one NVSwitch domain
 constexpr int kRangeTable = 320;              // workers whose item ranges ride in the kernel parameters (B200: 148 or 2 x 148)
@@ -159,11 +160,40 @@ __device__ __forceinline__ unsigned long long atom_add_u64(unsigned long long* p
     return old;
 }
 // asynchronous HBM -> L2 prefetch of a contiguous range (no registers, no shared memory)
-__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes, uint64_t pol) {
+    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" :: "l"(p), "r"(bytes), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void l2_prefetch_line(const void* p) {
     asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+}
+// L2 residency: the code stream is read exactly once per GEMV (evict_first), while the few KB of codebook / scales / bias
+// of every layer are re-read every token (evict_last): without the hints the 11 MB stream of each launch pushes them out
+// and every launch pays HBM latency for its codebook in the prologue and for its scales in the tail.
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint4 ldg_stream_u128_pol(const void* p, uint64_t pol) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ uint32_t ldg_u32_pol(const void* p, uint64_t pol) {
+    uint32_t r;
+    asm volatile("ld.global.nc.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(r) : "l"(p), "l"(pol));
+    return r;
+}
+__device__ __forceinline__ uint16_t ldg_u16_pol(const void* p, uint64_t pol) {
+    uint16_t r;
+    asm volatile("ld.global.nc.L2::cache_hint.u16 %0, [%1], %2;" : "=h"(r) : "l"(p), "l"(pol));
+    return r;
 }
 // ---- mbarrier + 1-D bulk async copy (TMA engine, no tensor map): global -> this CTA's shared memory ----
 __device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
@@ -173,10 +203,10 @@ __device__ __forceinline__ void fence_mbar_init() {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar, uint64_t pol) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 :: "r"(dst), "l"(src), "r"(bytes), "r"(mbar) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
     asm volatile(
@@ -211,10 +241,20 @@ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, 
     end   = (int)((T * (w + 1)) / W);
 }
 
+// One lookup = one full-rate 32-bit shared load of the word {codebook 0 | codebook 1 << 16} of (group, idx) + one IDP.2A that adds
+// the wanted 16-bit half to the accumulator (multipliers {1, 0} / {0, 1}).  (16-bit shared loads, the obvious alternative, ran
+// at about half the wavefront rate of 32-bit ones: the gather saturated at 0.55 wavefronts per clock and SM.)
+__device__ __forceinline__ uint32_t dp2a_lo(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t lds_u32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+
 // 32 lookups of one tile: the lane's two 16-byte code images (halves p = 0, 1) against the slice LUT at `lut`
 __device__ __forceinline__ uint32_t gather_tile(const uint8_t* lut, const uint4& w0, const uint4& w1, const uint32_t (&lm)[8]) {
     const uint32_t w[2][4] = {{w0.x, w0.y, w0.z, w0.w}, {w1.x, w1.y, w1.z, w1.w}};
-    uint32_t acc = 0;
+    uint32_t acc0 = 0, acc1 = 0;
     #pragma unroll
     for (int p = 0; p < 2; ++p)
         #pragma unroll
@@ -224,27 +264,52 @@ __device__ __forceinline__ uint32_t gather_tile(const uint8_t* lut, const uint4&
                 const int u = 2 * j + (b >> 1);                      // image bytes k = 4j + b, 4j + b + 1: (u, h = 0) and (u, h = 1)
                 const uint32_t ad0 = __byte_perm(w[p][j], lm[u], 0x6504u | (uint32_t)(b << 4));
                 const uint32_t ad1 = __byte_perm(w[p][j], lm[u], 0x6504u | (uint32_t)((b + 1) << 4));
-                const uint32_t v0 = *reinterpret_cast<const unsigned short*>(lut + ad0 + (128 * p));
-                const uint32_t v1 = *reinterpret_cast<const unsigned short*>(lut + ad1 + (128 * p + 2));
-                acc = acc + v0 + v1;                                 // IADD3
+                acc0 = dp2a_lo(lds_u32(lut + ad0 + (128 * p)), 0x0001u, acc0);      // codebook 0: low half
+                acc1 = dp2a_lo(lds_u32(lut + ad1 + (128 * p)), 0x0100u, acc1);      // codebook 1: high half
             }
-    return acc;
+    return acc0 + acc1;
 }
 
-// dynamic shared memory: [LUT 64 KiB][NW landing slots of one set = 4 KiB each][NW mbarriers x 8 B]
-template <int NW> constexpr size_t gemv_smem_bytes() { return (size_t)kSliceBytes + (size_t)NW * kSetBytes + (size_t)NW * 8; }
+// 16 lookups of one half tile (half p of the lane's image) against the slice LUT at `lut`
+template <int P>
+__device__ __forceinline__ uint32_t gather_half(const uint8_t* lut, const uint4& wv, const uint32_t (&lm)[8]) {
+    const uint32_t w[4] = {wv.x, wv.y, wv.z, wv.w};
+    uint32_t acc0 = 0, acc1 = 0;
+    #pragma unroll
+    for (int j = 0; j < 4; ++j)
+        #pragma unroll
+        for (int b = 0; b < 4; b += 2) {
+            const int u = 2 * j + (b >> 1);
+            const uint32_t ad0 = __byte_perm(w[j], lm[u], 0x6504u | (uint32_t)(b << 4));
+            const uint32_t ad1 = __byte_perm(w[j], lm[u], 0x6504u | (uint32_t)((b + 1) << 4));
+            acc0 = dp2a_lo(lds_u32(lut + ad0 + (128 * P)), 0x0001u, acc0);
+            acc1 = dp2a_lo(lds_u32(lut + ad1 + (128 * P)), 0x0100u, acc1);
+        }
+    return acc0 + acc1;
+}
 
-template <int DT, int NW>
-__global__ void __launch_bounds__(NW * 32, 2)
+// Code streaming modes.
+//   kStreamRegs  128-bit no-allocate loads into a rolling register ring of kRingPieces half tiles (512 B per warp and piece):
+//                no shared memory besides the LUT, <= 80 registers => THREE CTAs (of consecutive launches) per SM.
+//   kStreamBulk  one 4 KiB bulk async copy (cp.async.bulk + mbarrier) per set into a per-warp landing slot, moved to registers
+//                on arrival and refilled at once: 96 KiB of shared memory and 128 registers => two CTAs per SM.
+constexpr int kStreamRegs = 0, kStreamBulk = 1;
+constexpr int kRingPieces = 4;
+// dynamic shared memory: [LUT 64 KiB]( + [NW landing slots of one set = 4 KiB each][NW mbarriers x 8 B])
+template <int NW, int MODE> constexpr size_t gemv_smem_bytes() { return (size_t)kSliceBytes + (MODE == kStreamBulk ? (size_t)NW * kSetBytes + (size_t)NW * 8 : 0); }
+
+template <int DT, int NW, int MODE>
+__global__ void __launch_bounds__(NW * 32, MODE == kStreamRegs ? 3 : 2)
 lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     static_assert(16 % NW == 0, "NW divides the 16 idx blocks");
+    static_assert(NW * 32 >= kSliceGroups, "one thread per group of the slice loads x");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int NT = NW * 32;
     const uint32_t lut_base = smem_u32(smem_raw);
     const GemvProblem& PB = p.prob[p.n_prob > 1 ? (int)p.tab_prob[blockIdx.x] : 0];       // indexed constant-bank loads
 
     TL_STAMP(0);
 #if LUTVQ_DBG
+    if (p.flags & 0x1000u) pdl_launch_dependents();
     if (p.tl != nullptr && threadIdx.x == 0) {
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -256,15 +321,14 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_end[blockIdx.x]; }          // two constant-bank loads
     else worker_range(p, blockIdx.x, gridDim.x, begin, end);
 
-    // this warp's landing slot (one 4 KiB set, filled by ONE bulk copy: small copies are bound by the per-SM issue rate of
-    // the copy engine, measured 2.4-3.3 TB/s chip-wide with 1 KiB copies) + its mbarrier.  A set is moved from the slot into
-    // registers as soon as it has landed and the slot is refilled at once, so the next set's L2/HBM round trip runs under
-    // this set's 128 lookups per lane.
+    // kStreamBulk: this warp's landing slot (one 4 KiB set, filled by ONE bulk copy: small copies are bound by the per-SM issue
+    // rate of the copy engine, measured 2.4-3.3 TB/s chip-wide with 1 KiB copies) + its mbarrier.  A set is moved from the slot
+    // into registers as soon as it has landed and the slot is refilled at once.
     const uint32_t slot_base = lut_base + kSliceBytes + (uint32_t)warp * kSetBytes;
     const uint32_t mbar = lut_base + kSliceBytes + (uint32_t)NW * kSetBytes + (uint32_t)warp * 8;
 
     // The workers of different k-slices walk the same rows; each starts at a slice-dependent rotation of its own
-    // range so that the n_k atomics of one row pair are spread over the whole gather instead of colliding at one instant.
+    // range so that the n_k arrivals of one row set are spread over the whole gather instead of colliding at one instant.
     auto rot_of = [&](int ks_, int n) { return (int)(((unsigned)ks_ * (unsigned)n) / (unsigned)p.n_k); };
     // first segment of this worker's range: slice ks, sets [lo, hi)
     int pos = begin;
@@ -272,32 +336,38 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     int lo = begin - ks * PB.n_sets;
     int hi = min(PB.n_sets, lo + (end - begin));
     int seg_rot = rot_of(ks, hi - lo);
-    // packed address of local set index li (rotated) of the current segment
-    auto set_ptr = [&](int li) -> const uint8_t* {
+    // set (index inside the problem) that local index li (rotated) of the current segment stands for
+    auto set_of = [&](int li) -> int {
         int v = li + seg_rot;
         const int n = hi - lo;
         if (v >= n) v -= n;
-        return PB.codes + ((size_t)ks * PB.n_sets + (size_t)(lo + v)) * kSetBytes;
+        return lo + v;
     };
-    auto set_row0 = [&](int li) -> int {
-        int v = li + seg_rot;
-        const int n = hi - lo;
-        if (v >= n) v -= n;
-        return (lo + v) * kSetRows;
-    };
+    auto set_ptr = [&](int li) -> const uint8_t* { return PB.codes + ((size_t)ks * PB.n_sets + (size_t)set_of(li)) * kSetBytes; };
     // one set into this warp's landing slot (lane 0; the slot is free)
-    auto fill_slot = [&](const uint8_t* sp) { bulk_load(slot_base, sp, kSetBytes, mbar); };
+    const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
+    auto fill_slot = [&](const uint8_t* sp) { bulk_load(slot_base, sp, kSetBytes, mbar, pol_stream); };
 
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
-    // (1) ring barriers + the first tiles of this warp's first set, (2) the rest of the worker's share pushed HBM -> L2,
-    // (3) codebook MMA fragments + codebook row norms -- all BEFORE the programmatic-dependency wait.
+    // Codes and codebooks are weights: the first code pieces (registers / landing slot), the L2 prefetch of the worker's
+    // share and the codebook MMA fragments are all requested BEFORE the programmatic-dependency wait.
+    // kStreamRegs: the rolling register ring: piece i of this warp's stream = 16 bytes per lane at set_ptr(set) + (i % 8) * 512
+    uint4 ring[MODE == kStreamRegs ? kRingPieces : 1];
+    if (MODE == kStreamRegs) {
+        const uint8_t* sp = set_ptr(warp < hi - lo ? warp : 0) + lane * 16;
+        #pragma unroll
+        for (int i = 0; i < kRingPieces; ++i) ring[i] = (begin < end) ? ldg_stream_u128_pol(sp + i * 512, pol_stream) : make_uint4(0u, 0u, 0u, 0u);
+    }
     if (lane == 0) {
-        mbar_init(mbar, 1);
-        fence_mbar_init();
-        if (warp < hi - lo) fill_slot(set_ptr(warp));
+        if (MODE == kStreamBulk) {
+            mbar_init(mbar, 1);
+            fence_mbar_init();
+            if (warp < hi - lo) fill_slot(set_ptr(warp));
+        }
         // this worker's share is ONE contiguous range of the packed image: warp w prefetches items w, w + NW, ...
         const uint8_t* base = PB.codes + (size_t)begin * kSetBytes;
-        for (int c = warp; c < end - begin; c += NW) l2_prefetch_bulk(base + (size_t)c * kSetBytes, kSetBytes);
+        if (p.flags & kFlagL2Prefetch LUTVQ_DBG_AND(!(p.flags & 0x800u)))
+            for (int c = warp; c < end - begin; c += NW) l2_prefetch_bulk(base + (size_t)c * kSetBytes, kSetBytes, pol_stream);
     }
     TL_STAMP(9);
     if (p.n_k > 1 && begin < end) {
@@ -313,6 +383,11 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     }
     const int r = lane >> 2, q = lane & 3;
     constexpr int MB_PER_WARP = 16 / NW;                                   // 16 idx blocks of 16 per codebook
+    constexpr int NT = NW * 32;
+    // Every CTA of a launch reads the same 8 KiB codebook and the same x at the same moment: those few hot lines are served by
+    // a few L2 slices, and the launch's whole "skeleton" was bound by that traffic (measured: 3 us per launch with lookups,
+    // streaming and atomics switched off).  So each line is requested ONCE per CTA: the codebook only as MMA fragments (its row
+    // norms come out of the same registers), x only as the CTA's own 1 KiB slice through shared memory.
     uint32_t afrag[MB_PER_WARP][2][2];
     {
         const uint32_t* cb32 = static_cast<const uint32_t*>(PB.codebook);  // [2][256][4] words (2 values each)
@@ -322,23 +397,37 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
             const int m = warp * MB_PER_WARP + mi;
             #pragma unroll
             for (int n = 0; n < 2; ++n) {
-                afrag[mi][n][0] = __ldg(cb32 + (n * 256 + 16 * m + r) * 4 + q);
-                afrag[mi][n][1] = __ldg(cb32 + (n * 256 + 16 * m + r + 8) * 4 + q);
+                afrag[mi][n][0] = ldg_u32_pol(cb32 + (n * 256 + 16 * m + r) * 4 + q, pol_keep);
+                afrag[mi][n][1] = ldg_u32_pol(cb32 + (n * 256 + 16 * m + r + 8) * 4 + q, pol_keep);
             }
         }
     }
     __shared__ uint32_t red_c[NW], red_x[NW];
+    __shared__ __align__(16) uint4 xs[kSliceGroups];                      // the slice's 64 activation groups (silu(gate) * x applied)
     {
-        // max over the 512 codebook rows of |row|_2^2 (bits of a non-negative float order like the float; NaN highest)
-        uint32_t m = 0;
-        const uint4* cb128 = static_cast<const uint4*>(PB.codebook);
+        // max over this warp's codebook rows of |row|_2^2, from the fragments: a row's 8 values sit in the 4 lanes of a quad.
+        // (bits of a non-negative float order like the float; NaN highest)
+        uint32_t mc = 0;
         #pragma unroll
-        for (int i = 0; i < 512 / NT; ++i) m = max(m, __float_as_uint(sumsq8<DT>(__ldg(cb128 + threadIdx.x + i * NT))));
-        m = __reduce_max_sync(0xffffffffu, m);
-        if (lane == 0) red_c[warp] = m;
+        for (int mi = 0; mi < MB_PER_WARP; ++mi)
+            #pragma unroll
+            for (int n = 0; n < 2; ++n)
+                #pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float2 f = unpack2<DT>(afrag[mi][n][h]);
+                    float s2 = fmaf(f.y, f.y, f.x * f.x);
+                    s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
+                    s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
+                    mc = max(mc, __float_as_uint(s2));
+                }
+        mc = __reduce_max_sync(0xffffffffu, mc);
+        if (lane == 0) red_c[warp] = mc;
     }
     TL_STAMP(1);
     // The next launch may become resident now that OUR weight requests are in flight (it still waits for us below).
+#if LUTVQ_DBG
+    if (!(p.flags & 0x1000u))                                      // DEBUG 0x1000: the trigger was issued at kernel entry instead
+#endif
     pdl_launch_dependents();
     // X_READY: x is not the previous kernel's output and the workspace is exclusively ours (include/lutvq.h), so
     // nothing but the final y stores has to be ordered behind the previous kernel.
@@ -347,74 +436,73 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     if (!xready) pdl_wait();    // x and the workspace belong to the previous kernel until here
     TL_STAMP(2);
 
-    // ---------------- the activation-dependent part of the scale: max_g |x_g|_2^2 over ALL groups ----------------
     const bool gated = (DT == LUTVQ_F16) && p.x_gate != nullptr;
+    auto load_group = [&](int g) -> uint4 {                        // 16 bytes = one group of 8 activations, SwiGLU applied on the way in
+        uint4 v = ldcg_u128(static_cast<const uint4*>(p.x) + g);
+        if (gated) {
+            const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
+            v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
+            v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+        }
+        return v;
+    };
+    // the CTA's slice of x for a later segment: one coalesced 16-byte load per group (8 lines for the whole CTA)
+    auto load_x_slice = [&](int ks_) {
+        if (threadIdx.x < kSliceGroups) {
+            const int g = ks_ * kSliceGroups + (int)threadIdx.x;
+            xs[threadIdx.x] = (g < p.G) ? load_group(g) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+    // ---------------- the activation-dependent part of the scale: max_g |x_g|_2^2 over ALL groups ----------------
+    // ONE coalesced pass per CTA (every line of x requested once), XU loads in flight per thread; the groups of the CTA's
+    // own slice are dropped into shared memory on the way (the B fragments come from there, not from L2 again).
     {
         uint32_t m = 0;
-        const uint4* x128 = static_cast<const uint4*>(p.x);
-        const uint4* g128 = static_cast<const uint4*>(p.x_gate);
-        for (int g = threadIdx.x; g < p.G; g += NT) {
-            uint4 v = ldcg_u128(x128 + g);
-            if (gated) {
-                const uint4 gt = ldcg_u128(g128 + g);
-                v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
-                v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+        constexpr int XU = 4;
+        if (threadIdx.x < kSliceGroups && ks * kSliceGroups + (int)threadIdx.x >= p.G) xs[threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
+        for (int g0 = threadIdx.x; g0 < p.G; g0 += XU * NT) {
+            uint4 v[XU];
+            #pragma unroll
+            for (int u = 0; u < XU; ++u) {
+                const int g = g0 + u * NT;
+                v[u] = (g < p.G) ? load_group(g) : make_uint4(0u, 0u, 0u, 0u);
             }
-            m = max(m, __float_as_uint(sumsq8<DT>(v)));
+            #pragma unroll
+            for (int u = 0; u < XU; ++u) {
+                const int g = g0 + u * NT;
+                const unsigned loc = (unsigned)(g - ks * kSliceGroups);
+                if (g < p.G && loc < (unsigned)kSliceGroups) xs[loc] = v[u];
+                m = max(m, __float_as_uint(sumsq8<DT>(v[u])));
+            }
         }
         m = __reduce_max_sync(0xffffffffu, m);
         if (lane == 0) red_x[warp] = m;
     }
-    TL_STAMP(10);
-    // B fragments of slice ks: column (lane>>2) of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
-    auto load_bfrag = [&](uint32_t (&bfrag)[8], int ks_) {
-        const uint32_t* x32 = static_cast<const uint32_t*>(p.x);              // 4 words per group
-        #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int g = ks_ * kSliceGroups + build_group_of_col(j, r);
-            bfrag[j] = (g < p.G) ? ldcg_u32(x32 + g * 4 + q) : 0u;
-            if (gated && g < p.G) bfrag[j] = silu_mul_halves(ldcg_u32(static_cast<const uint32_t*>(p.x_gate) + g * 4 + q), bfrag[j]);
-        }
-    };
-    uint32_t bfrag[8];
-    load_bfrag(bfrag, ks);
 
     uint32_t lm[8];
     #pragma unroll
     for (int u = 0; u < 8; ++u) lm[u] = stream_lm(lane, u);
-    __syncthreads();
-    float fx_scale, fx_inv;
-    bool bad;
-    {
-        uint32_t mc = 0, mx = 0;
-        #pragma unroll
-        for (int i = 0; i < NW; ++i) { mc = max(mc, red_c[i]); mx = max(mx, red_x[i]); }
-        const float bound = sqrtf(__uint_as_float(mc) * __uint_as_float(mx));
-        bad = !(bound < __uint_as_float(0x7F800000u));                  // inf or NaN activations / codebooks: the outputs are NaN
-        const bool tiny = !(bound > 1e-30f);
-        fx_scale = (bad || tiny) ? 0.f : __fdiv_rn(kFxTarget, bound);
-        fx_inv   = (bad || tiny) ? 0.f : __fdiv_rn(bound, kFxTarget);
-    }
-    TL_STAMP(11);
     const bool b3 = (lane >> 3) & 1, b4 = (lane >> 4) & 1;
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
-    const int bias_total = p.n_k * kSliceTables * kFxBias;               // every table of every slice contributes the bias once
 
     // ---- split-k completion: see the file header ----
     using D = Dtype<DT>;
     using T = typename D::T;
+    const int bias_total = p.n_k * kSliceTables * kFxBias;               // every table of every slice contributes the bias once
     unsigned long long pend_old = 0, pend_add = 0;
     int pend_row = 0;
     bool pend_valid = false;
     const unsigned last_count = (unsigned)p.n_k - 1u;
+    float fx_scale = 0.f, fx_inv = 0.f;
+    bool bad = false;
     auto finish_one = [&](unsigned field, int row) {
         if (row < PB.O) {
             float v = (float)((int)field - bias_total) * fx_inv;
             if (bad) v = __uint_as_float(0x7FC00000u);
             T rr = D::from_f(v);                                                    // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
-            if (PB.scales) rr = D::mul(rr, static_cast<const T*>(PB.scales)[row]);   // flat_output *= scales             (cuda_kernel.cpp:101)
-            if (PB.bias)   rr = D::add(rr, static_cast<const T*>(PB.bias)[row]);     // flat_output += bias               (cuda_kernel.cpp:103)
+            if (PB.scales) { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.scales) + row, pol_keep); rr = D::mul(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output *= scales (cuda_kernel.cpp:101)
+            if (PB.bias)   { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.bias) + row, pol_keep);   rr = D::add(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output += bias   (cuda_kernel.cpp:103)
             store_y<DT>(p, PB, row, rr);
         }
     };
@@ -429,15 +517,39 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     };
 
     bool first_seg = true;
-    uint32_t phase = 0;                                            // parity of this warp's slot barrier: flips with every consumed set
+    uint32_t phase = 0;                                            // kStreamBulk: parity of this warp's slot barrier
     while (pos < end) {
         const int n_seg = hi - lo;
         // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
         if (!first_seg) {
-            __syncthreads();                                       // everyone is done reading the previous slice's LUT
-            if (lane == 0 && warp < n_seg) fill_slot(set_ptr(warp));
-            load_bfrag(bfrag, ks);
+            __syncthreads();                                       // everyone is done reading the previous slice's LUT and xs
+            if (MODE == kStreamBulk) { if (lane == 0 && warp < n_seg) fill_slot(set_ptr(warp)); }
+            else if (warp < n_seg) {
+                const uint8_t* sp = set_ptr(warp) + lane * 16;
+                #pragma unroll
+                for (int i = 0; i < kRingPieces; ++i) ring[i] = ldg_stream_u128_pol(sp + i * 512, pol_stream);
+            }
+            load_x_slice(ks);
         }
+        __syncthreads();                                           // xs and red_c are complete
+        if (first_seg) TL_STAMP(10);
+        if (first_seg) {
+            // ONE fixed-point scale per GEMV: S = 32704 / (max_k |C_k|_2 * max_g |x_g|_2) >= |L| by Cauchy-Schwarz, computed
+            // identically by every CTA from (x, codebook) alone
+            uint32_t mc = 0, mx = 0;
+            #pragma unroll
+            for (int i = 0; i < NW; ++i) { mc = max(mc, red_c[i]); mx = max(mx, red_x[i]); }
+            const float bound = sqrtf(__uint_as_float(mc) * __uint_as_float(mx));
+            bad = !(bound < __uint_as_float(0x7F800000u));          // inf or NaN activations / codebooks: the outputs are NaN
+            const bool tiny = !(bound > 1e-30f);
+            fx_scale = (bad || tiny) ? 0.f : __fdiv_rn(kFxTarget, bound);
+            fx_inv   = (bad || tiny) ? 0.f : __fdiv_rn(bound, kFxTarget);
+        }
+        // B fragments of the slice: column (lane>>2) of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
+        uint32_t bfrag[8];
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) bfrag[j] = reinterpret_cast<const uint32_t*>(xs)[build_group_of_col(j, r) * 4 + q];
+        if (first_seg) TL_STAMP(11);
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi) {
             const int m = warp * MB_PER_WARP + mi;
@@ -484,31 +596,54 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         // ---------------- K2: gather-accumulate over this warp's sets of the segment ----------------
         for (int li = warp; li < n_seg; li += NW) {
             const bool has_next = li + NW < n_seg;
-            uint4 w[4][2];
-#if LUTVQ_DBG
-            if (!(p.flags & 0x200u))                               // DEBUG 0x200: no code streaming at all (stale slot contents)
-#endif
-            mbar_wait(mbar, phase);
-            phase ^= 1u;
-            #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                w[t][0] = lds_v4(slot_base + t * kTileBytes + lane * 16);
-                w[t][1] = lds_v4(slot_base + t * kTileBytes + 512 + lane * 16);
-            }
             uint32_t acc[4];
-            #pragma unroll
-            for (int t = 0; t < 4; ++t) {
+            if (MODE == kStreamBulk) {
+                uint4 w[4][2];
 #if LUTVQ_DBG
-                if (p.flags & 0x100u) acc[t] = w[t][0].x ^ w[t][0].y ^ w[t][0].z ^ w[t][0].w ^ w[t][1].x ^ w[t][1].y ^ w[t][1].z ^ w[t][1].w;   // DEBUG: no lookups
-                else
+                if (!(p.flags & 0x200u))                           // DEBUG 0x200: no code streaming at all (stale slot contents)
 #endif
-                acc[t] = gather_tile(smem_raw, w[t][0], w[t][1], lm);
-                if (t == 0) {
-                    // Refill the slot with this warp's next set.  Every lane's 8 slot reads were issued before tile 0's
-                    // lookups consumed the first of them (in-order return), ~100 cycles ago; the copy lands >= an L2 round
-                    // trip from now.
-                    __syncwarp();
-                    if (lane == 0 && has_next LUTVQ_DBG_AND(!(p.flags & 0x200u))) fill_slot(set_ptr(li + NW));
+                mbar_wait(mbar, phase);
+                phase ^= 1u;
+                #pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    w[t][0] = lds_v4(slot_base + t * kTileBytes + lane * 16);
+                    w[t][1] = lds_v4(slot_base + t * kTileBytes + 512 + lane * 16);
+                }
+                #pragma unroll
+                for (int t = 0; t < 4; ++t) {
+#if LUTVQ_DBG
+                    if (p.flags & 0x100u) acc[t] = w[t][0].x ^ w[t][0].y ^ w[t][0].z ^ w[t][0].w ^ w[t][1].x ^ w[t][1].y ^ w[t][1].z ^ w[t][1].w;   // DEBUG: no lookups
+                    else
+#endif
+                    acc[t] = gather_tile(smem_raw, w[t][0], w[t][1], lm);
+                    if (t == 0) {
+                        // Refill the slot with this warp's next set.  Every lane's 8 slot reads were issued before tile 0's
+                        // lookups consumed the first of them (in-order return), ~100 cycles ago; the copy lands >= an L2 round
+                        // trip from now.
+                        __syncwarp();
+                        if (lane == 0 && has_next LUTVQ_DBG_AND(!(p.flags & 0x200u))) fill_slot(set_ptr(li + NW));
+                    }
+                }
+            } else {
+                const uint8_t* cur = set_ptr(li) + lane * 16;
+                const uint8_t* nxt = has_next ? set_ptr(li + NW) + lane * 16 : cur;
+                #pragma unroll
+                for (int pc = 0; pc < 8; ++pc) {
+                    const uint4 wv = ring[pc % kRingPieces];
+                    // the piece kRingPieces ahead in this warp's stream takes the freed ring slot (the last set re-reads
+                    // its own pieces: harmless, never consumed)
+                    const int ahead = pc + kRingPieces;
+#if LUTVQ_DBG
+                    if (!(p.flags & 0x200u))
+#endif
+                    ring[pc % kRingPieces] = ldg_stream_u128_pol(ahead < 8 ? cur + ahead * 512 : nxt + (ahead - 8) * 512, pol_stream);
+                    uint32_t a;
+#if LUTVQ_DBG
+                    if (p.flags & 0x100u) a = wv.x ^ wv.y ^ wv.z ^ wv.w;
+                    else
+#endif
+                    a = (pc & 1) ? gather_half<1>(smem_raw, wv, lm) : gather_half<0>(smem_raw, wv, lm);
+                    if (pc & 1) acc[pc >> 1] += a; else acc[pc >> 1] = a;
                 }
             }
             // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
@@ -519,7 +654,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
             uint32_t keep = b3 ? k1 : k0, give = b3 ? k0 : k1;
             keep += __shfl_xor_sync(0xffffffffu, give, 8);            // row (set row0 + lane): sum of its 128 entries, < 2^23
             const uint32_t nb = __shfl_xor_sync(0xffffffffu, keep, 1);
-            const int row = set_row0(li) + lane;
+            const int row = set_of(li) * kSetRows + lane;
             // finish the atomic issued one set ago (its L2 round trip has long completed), then issue this set's
             if (pend_valid) finish_pair(pend_old, pend_add, pend_row);
             pend_valid = false;
@@ -558,7 +693,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         }
         __syncthreads();
         if (last_flag) {
-            if (threadIdx.x == 0) *p.cta_arrivals = 0u;                               // self-cleaning, like the accumulators
+            if (threadIdx.x == 0) *p.cta_arrivals = 0u;                               // self-cleaning, like the counters
             __threadfence_system();
             const unsigned epoch = *p.push_sent + 1u;
             if ((int)threadIdx.x < p.n_push)
@@ -661,10 +796,10 @@ int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStrea
     return LUTVQ_OK;
 }
 
-template <int DT, int NW>
+template <int DT, int NW, int MODE>
 static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
-    auto kern = lut_gemv_2x8_kernel<DT, NW>;
-    constexpr size_t smem = gemv_smem_bytes<NW>();
+    auto kern = lut_gemv_2x8_kernel<DT, NW, MODE>;
+    constexpr size_t smem = gemv_smem_bytes<NW, MODE>();
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -689,10 +824,10 @@ static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bo
 template <int DT>
 static int launch_tuned(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
     GemvTuning t = g_tuning;
-    if (t.nw == 0) t.nw = 8;
-    if (t.nw == 8) return launch_variant<DT, 8>(p, grid, stream, pdl);      // 2 CTAs / SM: 64 KiB LUT + 32 KiB of landing slots each
-    if (t.nw == 4) return launch_variant<DT, 4>(p, grid, stream, pdl);      // 2-3 CTAs / SM of 4 warps
-    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d", t.nw);
+    if (t.nw == 0) { t.nw = 8; t.nslot = kStreamRegs; }
+    if (t.nw == 8 && t.nslot == kStreamRegs) return launch_variant<DT, 8, kStreamRegs>(p, grid, stream, pdl);   // 3 CTAs / SM: 64 KiB LUT, register ring
+    if (t.nw == 8 && t.nslot == kStreamBulk) return launch_variant<DT, 8, kStreamBulk>(p, grid, stream, pdl);   // 2 CTAs / SM: + 32 KiB of landing slots
+    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d mode=%d", t.nw, t.nslot);
 }
 
 // worker w of a problem planned as `pl` -> its item range [begin, end) over (slice, set) pairs, slice-major.
@@ -793,6 +928,10 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const voi
     }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
+    // A dependent launch sits behind griddepcontrol.wait while its predecessor runs: pushing its share HBM -> L2 meanwhile is
+    // free.  An independent (X_READY) launch streams at once, where the extra prefetch requests only cost bandwidth
+    // (tools/stream_probe: 5.9 vs 7.3 TB/s).
+    if (!(p.flags & LUTVQ_FLAG_X_READY)) p.flags |= kFlagL2Prefetch;
     p.tl = (g_timeline && W_total <= 256) ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
     if (dtype == LUTVQ_F16)  return launch_tuned<LUTVQ_F16>(p, W_total, stream, pdl);
     if (dtype == LUTVQ_BF16) return launch_tuned<LUTVQ_BF16>(p, W_total, stream, pdl);

@@ -88,7 +88,9 @@ def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False,
     requires.  The cache holds a ring of XREADY_WS_RING regions; plain calls always use region 0, ``rotate=True``
     (LUTVQ_FLAG_X_READY calls) steps through regions 1.. so that overlapping launches never share a region and never
     collide with a plain call's region 0.  (Inside a CUDA graph the region is baked at capture.)"""
-    need = (8 * ((prob_m + 31) // 32 * 32) + 256 + 255) // 256 * 256          # lutvq_packed_workspace_bytes, rounded
+    need = _ws_need.get((prob_m, prob_k))
+    if need is None:
+        need = _ws_need[(prob_m, prob_k)] = (int(lib().lutvq_packed_workspace_bytes(prob_m, prob_k)) + 255) // 256 * 256
     key = _key(dev) if stream is None else (dev.index, stream)
     ent = _ws_regions.get(key)
     if ent is None or ent[1] < need:
@@ -105,6 +107,12 @@ def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False,
 
 
 _ws_regions: Dict[Tuple[int, int], tuple] = {}
+_ws_need: Dict[Tuple[int, int], int] = {}
+
+
+def workspace_zero_bytes(prob_m: int) -> int:
+    """the part of a packed workspace every call hands back all-zero: 256-byte header + one arrival counter per 32-row set"""
+    return 256 + (4 * ((prob_m + 31) // 32) + 255) // 256 * 256
 
 
 def _flat_scales(scales: Optional[torch.Tensor]) -> Optional[torch.Tensor]:

@@ -1,0 +1,33 @@
+#!/bin/bash
+# GPU call 9 (round 2): L2 residency hints (codes evict_first, codebook/scales evict_last), scale prefetch restored; bench line
+cd "$(dirname "$0")/.."
+O=gpurun_out/r02i
+mkdir -p $O
+timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_sharded.py -m gpu -q -x --timeout 120 > $O/pytest.txt 2>&1
+tail -4 $O/pytest.txt
+N=tools/gemv_bench_dbg
+S="--shapes 4096x11008"
+{
+for T in 8,0 8,1; do
+  for W in 1 2; do timeout 30 tools/gemv_bench --packed 1 --tuning $T --reps 20 --depworkers $W; done
+  timeout 30 tools/gemv_bench --packed 1 --tuning $T --reps 20 --xready
+done
+for D in 0x100 0x400 0x700; do
+  timeout 30 $N --packed 1 --tuning 8,1 $S --reps 20 --dbg $D --xready
+  timeout 30 $N --packed 1 --tuning 8,1 $S --reps 20 --dbg $D --depworkers 2
+done
+} > $O/times.jsonl 2>&1
+cat $O/times.jsonl
+timeout 30 $N --timeline --packed 1 --tuning 8,1 $S --depworkers 1 > $O/tl_dep_bulk.txt 2>&1
+timeout 30 $N --timeline --packed 1 --tuning 8,1 $S --xready > $O/tl_xr_bulk.txt 2>&1
+grep -E "L5 " $O/tl_dep_bulk.txt $O/tl_xr_bulk.txt
+for T in 8,0 8,1; do
+timeout 600 python bench.py --steps 20 --warmup 5 --tuning $T --no-cpu-baseline > $O/bench_${T/,/_}.json 2> $O/bench_${T/,/_}.err
+tail -2 $O/bench_${T/,/_}.err
+python - <<PY
+import json
+d=json.load(open("$O/bench_${T/,/_}.json"))
+print("$T", d["value"], d["us_per_gemv"], d["dependent_chain_us_per_gemv"], d["roofline"]["frac"], [ (r["shape"], r["x_ready"]["us"], r["dependent"]["us"]) for r in d["sweep"]])
+print(d.get("decode",{}).get("tok_per_s"), d.get("decode_70b",{}).get("tok_per_s"))
+PY
+done
