@@ -11,7 +11,8 @@ namespace lutvq {
 int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push = nullptr);
-int gemv_stage_codes(const void* codes, int O, int I, void* ws, size_t ws_bytes, cudaStream_t stream, const void** staged, size_t* small_bytes);
+int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
+                        const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream);
 size_t gemv_workspace_bytes(int O, int G);
 size_t gemv_packed_workspace_bytes(int O, int G);
 size_t gemv_group_workspace_bytes(int n, const int* O);
@@ -127,11 +128,8 @@ int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* 
                          int dtype, void* ws, size_t ws_bytes, void* stream) {
     if (int rc = check_2x8_common(codes, codebook, prob_m, prob_k, dtype)) return rc;
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
-    const void* staged = nullptr;
-    size_t small = 0;
-    if (int rc = gemv_stage_codes(codes, prob_m, prob_k, ws, ws_bytes, static_cast<cudaStream_t>(stream), &staged, &small)) return rc;
-    return gemv_2x8_launch(staged, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, LUTVQ_FLAG_NO_PDL, ws, small,
-                           static_cast<cudaStream_t>(stream));
+    return gemv_2x8_launch_ref(codes, x, y, codebook, nullptr, nullptr, prob_m, prob_k, dtype, 0u, ws, ws_bytes,
+                               static_cast<cudaStream_t>(stream));
 }
 
 static int matmat_rows(const void* x, const void* codes, int packed, const void* codebooks, const void* scales,
@@ -142,14 +140,7 @@ static int matmat_rows(const void* x, const void* codes, int packed, const void*
     if (batch == 0) return LUTVQ_OK;                                  // empty input: nothing to launch (pointers may be null)
     LUTVQ_REQUIRE(x && y, "null x/y pointer");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    size_t region = ws_bytes;
-    if (!packed) {
-        // reference layout: one re-layout pass into the staging area, then the packed kernel (gemv_stage_codes)
-        const void* staged = nullptr;
-        if (int rc = gemv_stage_codes(codes, prob_m, prob_k, ws, ws_bytes, st, &staged, &region)) return rc;
-        codes = staged;
-        flags &= ~LUTVQ_FLAG_X_READY;                                 // the staged image is not a resident weight
-    }
+    const size_t region = ws_bytes;
     // cuda_kernel.cpp:404-414 loops the matvec over the flattened batch rows; so do we (one fused launch per row,
     // scale/bias folded into the kernel's epilogue instead of three extra elementwise kernels).
     // X_READY launches overlap under programmatic dependent launch, so consecutive rows must not share split-k words:
@@ -166,11 +157,11 @@ static int matmat_rows(const void* x, const void* codes, int packed, const void*
         const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * esz;
         void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * esz;
         unsigned f = flags;
-        if (!packed && b == 0) f |= LUTVQ_FLAG_NO_PDL;                // must not start before the prepack kernel has finished
         if (b > 0 && regions == 1) f &= ~LUTVQ_FLAG_X_READY;
         void* wsb = regions > 1 ? static_cast<uint8_t*>(ws) + (size_t)(b % regions) * need : ws;
-        if (int rc = gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb,
-                                     regions > 1 ? need : region, st))
+        const size_t wsn = regions > 1 ? need : region;
+        if (int rc = packed ? gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb, wsn, st)
+                            : gemv_2x8_launch_ref(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb, wsn, st))
             return rc;
     }
     return LUTVQ_OK;

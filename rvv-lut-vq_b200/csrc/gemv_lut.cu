@@ -1,42 +1,53 @@
-// gemv_lut.cu -- fused LUT-build + code-indexed gather-accumulate GEMV for AQLM 2x8 codes (sm_100a), round-2 design.
+// gemv_lut.cu -- fused LUT-build + code-indexed gather-accumulate GEMV for AQLM 2x8 codes (sm_100a).
 //
 // Replaces Code2x8MatVec (reference benchmark/AQLM/inference_lib/src/aqlm/inference_kernels/
 // cuda_kernel.cu:144-233) with the LUT formulation of the golden model (vq_dataflow_sim/vq.py:280-298):
 //
-//   K1  L[g][n][k] = sum_j C[n][k][j] * x[8g+j]      built per CTA for ITS 64-group k-slice with mma.sync.m16n8k8
-//                                                     (fp32 accumulate), stored as 16-bit fixed point: 128 tables in
-//                                                     64 KiB of shared memory (lut_layout.h)
-//   K2  y[o] = sum_g sum_n L[g][n][code(o,g,n)]       packed codes streamed HBM -> shared memory by 1-D bulk async copies
-//                                                     (cp.async.bulk + mbarrier, a private ring per warp), then per code
-//                                                     byte one PRMT + one LDS.U16 + half an IADD3, conflict-free for any
-//                                                     index pattern; warp-shuffle transposed reduction
+//   K1  L[g][n][k] = sum_j C[n][k][j] * x[8g+j]      built per CTA for ITS 32-group k-slice with
+//                                                     mma.sync.m16n8k8 (fp32 accumulate) into 64 KiB of smem
+//   K2  y[o] = sum_g sum_n L[g][n][code(o,g,n)]       codes streamed HBM -> L2 (bulk prefetch) -> registers
+//                                                     (one 128-bit no-allocate load per lane per 8-row tile),
+//                                                     one PRMT + one LDS + one FADD per code byte,
+//                                                     conflict-free for any index pattern (lut_layout.h)
 //
-// Fixed-point LUT.  One scale per GEMV: S = 32704 / bound with bound = max_k |C[n][k][:]|_2 * max_g |x[8g..8g+7]|_2 >= |L|
-// (Cauchy-Schwarz), computed identically by every CTA from (x, codebook) alone -- so the result does not depend on the
-// work decomposition.  entry = round(L * S) + 32768 as u16 (the conversion is one FFMA with the magic constant
-// 1.5 * 2^23 + 32768); sums of entries are exact integers, order-free => bit-reproducible.  Quantisation step
-// bound / 32704: about 4x finer than the fp16 LUT of the golden model (vq.py:285) for N(0,1) data.
+// Work decomposition.  The work items of one GEMV are (k-slice, 32-row set) pairs, linearised slice-major.
+// The grid is EXACTLY one CTA per SM (a "worker"); worker w owns a contiguous range of items:
+//   aligned  (n_k <= #SMs): the workers are dealt to the slices (floor or ceil(#SMs/n_k) each) and split that
+//            slice's row sets evenly -> one LUT build per worker;
+//   linear   (otherwise, or when cheaper): range w*T/W .. (w+1)*T/W, which may straddle slices (<= 2 builds
+//            when T/W >= n_sets, more for very long K).
+// One CTA per SM per launch matters under programmatic dependent launch: consecutive launches then pair up
+// 1:1 on every SM (occupancy 2), instead of a 144-CTA grid doubling up on the 4 idle SMs and straggling.
 //
-// Work decomposition.  Items = (k-slice, 32-row set), slice-major; one CTA ("worker") per SM owns a contiguous item
-// range: aligned (workers dealt to slices, one LUT build each) or linear (balanced, may straddle slices).  The ranges
-// ride in the kernel parameters.
+// Cross-CTA split-k reduction: one 64-bit accumulator word per output row, (fixed-point sum << 8) | arrivals.  Each
+// (row, k-slice) partial is ONE integer atomic add executed at the row's L2 home slice; the atomic's return value
+// tells the contributor whether it was the last of the n_k, in which case it holds the complete sum, applies the
+// reference epilogue order (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111), writes y and zeroes the word.
+// Integer addition commutes => the result is bit-identical whatever the arrival order; nothing polls, nothing
+// needs the CTAs of a launch to be co-resident, and the workspace is self-cleaning (all zero between launches).
+// The return value is examined PF sets after the atomic was issued, so its L2 round trip hides behind lookups;
+// workers of different k-slices walk their rows in rotated order so the n_k atomics of a row do not collide.
+// (Measured alternatives on B200, 4096x11008: {value, tag} words polled through L2 cost 1.7-2.7 us per launch
+// after the last store -- one poll round of 16 loads took 2.4 us -- against ~1 us for the atomic scheme.)
 //
-// Cross-CTA split-k reduction: one 64-bit word per PAIR of output rows:  [arrivals:6][row 2i+1 : 29][row 2i : 29].
-// Each (row pair, k-slice) partial is ONE integer atomic add at the word's L2 home; the contributor that sees
-// arrivals == n_k - 1 in the returned word holds both complete sums, applies the reference epilogue order (round to
-// dtype, * scale, + bias; cuda_kernel.cpp:95-111), writes y and zeroes the word.  Nothing polls; the workspace is
-// self-cleaning.  (Round 1 used one word per row and 64 tables per slice: 4x the atomics.)
+// Stream overlap (programmatic dependent launch).  Weights (codes, codebooks, scales, bias) never depend on the
+// previous kernel, so the first tile sets are requested into registers and the rest of the worker's share is pushed
+// HBM -> L2 BEFORE griddepcontrol.wait.  With LUTVQ_FLAG_X_READY the caller additionally promises that x was not
+// written by the kernel(s) immediately preceding this call in the stream and that the workspace is not shared with
+// them (include/lutvq.h); then the LUT build, the gather and the split-k atomics all run before the wait and only
+// the y stores (and this kernel's completion) are ordered behind the previous kernel.
 //
-// Stream overlap (programmatic dependent launch).  Codes and codebooks are weights: ring fills, L2 prefetch of the
-// worker's whole share, codebook fragments and codebook norms all happen BEFORE griddepcontrol.wait.  With
-// LUTVQ_FLAG_X_READY (include/lutvq.h) the LUT build, the gather and the atomics run before the wait too.
+// Two code layouts feed the same gather loop:
+//   reference  int8 [O][G][2] exactly as QuantizedLinear.codes: a warp's 128-bit load touches 8 rows x 64 B;
+//   packed     lutvq_code2x8_prepack(): [k-slice][32-row set][8-row tile][lane] x 16 B, the lane's register
+//              image, so a warp's load is 512 contiguous bytes and a worker's share is one contiguous range.
 //
 // Algorithmic HBM bytes per launch: O*(I/8)*2 codes + 8192 codebooks + 2I x + 2O scales + 2O y.
 #include "common.cuh"
 #include "lut_layout.h"
 
 #ifndef LUTVQ_DBG
-#define LUTVQ_DBG 0          // 1: compile the experiment knobs (flags 0x100 no lookups, 0x200 no ring refills, 0x400 no atomics)
+#define LUTVQ_DBG 0          // 1: compile the experiment knobs (flags 0x100 no lookups, 0x200 no streaming, 0x400 no atomics)
 #endif
 #if LUTVQ_DBG
 #define LUTVQ_DBG_AND(x) && (x)
@@ -47,13 +58,13 @@
 namespace lutvq {
 
 constexpr size_t kWsHeaderBytes = 256;        // reserved
-constexpr unsigned kFlagL2Prefetch = 0x10000u; // internal: push the worker's share HBM -> L2 in the prologue (dependent launches)
 
 constexpr int kMaxPeers = 8;                  // one NVSwitch domain
 constexpr int kRangeTable = 320;              // workers whose item ranges ride in the kernel parameters (B200: 148 or 2 x 148)
-constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
-constexpr int kMaxSlices = 63;                // the arrival counter of the split-k word has 6 bits
 
+constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
+
+// One linear layer of a (possibly grouped) launch.  Every worker (CTA) belongs to exactly one problem.
 // two fp16 lanes of silu(g) * u, rounded once: the arithmetic of decode_glue.cu silu_mul_kernel, bit for bit
 __device__ __forceinline__ uint32_t silu_mul_halves(uint32_t g, uint32_t u) {
     const __half2 gh = *reinterpret_cast<const __half2*>(&g), uh = *reinterpret_cast<const __half2*>(&u);
@@ -64,14 +75,13 @@ __device__ __forceinline__ uint32_t silu_mul_halves(uint32_t g, uint32_t u) {
     return *reinterpret_cast<const uint32_t*>(&r);
 }
 
-// One linear layer of a (possibly grouped) launch.  Every worker (CTA) belongs to exactly one problem.
 struct GemvProblem {
-    const uint8_t* codes;     // packed image (lutvq_code2x8_prepack)
+    const uint8_t* codes;     // reference layout [O][G][2]  or packed layout (see above)
     const void* codebook;     // [2][256][8]
     void* y;                  // [O]
     const void* scales;       // [O] or null
     const void* bias;         // [O] or null
-    unsigned long long* acc;  // [O_pad / 2] split-k accumulator words, zero between launches
+    unsigned long long* acc;  // [O_pad] split-k accumulator words, zero between launches
     int O, n_sets;
 };
 
@@ -126,49 +136,47 @@ template <> struct MmaK8<LUTVQ_BF16> {
     }
 };
 
-// the two values of a packed fp16x2 / bf16x2 word as floats
-template <int DT> __device__ __forceinline__ float2 unpack2(uint32_t w);
-template <> __device__ __forceinline__ float2 unpack2<LUTVQ_F16>(uint32_t w)  { return __half22float2(*reinterpret_cast<const __half2*>(&w)); }
-template <> __device__ __forceinline__ float2 unpack2<LUTVQ_BF16>(uint32_t w) { return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xFFFF0000u)); }
-// sum of squares of the 8 values of one 16-byte group / codebook row, fixed order (every CTA must get the same bits)
-template <int DT> __device__ __forceinline__ float sumsq8(uint4 v) {
-    float s = 0.f;
-    float2 f;
-    f = unpack2<DT>(v.x); s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s);
-    f = unpack2<DT>(v.y); s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s);
-    f = unpack2<DT>(v.z); s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s);
-    f = unpack2<DT>(v.w); s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s);
-    return s;
+__device__ __forceinline__ void sts_v4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
+// Split-k accumulator word (one per output row, zero between launches):  (fixed-point sum << 8) | arrivals.
+// Every (row, k-slice) partial is ONE 64-bit integer atomic add performed at the row's L2 home slice; integer
+// addition commutes, so the result is bit-identical whatever the arrival order.  The atomic returns the old word:
+// the contributor that sees arrivals == n_k - 1 holds the complete sum (old + its own), writes y and zeroes the word.
+// Fixed point: 2^-kFxBits per unit in a 56-bit signed field.  fp16 (|y| <= 65504): 2^-30 -> +-3.4e7 of range with
+// 9.3e-10 resolution (below half an ulp of every normal fp16 output).  bf16: 2^-20 -> +-3.4e10.  Partials are
+// saturated to the field (a non-finite partial saturates too: the output becomes +-inf in fp16, not NaN).
+template <int DT> struct Fx;
+template <> struct Fx<LUTVQ_F16>  { static constexpr float scale = 1073741824.f, inv = 1.f / 1073741824.f; };   // 2^30
+template <> struct Fx<LUTVQ_BF16> { static constexpr float scale = 1048576.f,    inv = 1.f / 1048576.f; };      // 2^20
 
-__device__ __forceinline__ void sts_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
-    uint4 v;
-    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint4 ldcg_u128(const void* p) {            // L2-coherent: x may be the previous kernel's output
-    uint4 v;
-    asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-    return v;
+template <int DT>
+__device__ __forceinline__ unsigned long long fx_contribution(float v) {
+    // clamp so that the sum of n_k <= 255 contributions cannot leave the signed 56-bit field: |fx| < 2^47
+    float sv = v * Fx<DT>::scale;
+    sv = fminf(fmaxf(sv, -1.4e14f), 1.4e14f);                   // NaN -> -1.4e14 (fmaxf/fminf drop NaN), 1.4e14 < 2^47
+    const long long fx = __float2ll_rn(sv);
+    return ((unsigned long long)fx << 8) + 1ull;
 }
 __device__ __forceinline__ unsigned long long atom_add_u64(unsigned long long* p, unsigned long long v) {
     unsigned long long old;
     asm volatile("atom.relaxed.gpu.global.add.u64 %0, [%1], %2;" : "=l"(old) : "l"(p), "l"(v) : "memory");
     return old;
 }
+template <int DT>
+__device__ __forceinline__ float fx_total(unsigned long long word) {
+    return (float)((long long)word >> 8) * Fx<DT>::inv;          // arithmetic shift drops the arrival count
+}
 // asynchronous HBM -> L2 prefetch of a contiguous range (no registers, no shared memory)
-__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes, uint64_t pol) {
-    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" :: "l"(p), "r"(bytes), "l"(pol) : "memory");
-}
-__device__ __forceinline__ void l2_prefetch_line(const void* p) {
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-}
 // L2 residency: the code stream is read exactly once per GEMV (evict_first), while the few KB of codebook / scales / bias
 // of every layer are re-read every token (evict_last): without the hints the 11 MB stream of each launch pushes them out
-// and every launch pays HBM latency for its codebook in the prologue and for its scales in the tail.
+// and every launch pays HBM latency for its codebook in the prologue and for its scales in the tail
+// (round 2: 5.13 -> 4.50 us per independent launch, 8.1 -> 7.7 dependent, on the 16-bit-LUT kernel this was measured on).
+__device__ __forceinline__ uint4 ldcg_u128(const void* p) {            // L2-coherent: x may be the previous kernel's output
+    uint4 v;
+    asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     uint64_t pol;
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
@@ -195,36 +203,53 @@ __device__ __forceinline__ uint16_t ldg_u16_pol(const void* p, uint64_t pol) {
     asm volatile("ld.global.nc.L2::cache_hint.u16 %0, [%1], %2;" : "=h"(r) : "l"(p), "l"(pol));
     return r;
 }
-// ---- mbarrier + 1-D bulk async copy (TMA engine, no tensor map): global -> this CTA's shared memory ----
-__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(mbar), "r"(count) : "memory");
+__device__ __forceinline__ void l2_prefetch_bulk_pol(const void* p, uint32_t bytes, uint64_t pol) {
+    asm volatile("cp.async.bulk.prefetch.L2.global.L2::cache_hint [%0], %1, %2;" :: "l"(p), "r"(bytes), "l"(pol) : "memory");
 }
-__device__ __forceinline__ void fence_mbar_init() {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar, uint64_t pol) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(mbar), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                 :: "r"(dst), "l"(src), "r"(bytes), "r"(mbar), "l"(pol) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "LAB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE;\n"
-        "bra LAB_WAIT;\n"
-        "DONE:\n"
-        "}\n" :: "r"(mbar), "r"(parity) : "memory");
+// per-thread (non-uniform address) L2 prefetch of the line holding p
+__device__ __forceinline__ void l2_prefetch_line(const void* p) {
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
 }
 
-// ---- fixed-point LUT entries (see the file header) ----
-constexpr float    kFxTarget   = 32704.f;                            // |L * S| <= 32704 < 32767: margin for the fp32 roundings of bound and S
-constexpr float    kFxMagicB   = 12582912.f + 32768.f;               // 1.5 * 2^23 + bias: float bits' low 16 = round(v) + 32768
-constexpr int      kFxBias     = 32768;
-constexpr unsigned long long kFieldMask = (1ull << 29) - 1ull;
+template <int DT>
+__device__ __forceinline__ void epilogue_store(void* y, const void* scales, const void* bias, int row, float acc) {
+    using D = Dtype<DT>;
+    using T = typename D::T;
+    T r = D::from_f(acc);                                                  // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
+    if (scales) r = D::mul(r, static_cast<const T*>(scales)[row]);         // flat_output *= scales             (cuda_kernel.cpp:101)
+    if (bias)   r = D::add(r, static_cast<const T*>(bias)[row]);           // flat_output += bias               (cuda_kernel.cpp:103)
+    static_cast<T*>(y)[row] = r;
+}
+
+// ---- fixed-point LUT entries --------------------------------------------------------------------------------
+// The LUT holds INTEGERS: entry = round(L * 2^e) with one exponent e per (CTA, k-slice), chosen from the bound
+// |L| <= 8 * max|codebook| * max|x_slice| so that |entry| <= 2^22 (the whole signed range of the magic-number trick).  The conversion is free: the build adds the
+// magic constant 1.5 * 2^23 with the scaling FMA, which leaves 0x4B400000 + entry in the float's bits, and the
+// gather adds those words as plain 32-bit integers (one IADD3 per TWO lookups instead of one FADD per lookup); the
+// 64 magic offsets of a row partial (64 tables) are removed once, mod 2^32.  Integer sums are exact and order-free;
+// resolution is 2^-22 of the slice bound, i.e. >= 2^11 times finer than the fp16 LUT of the golden model (vq.py:285).
+constexpr float    kFxMagic     = 12582912.f;                       // 1.5 * 2^23
+constexpr uint32_t kFxMagicBits = 0x4B400000u;
+constexpr uint32_t kFxMagic64   = (uint32_t)(64ull * kFxMagicBits); // 64 lookups per row partial, mod 2^32
+
+// |v| bits of the two halves of a packed fp16x2 / bf16x2 word, as an integer that orders like |v| (NaN highest)
+__device__ __forceinline__ uint32_t absmax_halves(uint32_t w) { return max(w & 0x7FFFu, (w >> 16) & 0x7FFFu); }
+template <int DT> __device__ __forceinline__ float abs_half_bits_to_float(uint32_t h);
+template <> __device__ __forceinline__ float abs_half_bits_to_float<LUTVQ_F16>(uint32_t h)  { return __half2float(__ushort_as_half((unsigned short)h)); }
+template <> __device__ __forceinline__ float abs_half_bits_to_float<LUTVQ_BF16>(uint32_t h) { return __uint_as_float(h << 16); }
+// scale 2^e and its inverse for a slice whose entries are bounded by `bound` (>= 0): |L * 2^e| <= 2^22, so a row
+// partial (64 entries) stays below 2^28.
+// Degenerate bounds: < 2^-107 -> inverse flushes to 0 (outputs 0); inf/NaN -> inverse NaN (the partial saturates).
+__device__ __forceinline__ void fx_scales(float bound, float& scale, float& inv) {
+    uint32_t ex = (__float_as_uint(bound) >> 23) & 0xFFu;            // bound < 2^(ex - 126)
+    const bool bad = ex == 255u;
+    ex = max(ex, 21u);
+    scale = __uint_as_float((275u - ex) << 23);                      // 2^(148 - ex): bound * scale < 2^22
+    inv   = bad ? __uint_as_float(0x7FC00000u) : __uint_as_float((ex - 21u) << 23);
+}
 
 // store one finished output element locally and into every peer's gather buffer (sharded decode)
 template <int DT>
@@ -234,6 +259,9 @@ __device__ __forceinline__ void store_y(const GemvParams& p, const GemvProblem& 
     for (int r = 0; r < p.n_push; ++r) static_cast<T*>(p.push_y[r])[row] = v;       // NVLink stores (peer memory)
 }
 
+// One warp tile set = 32 rows x 64 bytes: 4 tiles of 8 rows; per lane 4 x 16 bytes.
+struct CodeRegs { uint32_t w[4][4]; };
+
 // Fallback when the grid is larger than the tabulated ranges (never on a 148-SM B200): the linear plan, one problem.
 __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, int& begin, int& end) {
     const long long T = (long long)p.n_k * p.prob[0].n_sets;
@@ -241,75 +269,15 @@ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, 
     end   = (int)((T * (w + 1)) / W);
 }
 
-// One lookup = one full-rate 32-bit shared load of the word {codebook 0 | codebook 1 << 16} of (group, idx) + one IDP.2A that adds
-// the wanted 16-bit half to the accumulator (multipliers {1, 0} / {0, 1}).  (16-bit shared loads, the obvious alternative, ran
-// at about half the wavefront rate of 32-bit ones: the gather saturated at 0.55 wavefronts per clock and SM.)
-__device__ __forceinline__ uint32_t dp2a_lo(uint32_t a, uint32_t b, uint32_t c) {
-    uint32_t d;
-    asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
-    return d;
-}
-__device__ __forceinline__ uint32_t lds_u32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
-
-// 32 lookups of one tile: the lane's two 16-byte code images (halves p = 0, 1) against the slice LUT at `lut`
-__device__ __forceinline__ uint32_t gather_tile(const uint8_t* lut, const uint4& w0, const uint4& w1, const uint32_t (&lm)[8]) {
-    const uint32_t w[2][4] = {{w0.x, w0.y, w0.z, w0.w}, {w1.x, w1.y, w1.z, w1.w}};
-    uint32_t acc0 = 0, acc1 = 0;
-    #pragma unroll
-    for (int p = 0; p < 2; ++p)
-        #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            #pragma unroll
-            for (int b = 0; b < 4; b += 2) {
-                const int u = 2 * j + (b >> 1);                      // image bytes k = 4j + b, 4j + b + 1: (u, h = 0) and (u, h = 1)
-                const uint32_t ad0 = __byte_perm(w[p][j], lm[u], 0x6504u | (uint32_t)(b << 4));
-                const uint32_t ad1 = __byte_perm(w[p][j], lm[u], 0x6504u | (uint32_t)((b + 1) << 4));
-                acc0 = dp2a_lo(lds_u32(lut + ad0 + (128 * p)), 0x0001u, acc0);      // codebook 0: low half
-                acc1 = dp2a_lo(lds_u32(lut + ad1 + (128 * p)), 0x0100u, acc1);      // codebook 1: high half
-            }
-    return acc0 + acc1;
-}
-
-// 16 lookups of one half tile (half p of the lane's image) against the slice LUT at `lut`
-template <int P>
-__device__ __forceinline__ uint32_t gather_half(const uint8_t* lut, const uint4& wv, const uint32_t (&lm)[8]) {
-    const uint32_t w[4] = {wv.x, wv.y, wv.z, wv.w};
-    uint32_t acc0 = 0, acc1 = 0;
-    #pragma unroll
-    for (int j = 0; j < 4; ++j)
-        #pragma unroll
-        for (int b = 0; b < 4; b += 2) {
-            const int u = 2 * j + (b >> 1);
-            const uint32_t ad0 = __byte_perm(w[j], lm[u], 0x6504u | (uint32_t)(b << 4));
-            const uint32_t ad1 = __byte_perm(w[j], lm[u], 0x6504u | (uint32_t)((b + 1) << 4));
-            acc0 = dp2a_lo(lds_u32(lut + ad0 + (128 * P)), 0x0001u, acc0);
-            acc1 = dp2a_lo(lds_u32(lut + ad1 + (128 * P)), 0x0100u, acc1);
-        }
-    return acc0 + acc1;
-}
-
-// Code streaming modes.
-//   kStreamRegs  128-bit no-allocate loads into a rolling register ring of kRingPieces half tiles (512 B per warp and piece):
-//                no shared memory besides the LUT, <= 80 registers => THREE CTAs (of consecutive launches) per SM.
-//   kStreamBulk  one 4 KiB bulk async copy (cp.async.bulk + mbarrier) per set into a per-warp landing slot, moved to registers
-//                on arrival and refilled at once: 96 KiB of shared memory and 128 registers => two CTAs per SM.
-constexpr int kStreamRegs = 0, kStreamBulk = 1;
-constexpr int kRingPieces = 4;
-// dynamic shared memory: [LUT 64 KiB]( + [NW landing slots of one set = 4 KiB each][NW mbarriers x 8 B])
-template <int NW, int MODE> constexpr size_t gemv_smem_bytes() { return (size_t)kSliceBytes + (MODE == kStreamBulk ? (size_t)NW * kSetBytes + (size_t)NW * 8 : 0); }
-
-template <int DT, int NW, int MODE>
-__global__ void __launch_bounds__(NW * 32, MODE == kStreamRegs ? 3 : 2)
-lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
-    static_assert(16 % NW == 0, "NW divides the 16 idx blocks");
-    static_assert(NW * 32 >= kSliceGroups, "one thread per group of the slice loads x");
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB)
+lut_gemv_2x8_kernel(const GemvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t lut_base = smem_u32(smem_raw);
     const GemvProblem& PB = p.prob[p.n_prob > 1 ? (int)p.tab_prob[blockIdx.x] : 0];       // indexed constant-bank loads
 
     TL_STAMP(0);
 #if LUTVQ_DBG
-    if (p.flags & 0x1000u) pdl_launch_dependents();
     if (p.tl != nullptr && threadIdx.x == 0) {
         unsigned smid;
         asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
@@ -317,61 +285,86 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     }
 #endif
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int W = gridDim.x;
     int begin, end;
     if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_end[blockIdx.x]; }          // two constant-bank loads
-    else worker_range(p, blockIdx.x, gridDim.x, begin, end);
+    else worker_range(p, blockIdx.x, W, begin, end);
+    const size_t row_bytes = (size_t)p.G * 2;
+    const int last_row = PB.O - 1;
 
-    // kStreamBulk: this warp's landing slot (one 4 KiB set, filled by ONE bulk copy: small copies are bound by the per-SM issue
-    // rate of the copy engine, measured 2.4-3.3 TB/s chip-wide with 1 KiB copies) + its mbarrier.  A set is moved from the slot
-    // into registers as soon as it has landed and the slot is refilled at once.
-    const uint32_t slot_base = lut_base + kSliceBytes + (uint32_t)warp * kSetBytes;
-    const uint32_t mbar = lut_base + kSliceBytes + (uint32_t)NW * kSetBytes + (uint32_t)warp * 8;
+    // ---------------- streaming-side lane constants ----------------
+    // Reference layout: no predicated loads.  Rows past the end are clamped to the last row (result discarded)
+    // and lanes whose 16-byte chunk lies past the end of the row (last, partial k-slice) re-read chunk 0 --
+    // their tables were built from x = 0, so whatever index they fetch contributes exactly 0.
+    const int e = stream_first_half(lane);
+    const uint64_t pol_stream = l2_policy_evict_first();
+    auto load_set = [&](CodeRegs& r, int ks, int set) {
+        if (PACKED) {
+            const uint4* base = reinterpret_cast<const uint4*>(PB.codes) + (((size_t)ks * PB.n_sets + set) * 4) * 32 + lane;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const uint4 v = ldg_stream_u128_pol(base + t * 32, pol_stream);
+                r.w[t][0] = v.x; r.w[t][1] = v.y; r.w[t][2] = v.z; r.w[t][3] = v.w;
+            }
+        } else {
+            const int slice_byte0 = ks * kSliceTables;
+            const bool chunk_valid = (size_t)(slice_byte0 + 16 * stream_chunk(lane)) < row_bytes;
+            const uint8_t* lane_base = PB.codes + slice_byte0 + (chunk_valid ? 16 * stream_chunk(lane) : 0);
+            const int rbase = set * kSetRows + stream_row_in_tile(lane);
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const uint32_t row = (uint32_t)min(rbase + t * kTileRows, last_row);
+                const uint4 v = ldg_stream_u128_pol(lane_base + (uint64_t)row * (uint32_t)row_bytes, pol_stream);
+                // register word c holds memory word c ^ 2e (lut_layout.h)
+                r.w[t][0] = e ? v.z : v.x; r.w[t][1] = e ? v.w : v.y;
+                r.w[t][2] = e ? v.x : v.z; r.w[t][3] = e ? v.y : v.w;
+            }
+        }
+    };
 
+    TL_STAMP(8);
     // The workers of different k-slices walk the same rows; each starts at a slice-dependent rotation of its own
-    // range so that the n_k arrivals of one row set are spread over the whole gather instead of colliding at one instant.
+    // range so that the n_k atomics of one row are spread over the whole gather instead of colliding at one instant.
     auto rot_of = [&](int ks_, int n) { return (int)(((unsigned)ks_ * (unsigned)n) / (unsigned)p.n_k); };
+    auto wrap = [](int v, int n) { while (v >= n) v -= n; return v; };
     // first segment of this worker's range: slice ks, sets [lo, hi)
     int pos = begin;
     int ks = p.has_table ? (int)p.tab_ks[blockIdx.x] : (begin < end) ? (int)((unsigned)begin / (unsigned)PB.n_sets) : 0;
     int lo = begin - ks * PB.n_sets;
     int hi = min(PB.n_sets, lo + (end - begin));
-    int seg_rot = rot_of(ks, hi - lo);
-    // set (index inside the problem) that local index li (rotated) of the current segment stands for
-    auto set_of = [&](int li) -> int {
-        int v = li + seg_rot;
-        const int n = hi - lo;
-        if (v >= n) v -= n;
-        return lo + v;
-    };
-    auto set_ptr = [&](int li) -> const uint8_t* { return PB.codes + ((size_t)ks * PB.n_sets + (size_t)set_of(li)) * kSetBytes; };
-    // one set into this warp's landing slot (lane 0; the slot is free)
-    const uint64_t pol_stream = l2_policy_evict_first(), pol_keep = l2_policy_evict_last();
-    auto fill_slot = [&](const uint8_t* sp) { bulk_load(slot_base, sp, kSetBytes, mbar, pol_stream); };
 
+    int seg_rot = rot_of(ks, hi - lo);
     // ---------------- prologue that does not depend on the previous kernel in the stream ----------------
-    // Codes and codebooks are weights: the first code pieces (registers / landing slot), the L2 prefetch of the worker's
-    // share and the codebook MMA fragments are all requested BEFORE the programmatic-dependency wait.
-    // kStreamRegs: the rolling register ring: piece i of this warp's stream = 16 bytes per lane at set_ptr(set) + (i % 8) * 512
-    uint4 ring[MODE == kStreamRegs ? kRingPieces : 1];
-    if (MODE == kStreamRegs) {
-        const uint8_t* sp = set_ptr(warp < hi - lo ? warp : 0) + lane * 16;
-        #pragma unroll
-        for (int i = 0; i < kRingPieces; ++i) ring[i] = (begin < end) ? ldg_stream_u128_pol(sp + i * 512, pol_stream) : make_uint4(0u, 0u, 0u, 0u);
-    }
-    if (lane == 0) {
-        if (MODE == kStreamBulk) {
-            mbar_init(mbar, 1);
-            fence_mbar_init();
-            if (warp < hi - lo) fill_slot(set_ptr(warp));
-        }
-        // this worker's share is ONE contiguous range of the packed image: warp w prefetches items w, w + NW, ...
-        const uint8_t* base = PB.codes + (size_t)begin * kSetBytes;
-        if (p.flags & kFlagL2Prefetch LUTVQ_DBG_AND(!(p.flags & 0x800u)))
-            for (int c = warp; c < end - begin; c += NW) l2_prefetch_bulk(base + (size_t)c * kSetBytes, kSetBytes, pol_stream);
-    }
+    // Codes and codebooks are weights.  (1) the first PF tile sets are requested into registers, (2) the rest
+    // of this worker's share is pushed HBM -> L2, (3) x / the workspace header are pulled into L2 (L2 is the
+    // coherence point, so this is safe even while the previous kernel is still writing them), (4) the codebook
+    // MMA fragments are loaded -- all BEFORE the programmatic-dependency wait.
+    CodeRegs buf[PF];
+    #pragma unroll
+    for (int i = 0; i < PF; ++i)
+        if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + wrap(warp + i * NW + seg_rot, hi - lo));
     TL_STAMP(9);
+    if (PACKED) {
+        // the worker's whole share is ONE contiguous range of the packed image (linear item index * 2048 B)
+        if (lane == 0) {
+            const uint8_t* base = PB.codes + (size_t)begin * 2048;
+            const int n = end - begin;
+            for (int c = warp * 4 + PF * NW; c < n; c += NW * 4)
+                l2_prefetch_bulk_pol(base + (size_t)c * 2048, (uint32_t)min(4, n - c) * 2048u, pol_stream);
+        }
+    } else {
+        int ppos = begin;
+        while (ppos < end) {
+            const int s = ppos / PB.n_sets, l = ppos - s * PB.n_sets, h = min(PB.n_sets, l + (end - ppos));
+            const size_t off = (size_t)s * kSliceTables;
+            const int r1 = min(h * kSetRows, PB.O);
+            for (int r = l * kSetRows + threadIdx.x; r < r1; r += NW * 32)
+                l2_prefetch_line(PB.codes + (size_t)r * row_bytes + off);
+            ppos += h - l;
+        }
+    }
     if (p.n_k > 1 && begin < end) {
-        // scale / bias of this worker's first-segment rows: 64 B per set each, pulled into L2 for the finishing rows
+        // scale / bias of this worker's first-segment rows: 64 B per set each, pulled into L2 for the in-loop fetch
         const int nl = (hi - lo + 1) / 2;                             // 128-byte lines
         if ((int)threadIdx.x < nl) {
             const size_t off = (size_t)lo * 64 + (size_t)threadIdx.x * 128;
@@ -381,16 +374,20 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
             }
         }
     }
+    if (warp == NW - 1) {
+        if (lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
+        {
+            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * 512 + lane * 128);
+            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * 512 + lane * 128);
+        }
+    }
+    TL_STAMP(10);
     const int r = lane >> 2, q = lane & 3;
     constexpr int MB_PER_WARP = 16 / NW;                                   // 16 idx blocks of 16 per codebook
-    constexpr int NT = NW * 32;
-    // Every CTA of a launch reads the same 8 KiB codebook and the same x at the same moment: those few hot lines are served by
-    // a few L2 slices, and the launch's whole "skeleton" was bound by that traffic (measured: 3 us per launch with lookups,
-    // streaming and atomics switched off).  So each line is requested ONCE per CTA: the codebook only as MMA fragments (its row
-    // norms come out of the same registers), x only as the CTA's own 1 KiB slice through shared memory.
     uint32_t afrag[MB_PER_WARP][2][2];
     {
         const uint32_t* cb32 = static_cast<const uint32_t*>(PB.codebook);  // [2][256][4] words (2 values each)
+        const uint64_t pol_keep = l2_policy_evict_last();
         // A fragments for this warp's idx blocks: rows 16m + r and 16m + r + 8, k = 2q, 2q+1
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi) {
@@ -402,32 +399,20 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
             }
         }
     }
-    __shared__ uint32_t red_c[NW], red_x[NW];
-    __shared__ __align__(16) uint4 xs[kSliceGroups];                      // the slice's 64 activation groups (silu(gate) * x applied)
+    // max |codebook| over the CTA (every warp holds 1/NW of it in its A fragments): one REDUX + one smem word per warp
+    __shared__ uint32_t cmax_red[NW];
     {
-        // max over this warp's codebook rows of |row|_2^2, from the fragments: a row's 8 values sit in the 4 lanes of a quad.
-        // (bits of a non-negative float order like the float; NaN highest)
-        uint32_t mc = 0;
+        uint32_t m = 0;
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi)
             #pragma unroll
-            for (int n = 0; n < 2; ++n)
-                #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const float2 f = unpack2<DT>(afrag[mi][n][h]);
-                    float s2 = fmaf(f.y, f.y, f.x * f.x);
-                    s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
-                    s2 += __shfl_xor_sync(0xffffffffu, s2, 2);
-                    mc = max(mc, __float_as_uint(s2));
-                }
-        mc = __reduce_max_sync(0xffffffffu, mc);
-        if (lane == 0) red_c[warp] = mc;
+            for (int n = 0; n < 2; ++n) m = max(m, max(absmax_halves(afrag[mi][n][0]), absmax_halves(afrag[mi][n][1])));
+        m = __reduce_max_sync(0xffffffffu, m);
+        if (lane == 0) cmax_red[warp] = m;
     }
     TL_STAMP(1);
     // The next launch may become resident now that OUR weight requests are in flight (it still waits for us below).
-#if LUTVQ_DBG
-    if (!(p.flags & 0x1000u))                                      // DEBUG 0x1000: the trigger was issued at kernel entry instead
-#endif
+    // Measured on B200 (4096x11008, 3 CTAs/SM): triggering at kernel entry instead costs 5.4 us per launch vs 4.0 us.
     pdl_launch_dependents();
     // X_READY: x is not the previous kernel's output and the workspace is exclusively ours (include/lutvq.h), so
     // nothing but the final y stores has to be ordered behind the previous kernel.
@@ -435,249 +420,231 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     bool waited = !xready;
     if (!xready) pdl_wait();    // x and the workspace belong to the previous kernel until here
     TL_STAMP(2);
-
-    const bool gated = (DT == LUTVQ_F16) && p.x_gate != nullptr;
-    auto load_group = [&](int g) -> uint4 {                        // 16 bytes = one group of 8 activations, SwiGLU applied on the way in
-        uint4 v = ldcg_u128(static_cast<const uint4*>(p.x) + g);
-        if (gated) {
-            const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
-            v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
-            v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
-        }
-        return v;
-    };
-    // the CTA's slice of x for a later segment: one coalesced 16-byte load per group (8 lines for the whole CTA)
+    // The slice's 32 activation groups (512 B = 4 lines) are requested ONCE per CTA and shared through shared memory: every
+    // CTA of a slice reads the same few lines at the same moment, and when all 8 warps fetched their B fragments themselves
+    // (4 scattered 4-byte loads per lane) each hot line took 16 requests per CTA at its L2 slice.
+    constexpr int kSliceGroups = kSliceTables / 2;                    // 32 groups of 8 activations per k-slice
+    __shared__ __align__(16) uint4 xs[kSliceGroups];
     auto load_x_slice = [&](int ks_) {
         if (threadIdx.x < kSliceGroups) {
             const int g = ks_ * kSliceGroups + (int)threadIdx.x;
-            xs[threadIdx.x] = (g < p.G) ? load_group(g) : make_uint4(0u, 0u, 0u, 0u);
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (g < p.G) {
+                v = ldcg_u128(static_cast<const uint4*>(p.x) + g);        // L2-coherent: x may be the previous kernel's output
+                if (DT == LUTVQ_F16 && p.x_gate != nullptr) {
+                    const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
+                    v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
+                    v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+                }
+            }
+            xs[threadIdx.x] = v;
         }
     };
-    // ---------------- the activation-dependent part of the scale: max_g |x_g|_2^2 over ALL groups ----------------
-    // ONE coalesced pass per CTA (every line of x requested once), XU loads in flight per thread; the groups of the CTA's
-    // own slice are dropped into shared memory on the way (the B fragments come from there, not from L2 again).
+    load_x_slice(ks);
+
+    // PRMT operands (lut_layout.h): byte0 <- lm, byte1 <- code byte, bytes 2,3 <- 0.  The slice base and the
+    // (c&1)*128 half-select are compile-time constants for ptxas and ride in the LDS immediate.
+    uint32_t sel[4], lm[2][4];
+    #pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        sel[d] = stream_sel(lane, d);
+        lm[0][d] = stream_lm(lane, 0, d);
+        lm[1][d] = stream_lm(lane, 1, d);
+    }
+    __syncthreads();
+    float cmax8;
     {
         uint32_t m = 0;
-        constexpr int XU = 4;
-        if (threadIdx.x < kSliceGroups && ks * kSliceGroups + (int)threadIdx.x >= p.G) xs[threadIdx.x] = make_uint4(0u, 0u, 0u, 0u);
-        for (int g0 = threadIdx.x; g0 < p.G; g0 += XU * NT) {
-            uint4 v[XU];
-            #pragma unroll
-            for (int u = 0; u < XU; ++u) {
-                const int g = g0 + u * NT;
-                v[u] = (g < p.G) ? load_group(g) : make_uint4(0u, 0u, 0u, 0u);
-            }
-            #pragma unroll
-            for (int u = 0; u < XU; ++u) {
-                const int g = g0 + u * NT;
-                const unsigned loc = (unsigned)(g - ks * kSliceGroups);
-                if (g < p.G && loc < (unsigned)kSliceGroups) xs[loc] = v[u];
-                m = max(m, __float_as_uint(sumsq8<DT>(v[u])));
-            }
-        }
-        m = __reduce_max_sync(0xffffffffu, m);
-        if (lane == 0) red_x[warp] = m;
+        #pragma unroll
+        for (int i = 0; i < NW; ++i) m = max(m, cmax_red[i]);
+        cmax8 = 8.f * abs_half_bits_to_float<DT>(m);
     }
-
-    uint32_t lm[8];
-    #pragma unroll
-    for (int u = 0; u < 8; ++u) lm[u] = stream_lm(lane, u);
     const bool b3 = (lane >> 3) & 1, b4 = (lane >> 4) & 1;
     const bool odd = r & 1;
     const bool round16 = (p.flags & LUTVQ_FLAG_LUT_FP16) != 0;
+    bool first_seg = true;
+    float fx_scale = 1.f, fx_inv = 1.f;                                  // this segment's 2^e and 2^-e
 
-    // ---- split-k completion: see the file header ----
+    // ---- split-k completion: see the accumulator word comment above ----
     using D = Dtype<DT>;
     using T = typename D::T;
-    const int bias_total = p.n_k * kSliceTables * kFxBias;               // every table of every slice contributes the bias once
-    unsigned long long pend_old = 0, pend_add = 0;
-    int pend_row = 0;
-    bool pend_valid = false;
+    // A contribution's atomic is issued at the end of its set and its return value is examined PF sets later, so the
+    // L2 round trip hides behind lookups.  Pending state per slot: the returned word, the partial and the row.
+    static_assert(PA % PF == 0, "the pending-atomic ring must be a whole number of code rings");
+    unsigned long long pend_old[PA];
+    float pend_keep[PA];
+    int pend_row[PA];
+    bool pend_valid[PA];
+    #pragma unroll
+    for (int i = 0; i < PA; ++i) { pend_old[i] = 0; pend_keep[i] = 0.f; pend_row[i] = 0; pend_valid[i] = false; }
     const unsigned last_count = (unsigned)p.n_k - 1u;
-    float fx_scale = 0.f, fx_inv = 0.f;
-    bool bad = false;
-    auto finish_one = [&](unsigned field, int row) {
-        if (row < PB.O) {
-            float v = (float)((int)field - bias_total) * fx_inv;
-            if (bad) v = __uint_as_float(0x7FC00000u);
-            T rr = D::from_f(v);                                                    // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
-            if (PB.scales) { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.scales) + row, pol_keep); rr = D::mul(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output *= scales (cuda_kernel.cpp:101)
-            if (PB.bias)   { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.bias) + row, pol_keep);   rr = D::add(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output += bias   (cuda_kernel.cpp:103)
-            store_y<DT>(p, PB, row, rr);
-        }
-    };
-    auto finish_pair = [&](unsigned long long old, unsigned long long add, int row) {   // row = even row of the pair
-        if ((unsigned)(old >> 58) == last_count) {                 // this lane delivered the last partial of the pair
+    auto finish_row = [&](unsigned long long old, float keep, int row) {
+        if ((unsigned)(old & 255ull) == last_count) {              // this lane delivered the last partial of `row`
             if (!waited) { pdl_wait(); waited = true; }            // y stores are ordered behind the previous kernel
-            const unsigned long long total = old + add;
-            if (p.n_k > 1) asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(PB.acc + (row >> 1)), "l"(0ull) : "memory");   // hand the word back
-            finish_one((unsigned)(total & kFieldMask), row);
-            finish_one((unsigned)((total >> 29) & kFieldMask), row + 1);
+            const float total = fx_total<DT>(old + fx_contribution<DT>(keep));
+            asm volatile("st.global.cg.b64 [%0], %1;" :: "l"(PB.acc + row), "l"(0ull) : "memory");   // hand the word back
+            if (row < PB.O) {
+                T rr = D::from_f(total);                                               // Code2x8MatVec writes round(acc)   (cuda_kernel.cu:221-231)
+                const uint64_t pol_keep = l2_policy_evict_last();
+                // scale / bias were pulled into L2 by the prologue; only the last arriver (1 in n_k) pays this round trip
+                if (PB.scales) { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.scales) + row, pol_keep); rr = D::mul(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output *= scales (cuda_kernel.cpp:101)
+                if (PB.bias)   { const uint16_t b = ldg_u16_pol(static_cast<const T*>(PB.bias) + row, pol_keep);   rr = D::add(rr, *reinterpret_cast<const T*>(&b)); }   // flat_output += bias   (cuda_kernel.cpp:103)
+                store_y<DT>(p, PB, row, rr);
+            }
         }
     };
 
-    bool first_seg = true;
-    uint32_t phase = 0;                                            // kStreamBulk: parity of this warp's slot barrier
     while (pos < end) {
-        const int n_seg = hi - lo;
         // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
-        if (!first_seg) {
-            __syncthreads();                                       // everyone is done reading the previous slice's LUT and xs
-            if (MODE == kStreamBulk) { if (lane == 0 && warp < n_seg) fill_slot(set_ptr(warp)); }
-            else if (warp < n_seg) {
-                const uint8_t* sp = set_ptr(warp) + lane * 16;
-                #pragma unroll
-                for (int i = 0; i < kRingPieces; ++i) ring[i] = ldg_stream_u128_pol(sp + i * 512, pol_stream);
+        {
+            // B fragments: column r of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
+            uint32_t bfrag[4];
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) bfrag[j] = reinterpret_cast<const uint32_t*>(xs)[build_group_of_col(j, r) * 4 + q];
+            {   // the warp's 32 lanes x 4 words are exactly the slice's 256 activations
+                uint32_t m = max(max(absmax_halves(bfrag[0]), absmax_halves(bfrag[1])), max(absmax_halves(bfrag[2]), absmax_halves(bfrag[3])));
+                m = __reduce_max_sync(0xffffffffu, m);
+                fx_scales(cmax8 * abs_half_bits_to_float<DT>(m), fx_scale, fx_inv);
             }
-            load_x_slice(ks);
-        }
-        __syncthreads();                                           // xs and red_c are complete
-        if (first_seg) TL_STAMP(10);
-        if (first_seg) {
-            // ONE fixed-point scale per GEMV: S = 32704 / (max_k |C_k|_2 * max_g |x_g|_2) >= |L| by Cauchy-Schwarz, computed
-            // identically by every CTA from (x, codebook) alone
-            uint32_t mc = 0, mx = 0;
             #pragma unroll
-            for (int i = 0; i < NW; ++i) { mc = max(mc, red_c[i]); mx = max(mx, red_x[i]); }
-            const float bound = sqrtf(__uint_as_float(mc) * __uint_as_float(mx));
-            bad = !(bound < __uint_as_float(0x7F800000u));          // inf or NaN activations / codebooks: the outputs are NaN
-            const bool tiny = !(bound > 1e-30f);
-            fx_scale = (bad || tiny) ? 0.f : __fdiv_rn(kFxTarget, bound);
-            fx_inv   = (bad || tiny) ? 0.f : __fdiv_rn(bound, kFxTarget);
-        }
-        // B fragments of the slice: column (lane>>2) of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
-        uint32_t bfrag[8];
-        #pragma unroll
-        for (int j = 0; j < 8; ++j) bfrag[j] = reinterpret_cast<const uint32_t*>(xs)[build_group_of_col(j, r) * 4 + q];
-        if (first_seg) TL_STAMP(11);
-        #pragma unroll
-        for (int mi = 0; mi < MB_PER_WARP; ++mi) {
-            const int m = warp * MB_PER_WARP + mi;
-            #pragma unroll
-            for (int hb = 0; hb < 2; ++hb) {                       // N-tiles 4hb .. 4hb+3 = tile pairs 2hb, 2hb+1
+            for (int mi = 0; mi < MB_PER_WARP; ++mi) {
+                const int m = warp * MB_PER_WARP + mi;
                 float c[2][4][4];
                 #pragma unroll
                 for (int n = 0; n < 2; ++n)
                     #pragma unroll
-                    for (int jj = 0; jj < 4; ++jj) {
-                        c[n][jj][0] = c[n][jj][1] = c[n][jj][2] = c[n][jj][3] = 0.f;
-                        MmaK8<DT>::run(c[n][jj], afrag[mi][n][0], afrag[mi][n][1], bfrag[4 * hb + jj]);
+                    for (int j = 0; j < 4; ++j) {
+                        c[n][j][0] = c[n][j][1] = c[n][j][2] = c[n][j][3] = 0.f;
+                        MmaK8<DT>::run(c[n][j], afrag[mi][n][0], afrag[mi][n][1], bfrag[j]);
                     }
-                // words[ii][hh][e*2+f]: tile pair ii of this half, idx row r + 8hh, groups +0..3 = (tile 2ii+e, column 2q+f)
                 #pragma unroll
-                for (int hh = 0; hh < 2; ++hh) {
-                    uint32_t wd[2][4];
+                for (int n = 0; n < 2; ++n)
                     #pragma unroll
-                    for (int ii = 0; ii < 2; ++ii)
+                    for (int j = 0; j < 4; ++j)
                         #pragma unroll
-                        for (int e = 0; e < 2; ++e)
-                            #pragma unroll
-                            for (int f = 0; f < 2; ++f) {
-                                float v0 = c[0][2 * ii + e][2 * hh + f], v1 = c[1][2 * ii + e][2 * hh + f];
-                                if (round16) { v0 = __half2float(__float2half_rn(v0)); v1 = __half2float(__float2half_rn(v1)); }
-                                const uint32_t u0 = __float_as_uint(fmaf(v0, fx_scale, kFxMagicB));   // low 16 bits = round(v * S) + 32768
-                                const uint32_t u1 = __float_as_uint(fmaf(v1, fx_scale, kFxMagicB));
-                                wd[ii][2 * e + f] = __byte_perm(u0, u1, 0x5410);                       // {codebook 0 | codebook 1 << 16}
-                            }
-                    const int idx = 16 * m + r + 8 * hh;
-                    // first store: odd lanes take pair 1, even lanes pair 0 (8 distinct 16-byte columns per quarter-warp phase)
-                    const uint32_t first  = lut_base + build_store_offset(idx, 2 * hb + (odd ? 1 : 0), q);
-                    const uint32_t second = lut_base + build_store_offset(idx, 2 * hb + (odd ? 0 : 1), q);
-                    sts_v4(first,  odd ? wd[1][0] : wd[0][0], odd ? wd[1][1] : wd[0][1], odd ? wd[1][2] : wd[0][2], odd ? wd[1][3] : wd[0][3]);
-                    sts_v4(second, odd ? wd[0][0] : wd[1][0], odd ? wd[0][1] : wd[1][1], odd ? wd[0][2] : wd[1][2], odd ? wd[0][3] : wd[1][3]);
+                        for (int i = 0; i < 4; ++i) {
+                            float v = c[n][j][i];
+                            if (round16) v = __half2float(__float2half_rn(v));
+                            c[n][j][i] = fmaf(v, fx_scale, kFxMagic);      // float bits = 0x4B400000 + round(v * 2^e)
+                        }
+                // c[n][j][2h+u]: idx = 16m + r + 8h, table bytes beta = 2u+n of (chunk q, word w_j)
+                #pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int idx = 16 * m + r + 8 * h;
+                    #pragma unroll
+                    for (int jp = 0; jp < 2; ++jp) {
+                        const int j0 = 2 * jp, j1 = 2 * jp + 1;
+                        // first store: odd lanes take tile j1, even lanes tile j0 (8 distinct 16-byte columns per phase)
+                        float f0 = odd ? c[0][j1][2 * h] : c[0][j0][2 * h];
+                        float f1 = odd ? c[1][j1][2 * h] : c[1][j0][2 * h];
+                        float f2 = odd ? c[0][j1][2 * h + 1] : c[0][j0][2 * h + 1];
+                        float f3 = odd ? c[1][j1][2 * h + 1] : c[1][j0][2 * h + 1];
+                        float s0 = odd ? c[0][j0][2 * h] : c[0][j1][2 * h];
+                        float s1 = odd ? c[1][j0][2 * h] : c[1][j1][2 * h];
+                        float s2 = odd ? c[0][j0][2 * h + 1] : c[0][j1][2 * h + 1];
+                        float s3 = odd ? c[1][j0][2 * h + 1] : c[1][j1][2 * h + 1];
+                        const uint32_t first  = lut_base + build_store_offset(idx, odd ? j1 : j0, q);
+                        const uint32_t second = lut_base + build_store_offset(idx, odd ? j0 : j1, q);
+                        sts_v4(first, f0, f1, f2, f3);
+                        sts_v4(second, s0, s1, s2, s3);
+                    }
                 }
             }
         }
-        if (first_seg) TL_STAMP(12);
         __syncthreads();
         if (first_seg) TL_STAMP(3);
         first_seg = false;
 
-        // ---------------- K2: gather-accumulate over this warp's sets of the segment ----------------
-        for (int li = warp; li < n_seg; li += NW) {
-            const bool has_next = li + NW < n_seg;
-            uint32_t acc[4];
-            if (MODE == kStreamBulk) {
-                uint4 w[4][2];
-#if LUTVQ_DBG
-                if (!(p.flags & 0x200u))                           // DEBUG 0x200: no code streaming at all (stale slot contents)
-#endif
-                mbar_wait(mbar, phase);
-                phase ^= 1u;
+        // ---------------- K2: stream codes, gather-accumulate ----------------
+        {
+            const int n_seg = hi - lo;
+            int v = warp + seg_rot;                                  // rotated local index of this warp's next set
+            if (v >= n_seg) v -= n_seg;
+            int vnext = v;                                           // ... and of the set PF iterations ahead
+            #pragma unroll
+            for (int i = 0; i < PF; ++i) { vnext += NW; if (vnext >= n_seg) vnext -= n_seg; }
+            for (int li = warp; li < n_seg; li += PA * NW) {
                 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    w[t][0] = lds_v4(slot_base + t * kTileBytes + lane * 16);
-                    w[t][1] = lds_v4(slot_base + t * kTileBytes + 512 + lane * 16);
-                }
-                #pragma unroll
-                for (int t = 0; t < 4; ++t) {
+                for (int sa = 0; sa < PA; ++sa) {
+                    constexpr int kDummy = 0; (void)kDummy;
+                    const int st = sa % PF;                          // code-ring slot (compile-time after unrolling)
+                    if (li + sa * NW < n_seg) {                      // warp-uniform
+                        const int row = (lo + v) * kSetRows + lane;
+                        uint32_t acc[4];
 #if LUTVQ_DBG
-                    if (p.flags & 0x100u) acc[t] = w[t][0].x ^ w[t][0].y ^ w[t][0].z ^ w[t][0].w ^ w[t][1].x ^ w[t][1].y ^ w[t][1].z ^ w[t][1].w;   // DEBUG: no lookups
-                    else
+                        if (p.flags & 0x100u) {                      // DEBUG: no lookups (pure code streaming)
+                            #pragma unroll
+                            for (int t = 0; t < 4; ++t) acc[t] = buf[st].w[t][0] ^ buf[st].w[t][1] ^ buf[st].w[t][2] ^ buf[st].w[t][3];
+                        } else
 #endif
-                    acc[t] = gather_tile(smem_raw, w[t][0], w[t][1], lm);
-                    if (t == 0) {
-                        // Refill the slot with this warp's next set.  Every lane's 8 slot reads were issued before tile 0's
-                        // lookups consumed the first of them (in-order return), ~100 cycles ago; the copy lands >= an L2 round
-                        // trip from now.
-                        __syncwarp();
-                        if (lane == 0 && has_next LUTVQ_DBG_AND(!(p.flags & 0x200u))) fill_slot(set_ptr(li + NW));
+                        {
+                            #pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                                #pragma unroll
+                                for (int d = 0; d < 4; d += 2)
+                                    #pragma unroll
+                                    for (int t = 0; t < 4; ++t) {
+                                        const uint32_t ad0 = __byte_perm(buf[st].w[t][c], lm[c >> 1][d], sel[d]);
+                                        const uint32_t ad1 = __byte_perm(buf[st].w[t][c], lm[c >> 1][d + 1], sel[d + 1]);
+                                        const uint32_t v0 = *reinterpret_cast<const uint32_t*>(smem_raw + ad0 + stream_imm(c));
+                                        const uint32_t v1 = *reinterpret_cast<const uint32_t*>(smem_raw + ad1 + stream_imm(c));
+                                        if (c == 0 && d == 0) acc[t] = v0 + v1;
+                                        else                  acc[t] = acc[t] + v0 + v1;       // IADD3
+                                    }
+                        }
+                        // refill this stage with the set PF iterations ahead before the (short) reduction
+                        if (li + (sa + PF) * NW < n_seg LUTVQ_DBG_AND(!(p.flags & 0x200u))) load_set(buf[st], ks, lo + vnext);
+                        // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
+                        uint32_t k0 = b4 ? acc[2] : acc[0], k1 = b4 ? acc[3] : acc[1];
+                        uint32_t g0 = b4 ? acc[0] : acc[2], g1 = b4 ? acc[1] : acc[3];
+                        k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
+                        k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
+                        uint32_t keep_u = b3 ? k1 : k0, give = b3 ? k0 : k1;
+                        keep_u += __shfl_xor_sync(0xffffffffu, give, 8);
+                        const float keep = (float)(int)(keep_u - kFxMagic64) * fx_inv;     // 64 lookups' magic offsets, mod 2^32
+                        if (p.n_k == 1) {
+                            if (!waited) { pdl_wait(); waited = true; }
+                            if (row < PB.O) {
+                                T rr = D::from_f(keep);
+                                if (PB.scales) rr = D::mul(rr, static_cast<const T*>(PB.scales)[row]);
+                                if (PB.bias)   rr = D::add(rr, static_cast<const T*>(PB.bias)[row]);
+                                store_y<DT>(p, PB, row, rr);
+                            }
+                        } else {
+                            // finish the atomic this slot issued PA sets ago (its L2 round trip, ~1.3 us under load, has
+                            // long completed), then issue this set's
+                            if (pend_valid[sa]) finish_row(pend_old[sa], pend_keep[sa], pend_row[sa]);
+                            pend_row[sa] = row; pend_valid[sa] = true; pend_keep[sa] = keep;
+#if LUTVQ_DBG
+                            if (p.flags & 0x400u) { pend_old[sa] = 0; if (row < PB.O) static_cast<T*>(PB.y)[row] = D::from_f(keep); }   // DEBUG: no atomics
+                            else
+#endif
+                            pend_old[sa] = atom_add_u64(PB.acc + row, fx_contribution<DT>(keep));
+                        }
+                        v += NW;     if (v >= n_seg) v -= n_seg;
+                        vnext += NW; if (vnext >= n_seg) vnext -= n_seg;
                     }
                 }
-            } else {
-                const uint8_t* cur = set_ptr(li) + lane * 16;
-                const uint8_t* nxt = has_next ? set_ptr(li + NW) + lane * 16 : cur;
-                #pragma unroll
-                for (int pc = 0; pc < 8; ++pc) {
-                    const uint4 wv = ring[pc % kRingPieces];
-                    // the piece kRingPieces ahead in this warp's stream takes the freed ring slot (the last set re-reads
-                    // its own pieces: harmless, never consumed)
-                    const int ahead = pc + kRingPieces;
-#if LUTVQ_DBG
-                    if (!(p.flags & 0x200u))
-#endif
-                    ring[pc % kRingPieces] = ldg_stream_u128_pol(ahead < 8 ? cur + ahead * 512 : nxt + (ahead - 8) * 512, pol_stream);
-                    uint32_t a;
-#if LUTVQ_DBG
-                    if (p.flags & 0x100u) a = wv.x ^ wv.y ^ wv.z ^ wv.w;
-                    else
-#endif
-                    a = (pc & 1) ? gather_half<1>(smem_raw, wv, lm) : gather_half<0>(smem_raw, wv, lm);
-                    if (pc & 1) acc[pc >> 1] += a; else acc[pc >> 1] = a;
-                }
-            }
-            // transposed reduce over the 4 chunk lanes (lane bits 3,4): lane ends with tile (2*b4+b3), row lane&7
-            uint32_t k0 = b4 ? acc[2] : acc[0], k1 = b4 ? acc[3] : acc[1];
-            uint32_t g0 = b4 ? acc[0] : acc[2], g1 = b4 ? acc[1] : acc[3];
-            k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
-            k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
-            uint32_t keep = b3 ? k1 : k0, give = b3 ? k0 : k1;
-            keep += __shfl_xor_sync(0xffffffffu, give, 8);            // row (set row0 + lane): sum of its 128 entries, < 2^23
-            const uint32_t nb = __shfl_xor_sync(0xffffffffu, keep, 1);
-            const int row = set_of(li) * kSetRows + lane;
-            // finish the atomic issued one set ago (its L2 round trip has long completed), then issue this set's
-            if (pend_valid) finish_pair(pend_old, pend_add, pend_row);
-            pend_valid = false;
-            if (!(lane & 1)) {
-                const unsigned long long add = (unsigned long long)keep + ((unsigned long long)nb << 29) + (1ull << 58);
-                pend_add = add; pend_row = row; pend_valid = true;
-                if (p.n_k == 1) pend_old = 0;
-#if LUTVQ_DBG
-                else if (p.flags & 0x400u) pend_old = 0;              // DEBUG: no atomics
-#endif
-                else pend_old = atom_add_u64(PB.acc + (row >> 1), add);
             }
         }
-        pos += n_seg;
+        pos += hi - lo;
         if (pos < end) {                                           // next segment (linear plan only)
             ks = pos / PB.n_sets;
             lo = pos - ks * PB.n_sets;
             hi = min(PB.n_sets, lo + (end - pos));
             seg_rot = rot_of(ks, hi - lo);
+            #pragma unroll
+            for (int i = 0; i < PF; ++i)
+                if (lo + warp + i * NW < hi) load_set(buf[i], ks, lo + wrap(warp + i * NW + seg_rot, hi - lo));
+            load_x_slice(ks);                                      // the old slice's xs was last read before the post-build barrier
+            __syncthreads();                                       // everyone is done reading this slice's LUT; xs is complete
         }
     }
     TL_STAMP(4);
-    if (pend_valid) finish_pair(pend_old, pend_add, pend_row);
+
+    #pragma unroll
+    for (int i = 0; i < PA; ++i)
+        if (pend_valid[i]) finish_row(pend_old[i], pend_keep[i], pend_row[i]);
     TL_STAMP(5);
     if (!waited) pdl_wait();                                       // completion stays stream-ordered
     TL_STAMP(6);
@@ -693,7 +660,7 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
         }
         __syncthreads();
         if (last_flag) {
-            if (threadIdx.x == 0) *p.cta_arrivals = 0u;                               // self-cleaning, like the counters
+            if (threadIdx.x == 0) *p.cta_arrivals = 0u;                               // self-cleaning, like the accumulators
             __threadfence_system();
             const unsigned epoch = *p.push_sent + 1u;
             if ((int)threadIdx.x < p.n_push)
@@ -704,53 +671,46 @@ lut_gemv_2x8_kernel(const __grid_constant__ GemvParams p) {
     }
 }
 
-// packed image from reference-layout codes: [k-slice][set][tile][half][lane] x 16 B in lane-walk order (lut_layout.h)
+// [k-slice][set][tile][lane] x 16 B register images from reference-layout codes (see file header)
 __global__ void prepack_2x8_kernel(const uint8_t* __restrict__ codes, uint4* __restrict__ packed, int O, int G,
-                                   int n_k, int n_sets_total, uint4* __restrict__ zero, size_t zero16) {
-    // staging use (gemv_stage_codes): the split-k words in front of the staged image may hold a previous call's staged
-    // codes (another shape, same cached workspace): hand them over all-zero, as the GEMV kernel expects them
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < zero16; i += (size_t)gridDim.x * blockDim.x)
-        zero[i] = make_uint4(0u, 0u, 0u, 0u);
-    const size_t total = (size_t)n_k * n_sets_total * (kSetBytes / 16);
+                                   int n_k, int n_sets_total) {
+    const size_t total = (size_t)n_k * n_sets_total * 128;
     const size_t row_bytes = (size_t)G * 2;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int lane = (int)(i & 31), ph = (int)((i >> 5) & 1), t = (int)((i >> 6) & 3);
-        const size_t ss = i >> 8;
+        const int lane = (int)(i & 31), t = (int)((i >> 5) & 3);
+        const size_t ss = i >> 7;
         const int set = (int)(ss % n_sets_total), ks = (int)(ss / n_sets_total);
         const int row = set * kSetRows + t * kTileRows + stream_row_in_tile(lane);
-        const size_t off = (size_t)ks * kSliceTables + 16 * stream_chunk(lane, ph);
+        const size_t off = (size_t)ks * kSliceTables + 16 * stream_chunk(lane);
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (row < O && off < row_bytes) v = *reinterpret_cast<const uint4*>(codes + (size_t)row * row_bytes + off);
-        const uint32_t in[4] = {v.x, v.y, v.z, v.w};
-        uint32_t out[4];
-        pack_lane_image(in, lane, out);                            // image byte k = 2u + h holds chunk byte 2(u ^ r) + h
-        packed[i] = make_uint4(out[0], out[1], out[2], out[3]);
+        if (stream_first_half(lane)) v = make_uint4(v.z, v.w, v.x, v.y);
+        packed[i] = v;
     }
 }
 
 // ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
-struct GemvTuning { int nw = 0, nslot = 0; };   // 0 = choose per launch mode (launch_tuned)
+struct GemvTuning { int nw = 0, pf = 0, pa = 0; };   // 0 = choose per shape (launch_tuned)
 static GemvTuning g_tuning;
 static int g_dep_workers_per_sm = 2;   // workers (CTAs) per SM of a DEPENDENT launch, see gemv_2x8_launch_group
 void gemv_set_dependent_workers(int m) { g_dep_workers_per_sm = m < 1 ? 1 : (m > 2 ? 2 : m); }
-static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][16] stamps
+static unsigned long long* g_timeline = nullptr;   // debug: [64 launches][256 CTAs][8] stamps
 static unsigned g_timeline_seq = 0;
 void gemv_set_timeline(void* buf) { g_timeline = static_cast<unsigned long long*>(buf); g_timeline_seq = 0; }
 
 struct GemvPlan { int n_k, n_sets, W, aligned, q, r, max_range; };
 
-// One worker (CTA) per SM.  Cost model in units of one 32-row set of gather work (128 lookups per lane); a LUT build
-// (256 MMAs + 64 KiB of stores per CTA) costs about 6 of them.
+// One worker (CTA) per SM.  Cost model in units of one 32-row set of gather work; a LUT build costs about 10.
 static GemvPlan plan_gemv(int O, int G, int sm_count) {
     GemvPlan pl;
     pl.n_k = ceil_div(G * 2, kSliceTables);
     pl.n_sets = ceil_div(O, kSetRows);
     const long long T = (long long)pl.n_k * pl.n_sets;
     pl.W = (int)(T < sm_count ? T : sm_count);
-    if (pl.W > 1024) pl.W = 1024;
-    const int kBuildCost = 6;
+    if (pl.W > 1024) pl.W = 1024;                                  // worker_range's magic division is exact up to 1024
+    const int kBuildCost = 10;
     const long long per = (T + pl.W - 1) / pl.W;
     const long long lin_builds = 1 + (per + pl.n_sets - 1) / pl.n_sets;            // a range of `per` items touches at most this many slices
     const long long cost_linear = per + kBuildCost * (lin_builds > pl.n_k ? pl.n_k : lin_builds);
@@ -767,10 +727,7 @@ static GemvPlan plan_gemv(int O, int G, int sm_count) {
     return pl;
 }
 
-static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
-
-// header + one split-k word per PAIR of (padded) rows.  (Kept at 8 bytes per row: callers size rings from this.)
-size_t gemv_packed_workspace_bytes(int O, int G) {
+size_t gemv_workspace_bytes(int O, int G) {
     (void)G;
     const size_t O_pad = (size_t)ceil_div(O, kSetRows) * kSetRows;
     return kWsHeaderBytes + O_pad * sizeof(unsigned long long);
@@ -778,33 +735,29 @@ size_t gemv_packed_workspace_bytes(int O, int G) {
 
 size_t gemv_packed_bytes(int O, int G) {
     const int n_k = ceil_div(G * 2, kSliceTables);
-    return (size_t)n_k * ceil_div(O, kSetRows) * kSetBytes;
+    return (size_t)n_k * ceil_div(O, kSetRows) * 2048;
 }
 
-// the reference-layout entry points stage a packed image behind the split-k words
-size_t gemv_workspace_bytes(int O, int G) { return align256(gemv_packed_workspace_bytes(O, G)) + gemv_packed_bytes(O, G); }
-
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream, void* zero, size_t zero_bytes) {
+    (void)zero; (void)zero_bytes;
     const int G = I / 8;
     const int n_k = ceil_div(G * 2, kSliceTables), n_sets_total = ceil_div(O, kSetRows);
-    const size_t total = (size_t)n_k * n_sets_total * (kSetBytes / 16);
+    const size_t total = (size_t)n_k * n_sets_total * 128;
     int grid = (int)((total + 255) / 256);
     if (grid > 148 * 16) grid = 148 * 16;
-    prepack_2x8_kernel<<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(codes), static_cast<uint4*>(packed), O, G, n_k, n_sets_total,
-                                                 static_cast<uint4*>(zero), zero_bytes / 16);
+    prepack_2x8_kernel<<<grid, 256, 0, stream>>>(static_cast<const uint8_t*>(codes), static_cast<uint4*>(packed), O, G, n_k, n_sets_total);
     LUTVQ_CUDA_OK(cudaGetLastError());
     return LUTVQ_OK;
 }
 
-template <int DT, int NW, int MODE>
-static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
-    auto kern = lut_gemv_2x8_kernel<DT, NW, MODE>;
-    constexpr size_t smem = gemv_smem_bytes<NW, MODE>();
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB = 2>
+static int launch_variant(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
+    auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF, PA, MINB>;
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
     if (attr_device != dev) {
-        LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSliceBytes));
         attr_device = dev;
     }
     cudaLaunchConfig_t cfg{};
@@ -821,13 +774,33 @@ static int launch_variant(const GemvParams& p, int grid, cudaStream_t stream, bo
     return LUTVQ_OK;
 }
 
-template <int DT>
-static int launch_tuned(const GemvParams& p, int grid, cudaStream_t stream, bool pdl) {
+template <int DT, bool PACKED>
+static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
     GemvTuning t = g_tuning;
-    if (t.nw == 0) { t.nw = 8; t.nslot = kStreamRegs; }
-    if (t.nw == 8 && t.nslot == kStreamRegs) return launch_variant<DT, 8, kStreamRegs>(p, grid, stream, pdl);   // 3 CTAs / SM: 64 KiB LUT, register ring
-    if (t.nw == 8 && t.nslot == kStreamBulk) return launch_variant<DT, 8, kStreamBulk>(p, grid, stream, pdl);   // 2 CTAs / SM: + 32 KiB of landing slots
-    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d mode=%d", t.nw, t.nslot);
+    if (t.nw == 0) {
+        // Measured on B200 (X_READY ring, packed codes): 3 CTAs/SM with a 1-deep code ring wins while a row has few
+        // split-k arrivals (4096x11008: 3.75 vs 4.39 us; 4096x4096: 2.39 vs 2.51 us); with many k-slices the exposed
+        // atomic round trip of the shallow ring loses to 2 CTAs/SM with 2-deep rings (11008x4096: 6.08 vs 5.07 us).
+        // That is the INDEPENDENT (X_READY) ring.  A dependent chain (decode) runs one launch at a time: there the third
+        // resident CTA buys nothing, the deeper ring wins on every shape, and alternating between the two variants
+        // (different register / occupancy footprints) costs the PDL overlap: Llama-2-7B layer, 4 GEMV launches chained:
+        // 51.7 us mixed, 36.6 all 3-CTA, 31.0 all 2-CTA (tools/decode_parts.py).
+        t.nw = 8;
+        if (p.n_k <= 24 && (p.flags & LUTVQ_FLAG_X_READY)) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
+    }
+    if (t.nw == 8 && t.pf == 1 && t.pa == 1)  return launch_variant<DT, PACKED, 8, 1, 1, 3>(p, grid, smem, stream, pdl);   // 3 CTAs / SM
+    if (t.nw == 8 && t.pf == 2 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 2, 2, 2>(p, grid, smem, stream, pdl);   // 2 CTAs / SM, deeper ring
+#if LUTVQ_DBG
+    if (t.nw == 8 && t.pf == 2 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 2, 4>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 2 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 2, 6>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 1, 4>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 1, 6>(p, grid, smem, stream, pdl);
+    if (t.nw == 16 && t.pf == 1 && t.pa == 3) return launch_variant<DT, PACKED, 16, 1, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 4 && t.pf == 2 && t.pa == 8)  return launch_variant<DT, PACKED, 4, 2, 8, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 1 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 1, 2, 3>(p, grid, smem, stream, pdl);
+    if (t.nw == 8 && t.pf == 2 && t.pa == 8)  return launch_variant<DT, PACKED, 8, 2, 2, 3>(p, grid, smem, stream, pdl);   // "8,2,8" = (8,2,2) at 3 CTAs/SM
+#endif
+    return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d pa=%d", t.nw, t.pf, t.pa);
 }
 
 // worker w of a problem planned as `pl` -> its item range [begin, end) over (slice, set) pairs, slice-major.
@@ -858,16 +831,15 @@ size_t gemv_group_workspace_bytes(int n, const int* O) {
 
 // n linears that share x (and prob_k) in ONE launch: y_i = epilogue_i(W_i(codes_i) . x).  The workers (one CTA per SM)
 // are dealt to the problems in proportion to their rows; each problem is then planned exactly like a single GEMV on
-// its share of the SMs.  x_gate != null (fp16): the activations are silu(x_gate) * x, evaluated in the kernel's x loads.
-// Validation is done by the caller (api.cu / shard.cu).
-int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
+// its share of the SMs.  Validation is done by the caller (api.cu / shard.cu).
+// x_gate != null (fp16): the activations are silu(x_gate) * x, evaluated in the kernel's x loads.
+static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
+                            void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
     LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
-    LUTVQ_REQUIRE(aligned16(x) && (x_gate == nullptr || aligned16(x_gate)), "x must be 16-byte aligned (the reference reads it as int4 too, cuda_kernel.cu:147)");
     // An independent (X_READY) ring fills the SMs by overlapping consecutive launches, one worker per SM each.  A dependent
-    // launch runs alone: it may be planned over g_dep_workers_per_sm workers per SM.
+    // launch runs alone: it may be planned over g_dep_workers_per_sm workers per SM (2 fit with the 2-CTA variant).
     const int workers = di.sm_count * ((flags & LUTVQ_FLAG_X_READY) ? 1 : g_dep_workers_per_sm);
     LUTVQ_REQUIRE(n == 1 || workers <= kRangeTable, "grouped launches need the tabulated plan (<= %d workers)", kRangeTable);
     LUTVQ_REQUIRE(n == 1 || push == nullptr, "the fused push epilogue takes one linear per launch");
@@ -894,8 +866,7 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const voi
         if (share > left - (n - 1 - i)) share = left - (n - 1 - i);
         left -= share;
         GemvPlan pl = plan_gemv(items[i].O, G, share);
-        if (pl.n_k > kMaxSlices)
-            return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds %d (prob_k <= %d)", I, pl.n_k, kMaxSlices, kMaxSlices * kSliceGroups * 8);
+        if (pl.n_k > 255) return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds 255 (prob_k <= 65280)", I, pl.n_k);
         p.n_k = pl.n_k;
         GemvProblem& pb = p.prob[i];
         pb.codes = static_cast<const uint8_t*>(items[i].codes); pb.codebook = items[i].codebook; pb.y = items[i].y;
@@ -928,14 +899,16 @@ int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const voi
     }
     const bool pdl = !(flags & LUTVQ_FLAG_NO_PDL);
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
-    // A dependent launch sits behind griddepcontrol.wait while its predecessor runs: pushing its share HBM -> L2 meanwhile is
-    // free.  An independent (X_READY) launch streams at once, where the extra prefetch requests only cost bandwidth
-    // (tools/stream_probe: 5.9 vs 7.3 TB/s).
-    if (!(p.flags & LUTVQ_FLAG_X_READY)) p.flags |= kFlagL2Prefetch;
     p.tl = (g_timeline && W_total <= 256) ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
-    if (dtype == LUTVQ_F16)  return launch_tuned<LUTVQ_F16>(p, W_total, stream, pdl);
-    if (dtype == LUTVQ_BF16) return launch_tuned<LUTVQ_BF16>(p, W_total, stream, pdl);
+    const size_t smem = kSliceBytes;
+    if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, W_total, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, W_total, smem, stream, pdl);
+    if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, W_total, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, W_total, smem, stream, pdl);
     return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+}
+
+int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
+    return gemv_launch_impl(n, items, 1, x, x_gate, I, dtype, flags, ws, ws_bytes, stream, push);
 }
 
 // One GEMV on a packed code image: y = epilogue(W(codes) . x).
@@ -943,31 +916,24 @@ int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* code
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push) {
     const GemvItem it{packed, codebook, y, scales, bias, O};
-    return gemv_2x8_launch_group(1, &it, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, push);
+    return gemv_launch_impl(1, &it, 1, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, push);
 }
 
-// Reference-layout codes [O][G][2] -> a packed image in the staging area behind the split-k words of `ws` (one extra pass
-// over the codes; QuantizedLinear and every hot caller prepack once at load time instead).  The caller must launch the
-// first GEMV that reads the staged image WITHOUT programmatic overlap (LUTVQ_FLAG_NO_PDL), or it could read the staging
-// area before the prepack kernel has finished.
-int gemv_stage_codes(const void* codes, int O, int I, void* ws, size_t ws_bytes, cudaStream_t stream, const void** staged, size_t* small_bytes) {
-    DeviceInfo di;
-    if (int rc = get_device_info(&di)) return rc;                  // no device: fail loudly, there is no CPU fallback
-    const int G = I / 8;
-    const size_t small = align256(gemv_packed_workspace_bytes(O, G));
-    const size_t need = small + gemv_packed_bytes(O, G);
-    LUTVQ_REQUIRE(ws != nullptr && ws_bytes >= need, "workspace too small: the reference-layout entry points need %zu bytes (lutvq_workspace_bytes), got %zu", need, ws_bytes);
-    LUTVQ_REQUIRE(aligned16(ws), "workspace must be 16-byte aligned");
-    void* st = static_cast<uint8_t*>(ws) + small;
-    if (int rc = gemv_prepack_launch(codes, st, O, I, stream, ws, small)) return rc;     // small is a multiple of 256
-    *staged = st; *small_bytes = small;
-    return LUTVQ_OK;
+// One GEMV on reference-layout codes int8 [O][G][2] (the kernel's PACKED = false build: a warp's 128-bit load touches
+// 8 rows x 64 B; no re-layout pass, no staging area).
+int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
+                        const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
+                        cudaStream_t stream) {
+    const GemvItem it{codes, codebook, y, scales, bias, O};
+    return gemv_launch_impl(1, &it, 0, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr);
 }
 
-void gemv_set_tuning(int nw, int nslot, int unused) {
-    (void)unused;
-    g_tuning.nw = nw > 0 ? nw : 0;
-    g_tuning.nslot = nslot > 0 ? nslot : 0;
+size_t gemv_packed_workspace_bytes(int O, int G) { return gemv_workspace_bytes(O, G); }
+
+void gemv_set_tuning(int nw, int pf, int pa) {
+    if (nw > 0) g_tuning.nw = nw;
+    if (pf > 0) g_tuning.pf = pf;
+    if (pa > 0) g_tuning.pa = pa;
 }
 void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk) {
     DeviceInfo di;

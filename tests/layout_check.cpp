@@ -1,15 +1,13 @@
-// layout_check.cpp -- host-side proof of the shared-memory LUT layout used by gemv_lut.cu (round-2 layout: 128 u16 tables).
+// layout_check.cpp -- host-side proof of the shared-memory LUT layout used by gemv_lut.cu.
 // Built and run by tests/test_host_logic.py (g++, no GPU).  Exhaustively checks, with the SAME inline
 // functions the kernel uses (rvv-lut-vq_b200/csrc/lut_layout.h):
-//   1. the PRMT-composed LDS address of every (lane, half, image byte, idx) is the entry of the table that byte of the
-//      prepacked image belongs to (prepack permutation + kernel addressing agree), every lane visits each of its 32
-//      code bytes exactly once, and the 4 lanes of a row cover its 128 tables exactly once;
+//   1. the PRMT-composed LDS address of every (lane, step, idx) is the entry of the table the lane's code
+//      byte belongs to;
 //   2. the 32 lanes of every lookup step hit 32 distinct banks (conflict-free for any index pattern);
-//   3. the build side (mma.sync C fragments of both codebooks -> packed u16 pairs -> 128-bit stores) writes every
-//      (table, idx) entry exactly once, to the address the lookups read, and each quarter-warp phase of every store
-//      touches 8 distinct 16-byte columns;
-//   4. the transposed warp reduction leaves row `lane` of the 32-row set in lane `lane`;
-//   5. the split-k word: 63 slices of maximal partials fit the 29-bit fields, the arrival count survives.
+//   3. the build side (mma.sync C fragments -> 128-bit stores) writes every (table, idx) entry exactly once,
+//      to the address the lookups read, and each quarter-warp phase of every store touches 8 distinct
+//      16-byte columns;
+//   4. the transposed warp reduction leaves row `lane` of the 32-row set in lane `lane`.
 #include <cstdio>
 #include <cstdint>
 #include <cstdlib>
@@ -30,120 +28,96 @@ static uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {   // PTX prmt.b32 d
 #define CHECK(cond, ...) do { if (!(cond)) { printf("FAIL %s:%d: ", __FILE__, __LINE__); printf(__VA_ARGS__); printf("\n"); return 1; } } while (0)
 
 int main() {
-    // ---- 1 + 2: streaming side.  A tile row = 128 code bytes with distinct values so that idx identifies the table. ----
-    for (int p = 0; p < 2; ++p)
-        for (int k = 0; k < 16; ++k) {
+    // ---- 1 + 2: streaming side ----
+    for (int c = 0; c < 4; ++c)
+        for (int d = 0; d < 4; ++d) {
             std::set<int> banks;
             for (int lane = 0; lane < 32; ++lane) {
-                // the row's slice bytes in memory order: code(table) = (7 * table + 3 * row + 1) & 255
-                const int row = stream_row_in_tile(lane);
-                auto code_of = [&](int table) { return (7 * table + 3 * row + 1) & 255; };
-                const int chunk = stream_chunk(lane, p);
-                uint32_t in[4], img[4];
-                for (int w = 0; w < 4; ++w) {
-                    in[w] = 0;
-                    for (int b = 0; b < 4; ++b) in[w] |= (uint32_t)code_of(16 * chunk + 4 * w + b) << (8 * b);
+                const int e = stream_first_half(lane);
+                const int p = stream_pos(lane, c, d);
+                // the lane's 16 bytes: memory chunk stream_chunk(lane); registers w0,w1 = first loaded half (half e), w2,w3 = other half
+                uint8_t mem[16];
+                for (int i = 0; i < 16; ++i) mem[i] = (uint8_t)(17 * i + 3 * lane + 1);     // arbitrary distinct indices
+                uint32_t w[4];
+                for (int rw = 0; rw < 4; ++rw) {
+                    const int mw = rw ^ (2 * e);                                          // register word rw holds memory word rw^2e
+                    w[rw] = mem[4 * mw] | (mem[4 * mw + 1] << 8) | (mem[4 * mw + 2] << 16) | ((uint32_t)mem[4 * mw + 3] << 24);
                 }
-                pack_lane_image(in, lane, img);
-                const int j = k >> 2, b = k & 3, u = k >> 1, h = k & 1;
-                const uint32_t addr = prmt(img[j], stream_lm(lane, u), stream_sel(b)) + stream_imm(p, h);
-                const int table = stream_table(lane, p, k);
-                CHECK(table >= 16 * chunk && table < 16 * chunk + 16, "table out of chunk lane %d", lane);
-                const int idx = code_of(table);
-                CHECK(addr == lut_entry_offset(table, idx), "addr mismatch lane %d p %d k %d: %u vs %u", lane, p, k, addr, lut_entry_offset(table, idx));
-                CHECK(addr < (uint32_t)kSliceBytes, "addr out of the slice");
+                const uint32_t addr = prmt(w[c], stream_lm(lane, c >> 1, d), stream_sel(lane, d)) + stream_imm(c);
+                const int byte_in_chunk = p - 16 * stream_chunk(lane);
+                CHECK(byte_in_chunk >= 0 && byte_in_chunk < 16, "pos out of chunk lane %d", lane);
+                const int idx = mem[byte_in_chunk];
+                CHECK(addr == lut_entry_offset(p, idx), "addr mismatch lane %d c %d d %d: %u vs %u", lane, c, d, addr, lut_entry_offset(p, idx));
                 banks.insert((addr >> 2) & 31);
-                CHECK(((addr >> 2) & 31) == (uint32_t)lut_bank(table), "bank function");
             }
-            CHECK(banks.size() == 32, "bank conflict at step p=%d k=%d: %zu banks", p, k, banks.size());
+            CHECK(banks.size() == 32, "bank conflict at step c=%d d=%d: %zu banks", c, d, banks.size());
         }
-    for (int row = 0; row < 8; ++row) {
+    // every lane visits each of its 16 bytes exactly once
+    for (int lane = 0; lane < 32; ++lane) {
         std::set<int> seen;
-        for (int a = 0; a < 4; ++a) {
-            const int lane = 8 * a + row;
-            std::set<int> mine;
-            for (int p = 0; p < 2; ++p) for (int k = 0; k < 16; ++k) mine.insert(stream_table(lane, p, k));
-            CHECK(mine.size() == 32, "lane %d covers %zu tables", lane, mine.size());
-            seen.insert(mine.begin(), mine.end());
-        }
-        CHECK(seen.size() == 128 && *seen.begin() == 0 && *seen.rbegin() == 127, "row %d: %zu tables", row, seen.size());
-    }
-    // packed offsets of one item are a bijection onto [0, 4096)
-    {
-        std::set<uint32_t> offs;
-        for (int t = 0; t < 4; ++t) for (int p = 0; p < 2; ++p) for (int lane = 0; lane < 32; ++lane) for (int k = 0; k < 16; ++k) offs.insert(packed_offset(t, p, lane, k));
-        CHECK(offs.size() == (size_t)kSetBytes && *offs.rbegin() == (uint32_t)kSetBytes - 1, "packed offsets");
+        for (int c = 0; c < 4; ++c) for (int d = 0; d < 4; ++d) seen.insert(stream_pos(lane, c, d));
+        CHECK(seen.size() == 16, "lane %d covers %zu bytes", lane, seen.size());
+        CHECK(*seen.begin() == 16 * stream_chunk(lane) && *seen.rbegin() == 16 * stream_chunk(lane) + 15, "lane %d range", lane);
     }
 
-    // ---- 3: build side ----
-    std::vector<int> written(kSliceBytes / 2, 0);                  // per u16 entry
-    for (int m = 0; m < 16; ++m)                                   // idx block
-        for (int hb = 0; hb < 2; ++hb)
-            for (int hh = 0; hh < 2; ++hh)
-                for (int which = 0; which < 2; ++which) {          // first / second store instruction
-                    for (int phase = 0; phase < 4; ++phase) {      // quarter-warp phases of a 128-bit store
+    // ---- 3: build side.  written[offset/4] = (p, idx) tag ----
+    std::vector<int> written(kSliceBytes / 4, -1);
+    for (int m = 0; m < 16; ++m)                 // idx blocks of 16
+        for (int h = 0; h < 2; ++h)
+            for (int jp = 0; jp < 2; ++jp)
+                for (int which = 0; which < 2; ++which) {            // first / second store of the pair
+                    for (int phase = 0; phase < 4; ++phase) {
                         std::set<uint32_t> cols;
-                        for (int l8 = 0; l8 < 8; ++l8) {
-                            const int lane = 8 * phase + l8, r = lane >> 2, q = lane & 3;
-                            const bool odd = r & 1;
-                            const int pair_local = which == 0 ? (odd ? 1 : 0) : (odd ? 0 : 1);
-                            const int idx = 16 * m + r + 8 * hh;
-                            const uint32_t off = build_store_offset(idx, 2 * hb + pair_local, q);
-                            CHECK(off % 16 == 0 && off + 16 <= (uint32_t)kSliceBytes, "store offset");
-                            cols.insert((off % 128) / 16);
-                            for (int e = 0; e < 2; ++e)
-                                for (int f = 0; f < 2; ++f) {
-                                    // word 2e+f of the store = C fragment element (row r + 8hh, column 2q+f) of N-tile 4hb + 2*pair_local + e
-                                    const int group = build_group_of_col(4 * hb + 2 * pair_local + e, 2 * q + f);
-                                    CHECK(group >= 0 && group < kSliceGroups, "group range");
-                                    const uint32_t word_off = off + 4 * (2 * e + f);
-                                    for (int n = 0; n < 2; ++n) {                      // codebook n -> half n of the word
-                                        CHECK(word_off + 2 * n == lut_entry_offset(2 * group + n, idx), "build/lookup disagree idx %d group %d n %d", idx, group, n);
-                                        written[(word_off + 2 * n) / 2] += 1;
-                                    }
-                                }
+                        for (int lane = 8 * phase; lane < 8 * phase + 8; ++lane) {
+                            const int r = lane >> 2, q = lane & 3, odd = r & 1;
+                            const int j0 = 2 * jp, j1 = 2 * jp + 1;
+                            const int j = (which == 0) ? (odd ? j1 : j0) : (odd ? j0 : j1);
+                            const int idx = 16 * m + r + 8 * h;
+                            const uint32_t off = build_store_offset(idx, j, q);
+                            cols.insert((off >> 4) & 7);
+                            for (int beta = 0; beta < 4; ++beta) {
+                                const int u = beta >> 1, n = beta & 1;
+                                // C fragment: thread (r,q) holds columns 2q+u of N-tile j  -> local group
+                                const int group = build_group_of_col(j, 2 * q + u);
+                                const int p = 2 * group + n;                 // byte position of table (group, codebook n)
+                                CHECK(off + 4 * beta == lut_entry_offset(p, idx), "build offset mismatch");
+                                CHECK(written[(off >> 2) + beta] == -1, "entry written twice");
+                                written[(off >> 2) + beta] = p * 256 + idx;
+                            }
                         }
-                        CHECK(cols.size() == 8, "store phase conflict m=%d hb=%d hh=%d which=%d phase=%d: %zu columns", m, hb, hh, which, phase, cols.size());
+                        CHECK(cols.size() == 8, "store phase conflict: %zu columns", cols.size());
                     }
                 }
-    for (size_t i = 0; i < written.size(); ++i) CHECK(written[i] == 1, "entry %zu written %d times", i, written[i]);
-    {   // the B fragment columns cover the slice's 64 groups exactly once
+    for (int p = 0; p < 64; ++p)
+        for (int idx = 0; idx < 256; ++idx)
+            CHECK(written[lut_entry_offset(p, idx) >> 2] == p * 256 + idx, "entry (p=%d, idx=%d) not built", p, idx);
+    // B-fragment columns of the 4 N-tiles cover the 32 local groups exactly once
+    {
         std::set<int> groups;
-        for (int j = 0; j < 8; ++j) for (int col = 0; col < 8; ++col) groups.insert(build_group_of_col(j, col));
-        CHECK(groups.size() == 64 && *groups.begin() == 0 && *groups.rbegin() == 63, "B fragment columns");
+        for (int j = 0; j < 4; ++j) for (int col = 0; col < 8; ++col) groups.insert(build_group_of_col(j, col));
+        CHECK(groups.size() == 32 && *groups.rbegin() == 31, "N-tiles do not cover the slice groups");
     }
 
-    // ---- 4: transposed reduction.  acc[t] of lane (a, r) = partial of tile t, row r over chunks a, a+4 ----
+    // ---- 4: transposed reduction ----
     {
-        uint32_t acc[32][4], k0[32], k1[32], g0[32], g1[32], keep[32], give[32];
-        for (int lane = 0; lane < 32; ++lane)
-            for (int t = 0; t < 4; ++t) acc[lane][t] = 1000u * t + 10u * (lane & 7) + (1u << (16 + (lane >> 3)));   // distinct per (t, r), a marks the bit
-        for (int lane = 0; lane < 32; ++lane) {
-            const bool b4 = (lane >> 4) & 1;
-            k0[lane] = b4 ? acc[lane][2] : acc[lane][0]; k1[lane] = b4 ? acc[lane][3] : acc[lane][1];
-            g0[lane] = b4 ? acc[lane][0] : acc[lane][2]; g1[lane] = b4 ? acc[lane][1] : acc[lane][3];
+        // value held by lane L for tile t before the reduction: partial sum of row 8t + (L&7) over chunk L>>3
+        // encode as: contribution id = (row, chunk); result must be the set of 4 chunks of row == lane
+        std::vector<std::vector<std::set<int>>> acc(32, std::vector<std::set<int>>(4));
+        for (int L = 0; L < 32; ++L) for (int t = 0; t < 4; ++t) acc[L][t].insert((8 * t + (L & 7)) * 4 + (L >> 3));
+        std::vector<std::set<int>> k0(32), k1(32), g0(32), g1(32), keep(32), give(32);
+        for (int L = 0; L < 32; ++L) {
+            const bool b4 = (L >> 4) & 1;
+            k0[L] = b4 ? acc[L][2] : acc[L][0]; k1[L] = b4 ? acc[L][3] : acc[L][1];
+            g0[L] = b4 ? acc[L][0] : acc[L][2]; g1[L] = b4 ? acc[L][1] : acc[L][3];
         }
-        uint32_t k0b[32], k1b[32];
-        for (int lane = 0; lane < 32; ++lane) { k0b[lane] = k0[lane] + g0[lane ^ 16]; k1b[lane] = k1[lane] + g1[lane ^ 16]; }
-        for (int lane = 0; lane < 32; ++lane) {
-            const bool b3 = (lane >> 3) & 1;
-            keep[lane] = b3 ? k1b[lane] : k0b[lane]; give[lane] = b3 ? k0b[lane] : k1b[lane];
+        for (int L = 0; L < 32; ++L) { auto a = g0[L ^ 16], b = g1[L ^ 16]; k0[L].insert(a.begin(), a.end()); k1[L].insert(b.begin(), b.end()); }
+        for (int L = 0; L < 32; ++L) { const bool b3 = (L >> 3) & 1; keep[L] = b3 ? k1[L] : k0[L]; give[L] = b3 ? k0[L] : k1[L]; }
+        std::vector<std::set<int>> fin(32);
+        for (int L = 0; L < 32; ++L) { fin[L] = keep[L]; auto a = give[L ^ 8]; fin[L].insert(a.begin(), a.end()); }
+        for (int L = 0; L < 32; ++L) {
+            CHECK(fin[L].size() == 4, "lane %d reduced %zu terms", L, fin[L].size());
+            for (int v : fin[L]) CHECK(v / 4 == L, "lane %d holds a term of row %d", L, v / 4);
         }
-        for (int lane = 0; lane < 32; ++lane) {
-            const uint32_t total = keep[lane] + give[lane ^ 8];
-            const int t = lane >> 3, r = lane & 7;                  // row `lane` of the set = tile t, row r
-            const uint32_t want = 4u * (1000u * t + 10u * r) + (1u << 16) + (1u << 17) + (1u << 18) + (1u << 19);
-            CHECK(total == want, "reduction lane %d: %u vs %u", lane, total, want);
-        }
-    }
-
-    // ---- 5: split-k word ----
-    {
-        const unsigned long long maxpart = 128ull * 65535ull;       // a row's partial over one slice
-        unsigned long long word = 0;
-        for (int s = 0; s < 63; ++s) word += maxpart + (maxpart << 29) + (1ull << 58);
-        CHECK((word >> 58) == 63, "arrival count");
-        CHECK((word & ((1ull << 29) - 1)) == 63 * maxpart && ((word >> 29) & ((1ull << 29) - 1)) == 63 * maxpart, "fields overflow");
     }
     printf("layout OK\n");
     return 0;
