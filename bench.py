@@ -185,7 +185,7 @@ def graph_time_us(torch, stream, body, reps, inner=1):
     return a.elapsed_time(b) * 1e3 / (reps * inner)
 
 
-def measure_decode(torch, dist, model: str, world: int, rank: int, dev, tokens: int = DECODE_TOKENS, exchange: str = "push"):
+def measure_decode(torch, dist, model: str, world: int, rank: int, dev, tokens: int = DECODE_TOKENS, exchange: str = "ll"):
     """decode tok/s of the Llama-shaped AQLM 2x8 decoder (decode.py): one CUDA graph per token, CUDA events, max over ranks"""
     from rvv_lut_vq_b200.decode import LLAMA2_7B, LLAMA2_70B, Decoder
     from rvv_lut_vq_b200.sharded import ShardGroup
@@ -222,7 +222,11 @@ def measure_decode(torch, dist, model: str, world: int, rank: int, dev, tokens: 
            "launches_per_token": dec.launches_per_token, "graph": dec.graph is not None,
            "gemv_code_stream_bytes_per_token": gemv_bytes,
            "frac_of_hbm_peak": gemv_bytes / world / (us_tok * 1e-6) / 1e9 / peak,
-           "exchange": None if world == 1 else f"{exchange}: output-channel shards all-gathered over NVLink peer memory, 4 exchanges per layer",
+           "exchange": None if world == 1 else
+                       {"ll": "LL words: every finished row is stored as {value | epoch} into all ranks' gather slots over NVLink by the GEMV itself; "
+                              "the consuming kernels poll the words they read (no exchange launches, no flags, no fences); 4 exchanges per layer",
+                        "push": "push: one exchange launch per GEMV group forwards the slices over NVLink and waits on epoch flags; 4 per layer",
+                        "nccl": "nccl: all_gather_into_tensor per linear (eager)"}[exchange],
            "wait_errors": err, "last_token": last_token}
     del dec, group
     torch.cuda.empty_cache()
@@ -523,7 +527,7 @@ def main():
             prefill, dequant = measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak)
             ktb = kernel_to_beat()
         else:
-            decode70 = measure_decode(torch, dist, "70b", world, rank, dev)
+            decode70 = measure_decode(torch, dist, "70b", world, rank, dev, exchange=os.environ.get("LUTVQ_BENCH_EXCHANGE", "ll"))
 
     if rank != 0:
         if world > 1:

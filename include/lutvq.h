@@ -222,6 +222,32 @@ int    lutvq_shard_wait_mask(lutvq_shard_t* s, unsigned long long slot_mask, voi
 /* software pipelining: forward + publish the slots now (non-blocking), lutvq_shard_wait[_mask] on them later only waits */
 int    lutvq_shard_push_mask(lutvq_shard_t* s, unsigned long long slot_mask, void* stream);
 int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a wait timed out (epoch in *out); syncs the device */
+/* ---- "LL" exchange: the all-gather of a sharded decode without exchange launches, flags or fences ----
+ * Every finished output row of a sharded GEMV is written as ONE 32-bit word {value | epoch16 << 16} into the gather slot of
+ * EVERY rank (own rank included; peer memory over NVLink).  A word is valid once its upper half carries the expected epoch
+ * = f(step counter, sequence number of the exchange inside the step), so the consumer -- the next GEMV's activation load, the
+ * residual-add + RMSNorm, the attention kernel -- polls exactly the words it is about to use, in its own prologue.  Slot
+ * reuse needs no acknowledgement in a decode chain (a rank can only be one exchange ahead of the slowest peer; rotate through
+ * >= 2 slots).  Everything is device-side state: replays inside CUDA graphs.
+ *   lutvq_shard_ll_tick            ++step counter; call once per step (token) on every rank, before the step's first exchange
+ *   lutvq_sharded_matmat_group_ll  n <= 3 linears sharing an input, outputs as LL words into out_slots[i] at row_offsets[i]
+ *                                  with sequence numbers out_seq[i] (< 1024, unique within a step); input: plain x (x_slot < 0)
+ *                                  or the LL words of the local slot x_slot / x_seq; gate_slot >= 0: silu(gate) * x, both LL (fp16)
+ *   lutvq_decode_add_rmsnorm_ll / lutvq_decode_attention_ll   the glue kernels with their sharded operands taken from LL slots
+ *   lutvq_shard_ll_unpack          LL slot -> plain vector (for consumers that are not ours, and for tests)
+ * Polls are bounded (seconds): on a timeout the shard's error word (lutvq_shard_error) is set and the kernel returns. */
+int    lutvq_shard_ll_tick(lutvq_shard_t* s, void* stream);
+int    lutvq_sharded_matmat_group_ll(lutvq_shard_t* s, int n, const int* out_slots, const size_t* row_offsets, const unsigned* out_seq,
+                                     const void* x, int x_slot, unsigned x_seq, int gate_slot, unsigned gate_seq,
+                                     const void* const* packed, const void* const* codebooks, const void* const* scales,
+                                     const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                                     void* ws, size_t ws_bytes, void* stream);
+int    lutvq_shard_ll_unpack(lutvq_shard_t* s, int slot, unsigned seq, void* y, int n, void* stream);
+int    lutvq_decode_add_rmsnorm_ll(lutvq_shard_t* s, void* resid, int delta_slot, unsigned delta_seq, const void* w, void* y, int n,
+                                   float eps, void* stream);
+int    lutvq_decode_attention_ll(lutvq_shard_t* s, int q_slot, int k_slot, int v_slot, unsigned q_seq, unsigned k_seq, unsigned v_seq,
+                                 void* kcache, void* vcache, const int* pos, void* out, int n_heads, int n_kv_heads, int head_dim,
+                                 int max_seq, float rope_theta, void* stream);
 int    lutvq_shard_destroy(lutvq_shard_t* s);
 
 /* ---- integer LUT: lookup-and-add ----

@@ -75,6 +75,11 @@ SIGNATURES = {
     "lutvq_shard_push_mask": (I, [P, U64, P]),
     "lutvq_shard_error": (I, [P, P]),
     "lutvq_shard_destroy": (I, [P]),
+    "lutvq_shard_ll_tick": (I, [P, P]),
+    "lutvq_sharded_matmat_group_ll": (I, [P, I, P, P, P, P, I, U, I, U, P, P, P, P, P, I, I, U, P, SZ, P]),
+    "lutvq_shard_ll_unpack": (I, [P, I, U, P, I, P]),
+    "lutvq_decode_add_rmsnorm_ll": (I, [P, P, I, U, P, P, I, ctypes.c_float, P]),
+    "lutvq_decode_attention_ll": (I, [P, I, I, I, U, U, U, P, P, P, P, I, I, I, I, ctypes.c_float, P]),
     "lutvq_decode_add_rmsnorm": (I, [P, P, P, P, I, ctypes.c_float, P]),
     "lutvq_decode_silu_mul": (I, [P, P, P, I, P]),
     "lutvq_decode_attention": (I, [P, P, P, P, P, P, P, I, I, I, I, ctypes.c_float, P]),

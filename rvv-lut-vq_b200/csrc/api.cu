@@ -18,7 +18,7 @@ size_t gemv_packed_workspace_bytes(int O, int G);
 size_t gemv_group_workspace_bytes(int n, const int* O);
 void gemv_set_dependent_workers(int m);
 int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll = nullptr);
 size_t gemv_packed_bytes(int O, int G);
 int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStream_t stream, void* zero, size_t zero_bytes);
 void gemv_set_tuning(int nw, int pf, int pa);

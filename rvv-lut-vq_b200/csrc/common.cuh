@@ -45,6 +45,62 @@ struct GemvPush {
     unsigned* sent = nullptr;    // local pushes-completed counter of the slot
 };
 
+// ---- "LL" gather words of the sharded decode (shard.cu) ----
+// One 32-bit word per output row: {value: fp16/bf16 bits | epoch16 << 16}, written with ONE store into every rank's gather
+// slot (the own rank's too).  A word is valid once its upper half equals the expected epoch, so a consumer needs neither a
+// flag nor a fence nor a separate exchange launch: it polls the very words it is about to use (local memory, written remotely
+// over NVLink) and a 32-bit store is atomic.  epoch16 = (tick * 1024 + seq) mod 65535 + 1 is never 0 (= "never written").
+struct GemvLL {
+    int nranks = 0;                      // 0: no LL output
+    uint8_t* peer_base[8] = {};          // rank r's LL area as mapped here (peer_base[rank] = the local one)
+    size_t out_off[3] = {};              // per linear of a group: byte offset of (slot, this rank's first row) inside the LL area
+    unsigned out_seq[3] = {};            // per linear: sequence number of this exchange inside the step
+    const unsigned* tick = nullptr;      // device counter of steps (lutvq_shard_ll_tick), read after the dependency wait
+    const uint32_t* x_ll = nullptr;      // input activations as LL words of an earlier exchange (local slot), or null: plain x
+    unsigned x_seq = 0;
+    const uint32_t* gate_ll = nullptr;   // SwiGLU gate as LL words, or null
+    unsigned gate_seq = 0;
+    unsigned* error = nullptr;           // local error word: set when a bounded poll gives up
+};
+__device__ __forceinline__ unsigned ll_epoch16(unsigned tick, unsigned seq) { return (tick * 1024u + seq) % 65535u + 1u; }
+__device__ __forceinline__ uint4 ll_ld_v4(const uint32_t* p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ll_st(uint8_t* base, size_t off, uint32_t word) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(base + off), "r"(word) : "memory");
+}
+// 8 consecutive LL words (one group of 8 activations) -> the 8 values packed as 16 bytes; polls until all 8 carry `ep`.
+// Bounded: ~2^21 polls (seconds), then the error word is set and whatever is there is returned instead of hanging the GPU.
+__device__ __forceinline__ uint4 ll_load8(const uint32_t* w, unsigned ep, unsigned* error) {
+    uint4 a, b;
+    for (unsigned spin = 0;; ++spin) {
+        a = ll_ld_v4(w);
+        b = ll_ld_v4(w + 4);
+        const unsigned bad = ((a.x >> 16) ^ ep) | ((a.y >> 16) ^ ep) | ((a.z >> 16) ^ ep) | ((a.w >> 16) ^ ep) |
+                             ((b.x >> 16) ^ ep) | ((b.y >> 16) ^ ep) | ((b.z >> 16) ^ ep) | ((b.w >> 16) ^ ep);
+        if (bad == 0u) break;
+        if (spin > (1u << 21)) { if (error) *error = 0xFFFFFFFDu; break; }
+        if (spin > 64u) __nanosleep(100);
+    }
+    uint4 v;
+    v.x = (a.x & 0xFFFFu) | (a.y << 16); v.y = (a.z & 0xFFFFu) | (a.w << 16);
+    v.z = (b.x & 0xFFFFu) | (b.y << 16); v.w = (b.z & 0xFFFFu) | (b.w << 16);
+    return v;
+}
+// one LL word -> its 16 value bits
+__device__ __forceinline__ unsigned short ll_load1(const uint32_t* w, unsigned ep, unsigned* error) {
+    uint32_t v;
+    for (unsigned spin = 0;; ++spin) {
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(w) : "memory");
+        if ((v >> 16) == ep) break;
+        if (spin > (1u << 21)) { if (error) *error = 0xFFFFFFFDu; break; }
+        if (spin > 64u) __nanosleep(100);
+    }
+    return (unsigned short)(v & 0xFFFFu);
+}
+
 // one linear of a grouped GEMV launch (gemv_lut.cu gemv_2x8_launch_group)
 struct GemvItem { const void* codes; const void* codebook; void* y; const void* scales; const void* bias; int O; };
 

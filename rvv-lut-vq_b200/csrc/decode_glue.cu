@@ -7,6 +7,19 @@
 
 namespace lutvq {
 
+// Optional LL inputs (common.cuh "LL gather words"): operand k of a glue kernel comes from the local gather slot w[k] of an earlier
+// sharded GEMV (exchange sequence number seq[k]) instead of a plain buffer; the kernel polls exactly the words it consumes.
+struct LLIn {
+    const uint32_t* w[3] = {nullptr, nullptr, nullptr};
+    unsigned seq[3] = {0, 0, 0};
+    const unsigned* tick = nullptr;
+    unsigned* error = nullptr;
+};
+__device__ __forceinline__ __half ll_half(const LLIn& ll, int k, unsigned tick, int i) {
+    const unsigned short b = ll_load1(ll.w[k] + i, ll_epoch16(tick, ll.seq[k]), ll.error);
+    return *reinterpret_cast<const __half*>(&b);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -19,16 +32,18 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 // resid (+= delta, if given);  y = resid * rsqrt(mean(resid^2) + eps) * w.   One CTA, n <= 1024 * 16.
-__global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps) {
+__global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps, LLIn ll) {
     pdl_launch_dependents();
     pdl_wait();
+    const bool has_delta = delta != nullptr || ll.w[0] != nullptr;
+    const unsigned tick = ll.w[0] ? *ll.tick : 0u;
     __shared__ float red[32];
     float v[16];
     float ss = 0.f;
     int cnt = 0;
     for (int i = threadIdx.x; i < n; i += 1024, ++cnt) {
         float a = __half2float(resid[i]);
-        if (delta) { a = __half2float(__float2half_rn(a + __half2float(delta[i]))); resid[i] = __float2half_rn(a); }
+        if (has_delta) { a = __half2float(__float2half_rn(a + __half2float(ll.w[0] ? ll_half(ll, 0, tick, i) : delta[i]))); resid[i] = __float2half_rn(a); }
         v[cnt] = a;
         ss += a * a;
     }
@@ -46,7 +61,7 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const 
 // The same for n % 8 == 0, n <= 8192 (every Llama hidden size): one 16-byte load per operand and thread, all of them
 // in flight at once (the norm weights before griddepcontrol.wait: no kernel of the chain writes them), values kept
 // in registers -- the generic kernel above pays three dependent L2 round trips and a local-memory array.
-__global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps) {
+__global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, const __half* delta, const __half* w, __half* y, int n, float eps, LLIn ll) {
     pdl_launch_dependents();
     __shared__ float red[32];
     const int i0 = threadIdx.x * 8;
@@ -54,9 +69,11 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, c
     uint4 wv = make_uint4(0u, 0u, 0u, 0u), rv = wv, dv = wv;
     if (act) wv = __ldg(reinterpret_cast<const uint4*>(w + i0));
     pdl_wait();
+    const bool has_delta = delta != nullptr || ll.w[0] != nullptr;
     if (act) {
         rv = __ldcg(reinterpret_cast<const uint4*>(resid + i0));
-        if (delta) dv = __ldcg(reinterpret_cast<const uint4*>(delta + i0));
+        if (ll.w[0]) dv = ll_load8(ll.w[0] + i0, ll_epoch16(*ll.tick, ll.seq[0]), ll.error);
+        else if (delta) dv = __ldcg(reinterpret_cast<const uint4*>(delta + i0));
     }
     const __half* rh = reinterpret_cast<const __half*>(&rv);
     const __half* dh = reinterpret_cast<const __half*>(&dv);
@@ -65,10 +82,10 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, c
     #pragma unroll
     for (int j = 0; j < 8; ++j) {
         a[j] = __half2float(rh[j]);
-        if (delta) a[j] = __half2float(__float2half_rn(a[j] + __half2float(dh[j])));
+        if (has_delta) a[j] = __half2float(__float2half_rn(a[j] + __half2float(dh[j])));
         ss += a[j] * a[j];
     }
-    if (act && delta) {
+    if (act && has_delta) {
         uint4 o;
         __half* oh = reinterpret_cast<__half*>(&o);
         #pragma unroll
@@ -110,7 +127,7 @@ constexpr int kHeadDim = 128;
 constexpr int kAttnWarps = 8;
 __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __half* q, const __half* k_new, const __half* v_new,
                                                                      __half* kcache, __half* vcache, const int* pos_ptr, __half* out,
-                                                                     int n_heads, int n_kv, int max_seq, float theta) {
+                                                                     int n_heads, int n_kv, int max_seq, float theta, LLIn ll) {
     pdl_launch_dependents();
     extern __shared__ float sc[];                 // [max_seq] scores, then [kAttnWarps][kHeadDim] partial outputs
     float* part = sc + max_seq;
@@ -137,11 +154,14 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __ha
         const float freq = __powf(theta, -2.f * (float)i / (float)kHeadDim);
         float sn, cs;
         __sincosf((float)pos * freq, &sn, &cs);
-        const float a = __half2float(q[h * kHeadDim + d]), b = __half2float(q[h * kHeadDim + (d < half_d ? d + half_d : d - half_d)]);
+        const int dr = d < half_d ? d + half_d : d - half_d;          // rotate_half partner
+        const unsigned tick = ll.w[0] ? *ll.tick : 0u;
+        auto ld = [&](int k, const __half* plain, int i) { return ll.w[k] ? ll_half(ll, k, tick, i) : plain[i]; };
+        const float a = __half2float(ld(0, q, h * kHeadDim + d)), b = __half2float(ld(0, q, h * kHeadDim + dr));
         qs[d] = (d < half_d) ? a * cs - b * sn : a * cs + b * sn;
-        const float c = __half2float(k_new[kvh * kHeadDim + d]), e = __half2float(k_new[kvh * kHeadDim + (d < half_d ? d + half_d : d - half_d)]);
+        const float c = __half2float(ld(1, k_new, kvh * kHeadDim + d)), e = __half2float(ld(1, k_new, kvh * kHeadDim + dr));
         const __half kh = __float2half_rn((d < half_d) ? c * cs - e * sn : c * cs + e * sn);
-        const __half vh = v_new[kvh * kHeadDim + d];
+        const __half vh = ld(2, v_new, kvh * kHeadDim + d);
         ks[d] = __half2float(kh);                 // the current position comes from shared memory (rounded like the cache copy)
         vs[d] = __half2float(vh);
         if (h % (n_heads / n_kv) == 0) {
@@ -242,20 +262,37 @@ static int launch_pdl(void (*kern)(Args...), dim3 grid, dim3 block, size_t smem,
     return LUTVQ_OK;
 }
 
+// shard.cu: the local LL slot of a shard handle as a glue-kernel input
+int shard_ll_input(lutvq_shard_t* h, int slot, const uint32_t** words, const unsigned** tick, unsigned** error, size_t* capacity_rows);
+
 }  // namespace lutvq
 
 using namespace lutvq;
 
 extern "C" {
 
-int lutvq_decode_add_rmsnorm(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream) {
+static int add_rmsnorm_impl(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream, const LLIn& ll) {
     LUTVQ_REQUIRE(resid && w && y && n > 0 && n <= 16384, "bad arguments (n=%d, n <= 16384)", n);
     const bool vec8 = n % 8 == 0 && n <= 8192 && aligned16(resid) && aligned16(w) && aligned16(y) && (!delta || aligned16(delta));
     if (vec8)
         return launch_pdl(add_rmsnorm_vec8_kernel, dim3(1), dim3((n / 8 + 31) / 32 * 32), 0, static_cast<cudaStream_t>(stream), static_cast<__half*>(resid),
-                          static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps);
+                          static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps, ll);
     return launch_pdl(add_rmsnorm_kernel, dim3(1), dim3(1024), 0, static_cast<cudaStream_t>(stream), static_cast<__half*>(resid),
-                      static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps);
+                      static_cast<const __half*>(delta), static_cast<const __half*>(w), static_cast<__half*>(y), n, eps, ll);
+}
+
+int lutvq_decode_add_rmsnorm(void* resid, const void* delta, const void* w, void* y, int n, float eps, void* stream) {
+    return add_rmsnorm_impl(resid, delta, w, y, n, eps, stream, LLIn{});
+}
+
+int lutvq_decode_add_rmsnorm_ll(lutvq_shard_t* h, void* resid, int delta_slot, unsigned delta_seq, const void* w, void* y, int n, float eps,
+                                void* stream) {
+    LLIn ll;
+    size_t cap = 0;
+    if (int rc = shard_ll_input(h, delta_slot, &ll.w[0], &ll.tick, &ll.error, &cap)) return rc;
+    LUTVQ_REQUIRE((size_t)n <= cap, "n=%d exceeds the gather slot (%zu rows)", n, cap);
+    ll.seq[0] = delta_seq;
+    return add_rmsnorm_impl(resid, nullptr, w, y, n, eps, stream, ll);
 }
 
 int lutvq_decode_silu_mul(const void* gate, const void* up, void* y, int n, void* stream) {
@@ -264,15 +301,36 @@ int lutvq_decode_silu_mul(const void* gate, const void* up, void* y, int n, void
                       static_cast<const __half*>(gate), static_cast<const __half*>(up), static_cast<__half*>(y), n);
 }
 
-int lutvq_decode_attention(const void* q, const void* k_new, const void* v_new, void* kcache, void* vcache, const int* pos,
-                           void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream) {
-    LUTVQ_REQUIRE(q && k_new && v_new && kcache && vcache && pos && out, "null pointer");
+static int attention_impl(const void* q, const void* k_new, const void* v_new, void* kcache, void* vcache, const int* pos,
+                          void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream, const LLIn& ll) {
+    LUTVQ_REQUIRE(kcache && vcache && pos && out, "null pointer");
     LUTVQ_REQUIRE(head_dim == kHeadDim, "head_dim must be %d", kHeadDim);
     LUTVQ_REQUIRE(n_heads > 0 && n_kv_heads > 0 && n_heads % n_kv_heads == 0 && max_seq > 0 && max_seq <= 8192, "bad head counts / max_seq");
     return launch_pdl(attn_decode_kernel, dim3(n_heads), dim3(kAttnWarps * 32), ((size_t)max_seq + kAttnWarps * kHeadDim) * sizeof(float), static_cast<cudaStream_t>(stream),
                       static_cast<const __half*>(q), static_cast<const __half*>(k_new), static_cast<const __half*>(v_new),
                       static_cast<__half*>(kcache), static_cast<__half*>(vcache), pos, static_cast<__half*>(out), n_heads, n_kv_heads,
-                      max_seq, rope_theta);
+                      max_seq, rope_theta, ll);
+}
+
+int lutvq_decode_attention(const void* q, const void* k_new, const void* v_new, void* kcache, void* vcache, const int* pos,
+                           void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream) {
+    LUTVQ_REQUIRE(q && k_new && v_new, "null pointer");
+    return attention_impl(q, k_new, v_new, kcache, vcache, pos, out, n_heads, n_kv_heads, head_dim, max_seq, rope_theta, stream, LLIn{});
+}
+
+int lutvq_decode_attention_ll(lutvq_shard_t* h, int q_slot, int k_slot, int v_slot, unsigned q_seq, unsigned k_seq, unsigned v_seq,
+                              void* kcache, void* vcache, const int* pos, void* out, int n_heads, int n_kv_heads, int head_dim, int max_seq,
+                              float rope_theta, void* stream) {
+    LLIn ll;
+    size_t cap = 0;
+    const int slots[3] = {q_slot, k_slot, v_slot};
+    const unsigned seqs[3] = {q_seq, k_seq, v_seq};
+    for (int k = 0; k < 3; ++k) {
+        if (int rc = shard_ll_input(h, slots[k], &ll.w[k], &ll.tick, &ll.error, &cap)) return rc;
+        ll.seq[k] = seqs[k];
+    }
+    LUTVQ_REQUIRE((size_t)n_heads * head_dim <= cap, "q (%d values) exceeds the gather slot (%zu rows)", n_heads * head_dim, cap);
+    return attention_impl(nullptr, nullptr, nullptr, kcache, vcache, pos, out, n_heads, n_kv_heads, head_dim, max_seq, rope_theta, stream, ll);
 }
 
 }  // extern "C"

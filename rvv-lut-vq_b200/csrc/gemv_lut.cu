@@ -106,6 +106,7 @@ struct GemvParams {
     unsigned short tab_ks[kRangeTable];         // k-slice of item tab_begin[w]
     unsigned char tab_prob[kRangeTable];        // problem of worker w (ranges are per problem)
     unsigned long long* tl;   // debug timeline [256 CTAs][16] of %globaltimer stamps for this launch, or null
+    GemvLL ll;                // sharded decode: outputs as LL words into every rank's gather slot / inputs from LL words (common.cuh)
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -255,6 +256,15 @@ __device__ __forceinline__ void fx_scales(float bound, float& scale, float& inv)
 template <int DT>
 __device__ __forceinline__ void store_y(const GemvParams& p, const GemvProblem& PB, int row, typename Dtype<DT>::T v) {
     using T = typename Dtype<DT>::T;
+    if (p.ll.nranks > 0) {
+        // LL output: {value | epoch16 << 16} into every rank's gather slot (one atomic 32-bit store each, no flag, no fence)
+        const int pi = (int)(&PB - p.prob);
+        const unsigned ep = ll_epoch16(*p.ll.tick, p.ll.out_seq[pi]);       // after the dependency wait (every y store is)
+        const uint32_t word = (uint32_t)*reinterpret_cast<const unsigned short*>(&v) | (ep << 16);
+        const size_t off = p.ll.out_off[pi] + (size_t)row * 4;
+        for (int r = 0; r < p.ll.nranks; ++r) ll_st(p.ll.peer_base[r], off, word);
+        return;
+    }
     static_cast<T*>(PB.y)[row] = v;
     for (int r = 0; r < p.n_push; ++r) static_cast<T*>(p.push_y[r])[row] = v;       // NVLink stores (peer memory)
 }
@@ -375,7 +385,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         }
     }
     if (warp == NW - 1) {
-        if (lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
+        if (p.x != nullptr && lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
         {
             l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * 512 + lane * 128);
             if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * 512 + lane * 128);
@@ -430,11 +440,22 @@ lut_gemv_2x8_kernel(const GemvParams p) {
             const int g = ks_ * kSliceGroups + (int)threadIdx.x;
             uint4 v = make_uint4(0u, 0u, 0u, 0u);
             if (g < p.G) {
-                v = ldcg_u128(static_cast<const uint4*>(p.x) + g);        // L2-coherent: x may be the previous kernel's output
-                if (DT == LUTVQ_F16 && p.x_gate != nullptr) {
-                    const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
-                    v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
-                    v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+                if (p.ll.x_ll != nullptr) {
+                    // the activations are an earlier exchange's LL words in the local gather slot: poll this group's 8 words
+                    const unsigned tick = *p.ll.tick;
+                    v = ll_load8(p.ll.x_ll + (size_t)g * 8, ll_epoch16(tick, p.ll.x_seq), p.ll.error);
+                    if (p.ll.gate_ll != nullptr) {
+                        const uint4 gt = ll_load8(p.ll.gate_ll + (size_t)g * 8, ll_epoch16(tick, p.ll.gate_seq), p.ll.error);
+                        v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
+                        v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+                    }
+                } else {
+                    v = ldcg_u128(static_cast<const uint4*>(p.x) + g);        // L2-coherent: x may be the previous kernel's output
+                    if (DT == LUTVQ_F16 && p.x_gate != nullptr) {
+                        const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
+                        v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
+                        v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
+                    }
                 }
             }
             xs[threadIdx.x] = v;
@@ -834,7 +855,7 @@ size_t gemv_group_workspace_bytes(int n, const int* O) {
 // its share of the SMs.  Validation is done by the caller (api.cu / shard.cu).
 // x_gate != null (fp16): the activations are silu(x_gate) * x, evaluated in the kernel's x loads.
 static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                            void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
+                            void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll = nullptr) {
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
     LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
@@ -853,6 +874,9 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
     GemvParams p;
     p.n_prob = n; p.x = x; p.G = G;
     p.x_gate = x_gate;
+    p.ll = ll ? *ll : GemvLL{};
+    LUTVQ_REQUIRE(x != nullptr || p.ll.x_ll != nullptr, "null x pointer");
+    LUTVQ_REQUIRE(p.ll.gate_ll == nullptr || dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only");
     LUTVQ_REQUIRE(p.x_gate == nullptr || (dtype == LUTVQ_F16 && !(flags & LUTVQ_FLAG_X_READY)), "the fused SwiGLU input is fp16 only and never X_READY");
     p.has_table = 0;
     int W_total = 0, left = workers;
@@ -907,8 +931,8 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
 }
 
 int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push) {
-    return gemv_launch_impl(n, items, 1, x, x_gate, I, dtype, flags, ws, ws_bytes, stream, push);
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll) {
+    return gemv_launch_impl(n, items, 1, x, x_gate, I, dtype, flags, ws, ws_bytes, stream, push, ll);
 }
 
 // One GEMV on a packed code image: y = epilogue(W(codes) . x).

@@ -28,7 +28,7 @@ int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* code
                     cudaStream_t stream, const GemvPush* push);
 
 int gemv_2x8_launch_group(int n, const GemvItem* items, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push);
+                          void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll = nullptr);
 
 constexpr int    kShardMaxRanks  = 8;
 constexpr int    kShardMaxSlots  = 64;      // = bits of a slot mask; [slot][rank] epochs fill exactly the first kLocalOff bytes
@@ -39,6 +39,7 @@ constexpr size_t kLocalOff       = 2048;       // local-only area inside the fla
 struct Shard {
     int nranks = 0, rank = 0, n_slots = 0, device = -1;
     size_t slot_bytes = 0, total_bytes = 0;
+    size_t ll_off = 0, ll_slot_bytes = 0;      // LL gather words (common.cuh): n_slots slots of one 32-bit word per output row, behind the plain slots
     uint8_t* local = nullptr;                   // this rank's symmetric buffer
     uint8_t* peer[kShardMaxRanks] = {};         // peer[r] = rank r's buffer as mapped here (peer[rank] == local)
     bool ipc_opened[kShardMaxRanks] = {};
@@ -188,6 +189,23 @@ __global__ void __launch_bounds__(kExThreads) shard_exchange_kernel(uint8_t* loc
     }
 }
 
+// local state words behind sent[] / consumed[] / error / arrive: the LL step counter
+constexpr int kLLTickWord = 2 * kShardMaxSlots + 2;
+
+__global__ void shard_ll_tick_kernel(unsigned* tick) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    *tick += 1u;
+}
+
+// LL words of a slot -> a plain fp16 / bf16 vector (tests, and consumers that are not ours, e.g. a library GEMM)
+__global__ void shard_ll_unpack_kernel(const uint32_t* words, const unsigned* tick, unsigned seq, unsigned* error, unsigned short* y, int n) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const unsigned ep = ll_epoch16(*tick, seq);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) y[i] = ll_load1(words + i, ep, error);
+}
+
 static int launch_exchange(Shard* s, const ExchangeList& ex, cudaStream_t stream, int do_push = 1, int do_wait = 1) {
     PeerBases pb;
     for (int r = 0; r < kShardMaxRanks; ++r) pb.base[r] = r < s->nranks ? s->peer[r] : nullptr;
@@ -218,7 +236,9 @@ int lutvq_shard_create(lutvq_shard_t** out, int nranks, int rank, int n_slots, s
     LUTVQ_REQUIRE(s != nullptr, "out of host memory");
     s->nranks = nranks; s->rank = rank; s->n_slots = n_slots; s->device = di.device;
     s->slot_bytes = (slot_bytes + 255) / 256 * 256;
-    s->total_bytes = kShardFlagBytes + s->slot_bytes * n_slots;
+    s->ll_off = kShardFlagBytes + s->slot_bytes * n_slots;
+    s->ll_slot_bytes = 2 * s->slot_bytes;
+    s->total_bytes = s->ll_off + s->ll_slot_bytes * n_slots;
     cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&s->local), s->total_bytes);
     if (e != cudaSuccess) { delete s; return fail(LUTVQ_ECUDA, "cudaMalloc(%zu) failed: %s", s->total_bytes, cudaGetErrorString(e)); }
     e = cudaMemset(s->local, 0, s->total_bytes);
@@ -365,6 +385,104 @@ int lutvq_sharded_matmat_group_packed_swiglu(lutvq_shard_t* h, int n, const int*
     LUTVQ_REQUIRE(gate && up, "null gate/up pointer");
     LUTVQ_REQUIRE(dtype == LUTVQ_F16, "the fused SwiGLU input is fp16 only (dtype %d)", dtype);
     return sharded_group_impl(h, n, slots, row_offsets, up, gate, packed, codebooks, scales, bias, rows_local, prob_k, dtype, flags, ws, ws_bytes, stream);
+}
+
+}  // extern "C"
+
+namespace lutvq {
+int shard_ll_input(lutvq_shard_t* h, int slot, const uint32_t** words, const unsigned** tick, unsigned** error, size_t* capacity_rows) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
+    unsigned* lstate = reinterpret_cast<unsigned*>(s->local + kLocalOff);
+    *words = reinterpret_cast<const uint32_t*>(s->local + s->ll_off + s->ll_slot_bytes * slot);
+    *tick = lstate + kLLTickWord;
+    *error = lstate + 2 * kShardMaxSlots;
+    *capacity_rows = s->ll_slot_bytes / 4;
+    return LUTVQ_OK;
+}
+}  // namespace lutvq
+
+extern "C" {
+
+int lutvq_shard_ll_tick(lutvq_shard_t* h, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    unsigned* lstate = reinterpret_cast<unsigned*>(s->local + kLocalOff);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(1); cfg.blockDim = dim3(1); cfg.dynamicSmemBytes = 0; cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_ll_tick_kernel, lstate + kLLTickWord));
+    return LUTVQ_OK;
+}
+
+int lutvq_shard_ll_unpack(lutvq_shard_t* h, int slot, unsigned seq, void* y, int n, void* stream) {
+    const uint32_t* words; const unsigned* tick; unsigned* error; size_t cap;
+    if (int rc = shard_ll_input(h, slot, &words, &tick, &error, &cap)) return rc;
+    LUTVQ_REQUIRE(y != nullptr && n > 0 && (size_t)n <= cap, "bad y / n=%d (slot holds %zu rows)", n, cap);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((n + 255) / 256 < 64 ? (n + 255) / 256 : 64); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, shard_ll_unpack_kernel, words, tick, seq, error, static_cast<unsigned short*>(y), n));
+    return LUTVQ_OK;
+}
+
+// n <= 3 linears that share an input in ONE launch; every finished output row goes out as an LL word into ALL ranks' gather
+// slots (out_slots[i], at this rank's row offset) -- no exchange launch, no flag, no fence.  The input is either a plain
+// device vector x (x_slot < 0) or the LL words of an earlier exchange in the local slot x_slot (sequence number x_seq); with
+// gate_slot >= 0 the activations are silu(gate) * x, both from LL slots (fp16).
+int lutvq_sharded_matmat_group_ll(lutvq_shard_t* h, int n, const int* out_slots, const size_t* row_offsets, const unsigned* out_seq,
+                                  const void* x, int x_slot, unsigned x_seq, int gate_slot, unsigned gate_seq,
+                                  const void* const* packed, const void* const* codebooks, const void* const* scales,
+                                  const void* const* bias, const int* rows_local, int prob_k, int dtype, unsigned flags,
+                                  void* ws, size_t ws_bytes, void* stream) {
+    Shard* s = reinterpret_cast<Shard*>(h);
+    LUTVQ_REQUIRE(s != nullptr && s->attached, "shard not attached");
+    LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
+    LUTVQ_REQUIRE(out_slots && row_offsets && out_seq && packed && codebooks && rows_local, "null pointer");
+    LUTVQ_REQUIRE(prob_k > 0 && prob_k % 64 == 0, "bad prob_k=%d", prob_k);
+    LUTVQ_REQUIRE(!(flags & (LUTVQ_FLAG_PUSH_EPILOGUE | LUTVQ_FLAG_X_READY)), "LL launches are dependent launches without the flag-based push");
+    LUTVQ_REQUIRE((x != nullptr) != (x_slot >= 0), "exactly one of x / x_slot");
+    LUTVQ_REQUIRE(gate_slot < 0 || x_slot >= 0, "an LL gate needs an LL x");
+    if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+    unsigned* lstate = reinterpret_cast<unsigned*>(s->local + kLocalOff);
+    GemvLL ll;
+    ll.nranks = s->nranks;
+    for (int r = 0; r < s->nranks; ++r) ll.peer_base[r] = s->peer[r] + s->ll_off;
+    ll.tick = lstate + kLLTickWord;
+    ll.error = lstate + 2 * kShardMaxSlots;
+    GemvItem items[3];
+    for (int i = 0; i < n; ++i) {
+        const int slot = out_slots[i];
+        LUTVQ_REQUIRE(slot >= 0 && slot < s->n_slots, "slot %d out of range (n_slots=%d)", slot, s->n_slots);
+        LUTVQ_REQUIRE(slot != x_slot && slot != gate_slot, "a launch must not write the slot it reads");
+        for (int j = 0; j < i; ++j) LUTVQ_REQUIRE(out_slots[j] != slot, "the linears of a group need distinct slots");
+        LUTVQ_REQUIRE(rows_local[i] > 0 && (row_offsets[i] + (size_t)rows_local[i]) * 4 <= s->ll_slot_bytes, "rows of linear %d do not fit a slot", i);
+        LUTVQ_REQUIRE(out_seq[i] < 1024u, "sequence numbers are < 1024");
+        LUTVQ_REQUIRE(packed[i] && codebooks[i], "null pointer in linear %d", i);
+        ll.out_off[i] = s->ll_slot_bytes * slot + row_offsets[i] * 4;
+        ll.out_seq[i] = out_seq[i];
+        // y is unused in LL mode (store_y writes the LL words only); keep a valid pointer for the launcher's checks
+        items[i] = GemvItem{packed[i], codebooks[i], s->local + s->ll_off, scales ? scales[i] : nullptr, bias ? bias[i] : nullptr, rows_local[i]};
+    }
+    if (x_slot >= 0) {
+        LUTVQ_REQUIRE(x_slot < s->n_slots && (size_t)prob_k * 4 <= s->ll_slot_bytes, "x slot %d out of range or too small for prob_k=%d", x_slot, prob_k);
+        LUTVQ_REQUIRE(x_seq < 1024u && gate_seq < 1024u, "sequence numbers are < 1024");
+        ll.x_ll = reinterpret_cast<const uint32_t*>(s->local + s->ll_off + s->ll_slot_bytes * x_slot);
+        ll.x_seq = x_seq;
+        if (gate_slot >= 0) {
+            LUTVQ_REQUIRE(gate_slot < s->n_slots && dtype == LUTVQ_F16, "gate slot out of range, or not fp16");
+            ll.gate_ll = reinterpret_cast<const uint32_t*>(s->local + s->ll_off + s->ll_slot_bytes * gate_slot);
+            ll.gate_seq = gate_seq;
+        }
+    }
+    return gemv_2x8_launch_group(n, items, x, nullptr, prob_k, dtype, flags, ws, ws_bytes, static_cast<cudaStream_t>(stream), nullptr, &ll);
 }
 
 int lutvq_shard_wait(lutvq_shard_t* h, int slot, void* stream) {

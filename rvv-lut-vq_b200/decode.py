@@ -74,7 +74,7 @@ class Decoder:
         self.cfg, self.dev, self.world, self.rank, self.group, self.max_seq = cfg, torch.device(device), world, rank, group, max_seq
         self.exchange, self.pg, self.grouped = exchange, pg, grouped
         self.fuse_swiglu = fuse_swiglu and grouped and not (world > 1 and exchange == "nccl")
-        if world > 1 and exchange == "push":
+        if (world > 1 and exchange == "push") or exchange == "ll":
             assert group is not None
         self.lib = _lib.lib()
         dev, H = self.dev, cfg.hidden
@@ -205,8 +205,61 @@ class Decoder:
         self.launches_per_token += 1
         return [self.group.slot_tensor(s_, l.out_f, torch.float16) for s_, l in zip(slots, lins)]
 
+    # ---- LL exchange mode: every sharded output goes out as LL words, every consumer polls them (no exchange launches) ----
+    def _ll_next(self):
+        s = self._ll_slot
+        self._ll_slot = (s + 1) % self.group.n_slots
+        self._ll_seq += 1
+        return s, self._ll_seq
+
+    def _group_ll(self, L, names, x=None, x_ll=None, gate_ll=None):
+        """-> [(slot, seq)] of the outputs; x: plain tensor, or x_ll / gate_ll = (slot, seq) of earlier exchanges"""
+        lins = [L[k] for k in names]
+        outs = [self._ll_next() for _ in names]
+        n = len(names)
+        arr = lambda ts: (ctypes.c_void_p * n)(*[None if t is None else t.data_ptr() for t in ts])
+        sl = (ctypes.c_int * n)(*[o[0] for o in outs])
+        sq = (ctypes.c_uint * n)(*[o[1] for o in outs])
+        ro = (ctypes.c_size_t * n)(*[l.begin for l in lins])
+        rl = (ctypes.c_int * n)(*[l.rows for l in lins])
+        xs, xq = x_ll if x_ll is not None else (-1, 0)
+        gs, gq = gate_ll if gate_ll is not None else (-1, 0)
+        _lib.check(self.lib.lutvq_sharded_matmat_group_ll(
+            self.group._h, n, sl, ro, sq, None if x is None else ctypes.c_void_p(x.data_ptr()), xs, xq, gs, gq,
+            arr([l.packed for l in lins]), arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n), rl,
+            lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st()))
+        self.launches_per_token += 1
+        return outs
+
+    def _step_ll(self):
+        cfg, lib, P, st, h = self.cfg, self.lib, (lambda t: ctypes.c_void_p(t.data_ptr())), self._st, self.group._h
+        self._ll_slot, self._ll_seq = 0, 0
+        _lib.check(lib.lutvq_shard_ll_tick(h, st()))
+        self.resid.copy_(torch.index_select(self.embed, 0, self.token)[0])
+        delta = None
+        for L in self.layers:
+            if delta is None:
+                _lib.check(lib.lutvq_decode_add_rmsnorm(P(self.resid), None, P(L["norm1"]), P(self.normed), cfg.hidden, cfg.eps, st()))
+            else:
+                _lib.check(lib.lutvq_decode_add_rmsnorm_ll(h, P(self.resid), delta[0], delta[1], P(L["norm1"]), P(self.normed), cfg.hidden, cfg.eps, st()))
+            q, k, v = self._group_ll(L, ["q", "k", "v"], x=self.normed)
+            _lib.check(lib.lutvq_decode_attention_ll(h, q[0], k[0], v[0], q[1], k[1], v[1], P(L["kcache"]), P(L["vcache"]), P(self.pos),
+                                                     P(self.attn_out), cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_seq, cfg.rope_theta, st()))
+            (o,) = self._group_ll(L, ["o"], x=self.attn_out)
+            _lib.check(lib.lutvq_decode_add_rmsnorm_ll(h, P(self.resid), o[0], o[1], P(L["norm2"]), P(self.normed), cfg.hidden, cfg.eps, st()))
+            gate, up = self._group_ll(L, ["gate", "up"], x=self.normed)
+            (delta,) = self._group_ll(L, ["down"], x_ll=up, gate_ll=gate)            # silu(gate) * up inside the activation load
+            self.launches_per_token += 3
+        _lib.check(lib.lutvq_decode_add_rmsnorm_ll(h, P(self.resid), delta[0], delta[1], P(self.final_norm), P(self.normed), cfg.hidden, cfg.eps, st()))
+        torch.mv(self.lm_head, self.normed, out=self.logits)
+        self.token.copy_(torch.argmax(self.logits).reshape(1))
+        self.pos.add_(1)
+        self.launches_per_token += 3
+
     def step(self):
         """one token: reads self.token / self.pos, writes self.logits and the next token"""
+        if self.exchange == "ll":
+            return self._step_ll()
         cfg, lib, P = self.cfg, self.lib, (lambda t: ctypes.c_void_p(t.data_ptr()))
         st = self._st
         self.resid.copy_(torch.index_select(self.embed, 0, self.token)[0])

@@ -143,6 +143,46 @@ class ShardGroup:
         with torch.cuda.device(self.device):
             self._check(self._lib.lutvq_shard_wait_mask(self._h, mask, ops._stream(self.device)))
 
+    # ---- LL exchange (include/lutvq.h '"LL" exchange'): no exchange launch, no flags; consumers poll the words they use ----
+    def ll_tick(self) -> None:
+        """++step counter; once per step (token) on every rank, before the step's first exchange"""
+        from . import ops
+        self._check(self._lib.lutvq_shard_ll_tick(self._h, ops._stream(self.device)))
+
+    def matmat_group_ll(self, out_slots, row_offsets, out_seq, packed, codebooks, scales, bias, rows_local, in_features: int, *,
+                        x=None, x_slot: int = -1, x_seq: int = 0, gate_slot: int = -1, gate_seq: int = 0, dtype=None, ws=None) -> None:
+        """n <= 3 linears sharing an input in one launch; outputs as LL words into every rank's slot out_slots[i]"""
+        import torch
+        from . import ops
+        n = len(packed)
+        dt = ops.check_use_bfloat16(x) if x is not None else ops._DT[dtype or torch.float16]
+        arr = lambda ts: (ctypes.c_void_p * n)(*[None if t is None else t.data_ptr() for t in ts])
+        sl = (ctypes.c_int * n)(*out_slots)
+        ro = (ctypes.c_size_t * n)(*row_offsets)
+        sq = (ctypes.c_uint * n)(*out_seq)
+        rl = (ctypes.c_int * n)(*rows_local)
+        if ws is None:
+            need = int(self._lib.lutvq_group_workspace_bytes(n, rl, in_features))
+            key = ("ll", self.device.index)
+            ws = self._views.get(key)
+            if ws is None or ws.numel() < need:
+                ws = torch.zeros(max(need, 1 << 18), dtype=torch.uint8, device=self.device)
+                self._views[key] = ws
+        with torch.cuda.device(self.device):
+            self._check(self._lib.lutvq_sharded_matmat_group_ll(
+                self._h, n, sl, ro, sq, None if x is None else ops._ptr(x.contiguous()), x_slot, x_seq, gate_slot, gate_seq,
+                arr(packed), arr(codebooks), arr(scales), arr(bias if bias is not None else [None] * n), rl, in_features, dt, 0,
+                ops._ptr(ws), ws.numel(), ops._stream(self.device)))
+
+    def ll_unpack(self, slot: int, seq: int, out_features: int, dtype=None):
+        """LL slot -> plain vector (waits, bounded, until every word of the exchange `seq` of this step has landed)"""
+        import torch
+        from . import ops
+        y = torch.empty(out_features, dtype=dtype or torch.float16, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self._lib.lutvq_shard_ll_unpack(self._h, slot, seq, ops._ptr(y), out_features, ops._stream(self.device)))
+        return y
+
     def error(self) -> int:
         e = ctypes.c_uint(0)
         self._check(self._lib.lutvq_shard_error(self._h, ctypes.byref(e)))

@@ -106,6 +106,25 @@ def _worker(rank, world, port, tmp):
             assert torch.equal(y1.view(torch.int16), want.view(torch.int16)), f"push mode differs (rank {rank}, rep {rep})"
             assert torch.equal(y2.view(torch.int16), want.view(torch.int16)), f"nccl mode differs (rank {rank}, rep {rep})"
             dist.barrier()
+        # LL exchange across real peers: a sharded 2-GEMV chain (the second reads the first's LL words) == the unsharded chain
+        I2 = O
+        L2 = synth.make_layer_np(I2, 4096, seed=4, scales="randn", bias=False)
+        codes2, cb2, sc2 = c(L2["codes"]), c(L2["codebooks"]), c(L2["scales"]) * 0.01
+        lay2 = ShardedQuantizedLinear(codes2, cb2, sc2, None, 4096, world, rank, group=group, mode="push")
+        for rep in range(6):
+            x = c(L["x"])[0] * (1.0 + 0.25 * rep)
+            y1 = ops.code2x8_matmat(x.reshape(1, -1), codes, cb, sc * 0.01, bi)[0]
+            want2 = ops.code2x8_matmat(y1.reshape(1, -1), codes2, cb2, sc2, None)[0]
+            group.ll_tick()
+            s1, s2 = (2 * rep) % 4, (2 * rep + 1) % 4
+            group.matmat_group_ll([s1], [push.begin], [1], [push.packed], [push.codebooks], [push.scales * 0.01], [push.bias], [push.rows], I, x=x)
+            group.matmat_group_ll([s2], [lay2.begin], [2], [lay2.packed], [lay2.codebooks], [lay2.scales], None, [lay2.rows], I2, x_slot=s1, x_seq=1)
+            got1, got2 = group.ll_unpack(s1, 1, O), group.ll_unpack(s2, 2, 4096)
+            torch.cuda.synchronize()
+            assert group.error() == 0
+            assert torch.equal(got1.view(torch.int16), y1.view(torch.int16)), f"LL exchange 1 differs (rank {rank}, rep {rep})"
+            assert torch.equal(got2.view(torch.int16), want2.view(torch.int16)), f"LL exchange 2 differs (rank {rank}, rep {rep})"
+            dist.barrier()
         group.close()
         with open(os.path.join(tmp, f"ok{rank}"), "w") as f:
             f.write("ok")
@@ -119,6 +138,104 @@ def test_multi_gpu_push_and_nccl(tmp_path):
     world = min(torch.cuda.device_count(), 8)
     mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     assert all(os.path.exists(tmp_path / f"ok{r}") for r in range(world))
+
+
+# ------------------------------------------------------------------------------------------------ LL exchange
+@pytest.mark.parametrize("world,I,O,O2", [(1, 512, 256, 128), (2, 1024, 1024, 1000), (4, 4096, 4096, 4096), (8, 2048, 2048, 1024)])
+def test_ll_exchange_one_gpu(world, I, O, O2):
+    """every "rank" (one process, one GPU, own stream) pushes its rows as LL words into all ranks' slots; the consumers --
+    lutvq_shard_ll_unpack, a second sharded GEMV reading the LL words as its activations, and one with the fused SwiGLU --
+    must reproduce the unsharded results bit for bit, also over slot reuse and step (tick) changes"""
+    from rvv_lut_vq_b200 import ops, synth
+    from rvv_lut_vq_b200.sharded import ShardGroup, ShardedQuantizedLinear
+    A = synth.make_layer_np(I, O, seed=world * 11 + 1, scales="randn", bias=True)       # "gate"
+    B = synth.make_layer_np(I, O, seed=world * 11 + 2, scales="randn", bias=False)      # "up"
+    C = synth.make_layer_np(O, O2, seed=world * 11 + 3, scales="randn", bias=False)     # "down"
+    dA, dB, dC = ({k: cu(v) for k, v in L.items() if v is not None and k != "idx"} for L in (A, B, C))
+    for d in (dA, dB):
+        d["scales"] = d["scales"] * 0.05
+    groups = [ShardGroup(world, r, max(O, O2), n_slots=4) for r in range(world)]
+    for g in groups:
+        g.attach_same_process(groups)
+    mk = lambda d, Of, r: ShardedQuantizedLinear(d["codes"], d["codebooks"], d["scales"], d.get("bias"), Of, world, r, group=groups[r], mode="push")
+    la, lb, lc = ([mk(d, Of, r) for r in range(world)] for d, Of in ((dA, O), (dB, O), (dC, O2)))
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    torch.cuda.synchronize()
+    for rep in range(5):
+        x = dA["x"][0] * (1.0 + 0.5 * rep)
+        ya = ops.code2x8_matmat(x.reshape(1, -1), dA["codes"], dA["codebooks"], dA["scales"], dA["bias"])[0]
+        yb = ops.code2x8_matmat(x.reshape(1, -1), dB["codes"], dB["codebooks"], dB["scales"], None)[0]
+        pk = ops.code2x8_prepack(dC["codes"])
+        want_plain = ops.code2x8_matmat(yb.reshape(1, -1), dC["codes"], dC["codebooks"], dC["scales"], None)[0]
+        want_swiglu = ops.code2x8_matmat_group_packed(yb, [pk], [O2], [dC["codebooks"]], [dC["scales"]], None, gate=ya)[0]
+        torch.cuda.synchronize()
+        sa, sb, sc_, sd = 0, 1, 2, 3
+        for r in range(world):                               # step counter + the producers of every rank first (one GPU!)
+            with torch.cuda.stream(streams[r]):
+                g = groups[r]
+                g.ll_tick()
+                g.matmat_group_ll([sa, sb], [la[r].begin, lb[r].begin], [1, 2], [la[r].packed, lb[r].packed], [la[r].codebooks, lb[r].codebooks],
+                                  [la[r].scales, lb[r].scales], [la[r].bias, None], [la[r].rows, lb[r].rows], I, x=x)
+        for r in range(world):                               # consumers: GEMVs whose activations are the LL words
+            with torch.cuda.stream(streams[r]):
+                g = groups[r]
+                g.matmat_group_ll([sc_], [lc[r].begin], [3], [lc[r].packed], [lc[r].codebooks], [lc[r].scales], None, [lc[r].rows], O, x_slot=sb, x_seq=2)
+                g.matmat_group_ll([sd], [lc[r].begin], [4], [lc[r].packed], [lc[r].codebooks], [lc[r].scales], None, [lc[r].rows], O, x_slot=sb, x_seq=2,
+                                  gate_slot=sa, gate_seq=1)
+        outs = []
+        for r in range(world):
+            with torch.cuda.stream(streams[r]):
+                g = groups[r]
+                outs.append((g.ll_unpack(sa, 1, O), g.ll_unpack(sb, 2, O), g.ll_unpack(sc_, 3, O2), g.ll_unpack(sd, 4, O2)))
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert groups[r].error() == 0
+            for got, want, what in zip(outs[r], (ya, yb, want_plain, want_swiglu), ("gate", "up", "down(up)", "down(silu(gate)*up)")):
+                assert torch.equal(got.view(torch.int16), want.view(torch.int16)), f"rank {r} rep {rep}: {what} differs from the unsharded result"
+    for g in groups:
+        g.close()
+
+
+def test_ll_poll_times_out_instead_of_hanging():
+    from rvv_lut_vq_b200.sharded import ShardGroup
+    a, b = ShardGroup(2, 0, 64, n_slots=2), ShardGroup(2, 1, 64, n_slots=2)
+    a.attach_same_process([a, b])
+    b.attach_same_process([a, b])
+    a.ll_tick()
+    a.ll_unpack(0, 1, 64)                                  # nobody produced exchange 1: bounded poll, then the error word
+    torch.cuda.synchronize()
+    assert a.error() != 0
+    a.close()
+    b.close()
+
+
+def test_decode_ll_mode_equals_plain_mode():
+    """Decoder(exchange="ll") -- every linear's output as LL words, every consumer polling them -- produces the same tokens and
+    logits, bit for bit, as the plain single-GPU decoder (same kernels, same arithmetic; only the operand plumbing differs)"""
+    from rvv_lut_vq_b200.decode import Decoder, TINY
+    from rvv_lut_vq_b200.sharded import ShardGroup
+    dev = torch.device("cuda", 0)
+    plain = Decoder(TINY, dev, max_seq=64, seed=5)
+    group = ShardGroup(1, 0, max(TINY.intermediate, TINY.hidden), n_slots=8)
+    ll = Decoder(TINY, dev, world=1, rank=0, group=group, max_seq=64, seed=5, exchange="ll")
+    st = torch.cuda.Stream()
+    for dec in (plain, ll):
+        dec.reset(1)
+        dec.capture(st)
+        dec.reset(1)
+        for L in dec.layers:
+            L["kcache"].zero_(); L["vcache"].zero_()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(st):
+        for i in range(10):
+            plain.run_token()
+            ll.run_token()
+            st.synchronize()
+            assert group.error() == 0
+            assert torch.equal(plain.logits.view(torch.int16), ll.logits.view(torch.int16)), f"token {i}: logits differ"
+            assert int(plain.token[0]) == int(ll.token[0])
+    assert ll.launches_per_token < plain.launches_per_token + 3
+    group.close()
 
 
 # ------------------------------------------------------------------------------------------------ decode loop

@@ -17,7 +17,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="7b", choices=["7b", "70b", "tiny"])
     ap.add_argument("--tokens", type=int, default=128)
-    ap.add_argument("--exchange", default="push", choices=["push", "nccl"])
+    ap.add_argument("--exchange", default="ll", choices=["ll", "push", "nccl"])
     ap.add_argument("--ungrouped", action="store_true", help="one launch per linear instead of grouped q/k/v and gate/up launches")
     ap.add_argument("--unfused-swiglu", action="store_true", help="separate silu*up launch instead of the fused down_proj activation load")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (memory-bounded experiments)")
@@ -36,7 +36,7 @@ def main():
     if args.layers:
         import dataclasses
         cfg = dataclasses.replace(cfg, n_layers=args.layers)
-    group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if (world > 1 and args.exchange == "push") else None
+    group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if (world > 1 and args.exchange in ("push", "ll")) else None
     dec = Decoder(cfg, dev, world, rank, group, max_seq=args.tokens + 16, exchange=args.exchange, grouped=not args.ungrouped, fuse_swiglu=not args.unfused_swiglu)
     st = torch.cuda.Stream()
     dec.reset(1)
