@@ -128,3 +128,33 @@ def test_algorithmic_bytes_table():
     assert synth.gemv_algorithmic_bytes(4096, 4096) == 4227072
     assert synth.gemv_algorithmic_bytes(4096, 11008) == 11332608
     assert synth.gemv_algorithmic_bytes(11008, 4096) == 11318784
+
+
+def test_traffic_counter_matches_reference_rows():
+    """reference_dataflow_traffic replays VQ.dataflow_sim's loop nests (vq.py:68-267) on sizes only; every
+    counter of every (loop order, configuration) row equals what the reference's own code produced (oracle/gen_golden_dataflow.py)."""
+    import csv
+    from rvv_lut_vq_b200 import traffic
+    rows = list(csv.DictReader(open(os.path.join(ROOT, "tests", "golden", "dataflow_sim_ref.csv"))))
+    assert len(rows) == 28
+    for r in rows:
+        cfg = (int(r["D"]), int(r["M"]), int(r["N"]), int(r["K"]))
+        got = traffic.reference_dataflow_traffic(cfg, int(r["Din"]), int(r["Dout"]), r["Dataflow"], int(r["VLEN"]))
+        for k in ("codeword", "codebook", "lut", "inp", "psum"):
+            assert got[k] == float(r[k + "_MB"]), (r["VQ_type"], r["Dataflow"], k)
+        assert (got["N_tile"], got["M_tile"], got["CW_tile"]) == (int(r["N_tile"]), int(r["M_tile"]), int(r["CW_tile"]))
+    with pytest.raises(NotImplementedError):
+        traffic.reference_dataflow_traffic((128, 8, 1, 256), 1, 1024, "OMND-compact")
+
+
+def test_gpu_traffic_model_vs_measured_dram_bytes():
+    """the model's HBM figure is DESIGN.md's algorithmic byte count, and the DRAM bytes ncu measured for the kernel
+    (profiles/traffic.json) are within 2 % of it: no wasted re-reads"""
+    import json
+    from rvv_lut_vq_b200 import synth, traffic
+    for (i, o) in [(4096, 4096), (4096, 11008), (11008, 4096)]:
+        m = traffic.gemv_traffic_model(i, o)
+        assert m["hbm"] == synth.gemv_algorithmic_bytes(i, o)
+        assert m["smem_ld"] == 4 * m["hbm"] - 4 * (8192 + 2 * i + 4 * o) and m["n_k"] == -(-i // 256)
+    measured = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["lut_gemv_2x8_kernel_4096x11008_dram_bytes_per_launch"]
+    assert 1.0 <= measured / traffic.gemv_traffic_model(4096, 11008)["hbm"] <= 1.02
