@@ -50,10 +50,13 @@ class _Linear:
     """one AQLM 2x8 linear: this rank's rows (packed), shared codebooks; writes its output into ``out`` (the caller's
     buffer on one GPU, a gather slot when sharded)"""
 
-    def __init__(self, in_f: int, out_f: int, dev, seed: int, world: int, rank: int, keep_codes: bool = False):
+    def __init__(self, in_f: int, out_f: int, dev, seed: int, world: int, rank: int, keep_codes: bool = False, skeleton: bool = False):
         self.in_f, self.out_f = in_f, out_f
         self.begin, self.end = shard_rows(out_f, world, rank)
         self.rows = self.end - self.begin
+        if skeleton:                                       # weights come from a checkpoint (hf_loader.load_llama_decoder)
+            self.packed = self.codes = self.codebooks = self.scales = None
+            return
         g = torch.Generator(device=dev)
         g.manual_seed(seed)
         # the FULL layer is generated and this rank keeps its rows: the model is the same for every world size
@@ -70,7 +73,8 @@ class _Linear:
 
 class Decoder:
     def __init__(self, cfg: DecoderConfig, device, world: int = 1, rank: int = 0, group: Optional[ShardGroup] = None,
-                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True, fuse_swiglu: bool = True):
+                 max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True, fuse_swiglu: bool = True,
+                 skeleton: bool = False):
         self.cfg, self.dev, self.world, self.rank, self.group, self.max_seq = cfg, torch.device(device), world, rank, group, max_seq
         self.exchange, self.pg, self.grouped = exchange, pg, grouped
         self.fuse_swiglu = fuse_swiglu and grouped and not (world > 1 and exchange == "nccl")
@@ -81,7 +85,7 @@ class Decoder:
         shapes = cfg.linear_shapes()
         self.layers: List[dict] = []
         for li in range(cfg.n_layers):
-            L = {name: _Linear(i, o, dev, seed * 100003 + li * 16 + j, world, rank, keep_codes) for j, (name, (i, o)) in enumerate(shapes.items())}
+            L = {name: _Linear(i, o, dev, seed * 100003 + li * 16 + j, world, rank, keep_codes, skeleton) for j, (name, (i, o)) in enumerate(shapes.items())}
             L["norm1"] = torch.ones(H, dtype=torch.float16, device=dev)
             L["norm2"] = torch.ones(H, dtype=torch.float16, device=dev)
             kv = cfg.n_kv_heads

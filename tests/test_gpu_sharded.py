@@ -372,3 +372,49 @@ def test_decode_add_rmsnorm_vs_torch(n, with_delta):
     x = want_resid.float()
     want = x * torch.rsqrt((x * x).mean() + 1e-5) * w.float()
     assert (y.float() - want).abs().max() <= 2e-3 * want.abs().max()
+
+
+def test_decoder_from_hf_checkpoint(tmp_path):
+    """hf_loader.load_llama_decoder: a Decoder filled from an AQLM 2x8 checkpoint in the HF layout (convert_to_hf.py:50-100 key
+    names) decodes exactly like the decoder the checkpoint was written from"""
+    from rvv_lut_vq_b200 import hf_loader
+    from rvv_lut_vq_b200.decode import Decoder, TINY
+    from rvv_lut_vq_b200.hf_loader import _LLAMA_LINEARS
+    dev = torch.device("cuda", 0)
+    src = Decoder(TINY, dev, max_seq=32, seed=9, keep_codes=True)
+    cfg = {"model_type": "llama", "hidden_size": TINY.hidden, "intermediate_size": TINY.intermediate, "num_hidden_layers": TINY.n_layers,
+           "num_attention_heads": TINY.n_heads, "num_key_value_heads": TINY.n_kv_heads, "vocab_size": TINY.vocab, "rms_norm_eps": TINY.eps,
+           "rope_theta": TINY.rope_theta,
+           "quantization_config": {"quant_method": "aqlm", "nbits_per_codebook": 8, "num_codebooks": 2, "out_group_size": 1, "in_group_size": 8,
+                                   "linear_weights_not_to_quantize": ["model.embed_tokens.weight", "lm_head.weight"]}}
+    state = {"model.embed_tokens.weight": src.embed, "lm_head.weight": src.lm_head, "model.norm.weight": src.final_norm}
+    for li, L in enumerate(src.layers):
+        base = f"model.layers.{li}."
+        for name, hf in _LLAMA_LINEARS.items():
+            state[base + hf + ".codes"] = L[name].codes
+            state[base + hf + ".codebooks"] = L[name].codebooks
+            state[base + hf + ".scales"] = L[name].scales.reshape(-1, 1, 1, 1)
+        state[base + "input_layernorm.weight"] = L["norm1"]
+        state[base + "post_attention_layernorm.weight"] = L["norm2"]
+    hf_loader.save_checkpoint(str(tmp_path), cfg, state)
+    dec = hf_loader.load_llama_decoder(str(tmp_path), dev, max_seq=32)
+    qs = hf_loader.quantized_linears(*hf_loader.load_checkpoint(str(tmp_path)), device=dev, prefix_filter="model.layers.0.self_attn")
+    assert sorted(qs) == [f"model.layers.0.self_attn.{n}_proj" for n in ("k", "o", "q", "v")]
+    st = torch.cuda.Stream()
+    for d in (src, dec):
+        d.reset(1)
+        d.capture(st)
+        d.reset(1)
+        for L in d.layers:
+            L["kcache"].zero_(); L["vcache"].zero_()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(st):
+        for i in range(6):
+            src.run_token(); dec.run_token()
+            st.synchronize()
+            assert torch.equal(src.logits.view(torch.int16), dec.logits.view(torch.int16)), f"token {i}"
+    x = torch.randn((2, TINY.hidden), dtype=torch.float16, device=dev)
+    q0 = qs["model.layers.0.self_attn.q_proj"]
+    from rvv_lut_vq_b200 import ops
+    L0 = src.layers[0]["q"]
+    assert torch.equal(q0(x).view(torch.int16), ops.code2x8_matmat(x, L0.codes, L0.codebooks, L0.scales.reshape(-1, 1, 1, 1), None).view(torch.int16))

@@ -158,3 +158,37 @@ def test_gpu_traffic_model_vs_measured_dram_bytes():
         assert m["smem_ld"] == 4 * m["hbm"] - 4 * (8192 + 2 * i + 4 * o) and m["n_k"] == -(-i // 256)
     measured = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["lut_gemv_2x8_kernel_4096x11008_dram_bytes_per_launch"]
     assert 1.0 <= measured / traffic.gemv_traffic_model(4096, 11008)["hbm"] <= 1.02
+
+
+def test_hf_checkpoint_layout_round_trip(tmp_path):
+    """the HF layout convert_to_hf.py:50-100 writes -- state-dict key names, packed code dtypes, config.json's
+    quantization_config -- read back without transformers; malformed checkpoints fail loudly"""
+    from rvv_lut_vq_b200 import hf_loader, utils
+    cfg = {"model_type": "llama", "hidden_size": 64, "intermediate_size": 128, "num_hidden_layers": 1, "num_attention_heads": 2, "vocab_size": 50,
+           "quantization_config": {"quant_method": "aqlm", "nbits_per_codebook": 8, "num_codebooks": 2, "out_group_size": 1, "in_group_size": 8,
+                                   "linear_weights_not_to_quantize": ["model.embed_tokens.weight", "lm_head.weight"]}}
+    g = torch.Generator().manual_seed(0)
+    state = {}
+    for name, (i, o) in {"self_attn.q_proj": (64, 64), "mlp.down_proj": (128, 64)}.items():
+        p = "model.layers.0." + name
+        state[p + ".codes"] = utils.pack_int_data(torch.randint(256, (o, i // 8, 2), generator=g), 8)   # convert_to_hf.py:66
+        state[p + ".codebooks"] = torch.randn((2, 256, 1, 8), generator=g).half()
+        state[p + ".scales"] = torch.randn((o, 1, 1, 1), generator=g).half()
+    state["model.embed_tokens.weight"] = torch.randn((50, 64), generator=g).half()
+    hf_loader.save_checkpoint(str(tmp_path), cfg, state)
+    cfg2, state2 = hf_loader.load_checkpoint(str(tmp_path))
+    assert cfg2["quantization_config"]["num_codebooks"] == 2
+    assert set(state2) == set(state) and all(torch.equal(state2[k], state[k]) and state2[k].dtype == state[k].dtype for k in state)
+    assert hf_loader.quantized_prefixes(state2) == ["model.layers.0.mlp.down_proj", "model.layers.0.self_attn.q_proj"]
+    assert state2["model.layers.0.self_attn.q_proj.codes"].dtype == torch.int8
+    dc = hf_loader.llama_decoder_config(cfg2)
+    assert (dc.hidden, dc.intermediate, dc.n_layers, dc.n_heads, dc.n_kv_heads, dc.head_dim) == (64, 128, 1, 2, 2, 32)
+    bad = dict(state)
+    del bad["model.layers.0.self_attn.q_proj.scales"]
+    with pytest.raises(KeyError):
+        hf_loader.quantized_prefixes(bad)
+    cfg_bad = dict(cfg)
+    cfg_bad.pop("quantization_config")
+    hf_loader.save_checkpoint(str(tmp_path / "noq"), cfg_bad, state)
+    with pytest.raises(ValueError):
+        hf_loader.load_checkpoint(str(tmp_path / "noq"))
