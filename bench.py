@@ -190,6 +190,8 @@ def measure_decode(torch, dist, model: str, world: int, rank: int, dev, tokens: 
     from rvv_lut_vq_b200.decode import LLAMA2_7B, LLAMA2_70B, Decoder
     from rvv_lut_vq_b200.sharded import ShardGroup
     cfg = {"7b": LLAMA2_7B, "70b": LLAMA2_70B}[model]
+    if world == 1:
+        exchange = "push"                                        # one GPU: the plain decoder (no gather slots at all)
     group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if world > 1 else None
     dec = Decoder(cfg, dev, world, rank, group, max_seq=tokens + 16, exchange=exchange)
     st = torch.cuda.Stream(dev)
