@@ -26,8 +26,8 @@
  *   - scratch memory is passed in (ws, ws_bytes); size it with lutvq_workspace_bytes().  A workspace must
  *     be zero-filled once before first use (cudaMemset); every call leaves its first lutvq_packed_workspace_bytes()
  *     bytes (the split-k words) all-zero again, so it may be reused by any later call ON THE SAME STREAM (any shape).
- *     The rest is a staging area that only the reference-layout entry points use (they re-lay the codes into the
- *     packed image first; callers that prepack once at load time never touch it and may pass the small size);
+ *     (The GEMV needs exactly those bytes for packed and reference-layout codes alike; the rest of lutvq_workspace_bytes()
+ *     is the split-k scratch of the batch > 6 tensor-core path);
  *   - dtype is the storage/arithmetic type of x, codebooks, scales, bias, y (fp16 or bf16, the two types
  *     cuda_kernel.cpp:9-25 accepts).  Codes are int8 holding unsigned 8-bit indices
  *     (aqlm/../utils.py:24-31), layout [prob_m][prob_k/8][num_codebooks] exactly as QuantizedLinear.codes.
@@ -78,8 +78,7 @@ int         lutvq_version(void);                     /* 10000*major + 100*minor 
 /* fills what the launch heuristics see; any pointer may be NULL */
 int         lutvq_device_info(int* sm_count, int* cc_major, int* cc_minor, size_t* smem_optin_bytes);
 
-/* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch), including the staging
- * area of the reference-layout entry points (about prob_m * prob_k / 4 bytes). */
+/* Scratch needed by matvec / matmat / matmat_dequant for an [prob_m x prob_k] layer (any batch). */
 size_t lutvq_workspace_bytes(int prob_m, int prob_k);
 /* Scratch needed by the *_packed / group / sharded entry points: the split-k words only (8 bytes per output row + 256). */
 size_t lutvq_packed_workspace_bytes(int prob_m, int prob_k);
@@ -110,11 +109,11 @@ int lutvq_code2x8_matmat_ex(const void* x, const void* codes, const void* codebo
 
 /* Optional load-time re-layout of the codes for the GEMV (the reference does the same kind of one-off permutation
  * for its CPU kernel in QuantizedLinear.prepare_matmul_op, aqlm/../inference.py:78-83).  The packed image holds the
- * same code bytes, ordered [k-slice of 128 code bytes][32-row set][8-row tile][half][lane] x 16 B in the order each lane
- * walks them (rvv-lut-vq_b200/csrc/lut_layout.h), so that a worker's share is ONE contiguous range streamed by 1-D bulk
- * async copies; rows / k-slices are zero-padded to whole sets (lutvq_code2x8_packed_bytes >= prob_m*prob_k/4).
+ * same code bytes, ordered [k-slice of 64 code bytes][32-row set][8-row tile][lane] x 16 B = each lane's register image
+ * (rvv-lut-vq_b200/csrc/lut_layout.h), so that a warp's load is 512 contiguous bytes and a worker's share ONE contiguous range;
+ * rows / k-slices are zero-padded to whole sets (lutvq_code2x8_packed_bytes >= prob_m*prob_k/4).
  * lutvq_code2x8_matmat_packed == lutvq_code2x8_matmat_ex on the packed image (bit-identical results; the reference-layout
- * entry points run this very re-layout into the workspace's staging area on every call). */
+ * entry points read [prob_m][prob_k/8][2] directly: a warp's 128-bit load then touches 8 rows x 64 B). */
 size_t lutvq_code2x8_packed_bytes(int prob_m, int prob_k);
 int lutvq_code2x8_prepack(const void* codes, void* packed, int prob_m, int prob_k, void* stream);
 int lutvq_code2x8_matmat_packed(const void* x, const void* packed, const void* codebooks, const void* scales,
