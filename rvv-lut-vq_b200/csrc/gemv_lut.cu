@@ -359,6 +359,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         if (lane == 0) {
             const uint8_t* base = PB.codes + (size_t)begin * 2048;
             const int n = end - begin;
+#if LUTVQ_DBG
+            if (!(p.flags & 0x800u))                               // DEBUG 0x800: no L2 prefetch of the share
+#endif
             for (int c = warp * 4 + PF * NW; c < n; c += NW * 4)
                 l2_prefetch_bulk_pol(base + (size_t)c * 2048, (uint32_t)min(4, n - c) * 2048u, pol_stream);
         }
