@@ -318,6 +318,32 @@ int lutvq_tmac_preprocessor_int8(int K, const void* B, void* lut_scales, void* l
 int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, const void* qlut, const void* scales,
                               const void* lut_scales, const void* lut_biases, void* C, void* stream);
 
+/* ---- PQ4 fast-scan distance accumulation (csrc/pq4.cu) ----
+ * Replaces, with the same packed layouts (images packed by either side are interchangeable) and bit-identical uint16 results:
+ *   pq4_pack_codes            benchmark/kernel/faiss-simd/pq4_fast_scan.cpp:45-91    codes [ntotal][(M+1)/2] -> blocks [nb * nsq / 2]
+ *   pq4_pack_codes_range      pq4_fast_scan.cpp:93-137   ORs vectors [i0, i1) into blocks (zero-initialised by the caller)
+ *   pq4_pack_LUT              pq4_fast_scan.cpp:253-264  src [nq][nsq][16] -> dest [(sq/2 * nq + q) * 32 + 16 * (sq & 1)]
+ *   pq4_pack_LUT_qbs(_q_map)  pq4_fast_scan.cpp:266-322  one pq4_pack_LUT per base-16 digit of qbs; q_map: DEVICE int array or NULL
+ *   pq4_accumulate_loop       pq4_fast_scan_search_1.cpp:30-222 with a store-to-memory result handler:
+ *                             accu[q * ld + j] = sum_sq LUT[q][sq][code(j, sq)] modulo 2^16; scale >= 0 = NormTableScaler(scale):
+ *                             the last two sub-quantizers' values are multiplied by scale (uint16 wrap-around); scale < 0: none
+ *   pq4_accumulate_loop_qbs   pq4_fast_scan.h:170-188 (declared there, defined in a file the reference does not carry): bbs = 32,
+ *                             query blocks of 1..4 (the digits of qbs), LUT packed by pq4_pack_LUT_qbs, rows in digit order
+ * All pointers are device memory.  Errors mirror the reference's FAISS_THROW_IF_NOT checks (32-byte aligned codes / LUT,
+ * bbs % 32, nb % bbs, nsq % 2); the reference instantiates (nq, bbs/32) in {1x1..1x5, 2x1, 2x2, 3x1, 4x1} only, this
+ * library takes every bbs with nq = 1..4.  pq4_get/set_packed_element and CodePackerPQ4 (single-element host accessors)
+ * are mirrored in the Python host layer (pq4.py).  pq4_preferred_qbs is declared by the reference but defined nowhere in
+ * it: not provided. */
+int lutvq_pq4_pack_codes(const void* codes, size_t ntotal, size_t M, size_t nb, size_t bbs, size_t nsq, void* blocks, void* stream);
+int lutvq_pq4_pack_codes_range(const void* codes, size_t M, size_t i0, size_t i1, size_t bbs, size_t nsq, void* blocks, void* stream);
+int lutvq_pq4_pack_LUT(int nq, int nsq, const void* src, void* dest, void* stream);
+int lutvq_pq4_qbs_to_nq(int qbs);
+int lutvq_pq4_pack_LUT_qbs(int qbs, int nsq, const void* src, const int* q_map, void* dest, void* stream);
+int lutvq_pq4_accumulate_loop(int nq, size_t nb, int bbs, int nsq, const void* codes, const void* LUT, void* accu, size_t ld,
+                              int scale, void* stream);
+int lutvq_pq4_accumulate_loop_qbs(int qbs, size_t nb, int nsq, const void* codes, const void* LUT, void* accu, size_t ld, int scale,
+                                  void* stream);
+
 /* ---- decode glue (fp16, batch 1): the non-GEMV steps of a Llama-shaped decode step, so a whole token is one chain of
  * launches of this library inside a CUDA graph.  Not reference entry points (the reference takes these from HF
  * transformers, benchmark/llm/generate_benchmark.py) and not LUT-VQ work; they exist for the decode tok/s metric.

@@ -33,7 +33,7 @@ def build(force: bool = False) -> str:
     """Compile the C oracle (and, when /root/reference exists, oracle/_ref). Idempotent."""
     if force or not os.path.exists(_LIB_PATH) or any(
         os.path.exists(os.path.join(_HERE, s)) and os.path.getmtime(os.path.join(_HERE, s)) > os.path.getmtime(_LIB_PATH)
-        for s in ("lutvq_oracle.c", "tmac_oracle.c")
+        for s in ("lutvq_oracle.c", "tmac_oracle.c", "pq4_oracle.c")
     ):
         subprocess.check_call(["make", "-C", _HERE, "-B", "all"], stdout=subprocess.DEVNULL)
     if os.path.isdir("/root/reference") and os.path.exists(os.path.join(_HERE, "ref_wrap_tmac.cc")):
@@ -72,6 +72,15 @@ def lib() -> ctypes.CDLL:
         for name, args in sigs.items():
             fn = getattr(_lib, name)
             fn.argtypes, fn.restype = args, None
+        Z = ctypes.c_size_t
+        for name, args in {
+            "orc_pq4_pack_codes": [P, Z, Z, Z, Z, Z, P], "orc_pq4_pack_codes_range": [P, Z, Z, Z, Z, Z, P],
+            "orc_pq4_get_packed_element": [P, Z, Z, Z, Z], "orc_pq4_set_packed_element": [P, I, Z, Z, Z, Z],
+            "orc_pq4_pack_LUT": [I, I, P, P], "orc_pq4_pack_LUT_qbs": [I, I, P, P], "orc_pq4_pack_LUT_qbs_q_map": [I, I, P, P, P],
+            "orc_pq4_accumulate_loop": [I, Z, I, I, P, P, P, I],
+        }.items():
+            fn = getattr(_lib, name)
+            fn.argtypes, fn.restype = args, ctypes.c_int
     return _lib
 
 
@@ -401,9 +410,101 @@ def c_tmac_qgemm_lut_int8(M: int, K: int, bits: int, bm: int, A_u8, qlut_i8, sca
     return C
 
 
+# --------------------------------------------------------------------------------------------
+# PQ4 fast-scan (pq4_oracle.c; reference benchmark/kernel/faiss-simd/pq4_fast_scan{,_search_1}.cpp)
+# --------------------------------------------------------------------------------------------
+def aligned_u8(n: int, align: int = 32) -> np.ndarray:
+    """zeroed uint8[n] whose data pointer is `align`-byte aligned (the reference checks is_aligned_pointer)"""
+    raw = np.zeros(n + align, dtype=np.uint8)
+    off = (-raw.ctypes.data) % align
+    return raw[off:off + n]
+
+
+def pq4_nsq(M: int) -> int:
+    return (M + 1) // 2 * 2
+
+
+def c_pq4_pack_codes(codes_u8: np.ndarray, M: int, nb: int, bbs: int) -> np.ndarray:
+    """pq4_fast_scan.cpp:45-91.  codes [ntotal, (M+1)//2] uint8 (two 4-bit codes per byte) -> blocks uint8[nb * nsq / 2], aligned"""
+    codes_u8 = np.ascontiguousarray(codes_u8, dtype=np.uint8)
+    nsq = pq4_nsq(M)
+    blocks = aligned_u8(nb * nsq // 2)
+    if lib().orc_pq4_pack_codes(_p(codes_u8), codes_u8.shape[0], M, nb, bbs, nsq, _p(blocks)):
+        raise ValueError("pq4_pack_codes: bbs % 32, nb % bbs or nsq % 2 (pq4_fast_scan.cpp:53-55)")
+    return blocks
+
+
+def c_pq4_pack_codes_range(codes_u8: np.ndarray, M: int, i0: int, i1: int, bbs: int, blocks: np.ndarray) -> np.ndarray:
+    """pq4_fast_scan.cpp:93-137: ORs vectors [i0, i1) into `blocks` (modified in place and returned)"""
+    lib().orc_pq4_pack_codes_range(_p(np.ascontiguousarray(codes_u8, dtype=np.uint8)), M, i0, i1, bbs, pq4_nsq(M), _p(blocks))
+    return blocks
+
+
+def c_pq4_get_packed_element(blocks: np.ndarray, bbs: int, nsq: int, vector_id: int, sq: int) -> int:
+    return lib().orc_pq4_get_packed_element(_p(blocks), bbs, nsq, vector_id, sq)
+
+
+def c_pq4_set_packed_element(blocks: np.ndarray, code: int, bbs: int, nsq: int, vector_id: int, sq: int) -> None:
+    lib().orc_pq4_set_packed_element(_p(blocks), code, bbs, nsq, vector_id, sq)
+
+
+def c_pq4_pack_LUT(lut_u8: np.ndarray) -> np.ndarray:
+    """pq4_fast_scan.cpp:253-264.  lut [nq, nsq, 16] uint8 -> packed uint8[nq * nsq * 16], aligned"""
+    nq, nsq, _ = lut_u8.shape
+    dest = aligned_u8(nq * nsq * 16)
+    lib().orc_pq4_pack_LUT(nq, nsq, _p(np.ascontiguousarray(lut_u8, dtype=np.uint8)), _p(dest))
+    return dest
+
+
+def c_pq4_pack_LUT_qbs(qbs: int, lut_u8: np.ndarray, q_map: Optional[np.ndarray] = None) -> np.ndarray:
+    """pq4_fast_scan.cpp:266-281 / 305-322"""
+    nq, nsq, _ = lut_u8.shape
+    n_out = sum((qbs >> s) & 15 for s in range(0, 32, 4))
+    dest = aligned_u8(n_out * nsq * 16)
+    src = np.ascontiguousarray(lut_u8, dtype=np.uint8)
+    if q_map is None:
+        got = lib().orc_pq4_pack_LUT_qbs(qbs, nsq, _p(src), _p(dest))
+    else:
+        got = lib().orc_pq4_pack_LUT_qbs_q_map(qbs, nsq, _p(src), _p(np.ascontiguousarray(q_map, dtype=np.int32)), _p(dest))
+    if got < 0:
+        raise ValueError("pq4_pack_LUT_qbs: nsq % 2 (pq4_fast_scan.cpp:267)")
+    assert got == n_out
+    return dest
+
+
+def c_pq4_accumulate_loop(nq: int, nb: int, bbs: int, nsq: int, blocks: np.ndarray, lut_packed: np.ndarray, scale: int = -1) -> np.ndarray:
+    """pq4_fast_scan_search_1.cpp:137-222 with a store-to-memory handler -> uint16 [nq, nb]; scale < 0 = no NormTableScaler"""
+    accu = np.zeros((nq, nb), dtype=np.uint16)
+    if lib().orc_pq4_accumulate_loop(nq, nb, bbs, nsq, _p(blocks), _p(lut_packed), _p(accu), scale):
+        raise ValueError(f"pq4_accumulate_loop: alignment / bbs / nb, or nq={nq} bbs={bbs} not instantiated (pq4_fast_scan_search_1.cpp:147-168)")
+    return accu
+
+
+def np_pq4_distances(codes_u8: np.ndarray, lut_u8: np.ndarray, M: int, scale: int = -1) -> np.ndarray:
+    """what the packed pipeline must equal, from the UNPACKED codes: dis[q, j] = sum_sq lut[q, sq, code[j, sq]] mod 2**16,
+    the last two sub-quantizers times `scale` when a scaler is given"""
+    nq, nsq, _ = lut_u8.shape
+    n = codes_u8.shape[0]
+    nib = np.zeros((n, nsq), dtype=np.int64)
+    nib[:, 0:2 * codes_u8.shape[1]:2] = codes_u8 & 15
+    nib[:, 1:2 * codes_u8.shape[1]:2] = codes_u8 >> 4
+    if M < nsq:
+        nib[:, M:] = nib[:, M:]          # an odd M keeps whatever the high nibble of the last byte holds (the reference does too)
+    w = np.ones(nsq, dtype=np.int64)
+    if scale >= 0:
+        w[nsq - 2:] = scale
+    vals = lut_u8.astype(np.int64)[:, np.arange(nsq)[None, :], nib]          # [nq, n, nsq]
+    return ((vals * w).sum(-1) & 0xFFFF).astype(np.uint16)
+
+
 # ---- the reference's own compiled kernels (oracle/_ref, built by `make -C oracle ref` where /root/reference exists) ----
 def ref_tmac():
     path = os.path.join(_HERE, "_ref", "libtmac_ref.so")
+    return ctypes.CDLL(path) if os.path.exists(path) else None
+
+
+def ref_pq4():
+    path = os.path.join(_HERE, "_ref", "libpq4_ref.so")
     return ctypes.CDLL(path) if os.path.exists(path) else None
 
 

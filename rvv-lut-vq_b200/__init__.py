@@ -12,7 +12,7 @@ __all__ = ["_lib", "LutvqError", "build", "lib", "get_int_dtype", "pack_int_data
 
 def __getattr__(name):
     # torch-facing modules are imported lazily so that ABI-only users (ctypes) do not pay for them
-    if name in ("ops", "linear", "synth", "sharded", "decode", "hf_loader", "traffic", "kernel_selector", "torch_ops"):
+    if name in ("ops", "linear", "synth", "sharded", "decode", "hf_loader", "traffic", "kernel_selector", "torch_ops", "pq4"):
         import importlib
         return importlib.import_module(f"{__name__}.{name}")
     if name == "QuantizedLinear":

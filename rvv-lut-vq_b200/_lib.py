@@ -52,6 +52,13 @@ SIGNATURES = {
     "lutvq_partial_max_g4_int8_k8": (I, [P, P, P]),
     "lutvq_partial_max_reset": (I, [P, P]),
     "lutvq_lut_ctor_g4_int8": (I, [I, P, P, P, P, P]),
+    "lutvq_pq4_pack_codes": (I, [P, SZ, SZ, SZ, SZ, SZ, P, P]),
+    "lutvq_pq4_pack_codes_range": (I, [P, SZ, SZ, SZ, SZ, SZ, P, P]),
+    "lutvq_pq4_pack_LUT": (I, [I, I, P, P, P]),
+    "lutvq_pq4_qbs_to_nq": (I, [I]),
+    "lutvq_pq4_pack_LUT_qbs": (I, [I, I, P, P, P, P]),
+    "lutvq_pq4_accumulate_loop": (I, [I, SZ, I, I, P, P, P, SZ, I, P]),
+    "lutvq_pq4_accumulate_loop_qbs": (I, [I, SZ, I, P, P, P, SZ, I, P]),
     "lutvq_tmac_preprocessor_int8": (I, [I, P, P, P, P, P]),
     "lutvq_tmac_qgemm_lut_int8": (I, [I, I, I, I, P, P, P, P, P, P, P]),
     "lutvq_codeKx8_workspace_bytes": (SZ, [I, I, I]),

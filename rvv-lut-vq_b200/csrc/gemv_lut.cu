@@ -279,9 +279,16 @@ __device__ __forceinline__ void worker_range(const GemvParams& p, int w, int W, 
     end   = (int)((T * (w + 1)) / W);
 }
 
-template <int DT, bool PACKED, int NW, int PF, int PA, int MINB>
+// NCB = codebooks per group of 8 inputs (AQLM Kx8: 1, 2, 4 or 8).  A k-slice is 64 code bytes of every row whatever NCB is
+// (= 64 / NCB groups); only the LUT build knows which (group, codebook) a byte position means -- the gather, the split-k
+// protocol and the epilogue are format-blind.
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB, int NCB = 2>
 __global__ void __launch_bounds__(NW * 32, MINB)
 lut_gemv_2x8_kernel(const GemvParams p) {
+    static_assert(NCB == 1 || NCB == 2 || NCB == 4 || NCB == 8, "codebooks per group");
+    static_assert(!PACKED || NCB == 2, "the packed code image is built for 2x8");
+    constexpr int kSliceGroups = kSliceTables / NCB;                  // groups of 8 activations per k-slice
+    constexpr int kSliceXBytes = kSliceGroups * 16;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t lut_base = smem_u32(smem_raw);
     const GemvProblem& PB = p.prob[p.n_prob > 1 ? (int)p.tab_prob[blockIdx.x] : 0];       // indexed constant-bank loads
@@ -299,7 +306,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     int begin, end;
     if (p.has_table) { begin = p.tab_begin[blockIdx.x]; end = p.tab_end[blockIdx.x]; }          // two constant-bank loads
     else worker_range(p, blockIdx.x, W, begin, end);
-    const size_t row_bytes = (size_t)p.G * 2;
+    const size_t row_bytes = (size_t)p.G * NCB;
     const int last_row = PB.O - 1;
 
     // ---------------- streaming-side lane constants ----------------
@@ -388,25 +395,25 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         }
     }
     if (warp == NW - 1) {
-        if (p.x != nullptr && lane < 4 && (size_t)ks * 512 + lane * 128 < (size_t)p.G * 16)
+        if (p.x != nullptr && lane < kSliceXBytes / 128 && (size_t)ks * kSliceXBytes + lane * 128 < (size_t)p.G * 16)
         {
-            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * 512 + lane * 128);
-            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * 512 + lane * 128);
+            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * kSliceXBytes + lane * 128);
+            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * kSliceXBytes + lane * 128);
         }
     }
     TL_STAMP(10);
     const int r = lane >> 2, q = lane & 3;
     constexpr int MB_PER_WARP = 16 / NW;                                   // 16 idx blocks of 16 per codebook
-    uint32_t afrag[MB_PER_WARP][2][2];
+    uint32_t afrag[MB_PER_WARP][NCB][2];
     {
-        const uint32_t* cb32 = static_cast<const uint32_t*>(PB.codebook);  // [2][256][4] words (2 values each)
+        const uint32_t* cb32 = static_cast<const uint32_t*>(PB.codebook);  // [NCB][256][4] words (2 values each)
         const uint64_t pol_keep = l2_policy_evict_last();
         // A fragments for this warp's idx blocks: rows 16m + r and 16m + r + 8, k = 2q, 2q+1
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi) {
             const int m = warp * MB_PER_WARP + mi;
             #pragma unroll
-            for (int n = 0; n < 2; ++n) {
+            for (int n = 0; n < NCB; ++n) {
                 afrag[mi][n][0] = ldg_u32_pol(cb32 + (n * 256 + 16 * m + r) * 4 + q, pol_keep);
                 afrag[mi][n][1] = ldg_u32_pol(cb32 + (n * 256 + 16 * m + r + 8) * 4 + q, pol_keep);
             }
@@ -419,7 +426,7 @@ lut_gemv_2x8_kernel(const GemvParams p) {
         #pragma unroll
         for (int mi = 0; mi < MB_PER_WARP; ++mi)
             #pragma unroll
-            for (int n = 0; n < 2; ++n) m = max(m, max(absmax_halves(afrag[mi][n][0]), absmax_halves(afrag[mi][n][1])));
+            for (int n = 0; n < NCB; ++n) m = max(m, max(absmax_halves(afrag[mi][n][0]), absmax_halves(afrag[mi][n][1])));
         m = __reduce_max_sync(0xffffffffu, m);
         if (lane == 0) cmax_red[warp] = m;
     }
@@ -436,7 +443,6 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     // The slice's 32 activation groups (512 B = 4 lines) are requested ONCE per CTA and shared through shared memory: every
     // CTA of a slice reads the same few lines at the same moment, and when all 8 warps fetched their B fragments themselves
     // (4 scattered 4-byte loads per lane) each hot line took 16 requests per CTA at its L2 slice.
-    constexpr int kSliceGroups = kSliceTables / 2;                    // 32 groups of 8 activations per k-slice
     __shared__ __align__(16) uint4 xs[kSliceGroups];
     auto load_x_slice = [&](int ks_) {
         if (threadIdx.x < kSliceGroups) {
@@ -521,37 +527,41 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     while (pos < end) {
         // ---------------- K1: build this worker's 64 KiB LUT for slice ks ----------------
         {
-            // B fragments: column r of N-tile j is local group build_group_of_col(j, r); k = 2q, 2q+1
-            uint32_t bfrag[4];
+            // B fragments: column r of N-tile t is local group build_group<NCB>(t, r); k = 2q, 2q+1
+            constexpr int NT = 8 / NCB;                                // N-tiles of 8 groups per slice
+            uint32_t bfrag[NT];
             #pragma unroll
-            for (int j = 0; j < 4; ++j) bfrag[j] = reinterpret_cast<const uint32_t*>(xs)[build_group_of_col(j, r) * 4 + q];
-            {   // the warp's 32 lanes x 4 words are exactly the slice's 256 activations
-                uint32_t m = max(max(absmax_halves(bfrag[0]), absmax_halves(bfrag[1])), max(absmax_halves(bfrag[2]), absmax_halves(bfrag[3])));
+            for (int t = 0; t < NT; ++t) bfrag[t] = reinterpret_cast<const uint32_t*>(xs)[build_group<NCB>(t, r) * 4 + q];
+            {   // the warp's 32 lanes x NT words are exactly the slice's activations
+                uint32_t m = 0;
+                #pragma unroll
+                for (int t = 0; t < NT; ++t) m = max(m, absmax_halves(bfrag[t]));
                 m = __reduce_max_sync(0xffffffffu, m);
                 fx_scales(cmax8 * abs_half_bits_to_float<DT>(m), fx_scale, fx_inv);
             }
             #pragma unroll
             for (int mi = 0; mi < MB_PER_WARP; ++mi) {
                 const int m = warp * MB_PER_WARP + mi;
-                float c[2][4][4];
+                float c[8][4];                                         // MMA i = n * NT + t: codebook n x N-tile t
                 #pragma unroll
-                for (int n = 0; n < 2; ++n)
+                for (int n = 0; n < NCB; ++n)
                     #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        c[n][j][0] = c[n][j][1] = c[n][j][2] = c[n][j][3] = 0.f;
-                        MmaK8<DT>::run(c[n][j], afrag[mi][n][0], afrag[mi][n][1], bfrag[j]);
+                    for (int t = 0; t < NT; ++t) {
+                        float (&ci)[4] = c[n * NT + t];
+                        ci[0] = ci[1] = ci[2] = ci[3] = 0.f;
+                        MmaK8<DT>::run(ci, afrag[mi][n][0], afrag[mi][n][1], bfrag[t]);
                     }
                 #pragma unroll
-                for (int n = 0; n < 2; ++n)
+                for (int i = 0; i < 8; ++i)
                     #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            float v = c[n][j][i];
-                            if (round16) v = __half2float(__float2half_rn(v));
-                            c[n][j][i] = fmaf(v, fx_scale, kFxMagic);      // float bits = 0x4B400000 + round(v * 2^e)
-                        }
-                // c[n][j][2h+u]: idx = 16m + r + 8h, table bytes beta = 2u+n of (chunk q, word w_j)
+                    for (int k = 0; k < 4; ++k) {
+                        float v = c[i][k];
+                        if (round16) v = __half2float(__float2half_rn(v));
+                        c[i][k] = fmaf(v, fx_scale, kFxMagic);             // float bits = 0x4B400000 + round(v * 2^e)
+                    }
+                // The 16-byte store (idx = 16m + r + 8h, chunk q, word w_j) holds byte positions 16q + 4w_j + beta, beta = 0..3;
+                // build_val<NCB>(j, beta, h) names the MMA output that belongs there (lut_layout.h).
+                auto val = [&](int j, int beta, int h) -> float { return c[build_val_mma<NCB>(j, beta)][2 * h + build_val_col<NCB>(j, beta)]; };
                 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                     const int idx = 16 * m + r + 8 * h;
@@ -559,14 +569,14 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                     for (int jp = 0; jp < 2; ++jp) {
                         const int j0 = 2 * jp, j1 = 2 * jp + 1;
                         // first store: odd lanes take tile j1, even lanes tile j0 (8 distinct 16-byte columns per phase)
-                        float f0 = odd ? c[0][j1][2 * h] : c[0][j0][2 * h];
-                        float f1 = odd ? c[1][j1][2 * h] : c[1][j0][2 * h];
-                        float f2 = odd ? c[0][j1][2 * h + 1] : c[0][j0][2 * h + 1];
-                        float f3 = odd ? c[1][j1][2 * h + 1] : c[1][j0][2 * h + 1];
-                        float s0 = odd ? c[0][j0][2 * h] : c[0][j1][2 * h];
-                        float s1 = odd ? c[1][j0][2 * h] : c[1][j1][2 * h];
-                        float s2 = odd ? c[0][j0][2 * h + 1] : c[0][j1][2 * h + 1];
-                        float s3 = odd ? c[1][j0][2 * h + 1] : c[1][j1][2 * h + 1];
+                        float f0 = odd ? val(j1, 0, h) : val(j0, 0, h);
+                        float f1 = odd ? val(j1, 1, h) : val(j0, 1, h);
+                        float f2 = odd ? val(j1, 2, h) : val(j0, 2, h);
+                        float f3 = odd ? val(j1, 3, h) : val(j0, 3, h);
+                        float s0 = odd ? val(j0, 0, h) : val(j1, 0, h);
+                        float s1 = odd ? val(j0, 1, h) : val(j1, 1, h);
+                        float s2 = odd ? val(j0, 2, h) : val(j1, 2, h);
+                        float s3 = odd ? val(j0, 3, h) : val(j1, 3, h);
                         const uint32_t first  = lut_base + build_store_offset(idx, odd ? j1 : j0, q);
                         const uint32_t second = lut_base + build_store_offset(idx, odd ? j0 : j1, q);
                         sts_v4(first, f0, f1, f2, f3);
@@ -727,9 +737,9 @@ void gemv_set_timeline(void* buf) { g_timeline = static_cast<unsigned long long*
 struct GemvPlan { int n_k, n_sets, W, aligned, q, r, max_range; };
 
 // One worker (CTA) per SM.  Cost model in units of one 32-row set of gather work; a LUT build costs about 10.
-static GemvPlan plan_gemv(int O, int G, int sm_count) {
+static GemvPlan plan_gemv(int O, int G, int sm_count, int ncb = 2) {
     GemvPlan pl;
-    pl.n_k = ceil_div(G * 2, kSliceTables);
+    pl.n_k = ceil_div(G * ncb, kSliceTables);
     pl.n_sets = ceil_div(O, kSetRows);
     const long long T = (long long)pl.n_k * pl.n_sets;
     pl.W = (int)(T < sm_count ? T : sm_count);
@@ -774,9 +784,9 @@ int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStrea
     return LUTVQ_OK;
 }
 
-template <int DT, bool PACKED, int NW, int PF, int PA, int MINB = 2>
+template <int DT, bool PACKED, int NW, int PF, int PA, int MINB = 2, int NCB = 2>
 static int launch_variant(const GemvParams& p, int grid, size_t smem, cudaStream_t stream, bool pdl) {
-    auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF, PA, MINB>;
+    auto kern = lut_gemv_2x8_kernel<DT, PACKED, NW, PF, PA, MINB, NCB>;
     static thread_local int attr_device = -1;
     int dev = 0;
     LUTVQ_CUDA_OK(cudaGetDevice(&dev));
@@ -827,6 +837,15 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
     return fail(LUTVQ_EINVAL, "no kernel variant for tuning nw=%d pf=%d pa=%d", t.nw, t.pf, t.pa);
 }
 
+// AQLM Kx8 with K = NCB != 2 (reference layout only): the 2-CTA / 2-deep-ring variant, whatever the tuning knobs say
+template <int DT>
+static int launch_kx8(const GemvParams& p, int ncb, int grid, size_t smem, cudaStream_t stream, bool pdl) {
+    if (ncb == 1) return launch_variant<DT, false, 8, 2, 2, 2, 1>(p, grid, smem, stream, pdl);
+    if (ncb == 4) return launch_variant<DT, false, 8, 2, 2, 2, 4>(p, grid, smem, stream, pdl);
+    if (ncb == 8) return launch_variant<DT, false, 8, 2, 2, 1, 8>(p, grid, smem, stream, pdl);
+    return fail(LUTVQ_EUNSUPPORTED, "the fused LUT-GEMV takes 1, 2, 4 or 8 codebooks per group, got %d", ncb);
+}
+
 // worker w of a problem planned as `pl` -> its item range [begin, end) over (slice, set) pairs, slice-major.
 // Aligned plan: slices < r have q+1 workers, the others q; a slice's n_sets sets are dealt base (+1 for the first rem).
 static void host_worker_range(const GemvPlan& pl, int w, int& begin, int& end) {
@@ -858,7 +877,7 @@ size_t gemv_group_workspace_bytes(int n, const int* O) {
 // its share of the SMs.  Validation is done by the caller (api.cu / shard.cu).
 // x_gate != null (fp16): the activations are silu(x_gate) * x, evaluated in the kernel's x loads.
 static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void* x, const void* x_gate, int I, int dtype, unsigned flags,
-                            void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll = nullptr) {
+                            void* ws, size_t ws_bytes, cudaStream_t stream, const GemvPush* push, const GemvLL* ll = nullptr, int ncb = 2) {
     DeviceInfo di;
     if (int rc = get_device_info(&di)) return rc;
     LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
@@ -892,7 +911,7 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
         if (share < 1) share = 1;
         if (share > left - (n - 1 - i)) share = left - (n - 1 - i);
         left -= share;
-        GemvPlan pl = plan_gemv(items[i].O, G, share);
+        GemvPlan pl = plan_gemv(items[i].O, G, share, ncb);
         if (pl.n_k > 255) return fail(LUTVQ_EUNSUPPORTED, "prob_k=%d needs %d k-slices; the split-k arrival counter holds 255 (prob_k <= 65280)", I, pl.n_k);
         p.n_k = pl.n_k;
         GemvProblem& pb = p.prob[i];
@@ -928,6 +947,12 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
     p.flags = pdl ? flags : (flags & ~LUTVQ_FLAG_X_READY);        // the X_READY overlap only exists under PDL
     p.tl = (g_timeline && W_total <= 256) ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
     const size_t smem = kSliceBytes;
+    if (ncb != 2) {
+        LUTVQ_REQUIRE(!packed && n == 1, "Kx8 formats other than 2x8 run on reference-layout codes, one linear per launch");
+        if (dtype == LUTVQ_F16)  return launch_kx8<LUTVQ_F16>(p, ncb, W_total, smem, stream, pdl);
+        if (dtype == LUTVQ_BF16) return launch_kx8<LUTVQ_BF16>(p, ncb, W_total, smem, stream, pdl);
+        return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
+    }
     if (dtype == LUTVQ_F16)  return packed ? launch_tuned<LUTVQ_F16, true>(p, W_total, smem, stream, pdl)  : launch_tuned<LUTVQ_F16, false>(p, W_total, smem, stream, pdl);
     if (dtype == LUTVQ_BF16) return packed ? launch_tuned<LUTVQ_BF16, true>(p, W_total, smem, stream, pdl) : launch_tuned<LUTVQ_BF16, false>(p, W_total, smem, stream, pdl);
     return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
@@ -953,6 +978,15 @@ int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* c
                         cudaStream_t stream) {
     const GemvItem it{codes, codebook, y, scales, bias, O};
     return gemv_launch_impl(1, &it, 0, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr);
+}
+
+// One GEMV of an AQLM Kx8 layer (K = ncb codebooks of 256 entries per group of 8 inputs) on reference-layout codes
+// int8 [O][I/8][ncb]; rows must be whole 16-byte chunks ((I/8) * ncb % 16 == 0).  Same kernel as 2x8, other LUT build.
+int gemv_kx8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
+                        const void* bias, int O, int I, int ncb, int dtype, unsigned flags, void* ws, size_t ws_bytes,
+                        cudaStream_t stream) {
+    const GemvItem it{codes, codebook, y, scales, bias, O};
+    return gemv_launch_impl(1, &it, 0, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr, nullptr, ncb);
 }
 
 size_t gemv_packed_workspace_bytes(int O, int G) { return gemv_workspace_bytes(O, G); }

@@ -57,6 +57,27 @@ LUTVQ_HD uint32_t stream_imm(int c)                       { return (uint32_t)((c
 LUTVQ_HD int      build_word_of_tile(int j)               { return 2 * (j & 1) + (j >> 1); }   // w_j
 // local group (0..31) held by column `col` (0..7) of N-tile j, for a format with 2 code bytes per group
 LUTVQ_HD int      build_group_of_col(int j, int col)      { return 8 * (col >> 1) + 2 * build_word_of_tile(j) + (col & 1); }
+// ---- build side, any number of codebooks per group NCB in {1, 2, 4, 8} (AQLM Kx8) ----
+// Byte position p of a slice means (group p / NCB, codebook p % NCB).  The 8 MMAs of an idx block are i = n * NT + t
+// (codebook n, N-tile t of 8 groups, NT = 8 / NCB).  The 16-byte store (chunk a = q, word w_j) covers positions
+// 16q + 4w_j + beta; the thread owns MMA columns 2q + u.  Which x-group sits in column `col` of tile t, and which MMA
+// output is byte beta of store j:
+//   NCB = 1: t = 2j + n', group 16(col>>1) + 4w_j + 2n' + (col&1);  beta = 2n' + u   -> MMA 2j + (beta>>1),  u = beta & 1
+//   NCB = 2: t = j,       group  8(col>>1) + 2w_j + (col&1);        beta = 2u + n    -> MMA 4(beta&1) + j,   u = beta >> 1
+//   NCB = 4: t = k, j = 2k + u, group 4(col>>1) + w_{2k + (col&1)}; beta = n         -> MMA 2beta + (j>>1),  u = j & 1
+//   NCB = 8: t = 0,       group col;                  codebook 4(j>>1) + beta        -> MMA 4(j>>1) + beta,  u = j & 1
+template <int NCB> LUTVQ_HD int build_group(int t, int col) {
+    return NCB == 1 ? 16 * (col >> 1) + 4 * build_word_of_tile(t >> 1) + 2 * (t & 1) + (col & 1)
+         : NCB == 2 ? build_group_of_col(t, col)
+         : NCB == 4 ? 4 * (col >> 1) + build_word_of_tile(2 * t + (col & 1))
+                    : col;
+}
+template <int NCB> LUTVQ_HD int build_val_mma(int j, int beta) {
+    return NCB == 1 ? 2 * j + (beta >> 1) : NCB == 2 ? 4 * (beta & 1) + j : NCB == 4 ? 2 * beta + (j >> 1) : 4 * (j >> 1) + beta;
+}
+template <int NCB> LUTVQ_HD int build_val_col(int j, int beta) {
+    return NCB == 1 ? (beta & 1) : NCB == 2 ? (beta >> 1) : (j & 1);
+}
 LUTVQ_HD uint32_t build_store_offset(int idx, int j, int q){ return (uint32_t)(idx * kIdxStride + (j >> 1) * 128 + 32 * q + (j & 1) * 16); }
 
 }  // namespace lutvq

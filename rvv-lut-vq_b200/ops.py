@@ -319,9 +319,15 @@ def code2x8_matmat_group_packed(input: torch.Tensor, packed: List[torch.Tensor],
     return ys
 
 
+def _kx8_fused(in_features: int, N: int) -> bool:
+    """csrc/kx8.cu kx8_fused: the fused LUT-GEMV takes 1 / 2 / 4 / 8 codebooks when a code row is whole 16-byte chunks"""
+    return N in (1, 2, 4, 8) and (in_features // 8 * N) % 16 == 0
+
+
 def codeKx8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
                    bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """codeKx8_matmat / code1x8_matmat (cuda_kernel.cpp:521-684): any number of 256-entry codebooks, groups of 8, fp16."""
+    """codeKx8_matmat / code1x8_matmat (cuda_kernel.cpp:521-684): any number of 256-entry codebooks, groups of 8.
+    N in {1, 2, 4, 8}: the fused LUT-GEMV (fp16 / bf16); other N: the unfused fp32 LUT pair (fp16)."""
     dtype = check_use_bfloat16(input)
     dev = _require_cuda(input, codes, codebooks, scales, bias)
     N = codes.size(-1)
@@ -329,16 +335,21 @@ def codeKx8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Te
     flat = input.reshape(-1, in_features).contiguous()
     y = torch.empty((flat.size(0), out_features), dtype=input.dtype, device=dev)
     need = int(lib().lutvq_codeKx8_workspace_bytes(out_features, in_features, N))
-    ws = torch.empty(need, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
+        if _kx8_fused(in_features, N):
+            ws = workspace(dev, out_features, in_features)          # zero-initialised split-k words, handed back zero by every call
+            if ws.numel() < need:
+                ws = torch.zeros(need, dtype=torch.uint8, device=dev)
+        else:
+            ws = torch.empty(need, dtype=torch.uint8, device=dev)   # scratch LUT of the unfused path: never the shared zeroed words
         check(lib().lutvq_codeKx8_matmat(_ptr(flat), _ptr(codes.contiguous()), _ptr(codebooks.contiguous()), _ptr(_flat_scales(scales)),
                                          _ptr(None if bias is None else bias.contiguous()), _ptr(y), flat.size(0), out_features, in_features, N,
-                                         dtype, _ptr(ws), need, _stream(dev)))
+                                         dtype, _ptr(ws), ws.numel(), _stream(dev)))
     return y.reshape(tuple(input.shape[:-1]) + (out_features,))
 
 
 def codeKx8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:
-    """CodeKx8Dequant (cuda_kernel.cu:392-468): W = ((cb0 + cb1) + cb2) + ... in fp16, then * scales."""
+    """CodeKx8Dequant (cuda_kernel.cu:392-468): W = ((cb0 + cb1) + cb2) + ... in the storage type (fp16 / bf16), then * scales."""
     dtype = check_use_bfloat16(codebooks)
     dev = _require_cuda(codes, codebooks, scales)
     O, G, N = codes.shape

@@ -27,7 +27,47 @@ static uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {   // PTX prmt.b32 d
 
 #define CHECK(cond, ...) do { if (!(cond)) { printf("FAIL %s:%d: ", __FILE__, __LINE__); printf(__VA_ARGS__); printf("\n"); return 1; } } while (0)
 
+// ---- 3b: build side for NCB codebooks per group (AQLM Kx8).  Simulates the kernel's 8 MMAs per idx block symbolically:
+// MMA i = n * NT + t yields, in thread (r, q), element (h, u) = entry of (idx 16m + r + 8h, codebook n, group of column 2q+u of
+// tile t); the store code picks build_val_mma / build_val_col.  Every (position, idx) must be written once, with the entry of
+// (group p / NCB, codebook p % NCB).
+template <int NCB>
+static int check_build() {
+    constexpr int NT = 8 / NCB;
+    std::vector<int> written(kSliceBytes / 4, -1);
+    for (int m = 0; m < 16; ++m)
+        for (int h = 0; h < 2; ++h)
+            for (int jp = 0; jp < 2; ++jp)
+                for (int which = 0; which < 2; ++which)
+                    for (int lane = 0; lane < 32; ++lane) {
+                        const int r = lane >> 2, q = lane & 3, odd = r & 1;
+                        const int j0 = 2 * jp, j1 = 2 * jp + 1;
+                        const int j = (which == 0) ? (odd ? j1 : j0) : (odd ? j0 : j1);
+                        const int idx = 16 * m + r + 8 * h;
+                        const uint32_t off = build_store_offset(idx, j, q);
+                        for (int beta = 0; beta < 4; ++beta) {
+                            const int i = build_val_mma<NCB>(j, beta), u = build_val_col<NCB>(j, beta);
+                            CHECK(i >= 0 && i < 8 && (u == 0 || u == 1), "NCB=%d: bad MMA index", NCB);
+                            const int n = i / NT, t = i % NT;                               // codebook, N-tile of MMA i
+                            const int group = build_group<NCB>(t, 2 * q + u);
+                            CHECK(group >= 0 && group < 64 / NCB, "NCB=%d: group %d out of the slice", NCB, group);
+                            const int p = group * NCB + n;
+                            CHECK(off + 4 * beta == lut_entry_offset(p, idx), "NCB=%d: build offset mismatch (j=%d beta=%d q=%d)", NCB, j, beta, q);
+                            CHECK(written[(off >> 2) + beta] == -1, "NCB=%d: entry written twice", NCB);
+                            written[(off >> 2) + beta] = p * 256 + idx;
+                        }
+                    }
+    for (int p = 0; p < 64; ++p)
+        for (int idx = 0; idx < 256; ++idx)
+            CHECK(written[lut_entry_offset(p, idx) >> 2] == p * 256 + idx, "NCB=%d: entry (p=%d, idx=%d) not built", NCB, p, idx);
+    std::set<int> groups;                                           // the NT tiles cover the slice's groups exactly once
+    for (int t = 0; t < NT; ++t) for (int col = 0; col < 8; ++col) groups.insert(build_group<NCB>(t, col));
+    CHECK((int)groups.size() == 64 / NCB && *groups.rbegin() == 64 / NCB - 1, "NCB=%d: N-tiles do not cover the slice groups", NCB);
+    return 0;
+}
+
 int main() {
+    if (check_build<1>() || check_build<2>() || check_build<4>() || check_build<8>()) return 1;
     // ---- 1 + 2: streaming side ----
     for (int c = 0; c < 4; ++c)
         for (int d = 0; d < 4; ++d) {

@@ -538,6 +538,50 @@ def test_torch_ops_aqlm_registered_and_equal(pkg, ops):
         torch.ops.aqlm.code2x8_matmat(x.cpu(), codes.cpu(), cb.cpu(), sc.cpu(), None)
 
 
+@pytest.mark.parametrize("N,I,O,batch,dtype", [(1, 4096, 4096, 1, "f16"), (1, 11008, 4096, 2, "bf16"), (4, 4096, 4096, 1, "f16"), (4, 4096, 11008, 3, "bf16"),
+                                               (8, 4096, 1024, 1, "f16"), (8, 1024, 515, 2, "bf16"), (4, 32, 33, 1, "f16"), (1, 128, 7, 1, "f16"),
+                                               (3, 512, 96, 2, "f16"), (1, 192, 40, 1, "f16")])
+def test_codeKx8_fused_vs_oracle(pkg, ops, orc, N, I, O, batch, dtype):
+    """N in {1, 4, 8} codebooks through the fused LUT-GEMV (gemv_lut.cu templated on the codebooks per group), Llama-sized and
+    ragged shapes, fp16 and bf16, against the float64 evaluation of the same operands (oracle C), scale + bias in the
+    reference's rounding order.  N = 3 and I = 192 (24 code bytes per row) stay on the unfused path: same bar."""
+    rng = np.random.default_rng(N * 100000 + I + O)
+    dt = 0 if dtype == "f16" else 1
+    tdt = torch.float16 if dt == 0 else torch.bfloat16
+    idx = rng.integers(0, 256, size=(O, I // 8, N))
+    codes = orc.np_pack_int_data(idx, 8)
+    cb = torch.from_numpy(rng.standard_normal((N, 256, 1, 8)).astype(np.float32)).to(tdt)
+    x = torch.from_numpy(rng.standard_normal((batch, I)).astype(np.float32)).to(tdt)
+    sc = torch.from_numpy(rng.standard_normal((O, 1, 1, 1)).astype(np.float32)).to(tdt)
+    bi = torch.from_numpy(rng.standard_normal(O).astype(np.float32)).to(tdt)
+    tb = lambda t: t.contiguous().view(torch.int16).numpy().view(np.uint16)
+    ones = torch.ones((O, 1, 1, 1), dtype=tdt)
+    y = ops.codeKx8_matmat(x.cuda(), cu(codes), cb.cuda(), sc.cuda(), bi.cuda())
+    y_acc = ops.codeKx8_matmat(x.cuda(), cu(codes), cb.cuda(), ones.cuda(), None)     # round(acc) * 1: the accumulator itself
+    assert y.shape == (batch, O)
+    for b in range(batch):
+        acc = orc.c_aqlm_gemv_f64(tb(x[b]), codes, tb(cb), dt)
+        assert rel_err(y_acc[b].double().cpu().numpy(), acc) <= (TOL_GEMV if dt == 0 else 8e-3)      # bf16 outputs carry 8 mantissa bits
+        # the epilogue is round(acc) * scale + bias in the storage type (cuda_kernel.cpp:95-111): bit-exact from OUR rounded accumulator
+        want = orc.c_scale_bias_epilogue(tb(y_acc[b].cpu()).reshape(1, -1), tb(sc.reshape(-1)), tb(bi), dt).reshape(-1)
+        assert np.array_equal(tb(y[b].cpu()), want)
+    if dt == 1 and N in (1, 4, 8):                                   # bf16 dequantize: sequential adds in the storage type
+        W = ops.codeKx8_dequant(cu(codes), cb.cuda(), None)
+        seq = cb[0, torch.from_numpy(idx[:, :, 0]), 0, :]
+        for n in range(1, N):
+            seq = seq + cb[n, torch.from_numpy(idx[:, :, n]), 0, :]
+        assert torch.equal(W.cpu().view(torch.int16), seq.reshape(O, I).contiguous().view(torch.int16))
+
+
+def test_codeKx8_fused_matches_2x8_kernel_bitwise(pkg, ops, orc):
+    """N = 2 through lutvq_codeKx8_matmat is the very kernel of lutvq_code2x8_matmat: identical bits"""
+    from rvv_lut_vq_b200 import synth
+    L = synth.make_layer_np(1024, 320, seed=4, scales="randn", bias=True)
+    a = ops.codeKx8_matmat(cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]), cu(L["bias"]))
+    b = ops.code2x8_matmat(cu(L["x"]), cu(L["codes"]), cu(L["codebooks"]), cu(L["scales"]), cu(L["bias"]))
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
 @pytest.mark.parametrize("fmt", ["1x8", "4x8", "1x16g8", "1x16g16"])
 def test_quantized_linear_other_formats(pkg, ops, orc, fmt):
     """QuantizedLinear dispatches on (num_codebooks, nbits, group) like kernel_selector.py:21-102; gemv op and gemm op agree with float64"""

@@ -220,3 +220,48 @@ def test_aqlm_1x16_dequantize_bit_exact(orc, golden_dir, name):
     if wb:
         y64 = y64 + g["bias"].astype(np.float64)
     assert np.abs(y64 - g["y_dense"]).max() / np.abs(g["y_dense"]).max() < 1e-5
+
+
+# ---- PQ4 fast-scan: pq4_oracle.c vs fixtures produced by the reference's own compiled code ----
+PQ4_CASES = ["q1_b32_m32", "q1_b64_m16", "q1_b96_m8", "q1_b128_m64", "q1_b160_m600", "q2_b32_m7", "q2_b64_m16_s3", "q3_b32_m64_s200", "q4_b32_m20"]
+
+
+@pytest.mark.parametrize("name", PQ4_CASES)
+def test_pq4_oracle_vs_reference_fixture(orc, golden_dir, name):
+    """pq4_fast_scan.cpp:45-137,253-264 and pq4_fast_scan_search_1.cpp:30-222 (gen_golden_pq4.py ran oracle/_ref/libpq4_ref.so)."""
+    g = _load(golden_dir, "pq4_" + name)
+    nq, bbs, M, ntotal, scale = [int(v) for v in g["cfg"]]
+    nsq, nb = orc.pq4_nsq(M), -(-ntotal // bbs) * bbs
+    blocks = orc.c_pq4_pack_codes(g["codes"], M, nb, bbs)
+    assert np.array_equal(blocks, g["blocks"])
+    cut = ntotal // 3 + 1
+    br = orc.aligned_u8(nb * nsq // 2)
+    orc.c_pq4_pack_codes_range(g["codes"][:cut], M, 0, cut, bbs, br)
+    orc.c_pq4_pack_codes_range(g["codes"][cut:], M, cut, ntotal, bbs, br)
+    assert np.array_equal(br, g["blocks"])
+    lp = orc.c_pq4_pack_LUT(g["lut"])
+    assert np.array_equal(lp, g["lut_packed"])
+    accu = orc.c_pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lp, scale)
+    assert np.array_equal(accu, g["accu"])
+    assert np.array_equal(accu[:, :ntotal], orc.np_pq4_distances(g["codes"], g["lut"], M, scale))      # the closed form on unpacked codes
+    got = [orc.c_pq4_get_packed_element(blocks, bbs, nsq, int(v), int(s)) for v, s in zip(g["elem_v"], g["elem_sq"])]
+    assert got == g["elems"].tolist()
+
+
+def test_pq4_oracle_packers_and_errors(orc, golden_dir):
+    g = _load(golden_dir, "pq4_packers")
+    nsq, bbs, qbs = int(g["nsq"][0]), int(g["bbs"][0]), int(g["qbs"][0])
+    assert np.array_equal(orc.c_pq4_pack_LUT_qbs(qbs, g["lut"]), g["lut_qbs"])
+    assert np.array_equal(orc.c_pq4_pack_LUT_qbs(qbs, g["lut"], g["q_map"]), g["lut_qbs_qmap"])
+    block = orc.aligned_u8(g["block"].size)                      # CodePackerPQ4::pack_1 = set_packed_element per nibble
+    for flat, off in zip(g["flat"], g["offsets"]):
+        for i, c in enumerate(flat):
+            orc.c_pq4_set_packed_element(block, int(c) & 15, bbs, nsq, int(off), 2 * i)
+            orc.c_pq4_set_packed_element(block, int(c) >> 4, bbs, nsq, int(off), 2 * i + 1)
+    assert np.array_equal(block, g["block"])
+    with pytest.raises(ValueError):                              # nq = 5 is not instantiated (pq4_fast_scan_search_1.cpp:156-168)
+        orc.c_pq4_accumulate_loop(5, 32, 32, 2, orc.aligned_u8(32), orc.aligned_u8(5 * 32))
+    with pytest.raises(ValueError):                              # nb % bbs
+        orc.c_pq4_accumulate_loop(1, 32, 64, 2, orc.aligned_u8(64), orc.aligned_u8(32))
+    with pytest.raises(ValueError):                              # bbs % 32 (pq4_fast_scan.cpp:53)
+        orc.c_pq4_pack_codes(np.zeros((4, 1), np.uint8), 2, 48, 48)
