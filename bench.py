@@ -242,15 +242,22 @@ def measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak):
     NB = 24
     Ls = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=900 + k, scales="ones") for k in range(NB)]
     rows = []
-    for batch in (16, 32, 64, 128, 256):
+    for batch in (16, 32, 64, 128, 256, 2048):
         x = torch.randn((batch, IN_F), device=dev, dtype=torch.float16)
 
-        def body():
-            for L in Ls:
-                ops.code2x8_matmat_dequant(x, L["codes"], L["codebooks"], L["scales"], None)
-        us = graph_time_us(torch, st, body, 5, NB)
+        def body_of(fn):
+            def body():
+                for L in Ls:
+                    fn(x, L["codes"], L["codebooks"], L["scales"], None)
+            return body
+        # the op a user calls (fused tcgen05 kernel below ops.TWO_STEP_MIN_ROWS rows, dequantize-once + library GEMM above) and both routes
+        us = graph_time_us(torch, st, body_of(ops.code2x8_matmat_dequant), 5, NB)
+        us_fused = graph_time_us(torch, st, body_of(ops.code2x8_matmat_dequant_fused), 5, NB)
+        us_two = graph_time_us(torch, st, body_of(ops.code2x8_matmat_dequant_two_step), 5, NB)
         flops = 2.0 * batch * IN_F * OUT_F
-        rows.append({"batch": batch, "us": round(us, 2), "tflops": round(flops / us / 1e6, 1), "frac_of_bf16_peak": round(flops / us / 1e6 / bf16_peak, 4),
+        rows.append({"batch": batch, "us": round(us, 2), "route": "two_step" if batch >= ops.TWO_STEP_MIN_ROWS else "fused",
+                     "fused_tcgen05_us": round(us_fused, 2), "dequant_plus_library_gemm_us": round(us_two, 2),
+                     "tflops": round(flops / us / 1e6, 1), "frac_of_bf16_peak": round(flops / us / 1e6 / bf16_peak, 4),
                      "code_stream_GBps": round(OUT_F * IN_F / 4 / us / 1e3, 1)})
     W = [torch.empty((OUT_F, IN_F), dtype=torch.float16, device=dev) for _ in range(2)]
     lib = __import__("rvv_lut_vq_b200").lib()

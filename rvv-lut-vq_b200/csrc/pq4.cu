@@ -14,6 +14,8 @@
 // Bound: HBM (nb * nsq / 2 code bytes in, nq * nb * 2 bytes out); ~2.2 issue slots per lookup.
 #include "common.cuh"
 
+#include <type_traits>
+
 namespace lutvq {
 
 constexpr int kPq4Threads = 256;
@@ -154,6 +156,125 @@ __global__ void __launch_bounds__(kPq4Threads) pq4_accumulate_kernel(size_t n_gr
     }
 }
 
+// ---- second kernel: byte-indexed pair tables in shared memory (the fused LUT-GEMV's gather idea applied to PQ4) ----
+// A code BYTE holds the codes of vectors v (low nibble) and v + 16 (high nibble) for one sub-quantizer, so a 256-entry table
+// tab[c] = {T[c & 15], T[c >> 4]} returns BOTH lookups of a byte, already widened to two uint16, with one LDS.32; they are
+// accumulated with one integer add.  That is 1 PRMT (address) + 1 LDS + 1 add per byte = 0.5 ALU-pipe slots per lookup where
+// the PRMT kernel above needs 1.9 (it is bound by the ALU pipe, 64 lanes / clk / SM, at 0.45 of the HBM peak).
+// Layout: entry (sq, c) = NQP words (one per query) at plane(sq / SPP) * 64 KiB + c * 256 + (sq % SPP) * 4 NQP, SPP = 64 / NQP --
+// the bank depends on the TABLE only, never on the code.  2 lanes per group of 32 vectors (lane = 16 groups x {sq 2p half, sq 2p+1 half}); lane (grp, h)
+// walks the pairs in the rotated order p + grp, so at every step the 32 lanes of a warp use 32 different tables = 32 different
+// banks (needs >= 16 pairs): conflict-free for any codes.  A NormTableScaler is baked into the last two tables (value * scale
+// mod 2^16); their adds, and every add once nsq * 255 can reach 2^16, are done per uint16 half.
+constexpr int kPq4BThreads = 256;
+constexpr int kPq4BChunk = 4;                // pairs (16-byte loads) per lane and pipeline stage
+constexpr int kPq4PlaneBytes = 65536;
+
+template <int NQ>
+__global__ void __launch_bounds__(kPq4BThreads) pq4_bytelut_kernel(size_t n_groups, int BB, int nsq, const uint8_t* __restrict__ codes,
+                                                                     const uint8_t* __restrict__ LUT, uint16_t* __restrict__ accu,
+                                                                     size_t ld, int scale) {
+    extern __shared__ __align__(1024) uint8_t tab[];
+    const int npairs = nsq / 2, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // An entry holds the pairs of ALL queries of the call side by side (NQP = 1, 2 or 4 words), so one LDS.32 / .64 / .128
+    // serves every query: the lookups are bound by the LDS instruction rate, not by its bytes.
+    constexpr int NQP = NQ == 3 ? 4 : NQ, SPP = 64 / NQP;            // words per entry; tables (sub-quantizers) per 64 KiB plane
+    const int n_planes = (nsq + SPP - 1) / SPP;
+    // ---- build: warp w fills rows c = 32w .. 32w+31, lane = word of the 256-byte row (conflict-free stores) ----
+    for (int pw = 0; pw < n_planes * 2; ++pw) {
+        const int word = (pw & 1) * 32 + lane, sq = (pw >> 1) * SPP + word / NQP, q = word % NQP;
+        if (sq < nsq && q < NQ) {
+            const uint8_t* T = LUT + ((size_t)(sq / 2 * NQ + q) * 32 + 16 * (sq & 1));
+            const uint32_t k = (scale >= 0 && sq >= nsq - 2) ? (uint32_t)scale : 1u;
+            uint8_t* dst = tab + (size_t)(pw >> 1) * kPq4PlaneBytes + word * 4;
+            for (int c = warp * 32; c < warp * 32 + 32; ++c) {
+                const uint32_t lo = (__ldg(T + (c & 15)) * k) & 0xffffu, hi = (__ldg(T + (c >> 4)) * k) & 0xffffu;
+                *reinterpret_cast<uint32_t*>(dst + c * 256) = lo | (hi << 16);
+            }
+        }
+    }
+    __syncthreads();
+    const int h = lane & 1, grp = lane >> 1;
+    const bool safe_adds = (size_t)nsq * 255 >= 65536;                // per-lane sums can carry between the uint16 halves
+    const size_t pstride = (size_t)BB * 32, gstride = (size_t)gridDim.x * (kPq4BThreads / 2);
+    auto base_of = [&](size_t g_) {
+        const unsigned gi = (unsigned)g_, blk = BB == 1 ? gi : gi / (unsigned)BB, b = gi - blk * (unsigned)BB;
+        return codes + (size_t)blk * ((size_t)BB * 32 * npairs) + b * 32 + h * 16;
+    };
+    auto pair_of = [&](int i) { int p = i + grp; return p >= npairs ? p - npairs : p; };      // rotated walk (npairs >= 16 > grp)
+    auto load_chunk = [&](uint4 (&buf)[kPq4BChunk], const uint8_t* base_, int c_) {
+        #pragma unroll
+        for (int u = 0; u < kPq4BChunk; ++u) {
+            const int i = c_ * kPq4BChunk + u;
+            buf[u] = i < npairs ? __ldg(reinterpret_cast<const uint4*>(base_ + pair_of(i) * pstride)) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+    const int n_chunks = (npairs + kPq4BChunk - 1) / kPq4BChunk;
+    size_t g = (size_t)blockIdx.x * (kPq4BThreads / 2) + (threadIdx.x >> 1);
+    if (g >= n_groups) return;
+    const uint8_t* base = base_of(g);
+    uint4 cur[kPq4BChunk], nxt[kPq4BChunk];
+    load_chunk(cur, base, 0);
+    for (;;) {
+        const size_t g_next = g + gstride;
+        const uint8_t* base_next = g_next < n_groups ? base_of(g_next) : nullptr;
+        uint32_t acc[NQ][16];
+        #pragma unroll
+        for (int q = 0; q < NQ; ++q)
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) acc[q][j] = 0u;
+        for (int c = 0; c < n_chunks; ++c) {
+            if (c + 1 < n_chunks) load_chunk(nxt, base, c + 1);
+            else if (base_next != nullptr) load_chunk(nxt, base_next, 0);
+            #pragma unroll
+            for (int u = 0; u < kPq4BChunk; ++u) {
+                const int i = c * kPq4BChunk + u;
+                if (i < npairs) {                                      // uniform over the CTA
+                    const int sq = 2 * pair_of(i) + h;
+                    const bool safe = safe_adds || (scale >= 0 && sq >= nsq - 2);
+                    const uint32_t w[4] = {cur[u].x, cur[u].y, cur[u].z, cur[u].w};
+                    const uint32_t lm = (uint32_t)((sq % SPP) * 4 * NQP) | ((uint32_t)(sq / SPP) << 16);   // byte 0: table column, byte 2: plane
+                    auto gather = [&](auto safe_c) {
+                        #pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const uint8_t* e = tab + __byte_perm(w[j >> 2], lm, 0x7604u | ((j & 3) << 4));
+                            uint32_t v[NQP];
+                            if (NQP == 1) v[0] = *reinterpret_cast<const uint32_t*>(e);
+                            else if (NQP == 2) { const uint2 t2 = *reinterpret_cast<const uint2*>(e); v[0] = t2.x; v[NQP - 1] = t2.y; }
+                            else { const uint4 t4 = *reinterpret_cast<const uint4*>(e); v[0] = t4.x; v[1 % NQP] = t4.y; v[2 % NQP] = t4.z; v[3 % NQP] = t4.w; }
+                            #pragma unroll
+                            for (int q = 0; q < NQ; ++q) acc[q][j] = decltype(safe_c)::value ? add16x2(acc[q][j], v[q]) : acc[q][j] + v[q];
+                        }
+                    };
+                    if (!safe) gather(std::false_type{}); else gather(std::true_type{});
+                }
+            }
+            #pragma unroll
+            for (int u = 0; u < kPq4BChunk; ++u) cur[u] = nxt[u];
+        }
+        // the two lanes of a group hold the even / odd sub-quantizers of every pair: combine (per uint16 half), then lane h
+        // stores vectors 16h .. 16h+15.  Byte j of a half is vector perm0[j] = j/2 + 8 (j & 1) (+16 in the high uint16).
+        const unsigned duo = 0x3u << (lane & 30);
+        #pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            #pragma unroll
+            for (int j = 0; j < 16; ++j) acc[q][j] = add16x2(acc[q][j], __shfl_xor_sync(duo, acc[q][j], 1));
+            const uint32_t sel = h ? 0x7632u : 0x5410u;
+            uint4 o0, o1;                                              // vectors 16h + 0..7 and 16h + 8..15
+            o0.x = __byte_perm(acc[q][0], acc[q][2], sel);   o0.y = __byte_perm(acc[q][4], acc[q][6], sel);
+            o0.z = __byte_perm(acc[q][8], acc[q][10], sel);  o0.w = __byte_perm(acc[q][12], acc[q][14], sel);
+            o1.x = __byte_perm(acc[q][1], acc[q][3], sel);   o1.y = __byte_perm(acc[q][5], acc[q][7], sel);
+            o1.z = __byte_perm(acc[q][9], acc[q][11], sel);  o1.w = __byte_perm(acc[q][13], acc[q][15], sel);
+            uint4* out = reinterpret_cast<uint4*>(accu + (size_t)q * ld + g * 32 + h * 16);
+            out[0] = o0;
+            out[1] = o1;
+        }
+        if (base_next == nullptr) break;
+        g = g_next;
+        base = base_next;
+    }
+}
+
 // pq4_fast_scan.cpp:45-137: one thread per byte of the packed image.  v_base/v_count: which global vector ids `codes` holds
 // (rows v_base .. v_base + v_count); accumulate: OR into the image (pack_codes_range) instead of overwriting it.
 __global__ void pq4_pack_codes_kernel(const uint8_t* __restrict__ codes, size_t v_base, size_t v_count, size_t ncol, size_t block0, size_t n_bytes,
@@ -180,6 +301,9 @@ __global__ void pq4_pack_lut_kernel(int nq, int nsq, const uint8_t* __restrict__
     dest[(size_t)(sq / 2 * nq + qi) * 32 + 16 * (sq & 1) + e] = src[((size_t)q * nsq + sq) * 16 + e];
 }
 
+static int g_pq4_mode = 0;                   // 0: choose by size; 1: PRMT kernel; 2: byte-table kernel whenever it applies (tests)
+void pq4_set_mode(int m) { g_pq4_mode = m; }
+
 static int pq4_accumulate_launch(int nq, size_t nb, int bbs, int nsq, const uint8_t* codes, const uint8_t* LUT, uint16_t* accu, size_t ld,
                                  int scale, cudaStream_t st) {
     DeviceInfo di;
@@ -188,6 +312,30 @@ static int pq4_accumulate_launch(int nq, size_t nb, int bbs, int nsq, const uint
     LUTVQ_REQUIRE(smem <= di.smem_optin - 1024, "packed LUT of %zu bytes does not fit in shared memory", smem);
     const size_t n_groups = nb / 32;
     LUTVQ_REQUIRE(n_groups < (1ull << 32), "nb=%zu: at most 2^37 database vectors per call", nb);
+    // Large scans with >= 16 pairs take the byte-table kernel (HBM-bound); it needs 64 KiB of shared memory per 64 tables,
+    // 16-byte aligned outputs and enough groups to amortise the per-CTA table build.
+    const int nqp = nq == 3 ? 4 : nq, planes = (nsq + 64 / nqp - 1) / (64 / nqp);
+    const bool bytelut = g_pq4_mode != 1 && nsq >= 32 && nsq <= 512 && (size_t)planes * kPq4PlaneBytes <= di.smem_optin - 1024 &&
+                         (n_groups >= 8192 || g_pq4_mode == 2) && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(accu) & 15u) == 0;
+    if (bytelut) {
+        const size_t smem2 = (size_t)planes * kPq4PlaneBytes;
+        const int per_sm = planes == 1 ? (nq == 1 ? 3 : 2) : 1;        // registers: 73 / 128 / 139 / 141 for nq = 1..4
+        const size_t want2 = (n_groups + kPq4BThreads / 2 - 1) / (kPq4BThreads / 2), cap2 = (size_t)di.sm_count * per_sm;
+        const unsigned grid2 = (unsigned)(want2 < cap2 ? want2 : cap2);
+#define LUTVQ_PQ4B_LAUNCH(NQ)                                                                                                      \
+    case NQ: {                                                                                                                     \
+        LUTVQ_CUDA_OK(cudaFuncSetAttribute(pq4_bytelut_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));      \
+        pq4_bytelut_kernel<NQ><<<grid2, kPq4BThreads, smem2, st>>>(n_groups, bbs / 32, nsq, codes, LUT, accu, ld, scale);          \
+        break;                                                                                                                     \
+    }
+        switch (nq) {
+            LUTVQ_PQ4B_LAUNCH(1) LUTVQ_PQ4B_LAUNCH(2) LUTVQ_PQ4B_LAUNCH(3) LUTVQ_PQ4B_LAUNCH(4)
+            default: return fail(LUTVQ_EINVAL, "nq=%d: the kernel takes 1..4 queries per call", nq);
+        }
+#undef LUTVQ_PQ4B_LAUNCH
+        LUTVQ_CUDA_OK(cudaGetLastError());
+        return LUTVQ_OK;
+    }
     const size_t want = (n_groups + kPq4Threads / 4 - 1) / (kPq4Threads / 4), cap = (size_t)di.sm_count * 8;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
 #define LUTVQ_PQ4_LAUNCH(NQ)                                                                                                       \
@@ -210,6 +358,9 @@ static int pq4_accumulate_launch(int nq, size_t nb, int bbs, int nsq, const uint
 using namespace lutvq;
 
 extern "C" {
+
+// tests / tools: 0 = choose the accumulation kernel by size (default), 1 = PRMT kernel, 2 = byte-table kernel whenever it applies
+void lutvq_debug_set_pq4_mode(int mode) { pq4_set_mode(mode); }
 
 int lutvq_pq4_pack_codes(const void* codes, size_t ntotal, size_t M, size_t nb, size_t bbs, size_t nsq, void* blocks, void* stream) {
     LUTVQ_REQUIRE(bbs > 0 && bbs % 32 == 0 && nb % bbs == 0 && nsq % 2 == 0, "bbs %% 32, nb %% bbs and nsq %% 2 must be 0 (pq4_fast_scan.cpp:53-55)");

@@ -6,6 +6,7 @@ every op is one or more launches of our own sm_100a kernels through the C-ABI.  
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -227,10 +228,41 @@ def _fn_matmat_packed():
     return _matmat_packed_fn
 
 
+def code2x8_matmat_dequant_fused(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                                 bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """cuda_kernel.cpp:450-484 as ONE kernel: dequantize into shared memory + tcgen05 GEMM (W never exists in HBM), the
+    reference's epilogue order (round(acc) * scale + bias).  Batches above 256 rows are chunked (the codes are re-read per chunk)."""
+    return _matmat("lutvq_code2x8_matmat_dequant", input, codes, codebooks, scales, bias)
+
+
+def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                                    bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """cuda_kernel.cpp:450-484 the way the reference does it: dequantize W once (our kernel, scale folded in as ONE rounded
+    multiply per weight like code2x8_dequant, cuda_kernel.cpp:445), then the plain library GEMM the reference also calls
+    (F.linear = cuBLAS, bias in its epilogue).  W is written once and read from L2; the cost of dequantizing is paid once
+    whatever the batch is."""
+    check_use_bfloat16(input)
+    W = code2x8_dequant(codes, codebooks, scales)
+    flat = input.reshape(-1, input.size(-1))
+    return torch.nn.functional.linear(flat, W, bias).reshape(tuple(input.shape[:-1]) + (W.size(0),))
+
+
+# rows from which dequantize-once + library GEMM beats the fused kernel.  Measured on B200, 4096x11008, a ring of 24 L2-cold
+# layers, scales applied (bench.py `prefill`, profiles/r02_bench_line.json): fused 28.6 / 31.0 / 33.6 / 39.3 / 46.9 us at
+# 16 / 32 / 64 / 128 / 256 rows and 387 us at 2048 (chunks of 256 re-read the codes); two-step 37.9 / 37.9 / 38.2 / 35.8 / 41.9 us and
+# 157 us at 2048 (0.72 of the bf16 peak).  (With W's destination L2-resident the two-step route already wins at 32 rows:
+# profiles/r02_prefill_crossover.jsonl.)
+TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "128"))
+
+
 def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """cuda_kernel.cpp:450-484: the prefill path (dequant fused into a tcgen05 GEMM instead of dequant + cuBLAS)."""
-    return _matmat("lutvq_code2x8_matmat_dequant", input, codes, codebooks, scales, bias)
+    """cuda_kernel.cpp:450-484, the prefill op: the fused tcgen05 kernel below TWO_STEP_MIN_ROWS rows, dequantize-once +
+    library GEMM from there on (whichever is faster on B200; both within the north-star tolerance of the float64 result)."""
+    rows = input.numel() // max(input.size(-1), 1)
+    if rows >= TWO_STEP_MIN_ROWS:
+        return code2x8_matmat_dequant_two_step(input, codes, codebooks, scales, bias)
+    return code2x8_matmat_dequant_fused(input, codes, codebooks, scales, bias)
 
 
 def code2x8_dequant(codes: torch.Tensor, codebooks: torch.Tensor, scales: Optional[torch.Tensor]) -> torch.Tensor:

@@ -267,7 +267,7 @@ def test_matmat_dequant_tensor_core(pkg, ops, orc, I, O, batch, dt, bias):
     x, cb, sc = conv(L["x"]), conv(L["codebooks"]), conv(L["scales"])
     bi = conv(L["bias"]) if bias else None
     codes = cu(L["codes"])
-    y = ops.code2x8_matmat_dequant(x, codes, cb, sc, bi)
+    y = ops.code2x8_matmat_dequant_fused(x, codes, cb, sc, bi)
     assert y.shape == (batch, O) and y.dtype == tdt
     # the oracle's own chain: orc_dequantize (bit-exact weights) -> orc_dense_gemm_f64 (float64 contraction of the same operands)
     dtn = 0 if dt == "f16" else 1
@@ -284,9 +284,15 @@ def test_matmat_dequant_tensor_core(pkg, ops, orc, I, O, batch, dt, bias):
     ulp = (y.view(torch.int16).int() - ref.view(torch.int16).int()).abs()
     assert (ulp <= 2).float().mean() > 0.995
     # deterministic (fixed-order split-k) and leaves its workspace clean
-    assert torch.equal(ops.code2x8_matmat_dequant(x, codes, cb, sc, bi), y)
+    assert torch.equal(ops.code2x8_matmat_dequant_fused(x, codes, cb, sc, bi), y)
     for ws in ops._gemm_workspaces.values():
         assert torch.count_nonzero(ws[:256 + 4 * ((O + 127) // 128)]) == 0     # header + tile counters (partials need no cleaning)
+    # the dispatching op (fused below ops.TWO_STEP_MIN_ROWS rows, dequantize-once + library GEMM above) and the two-step route
+    # itself: same float64 bar; the two-step route folds the scale into W (one RN multiply per weight, cuda_kernel.cpp:445)
+    for fn in (ops.code2x8_matmat_dequant, ops.code2x8_matmat_dequant_two_step):
+        y2 = fn(x, codes, cb, sc, bi)
+        assert y2.shape == (batch, O) and y2.dtype == tdt
+        assert rel_err(y2.double().cpu().numpy(), want64.cpu().numpy()) <= tol
 
 
 def test_quantized_linear_prefill_dispatch(pkg, orc):

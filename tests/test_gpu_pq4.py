@@ -44,8 +44,14 @@ def test_pq4_fixture_bit_exact(pq4, golden_dir, name):
     assert np.array_equal(host(br), g["blocks"])
     lp = pq4.pq4_pack_LUT(nq, nsq, cu(g["lut"]))
     assert np.array_equal(host(lp), g["lut_packed"])
-    accu = pq4.pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lp, None, None if scale < 0 else scale)
-    assert np.array_equal(host(accu), g["accu"])
+    from rvv_lut_vq_b200._lib import lib
+    for mode in (0, 1, 2):                       # size-based choice, PRMT kernel, byte-table kernel (where it applies)
+        lib().lutvq_debug_set_pq4_mode(mode)
+        try:
+            accu = pq4.pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lp, None, None if scale < 0 else scale)
+        finally:
+            lib().lutvq_debug_set_pq4_mode(0)
+        assert np.array_equal(host(accu), g["accu"]), f"mode {mode}"
     got = [pq4.pq4_get_packed_element(blocks, bbs, nsq, int(v), int(s)) for v, s in zip(g["elem_v"][:8], g["elem_sq"][:8])]
     assert got == g["elems"][:8].tolist()
 
@@ -84,6 +90,28 @@ def test_pq4_vs_oracle(pq4, orc, nq, bbs, M, ntotal, scale):
     if nb > ntotal:                                              # padding vectors carry code 0 everywhere
         pad = orc.np_pq4_distances(np.zeros((1, (M + 1) // 2), np.uint8), lut, M, scale)
         assert np.array_equal(accu[:, ntotal:], np.repeat(pad, nb - ntotal, axis=1))
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("nq,bbs,M,ntotal,scale", [(1, 32, 32, 2048, -1), (2, 64, 40, 1000, -1), (4, 32, 64, 4096, 31), (1, 128, 512, 640, -1),
+                                                  (2, 32, 96, 512, 65535), (3, 96, 34, 960, 3), (1, 32, 300, 256, 1000)])
+def test_pq4_both_kernels_vs_oracle(pq4, orc, mode, nq, bbs, M, ntotal, scale):
+    """the PRMT kernel (mode 1) and the byte-table kernel (mode 2: >= 16 pairs, tables in shared memory) forced in turn:
+    table counts that are not multiples of 32 (rotated walk wraps), 3 shared-memory planes, nsq * 255 >= 2^16 (per-half adds),
+    scalers that overflow uint16"""
+    from rvv_lut_vq_b200._lib import lib
+    rng = np.random.default_rng(nq * 1000 + bbs + M + 7)
+    nsq, nb = pq4.pq4_nsq(M), -(-ntotal // bbs) * bbs
+    codes = rng.integers(0, 256, size=(ntotal, (M + 1) // 2), dtype=np.uint8)
+    lut = rng.integers(0, 256, size=(nq, nsq, 16), dtype=np.uint8)
+    blocks = pq4.pq4_pack_codes(cu(codes), ntotal, M, nb, bbs, nsq)
+    lp = pq4.pq4_pack_LUT(nq, nsq, cu(lut))
+    lib().lutvq_debug_set_pq4_mode(mode)
+    try:
+        accu = host(pq4.pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lp, None, None if scale < 0 else scale))
+    finally:
+        lib().lutvq_debug_set_pq4_mode(0)
+    assert np.array_equal(accu[:, :ntotal], orc.np_pq4_distances(codes, lut, M, scale))
 
 
 def test_pq4_qbs_blocks(pq4, orc):

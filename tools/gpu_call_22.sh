@@ -1,0 +1,11 @@
+#!/bin/bash
+# GPU call 22 (round 2): PQ4 byte-table kernel with one wide LDS for all queries; prefill crossover vs dequant + library GEMM up to batch 4096
+cd "$(dirname "$0")/.."
+O=gpurun_out/r02v
+mkdir -p $O
+timeout 600 python -m pytest tests/test_gpu_pq4.py -m gpu -q --timeout 300 > $O/pytest_pq4.txt 2>&1
+tail -8 $O/pytest_pq4.txt
+timeout 600 python tools/pq4_bench.py > $O/pq4_bench.jsonl 2> $O/pq4_bench.err
+cat $O/pq4_bench.jsonl | cut -c1-330; tail -3 $O/pq4_bench.err
+timeout 900 python tools/prefill_bench.py > $O/prefill.jsonl 2> $O/prefill.err
+cat $O/prefill.jsonl; tail -3 $O/prefill.err

@@ -22,8 +22,11 @@ def main():
     ref_path = os.path.join(ROOT, "oracle", "_ref", "libpq4_ref.so")
     ref = ctypes.CDLL(ref_path) if os.path.exists(ref_path) else None
     dev = torch.device("cuda:0")
-    for nq, bbs, nsq, nb in [(1, 32, 32, 1 << 24), (2, 32, 32, 1 << 24), (4, 32, 32, 1 << 24), (1, 256, 32, 1 << 24), (1, 32, 64, 1 << 23), (1, 32, 16, 1 << 25),
-                             (4, 32, 64, 1 << 23)]:
+    cases = [(1, 32, 32, 1 << 24), (2, 32, 32, 1 << 24), (4, 32, 32, 1 << 24), (1, 256, 32, 1 << 24), (1, 32, 64, 1 << 23), (1, 32, 16, 1 << 25),
+                             (4, 32, 64, 1 << 23)]
+    if os.environ.get("PQ4_BENCH_CASES"):
+        cases = [cases[int(k)] for k in os.environ["PQ4_BENCH_CASES"].split(",")]
+    for nq, bbs, nsq, nb in cases:
         g = torch.Generator(device=dev).manual_seed(1)
         blocks = torch.randint(0, 256, (nb * nsq // 2,), dtype=torch.uint8, device=dev, generator=g)
         lut = torch.randint(0, 256, (nq * nsq * 16,), dtype=torch.uint8, device=dev, generator=g)
@@ -58,6 +61,17 @@ def main():
             cpu_us = (time.perf_counter() - t0) / 3 * 1e6
             same = bool(np.array_equal(acc, accu[:, :n_cpu].cpu().numpy()))
             out.update(reference_avx2_1core_gbps=round((n_cpu * nsq // 2 + nq * n_cpu * 2) / cpu_us / 1e3, 2), reference_sample_vectors=n_cpu, bit_identical_to_reference=same)
+        r._lib.lib().lutvq_debug_set_pq4_mode(1)                          # the PRMT kernel on the same inputs
+        for _ in range(2):
+            pq4.pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lut, accu)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            pq4.pq4_accumulate_loop(nq, nb, bbs, nsq, blocks, lut, accu)
+        e1.record()
+        torch.cuda.synchronize()
+        r._lib.lib().lutvq_debug_set_pq4_mode(0)
+        out["prmt_kernel_us"] = round(e0.elapsed_time(e1) * 1e3 / reps, 1)
         print(json.dumps(out), flush=True)
 
 

@@ -38,7 +38,7 @@ def main():
     peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
     I, O, NB = 4096, 11008, 24
     Ls = [synth.make_layer_torch(I, O, dev, seed=k, scales="ones") for k in range(NB)]
-    for batch in (16, 32, 64, 128, 256):
+    for batch in (16, 32, 64, 128, 256, 512, 1024, 2048, 4096):
         x = torch.randn((batch, I), device=dev, dtype=torch.float16)
         k = [0]
 
@@ -46,11 +46,11 @@ def main():
             L = Ls[k[0] % NB]
             k[0] += 1
             ops.code2x8_matmat_dequant(x, L["codes"], L["codebooks"], L["scales"], None)
-        us = timed(f, 48)
+        us = timed(f, 48 if batch <= 256 else 12)
         flops = 2.0 * batch * I * O
         xw = x.float()
         W = ops.code2x8_dequant(Ls[0]["codes"], Ls[0]["codebooks"], None)
-        us_cublas = timed(lambda: torch.nn.functional.linear(x, W), 48)
+        us_cublas = timed(lambda: torch.nn.functional.linear(x, W), 48 if batch <= 256 else 12)
         us_deq = timed(lambda: ops.code2x8_dequant(Ls[k[0] % NB]["codes"], Ls[k[0] % NB]["codebooks"], None), 24)
         print(json.dumps({"op": "code2x8_matmat_dequant", "shape": f"{I}x{O}", "batch": batch, "us": round(us, 2),
                           "tflops": round(flops / us / 1e6, 1), "frac_of_bf16_burst_peak": round(flops / us / 1e6 / peaks["bf16_tflops"], 4),
