@@ -497,6 +497,12 @@ def main():
             y_host[i % NBUF].copy_(yd, non_blocking=True)
         torch.cuda.synchronize()
         eager_call_us = (time.perf_counter() - t0) / n_calls * 1e6
+        # the op call alone (input already on the device, no copies): host cost of QuantizedLinear's per-token call
+        t0 = time.perf_counter()
+        for i in range(n_calls):
+            ops.code2x8_matmat_packed(xd1, packed[i % NBUF], OUT_F, layers[i % NBUF]["codebooks"], layers[i % NBUF]["scales"], None)
+        torch.cuda.synchronize()
+        eager_op_only_us = (time.perf_counter() - t0) / n_calls * 1e6
 
         # ---- the other shapes of the configs[1] sweep (not part of the timed region above) ----
         sweep = []
@@ -570,7 +576,7 @@ def main():
         "us_per_gemv": us_per_gemv,
         "dependent_chain_us_per_gemv": dep_us,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": NBUF * IN_F * 2, "d2h_bytes_per_step": NBUF * world * OUT_F * 2,
-                "us_per_gemv": e2e_ms * 1e3 / NBUF, "eager_torch_op_call_us": eager_call_us,
+                "us_per_gemv": e2e_ms * 1e3 / NBUF, "eager_torch_op_call_us": eager_call_us, "eager_torch_op_only_us": eager_op_only_us,
                 "how": "per step: one H2D copy of the step's NBUF activation rows from pinned host memory, the step's C-ABI GEMVs, one D2H copy of the NBUF output rows"},
         "gpu_launches": args.steps * (NBUF + n_exch),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
