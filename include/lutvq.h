@@ -318,6 +318,21 @@ int lutvq_tmac_preprocessor_int8(int K, const void* B, void* lut_scales, void* l
 int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, const void* qlut, const void* scales,
                               const void* lut_scales, const void* lut_biases, void* C, void* stream);
 
+/* ---- no-allocation variant of lutvq_code2x8_matmat (csrc/noalloc.cu) ----
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc or carry
+ * a workspace (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Same arguments and results as lutvq_code2x8_matmat (reference-layout codes int8 [prob_m][prob_k/8][2], bit-identical outputs)
+ * minus the workspace: the split-k words live in a file-scope static __device__ array inside the library, sized for
+ * prob_m <= LUTVQ_NOALLOC_MAX_ROWS (lutvq_noalloc_scratch_bytes() = 256 + 8 * LUTVQ_NOALLOC_MAX_ROWS bytes = 257 KiB, held by every
+ * GPU that loads the library until exit).  Larger prob_m is rejected with LUTVQ_EINVAL and a message naming the limit.
+ * The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine): one stream-ordered memset of the region
+ * it uses + one kernel launch per batch row.  ALL calls on a device share the one array: calls that overlap on the GPU (two
+ * streams) race -- serialise them on one stream, or use lutvq_code2x8_matmat with private workspaces. */
+#define LUTVQ_NOALLOC_MAX_ROWS 32768
+size_t lutvq_noalloc_scratch_bytes(void);
+int lutvq_code2x8_matmat_noalloc(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias,
+                                 void* y, int batch, int prob_m, int prob_k, int dtype, void* stream);
+
 /* ---- PQ4 fast-scan distance accumulation (csrc/pq4.cu) ----
  * Replaces, with the same packed layouts (images packed by either side are interchangeable) and bit-identical uint16 results:
  *   pq4_pack_codes            benchmark/kernel/faiss-simd/pq4_fast_scan.cpp:45-91    codes [ntotal][(M+1)/2] -> blocks [nb * nsq / 2]

@@ -52,6 +52,8 @@ SIGNATURES = {
     "lutvq_partial_max_g4_int8_k8": (I, [P, P, P]),
     "lutvq_partial_max_reset": (I, [P, P]),
     "lutvq_lut_ctor_g4_int8": (I, [I, P, P, P, P, P]),
+    "lutvq_noalloc_scratch_bytes": (SZ, []),
+    "lutvq_code2x8_matmat_noalloc": (I, [P, P, P, P, P, P, I, I, I, I, P]),
     "lutvq_pq4_pack_codes": (I, [P, SZ, SZ, SZ, SZ, SZ, P, P]),
     "lutvq_pq4_pack_codes_range": (I, [P, SZ, SZ, SZ, SZ, SZ, P, P]),
     "lutvq_pq4_pack_LUT": (I, [I, I, P, P, P]),
