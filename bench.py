@@ -276,6 +276,39 @@ def measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak):
     return rows, dq_row
 
 
+def measure_small_batch(torch, dev):
+    """batch 1..8 through lutvq_code2x8_matmat_packed on 4096x11008 (a dependent chain over a ring of L2-cold layers): us per call with
+    the rows of a call grouped into one launch (what ops / QuantizedLinear do) and with one launch per row (the reference's loop)"""
+    from rvv_lut_vq_b200 import ops, synth
+    lib = __import__("rvv_lut_vq_b200").lib()
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    st = torch.cuda.Stream(dev)
+    NB = 32
+    Ls = [synth.make_layer_torch(IN_F, OUT_F, dev, seed=700 + k, scales="randn") for k in range(NB)]
+    pk = [ops.code2x8_prepack(L["codes"]) for L in Ls]
+    need = (int(lib.lutvq_packed_workspace_bytes(OUT_F, IN_F)) + 255) // 256 * 256
+    ws = torch.zeros(need * 8, dtype=torch.uint8, device=dev)
+    rows = []
+    for batch in (1, 2, 4, 6, 8):
+        x = torch.randn((batch, IN_F), device=dev, dtype=torch.float16)
+        y = torch.empty((batch, OUT_F), device=dev, dtype=torch.float16)
+        r = {"batch": batch}
+        for name, nbytes in (("us", need * min(batch, 8)), ("one_launch_per_row_us", need)):
+            def body():
+                s = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+                for k, L in enumerate(Ls):
+                    rc = lib.lutvq_code2x8_matmat_packed(P(x), P(pk[k]), P(L["codebooks"]), P(L["scales"]), None, P(y), batch, OUT_F, IN_F, 0, 0,
+                                                         P(ws), nbytes, s)
+                    assert rc == 0, lib.lutvq_last_error()
+            r[name] = round(graph_time_us(torch, st, body, 5, NB), 2)
+        rows.append(r)
+    for r in rows:
+        r["vs_batch1"] = round(r["us"] / rows[0]["us"], 2)
+    del Ls, pk, ws
+    torch.cuda.empty_cache()
+    return rows
+
+
 def kernel_to_beat():
     """the reference's own CUDA kernels on this GPU (baseline/_ref/aqlm_cuda, tools/ref_cuda_bench.py); never fatal"""
     try:
@@ -534,12 +567,13 @@ def main():
     torch.cuda.empty_cache()
 
     # ---- decode tok/s (the second half of BASELINE.json's metric) ----
-    decode = decode70 = prefill = dequant = ktb = None
+    decode = decode70 = prefill = dequant = ktb = small_batch = None
     if not args.no_extras:
         if world == 1:
             decode = measure_decode(torch, dist, "7b", 1, 0, dev)
             decode70 = measure_decode(torch, dist, "70b", 1, 0, dev)
             prefill, dequant = measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak)
+            small_batch = measure_small_batch(torch, dev)
             ktb = kernel_to_beat()
         else:
             decode70 = measure_decode(torch, dist, "70b", world, rank, dev, exchange=os.environ.get("LUTVQ_BENCH_EXCHANGE", "ll"))
@@ -592,6 +626,8 @@ def main():
         out["decode"] = decode
     if decode70 is not None:
         out["decode_70b"] = decode70
+    if small_batch is not None:
+        out["small_batch"] = {"shape": f"{IN_F}x{OUT_F}", "rows": small_batch}
     if prefill is not None:
         out["prefill"] = prefill
         out["dequant"] = dequant

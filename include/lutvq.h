@@ -99,7 +99,11 @@ int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* 
                          int prob_m, int prob_k, int dtype, void* ws, size_t ws_bytes, void* stream);
 
 /* y[b][o] = round(round(acc) * scales[o]) + bias[o]   for b < batch  (reference epilogue order, fused)
- * x dtype [batch][prob_k]; scales dtype [prob_m] (NULL = no scaling); bias dtype [prob_m] or NULL; y dtype [batch][prob_m]. */
+ * x dtype [batch][prob_k]; scales dtype [prob_m] (NULL = no scaling); bias dtype [prob_m] or NULL; y dtype [batch][prob_m].
+ * cuda_kernel.cpp:404-414 launches its kernel once per row.  Here up to 8 rows go out as ONE launch (each row takes a share of the
+ * SMs; the rows share the kernel's fixed cost and read the layer's codes at the same pace, so HBM sees them once) when ws holds
+ * min(batch, LUTVQ_XREADY_WS_RING) regions of ceil256(lutvq_packed_workspace_bytes(prob_m, prob_k)) bytes (zero-initialised, handed
+ * back zero); with a single region it is one launch per row.  Results are bit-identical either way.  (_matmat_packed: the same.) */
 int lutvq_code2x8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales,
                          const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
                          void* ws, size_t ws_bytes, void* stream);

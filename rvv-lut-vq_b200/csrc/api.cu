@@ -11,6 +11,10 @@ namespace lutvq {
 int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* codebook, const void* scales,
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push = nullptr);
+int gemv_2x8_launch_rows(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
+                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream);
+int gemv_max_rows_per_launch();
+size_t gemv_rows_workspace_bytes(int rows, int O);
 int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
                         const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream);
 size_t gemv_workspace_bytes(int O, int G);
@@ -143,25 +147,33 @@ static int matmat_rows(const void* x, const void* codes, int packed, const void*
     const size_t region = ws_bytes;
     // cuda_kernel.cpp:404-414 loops the matvec over the flattened batch rows; so do we (one fused launch per row,
     // scale/bias folded into the kernel's epilogue instead of three extra elementwise kernels).
-    // X_READY launches overlap under programmatic dependent launch, so consecutive rows must not share split-k words:
-    // row b takes workspace region b % LUTVQ_XREADY_WS_RING when the caller's workspace holds that many regions,
-    // otherwise the promise is dropped for the rows after the first.
-    const size_t need = (gemv_packed_workspace_bytes(prob_m, prob_k / 8) + 255) / 256 * 256;
-    int regions = 1;
-    if (packed && batch > 1 && (flags & LUTVQ_FLAG_X_READY)) {
-        const int want = batch < LUTVQ_XREADY_WS_RING ? batch : LUTVQ_XREADY_WS_RING;
-        if (ws_bytes >= need * (size_t)want) regions = want;
+    // Small batches go out as ONE launch per gemv_max_rows_per_launch() rows when the workspace holds their split-k words
+    // (gemv_rows_workspace_bytes; a ring of min(batch, LUTVQ_XREADY_WS_RING) single-row regions is enough): the rows share the
+    // kernel's fixed cost and the code stream (gemv_lut.cu, gemv_2x8_launch_rows).
+    {
+        const int per = batch < gemv_max_rows_per_launch() ? batch : gemv_max_rows_per_launch();
+        if (batch > 1 && ws_bytes >= gemv_rows_workspace_bytes(per, prob_m)) {
+            for (int b0 = 0; b0 < batch; b0 += per) {
+                const int nb = batch - b0 < per ? batch - b0 : per;
+                unsigned f = flags;
+                if (b0 > 0) f &= ~LUTVQ_FLAG_X_READY;                 // the chunks of one call share the workspace: they run in turn
+                if (int rc = gemv_2x8_launch_rows(codes, packed, static_cast<const uint8_t*>(x) + (size_t)b0 * prob_k * 2,
+                                                  static_cast<uint8_t*>(y) + (size_t)b0 * prob_m * 2, codebooks, scales, bias, nb, prob_m, prob_k,
+                                                  dtype, f, ws, ws_bytes, st))
+                    return rc;
+            }
+            return LUTVQ_OK;
+        }
     }
-    const size_t esz = 2;
+    // Otherwise one launch per row.  X_READY launches overlap under programmatic dependent launch, so consecutive rows must not
+    // share split-k words: with a single-region workspace the promise is dropped for the rows after the first.
     for (int b = 0; b < batch; ++b) {
-        const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * esz;
-        void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * esz;
+        const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * 2;
+        void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * 2;
         unsigned f = flags;
-        if (b > 0 && regions == 1) f &= ~LUTVQ_FLAG_X_READY;
-        void* wsb = regions > 1 ? static_cast<uint8_t*>(ws) + (size_t)(b % regions) * need : ws;
-        const size_t wsn = regions > 1 ? need : region;
-        if (int rc = packed ? gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb, wsn, st)
-                            : gemv_2x8_launch_ref(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, wsb, wsn, st))
+        if (b > 0) f &= ~LUTVQ_FLAG_X_READY;
+        if (int rc = packed ? gemv_2x8_launch(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, ws, region, st)
+                            : gemv_2x8_launch_ref(codes, xb, yb, codebooks, scales, bias, prob_m, prob_k, dtype, f, ws, region, st))
             return rc;
     }
     return LUTVQ_OK;

@@ -102,7 +102,9 @@ __device__ __forceinline__ unsigned short ll_load1(const uint32_t* w, unsigned e
 }
 
 // one linear of a grouped GEMV launch (gemv_lut.cu gemv_2x8_launch_group)
-struct GemvItem { const void* codes; const void* codebook; void* y; const void* scales; const void* bias; int O; };
+// one linear of a grouped GEMV launch.  x_off: byte offset of THIS item's activation row from the launch's x pointer (0 for the
+// linears of a layer that share one input; b * prob_k * 2 for the rows of a multi-row call, which share the codes instead)
+struct GemvItem { const void* codes; const void* codebook; void* y; const void* scales; const void* bias; int O; size_t x_off = 0; };
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

@@ -62,7 +62,7 @@ constexpr size_t kWsHeaderBytes = 256;        // reserved
 constexpr int kMaxPeers = 8;                  // one NVSwitch domain
 constexpr int kRangeTable = 320;              // workers whose item ranges ride in the kernel parameters (B200: 148 or 2 x 148)
 
-constexpr int kMaxProblems = 3;               // linears that share x and go out in ONE launch (q/k/v, gate/up)
+constexpr int kMaxProblems = 8;               // linears that share x (q/k/v, gate/up) or rows of a small batch that share the codes: ONE launch
 
 // One linear layer of a (possibly grouped) launch.  Every worker (CTA) belongs to exactly one problem.
 // two fp16 lanes of silu(g) * u, rounded once: the arithmetic of decode_glue.cu silu_mul_kernel, bit for bit
@@ -83,6 +83,7 @@ struct GemvProblem {
     const void* bias;         // [O] or null
     unsigned long long* acc;  // [O_pad] split-k accumulator words, zero between launches
     int O, n_sets;
+    unsigned x_off;           // byte offset of this problem's activation row from GemvParams::x / x_gate (rows of a multi-row call)
 };
 
 struct GemvParams {
@@ -397,8 +398,8 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     if (warp == NW - 1) {
         if (p.x != nullptr && lane < kSliceXBytes / 128 && (size_t)ks * kSliceXBytes + lane * 128 < (size_t)p.G * 16)
         {
-            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + (size_t)ks * kSliceXBytes + lane * 128);
-            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + (size_t)ks * kSliceXBytes + lane * 128);
+            l2_prefetch_line(static_cast<const uint8_t*>(p.x) + PB.x_off + (size_t)ks * kSliceXBytes + lane * 128);
+            if (p.x_gate) l2_prefetch_line(static_cast<const uint8_t*>(p.x_gate) + PB.x_off + (size_t)ks * kSliceXBytes + lane * 128);
         }
     }
     TL_STAMP(10);
@@ -459,9 +460,9 @@ lut_gemv_2x8_kernel(const GemvParams p) {
                         v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
                     }
                 } else {
-                    v = ldcg_u128(static_cast<const uint4*>(p.x) + g);        // L2-coherent: x may be the previous kernel's output
+                    v = ldcg_u128(reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.x) + PB.x_off) + g);   // L2-coherent: x may be the previous kernel's output
                     if (DT == LUTVQ_F16 && p.x_gate != nullptr) {
-                        const uint4 gt = ldcg_u128(static_cast<const uint4*>(p.x_gate) + g);
+                        const uint4 gt = ldcg_u128(reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(p.x_gate) + PB.x_off) + g);
                         v.x = silu_mul_halves(gt.x, v.x); v.y = silu_mul_halves(gt.y, v.y);
                         v.z = silu_mul_halves(gt.z, v.z); v.w = silu_mul_halves(gt.w, v.w);
                     }
@@ -903,7 +904,7 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
     p.has_table = 0;
     int W_total = 0, left = workers;
     uint8_t* accp = static_cast<uint8_t*>(ws) + kWsHeaderBytes;
-    for (int i = 0; i < kMaxProblems; ++i) p.prob[i] = GemvProblem{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0};
+    for (int i = 0; i < kMaxProblems; ++i) p.prob[i] = GemvProblem{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0u};
     for (int i = 0; i < n; ++i) {
         // SM share of problem i: proportional to its row sets, at least one, the last problem takes the remainder
         const int n_sets_i = ceil_div(items[i].O, kSetRows);
@@ -919,6 +920,8 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
         pb.scales = items[i].scales; pb.bias = items[i].bias;
         pb.acc = reinterpret_cast<unsigned long long*>(accp);
         pb.O = items[i].O; pb.n_sets = pl.n_sets;
+        LUTVQ_REQUIRE(items[i].x_off < (1ull << 32) && items[i].x_off % 16 == 0, "activation row offset must be 16-byte aligned and below 4 GiB");
+        pb.x_off = (unsigned)items[i].x_off;
         accp += (size_t)pl.n_sets * kSetRows * sizeof(unsigned long long);
         if (W_total + pl.W <= kRangeTable LUTVQ_DBG_AND(!(flags & 0x1000u))) {
             for (int w = 0; w < pl.W; ++w) {
@@ -987,6 +990,24 @@ int gemv_kx8_launch_ref(const void* codes, const void* x, void* y, const void* c
                         cudaStream_t stream) {
     const GemvItem it{codes, codebook, y, scales, bias, O};
     return gemv_launch_impl(1, &it, 0, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr, nullptr, ncb);
+}
+
+// `rows` (1..kMaxProblems) activation rows against ONE layer in one launch: the rows are the "problems" of a grouped launch -- each
+// gets a share of the SMs, its own split-k words and its own x row (x_off); they stream the same codes at the same pace, so the
+// second..last readers of a code line hit L2.  The kernel's fixed part (prologue, dependency wait, LUT build latency, tail) is
+// paid once per launch instead of once per row.  Workspace: gemv_rows_workspace_bytes(rows, O).  Results are bit-identical to
+// `rows` single-row launches (integer split-k sums).
+int gemv_2x8_launch_rows(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
+                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream) {
+    LUTVQ_REQUIRE(rows >= 1 && rows <= kMaxProblems, "1..%d rows per launch, got %d", kMaxProblems, rows);
+    GemvItem items[kMaxProblems];
+    for (int b = 0; b < rows; ++b)
+        items[b] = GemvItem{codes, codebook, static_cast<uint8_t*>(y) + (size_t)b * O * 2, scales, bias, O, (size_t)b * I * 2};
+    return gemv_launch_impl(rows, items, packed, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr);
+}
+int gemv_max_rows_per_launch() { return kMaxProblems; }
+size_t gemv_rows_workspace_bytes(int rows, int O) {
+    return kWsHeaderBytes + (size_t)rows * ceil_div(O, kSetRows) * kSetRows * sizeof(unsigned long long);
 }
 
 size_t gemv_packed_workspace_bytes(int O, int G) { return gemv_workspace_bytes(O, G); }

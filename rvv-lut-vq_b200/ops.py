@@ -107,6 +107,26 @@ def workspace(dev: torch.device, prob_m: int, prob_k: int, rotate: bool = False,
     return ent[0][i]
 
 
+_batch_workspaces: Dict[Tuple[int, int], torch.Tensor] = {}
+BATCH_GROUPED = os.environ.get("LUTVQ_BATCH_GROUPED", "1") != "0"      # experiment switch: 0 = one launch per row of a multi-row call
+
+
+def batch_workspace(dev: torch.device, prob_m: int, prob_k: int, rows: int, stream: Optional[int] = None) -> torch.Tensor:
+    """min(rows, XREADY_WS_RING) zero-initialised regions for ONE multi-row GEMV call (include/lutvq.h, lutvq_code2x8_matmat): up to 8
+    rows of the call then go out as one launch.  A buffer of its own per (device, stream), so it never collides with the X_READY
+    ring of `workspace()`; the next multi-row call on the stream reuses it (it waits for everything before it)."""
+    need = _ws_need.get((prob_m, prob_k))
+    if need is None:
+        need = _ws_need[(prob_m, prob_k)] = (int(lib().lutvq_packed_workspace_bytes(prob_m, prob_k)) + 255) // 256 * 256
+    total = need * min(rows, XREADY_WS_RING)
+    key = _key(dev) if stream is None else (dev.index, stream)
+    ws = _batch_workspaces.get(key)
+    if ws is None or ws.numel() < total:
+        ws = torch.zeros(max(total, 1 << 20), dtype=torch.uint8, device=dev)
+        _batch_workspaces[key] = ws
+    return ws[:total]
+
+
 _ws_regions: Dict[Tuple[int, int], tuple] = {}
 _ws_need: Dict[Tuple[int, int], int] = {}
 
@@ -144,6 +164,8 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
     with torch.cuda.device(dev):
         if fn_name == "lutvq_code2x8_matmat_dequant":
             ws = gemm_workspace(dev, out_features, in_features, batch)
+        elif batch > 1 and BATCH_GROUPED and not (flags or 0) & _lib.FLAG_X_READY:
+            ws = batch_workspace(dev, out_features, in_features, batch)
         else:
             ws = stage_workspace(dev, out_features, in_features)
         fn = getattr(lib(), fn_name)
@@ -206,7 +228,10 @@ def code2x8_matmat_packed(input: torch.Tensor, packed: torch.Tensor, out_feature
         torch.cuda.set_device(dev)
     try:
         stream = torch.cuda.current_stream(dev).cuda_stream
-        ws = workspace(dev, out_features, in_features, rotate=x_ready, stream=stream)
+        if batch > 1 and BATCH_GROUPED and not x_ready:
+            ws = batch_workspace(dev, out_features, in_features, batch, stream)
+        else:
+            ws = workspace(dev, out_features, in_features, rotate=x_ready, stream=stream)
         rc = _fn_matmat_packed()(flat_input.data_ptr(), packed.data_ptr(), cb.data_ptr(), 0 if sc is None else sc.data_ptr(),
                                  0 if bi is None else bi.data_ptr(), flat_output.data_ptr(), batch, out_features, in_features, dtype, flags,
                                  ws.data_ptr(), ws.numel(), stream)

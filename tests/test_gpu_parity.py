@@ -308,6 +308,44 @@ def test_quantized_linear_prefill_dispatch(pkg, orc):
     assert rel_err(y_gemm.float().cpu().numpy(), y_gemv.float().cpu().numpy()) <= 1e-3
 
 
+@pytest.mark.parametrize("I,O,batch,dtype", [(4096, 11008, 2, "f16"), (4096, 4096, 4, "f16"), (11008, 4096, 6, "f16"), (4096, 11008, 11, "bf16"),
+                                             (1024, 96, 5, "f16")])
+def test_multi_row_call_groups_rows_bit_identically(pkg, ops, I, O, batch, dtype):
+    """up to 8 rows of one lutvq_code2x8_matmat[_packed] call go out as ONE grouped launch when the workspace holds their split-k
+    words (batch 11 = 8 + 3): same bits as one row per call, the workspace comes back all-zero, and x produced by the kernel just
+    before the call is honoured (a race would show up as stale rows)."""
+    from rvv_lut_vq_b200 import synth
+    tdt = torch.float16 if dtype == "f16" else torch.bfloat16
+    L = synth.make_layer_np(I, O, seed=I + O + batch, scales="randn", bias=True, batch=batch)
+    conv = (lambda a: cu(a)) if dtype == "f16" else (lambda a: cu(a.astype(np.float32)).to(torch.bfloat16))
+    x, cb, sc, bi = conv(L["x"]), conv(L["codebooks"]), conv(L["scales"]), conv(L["bias"])
+    codes = cu(L["codes"])
+    packed = ops.code2x8_prepack(codes)
+    rows = torch.cat([ops.code2x8_matmat_packed(x[b:b + 1], packed, O, cb, sc, bi) for b in range(batch)])      # one row per call
+    assert ops.BATCH_GROUPED
+    got_p = ops.code2x8_matmat_packed(x, packed, O, cb, sc, bi)
+    got_r = ops.code2x8_matmat(x, codes, cb, sc, bi)
+    torch.cuda.synchronize()
+    assert torch.equal(got_p.view(torch.int16), rows.view(torch.int16))
+    assert torch.equal(got_r.view(torch.int16), rows.view(torch.int16))
+    for ws in ops._batch_workspaces.values():
+        assert torch.count_nonzero(ws) == 0
+    # producer -> multi-row call -> consumer, many times: x changes every iteration and is written by the kernel right before the call
+    acc = torch.zeros((batch, O), dtype=torch.float32, device="cuda")
+    want = torch.zeros_like(acc)
+    for it in range(20):
+        xi = (x.float() * (1.0 + 0.25 * it)).to(tdt)                     # producer kernels
+        y = ops.code2x8_matmat_packed(xi, packed, O, cb, sc, bi)
+        acc += y.float()                                                 # consumer right behind the last row
+    torch.cuda.synchronize()
+    for it in range(20):
+        xi = (x.float() * (1.0 + 0.25 * it)).to(tdt)
+        torch.cuda.synchronize()
+        want += torch.cat([ops.code2x8_matmat_packed(xi[b:b + 1], packed, O, cb, sc, bi) for b in range(batch)]).float()
+        torch.cuda.synchronize()
+    assert torch.equal(acc, want)
+
+
 # ------------------------------------------------------------------ edge cases / API behaviour
 def test_empty_batch_and_shapes(pkg, ops):
     from rvv_lut_vq_b200 import synth
