@@ -237,6 +237,12 @@ int    lutvq_shard_error(lutvq_shard_t* s, unsigned* out);        /* nonzero: a 
  *                                  with sequence numbers out_seq[i] (< 1024, unique within a step); input: plain x (x_slot < 0)
  *                                  or the LL words of the local slot x_slot / x_seq; gate_slot >= 0: silu(gate) * x, both LL (fp16)
  *   lutvq_decode_add_rmsnorm_ll / lutvq_decode_attention_ll   the glue kernels with their sharded operands taken from LL slots
+ *   lutvq_decode_add_rmsnorm_ll_out / lutvq_decode_attention_ll_out   the same, with the result ALSO written as LL words into the
+ *                                  LOCAL slot y_slot / out_slot (delta_slot < 0: no delta).  This makes "dataflow launches" possible:
+ *                                  lutvq_sharded_matmat_group_ll with LUTVQ_FLAG_X_READY and x_slot >= 0 does not wait for the
+ *                                  launch before it to complete before it reads its activations -- it streams its codes, then
+ *                                  polls the LL words (they carry their own validity) -- and only orders its stores behind it.
+ *                                  Its workspace must not be shared with the LUTVQ_XREADY_WS_RING - 1 launches around it.
  *   lutvq_shard_ll_unpack          LL slot -> plain vector (for consumers that are not ours, and for tests)
  * Polls are bounded (seconds): on a timeout the shard's error word (lutvq_shard_error) is set and the kernel returns. */
 int    lutvq_shard_ll_tick(lutvq_shard_t* s, void* stream);
@@ -251,6 +257,11 @@ int    lutvq_decode_add_rmsnorm_ll(lutvq_shard_t* s, void* resid, int delta_slot
 int    lutvq_decode_attention_ll(lutvq_shard_t* s, int q_slot, int k_slot, int v_slot, unsigned q_seq, unsigned k_seq, unsigned v_seq,
                                  void* kcache, void* vcache, const int* pos, void* out, int n_heads, int n_kv_heads, int head_dim,
                                  int max_seq, float rope_theta, void* stream);
+int    lutvq_decode_add_rmsnorm_ll_out(lutvq_shard_t* s, void* resid, int delta_slot, unsigned delta_seq, const void* w, void* y,
+                                       int y_slot, unsigned y_seq, int n, float eps, void* stream);
+int    lutvq_decode_attention_ll_out(lutvq_shard_t* s, int q_slot, int k_slot, int v_slot, unsigned q_seq, unsigned k_seq, unsigned v_seq,
+                                     void* kcache, void* vcache, const int* pos, void* out, int out_slot, unsigned out_seq, int n_heads,
+                                     int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream);
 int    lutvq_shard_destroy(lutvq_shard_t* s);
 
 /* ---- integer LUT: lookup-and-add ----

@@ -89,6 +89,8 @@ SIGNATURES = {
     "lutvq_shard_ll_unpack": (I, [P, I, U, P, I, P]),
     "lutvq_decode_add_rmsnorm_ll": (I, [P, P, I, U, P, P, I, ctypes.c_float, P]),
     "lutvq_decode_attention_ll": (I, [P, I, I, I, U, U, U, P, P, P, P, I, I, I, I, ctypes.c_float, P]),
+    "lutvq_decode_add_rmsnorm_ll_out": (I, [P, P, I, U, P, P, I, U, I, ctypes.c_float, P]),
+    "lutvq_decode_attention_ll_out": (I, [P, I, I, I, U, U, U, P, P, P, P, I, U, I, I, I, I, ctypes.c_float, P]),
     "lutvq_decode_add_rmsnorm": (I, [P, P, P, P, I, ctypes.c_float, P]),
     "lutvq_decode_silu_mul": (I, [P, P, P, I, P]),
     "lutvq_decode_attention": (I, [P, P, P, P, P, P, P, I, I, I, I, ctypes.c_float, P]),

@@ -14,7 +14,18 @@ struct LLIn {
     unsigned seq[3] = {0, 0, 0};
     const unsigned* tick = nullptr;
     unsigned* error = nullptr;
+    // optional LL OUTPUT: the result also goes out as {value | epoch} words into a LOCAL gather slot, so that the GEMV that
+    // consumes it can poll for it instead of waiting for this kernel to complete (DESIGN 4.5 "dataflow launches")
+    uint32_t* out = nullptr;
+    unsigned out_seq = 0;
 };
+__device__ __forceinline__ void ll_store8(uint32_t* dst, const uint4& halves, unsigned ep) {
+    const uint32_t e = ep << 16;
+    const uint4 lo = make_uint4((halves.x & 0xffffu) | e, (halves.x >> 16) | e, (halves.y & 0xffffu) | e, (halves.y >> 16) | e);
+    const uint4 hi = make_uint4((halves.z & 0xffffu) | e, (halves.z >> 16) | e, (halves.w & 0xffffu) | e, (halves.w >> 16) | e);
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w) : "memory");
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" :: "l"(dst + 4), "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w) : "memory");
+}
 __device__ __forceinline__ __half ll_half(const LLIn& ll, int k, unsigned tick, int i) {
     const unsigned short b = ll_load1(ll.w[k] + i, ll_epoch16(tick, ll.seq[k]), ll.error);
     return *reinterpret_cast<const __half*>(&b);
@@ -55,7 +66,12 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_kernel(__half* resid, const 
     for (int i = 0; i < 32; ++i) tot += red[i];
     const float r = rsqrtf(tot / (float)n + eps);
     cnt = 0;
-    for (int i = threadIdx.x; i < n; i += 1024, ++cnt) y[i] = __float2half_rn(v[cnt] * r * __half2float(w[i]));
+    const unsigned ep_out = ll.out ? ll_epoch16(*ll.tick, ll.out_seq) : 0u;
+    for (int i = threadIdx.x; i < n; i += 1024, ++cnt) {
+        const __half o = __float2half_rn(v[cnt] * r * __half2float(w[i]));
+        y[i] = o;
+        if (ll.out) asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(ll.out + i), "r"((uint32_t)__half_as_ushort(o) | (ep_out << 16)) : "memory");
+    }
 }
 
 // The same for n % 8 == 0, n <= 8192 (every Llama hidden size): one 16-byte load per operand and thread, all of them
@@ -105,6 +121,7 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_vec8_kernel(__half* resid, c
         #pragma unroll
         for (int j = 0; j < 8; ++j) oh[j] = __float2half_rn(a[j] * r * __half2float(wh[j]));
         *reinterpret_cast<uint4*>(y + i0) = o;
+        if (ll.out) ll_store8(ll.out + i0, o, ll_epoch16(*ll.tick, ll.out_seq));
     }
 }
 
@@ -246,7 +263,10 @@ __global__ void __launch_bounds__(kAttnWarps * 32) attn_decode_kernel(const __ha
         float o = 0.f;
         #pragma unroll
         for (int w = 0; w < kAttnWarps; ++w) o += part[w * kHeadDim + tid];
-        out[h * kHeadDim + tid] = __float2half_rn(o * inv);
+        const __half oh = __float2half_rn(o * inv);
+        out[h * kHeadDim + tid] = oh;
+        if (ll.out) asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(ll.out + h * kHeadDim + tid),
+                                 "r"((uint32_t)__half_as_ushort(oh) | (ll_epoch16(*ll.tick, ll.out_seq) << 16)) : "memory");
     }
 }
 
@@ -295,6 +315,25 @@ int lutvq_decode_add_rmsnorm_ll(lutvq_shard_t* h, void* resid, int delta_slot, u
     return add_rmsnorm_impl(resid, nullptr, w, y, n, eps, stream, ll);
 }
 
+// The same with the normalised vector ALSO written as LL words into the local slot y_slot (sequence number y_seq); delta_slot < 0:
+// no delta (first layer of a token).
+int lutvq_decode_add_rmsnorm_ll_out(lutvq_shard_t* h, void* resid, int delta_slot, unsigned delta_seq, const void* w, void* y, int y_slot,
+                                    unsigned y_seq, int n, float eps, void* stream) {
+    LLIn ll;
+    size_t cap = 0;
+    if (delta_slot >= 0) {
+        if (int rc = shard_ll_input(h, delta_slot, &ll.w[0], &ll.tick, &ll.error, &cap)) return rc;
+        LUTVQ_REQUIRE((size_t)n <= cap, "n=%d exceeds the gather slot (%zu rows)", n, cap);
+        ll.seq[0] = delta_seq;
+    }
+    const uint32_t* ow = nullptr;
+    if (int rc = shard_ll_input(h, y_slot, &ow, &ll.tick, &ll.error, &cap)) return rc;
+    LUTVQ_REQUIRE((size_t)n <= cap, "n=%d exceeds the gather slot (%zu rows)", n, cap);
+    ll.out = const_cast<uint32_t*>(ow);
+    ll.out_seq = y_seq;
+    return add_rmsnorm_impl(resid, nullptr, w, y, n, eps, stream, ll);
+}
+
 int lutvq_decode_silu_mul(const void* gate, const void* up, void* y, int n, void* stream) {
     LUTVQ_REQUIRE(gate && up && y && n > 0, "bad arguments");
     return launch_pdl(silu_mul_kernel, dim3((n + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream),
@@ -330,6 +369,26 @@ int lutvq_decode_attention_ll(lutvq_shard_t* h, int q_slot, int k_slot, int v_sl
         ll.seq[k] = seqs[k];
     }
     LUTVQ_REQUIRE((size_t)n_heads * head_dim <= cap, "q (%d values) exceeds the gather slot (%zu rows)", n_heads * head_dim, cap);
+    return attention_impl(nullptr, nullptr, nullptr, kcache, vcache, pos, out, n_heads, n_kv_heads, head_dim, max_seq, rope_theta, stream, ll);
+}
+
+// The same with the attention output ALSO written as LL words into the local slot out_slot (sequence number out_seq).
+int lutvq_decode_attention_ll_out(lutvq_shard_t* h, int q_slot, int k_slot, int v_slot, unsigned q_seq, unsigned k_seq, unsigned v_seq,
+                                  void* kcache, void* vcache, const int* pos, void* out, int out_slot, unsigned out_seq, int n_heads,
+                                  int n_kv_heads, int head_dim, int max_seq, float rope_theta, void* stream) {
+    LLIn ll;
+    size_t cap = 0;
+    const int slots[3] = {q_slot, k_slot, v_slot};
+    const unsigned seqs[3] = {q_seq, k_seq, v_seq};
+    for (int k = 0; k < 3; ++k) {
+        if (int rc = shard_ll_input(h, slots[k], &ll.w[k], &ll.tick, &ll.error, &cap)) return rc;
+        ll.seq[k] = seqs[k];
+    }
+    const uint32_t* ow = nullptr;
+    if (int rc = shard_ll_input(h, out_slot, &ow, &ll.tick, &ll.error, &cap)) return rc;
+    LUTVQ_REQUIRE((size_t)n_heads * head_dim <= cap, "q (%d values) exceeds the gather slot (%zu rows)", n_heads * head_dim, cap);
+    ll.out = const_cast<uint32_t*>(ow);
+    ll.out_seq = out_seq;
     return attention_impl(nullptr, nullptr, nullptr, kcache, vcache, pos, out, n_heads, n_kv_heads, head_dim, max_seq, rope_theta, stream, ll);
 }
 

@@ -447,6 +447,23 @@ lut_gemv_2x8_kernel(const GemvParams p) {
     __shared__ __align__(16) uint4 xs[kSliceGroups];
     auto load_x_slice = [&](int ks_) {
         if (threadIdx.x < kSliceGroups) {
+            if (NCB == 2 && p.ll.x_ll != nullptr && (p.flags & LUTVQ_FLAG_X_READY)) {
+                // dataflow launch: the words may be several microseconds away and EVERY CTA of the launch (and of the launches
+                // queued behind it) waits for the same few lines.  One lane polls one word, with a pause between polls, the rest
+                // of the warp waits at the barrier.  (All 32 lanes of every CTA polling at full rate saturate the L2 slice that
+                // holds the lines and hold up the very stores they wait for: 2.0 ms per 7B token instead of 1.2.)
+                if (threadIdx.x == 0) {
+                    const unsigned ep0 = ll_epoch16(*p.ll.tick, p.ll.x_seq);
+                    const uint32_t* w0 = p.ll.x_ll + (size_t)min(ks_ * kSliceGroups, p.G - 1) * 8;
+                    for (unsigned spin = 0; spin < (1u << 18); ++spin) {
+                        uint32_t v0;
+                        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v0) : "l"(w0) : "memory");
+                        if ((v0 >> 16) == ep0) break;
+                        __nanosleep(250u);
+                    }
+                }
+                __syncwarp();
+            }
             const int g = ks_ * kSliceGroups + (int)threadIdx.x;
             uint4 v = make_uint4(0u, 0u, 0u, 0u);
             if (g < p.G) {
@@ -821,7 +838,7 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
         // (different register / occupancy footprints) costs the PDL overlap: Llama-2-7B layer, 4 GEMV launches chained:
         // 51.7 us mixed, 36.6 all 3-CTA, 31.0 all 2-CTA (tools/decode_parts.py).
         t.nw = 8;
-        if (p.n_k <= 24 && (p.flags & LUTVQ_FLAG_X_READY)) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
+        if (p.n_k <= 24 && (p.flags & LUTVQ_FLAG_X_READY) && p.ll.x_ll == nullptr) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
     }
     if (t.nw == 8 && t.pf == 1 && t.pa == 1)  return launch_variant<DT, PACKED, 8, 1, 1, 3>(p, grid, smem, stream, pdl);   // 3 CTAs / SM
     if (t.nw == 8 && t.pf == 2 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 2, 2, 2>(p, grid, smem, stream, pdl);   // 2 CTAs / SM, deeper ring
@@ -884,7 +901,10 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
     LUTVQ_REQUIRE(n >= 1 && n <= kMaxProblems, "a group holds 1..%d linears, got %d", kMaxProblems, n);
     // An independent (X_READY) ring fills the SMs by overlapping consecutive launches, one worker per SM each.  A dependent
     // launch runs alone: it may be planned over g_dep_workers_per_sm workers per SM (2 fit with the 2-CTA variant).
-    const int workers = di.sm_count * ((flags & LUTVQ_FLAG_X_READY) ? 1 : g_dep_workers_per_sm);
+    // A dataflow launch (X_READY with LL activations, shard.cu) is a link of a dependent chain too: only one of the co-resident
+    // launches has its data at any time, so it is planned -- and tuned -- like a dependent launch.
+    const bool independent = (flags & LUTVQ_FLAG_X_READY) && !(ll && ll->x_ll);
+    const int workers = di.sm_count * (independent ? 1 : g_dep_workers_per_sm);
     LUTVQ_REQUIRE(n == 1 || workers <= kRangeTable, "grouped launches need the tabulated plan (<= %d workers)", kRangeTable);
     LUTVQ_REQUIRE(n == 1 || push == nullptr, "the fused push epilogue takes one linear per launch");
     const int G = I / 8;

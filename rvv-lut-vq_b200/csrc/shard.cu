@@ -447,7 +447,10 @@ int lutvq_sharded_matmat_group_ll(lutvq_shard_t* h, int n, const int* out_slots,
     LUTVQ_REQUIRE(n >= 1 && n <= 3, "a group holds 1..3 linears, got %d", n);
     LUTVQ_REQUIRE(out_slots && row_offsets && out_seq && packed && codebooks && rows_local, "null pointer");
     LUTVQ_REQUIRE(prob_k > 0 && prob_k % 64 == 0, "bad prob_k=%d", prob_k);
-    LUTVQ_REQUIRE(!(flags & (LUTVQ_FLAG_PUSH_EPILOGUE | LUTVQ_FLAG_X_READY)), "LL launches are dependent launches without the flag-based push");
+    LUTVQ_REQUIRE(!(flags & LUTVQ_FLAG_PUSH_EPILOGUE), "LL launches do not take the flag-based push");
+    // X_READY on an LL launch = "dataflow launch": the activations are LL words, which carry their own validity, so the kernel
+    // does not wait for the launch before it to complete before reading them (it polls); it still orders its stores behind it.
+    LUTVQ_REQUIRE(!(flags & LUTVQ_FLAG_X_READY) || x_slot >= 0, "LUTVQ_FLAG_X_READY on an LL launch needs the activations as LL words (x_slot >= 0)");
     LUTVQ_REQUIRE((x != nullptr) != (x_slot >= 0), "exactly one of x / x_slot");
     LUTVQ_REQUIRE(gate_slot < 0 || x_slot >= 0, "an LL gate needs an LL x");
     if (dtype != LUTVQ_F16 && dtype != LUTVQ_BF16) return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);

@@ -10,6 +10,7 @@ Every linear goes through liblutvq's C-ABI: ``lutvq_code2x8_matmat_packed`` on o
 from __future__ import annotations
 
 import ctypes
+import os
 from dataclasses import dataclass
 from typing import List, Optional
 
@@ -74,9 +75,11 @@ class _Linear:
 class Decoder:
     def __init__(self, cfg: DecoderConfig, device, world: int = 1, rank: int = 0, group: Optional[ShardGroup] = None,
                  max_seq: int = 512, seed: int = 0, exchange: str = "push", pg=None, keep_codes: bool = False, grouped: bool = True, fuse_swiglu: bool = True,
-                 skeleton: bool = False):
+                 skeleton: bool = False, dataflow: Optional[bool] = None):
         self.cfg, self.dev, self.world, self.rank, self.group, self.max_seq = cfg, torch.device(device), world, rank, group, max_seq
         self.exchange, self.pg, self.grouped = exchange, pg, grouped
+        # LL exchange: GEMVs as dataflow launches (_step_ll_dataflow).  Off by default: measured slower
+        self.dataflow = (os.environ.get("LUTVQ_LL_DATAFLOW", "0") != "0") if dataflow is None else bool(dataflow)
         self.fuse_swiglu = fuse_swiglu and grouped and not (world > 1 and exchange == "nccl")
         if (world > 1 and exchange == "push") or exchange == "ll":
             assert group is not None
@@ -216,8 +219,9 @@ class Decoder:
         self._ll_seq += 1
         return s, self._ll_seq
 
-    def _group_ll(self, L, names, x=None, x_ll=None, gate_ll=None):
-        """-> [(slot, seq)] of the outputs; x: plain tensor, or x_ll / gate_ll = (slot, seq) of earlier exchanges"""
+    def _group_ll(self, L, names, x=None, x_ll=None, gate_ll=None, dataflow=False):
+        """-> [(slot, seq)] of the outputs; x: plain tensor, or x_ll / gate_ll = (slot, seq) of earlier exchanges.
+        dataflow (x_ll only): the launch does not wait for the launch before it -- it polls its LL activations (lutvq.h)"""
         lins = [L[k] for k in names]
         outs = [self._ll_next() for _ in names]
         n = len(names)
@@ -231,9 +235,40 @@ class Decoder:
         _lib.check(self.lib.lutvq_sharded_matmat_group_ll(
             self.group._h, n, sl, ro, sq, None if x is None else ctypes.c_void_p(x.data_ptr()), xs, xq, gs, gq,
             arr([l.packed for l in lins]), arr([l.codebooks for l in lins]), arr([l.scales for l in lins]), arr([None] * n), rl,
-            lins[0].in_f, 0, 0, self._next_ws(), self.ws_need, self._st()))
+            lins[0].in_f, 0, _lib.FLAG_X_READY if (dataflow and x_ll is not None) else 0, self._next_ws(), self.ws_need, self._st()))
         self.launches_per_token += 1
         return outs
+
+    def _step_ll_dataflow(self):
+        """_step_ll with every GEMV a dataflow launch: the glue kernels also write their outputs as LL words (local slots), so each
+        GEMV streams its codes and builds its LUT as soon as the words arrive instead of after the kernel before it has completed
+        (and the launch gap after that).  The glue kernels keep their dependency wait: completion stays transitive."""
+        cfg, lib, P, st, h = self.cfg, self.lib, (lambda t: ctypes.c_void_p(t.data_ptr())), self._st, self.group._h
+        self._ll_slot, self._ll_seq = 0, 0
+        _lib.check(lib.lutvq_shard_ll_tick(h, st()))
+        self.resid.copy_(torch.index_select(self.embed, 0, self.token)[0])
+        delta = (-1, 0)
+        for L in self.layers:
+            n1 = self._ll_next()
+            _lib.check(lib.lutvq_decode_add_rmsnorm_ll_out(h, P(self.resid), delta[0], delta[1], P(L["norm1"]), P(self.normed), n1[0], n1[1],
+                                                           cfg.hidden, cfg.eps, st()))
+            q, k, v = self._group_ll(L, ["q", "k", "v"], x_ll=n1, dataflow=True)
+            ao = self._ll_next()
+            _lib.check(lib.lutvq_decode_attention_ll_out(h, q[0], k[0], v[0], q[1], k[1], v[1], P(L["kcache"]), P(L["vcache"]), P(self.pos),
+                                                         P(self.attn_out), ao[0], ao[1], cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, self.max_seq,
+                                                         cfg.rope_theta, st()))
+            (o,) = self._group_ll(L, ["o"], x_ll=ao, dataflow=True)
+            n2 = self._ll_next()
+            _lib.check(lib.lutvq_decode_add_rmsnorm_ll_out(h, P(self.resid), o[0], o[1], P(L["norm2"]), P(self.normed), n2[0], n2[1],
+                                                           cfg.hidden, cfg.eps, st()))
+            gate, up = self._group_ll(L, ["gate", "up"], x_ll=n2, dataflow=True)
+            (delta,) = self._group_ll(L, ["down"], x_ll=up, gate_ll=gate, dataflow=True)
+            self.launches_per_token += 3
+        _lib.check(lib.lutvq_decode_add_rmsnorm_ll(h, P(self.resid), delta[0], delta[1], P(self.final_norm), P(self.normed), cfg.hidden, cfg.eps, st()))
+        torch.mv(self.lm_head, self.normed, out=self.logits)
+        self.token.copy_(torch.argmax(self.logits).reshape(1))
+        self.pos.add_(1)
+        self.launches_per_token += 3
 
     def _step_ll(self):
         cfg, lib, P, st, h = self.cfg, self.lib, (lambda t: ctypes.c_void_p(t.data_ptr())), self._st, self.group._h
@@ -263,7 +298,7 @@ class Decoder:
     def step(self):
         """one token: reads self.token / self.pos, writes self.logits and the next token"""
         if self.exchange == "ll":
-            return self._step_ll()
+            return self._step_ll_dataflow() if self.dataflow else self._step_ll()
         cfg, lib, P = self.cfg, self.lib, (lambda t: ctypes.c_void_p(t.data_ptr()))
         st = self._st
         self.resid.copy_(torch.index_select(self.embed, 0, self.token)[0])

@@ -209,15 +209,18 @@ def test_ll_poll_times_out_instead_of_hanging():
     b.close()
 
 
-def test_decode_ll_mode_equals_plain_mode():
-    """Decoder(exchange="ll") -- every linear's output as LL words, every consumer polling them -- produces the same tokens and
+@pytest.mark.parametrize("dataflow", [False, True])
+def test_decode_ll_mode_equals_plain_mode(dataflow):
+    """dataflow: the GEMVs are dataflow launches (they poll their LL activations instead of waiting for the launch before them; the
+    glue kernels write their outputs as LL words too).
+    Decoder(exchange="ll") -- every linear's output as LL words, every consumer polling them -- produces the same tokens and
     logits, bit for bit, as the plain single-GPU decoder (same kernels, same arithmetic; only the operand plumbing differs)"""
     from rvv_lut_vq_b200.decode import Decoder, TINY
     from rvv_lut_vq_b200.sharded import ShardGroup
     dev = torch.device("cuda", 0)
     plain = Decoder(TINY, dev, max_seq=64, seed=5)
     group = ShardGroup(1, 0, max(TINY.intermediate, TINY.hidden), n_slots=8)
-    ll = Decoder(TINY, dev, world=1, rank=0, group=group, max_seq=64, seed=5, exchange="ll")
+    ll = Decoder(TINY, dev, world=1, rank=0, group=group, max_seq=64, seed=5, exchange="ll", dataflow=dataflow)
     st = torch.cuda.Stream()
     for dec in (plain, ll):
         dec.reset(1)

@@ -20,6 +20,9 @@ def main():
     ap.add_argument("--exchange", default="ll", choices=["ll", "push", "nccl"])
     ap.add_argument("--ungrouped", action="store_true", help="one launch per linear instead of grouped q/k/v and gate/up launches")
     ap.add_argument("--unfused-swiglu", action="store_true", help="separate silu*up launch instead of the fused down_proj activation load")
+    ap.add_argument("--plain", action="store_true", help="one GPU: plain dependent launches instead of the LL hand-over")
+    ap.add_argument("--dataflow", action="store_true", help="LL exchange with the GEMVs as dataflow launches (they poll their LL activations instead of waiting)")
+    ap.add_argument("--tuning", default="", help="nw,pf,pa for every GEMV (lutvq_debug_set_gemv_tuning)")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (memory-bounded experiments)")
     args = ap.parse_args()
     import torch.distributed as dist
@@ -36,8 +39,18 @@ def main():
     if args.layers:
         import dataclasses
         cfg = dataclasses.replace(cfg, n_layers=args.layers)
-    group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=8) if (world > 1 and args.exchange in ("push", "ll")) else None
-    dec = Decoder(cfg, dev, world, rank, group, max_seq=args.tokens + 16, exchange=args.exchange, grouped=not args.ungrouped, fuse_swiglu=not args.unfused_swiglu)
+    if world > 1 and args.exchange in ("push", "ll"):
+        group = ShardGroup.from_process_group(max(cfg.intermediate, cfg.hidden), n_slots=16)
+    elif world == 1 and args.exchange == "ll" and not args.plain:
+        group = ShardGroup(1, 0, max(cfg.intermediate, cfg.hidden), n_slots=16)       # one rank: the LL words are the kernel-to-kernel hand-over
+    else:
+        group = None
+    if args.tuning:
+        import rvv_lut_vq_b200 as r
+        r.lib().lutvq_debug_set_gemv_tuning(*[int(v) for v in args.tuning.split(",")])
+    exchange = args.exchange if group is not None or world > 1 else "push"
+    dec = Decoder(cfg, dev, world, rank, group, max_seq=args.tokens + 16, exchange=exchange, grouped=not args.ungrouped, fuse_swiglu=not args.unfused_swiglu,
+                  dataflow=args.dataflow)
     st = torch.cuda.Stream()
     dec.reset(1)
     dec.capture(st)
@@ -68,7 +81,7 @@ def main():
             peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))["hbm_gbs"]
         except Exception:
             pass
-        print(json.dumps({"metric": "decode_tok_per_s", "model": cfg.name, "layers": cfg.n_layers, "n_gpus": world, "exchange": args.exchange if world > 1 else None, "grouped_launches": not args.ungrouped, "fused_swiglu": dec.fuse_swiglu,
+        print(json.dumps({"metric": "decode_tok_per_s", "model": cfg.name, "layers": cfg.n_layers, "n_gpus": world, "exchange": exchange if group is not None or world > 1 else None, "dataflow": bool(dec.dataflow and exchange == "ll"), "tuning": args.tuning or None, "grouped_launches": not args.ungrouped, "fused_swiglu": dec.fuse_swiglu,
                           "value": 1e6 / us_tok, "unit": "tok/s", "us_per_token": us_tok, "tokens": args.tokens, "batch": 1,
                           "launches_per_token": dec.launches_per_token, "graph": dec.graph is not None,
                           "gemv_code_stream_bytes_per_token": gemv_bytes,
