@@ -90,11 +90,12 @@ size_t lutvq_workspace_bytes_ex(int prob_m, int prob_k, int max_batch);
  * x        dtype [prob_k]                 (16-byte aligned: Code2x8MatVec reads it as int4 too, cuda_kernel.cu:147)
  * y        dtype [prob_m]
  * codebook dtype [2][256][8]
- * Arithmetic: LUT entries L = C . x_group from tensor-core MMAs (fp32 accumulate), stored as 16-bit fixed point with ONE
- * scale per GEMV (step = max_k|C_k|_2 * max_g|x_g|_2 / 32704, finer than the fp16 LUT of vq.py:285); the gather adds
- * integers (exact, order-free => bit-reproducible); one rounding to dtype.  Tolerance (tests): max|y - y64| <= 1e-3 *
- * max|y64| against the float64 evaluation of the same operands.  prob_k <= 32256 (63 k-slices of 512 activations).
- * Non-finite activations or codebooks make EVERY output NaN (the reference propagates them row by row). */
+ * Arithmetic: LUT entries L = C . x_group from tensor-core MMAs (fp32 accumulate), stored as fixed point with one power-of-two
+ * scale per k-slice of 256 activations (|L * 2^e| <= 2^22: about 22 significant bits, far finer than the fp16 LUT of vq.py:285);
+ * the gather adds integers and the k-slices of a row meet in a 64-bit fixed-point word (exact, order-free => bit-reproducible);
+ * one rounding to dtype.  Tolerance (tests): max|y - y64| <= 1e-3 * max|y64| against the float64 evaluation of the same
+ * operands.  prob_k <= 65280 (255 k-slices).  A non-finite activation or codebook entry saturates the rows it touches to +-inf
+ * (the reference's FMA chain yields NaN there). */
 int lutvq_code2x8_matvec(const void* codes, const void* x, void* y, const void* codebook,
                          int prob_m, int prob_k, int dtype, void* ws, size_t ws_bytes, void* stream);
 

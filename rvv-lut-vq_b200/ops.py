@@ -182,7 +182,9 @@ def _matmat(fn_name: str, input, codes, codebooks, scales, bias, flags: Optional
 def code2x8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
                    bias: Optional[torch.Tensor] = None, *, lut_fp16: bool = False, x_ready: bool = False) -> torch.Tensor:
     """cuda_kernel.cpp:387-421 (+ epilogue :95-111): the decode / small-batch path (fused LUT-GEMV per row).
-    ``x_ready``: LUTVQ_FLAG_X_READY (input not produced by the kernel just before this call on the stream)."""
+    ``x_ready``: LUTVQ_FLAG_X_READY -- the caller's promise of include/lutvq.h: the input was COMPLETE before the whole run of
+    back-to-back launches this call belongs to started ("not produced by the kernel right before" is NOT enough: with
+    producer -> A -> B(x_ready), B can read x before the producer has finished), and the workspace ring is not shared."""
     flags = (_lib.FLAG_LUT_FP16 if lut_fp16 else 0) | (_lib.FLAG_X_READY if x_ready else 0)
     if flags:
         return _matmat("lutvq_code2x8_matmat_ex", input, codes, codebooks, scales, bias, flags)
