@@ -17,12 +17,15 @@
 
 namespace lutvq {
 
-constexpr int k1x16Warps = 8;
+constexpr int k1x16Warps = 16;               // 16 rows per CTA trip: half as many copies of x into shared memory as with 8
 constexpr int k1x16MaxBatch = 4;
 
-__device__ __forceinline__ uint4 ldg_nc_u128(const void* p) {      // read-only path; L1 may keep hot codebook rows
+// codebook rows: 16 random bytes out of 1-2 MiB per code.  They are served by L2; letting them allocate in L1 (ld.global.nc)
+// streams whole sectors through a cache that cannot hold the table -- measured 15 / 28 / 39 us per GEMV on the three 7B shapes where
+// the reference's kernel, which bypasses L1 (cuda_kernel.cu:48-50), takes 12.5 / 26.6 / 27.6.
+__device__ __forceinline__ uint4 ldg_nc_u128(const void* p) {
     uint4 r;
-    asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    asm volatile("ld.global.cg.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
 template <int DT> __device__ __forceinline__ float2 cvt2(uint32_t w);
@@ -42,11 +45,18 @@ template <int DT> __device__ __forceinline__ float dot8(const uint4& c, const ui
 // pieces), so the lane stride is 8V + 1 pieces = an odd multiple of 4 banks and a quarter warp covers all 32 banks
 template <int V> __device__ __forceinline__ uint32_t xpad(uint32_t v) { return (v + (v / (8u * V))) * 16u; }
 
-template <int DT, int GS, int NB>
-__global__ void __launch_bounds__(k1x16Warps * 32)
+static int g_1x16_mode = 0;      // experiments (fp16, group 8, one row): 1 = the reference's HFMA2 arithmetic, 2 = gather only (no math)
+void code1x16_set_mode(int m) { g_1x16_mode = m; }
+static int g_1x16_split = 0, g_1x16_per_sm = 0;      // experiments: override the launch plan (0 = automatic)
+void code1x16_set_plan(int split, int per_sm) { g_1x16_split = split; g_1x16_per_sm = per_sm; }
+
+// `split` (1, 2 or 4) warps share one output row (contiguous K ranges, partial sums through shared memory): layers with few rows per
+// SM would otherwise leave the SM with too few gathers in flight (the kernel is bound by the latency of the codebook gather).
+template <int DT, int GS, int NB, int MODE = 0>
+__global__ void __launch_bounds__(k1x16Warps * 32, (NB == 1 && GS == 8) ? 3 : 1)
 code1x16_gemv_kernel(const uint16_t* __restrict__ codes, const void* __restrict__ x, void* __restrict__ y,
                      const uint4* __restrict__ codebook, const void* __restrict__ scales, const void* __restrict__ bias,
-                     int O, int G, int I, int nb, int raw) {
+                     int O, int G, int I, int nb, int raw, int split) {
     using D = Dtype<DT>;
     using T = typename D::T;
     extern __shared__ __align__(16) uint8_t sx[];
@@ -61,13 +71,21 @@ code1x16_gemv_kernel(const uint16_t* __restrict__ codes, const void* __restrict_
     }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int n_warps = gridDim.x * k1x16Warps;
-    for (int row = blockIdx.x * k1x16Warps + warp; row < O; row += n_warps) {
-        const uint16_t* crow = codes + (size_t)row * G;
+    // balanced contiguous row ranges: CTA c owns rows [c * O / grid, (c + 1) * O / grid), its warps take them in turn
+    const int row0 = (int)((long long)blockIdx.x * O / gridDim.x), row1 = (int)((long long)(blockIdx.x + 1) * O / gridDim.x);
+    __shared__ float red[k1x16Warps][NB];
+    const int teams = k1x16Warps / split, team = warp / split, part = warp - team * split;
+    const int chunks = G / 8, cpp = ((chunks + split - 1) / split + 31) / 32 * 32;       // 8-code chunks per part: whole warp iterations
+    const int g_begin = part * cpp * 8, g_end = min(G, (part + 1) * cpp * 8);
+    const int n_trips = (row1 - row0 + teams - 1) / teams;                             // uniform over the CTA (barriers below)
+    for (int trip = 0; trip < n_trips; ++trip) {
+        const int row = row0 + trip * teams + team;
+        const bool valid = row < row1;
+        const uint16_t* crow = codes + (size_t)(valid ? row : row0) * G;
         float acc[NB];
         #pragma unroll
         for (int b = 0; b < NB; ++b) acc[b] = 0.f;
-        for (int g0 = lane * 8; g0 < G; g0 += 256) {
+        for (int g0 = g_begin + lane * 8; valid && g0 < g_end; g0 += 256) {
             // 8 codes = one 128-bit load when the row allows it (G % 8 == 0 is required by the host)
             const uint4 cw = ldg_stream_u128(crow + g0);
             const uint32_t w[4] = {cw.x, cw.y, cw.z, cw.w};
@@ -83,17 +101,43 @@ code1x16_gemv_kernel(const uint16_t* __restrict__ codes, const void* __restrict_
                 #pragma unroll
                 for (int v = 0; v < V; ++v) {
                     const uint32_t off = xpad<V>((uint32_t)((g0 + i) * V + v));
+                    if (MODE == 2) { acc[0] += __uint_as_float((cb[i][v].x ^ cb[i][v].y ^ cb[i][v].z ^ cb[i][v].w) & 0x3f800000u); continue; }
+                    if (MODE == 1) {
+                        const uint4 xv = *reinterpret_cast<const uint4*>(sx + off);
+                        const __half2* a = reinterpret_cast<const __half2*>(&cb[i][v]);
+                        const __half2* bb = reinterpret_cast<const __half2*>(&xv);
+                        __half2 r2 = __hmul2(a[0], bb[0]);
+                        r2 = __hfma2(a[1], bb[1], r2); r2 = __hfma2(a[2], bb[2], r2); r2 = __hfma2(a[3], bb[3], r2);
+                        acc[0] += __half2float(r2.x) + __half2float(r2.y);
+                        continue;
+                    }
                     #pragma unroll
                     for (int b = 0; b < NB; ++b) acc[b] = dot8<DT>(cb[i][v], *reinterpret_cast<const uint4*>(sx + b * row_stride + off), acc[b]);
                 }
         }
         #pragma unroll
         for (int b = 0; b < NB; ++b) {
-            float a = acc[b];
             #pragma unroll
-            for (int s = 16; s > 0; s >>= 1) a += __shfl_xor_sync(0xffffffffu, a, s);
-            if (lane == 0 && b < nb) {
-                T r = D::from_f(a);                                                        // Code1x16MatVec writes round(acc) (cuda_kernel.cu:86-92)
+            for (int s_ = 16; s_ > 0; s_ >>= 1) acc[b] += __shfl_xor_sync(0xffffffffu, acc[b], s_);
+        }
+        if (split > 1) {                                                                   // uniform over the grid
+            if (lane == 0) {
+                #pragma unroll
+                for (int b = 0; b < NB; ++b) red[warp][b] = acc[b];
+            }
+            __syncthreads();
+            if (part == 0 && lane == 0) {
+                #pragma unroll
+                for (int b = 0; b < NB; ++b)
+                    for (int q = 1; q < split; ++q) acc[b] += red[warp + q][b];               // fixed order: deterministic
+            }
+            __syncthreads();
+        }
+        if (valid && part == 0 && lane == 0) {
+            #pragma unroll
+            for (int b = 0; b < NB; ++b) {
+                if (b >= nb) break;
+                T r = D::from_f(acc[b]);                                                   // Code1x16MatVec writes round(acc) (cuda_kernel.cu:86-92)
                 if (!raw) {
                     if (scales) r = D::mul(r, static_cast<const T*>(scales)[row]);         // flat_output *= scales (cuda_kernel.cpp:101)
                     if (bias)   r = D::add(r, static_cast<const T*>(bias)[row]);           // flat_output += bias   (cuda_kernel.cpp:103)
@@ -134,15 +178,25 @@ template <int DT, int GS, int NB>
 static int launch_gemv(const void* codes, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
                        int O, int I, int nb, int raw, cudaStream_t stream, const DeviceInfo& di) {
     auto kern = code1x16_gemv_kernel<DT, GS, NB>;
+    if (DT == LUTVQ_F16 && GS == 8 && NB == 1 && g_1x16_mode == 1) kern = code1x16_gemv_kernel<DT, GS, NB, (DT == LUTVQ_F16 && GS == 8 && NB == 1) ? 1 : 0>;
+    if (DT == LUTVQ_F16 && GS == 8 && NB == 1 && g_1x16_mode == 2) kern = code1x16_gemv_kernel<DT, GS, NB, (DT == LUTVQ_F16 && GS == 8 && NB == 1) ? 2 : 0>;
     const int n_v = I / 8;
     const size_t smem = (size_t)NB * ((size_t)(n_v + (n_v >> 3)) * 16 + 16);
     if (smem > 48 * 1024) {
         LUTVQ_REQUIRE(smem <= di.smem_optin, "prob_k=%d needs %zu bytes of shared memory for x (limit %zu)", I, smem, di.smem_optin);
         LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
-    int ctas = ceil_div(O, k1x16Warps);
-    const int cap = di.sm_count * (NB == 1 ? 6 : 3);
-    if (ctas > cap) ctas = cap;
+    // Launch plan, measured on B200 (tools/sweep_1x16.py, us per GEMV at 4096->4096 / 4096->11008 / 11008->4096, fp16, group 8):
+    // exactly as many CTAs per SM as are resident (3 x 16 warps at <= 42 registers) = one full wave with balanced row ranges:
+    // 11.2 / 24.3 / 25.8; 2 per SM: 14.6 / 35.1 / 35.1; 6 per SM: 14.1 / 25.5 / 31.6; rows split over 2 or 4 warps: never better.
+    // (The reference's Code1x16MatVec on the same GPU: 12.5 / 26.5 / 27.6.)
+    int split = 1;
+    if (g_1x16_split == 1 || g_1x16_split == 2 || g_1x16_split == 4) split = g_1x16_split;
+    while (split > 1 && (I / GS) / split < 256) split >>= 1;
+    int per_sm = NB == 1 ? 3 : 2;
+    if (g_1x16_per_sm > 0) per_sm = g_1x16_per_sm;
+    int ctas = di.sm_count * per_sm;
+    if (ctas > O) ctas = O;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(k1x16Warps * 32); cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -150,7 +204,7 @@ static int launch_gemv(const void* codes, const void* x, void* y, const void* co
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
     LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, static_cast<const uint16_t*>(codes), x, y, static_cast<const uint4*>(codebook), scales, bias,
-                                     O, I / GS, I, nb, raw));
+                                     O, I / GS, I, nb, raw, split));
     return LUTVQ_OK;
 }
 
@@ -186,6 +240,9 @@ static int check_1x16(const void* codes, const void* codebook, int O, int I, int
 using namespace lutvq;
 
 extern "C" {
+
+void lutvq_debug_set_1x16_mode(int mode) { code1x16_set_mode(mode); }
+void lutvq_debug_set_1x16_plan(int split, int per_sm) { code1x16_set_plan(split, per_sm); }
 
 int lutvq_code1x16_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias, void* y,
                           int batch, int prob_m, int prob_k, int group_size, int dtype, void* stream) {
