@@ -12,7 +12,7 @@ int gemv_2x8_launch(const void* packed, const void* x, void* y, const void* code
                     const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes,
                     cudaStream_t stream, const GemvPush* push = nullptr);
 int gemv_2x8_launch_rows(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
-                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream);
+                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream, int ncb = 2);
 int gemv_max_rows_per_launch();
 size_t gemv_rows_workspace_bytes(int rows, int O);
 int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,

@@ -971,7 +971,7 @@ static int gemv_launch_impl(int n, const GemvItem* items, int packed, const void
     p.tl = (g_timeline && W_total <= 256) ? g_timeline + (size_t)(g_timeline_seq++ % 64) * 256 * 16 : nullptr;
     const size_t smem = kSliceBytes;
     if (ncb != 2) {
-        LUTVQ_REQUIRE(!packed && n == 1, "Kx8 formats other than 2x8 run on reference-layout codes, one linear per launch");
+        LUTVQ_REQUIRE(!packed, "Kx8 formats other than 2x8 run on reference-layout codes");
         if (dtype == LUTVQ_F16)  return launch_kx8<LUTVQ_F16>(p, ncb, W_total, smem, stream, pdl);
         if (dtype == LUTVQ_BF16) return launch_kx8<LUTVQ_BF16>(p, ncb, W_total, smem, stream, pdl);
         return fail(LUTVQ_EUNSUPPORTED, "dtype %d not supported (fp16=0, bf16=1)", dtype);
@@ -1018,12 +1018,12 @@ int gemv_kx8_launch_ref(const void* codes, const void* x, void* y, const void* c
 // paid once per launch instead of once per row.  Workspace: gemv_rows_workspace_bytes(rows, O).  Results are bit-identical to
 // `rows` single-row launches (integer split-k sums).
 int gemv_2x8_launch_rows(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
-                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream) {
+                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream, int ncb) {
     LUTVQ_REQUIRE(rows >= 1 && rows <= kMaxProblems, "1..%d rows per launch, got %d", kMaxProblems, rows);
     GemvItem items[kMaxProblems];
     for (int b = 0; b < rows; ++b)
         items[b] = GemvItem{codes, codebook, static_cast<uint8_t*>(y) + (size_t)b * O * 2, scales, bias, O, (size_t)b * I * 2};
-    return gemv_launch_impl(rows, items, packed, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr);
+    return gemv_launch_impl(rows, items, packed, x, nullptr, I, dtype, flags, ws, ws_bytes, stream, nullptr, nullptr, ncb);
 }
 int gemv_max_rows_per_launch() { return kMaxProblems; }
 size_t gemv_rows_workspace_bytes(int rows, int O) {

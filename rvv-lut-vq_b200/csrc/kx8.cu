@@ -18,6 +18,10 @@ int lut_build_launch(const void* x, const void* codebook, void* lut, int M, int 
 int lut_gemv_launch(const void* codeword, const void* lut, void* out, int d_out, int M, int N, int K,
                     int lut_is_fp32, int acc_mode, cudaStream_t stream);
 size_t gemv_workspace_bytes(int O, int G);
+int gemv_2x8_launch_rows(const void* codes, int packed, const void* x, void* y, const void* codebook, const void* scales, const void* bias,
+                         int rows, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream, int ncb);
+int gemv_max_rows_per_launch();
+size_t gemv_rows_workspace_bytes(int rows, int O);
 int gemv_2x8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
                         const void* bias, int O, int I, int dtype, unsigned flags, void* ws, size_t ws_bytes, cudaStream_t stream);
 int gemv_kx8_launch_ref(const void* codes, const void* x, void* y, const void* codebook, const void* scales,
@@ -94,7 +98,19 @@ int lutvq_codeKx8_matmat(const void* x, const void* codes, const void* codebooks
     if (int rc = get_device_info(&di)) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (fused) {
-        // one fused launch per batch row, like cuda_kernel.cpp:540-552 loops CodeKx8MatVec; scale / bias ride in the epilogue
+        // up to 8 rows per launch when the workspace holds their split-k words (as lutvq_code2x8_matmat does, lutvq.h) ...
+        const int per = batch < gemv_max_rows_per_launch() ? batch : gemv_max_rows_per_launch();
+        if (batch > 1 && ws_bytes >= gemv_rows_workspace_bytes(per, prob_m)) {
+            for (int b0 = 0; b0 < batch; b0 += per) {
+                const int nb = batch - b0 < per ? batch - b0 : per;
+                if (int rc = gemv_2x8_launch_rows(codes, 0, static_cast<const uint8_t*>(x) + (size_t)b0 * prob_k * 2,
+                                                  static_cast<uint8_t*>(y) + (size_t)b0 * prob_m * 2, codebooks, scales, bias, nb, prob_m, prob_k,
+                                                  dtype, 0u, ws, ws_bytes, st, num_codebooks))
+                    return rc;
+            }
+            return LUTVQ_OK;
+        }
+        // ... else one fused launch per batch row, like cuda_kernel.cpp:540-552 loops CodeKx8MatVec; scale / bias ride in the epilogue
         for (int b = 0; b < batch; ++b) {
             const void* xb = static_cast<const uint8_t*>(x) + (size_t)b * prob_k * 2;
             void* yb = static_cast<uint8_t*>(y) + (size_t)b * prob_m * 2;

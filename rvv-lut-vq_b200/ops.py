@@ -404,7 +404,9 @@ def codeKx8_matmat(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Te
     y = torch.empty((flat.size(0), out_features), dtype=input.dtype, device=dev)
     need = int(lib().lutvq_codeKx8_workspace_bytes(out_features, in_features, N))
     with torch.cuda.device(dev):
-        if _kx8_fused(in_features, N):
+        if _kx8_fused(in_features, N) and flat.size(0) > 1 and BATCH_GROUPED:
+            ws = batch_workspace(dev, out_features, in_features, flat.size(0))     # up to 8 rows per launch (lutvq.h)
+        elif _kx8_fused(in_features, N):
             ws = workspace(dev, out_features, in_features)          # zero-initialised split-k words, handed back zero by every call
             if ws.numel() < need:
                 ws = torch.zeros(need, dtype=torch.uint8, device=dev)

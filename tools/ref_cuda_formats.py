@@ -59,6 +59,34 @@ def main():
                 den = float(y_ref.float().abs().max())
                 print(json.dumps({"format": fmt, "shape": f"{I}->{O}", "ring": nb, "reference_us": round(us_ref, 2), "ours_us": round(us_our, 2),
                                   "speedup": round(us_ref / us_our, 2), "max_abs_diff_over_max": float((y_our.float() - y_ref.float()).abs().max()) / den, **extra}), flush=True)
+                # dequantize (+ scales) and a batch-4 call of the same format
+                if (I, O) == (4096, 11008):
+                    dq_ours = ops.code1x16_dequant if fmt == "1x16" else ops.code1x8_dequant
+                    dq_ref = ref.code1x16_dequant if fmt == "1x16" else ref.code1x8_dequant
+
+                    def dq(fn):
+                        def b():
+                            for k, c in enumerate(Ls[:8]):
+                                res[k] = fn(c, cb, sc)
+                        return b
+                    t_ref = time_graph(torch, st, dq(dq_ref), 5) / 8
+                    w_ref = res[0].clone()
+                    t_our = time_graph(torch, st, dq(dq_ours), 5) / 8
+                    print(json.dumps({"format": fmt, "op": "dequant", "shape": f"{I}x{O}", "reference_us": round(t_ref, 2), "ours_us": round(t_our, 2),
+                                      "speedup": round(t_ref / t_our, 2), "bit_identical": bool(torch.equal(res[0].view(torch.int16), w_ref.view(torch.int16)))}), flush=True)
+                    x4 = torch.randn((4, I), device=dev, generator=g).half()
+
+                    def b4(fn):
+                        def b():
+                            for k, c in enumerate(Ls):
+                                res[k] = fn(x4, c, cb, sc, None)
+                        return b
+                    t_ref = time_graph(torch, st, b4(theirs), 5) / nb
+                    y4 = res[0].clone()
+                    t_our = time_graph(torch, st, b4(ours), 5) / nb
+                    print(json.dumps({"format": fmt, "op": "matmat batch 4", "shape": f"{I}->{O}", "reference_us": round(t_ref, 2), "ours_us": round(t_our, 2),
+                                      "speedup": round(t_ref / t_our, 2),
+                                      "max_abs_diff_over_max": float((res[0].float() - y4.float()).abs().max()) / float(y4.float().abs().max())}), flush=True)
                 del Ls, res
 
 
