@@ -183,36 +183,85 @@ __global__ void __launch_bounds__(128) lut_ctor_kernel(int act_k, int8_t* __rest
     if (threadIdx.x == 0) { lut_scales[seg] = scales; lut_biases[seg] = biases; }
 }
 
-// qgemm_lut_t1_int8_m{bm}_k{K}_n1_b{bits} (kernels.cc:827-960), one CTA per tile of bm bit-plane rows, a thread per byte
-// lane: CBits stays in registers over the K/32 sequential tbl_g4_int8_float_update(k8, ak8) calls, then goes through
-// shared memory for the bit-plane combination C = ((c0 * 0.5 + c1) + c2 * 2) + c3 * 4.
-__global__ void tmac_qgemm_kernel(int K, int bits, int bm, const uint8_t* __restrict__ A, const int8_t* __restrict__ qlut,
-                                  const float* __restrict__ scales, const float* __restrict__ lut_scales,
-                                  const float* __restrict__ lut_biases, float* __restrict__ C) {
-    extern __shared__ float cbits[];
-    const int tile = blockIdx.x, kt_n = K / 32, lanes = bm / 2;
-    const TblFloatCfg g{8, bits, 8, 0, 0};
-    for (int t = threadIdx.x; t < lanes; t += blockDim.x) {
-        const int i = (t >> 4) << 4, l = t & 15;
-        float cb = 0.f, ct = 0.f;                                    // tbl_float_reset
-        for (int kt = 0; kt < kt_n; ++kt) {
-            const size_t blk = (size_t)tile * kt_n + kt;
-            float ob, ot;
-            tbl_float_lane(g, i, l, cb, ct, qlut + (size_t)kt * 128, A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8 + l,
-                           scales + blk * (size_t)(bm / bits), lut_scales + kt, lut_biases + kt, ob, ot);
-            cb = ob; ct = ot;
+// qgemm_lut_t1_int8_m{bm}_k{K}_n1_b{bits} (kernels.cc:827-960): per byte lane (two bit-plane rows) and k-block of 32 activations
+//     x = sum of 8 table lookups (int16) * lut_scale (+ lut_bias on the first bit plane);   c = fma(x, scale, c)
+// then C = ((c0 * 0.5 + c1) + c2 * 2) + c3 * 4 over the bit planes.  The fp32 chain over the k-blocks is order-dependent, the
+// lookups are not: a CTA owns 16 byte lanes (48 for 3 bits: the bit planes of an output then lie inside the CTA) and
+//   phase 1  all its threads (lane x 32 k-slots) compute x and fetch the scale for a chunk of k-blocks into shared memory,
+//   phase 2  one thread per (lane, nibble) runs the chunk's fma chain in the reference's order (loads hoisted, 4 clocks a step),
+// so the grid is M * bits / 32 CTAs instead of M * bits / bm and a lane's lookups are no longer one serial chain of K / 32 global
+// round trips (first version: 128 us per 4096 x 4096 4-bit GEMV whatever M was).  Results are bit-identical to that version.
+constexpr int kTmacThreads = 512;
+__global__ void __launch_bounds__(kTmacThreads) tmac_qgemm_kernel(int K, int bits, int bm, int nblk, int chunk, const uint8_t* __restrict__ A,
+                                                                  const int8_t* __restrict__ qlut, const float* __restrict__ scales,
+                                                                  const float* __restrict__ lut_scales, const float* __restrict__ lut_biases,
+                                                                  float* __restrict__ C) {
+    extern __shared__ float sm_f[];
+    const int LC = 16 * nblk, W = 2 * LC;                            // byte lanes and cbits of this CTA
+    float* sv = sm_f;                                                // [chunk][W]  x values
+    float* ss = sm_f + (size_t)chunk * W;                            // [chunk][W]  scales
+    __shared__ float cb[96];
+    const int ctas_per_tile = bm / 2 / LC, tile = blockIdx.x / ctas_per_tile, sub = blockIdx.x - tile * ctas_per_tile;
+    const int kt_n = K / 32, KP = kTmacThreads / LC;
+    const int ll = threadIdx.x % LC, q = threadIdx.x / LC;           // phase 1: local lane, k-slot
+    const int lane_t = sub * LC + ll, i = (lane_t >> 4) << 4, l = lane_t & 15, e = l & 7;
+    const int ib_bot = i / 4 + (l >> 3), ib_top = ib_bot + 2;
+    const bool plain_b = (ib_bot % bits) != 0, plain_t = (ib_top % bits) != 0;
+    float c = 0.f;                                                   // tbl_float_reset; phase-2 threads only
+    for (int kc = 0; kc < kt_n; kc += chunk) {
+        const int kend = min(kt_n, kc + chunk);
+        if (q < KP)
+            for (int kt = kc + q; kt < kend; kt += KP) {
+                const size_t blk = (size_t)tile * kt_n + kt;
+                const uint8_t* a = A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8 + l;
+                const int8_t* lut = qlut + (size_t)kt * 128;
+                int bot = 0, top = 0;
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const uint4 tab = ld_table(lut, k);
+                    const unsigned v = __ldg(a + k * 16);
+                    bot += lut16(tab, v & 15u);
+                    top += lut16(tab, v >> 4);
+                }
+                const float fb = (float)(int)(int16_t)bot, ft = (float)(int)(int16_t)top;
+                const float lut_s = __ldg(lut_scales + kt), lut_b = __ldg(lut_biases + kt);
+                const float* sc = scales + blk * (size_t)(bm / bits);
+                float* pv = sv + (size_t)(kt - kc) * W + 2 * ll;
+                float* ps = ss + (size_t)(kt - kc) * W + 2 * ll;
+                pv[0] = plain_b ? __fmul_rn(fb, lut_s) : fmaf(fb, lut_s, lut_b);
+                pv[1] = plain_t ? __fmul_rn(ft, lut_s) : fmaf(ft, lut_s, lut_b);
+                ps[0] = __ldg(sc + (ib_bot / bits) * 8 + e);
+                ps[1] = __ldg(sc + (ib_top / bits) * 8 + e);
+            }
+        __syncthreads();
+        if (threadIdx.x < W) {
+            const float* pv = sv + threadIdx.x;
+            const float* ps = ss + threadIdx.x;
+            const int n = kend - kc;
+            int k = 0;
+            for (; k + 8 <= n; k += 8) {
+                float v[8], sc8[8];
+                #pragma unroll
+                for (int u = 0; u < 8; ++u) { v[u] = pv[(size_t)(k + u) * W]; sc8[u] = ps[(size_t)(k + u) * W]; }
+                #pragma unroll
+                for (int u = 0; u < 8; ++u) c = fmaf(v[u], sc8[u], c);
+            }
+            for (; k < n; ++k) c = fmaf(pv[(size_t)k * W], ps[(size_t)k * W], c);
         }
-        cbits[i * 2 + l] = cb;
-        cbits[i * 2 + 16 + l] = ct;
+        __syncthreads();
+    }
+    if (threadIdx.x < W) {
+        const int lane_local = threadIdx.x >> 1, which = threadIdx.x & 1;
+        cb[(lane_local >> 4) * 32 + which * 16 + (lane_local & 15)] = c;   // cbits[i * 2 + l] (low nibble), cbits[i * 2 + 16 + l] (high)
     }
     __syncthreads();
     const float alphas[4] = {0.5f, 1.f, 2.f, 4.f};
-    const int n_out = bm / bits;
-    for (int o = threadIdx.x; o < n_out; o += blockDim.x) {
-        const int j = o >> 3, e = o & 7;
-        float acc = __fmul_rn(cbits[8 * bits * j + e], alphas[0]);
-        for (int bp = 1; bp < bits; ++bp) acc = __fadd_rn(acc, __fmul_rn(cbits[8 * bits * j + 8 * bp + e], alphas[bp]));
-        C[(size_t)tile * n_out + o] = acc;
+    const int n_out_cta = W / bits, n_out_tile = bm / bits;
+    for (int o = threadIdx.x; o < n_out_cta; o += blockDim.x) {
+        const int j = o >> 3, eo = o & 7;
+        float acc = __fmul_rn(cb[8 * bits * j + eo], alphas[0]);
+        for (int bp = 1; bp < bits; ++bp) acc = __fadd_rn(acc, __fmul_rn(cb[8 * bits * j + 8 * bp + eo], alphas[bp]));
+        C[(size_t)tile * n_out_tile + (size_t)sub * n_out_cta + o] = acc;
     }
 }
 
@@ -308,11 +357,11 @@ int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, con
     LUTVQ_REQUIRE(aligned16(qlut), "qlut must be 16-byte aligned");
     if (int rc = need_device()) return rc;
     const int tiles = (int)((long long)M * bits / bm);
-    int threads = bm / 2;
-    if (threads > 256) threads = 256;
-    threads = (threads + 31) / 32 * 32;
-    tmac_qgemm_kernel<<<tiles, threads, (size_t)bm * sizeof(float), static_cast<cudaStream_t>(stream)>>>(
-        K, bits, bm, static_cast<const uint8_t*>(A), static_cast<const int8_t*>(qlut), static_cast<const float*>(scales),
+    const int nblk = bits == 3 ? 3 : 1, LC = 16 * nblk;             // bm % (8 * bits) == 0 and bm % 32 == 0 => bm / 2 % LC == 0
+    const int chunk = nblk == 1 ? 128 : 40;                           // k-blocks per shared-memory chunk (<= 32 KiB)
+    const size_t smem = (size_t)chunk * 2 * LC * 2 * sizeof(float);
+    tmac_qgemm_kernel<<<tiles * (bm / 2 / LC), kTmacThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+        K, bits, bm, nblk, chunk, static_cast<const uint8_t*>(A), static_cast<const int8_t*>(qlut), static_cast<const float*>(scales),
         static_cast<const float*>(lut_scales), static_cast<const float*>(lut_biases), static_cast<float*>(C));
     LUTVQ_CUDA_OK(cudaGetLastError());
     return LUTVQ_OK;
