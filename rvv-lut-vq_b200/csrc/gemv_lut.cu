@@ -839,11 +839,14 @@ static int launch_tuned(const GemvParams& p, int grid, size_t smem, cudaStream_t
         // 51.7 us mixed, 36.6 all 3-CTA, 31.0 all 2-CTA (tools/decode_parts.py).
         t.nw = 8;
         if (p.n_k <= 24 && (p.flags & LUTVQ_FLAG_X_READY) && p.ll.x_ll == nullptr) { t.pf = 1; t.pa = 1; } else { t.pf = 2; t.pa = 2; }
+        // dependent launches: the split-k atomic's return is examined 4 sets later instead of 2 (ncu on a batch-8 launch: a quarter
+        // of the stall samples sat on that return): Llama-2-7B decode 812 -> 825 tok/s, batch-1 dependent 6.63 -> 6.42 us
+        if (!(p.flags & LUTVQ_FLAG_X_READY)) t.pa = 4;
     }
     if (t.nw == 8 && t.pf == 1 && t.pa == 1)  return launch_variant<DT, PACKED, 8, 1, 1, 3>(p, grid, smem, stream, pdl);   // 3 CTAs / SM
     if (t.nw == 8 && t.pf == 2 && t.pa == 2)  return launch_variant<DT, PACKED, 8, 2, 2, 2>(p, grid, smem, stream, pdl);   // 2 CTAs / SM, deeper ring
+    if (t.nw == 8 && t.pf == 2 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 2, 4>(p, grid, smem, stream, pdl);   // atomic returns examined 4 sets later
 #if LUTVQ_DBG
-    if (t.nw == 8 && t.pf == 2 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 2, 4>(p, grid, smem, stream, pdl);
     if (t.nw == 8 && t.pf == 2 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 2, 6>(p, grid, smem, stream, pdl);
     if (t.nw == 8 && t.pf == 1 && t.pa == 4)  return launch_variant<DT, PACKED, 8, 1, 4>(p, grid, smem, stream, pdl);
     if (t.nw == 8 && t.pf == 1 && t.pa == 6)  return launch_variant<DT, PACKED, 8, 1, 6>(p, grid, smem, stream, pdl);

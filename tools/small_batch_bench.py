@@ -36,9 +36,11 @@ def graph_us(st, body, reps, inner):
 def main():
     dev = torch.device("cuda:0")
     lib = r.lib()
+    if os.environ.get("GEMV_TUNING"):
+        lib.lutvq_debug_set_gemv_tuning(*[int(v) for v in os.environ["GEMV_TUNING"].split(",")])
     P = lambda t: ctypes.c_void_p(t.data_ptr())
     st = torch.cuda.Stream(dev)
-    for I, O in ((4096, 11008), (4096, 4096), (11008, 4096)):
+    for I, O in ((4096, 11008),) if os.environ.get("GEMV_TUNING") else ((4096, 11008), (4096, 4096), (11008, 4096)):
         NB = 40
         Ls = [synth.make_layer_torch(I, O, dev, seed=k, scales="randn") for k in range(NB)]
         packed = [ops.code2x8_prepack(L["codes"]) for L in Ls]
