@@ -265,6 +265,107 @@ __global__ void __launch_bounds__(kTmacThreads) tmac_qgemm_kernel(int K, int bit
     }
 }
 
+// Second version of the same kernel: phase 1 does FOUR lookups per PRMT triple (pq4.cu's trick).  A thread owns one (k-block, block of
+// 16 byte lanes): it reads the block's 128 bytes [table k][lane] as 8 x 16 bytes and the 8 tables as 8 x 16 bytes; 16 bits of a row =
+// two byte lanes = 4 codes that share table k, so  prmt(prmt(T0,T1,s&0x7777), prmt(T2,T3,s&0x7777), 0x3210|bit3<<2)  returns
+// (low, high nibble of lane 2j, low, high of lane 2j+1).  Tables are biased by +128 (xor 0x80) so the 8 results per lane add up as
+// unsigned bytes packed in one register (R += r; H += odd bytes; even sums = R - (H << 8)); 8 * 255 < 2^16, the bias 8 * 128 comes
+// off at the end.  ~3 instructions per lookup instead of ~30.  Phase 2 (the order-dependent fma chain) is unchanged.
+constexpr int kTmacV2Threads = 128;
+__global__ void __launch_bounds__(kTmacV2Threads) tmac_qgemm_v2_kernel(int K, int bits, int bm, int nblk, int chunk, const uint8_t* __restrict__ A,
+                                                                       const int8_t* __restrict__ qlut, const float* __restrict__ scales,
+                                                                       const float* __restrict__ lut_scales, const float* __restrict__ lut_biases,
+                                                                       float* __restrict__ C) {
+    extern __shared__ __align__(16) float sm_f[];
+    const int LC = 16 * nblk, W = 2 * LC, SW = (LC / 4 / bits) * 8;  // byte lanes, cbits and scale floats (per k-block) of this CTA
+    float* sv = sm_f;                                                // [chunk][W]   x values
+    float* ssc = sm_f + (size_t)chunk * W;                           // [chunk][SW]  scales
+    __shared__ float cb[96];
+    const int ctas_per_tile = bm / 2 / LC, tile = blockIdx.x / ctas_per_tile, sub = blockIdx.x - tile * ctas_per_tile;
+    const int kt_n = K / 32;
+    const int ib0 = sub * LC / 4, s0 = (ib0 / bits) * 8;            // first scale float of the CTA inside a k-block's scale row
+    // phase-2 identity of this thread: (byte lane, nibble) -> its scale column
+    const int lane2 = threadIdx.x >> 1, which = threadIdx.x & 1;
+    const int i2 = ((sub * LC + lane2) >> 4) << 4, l2 = lane2 & 15;
+    const int ib2 = i2 / 4 + (l2 >> 3) + 2 * which, soff2 = (ib2 / bits) * 8 + (l2 & 7) - s0;
+    float c = 0.f;                                                   // tbl_float_reset
+    for (int kc = 0; kc < kt_n; kc += chunk) {
+        const int kend = min(kt_n, kc + chunk), n_items = (kend - kc) * nblk;
+        for (int it = threadIdx.x; it < n_items; it += kTmacV2Threads) {
+            const int kt = kc + it / nblk, b = it - (it / nblk) * nblk;
+            const int i = sub * LC + b * 16;                         // first byte lane of the block inside the tile (multiple of 16)
+            const size_t blk = (size_t)tile * kt_n + kt;
+            const uint4* a = reinterpret_cast<const uint4*>(A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8);
+            const uint4* tabs = reinterpret_cast<const uint4*>(qlut + (size_t)kt * 128);
+            uint32_t R[8], H[8];
+            #pragma unroll
+            for (int j = 0; j < 8; ++j) R[j] = H[j] = 0u;
+            #pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                uint4 T = __ldg(tabs + k);
+                T.x ^= 0x80808080u; T.y ^= 0x80808080u; T.z ^= 0x80808080u; T.w ^= 0x80808080u;
+                const uint4 av = __ldg(a + k);
+                const uint32_t w[4] = {av.x, av.y, av.z, av.w};
+                #pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t sj = (j & 1) ? (w[j >> 1] >> 16) : w[j >> 1];
+                    const uint32_t m = sj & 0x7777u;
+                    const uint32_t r = __byte_perm(__byte_perm(T.x, T.y, m), __byte_perm(T.z, T.w, m), ((sj >> 1) & 0x4444u) | 0x3210u);
+                    R[j] += r;
+                    H[j] += __byte_perm(r, 0u, 0x4341);
+                }
+            }
+            const float lut_s = __ldg(lut_scales + kt), lut_b = __ldg(lut_biases + kt);
+            float4* out = reinterpret_cast<float4*>(sv + (size_t)(kt - kc) * W + b * 32);
+            #pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t E = R[j] - (H[j] << 8);               // even bytes: low nibbles of lanes 2j, 2j+1;  H: their high nibbles
+                const int ib_bot = i / 4 + (j >> 2), ib_top = ib_bot + 2;            // lanes 2j, 2j+1 share l >> 3 = j >> 2
+                const bool plain_b = (ib_bot % bits) != 0, plain_t = (ib_top % bits) != 0;
+                const float f0 = (float)((int)(E & 0xffffu) - 1024), f1 = (float)((int)(H[j] & 0xffffu) - 1024);
+                const float f2 = (float)((int)(E >> 16) - 1024), f3 = (float)((int)(H[j] >> 16) - 1024);
+                float4 o;
+                o.x = plain_b ? __fmul_rn(f0, lut_s) : fmaf(f0, lut_s, lut_b);
+                o.y = plain_t ? __fmul_rn(f1, lut_s) : fmaf(f1, lut_s, lut_b);
+                o.z = plain_b ? __fmul_rn(f2, lut_s) : fmaf(f2, lut_s, lut_b);
+                o.w = plain_t ? __fmul_rn(f3, lut_s) : fmaf(f3, lut_s, lut_b);
+                out[j] = o;
+            }
+            if (b == 0) {                                            // the k-block's scales of this CTA: SW contiguous floats
+                const float4* sc = reinterpret_cast<const float4*>(scales + blk * (size_t)(bm / bits) + s0);
+                float4* dst = reinterpret_cast<float4*>(ssc + (size_t)(kt - kc) * SW);
+                for (int v = 0; v < SW / 4; ++v) dst[v] = __ldg(sc + v);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < W) {
+            const float* pv = sv + threadIdx.x;
+            const float* ps = ssc + soff2;
+            const int n = kend - kc;
+            int k = 0;
+            for (; k + 8 <= n; k += 8) {
+                float v[8], sc8[8];
+                #pragma unroll
+                for (int u = 0; u < 8; ++u) { v[u] = pv[(size_t)(k + u) * W]; sc8[u] = ps[(size_t)(k + u) * SW]; }
+                #pragma unroll
+                for (int u = 0; u < 8; ++u) c = fmaf(v[u], sc8[u], c);
+            }
+            for (; k < n; ++k) c = fmaf(pv[(size_t)k * W], ps[(size_t)k * SW], c);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x < W) cb[(lane2 >> 4) * 32 + which * 16 + (lane2 & 15)] = c;   // cbits[i * 2 + l] (low nibble), cbits[i * 2 + 16 + l] (high)
+    __syncthreads();
+    const float alphas[4] = {0.5f, 1.f, 2.f, 4.f};
+    const int n_out_cta = W / bits, n_out_tile = bm / bits;
+    for (int o = threadIdx.x; o < n_out_cta; o += blockDim.x) {
+        const int j = o >> 3, eo = o & 7;
+        float acc = __fmul_rn(cb[8 * bits * j + eo], alphas[0]);
+        for (int bp = 1; bp < bits; ++bp) acc = __fadd_rn(acc, __fmul_rn(cb[8 * bits * j + 8 * bp + eo], alphas[bp]));
+        C[(size_t)tile * n_out_tile + (size_t)sub * n_out_cta + o] = acc;
+    }
+}
+
 static int need_device() {
     DeviceInfo di;
     return get_device_info(&di);                     // no device: LUTVQ_ECUDA, there is no CPU fallback
@@ -359,6 +460,15 @@ int lutvq_tmac_qgemm_lut_int8(int M, int K, int bits, int bm, const void* A, con
     const int tiles = (int)((long long)M * bits / bm);
     const int nblk = bits == 3 ? 3 : 1, LC = 16 * nblk;             // bm % (8 * bits) == 0 and bm % 32 == 0 => bm / 2 % LC == 0
     const int chunk = nblk == 1 ? 128 : 40;                           // k-blocks per shared-memory chunk (<= 32 KiB)
+    if (aligned16(A) && aligned16(scales)) {                         // 128-bit loads of the weight bytes and the scales
+        const int SW = (LC / 4 / bits) * 8;
+        const size_t smem2 = (size_t)chunk * (2 * LC + SW) * sizeof(float);
+        tmac_qgemm_v2_kernel<<<tiles * (bm / 2 / LC), kTmacV2Threads, smem2, static_cast<cudaStream_t>(stream)>>>(
+            K, bits, bm, nblk, chunk, static_cast<const uint8_t*>(A), static_cast<const int8_t*>(qlut), static_cast<const float*>(scales),
+            static_cast<const float*>(lut_scales), static_cast<const float*>(lut_biases), static_cast<float*>(C));
+        LUTVQ_CUDA_OK(cudaGetLastError());
+        return LUTVQ_OK;
+    }
     const size_t smem = (size_t)chunk * 2 * LC * 2 * sizeof(float);
     tmac_qgemm_kernel<<<tiles * (bm / 2 / LC), kTmacThreads, smem, static_cast<cudaStream_t>(stream)>>>(
         K, bits, bm, nblk, chunk, static_cast<const uint8_t*>(A), static_cast<const int8_t*>(qlut), static_cast<const float*>(scales),
