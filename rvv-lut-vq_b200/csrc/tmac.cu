@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(kTmacThreads) tmac_qgemm_kernel(int K, int bit
 // (low, high nibble of lane 2j, low, high of lane 2j+1).  Tables are biased by +128 (xor 0x80) so the 8 results per lane add up as
 // unsigned bytes packed in one register (R += r; H += odd bytes; even sums = R - (H << 8)); 8 * 255 < 2^16, the bias 8 * 128 comes
 // off at the end.  ~3 instructions per lookup instead of ~30.  Phase 2 (the order-dependent fma chain) is unchanged.
-constexpr int kTmacV2Threads = 128;
+constexpr int kTmacV2Threads = 256;
 __global__ void __launch_bounds__(kTmacV2Threads) tmac_qgemm_v2_kernel(int K, int bits, int bm, int nblk, int chunk, const uint8_t* __restrict__ A,
                                                                        const int8_t* __restrict__ qlut, const float* __restrict__ scales,
                                                                        const float* __restrict__ lut_scales, const float* __restrict__ lut_biases,
@@ -290,24 +290,27 @@ __global__ void __launch_bounds__(kTmacV2Threads) tmac_qgemm_v2_kernel(int K, in
     const int ib2 = i2 / 4 + (l2 >> 3) + 2 * which, soff2 = (ib2 / bits) * 8 + (l2 & 7) - s0;
     float c = 0.f;                                                   // tbl_float_reset
     for (int kc = 0; kc < kt_n; kc += chunk) {
-        const int kend = min(kt_n, kc + chunk), n_items = (kend - kc) * nblk;
+        // an item = (k-block, block of 16 byte lanes, half of the block): 8 lanes x 8 tables per thread -- twice the threads of a
+        // whole-block item (the grid is only M * bits / 32 CTAs: more warps per SM, not fewer instructions, is what helps here)
+        const int kend = min(kt_n, kc + chunk), n_items = (kend - kc) * nblk * 2;
         for (int it = threadIdx.x; it < n_items; it += kTmacV2Threads) {
-            const int kt = kc + it / nblk, b = it - (it / nblk) * nblk;
+            const int hb = it & 1, itb = it >> 1;
+            const int kt = kc + itb / nblk, b = itb - (itb / nblk) * nblk;
             const int i = sub * LC + b * 16;                         // first byte lane of the block inside the tile (multiple of 16)
             const size_t blk = (size_t)tile * kt_n + kt;
-            const uint4* a = reinterpret_cast<const uint4*>(A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8);
+            const uint2* a = reinterpret_cast<const uint2*>(A + blk * (size_t)(bm / 2 * 8) + (size_t)i * 8 + hb * 8);   // + k * 16 bytes
             const uint4* tabs = reinterpret_cast<const uint4*>(qlut + (size_t)kt * 128);
-            uint32_t R[8], H[8];
+            uint32_t R[4], H[4];
             #pragma unroll
-            for (int j = 0; j < 8; ++j) R[j] = H[j] = 0u;
+            for (int j = 0; j < 4; ++j) R[j] = H[j] = 0u;
             #pragma unroll
             for (int k = 0; k < 8; ++k) {
                 uint4 T = __ldg(tabs + k);
                 T.x ^= 0x80808080u; T.y ^= 0x80808080u; T.z ^= 0x80808080u; T.w ^= 0x80808080u;
-                const uint4 av = __ldg(a + k);
-                const uint32_t w[4] = {av.x, av.y, av.z, av.w};
+                const uint2 av = __ldg(a + 2 * k);
+                const uint32_t w[2] = {av.x, av.y};
                 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
+                for (int j = 0; j < 4; ++j) {
                     const uint32_t sj = (j & 1) ? (w[j >> 1] >> 16) : w[j >> 1];
                     const uint32_t m = sj & 0x7777u;
                     const uint32_t r = __byte_perm(__byte_perm(T.x, T.y, m), __byte_perm(T.z, T.w, m), ((sj >> 1) & 0x4444u) | 0x3210u);
@@ -316,12 +319,12 @@ __global__ void __launch_bounds__(kTmacV2Threads) tmac_qgemm_v2_kernel(int K, in
                 }
             }
             const float lut_s = __ldg(lut_scales + kt), lut_b = __ldg(lut_biases + kt);
-            float4* out = reinterpret_cast<float4*>(sv + (size_t)(kt - kc) * W + b * 32);
+            float4* out = reinterpret_cast<float4*>(sv + (size_t)(kt - kc) * W + b * 32 + hb * 16);
+            const int ib_bot = i / 4 + hb, ib_top = ib_bot + 2;      // the 8 lanes of a half share l >> 3 = hb
+            const bool plain_b = (ib_bot % bits) != 0, plain_t = (ib_top % bits) != 0;
             #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const uint32_t E = R[j] - (H[j] << 8);               // even bytes: low nibbles of lanes 2j, 2j+1;  H: their high nibbles
-                const int ib_bot = i / 4 + (j >> 2), ib_top = ib_bot + 2;            // lanes 2j, 2j+1 share l >> 3 = j >> 2
-                const bool plain_b = (ib_bot % bits) != 0, plain_t = (ib_top % bits) != 0;
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t E = R[j] - (H[j] << 8);               // even bytes: low nibbles of two lanes;  H: their high nibbles
                 const float f0 = (float)((int)(E & 0xffffu) - 1024), f1 = (float)((int)(H[j] & 0xffffu) - 1024);
                 const float f2 = (float)((int)(E >> 16) - 1024), f3 = (float)((int)(H[j] >> 16) - 1024);
                 float4 o;
@@ -331,7 +334,7 @@ __global__ void __launch_bounds__(kTmacV2Threads) tmac_qgemm_v2_kernel(int K, in
                 o.w = plain_t ? __fmul_rn(f3, lut_s) : fmaf(f3, lut_s, lut_b);
                 out[j] = o;
             }
-            if (b == 0) {                                            // the k-block's scales of this CTA: SW contiguous floats
+            if (b == 0 && hb == 0) {                                 // the k-block's scales of this CTA: SW contiguous floats
                 const float4* sc = reinterpret_cast<const float4*>(scales + blk * (size_t)(bm / bits) + s0);
                 float4* dst = reinterpret_cast<float4*>(ssc + (size_t)(kt - kc) * SW);
                 for (int v = 0; v < SW / 4; ++v) dst[v] = __ldg(sc + v);

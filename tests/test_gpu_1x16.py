@@ -102,3 +102,28 @@ def test_1x16_errors(ops):
     with pytest.raises(LutvqError):              # prob_k not a multiple of 8 codes
         ops.code1x16_matmat(torch.zeros((1, 40), dtype=torch.float16, device="cuda"), torch.zeros((8, 5, 1), dtype=torch.int16, device="cuda"),
                             torch.zeros((1, 65536, 1, 8), dtype=torch.float16, device="cuda"), torch.ones((8, 1, 1, 1), dtype=torch.float16, device="cuda"))
+
+
+def test_1x16_launch_plan_overrides_are_bit_identical(ops, orc):
+    """the kernel's other launch shapes (rows shared by 2 / 4 warps with a shared-memory reduction, more / fewer CTAs per SM; reachable
+    through lutvq_debug_set_1x16_plan, which tools/sweep_1x16.py uses) give the same bits as the default plan up to the summation
+    order of the row splits: exact equality for split 1, 1e-3 of the layer's range otherwise"""
+    from rvv_lut_vq_b200._lib import lib
+    rng = np.random.default_rng(3)
+    I, O = 4096, 1000
+    idx = rng.integers(0, 65536, size=(O, I // 8, 1))
+    codes = cu(orc.np_pack_int_data(idx, 16))
+    cb = torch.from_numpy(rng.standard_normal((1, 65536, 1, 8)).astype(np.float32)).half().cuda()
+    sc = torch.from_numpy(rng.standard_normal((O, 1, 1, 1)).astype(np.float32)).half().cuda()
+    x = torch.from_numpy(rng.standard_normal((3, I)).astype(np.float32)).half().cuda()
+    want = ops.code1x16_matmat(x, codes, cb, sc, None)
+    try:
+        for split, per_sm in ((1, 1), (1, 6), (2, 3), (4, 2)):
+            lib().lutvq_debug_set_1x16_plan(split, per_sm)
+            got = ops.code1x16_matmat(x, codes, cb, sc, None)
+            if split == 1:
+                assert torch.equal(got.view(torch.int16), want.view(torch.int16))
+            else:
+                assert rel_err(got.float().cpu().numpy(), want.float().cpu().numpy()) <= TOL
+    finally:
+        lib().lutvq_debug_set_1x16_plan(0, 0)
