@@ -146,7 +146,7 @@ def run_reference(args):
 def cpu_baseline(seconds: float = 12.0):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as orc
-    bufs = 4
+    bufs = 16                                     # the same 180 MB working set as the reference arm (larger than the host's last-level cache)
     layers, x = _cpu_layers(bufs)
     f = orc.RowMajorGemv(OUT_F, IN_F // 8)
     orc.calibrate_threads(lambda: f(x, *layers[0]))
