@@ -309,7 +309,8 @@ def test_quantized_linear_prefill_dispatch(pkg, orc):
 
 
 @pytest.mark.parametrize("I,O,batch,dtype", [(4096, 11008, 2, "f16"), (4096, 4096, 4, "f16"), (11008, 4096, 6, "f16"), (4096, 11008, 11, "bf16"),
-                                             (1024, 96, 5, "f16")])
+                                             (1024, 96, 5, "f16"), (320, 515, 7, "f16"), (1024, 33, 8, "bf16"), (4096, 4096, 8, "f16"),
+                                             (64, 8, 2, "f16"), (8192, 1024, 3, "f16")])
 def test_multi_row_call_groups_rows_bit_identically(pkg, ops, I, O, batch, dtype):
     """up to 8 rows of one lutvq_code2x8_matmat[_packed] call go out as ONE grouped launch when the workspace holds their split-k
     words (batch 11 = 8 + 3): same bits as one row per call, the workspace comes back all-zero, and x produced by the kernel just
