@@ -12,11 +12,14 @@
 //              group two conflict-free 128-bit reads of the 8x replicated codebooks, one HADD2 x4 (the SAME single
 //              RN add as Code2x8Dequant, cuda_kernel.cu:283-289), one 128-bit store -- exactly one "core matrix row"
 //              of the no-swizzle K-major UMMA layout  addr = kchunk * (rows*16) + row*16.
-//              The activation tile is brought in by cp.async in the same layout.  Afterwards the same warps run the
+//              The activation tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA tensor copy
+//              (cp.async.bulk.tensor, issued by one producer thread, completing on the stage's full barrier; rows past
+//              the batch are zero-filled by the copy engine).  Afterwards the same warps run the
 //              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
 //   warp 8     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
 //              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
-//   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp, empty: tcgen05.commit).
+//   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp + the TMA issuer's expect_tx arrival
+//   and the copy's bytes, empty: tcgen05.commit).
 //
 // Split-k (few row tiles, e.g. 4096 outputs = 32 tiles on 148 SMs): partial accumulators go to the workspace in
 // fp32, a per-tile arrival counter elects the last CTA, which adds the partials IN FIXED ORDER (deterministic) and
@@ -25,6 +28,8 @@
 // Bound: tensor pipe only at large batch; below ~128 columns the producers' shared-memory traffic (48 B per group)
 // is the limiter.  Algorithmic flops 2*batch*I*O; algorithmic HBM bytes as the GEMV + 2*batch*(I+O).
 #include "common.cuh"
+
+#include <cuda.h>     // CUtensorMap and its enums only: the encoder is looked up through the runtime, no libcuda link
 
 namespace lutvq {
 
@@ -88,11 +93,14 @@ __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
                  : "r"(taddr) : "memory");
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
 }
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+// one box of the 2-D tensor map (coordinates: c0 = element along k, c1 = batch row) -> shared memory; its bytes complete on `bar`
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
 
 __device__ __forceinline__ uint4 lds128(uint32_t a) {       // read-only data (the codebook copies): free to be scheduled
     uint4 v;
@@ -131,7 +139,7 @@ __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
 
 template <int DT, int P, int BPS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_dequant_tc_kernel(const GemmParams p) {
+gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap xmap) {
     using D = Dtype<DT>;
     using T = typename D::T;
     using T2 = typename D::T2;
@@ -160,7 +168,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
 
     // ---------------- one-time setup ----------------
     if (tid == kProducerThreads) {
-        for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads / 32); mbar_init(empty_bar(i), 1); }
+        for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads / 32 + 1); mbar_init(empty_bar(i), 1); }
         mbar_init(accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -181,27 +189,20 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         // =============================== producers: dequantize A, copy B ===============================
         const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
         const uint32_t cbB = cbA + 256u * 8u * 16u;
-        const uint8_t* xb = static_cast<const uint8_t*>(p.x);
         // Activation tile: SWIZZLE_128B K-major -- batch row n = 128 contiguous bytes (64 k), its 16-byte pieces XOR-permuted
-        // by n & 7.  Eight lanes copy one row: 128 contiguous bytes in global AND in shared memory, i.e. one wavefront
-        // per row (the no-swizzle layout scattered every 16-byte piece to its own wavefront: 2048 per k block at batch
-        // 256).  Padding rows n >= batch are left as they are: D column n depends on B row n only and is never read.
-        // thread -> (row n0 = tid / 8 (+32 per step: same n & 7), piece j = tid % 8): pointer bumps only in the copy loop
-        const int bn0 = tid >> 3, bj = tid & 7;
-        const uint8_t* const bsrc = xb + (size_t)bn0 * p.I * 2 + bj * 16;
-        const uint32_t bdst = (uint32_t)bn0 * 128u + (uint32_t)((bj ^ (bn0 & 7)) * 16);
-        const size_t bsrc_step = (size_t)(kProducerThreads / 8) * p.I * 2;
+        // by n & 7: exactly what the copy engine writes for a {64, n_pad} box of the [batch][I] tensor map with
+        // CU_TENSOR_MAP_SWIZZLE_128B into a 1024-byte aligned block.  One thread posts the stage's byte count on the full
+        // barrier and issues one tensor copy per k block; rows n >= batch lie outside the tensor and arrive as zeros.
         auto issue_B = [&](int kb, int s) {                              // the BPS k blocks of one stage, first one = kb
-            if (p.dbg & 4) { cp_async_commit(); return; }
+            if (tid != 0) return;
+            const int nblk = kb1 - kb < BPS ? kb1 - kb : BPS;
+            if (p.dbg & 4) { mbar_arrive(full_bar(s)); return; }
+            mbar_arrive_expect_tx(full_bar(s), (uint32_t)nblk * bblock);
             #pragma unroll
             for (int b = 0; b < BPS; ++b) {
-                if (kb + b >= kb1) break;
-                uint32_t dst = sB + (uint32_t)s * bstage + (uint32_t)b * bblock + bdst;
-                const uint8_t* src = bsrc + (size_t)(kb + b) * (kBK * 2);
-                for (int n = bn0; n < p.batch; n += kProducerThreads / 8, dst += (kProducerThreads / 8) * 128u, src += bsrc_step)
-                    cp_async16(dst, src);
+                if (b >= nblk) break;
+                tma_load_2d(sB + (uint32_t)s * bstage + (uint32_t)b * bblock, &xmap, full_bar(s), (kb + b) * kBK, 0);
             }
-            cp_async_commit();
         };
         // The loop is bound by instruction issue (one producer warp per scheduler), so everything that is not a codebook
         // read, an add or a store is kept out of it: stage indices and parities are carried, not divided; the code
@@ -236,8 +237,8 @@ gemm_dequant_tc_kernel(const GemmParams p) {
             #pragma unroll
             for (int j = 0; j < P; ++j) cur[j] = lds64_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 8u);
         };
-        // Activations are issued D k blocks ahead (D = min(3, S - 2) >= 1): one block ahead left every block waiting for
-        // most of an L2 round trip in cp.async.wait_group.
+        // Activations are issued D stages ahead (D = min(3, S - 2) >= 1); every producer waits for that stage to be empty
+        // at the same point, which is also what makes its own later stores into the stage safe.
         const int LA = p.lookahead;
         int s = 0, sD = LA;                                              // stage of this k block / of block +D  (D < S)
         uint32_t parD = 1u;                                              // parity to wait for on empty[sD]
@@ -245,8 +246,6 @@ gemm_dequant_tc_kernel(const GemmParams p) {
             if (kb + LA * BPS < kb1) {
                 mbar_wait(empty_bar(sD), parD);
                 issue_B(kb + LA * BPS, sD);
-            } else {
-                cp_async_commit();
             }
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
@@ -273,7 +272,6 @@ gemm_dequant_tc_kernel(const GemmParams p) {
                     }
                 }
             }
-            if (LA == 3) cp_async_wait<3>(); else if (LA == 2) cp_async_wait<2>(); else cp_async_wait<1>();   // this stage's activations have landed
             if (!(p.dbg & 16)) fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
@@ -286,7 +284,7 @@ gemm_dequant_tc_kernel(const GemmParams p) {
         read_chunk(0);
         if (kb0 + P < kb1) load_chunk(1);
         for (int d = 0; d < LA; ++d) {
-            if (kb0 + d * BPS < kb1) issue_B(kb0 + d * BPS, d); else cp_async_commit();
+            if (kb0 + d * BPS < kb1) issue_B(kb0 + d * BPS, d);
         }
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
             #pragma unroll
@@ -432,8 +430,38 @@ size_t gemm_workspace_bytes_for(int O, int I, int max_batch) {
 }
 size_t gemm_workspace_bytes(int O, int I) { return gemm_workspace_bytes_for(O, I, kGemmMaxBatch); }
 
+// cuTensorMapEncodeTiled, looked up once through the runtime (the library does not link libcuda)
+typedef CUresult (*TensorMapEncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                           const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                           CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static TensorMapEncodeTiledFn tensor_map_encoder() {
+    static TensorMapEncodeTiledFn fn = [] {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) f = nullptr;
+        return reinterpret_cast<TensorMapEncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+// tensor map of the activations x[batch][I] (16-bit elements) with a {64 k, n_pad rows} box, 128-byte swizzle
+static int make_x_map(CUtensorMap* map, const void* x, int batch, int I, int n_pad, int dtype) {
+    TensorMapEncodeTiledFn enc = tensor_map_encoder();
+    if (!enc) return fail(LUTVQ_ECUDA, "cuTensorMapEncodeTiled not available from this driver");
+    LUTVQ_REQUIRE(aligned16(x), "x must be 16-byte aligned");
+    const cuuint64_t dims[2] = {(cuuint64_t)I, (cuuint64_t)batch};
+    const cuuint64_t strides[1] = {(cuuint64_t)I * 2};
+    const cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)n_pad};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, dtype == LUTVQ_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(x),
+                           dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(LUTVQ_ECUDA, "cuTensorMapEncodeTiled failed (CUresult %d) for x[%d][%d], box {%d, %d}", (int)r, batch, I, kBK, n_pad);
+    return LUTVQ_OK;
+}
+
 template <int DT, int P, int BPS>
-static int launch_gemm(const GemmParams& p, dim3 grid, size_t smem, cudaStream_t stream) {
+static int launch_gemm(const GemmParams& p, const CUtensorMap& xmap, dim3 grid, size_t smem, cudaStream_t stream) {
     auto kern = gemm_dequant_tc_kernel<DT, P, BPS>;
     static thread_local int attr_device = -1;
     int dev = 0;
@@ -442,7 +470,7 @@ static int launch_gemm(const GemmParams& p, dim3 grid, size_t smem, cudaStream_t
         LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_device = dev;
     }
-    kern<<<grid, kGemmThreads, smem, stream>>>(p);
+    kern<<<grid, kGemmThreads, smem, stream>>>(p, xmap);
     LUTVQ_CUDA_OK(cudaGetLastError());
     return LUTVQ_OK;
 }
@@ -488,10 +516,12 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
             p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256 + gemv_acc_bytes(O));
         }
         const dim3 grid(pl.n_tiles, pl.ksplit);
+        CUtensorMap xmap;
+        if (int rc = make_x_map(&xmap, p.x, nb, I, p.n_pad, dtype)) return rc;
         int rc;
-        if (bps == 2)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, grid, smem, stream);
-        else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, grid, smem, stream);
-        else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, grid, smem, stream);
+        if (bps == 2)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, xmap, grid, smem, stream);
+        else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, xmap, grid, smem, stream);
+        else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, xmap, grid, smem, stream);
         if (rc) return rc;
     }
     return LUTVQ_OK;
