@@ -12,12 +12,13 @@
 //              group two conflict-free 128-bit reads of the 8x replicated codebooks, one HADD2 x4 (the SAME single
 //              RN add as Code2x8Dequant, cuda_kernel.cu:283-289), one 128-bit store -- exactly one "core matrix row"
 //              of the no-swizzle K-major UMMA layout  addr = kchunk * (rows*16) + row*16.
-//              The activation tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA tensor copy
-//              (cp.async.bulk.tensor, issued by one producer thread, completing on the stage's full barrier; rows past
-//              the batch are zero-filled by the copy engine).  Afterwards the same warps run the
+//              Afterwards the same warps run the
 //              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
 //   warp 8     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
 //              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
+//   warp 9     one thread brings in the activations: the tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA
+//              tensor copy (cp.async.bulk.tensor) completing on the stage's full barrier, issued as soon as the stage is
+//              empty, i.e. up to kStages stages ahead of the dequantization; rows past the batch arrive as zeros.
 //   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp + the TMA issuer's expect_tx arrival
 //   and the copy's bytes, empty: tcgen05.commit).
 //
@@ -36,7 +37,7 @@ namespace lutvq {
 constexpr int kBM = 128;                 // output channels per CTA (UMMA M)
 constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 code bytes per row
 constexpr int kProducerThreads = 256;      // 8 warps: thread = (output row, half of the k block); two warps per scheduler hide the LDS latency
-constexpr int kGemmThreads = 288;          // + the MMA warp
+constexpr int kGemmThreads = 320;          // + the MMA warp + the TMA warp
 constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
 constexpr int kAStageBytes = kBM * kBK * 2;        // 16 KiB
 
@@ -51,7 +52,6 @@ struct GemmParams {
     float* partial;         // [ksplit][n_pad][O_pad] fp32 partial accumulators (ksplit > 1)
     int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, tmem_cols;
     int rpc;                // output rows this CTA owns (<= 128, multiple of 8): rows of the M=128 tile past it are never dequantized or stored
-    int lookahead;          // k blocks the activation copies run ahead (1..3, < stages)
     int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
     int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
 };
@@ -175,7 +175,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     if (warp == kProducerThreads / 32) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)p.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-    } else {
+    } else if (warp < kProducerThreads / 32) {
         #pragma unroll 8
         for (int i = tid; i < 2 * 256 * 8; i += kProducerThreads) sh_cb[i] = __ldg(p.codebook + (i >> 3));
     }
@@ -189,21 +189,6 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // =============================== producers: dequantize A, copy B ===============================
         const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
         const uint32_t cbB = cbA + 256u * 8u * 16u;
-        // Activation tile: SWIZZLE_128B K-major -- batch row n = 128 contiguous bytes (64 k), its 16-byte pieces XOR-permuted
-        // by n & 7: exactly what the copy engine writes for a {64, n_pad} box of the [batch][I] tensor map with
-        // CU_TENSOR_MAP_SWIZZLE_128B into a 1024-byte aligned block.  One thread posts the stage's byte count on the full
-        // barrier and issues one tensor copy per k block; rows n >= batch lie outside the tensor and arrive as zeros.
-        auto issue_B = [&](int kb, int s) {                              // the BPS k blocks of one stage, first one = kb
-            if (tid != 0) return;
-            const int nblk = kb1 - kb < BPS ? kb1 - kb : BPS;
-            if (p.dbg & 4) { mbar_arrive(full_bar(s)); return; }
-            mbar_arrive_expect_tx(full_bar(s), (uint32_t)nblk * bblock);
-            #pragma unroll
-            for (int b = 0; b < BPS; ++b) {
-                if (b >= nblk) break;
-                tma_load_2d(sB + (uint32_t)s * bstage + (uint32_t)b * bblock, &xmap, full_bar(s), (kb + b) * kBK, 0);
-            }
-        };
         // The loop is bound by instruction issue (one producer warp per scheduler), so everything that is not a codebook
         // read, an add or a store is kept out of it: stage indices and parities are carried, not divided; the code
         // stream is staged per CHUNK of P k blocks.  A chunk = P*16 bytes of every row: each thread loads P 16-byte
@@ -237,16 +222,10 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             #pragma unroll
             for (int j = 0; j < P; ++j) cur[j] = lds64_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 8u);
         };
-        // Activations are issued D stages ahead (D = min(3, S - 2) >= 1); every producer waits for that stage to be empty
-        // at the same point, which is also what makes its own later stores into the stage safe.
-        const int LA = p.lookahead;
-        int s = 0, sD = LA;                                              // stage of this k block / of block +D  (D < S)
-        uint32_t parD = 1u;                                              // parity to wait for on empty[sD]
+        int s = 0;                                                       // stage of this k block
+        uint32_t parE = 1u;                                              // parity to wait for on empty[s] (a fresh barrier passes parity 1)
         auto do_stage = [&](int kb, const uint2 c0, const uint2 c1) {    // k blocks kb .. kb+BPS-1 (c1 unused when BPS == 1)
-            if (kb + LA * BPS < kb1) {
-                mbar_wait(empty_bar(sD), parD);
-                issue_B(kb + LA * BPS, sD);
-            }
+            mbar_wait(empty_bar(s), parE);                               // the MMAs that read this stage's last contents have retired
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
                 if (kb + sb >= kb1) break;
@@ -275,17 +254,13 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             if (!(p.dbg & 16)) fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
-            if (++s == S) s = 0;
-            if (++sD == S) { sD = 0; parD ^= 1u; }
+            if (++s == S) { s = 0; parE ^= 1u; }
         };
         load_chunk(0);
         store_chunk(0);
         asm volatile("bar.sync 1, 256;" ::: "memory");
         read_chunk(0);
         if (kb0 + P < kb1) load_chunk(1);
-        for (int d = 0; d < LA; ++d) {
-            if (kb0 + d * BPS < kb1) issue_B(kb0 + d * BPS, d);
-        }
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
             #pragma unroll
             for (int j = 0; j < P; j += BPS)
@@ -346,6 +321,30 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                 if (tid == 0) p.counters[tile] = 0u;                     // hand the counter back
             }
         }
+    } else if (warp == kProducerThreads / 32 + 1) {
+        // =============================== activation copies (warp 9, one thread) ===============================
+        // Activation tile: SWIZZLE_128B K-major -- batch row n = 128 contiguous bytes (64 k), its 16-byte pieces XOR-permuted
+        // by n & 7: exactly what the copy engine writes for a {64, n_pad} box of the [batch][I] tensor map with
+        // CU_TENSOR_MAP_SWIZZLE_128B into a 1024-byte aligned block.  Per stage: wait until it is empty, post the byte
+        // count on its full barrier, one tensor copy per k block; rows n >= batch lie outside the tensor and arrive as zeros.
+        if (lane == 0) {
+            int s = 0;
+            uint32_t par = 1u;
+            for (int kb = kb0; kb < kb1; kb += BPS) {
+                mbar_wait(empty_bar(s), par);
+                const int nblk = kb1 - kb < BPS ? kb1 - kb : BPS;
+                if (p.dbg & 4) {
+                    mbar_arrive(full_bar(s));
+                } else {
+                    mbar_arrive_expect_tx(full_bar(s), (uint32_t)nblk * bblock);
+                    #pragma unroll
+                    for (int b = 0; b < BPS; ++b)
+                        if (b < nblk) tma_load_2d(sB + (uint32_t)s * bstage + (uint32_t)b * bblock, &xmap, full_bar(s), (kb + b) * kBK, 0);
+                }
+                if (++s == S) { s = 0; par ^= 1u; }
+            }
+        }
+        __syncwarp();
     } else {
         // =============================== MMA issuer (warp 8) ===============================
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
@@ -505,7 +504,6 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         if (S > 8) S = 8;
         if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
         p.stages = S;
-        p.lookahead = S - 2 < 1 ? 1 : (S - 2 > 3 ? 3 : S - 2);
         const size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
         p.counters = nullptr; p.partial = nullptr;
         if (pl.ksplit > 1) {

@@ -284,11 +284,11 @@ def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, co
 
 
 # rows from which dequantize-once + library GEMM beats the fused kernel.  Measured on B200, 4096x11008, a ring of 24 L2-cold
-# layers, scales applied (bench.py `prefill`, profiles/r02_bench_line.json): fused 28.6 / 31.0 / 33.6 / 39.3 / 46.9 us at
-# 16 / 32 / 64 / 128 / 256 rows and 387 us at 2048 (chunks of 256 re-read the codes); two-step 37.9 / 37.9 / 38.2 / 35.8 / 41.9 us and
-# 157 us at 2048 (0.72 of the bf16 peak).  (With W's destination L2-resident the two-step route already wins at 32 rows:
-# profiles/r02_prefill_crossover.jsonl.)
-TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "128"))
+# layers (tools/prefill_bench.py, profiles/r02_prefill_tma.jsonl): fused 22.8 / 22.9 / 24.3 / 28.4 / 33.6 us at
+# 16 / 32 / 64 / 128 / 256 rows, then 68 us at 512 and 271 us at 2048 (one launch takes <= 256 rows: chunks re-read the codes);
+# two-step 35.9 / 41.9 / 57.9 us at 128 / 256 / 512 rows and 155 us at 2048 (0.72 of the bf16 peak).  So: one launch of the fused
+# kernel while the rows fit one, the two-step route above.
+TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "257"))
 
 
 def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
