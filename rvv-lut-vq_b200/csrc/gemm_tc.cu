@@ -39,7 +39,8 @@ constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 cod
 constexpr int kProducerThreads = 256;      // 8 warps: thread = (output row, half of the k block); two warps per scheduler hide the LDS latency
 constexpr int kGemmThreads = 320;          // + the MMA warp + the TMA warp
 constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
-constexpr int kAStageBytes = kBM * kBK * 2;        // 16 KiB
+constexpr int kATmemCols = kBK / 2;                // a k block of A in tensor memory: 128 lanes (rows) x 32 columns (2 fp16 each)
+constexpr int kTmemCols = 512;                     // the whole tensor memory of the SM: accumulator columns, then the A ring
 
 struct GemmParams {
     const uint8_t* codes;   // [O][G][2]
@@ -50,7 +51,7 @@ struct GemmParams {
     void* y;                // [batch][O]
     unsigned int* counters; // [n_tiles] split-k arrival counters (zero between launches)
     float* partial;         // [ksplit][n_pad][O_pad] fp32 partial accumulators (ksplit > 1)
-    int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, tmem_cols;
+    int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, a_col0;    // a_col0 = first tensor-memory column of the A ring (after the n_pad accumulator columns)
     int rpc;                // output rows this CTA owns (<= 128, multiple of 8): rows of the M=128 tile past it are never dequantized or stored
     int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
     int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
@@ -73,19 +74,26 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "DONE_%=:\n\t}"
         :: "r"(bar), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
-__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+// D (tensor memory) (+)= A (TENSOR MEMORY: lane = row, 8 columns = 16 K-major 16-bit elements) * B (shared memory descriptor)
+__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// 16 consecutive 32-bit columns of this thread's lane (warp w reaches lanes 32*(w%4) .. +31); warp-collective
+__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                 :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
@@ -121,12 +129,6 @@ __device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-// K-major, no-swizzle UMMA shared-memory descriptor (cute::UMMA::SmemDescriptor): 8-row x 16-byte core matrices,
-// rows 16 B apart; SBO = distance between 8-row groups, LBO = distance between the two k core matrices of one MMA.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
-           ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);   // version 1 (Blackwell), layout_type 0 = SWIZZLE_NONE
-}
 // K-major SWIZZLE_128B descriptor: rows of 128 bytes, 8-row atoms 1024 bytes apart (SBO), LBO unused (1), layout_type 2;
 // the atom base must be 1024-byte aligned; a K=16 step inside the 128-byte span advances the start address by 32 bytes.
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
@@ -148,11 +150,9 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     uint4* sh_cb = reinterpret_cast<uint4*>(smem);
     const int S = p.stages;
     const uint32_t sC = sbase + kCbSmemBytes;                               // 2 code-chunk buffers of 128 rows x chunk x 16 B
-    const uint32_t sA = sC + 2u * (uint32_t)kBM * (uint32_t)P * 16u;
     // a pipeline stage = BPS k blocks (every mbarrier round trip costs ~150 cycles per warp: small batches take 2 per stage)
-    constexpr uint32_t astage = (uint32_t)BPS * kAStageBytes;
     const uint32_t bblock = (uint32_t)p.n_pad * 128u, bstage = (uint32_t)BPS * bblock;
-    const uint32_t sB = sA + (uint32_t)S * astage;
+    const uint32_t sB = sC + 2u * (uint32_t)kBM * (uint32_t)P * 16u;       // activation stages (1024-byte aligned: SWIZZLE_128B)
     const uint32_t bars = sB + (uint32_t)S * bstage;
     auto full_bar  = [&](int i) { return bars + 8u * (uint32_t)i; };
     auto empty_bar = [&](int i) { return bars + 8u * (uint32_t)(S + i); };
@@ -173,7 +173,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kProducerThreads / 32) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)p.tmem_cols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(tmem_slot), "r"((uint32_t)kTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     } else if (warp < kProducerThreads / 32) {
         #pragma unroll 8
@@ -222,17 +222,26 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             #pragma unroll
             for (int j = 0; j < P; ++j) cur[j] = lds64_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 8u);
         };
+        // A goes to TENSOR MEMORY, not shared memory: lane = output row of the tile, a k block = 32 columns (two 16-bit
+        // elements each, K-major), ring of S * BPS k blocks after the accumulator's columns.  A thread's 4 groups are 16
+        // consecutive columns of its own lane: one tcgen05.st 32x32b.x16 per k block (a warp reaches lanes 32*(warp%4)..+31,
+        // which is how rows are dealt to warps already).  The MMA reads it as its A operand ([tmem] form), so the
+        // dequantized tile costs no shared-memory store and no shared-memory read by the tensor core.
+        // Whole warps past the CTA's rows skip the work; dead rows inside a live warp run on zero codes (never stored).
+        const bool warp_live = (warp & 3) * 32 < p.rpc;
+        const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 16u;
         int s = 0;                                                       // stage of this k block
         uint32_t parE = 1u;                                              // parity to wait for on empty[s] (a fresh barrier passes parity 1)
         auto do_stage = [&](int kb, const uint2 c0, const uint2 c1) {    // k blocks kb .. kb+BPS-1 (c1 unused when BPS == 1)
             mbar_wait(empty_bar(s), parE);                               // the MMAs that read this stage's last contents have retired
+            tc_fence_after();
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
                 if (kb + sb >= kb1) break;
                 const uint32_t w[2] = {sb ? c1.x : c0.x, sb ? c1.y : c0.y};
-                const uint32_t a_dst = sA + (uint32_t)s * astage + (uint32_t)sb * kAStageBytes + (uint32_t)row * 16u + (uint32_t)hk * (4u * kBM * 16u);
-                if (!(p.dbg & 2) && row < p.rpc) {                       // 4 groups: 8 reads in flight, then adds and stores
+                if (!(p.dbg & 2) && warp_live) {                         // 4 groups: 8 reads in flight, then adds and ONE tensor-memory store
                     uint4 a[4], b[4];
+                    uint32_t v[16];
                     #pragma unroll
                     for (int g = 0; g < 4; ++g) {                        // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
                         const uint32_t wg = w[g >> 1];
@@ -241,17 +250,19 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                     }
                     #pragma unroll
                     for (int g = 0; g < 4; ++g) {
-                        uint4 r;
                         const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
                         const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
-                        T2* r2 = reinterpret_cast<T2*>(&r);
                         #pragma unroll
-                        for (int jj = 0; jj < 4; ++jj) r2[jj] = D::add2(a2[jj], b2[jj]);
-                        sts128(a_dst + (uint32_t)g * (kBM * 16u), r);
+                        for (int jj = 0; jj < 4; ++jj) {                 // column 4g + jj of the half = elements k = 8g + 2jj, + 1
+                            const T2 r = D::add2(a2[jj], b2[jj]);
+                            v[4 * g + jj] = *reinterpret_cast<const uint32_t*>(&r);
+                        }
                     }
+                    tc_st16(a_lane + (uint32_t)(s * BPS + sb) * kATmemCols, v);
                 }
             }
-            if (!(p.dbg & 16)) fence_proxy_async_smem();                 // generic-proxy writes -> visible to the tensor core
+            tc_wait_st();                                                // this warp's rows of the stage are in tensor memory
+            tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
             if (++s == S) { s = 0; parE ^= 1u; }
@@ -359,9 +370,9 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                     if (kb + sb >= kb1) break;
                     #pragma unroll
                     for (int k = 0; k < kBK / 16; ++k) {
-                        const uint64_t adesc = umma_desc(sA + (uint32_t)s * astage + (uint32_t)sb * kAStageBytes + (uint32_t)k * (2u * kBM * 16u), kBM * 16u, 128u);
+                        const uint32_t a_t = tmem_base + (uint32_t)p.a_col0 + (uint32_t)(s * BPS + sb) * kATmemCols + (uint32_t)k * 8u;
                         const uint64_t bdesc = umma_desc_sw128(sB + (uint32_t)s * bstage + (uint32_t)sb * bblock + (uint32_t)k * 32u);
-                        if (!(p.dbg & 1)) tc_mma_f16(tmem_base, adesc, bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
+                        if (!(p.dbg & 1)) tc_mma_f16_ts(tmem_base, a_t, bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
                     }
                 }
                 tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
@@ -377,7 +388,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     tc_fence_before();
     __syncthreads();
     if (warp == kProducerThreads / 32)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)kTmemCols) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -493,18 +504,20 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.n_pad = ceil_div(nb, 16) * 16;
         p.nkb = pl.nkb; p.ksplit = pl.ksplit;
         p.dbg = g_gemm_dbg;
-        p.tmem_cols = 32;
-        while (p.tmem_cols < p.n_pad) p.tmem_cols *= 2;
+        p.a_col0 = ceil_div(p.n_pad, 32) * 32;                          // accumulator: columns [0, n_pad); A ring behind it
         const int bps = (p.n_pad <= 64 && !(g_gemm_dbg & 128)) ? 2 : 1;   // k blocks per pipeline stage
-        const size_t stage_bytes = (size_t)bps * ((size_t)kAStageBytes + (size_t)p.n_pad * 128);
+        const size_t stage_bytes = (size_t)bps * (size_t)p.n_pad * 128;       // activations only: A lives in tensor memory
         p.chunk = (p.n_pad <= 128 && bps == 1) ? 8 : 4;
         const size_t code_bytes = 2 * (size_t)kBM * p.chunk * 16;
         const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - code_bytes - 1024;
         int S = (int)(budget / stage_bytes);
         if (S > 8) S = 8;
+        const int s_tmem = (kTmemCols - p.a_col0) / (bps * kATmemCols);   // k blocks of A the tensor memory holds
+        if (S > s_tmem) S = s_tmem;
         if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
         p.stages = S;
-        const size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
+        size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
+        if (smem < (size_t)116 * 1024) smem = (size_t)116 * 1024;         // one CTA per SM: each allocates the whole tensor memory
         p.counters = nullptr; p.partial = nullptr;
         if (pl.ksplit > 1) {
             const size_t need = gemm_workspace_bytes_for(O, I, nb);
