@@ -166,6 +166,22 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     const int row0 = tile * p.rpc;
     const int kb0 = (int)(((long long)z * p.nkb) / p.ksplit), kb1 = (int)(((long long)(z + 1) * p.nkb) / p.ksplit);
 
+    // The code stream is staged per CHUNK of P k blocks = P*16 bytes of every row: each producer thread loads P/2 16-byte
+    // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead).  Chunk 0 is requested
+    // before anything else: its HBM round trip then runs beside the codebook's instead of after it.
+    constexpr int lgP = P == 8 ? 3 : 2;
+    uint4 pre[P / 2];
+    auto load_chunk = [&](int c) {
+        const int kbase = kb0 + c * P;
+        #pragma unroll
+        for (int i = 0; i < P / 2; ++i) {
+            const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
+            const int grow = min(row0 + r, p.O - 1);                     // rows past the end recompute the last row; never stored
+            pre[i] = (kb < kb1 && r < p.rpc) ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
+        }
+    };
+    if (warp < kProducerThreads / 32) load_chunk(0);
+
     // ---------------- one-time setup ----------------
     if (tid == kProducerThreads) {
         for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads / 32 + 1); mbar_init(empty_bar(i), 1); }
@@ -183,6 +199,11 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    // Up to here only weights were read (code chunk 0, codebook).  The successor may be released right away -- it cannot
+    // co-reside (shared memory, tensor memory), it takes the SM when this CTA exits; activations, outputs and the split-k
+    // workspace are touched only once the predecessor has completed.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp < kProducerThreads / 32) {
         const int row = tid & (kBM - 1), hk = tid >> 7;                  // this thread's row of the tile and half (4 groups) of every k block
@@ -195,20 +216,9 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead), stores them
         // XOR-swizzled into one of two shared buffers, and after one producer barrier reads its own row's P code words
         // back with conflict-free 128-bit loads.
-        constexpr int lgP = P == 8 ? 3 : 2;
         constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
         auto swz = [](int r, int c) { return P == 8 ? (c ^ (r & 7)) : (c ^ ((r >> 1) & 3)); };
-        uint4 pre[P / 2];
         uint2 cur[P];
-        auto load_chunk = [&](int c) {
-            const int kbase = kb0 + c * P;
-            #pragma unroll
-            for (int i = 0; i < P / 2; ++i) {
-                const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
-                const int grow = min(row0 + r, p.O - 1);                 // rows past the end recompute the last row; never stored
-                pre[i] = (kb < kb1 && r < p.rpc) ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
-            }
-        };
         auto store_chunk = [&](int c) {
             const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
             #pragma unroll
@@ -232,13 +242,13 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 16u;
         int s = 0;                                                       // stage of this k block
         uint32_t parE = 1u;                                              // parity to wait for on empty[s] (a fresh barrier passes parity 1)
-        auto do_stage = [&](int kb, const uint2 c0, const uint2 c1) {    // k blocks kb .. kb+BPS-1 (c1 unused when BPS == 1)
+        auto do_stage = [&](int kb, const uint2* cw) {                   // k blocks kb .. kb+BPS-1, code words cw[0 .. BPS-1]
             mbar_wait(empty_bar(s), parE);                               // the MMAs that read this stage's last contents have retired
             tc_fence_after();
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
                 if (kb + sb >= kb1) break;
-                const uint32_t w[2] = {sb ? c1.x : c0.x, sb ? c1.y : c0.y};
+                const uint32_t w[2] = {cw[sb].x, cw[sb].y};
                 if (!(p.dbg & 2) && warp_live) {                         // 4 groups: 8 reads in flight, then adds and ONE tensor-memory store
                     uint4 a[4], b[4];
                     uint32_t v[16];
@@ -267,7 +277,6 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
             if (++s == S) { s = 0; parE ^= 1u; }
         };
-        load_chunk(0);
         store_chunk(0);
         asm volatile("bar.sync 1, 256;" ::: "memory");
         read_chunk(0);
@@ -275,7 +284,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
             #pragma unroll
             for (int j = 0; j < P; j += BPS)
-                if (kbc + j < kb1) do_stage(kbc + j, cur[j], cur[j + BPS - 1]);
+                if (kbc + j < kb1) do_stage(kbc + j, &cur[j]);
             if (kbc + P < kb1 && !(p.dbg & 32)) {
                 store_chunk(c + 1);
                 asm volatile("bar.sync 1, 256;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
@@ -480,8 +489,19 @@ static int launch_gemm(const GemmParams& p, const CUtensorMap& xmap, dim3 grid, 
         LUTVQ_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_device = dev;
     }
-    kern<<<grid, kGemmThreads, smem, stream>>>(p, xmap);
-    LUTVQ_CUDA_OK(cudaGetLastError());
+    // programmatic dependent launch: the CTAs of this launch take their SMs as the previous kernel's CTAs leave them (no
+    // grid-wide drain + launch latency in between); everything before griddepcontrol.wait touches weights only
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (p.dbg & 2048) ? 0 : 1;
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p, xmap));
     return LUTVQ_OK;
 }
 
@@ -505,7 +525,10 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.nkb = pl.nkb; p.ksplit = pl.ksplit;
         p.dbg = g_gemm_dbg;
         p.a_col0 = ceil_div(p.n_pad, 32) * 32;                          // accumulator: columns [0, n_pad); A ring behind it
-        const int bps = (p.n_pad <= 64 && !(g_gemm_dbg & 128)) ? 2 : 1;   // k blocks per pipeline stage
+        int bps = p.n_pad <= 64 ? 4 : p.n_pad <= 128 ? 2 : 1;             // k blocks per pipeline stage (a stage hand-over costs ~0.25 us)
+        if (g_gemm_dbg & 128) bps = 1;
+        if (g_gemm_dbg & 256) bps = 2;
+        if ((g_gemm_dbg & 512) && bps == 1) bps = 2;
         const size_t stage_bytes = (size_t)bps * (size_t)p.n_pad * 128;       // activations only: A lives in tensor memory
         p.chunk = (p.n_pad <= 128 && bps == 1) ? 8 : 4;
         const size_t code_bytes = 2 * (size_t)kBM * p.chunk * 16;
@@ -530,7 +553,8 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         CUtensorMap xmap;
         if (int rc = make_x_map(&xmap, p.x, nb, I, p.n_pad, dtype)) return rc;
         int rc;
-        if (bps == 2)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, xmap, grid, smem, stream);
+        if (bps == 4)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 4>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 4>(p, xmap, grid, smem, stream);
+        else if (bps == 2)     rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, xmap, grid, smem, stream);
         else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, xmap, grid, smem, stream);
         else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, xmap, grid, smem, stream);
         if (rc) return rc;

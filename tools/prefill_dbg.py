@@ -1,5 +1,5 @@
 """Prefill kernel with parts switched off (lutvq_debug_set_gemm_mode: 1 = no MMAs, 2 = no dequantization, 4 = no
-activation copies, 8 = 128-row tiles, 16 = no proxy fence, 32 = no code staging after chunk 0, 128 = 1 k block per stage); timing only, results are wrong in every mode but 0.  Graph-captured, ring of 24 layers."""
+activation copies, 8 = 128-row tiles, 16 = no proxy fence, 32 = no code staging after chunk 0, 128 = 1 k block per stage, 256 = 2, 2048 = no programmatic dependent launch); timing only, results are wrong in every mode but 0.  Graph-captured, ring of 24 layers."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from rvv_lut_vq_b200 import ops, synth, _lib
@@ -7,7 +7,7 @@ from prefill_bench import timed
 dev = torch.device('cuda', 0)
 Ls = [synth.make_layer_torch(4096, 11008, dev, seed=k, scales="ones") for k in range(24)]
 MODES = [int(a) for a in sys.argv[1:]] or [0]
-for batch in (16, 64, 256):
+for batch in (16, 64, 128, 256):
     x = torch.randn((batch, 4096), device=dev, dtype=torch.float16)
     for mode in MODES:
         _lib.lib().lutvq_debug_set_gemm_mode(mode)
