@@ -284,10 +284,10 @@ def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, co
 
 
 # rows from which dequantize-once + library GEMM beats the fused kernel.  Measured on B200, 4096x11008, a ring of 24 L2-cold
-# layers (tools/prefill_bench.py, profiles/r02_prefill_tma.jsonl): fused 22.8 / 22.9 / 24.3 / 28.4 / 33.6 us at
-# 16 / 32 / 64 / 128 / 256 rows, then 68 us at 512 and 271 us at 2048 (one launch takes <= 256 rows: chunks re-read the codes);
-# two-step 35.9 / 41.9 / 57.9 us at 128 / 256 / 512 rows and 155 us at 2048 (0.72 of the bf16 peak).  So: one launch of the fused
-# kernel while the rows fit one, the two-step route above.
+# layers, scales applied (bench.py `prefill`, profiles/r02_bench_line.json): fused 16.9 / 17.0 / 18.0 / 21.9 / 30.4 us at
+# 16 / 32 / 64 / 128 / 256 rows, then 62 us at 512 and 269 us at 2048 (one launch takes <= 256 rows: chunks re-read the codes);
+# two-step 38.8 / 38.3 / 38.6 / 36.2 / 41.7 us at 16 .. 256 rows, 58 at 512 and 165 us at 2048 (0.70-0.72 of the bf16 peak).  So: one
+# launch of the fused kernel while the rows fit one, the two-step route above.
 TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "257"))
 
 
