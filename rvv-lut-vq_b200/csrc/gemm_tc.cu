@@ -1,33 +1,36 @@
-// gemm_tc.cu -- prefill path: y[b][o] = epilogue( sum_k x[b][k] * W[o][k] ) with W dequantized ON THE FLY into shared
-// memory and contracted on the 5th-generation tensor cores (tcgen05.mma, fp32 accumulators in TMEM).
+// gemm_tc.cu -- prefill path: y[b][o] = epilogue( sum_k x[b][k] * W[o][k] ) with W dequantized ON THE FLY into TENSOR
+// MEMORY and contracted on the 5th-generation tensor cores (tcgen05.mma with A from TMEM, fp32 accumulators in TMEM).
 //
 // Replaces code2x8_matmat_dequant (reference benchmark/AQLM/inference_lib/src/aqlm/inference_kernels/
 // cuda_kernel.cpp:450-484): Code2x8Dequant writes the whole fp16 W to HBM (2*O*I bytes), cuBLAS F.linear reads it
 // back, three elementwise kernels apply scale / bias.  Here W never exists in HBM: the only weight traffic is the
 // code stream (O*I/4 bytes), and the epilogue (round to dtype, * scale, + bias; cuda_kernel.cpp:95-111) is fused.
 //
-// One CTA = one 128-row tile of output channels x the whole (padded) batch, over a k-range of the split:
-//   D[128 x N] (TMEM, fp32)  +=  A[128 x 64] (smem, dequantized weights, K-major)  *  B[N x 64]^T (smem, activations)
-//   warps 0-7  producers: each thread owns one output row and one half of every 64-wide k block (4 groups = 8 code bytes); per
-//              group two conflict-free 128-bit reads of the 8x replicated codebooks, one HADD2 x4 (the SAME single
-//              RN add as Code2x8Dequant, cuda_kernel.cu:283-289), one 128-bit store -- exactly one "core matrix row"
-//              of the no-swizzle K-major UMMA layout  addr = kchunk * (rows*16) + row*16.
-//              Afterwards the same warps run the
-//              epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch columns).
-//   warp 8     one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16) four times per stage and
-//              tcgen05.commit's the stage back to the producers; it also owns the TMEM allocation.
-//   warp 9     one thread brings in the activations: the tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA
+// One CTA = one tile of up to 128 output channels x the whole (padded) batch, over a k-range of the split:
+//   D[128 x N] (TMEM, fp32)  +=  A[128 x 64] (TMEM, dequantized weights, lane = row)  *  B[N x 64]^T (smem, activations)
+//   warps 0-15 producers: each thread owns one output row and one quarter of every 64-wide k block (2 groups = 4 code bytes);
+//              per group two conflict-free 128-bit reads of the 8x replicated codebooks in shared memory, one HADD2 x4 (the
+//              SAME single RN add as Code2x8Dequant, cuda_kernel.cu:283-289); the 8 resulting 32-bit words are 8 consecutive
+//              columns of the thread's own tensor-memory lane: one tcgen05.st per k block.  The code stream is staged per
+//              chunk of 4 / 8 k blocks (coalesced 16-byte loads a chunk ahead -> swizzled shared buffer -> per-row words).
+//              Afterwards the same warps run the epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch
+//              columns).
+//   warp 16    one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16; A operand = tensor-memory address,
+//              B operand = SWIZZLE_128B shared-memory descriptor) four times per k block and tcgen05.commit's the stage
+//              back; it also owns the TMEM allocation (all 512 columns: accumulator first, the A ring behind it).
+//   warp 17    one thread brings in the activations: the tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA
 //              tensor copy (cp.async.bulk.tensor) completing on the stage's full barrier, issued as soon as the stage is
-//              empty, i.e. up to kStages stages ahead of the dequantization; rows past the batch arrive as zeros.
-//   mbarrier pipeline of kStages smem stages (full: one arrival per producer warp + the TMA issuer's expect_tx arrival
-//   and the copy's bytes, empty: tcgen05.commit).
+//              empty, i.e. up to the whole ring ahead of the dequantization; rows past the batch arrive as zeros.
+//   mbarrier ring of `stages` stages of 1 / 2 / 4 k blocks (full: one arrival per producer warp + the copy thread's
+//   expect_tx arrival and the copy's bytes; empty: tcgen05.commit).  Programmatic dependent launch: everything before
+//   griddepcontrol.wait reads weights only.
 //
 // Split-k (few row tiles, e.g. 4096 outputs = 32 tiles on 148 SMs): partial accumulators go to the workspace in
 // fp32, a per-tile arrival counter elects the last CTA, which adds the partials IN FIXED ORDER (deterministic) and
 // runs the epilogue; it resets the counter, so the workspace is all-zero again between launches.
 //
-// Bound: tensor pipe only at large batch; below ~128 columns the producers' shared-memory traffic (48 B per group)
-// is the limiter.  Algorithmic flops 2*batch*I*O; algorithmic HBM bytes as the GEMV + 2*batch*(I+O).
+// Bound: the tensor pipe at 256 columns (62 % of the active cycles, 80 of 128 MMA rows live); stage hand-overs
+// and latency below.  Algorithmic flops 2*batch*I*O; algorithmic HBM bytes as the GEMV + 2*batch*(I+O).
 #include "common.cuh"
 
 #include <cuda.h>     // CUtensorMap and its enums only: the encoder is looked up through the runtime, no libcuda link
@@ -36,8 +39,8 @@ namespace lutvq {
 
 constexpr int kBM = 128;                 // output channels per CTA (UMMA M)
 constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 code bytes per row
-constexpr int kProducerThreads = 256;      // 8 warps: thread = (output row, half of the k block); two warps per scheduler hide the LDS latency
-constexpr int kGemmThreads = 320;          // + the MMA warp + the TMA warp
+constexpr int kProducerThreads = 512;      // 16 warps: thread = (output row, quarter of the k block); four warps per scheduler hide the LDS / STTM latency
+constexpr int kGemmThreads = 576;          // + the MMA warp + the TMA warp
 constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
 constexpr int kATmemCols = kBK / 2;                // a k block of A in tensor memory: 128 lanes (rows) x 32 columns (2 fp16 each)
 constexpr int kTmemCols = 512;                     // the whole tensor memory of the SM: accumulator columns, then the A ring
@@ -87,11 +90,10 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
         :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
-// 16 consecutive 32-bit columns of this thread's lane (warp w reaches lanes 32*(w%4) .. +31); warp-collective
-__device__ __forceinline__ void tc_st16(uint32_t taddr, const uint32_t (&v)[16]) {
-    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-                 :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-                    "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
+// 8 consecutive 32-bit columns of this thread's lane (warp w reaches lanes 32*(w%4) .. +31); warp-collective
+__device__ __forceinline__ void tc_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
 }
 __device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
@@ -120,9 +122,9 @@ __device__ __forceinline__ uint4 lds128_sync(uint32_t a) {  // data another thre
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ uint2 lds64_sync(uint32_t a) {
-    uint2 v;
-    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(a) : "memory");
+__device__ __forceinline__ uint32_t lds32_sync(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
 __device__ __forceinline__ void sts128(uint32_t a, const uint4 v) {
@@ -170,11 +172,11 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead).  Chunk 0 is requested
     // before anything else: its HBM round trip then runs beside the codebook's instead of after it.
     constexpr int lgP = P == 8 ? 3 : 2;
-    uint4 pre[P / 2];
+    uint4 pre[P / 4];
     auto load_chunk = [&](int c) {
         const int kbase = kb0 + c * P;
         #pragma unroll
-        for (int i = 0; i < P / 2; ++i) {
+        for (int i = 0; i < P / 4; ++i) {
             const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
             const int grow = min(row0 + r, p.O - 1);                     // rows past the end recompute the last row; never stored
             pre[i] = (kb < kb1 && r < p.rpc) ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
@@ -206,7 +208,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
     if (warp < kProducerThreads / 32) {
-        const int row = tid & (kBM - 1), hk = tid >> 7;                  // this thread's row of the tile and half (4 groups) of every k block
+        const int row = tid & (kBM - 1), hk = tid >> 7;                  // this thread's row of the tile and quarter (2 groups = 4 code bytes) of every k block
         // =============================== producers: dequantize A, copy B ===============================
         const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
         const uint32_t cbB = cbA + 256u * 8u * 16u;
@@ -218,11 +220,11 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // back with conflict-free 128-bit loads.
         constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
         auto swz = [](int r, int c) { return P == 8 ? (c ^ (r & 7)) : (c ^ ((r >> 1) & 3)); };
-        uint2 cur[P];
+        uint32_t cur[P];
         auto store_chunk = [&](int c) {
             const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
             #pragma unroll
-            for (int i = 0; i < P / 2; ++i) {
+            for (int i = 0; i < P / 4; ++i) {
                 const int q = i * kProducerThreads + tid, r = q >> lgP;
                 sts128(buf + (uint32_t)((r << lgP) + swz(r, q & (P - 1))) * 16u, pre[i]);
             }
@@ -230,45 +232,44 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         auto read_chunk = [&](int c) {
             const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
             #pragma unroll
-            for (int j = 0; j < P; ++j) cur[j] = lds64_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 8u);
+            for (int j = 0; j < P; ++j) cur[j] = lds32_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 4u);
         };
         // A goes to TENSOR MEMORY, not shared memory: lane = output row of the tile, a k block = 32 columns (two 16-bit
-        // elements each, K-major), ring of S * BPS k blocks after the accumulator's columns.  A thread's 4 groups are 16
-        // consecutive columns of its own lane: one tcgen05.st 32x32b.x16 per k block (a warp reaches lanes 32*(warp%4)..+31,
+        // elements each, K-major), ring of S * BPS k blocks after the accumulator's columns.  A thread's 2 groups are 8
+        // consecutive columns of its own lane: one tcgen05.st 32x32b.x8 per k block (a warp reaches lanes 32*(warp%4)..+31,
         // which is how rows are dealt to warps already).  The MMA reads it as its A operand ([tmem] form), so the
         // dequantized tile costs no shared-memory store and no shared-memory read by the tensor core.
         // Whole warps past the CTA's rows skip the work; dead rows inside a live warp run on zero codes (never stored).
         const bool warp_live = (warp & 3) * 32 < p.rpc;
-        const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 16u;
+        const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 8u;
         int s = 0;                                                       // stage of this k block
         uint32_t parE = 1u;                                              // parity to wait for on empty[s] (a fresh barrier passes parity 1)
-        auto do_stage = [&](int kb, const uint2* cw) {                   // k blocks kb .. kb+BPS-1, code words cw[0 .. BPS-1]
+        auto do_stage = [&](int kb, const uint32_t* cw) {                   // k blocks kb .. kb+BPS-1, code words cw[0 .. BPS-1]
             mbar_wait(empty_bar(s), parE);                               // the MMAs that read this stage's last contents have retired
             tc_fence_after();
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
                 if (kb + sb >= kb1) break;
-                const uint32_t w[2] = {cw[sb].x, cw[sb].y};
-                if (!(p.dbg & 2) && warp_live) {                         // 4 groups: 8 reads in flight, then adds and ONE tensor-memory store
-                    uint4 a[4], b[4];
-                    uint32_t v[16];
+                const uint32_t w = cw[sb];
+                if (!(p.dbg & 2) && warp_live) {                         // 2 groups: 4 reads in flight, then adds and ONE tensor-memory store
+                    uint4 a[2], b[2];
+                    uint32_t v[8];
                     #pragma unroll
-                    for (int g = 0; g < 4; ++g) {                        // bytes 2g / 2g+1 of the half = codebook-0 / codebook-1 index
-                        const uint32_t wg = w[g >> 1];
-                        a[g] = lds128(cbA + __byte_perm(wg, 0u, 0x4440u + 2u * (g & 1)) * 128u);
-                        b[g] = lds128(cbB + __byte_perm(wg, 0u, 0x4441u + 2u * (g & 1)) * 128u);
+                    for (int g = 0; g < 2; ++g) {                        // bytes 2g / 2g+1 of the quarter = codebook-0 / codebook-1 index
+                        a[g] = lds128(cbA + __byte_perm(w, 0u, 0x4440u + 2u * g) * 128u);
+                        b[g] = lds128(cbB + __byte_perm(w, 0u, 0x4441u + 2u * g) * 128u);
                     }
                     #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
+                    for (int g = 0; g < 2; ++g) {
                         const T2* a2 = reinterpret_cast<const T2*>(&a[g]);
                         const T2* b2 = reinterpret_cast<const T2*>(&b[g]);
                         #pragma unroll
-                        for (int jj = 0; jj < 4; ++jj) {                 // column 4g + jj of the half = elements k = 8g + 2jj, + 1
+                        for (int jj = 0; jj < 4; ++jj) {                 // column 4g + jj of the quarter = elements k = 8g + 2jj, + 1
                             const T2 r = D::add2(a2[jj], b2[jj]);
                             v[4 * g + jj] = *reinterpret_cast<const uint32_t*>(&r);
                         }
                     }
-                    tc_st16(a_lane + (uint32_t)(s * BPS + sb) * kATmemCols, v);
+                    tc_st8(a_lane + (uint32_t)(s * BPS + sb) * kATmemCols, v);
                 }
             }
             tc_wait_st();                                                // this warp's rows of the stage are in tensor memory
@@ -278,7 +279,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             if (++s == S) { s = 0; parE ^= 1u; }
         };
         store_chunk(0);
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, 512;" ::: "memory");
         read_chunk(0);
         if (kb0 + P < kb1) load_chunk(1);
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
@@ -287,7 +288,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                 if (kbc + j < kb1) do_stage(kbc + j, &cur[j]);
             if (kbc + P < kb1 && !(p.dbg & 32)) {
                 store_chunk(c + 1);
-                asm volatile("bar.sync 1, 256;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
+                asm volatile("bar.sync 1, 512;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
                 read_chunk(c + 1);
                 if (kbc + 2 * P < kb1) load_chunk(c + 2);
             }
@@ -309,7 +310,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             static_cast<T*>(p.y)[(size_t)b * p.O + o] = rr;
         };
         if (p.ksplit == 1) {
-            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 32) {
+            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 64) {
                 uint32_t v[16];
                 tc_ld16(taddr + (uint32_t)c0, v);
                 #pragma unroll
@@ -318,7 +319,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             }
         } else {
             float* mine = p.partial + ((size_t)z * p.n_pad) * p.O_pad + o;
-            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 32) {
+            for (int c0 = hk * 16; c0 < p.n_pad; c0 += 64) {
                 uint32_t v[16];
                 tc_ld16(taddr + (uint32_t)c0, v);
                 #pragma unroll
@@ -326,13 +327,13 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                     if (live && c0 + j < p.batch) __stcg(mine + (size_t)(c0 + j) * p.O_pad, __uint_as_float(v[j]));
             }
             __threadfence();
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, 512;" ::: "memory");
             if (tid == 0) *last_flag_ptr = (atomicAdd(p.counters + tile, 1u) == (unsigned)p.ksplit - 1u) ? 1u : 0u;
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, 512;" ::: "memory");
             if (*last_flag_ptr) {                                        // last CTA of this tile: fixed-order sum of the partials
                 __threadfence();
                 if (live)
-                    for (int b = hk; b < p.batch; b += 2) {
+                    for (int b = hk; b < p.batch; b += 4) {
                         float acc = 0.f;
                         for (int zz = 0; zz < p.ksplit; ++zz)
                             acc += __ldcg(p.partial + ((size_t)zz * p.n_pad + b) * p.O_pad + o);
