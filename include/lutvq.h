@@ -154,16 +154,20 @@ int lutvq_code2x8_dequant(const void* codes, void* W, const void* codebook, cons
 /* Kx8 generalisation (num_codebooks N in 1..8 codebooks of 256 entries, groups of 8; fp16; batch >= 0):
  *   lutvq_codeKx8_matmat   <- codeKx8_matmat / code1x8_matmat + CodeKx8MatVec   aqlm/cuda_kernel.cpp:521-684, cuda_kernel.cu:296-390
  *   lutvq_codeKx8_dequant  <- CodeKx8Dequant (sequential fp16 adds in codebook order) aqlm/cuda_kernel.cu:392-468
- * codes int8 [prob_m][prob_k/8][N]; codebooks fp16 [N][256][8].  Correct, unfused (fp32 LUT in the workspace + gather +
- * reference epilogue); the tuned fused kernel is the N = 2 path above.  ws >= lutvq_codeKx8_workspace_bytes. */
+ * codes int8 [prob_m][prob_k/8][N]; codebooks fp16 / bf16 [N][256][8].  N = 1, 2, 4, 8 run on the tuned fused LUT-GEMV (kernel
+ * templated on the codebooks per group); N = 3, 5, 6, 7 take the unfused pair (fp32 LUT in the workspace + gather + reference
+ * epilogue).  ws >= lutvq_codeKx8_workspace_bytes. */
 size_t lutvq_codeKx8_workspace_bytes(int prob_m, int prob_k, int num_codebooks);
 int lutvq_codeKx8_matmat(const void* x, const void* codes, const void* codebooks, const void* scales, const void* bias, void* y,
                          int batch, int prob_m, int prob_k, int num_codebooks, int dtype, void* ws, size_t ws_bytes, void* stream);
 int lutvq_codeKx8_dequant(const void* codes, void* W, const void* codebooks, const void* scales, int prob_m, int prob_k,
                           int num_codebooks, int dtype, void* stream);
 
-/* Prefill path: y = x . W^T with W dequantized on the fly into shared memory and contracted on the
- * tcgen05 tensor cores (fp32 accumulation in TMEM), then the matmat epilogue.  Same arguments as matmat. */
+/* Prefill path: y = x . W^T with W dequantized on the fly into TENSOR MEMORY (A operand of tcgen05.mma; the activations arrive
+ * by TMA tensor copies) and contracted on the tcgen05 tensor cores (fp32 accumulation in TMEM), then the matmat epilogue.  Same
+ * arguments as matmat; x must be 16-byte aligned.  A launch takes up to 256 rows; larger batches are chunked (the host-side op
+ * switches to lutvq_code2x8_dequant + a library GEMM above 256 rows).  Launched with programmatic stream
+ * serialization: reads codes / codebooks before the previous kernel on the stream has completed (weights must not be written by it). */
 int lutvq_code2x8_matmat_dequant(const void* x, const void* codes, const void* codebooks, const void* scales,
                                  const void* bias, void* y, int batch, int prob_m, int prob_k, int dtype,
                                  void* ws, size_t ws_bytes, void* stream);
