@@ -100,6 +100,7 @@ DEBUG_SIGNATURES = {
     "lutvq_debug_set_dependent_workers": (None, [I]),
     "lutvq_debug_get_gemv_plan": (None, [I, I, P, P, P]),
     "lutvq_debug_set_gemm_mode": (None, [I]),
+    "lutvq_debug_set_gemm_stamps": (None, [P]),
     "lutvq_debug_set_pq4_mode": (None, [I]),
     "lutvq_debug_set_1x16_mode": (None, [I]),
     "lutvq_debug_set_1x16_plan": (None, [I, I]),

@@ -28,6 +28,7 @@ int gemv_prepack_launch(const void* codes, void* packed, int O, int I, cudaStrea
 void gemv_set_tuning(int nw, int pf, int pa);
 void gemv_set_timeline(void* buf);
 void gemm_set_debug_mode(int m);
+void gemm_set_stamps(void* dev_ptr);
 void gemv_get_plan(int O, int I, int* n_k, int* n_chunks, int* rows_per_chunk);
 int code2x8_dequant_launch(const void* codes, void* W, const void* codebook, const void* scales, int O, int I,
                            int dtype, cudaStream_t stream);
@@ -293,6 +294,7 @@ void lutvq_debug_set_gemv_tuning(int nw, int pf, int pa) { gemv_set_tuning(nw, p
 void lutvq_debug_set_timeline(void* buf) { gemv_set_timeline(buf); }
 void lutvq_debug_set_dependent_workers(int per_sm) { gemv_set_dependent_workers(per_sm); }
 void lutvq_debug_set_gemm_mode(int m) { gemm_set_debug_mode(m); }
+void lutvq_debug_set_gemm_stamps(void* dev_ptr) { gemm_set_stamps(dev_ptr); }
 void lutvq_debug_get_gemv_plan(int prob_m, int prob_k, int* n_k, int* n_chunks, int* rows_per_chunk) {
     gemv_get_plan(prob_m, prob_k, n_k, n_chunks, rows_per_chunk);
 }

@@ -57,6 +57,7 @@ struct GemmParams {
     int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, a_col0;    // a_col0 = first tensor-memory column of the A ring (after the n_pad accumulator columns)
     int rpc;                // output rows this CTA owns (<= 128, multiple of 8): rows of the M=128 tile past it are never dequantized or stored
     int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
+    unsigned long long* stamps;   // experiments only (lutvq_debug_set_gemm_stamps): [CTA][8] %globaltimer stamps of thread 0, or null
     int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
 };
 
@@ -141,6 +142,14 @@ __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
     return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+__device__ __forceinline__ void gemm_stamp(const GemmParams& p, int i) {
+    if (p.stamps != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.stamps[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 8 + i] = t;
+    }
+}
+
 template <int DT, int P, int BPS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap xmap) {
@@ -184,6 +193,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     };
     if (warp < kProducerThreads / 32) load_chunk(0);
 
+    gemm_stamp(p, 0);
     // ---------------- one-time setup ----------------
     if (tid == kProducerThreads) {
         for (int i = 0; i < S; ++i) { mbar_init(full_bar(i), kProducerThreads / 32 + 1); mbar_init(empty_bar(i), 1); }
@@ -204,8 +214,10 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     // Up to here only weights were read (code chunk 0, codebook).  The successor may be released right away -- it cannot
     // co-reside (shared memory, tensor memory), it takes the SM when this CTA exits; activations, outputs and the split-k
     // workspace are touched only once the predecessor has completed.
+    gemm_stamp(p, 1);
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    gemm_stamp(p, 2);
 
     if (warp < kProducerThreads / 32) {
         const int row = tid & (kBM - 1), hk = tid >> 7;                  // this thread's row of the tile and quarter (2 groups = 4 code bytes) of every k block
@@ -286,6 +298,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             #pragma unroll
             for (int j = 0; j < P; j += BPS)
                 if (kbc + j < kb1) do_stage(kbc + j, &cur[j]);
+            if (c == 0) gemm_stamp(p, 3);
             if (kbc + P < kb1 && !(p.dbg & 32)) {
                 store_chunk(c + 1);
                 asm volatile("bar.sync 1, 512;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
@@ -295,8 +308,10 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         }
 
         // =============================== epilogue ===============================
+        gemm_stamp(p, 4);
         mbar_wait(accum_bar, 0u);
         tc_fence_after();
+        gemm_stamp(p, 5);
         const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);   // a warp reaches TMEM lanes 32*(warp%4)..+31
         const int o = row0 + row;
         const bool live = row < p.rpc && o < p.O;                        // the two warps of a row split the batch columns
@@ -394,6 +409,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         __syncwarp();
     }
 
+    gemm_stamp(p, 6);
     // ---------------- teardown ----------------
     tc_fence_before();
     __syncthreads();
@@ -407,6 +423,8 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
 
 static int g_gemm_dbg = 0;
 void gemm_set_debug_mode(int m) { g_gemm_dbg = m; }
+static unsigned long long* g_gemm_stamps = nullptr;
+void gemm_set_stamps(void* dev_ptr) { g_gemm_stamps = static_cast<unsigned long long*>(dev_ptr); }
 
 struct GemmPlan { int n_tiles, rpc, O_pad, nkb, ksplit; };
 
@@ -525,6 +543,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         p.n_pad = ceil_div(nb, 16) * 16;
         p.nkb = pl.nkb; p.ksplit = pl.ksplit;
         p.dbg = g_gemm_dbg;
+        p.stamps = g_gemm_stamps;
         p.a_col0 = ceil_div(p.n_pad, 32) * 32;                          // accumulator: columns [0, n_pad); A ring behind it
         int bps = p.n_pad <= 64 ? 4 : p.n_pad <= 128 ? 2 : 1;             // k blocks per pipeline stage (a stage hand-over costs ~0.25 us)
         if (g_gemm_dbg & 128) bps = 1;

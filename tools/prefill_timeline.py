@@ -1,0 +1,34 @@
+#!/usr/bin/env python
+"""Where a CTA of the prefill kernel spends its life: %globaltimer stamps of thread 0 (lutvq_debug_set_gemm_stamps) for a run of
+back-to-back launches on 4096x11008; prints, per batch size, the average over CTAs and launches of each interval in us.
+stamps: 0 entry, 1 set-up done, 2 dependency wait passed, 3 first code chunk's stages handed over, 4 producer loop done,
+5 accumulator complete, 6 epilogue done."""
+import ctypes, os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from rvv_lut_vq_b200 import ops, synth, _lib
+
+dev = torch.device("cuda", 0)
+NB, LAUNCHES = 24, 48
+Ls = [synth.make_layer_torch(4096, 11008, dev, seed=k, scales="ones") for k in range(NB)]
+lib = _lib.lib()
+NAMES = ["set-up", "dependency wait", "first chunk", "rest of the loop", "wait for the accumulator", "epilogue"]
+for batch in (16, 64, 256):
+    x = torch.randn((batch, 4096), device=dev, dtype=torch.float16)
+    bufs = [torch.zeros((160, 8), dtype=torch.int64, device=dev) for _ in range(LAUNCHES)]
+    for _ in range(2):
+        for k in range(LAUNCHES):
+            lib.lutvq_debug_set_gemm_stamps(ctypes.c_void_p(bufs[k].data_ptr()))
+            L = Ls[k % NB]
+            ops.code2x8_matmat_dequant_fused(x, L["codes"], L["codebooks"], L["scales"], None)
+    lib.lutvq_debug_set_gemm_stamps(None)
+    torch.cuda.synchronize()
+    t = torch.stack(bufs).double().cpu()[8:, :138, :7]                     # [launch][CTA][stamp], first launches dropped
+    iv = (t[:, :, 1:] - t[:, :, :-1]).mean(dim=(0, 1)) / 1e3
+    life = (t[:, :, 6] - t[:, :, 0]).mean() / 1e3
+    start = t[:, :, 0].min(dim=1).values
+    period = ((start[1:] - start[:-1]).mean() / 1e3).item()
+    spread = ((t[:, :, 0].max(dim=1).values - start).mean() / 1e3).item()
+    end_spread = ((t[:, :, 6].max(dim=1).values - t[:, :, 6].min(dim=1).values).mean() / 1e3).item()
+    print(f"batch {batch}: launch period {period:.2f} us (eager launches), CTA life {life:.2f} us, entry spread {spread:.2f}, exit spread {end_spread:.2f}")
+    print("   " + ", ".join(f"{n} {v:.2f}" for n, v in zip(NAMES, iv.tolist())), flush=True)
