@@ -57,7 +57,7 @@ struct GemmParams {
     int O, O_pad, I, batch, n_pad, nkb, ksplit, stages, a_col0;    // a_col0 = first tensor-memory column of the A ring (after the n_pad accumulator columns)
     int rpc;                // output rows this CTA owns (<= 128, multiple of 8): rows of the M=128 tile past it are never dequantized or stored
     int chunk;              // k blocks per staged code chunk: 8 (128 B per row) or 4
-    unsigned long long* stamps;   // experiments only (lutvq_debug_set_gemm_stamps): [CTA][8] %globaltimer stamps of thread 0, or null
+    unsigned long long* stamps;   // experiments only (lutvq_debug_set_gemm_stamps): [CTA][16]: %globaltimer stamps of thread 0 (0..6), cycle totals (8..12), or null
     int dbg;                // experiments only (lutvq_debug_set_gemm_mode): 1 = no MMAs, 2 = no dequantization, 4 = no activation copies
 };
 
@@ -90,6 +90,22 @@ __device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, 
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
         :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// the same, executed by a CONVERGED warp: one elected lane issues
+__device__ __forceinline__ void tc_mma_f16_ts_elect(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
+    asm volatile(
+        "{\n\t.reg .pred e;\n\t"
+        "elect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+        :: "r"(bar) : "memory");
 }
 // 8 consecutive 32-bit columns of this thread's lane (warp w reaches lanes 32*(w%4) .. +31); warp-collective
 __device__ __forceinline__ void tc_st8(uint32_t taddr, const uint32_t (&v)[8]) {
@@ -142,12 +158,24 @@ __device__ __forceinline__ uint32_t umma_idesc(int bf16, int M, int N) {
     return (1u << 4) | ((uint32_t)bf16 << 7) | ((uint32_t)bf16 << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// Timeline instrumentation (tools/prefill_timeline.py): compiled in only with -DLUTVQ_GEMM_TIMELINE (make EXTRA=-DLUTVQ_GEMM_TIMELINE);
+// otherwise all of it folds away.
+#ifdef LUTVQ_GEMM_TIMELINE
+constexpr bool kTimeline = true;
+#else
+constexpr bool kTimeline = false;
+#endif
+__device__ __forceinline__ long long tl_clock() { return kTimeline ? clock64() : 0ll; }
 __device__ __forceinline__ void gemm_stamp(const GemmParams& p, int i) {
-    if (p.stamps != nullptr && threadIdx.x == 0) {
+    if (kTimeline && p.stamps != nullptr && threadIdx.x == 0) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        p.stamps[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 8 + i] = t;
+        p.stamps[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 16 + i] = t;
     }
+}
+// cycle totals of one thread (experiments): slot i of the CTA's row
+__device__ __forceinline__ void gemm_total(const GemmParams& p, int i, long long cycles) {
+    if (kTimeline && p.stamps != nullptr) p.stamps[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 16 + i] = (unsigned long long)cycles;
 }
 
 template <int DT, int P, int BPS>
@@ -254,10 +282,13 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // Whole warps past the CTA's rows skip the work; dead rows inside a live warp run on zero codes (never stored).
         const bool warp_live = (warp & 3) * 32 < p.rpc;
         const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 8u;
+        long long t_empty = 0, t_stage = 0, t_st = 0;                    // experiments: cycles in the empty wait / code staging / STTM wait
         int s = 0;                                                       // stage of this k block
         uint32_t parE = 1u;                                              // parity to wait for on empty[s] (a fresh barrier passes parity 1)
         auto do_stage = [&](int kb, const uint32_t* cw) {                   // k blocks kb .. kb+BPS-1, code words cw[0 .. BPS-1]
+            const long long tw0 = tl_clock();
             mbar_wait(empty_bar(s), parE);                               // the MMAs that read this stage's last contents have retired
+            t_empty += tl_clock() - tw0;
             tc_fence_after();
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
@@ -284,7 +315,9 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                     tc_st8(a_lane + (uint32_t)(s * BPS + sb) * kATmemCols, v);
                 }
             }
+            const long long ts0 = tl_clock();
             tc_wait_st();                                                // this warp's rows of the stage are in tensor memory
+            t_st += tl_clock() - ts0;
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
@@ -300,14 +333,17 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                 if (kbc + j < kb1) do_stage(kbc + j, &cur[j]);
             if (c == 0) gemm_stamp(p, 3);
             if (kbc + P < kb1 && !(p.dbg & 32)) {
+                const long long tg0 = tl_clock();
                 store_chunk(c + 1);
                 asm volatile("bar.sync 1, 512;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
                 read_chunk(c + 1);
                 if (kbc + 2 * P < kb1) load_chunk(c + 2);
+                t_stage += tl_clock() - tg0;
             }
         }
 
         // =============================== epilogue ===============================
+        if (tid == 0) { gemm_total(p, 8, t_empty); gemm_total(p, 9, t_stage); gemm_total(p, 10, t_st); }
         gemm_stamp(p, 4);
         mbar_wait(accum_bar, 0u);
         tc_fence_after();
@@ -382,31 +418,43 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         }
         __syncwarp();
     } else {
-        // =============================== MMA issuer (warp 8) ===============================
+        // =============================== MMA issuer ===============================
+        // The whole warp runs this loop CONVERGED and one elected lane issues (elect.sync inside the asm): under `if (lane == 0)`
+        // the compiler wraps every tcgen05 instruction in an ELECT / vote / branch loop, and with the descriptors rebuilt per MMA
+        // (shift, mask, or: a chain of dependent uniform-datapath ops) one MMA took ~96 cycles to ISSUE -- 256 of them were the
+        // whole loop time at <= 64 columns.  The descriptors' low words now advance by adds: B by 2 per k step (32 bytes), by
+        // bblock/16 per k block; A by 8 columns per k step.
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
+        const uint64_t bdesc0 = umma_desc_sw128(sB);
+        const uint32_t bdesc_hi = (uint32_t)(bdesc0 >> 32), bstage16 = bstage >> 4, bblock16 = bblock >> 4;
+        const bool do_mma = !(p.dbg & 1);
+        uint32_t b_lo = (uint32_t)bdesc0;                                // low word of the stage's first descriptor
+        uint32_t a_t = tmem_base + (uint32_t)p.a_col0;                   // the stage's first A column
         int s = 0;
         uint32_t par = 0u;
+        long long t_full = 0;
+        const long long tl0 = tl_clock();
         for (int kb = kb0; kb < kb1; kb += BPS) {
+            const long long tf0 = tl_clock();
             mbar_wait(full_bar(s), par);
+            t_full += tl_clock() - tf0;
             tc_fence_after();
-            if (lane == 0) {
+            #pragma unroll
+            for (int sb = 0; sb < BPS; ++sb) {
+                if (kb + sb >= kb1) break;
                 #pragma unroll
-                for (int sb = 0; sb < BPS; ++sb) {
-                    if (kb + sb >= kb1) break;
-                    #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k) {
-                        const uint32_t a_t = tmem_base + (uint32_t)p.a_col0 + (uint32_t)(s * BPS + sb) * kATmemCols + (uint32_t)k * 8u;
-                        const uint64_t bdesc = umma_desc_sw128(sB + (uint32_t)s * bstage + (uint32_t)sb * bblock + (uint32_t)k * 32u);
-                        if (!(p.dbg & 1)) tc_mma_f16_ts(tmem_base, a_t, bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
-                    }
+                for (int k = 0; k < kBK / 16; ++k) {
+                    const uint64_t bdesc = ((uint64_t)bdesc_hi << 32) | (uint64_t)(b_lo + (uint32_t)sb * bblock16 + (uint32_t)k * 2u);
+                    if (do_mma) tc_mma_f16_ts_elect(tmem_base, a_t + (uint32_t)(sb * kATmemCols + k * 8), bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
                 }
-                tc_commit(empty_bar(s));                                 // smem stage free once these MMAs have read it
             }
-            __syncwarp();
-            if (++s == S) { s = 0; par ^= 1u; }
+            tc_commit_elect(empty_bar(s));                               // smem stage free once these MMAs have read it
+            b_lo += bstage16;
+            a_t += (uint32_t)(BPS * kATmemCols);
+            if (++s == S) { s = 0; par ^= 1u; b_lo = (uint32_t)bdesc0; a_t = tmem_base + (uint32_t)p.a_col0; }
         }
-        if (lane == 0) tc_commit(accum_bar);                             // accumulator complete
-        __syncwarp();
+        if (lane == 0) { gemm_total(p, 11, t_full); gemm_total(p, 12, tl_clock() - tl0); }
+        tc_commit_elect(accum_bar);                                      // accumulator complete
     }
 
     gemm_stamp(p, 6);
@@ -424,7 +472,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
 static int g_gemm_dbg = 0;
 void gemm_set_debug_mode(int m) { g_gemm_dbg = m; }
 static unsigned long long* g_gemm_stamps = nullptr;
-void gemm_set_stamps(void* dev_ptr) { g_gemm_stamps = static_cast<unsigned long long*>(dev_ptr); }
+void gemm_set_stamps(void* dev_ptr) { g_gemm_stamps = static_cast<unsigned long long*>(dev_ptr); }   // no effect without LUTVQ_GEMM_TIMELINE
 
 struct GemmPlan { int n_tiles, rpc, O_pad, nkb, ksplit; };
 
