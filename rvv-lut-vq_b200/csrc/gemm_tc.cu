@@ -11,8 +11,8 @@
 //   warps 0-15 producers: each thread owns one output row and one quarter of every 64-wide k block (2 groups = 4 code bytes);
 //              per group two conflict-free 128-bit reads of the 8x replicated codebooks in shared memory, one HADD2 x4 (the
 //              SAME single RN add as Code2x8Dequant, cuda_kernel.cu:283-289); the 8 resulting 32-bit words are 8 consecutive
-//              columns of the thread's own tensor-memory lane: one tcgen05.st per k block.  The code stream is staged per
-//              chunk of 4 / 8 k blocks (coalesced 16-byte loads a chunk ahead -> swizzled shared buffer -> per-row words).
+//              columns of the thread's own tensor-memory lane: one tcgen05.st per k block.  Its code words come from the
+//              chunk ring (warp 18): wait for the chunk's barrier, one 32-bit shared load per k block, release the slot.
 //              Afterwards the same warps run the epilogue (tcgen05.ld 32x32b: thread = output channel, registers = batch
 //              columns).
 //   warp 16    one elected thread issues tcgen05.mma (M=128, N=batch padded to 16, K=16; A operand = tensor-memory address,
@@ -21,6 +21,9 @@
 //   warp 17    one thread brings in the activations: the tile of a k block (batch x 64, SWIZZLE_128B K-major) is ONE 2-D TMA
 //              tensor copy (cp.async.bulk.tensor) completing on the stage's full barrier, issued as soon as the stage is
 //              empty, i.e. up to the whole ring ahead of the dequantization; rows past the batch arrive as zeros.
+//   warp 18    one thread brings in the CODES: per chunk of 4 (8) k blocks one TMA tensor copy of {64 (128) bytes x the CTA's
+//              rows} of the [O][I/4] byte matrix (64- / 128-byte swizzle) into a ring of kCodeRing shared buffers, up to the whole
+//              ring ahead and starting before anything else in the kernel.  No register staging, no block-wide barrier.
 //   mbarrier ring of `stages` stages of 1 / 2 / 4 k blocks (full: one arrival per producer warp + the copy thread's
 //   expect_tx arrival and the copy's bytes; empty: tcgen05.commit).  Programmatic dependent launch: everything before
 //   griddepcontrol.wait reads weights only.
@@ -40,7 +43,8 @@ namespace lutvq {
 constexpr int kBM = 128;                 // output channels per CTA (UMMA M)
 constexpr int kBK = 64;                  // k per stage = 8 AQLM groups = 16 code bytes per row
 constexpr int kProducerThreads = 512;      // 16 warps: thread = (output row, quarter of the k block); four warps per scheduler hide the LDS / STTM latency
-constexpr int kGemmThreads = 576;          // + the MMA warp + the TMA warp
+constexpr int kGemmThreads = 608;          // + the MMA warp + the activation-copy warp + the code-copy warp
+constexpr int kCodeRing = 4;               // code chunks in flight per CTA (shared-memory ring filled by TMA)
 constexpr int kCbSmemBytes = 2 * 256 * 8 * 16;     // [cb][idx][copy] x 16 B (same replication as dequant.cu)
 constexpr int kATmemCols = kBK / 2;                // a k block of A in tensor memory: 128 lanes (rows) x 32 columns (2 fp16 each)
 constexpr int kTmemCols = 512;                     // the whole tensor memory of the SM: accumulator columns, then the A ring
@@ -180,7 +184,7 @@ __device__ __forceinline__ void gemm_total(const GemmParams& p, int i, long long
 
 template <int DT, int P, int BPS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap xmap) {
+gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap xmap, const __grid_constant__ CUtensorMap cmap) {
     using D = Dtype<DT>;
     using T = typename D::T;
     using T2 = typename D::T2;
@@ -188,10 +192,11 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     const uint32_t sbase = smem_u32(smem);
     uint4* sh_cb = reinterpret_cast<uint4*>(smem);
     const int S = p.stages;
-    const uint32_t sC = sbase + kCbSmemBytes;                               // 2 code-chunk buffers of 128 rows x chunk x 16 B
+    const uint32_t sC = sbase + kCbSmemBytes;                               // ring of kCodeRing code chunks of 128 rows x P x 16 B
+    constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
     // a pipeline stage = BPS k blocks (every mbarrier round trip costs ~150 cycles per warp: small batches take 2 per stage)
     const uint32_t bblock = (uint32_t)p.n_pad * 128u, bstage = (uint32_t)BPS * bblock;
-    const uint32_t sB = sC + 2u * (uint32_t)kBM * (uint32_t)P * 16u;       // activation stages (1024-byte aligned: SWIZZLE_128B)
+    const uint32_t sB = sC + (uint32_t)kCodeRing * cbuf;                   // activation stages (1024-byte aligned: SWIZZLE_128B)
     const uint32_t bars = sB + (uint32_t)S * bstage;
     auto full_bar  = [&](int i) { return bars + 8u * (uint32_t)i; };
     auto empty_bar = [&](int i) { return bars + 8u * (uint32_t)(S + i); };
@@ -199,27 +204,35 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
     const uint32_t tmem_slot = accum_bar + 8u;
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem + (tmem_slot - sbase));
     volatile uint32_t* last_flag_ptr = tmem_slot_ptr + 1;
+    auto code_full  = [&](int i) { return tmem_slot + 8u + 8u * (uint32_t)i; };
+    auto code_empty = [&](int i) { return tmem_slot + 8u + 8u * (uint32_t)(kCodeRing + i); };
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int tile = blockIdx.x, z = blockIdx.y;
     const int row0 = tile * p.rpc;
     const int kb0 = (int)(((long long)z * p.nkb) / p.ksplit), kb1 = (int)(((long long)(z + 1) * p.nkb) / p.ksplit);
 
-    // The code stream is staged per CHUNK of P k blocks = P*16 bytes of every row: each producer thread loads P/2 16-byte
-    // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead).  Chunk 0 is requested
-    // before anything else: its HBM round trip then runs beside the codebook's instead of after it.
+    // The code stream arrives per CHUNK of P k blocks = P*16 bytes of each of the CTA's rows: ONE TMA tensor copy per chunk
+    // (box {P*16 bytes, rpc rows} of the [O][I/4] byte matrix, 64- / 128-byte swizzle = the XOR the per-row reads undo) into a
+    // ring of kCodeRing shared buffers, issued by a warp of its own up to the whole ring ahead.  No register staging, no
+    // block-wide barrier: a producer warp waits for the chunk's barrier, reads its rows' words and moves on at its own pace.
+    // The first chunks are requested before anything else (weights: nothing to wait for).
     constexpr int lgP = P == 8 ? 3 : 2;
-    uint4 pre[P / 4];
-    auto load_chunk = [&](int c) {
-        const int kbase = kb0 + c * P;
-        #pragma unroll
-        for (int i = 0; i < P / 4; ++i) {
-            const int q = i * kProducerThreads + tid, r = q >> lgP, kb = kbase + (q & (P - 1));
-            const int grow = min(row0 + r, p.O - 1);                     // rows past the end recompute the last row; never stored
-            pre[i] = (kb < kb1 && r < p.rpc) ? ldg_stream_u128(p.codes + (size_t)grow * (size_t)(p.I / 4) + (size_t)kb * 16) : make_uint4(0u, 0u, 0u, 0u);
-        }
+    const uint32_t chunk_bytes = (uint32_t)p.rpc * P * 16u;
+    int cw_c = 0, cw_b = 0;                                              // code warp: next chunk / its ring slot
+    uint32_t cw_par = 0u;
+    auto issue_code = [&]() {                                            // one thread
+        mbar_arrive_expect_tx(code_full(cw_b), chunk_bytes);
+        tma_load_2d(sC + (uint32_t)cw_b * cbuf, &cmap, code_full(cw_b), (kb0 + cw_c * P) * 16, row0);
+        ++cw_c;
+        if (++cw_b == kCodeRing) cw_b = 0;
     };
-    if (warp < kProducerThreads / 32) load_chunk(0);
+    const int n_chunks = (kb1 - kb0 + P - 1) / P;
+    if (tid == kProducerThreads + 64) {
+        for (int i = 0; i < kCodeRing; ++i) { mbar_init(code_full(i), 1); mbar_init(code_empty(i), kProducerThreads / 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        while (cw_c < n_chunks && cw_c < kCodeRing) issue_code();
+    }
 
     gemm_stamp(p, 0);
     // ---------------- one-time setup ----------------
@@ -252,27 +265,18 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // =============================== producers: dequantize A, copy B ===============================
         const uint32_t cbA = sbase + (uint32_t)(lane & 7) * 16u;         // this lane's copy of codebook 0; entry i at + i*128
         const uint32_t cbB = cbA + 256u * 8u * 16u;
-        // The loop is bound by instruction issue (one producer warp per scheduler), so everything that is not a codebook
-        // read, an add or a store is kept out of it: stage indices and parities are carried, not divided; the code
-        // stream is staged per CHUNK of P k blocks.  A chunk = P*16 bytes of every row: each thread loads P 16-byte
-        // pieces so that a warp reads whole rows' contiguous bytes (registers, a whole chunk ahead), stores them
-        // XOR-swizzled into one of two shared buffers, and after one producer barrier reads its own row's P code words
-        // back with conflict-free 128-bit loads.
-        constexpr uint32_t cbuf = (uint32_t)kBM * P * 16u;
         auto swz = [](int r, int c) { return P == 8 ? (c ^ (r & 7)) : (c ^ ((r >> 1) & 3)); };
         uint32_t cur[P];
-        auto store_chunk = [&](int c) {
-            const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
-            #pragma unroll
-            for (int i = 0; i < P / 4; ++i) {
-                const int q = i * kProducerThreads + tid, r = q >> lgP;
-                sts128(buf + (uint32_t)((r << lgP) + swz(r, q & (P - 1))) * 16u, pre[i]);
-            }
-        };
-        auto read_chunk = [&](int c) {
-            const uint32_t buf = sC + (uint32_t)(c & 1) * cbuf;
+        int rb = 0;                                                      // ring slot of the chunk being read
+        uint32_t rpar = 0u;
+        auto read_chunk = [&]() {
+            mbar_wait(code_full(rb), rpar);
+            const uint32_t buf = sC + (uint32_t)rb * cbuf;
             #pragma unroll
             for (int j = 0; j < P; ++j) cur[j] = lds32_sync(buf + (uint32_t)((row << lgP) + swz(row, j)) * 16u + (uint32_t)hk * 4u);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(code_empty(rb));                  // this warp's words are in registers: one arrival per warp
+            if (++rb == kCodeRing) { rb = 0; rpar ^= 1u; }
         };
         // A goes to TENSOR MEMORY, not shared memory: lane = output row of the tile, a k block = 32 columns (two 16-bit
         // elements each, K-major), ring of S * BPS k blocks after the accumulator's columns.  A thread's 2 groups are 8
@@ -323,23 +327,14 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             if (lane == 0) mbar_arrive(full_bar(s));                     // one arrival per warp
             if (++s == S) { s = 0; parE ^= 1u; }
         };
-        store_chunk(0);
-        asm volatile("bar.sync 1, 512;" ::: "memory");
-        read_chunk(0);
-        if (kb0 + P < kb1) load_chunk(1);
         for (int kbc = kb0, c = 0; kbc < kb1; kbc += P, ++c) {
+            const long long tg0 = tl_clock();
+            read_chunk();
+            t_stage += tl_clock() - tg0;
             #pragma unroll
             for (int j = 0; j < P; j += BPS)
                 if (kbc + j < kb1) do_stage(kbc + j, &cur[j]);
             if (c == 0) gemm_stamp(p, 3);
-            if (kbc + P < kb1 && !(p.dbg & 32)) {
-                const long long tg0 = tl_clock();
-                store_chunk(c + 1);
-                asm volatile("bar.sync 1, 512;" ::: "memory");           // every producer's pieces of chunk c+1 are stored; chunk c-1's buffer is read
-                read_chunk(c + 1);
-                if (kbc + 2 * P < kb1) load_chunk(c + 2);
-                t_stage += tl_clock() - tg0;
-            }
         }
 
         // =============================== epilogue ===============================
@@ -414,6 +409,17 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                         if (b < nblk) tma_load_2d(sB + (uint32_t)s * bstage + (uint32_t)b * bblock, &xmap, full_bar(s), (kb + b) * kBK, 0);
                 }
                 if (++s == S) { s = 0; par ^= 1u; }
+            }
+        }
+        __syncwarp();
+    } else if (warp == kProducerThreads / 32 + 2) {
+        // =============================== code copies (one thread): the chunks past the first ring ===============================
+        if (lane == 0) {
+            while (cw_c < n_chunks) {
+                mbar_wait(code_empty(cw_b), cw_par);                     // every producer warp has read the chunk that was here
+                const bool wrap = cw_b == kCodeRing - 1;
+                issue_code();
+                if (wrap) cw_par ^= 1u;
             }
         }
         __syncwarp();
@@ -546,8 +552,25 @@ static int make_x_map(CUtensorMap* map, const void* x, int batch, int I, int n_p
     return LUTVQ_OK;
 }
 
+// tensor map of the codes as a byte matrix [O][I/4] with a {chunk*16 bytes, rpc rows} box; the swizzle (64 bytes for chunks of 4
+// k blocks, 128 for 8) is the XOR the producers' per-row reads undo; rows past O arrive as zeros
+static int make_code_map(CUtensorMap* map, const void* codes, int O, int I, int chunk, int rpc) {
+    TensorMapEncodeTiledFn enc = tensor_map_encoder();
+    if (!enc) return fail(LUTVQ_ECUDA, "cuTensorMapEncodeTiled not available from this driver");
+    LUTVQ_REQUIRE(aligned16(codes), "codes must be 16-byte aligned");
+    const cuuint64_t dims[2] = {(cuuint64_t)I / 4, (cuuint64_t)O};
+    const cuuint64_t strides[1] = {(cuuint64_t)I / 4};
+    const cuuint32_t box[2] = {(cuuint32_t)chunk * 16u, (cuuint32_t)rpc};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(codes), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           chunk == 8 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(LUTVQ_ECUDA, "cuTensorMapEncodeTiled failed (CUresult %d) for codes[%d][%d], box {%d, %d}", (int)r, O, I / 4, chunk * 16, rpc);
+    return LUTVQ_OK;
+}
+
 template <int DT, int P, int BPS>
-static int launch_gemm(const GemmParams& p, const CUtensorMap& xmap, dim3 grid, size_t smem, cudaStream_t stream) {
+static int launch_gemm(const GemmParams& p, const CUtensorMap& xmap, const CUtensorMap& cmap, dim3 grid, size_t smem, cudaStream_t stream) {
     auto kern = gemm_dequant_tc_kernel<DT, P, BPS>;
     static thread_local int attr_device = -1;
     int dev = 0;
@@ -568,7 +591,7 @@ static int launch_gemm(const GemmParams& p, const CUtensorMap& xmap, dim3 grid, 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (p.dbg & 2048) ? 0 : 1;
-    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p, xmap));
+    LUTVQ_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, p, xmap, cmap));
     return LUTVQ_OK;
 }
 
@@ -599,7 +622,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         if ((g_gemm_dbg & 512) && bps == 1) bps = 2;
         const size_t stage_bytes = (size_t)bps * (size_t)p.n_pad * 128;       // activations only: A lives in tensor memory
         p.chunk = (p.n_pad <= 128 && bps == 1) ? 8 : 4;
-        const size_t code_bytes = 2 * (size_t)kBM * p.chunk * 16;
+        const size_t code_bytes = (size_t)kCodeRing * kBM * p.chunk * 16;
         const size_t budget = (size_t)227 * 1024 - kCbSmemBytes - code_bytes - 1024;
         int S = (int)(budget / stage_bytes);
         if (S > 8) S = 8;
@@ -607,7 +630,7 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
         if (S > s_tmem) S = s_tmem;
         if (S < 2) return fail(LUTVQ_EUNSUPPORTED, "not enough shared memory for 2 pipeline stages");
         p.stages = S;
-        size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32;
+        size_t smem = kCbSmemBytes + code_bytes + (size_t)S * stage_bytes + 16 * (size_t)S + 32 + 16 * kCodeRing;
         if (smem < (size_t)116 * 1024) smem = (size_t)116 * 1024;         // one CTA per SM: each allocates the whole tensor memory
         p.counters = nullptr; p.partial = nullptr;
         if (pl.ksplit > 1) {
@@ -618,13 +641,14 @@ int gemm_dequant_tc_launch(const void* x, const void* codes, const void* codeboo
             p.partial = reinterpret_cast<float*>(static_cast<uint8_t*>(ws) + 256 + gemv_acc_bytes(O));
         }
         const dim3 grid(pl.n_tiles, pl.ksplit);
-        CUtensorMap xmap;
+        CUtensorMap xmap, cmap;
         if (int rc = make_x_map(&xmap, p.x, nb, I, p.n_pad, dtype)) return rc;
+        if (int rc = make_code_map(&cmap, codes, O, I, p.chunk, p.rpc)) return rc;
         int rc;
-        if (bps == 4)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 4>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 4>(p, xmap, grid, smem, stream);
-        else if (bps == 2)     rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, xmap, grid, smem, stream);
-        else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, xmap, grid, smem, stream);
-        else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, xmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, xmap, grid, smem, stream);
+        if (bps == 4)          rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 4>(p, xmap, cmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 4>(p, xmap, cmap, grid, smem, stream);
+        else if (bps == 2)     rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 2>(p, xmap, cmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 2>(p, xmap, cmap, grid, smem, stream);
+        else if (p.chunk == 8) rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 8, 1>(p, xmap, cmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 8, 1>(p, xmap, cmap, grid, smem, stream);
+        else                   rc = dtype == LUTVQ_F16 ? launch_gemm<LUTVQ_F16, 4, 1>(p, xmap, cmap, grid, smem, stream) : launch_gemm<LUTVQ_BF16, 4, 1>(p, xmap, cmap, grid, smem, stream);
         if (rc) return rc;
     }
     return LUTVQ_OK;

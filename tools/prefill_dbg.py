@@ -1,5 +1,5 @@
 """Prefill kernel with parts switched off (lutvq_debug_set_gemm_mode: 1 = no MMAs, 2 = no dequantization, 4 = no
-activation copies, 8 = 128-row tiles, 16 = no proxy fence, 32 = no code staging after chunk 0, 128 = 1 k block per stage, 256 = 2, 2048 = no programmatic dependent launch); timing only, results are wrong in every mode but 0.  Graph-captured, ring of 24 layers."""
+activation copies, 8 = 128-row tiles, 16 = no proxy fence, 128 = 1 k block per stage, 256 = 2, 2048 = no programmatic dependent launch); timing only, results are wrong in every mode but 0.  Graph-captured, ring of 24 layers."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from rvv_lut_vq_b200 import ops, synth, _lib
