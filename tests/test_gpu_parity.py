@@ -239,7 +239,7 @@ def test_dequant_full_matrix_checksum(pkg, ops, orc):
     assert np.array_equal((got * weights).sum(axis=1), (Wref.astype(np.uint64) * weights).sum(axis=1))
 
 
-# ------------------------------------------------------------------ prefill: dequant -> smem -> tcgen05 GEMM
+# ------------------------------------------------------------------ prefill: dequant -> tensor memory -> tcgen05 GEMM
 GEMM_CASES = [
     # (in, out, batch, dtype, bias)
     (256, 128, 16, "f16", False),          # one row tile, 4 k blocks, no split
@@ -252,6 +252,11 @@ GEMM_CASES = [
     (4096, 11008, 16, "f16", True),        # 138 CTAs x 80 rows (rows-per-CTA plan), 2 k blocks per pipeline stage
     (11008, 4096, 32, "f16", True),        # split-k 4 x 43 k blocks: odd tail stage with 2 k blocks per stage
     (320, 200, 8, "bf16", False),          # 5 k blocks, ragged rows, one chunk
+    (64, 256, 3, "f16", False),            # ONE k block: a single, partial code chunk (fewer chunks than ring slots); no bias: with 64 terms a bias
+                                           # cancels enough outputs to near zero that the 2-ulp bar below stops meaning anything (the float64 bar held)
+    (512, 40, 129, "f16", False),          # 144 columns -> 1 k block per stage; fewer rows than two row warps
+    (1536, 300, 65, "bf16", True),         # 80 columns -> 2 k blocks per stage; 24 k blocks = 6 code chunks > the ring of 4
+    (8192, 1024, 40, "f16", True),         # 8 row tiles -> split-k 16 (8 k blocks per CTA = 2 chunks each)
 ]
 
 
