@@ -2,7 +2,7 @@
 rule (reference: benchmark/AQLM/inference_lib/src/aqlm/inference.py:11-142, kernel_selector.py:21-145).
 
 Formats with a kernel: AQLM 2x8 (the north-star hot path: fused LUT-GEMV on a prepacked code image for batch <= 6,
-dequantize-into-smem + tcgen05 GEMM above), 1x8 / Kx8 (N <= 8 codebooks of 256), 1x16 (65536-entry codebook, groups of 8 or
+dequantize-into-tensor-memory + tcgen05 GEMM above), 1x8 / Kx8 (N <= 8 codebooks of 256), 1x16 (65536-entry codebook, groups of 8 or
 16).  CUDA only; anything else raises NotImplementedError instead of taking a generic / Triton / CPU route."""
 from __future__ import annotations
 
@@ -17,6 +17,8 @@ from .kernel_selector import get_backward_pass_kernel, get_forward_pass_kernel
 from .utils import get_int_dtype
 
 GEMV_BATCH_THRESHOLD = 6  # inference.py:95: prod(input.shape[:-1]) <= 6 -> gemv op, else gemm op
+# (The reference's rule, kept as the default.  Measured on B200 at 4096x11008 the two ops cross at 3-4 rows: grouped GEMV 11.8 / 16.3 / 19.6 us
+# at 3 / 4 / 6 rows, the tcgen05 prefill kernel 14.1 us for any batch up to 16 -- DESIGN 4.1 / 4.4; lower this constant to 3 to take it.)
 
 
 class QuantizedLinear(nn.Module):
