@@ -285,6 +285,10 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // dequantized tile costs no shared-memory store and no shared-memory read by the tensor core.
         // Whole warps past the CTA's rows skip the work; dead rows inside a live warp run on zero codes (never stored).
         const bool warp_live = (warp & 3) * 32 < p.rpc;
+        // Rows past the CTA's share inside a live warp: in the 1-k-block-per-stage build (> 128 columns), where the tensor core's reads of the
+        // activation tile (32 KiB per k block) compete with the codebook reads for shared memory, their lookups are predicated off (28.5 -> 27.5 us
+        // at 256 rows); in the other builds the branch costs more than the wavefronts (+0.7 us at 16 rows even when no lane takes it), so every
+        // lane of a live warp looks up (zero codes).
         const uint32_t a_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)p.a_col0 + (uint32_t)hk * 8u;
         long long t_empty = 0, t_stage = 0, t_st = 0;                    // experiments: cycles in the empty wait / code staging / STTM wait
         int s = 0;                                                       // stage of this k block
@@ -302,9 +306,13 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
                     uint4 a[2], b[2];
                     uint32_t v[8];
                     #pragma unroll
-                    for (int g = 0; g < 2; ++g) {                        // bytes 2g / 2g+1 of the quarter = codebook-0 / codebook-1 index
-                        a[g] = lds128(cbA + __byte_perm(w, 0u, 0x4440u + 2u * g) * 128u);
-                        b[g] = lds128(cbB + __byte_perm(w, 0u, 0x4441u + 2u * g) * 128u);
+                    for (int g = 0; g < 2; ++g) a[g] = b[g] = make_uint4(0u, 0u, 0u, 0u);
+                    if (BPS != 1 || row < p.rpc) {                                // > 128 columns: dead rows of a live warp (80 rows per CTA: rows 80..95) cost no wavefronts
+                        #pragma unroll
+                        for (int g = 0; g < 2; ++g) {                    // bytes 2g / 2g+1 of the quarter = codebook-0 / codebook-1 index
+                            a[g] = lds128(cbA + __byte_perm(w, 0u, 0x4440u + 2u * g) * 128u);
+                            b[g] = lds128(cbB + __byte_perm(w, 0u, 0x4441u + 2u * g) * 128u);
+                        }
                     }
                     #pragma unroll
                     for (int g = 0; g < 2; ++g) {
