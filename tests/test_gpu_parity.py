@@ -678,3 +678,45 @@ def test_quantized_linear_repacks_after_reload_and_backward(pkg, ops):
     W = ops.code2x8_dequant(cu(B["codes"]), cu(B["codebooks"]), cu(B["scales"]))
     want = W.double().sum(dim=0)
     assert rel_err(xg.grad.double().cpu().numpy().reshape(-1), want.cpu().numpy()) <= 5e-3
+
+
+def test_prefill_chain_respects_stream_order(pkg, ops):
+    """The prefill kernel is launched with programmatic stream serialization and starts on its weights before the previous kernel
+    has finished (gemm_tc.cu: everything before griddepcontrol.wait).  A chain in which every call's input is the previous call's
+    output, issued back to back, must give the bits of the same chain with a device synchronisation after every call."""
+    from rvv_lut_vq_b200 import synth
+    dev = torch.device("cuda", 0)
+    for (n, batch, dtype) in [(1024, 16, torch.float16), (2048, 200, torch.float16), (1024, 64, torch.bfloat16)]:
+        Ls = [synth.make_layer_torch(n, n, dev, dtype=dtype, seed=90 + k, scales="ones") for k in range(3)]
+        x = torch.randn((batch, n), device=dev, dtype=torch.float32).to(dtype)
+        for L in Ls:                                     # scale every layer so that the chain stays O(1): weights ~ N(0, 2), n terms
+            L["scales"] = (L["scales"].float() / (2.0 * n) ** 0.5).to(dtype)
+
+        def chain(sync):
+            y = x
+            for rep in range(4):
+                for L in Ls:
+                    y = ops.code2x8_matmat_dequant_fused(y, L["codes"], L["codebooks"], L["scales"], None)
+                    if sync:
+                        torch.cuda.synchronize()
+            torch.cuda.synchronize()
+            return y
+        y_sync = chain(True)
+        assert torch.isfinite(y_sync.float()).all() and float(y_sync.float().abs().max()) > 1e-3
+        for _ in range(3):
+            assert torch.equal(chain(False).view(torch.int16), y_sync.view(torch.int16))
+        # eager launches are ~20 us apart; inside a CUDA graph the 12 launches really run back to back (the bench's situation)
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            chain(False)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=st):
+                y = x
+                for rep in range(4):
+                    for L in Ls:
+                        y = ops.code2x8_matmat_dequant_fused(y, L["codes"], L["codebooks"], L["scales"], None)
+            for _ in range(5):
+                g.replay()
+                st.synchronize()
+                assert torch.equal(y.view(torch.int16), y_sync.view(torch.int16))
+        torch.cuda.synchronize()
