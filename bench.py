@@ -255,7 +255,7 @@ def measure_prefill_dequant(torch, dev, bf16_peak, hbm_peak):
         us_fused = graph_time_us(torch, st, body_of(ops.code2x8_matmat_dequant_fused), 5, NB)
         us_two = graph_time_us(torch, st, body_of(ops.code2x8_matmat_dequant_two_step), 5, NB)
         flops = 2.0 * batch * IN_F * OUT_F
-        rows.append({"batch": batch, "us": round(us, 2), "route": "two_step" if batch >= ops.TWO_STEP_MIN_ROWS else "fused",
+        rows.append({"batch": batch, "us": round(us, 2), "route": "two_step" if batch >= ops.two_step_min_rows(OUT_F, IN_F) else "fused",
                      "fused_tcgen05_us": round(us_fused, 2), "dequant_plus_library_gemm_us": round(us_two, 2),
                      "tflops": round(flops / us / 1e6, 1), "frac_of_bf16_peak": round(flops / us / 1e6 / bf16_peak, 4),
                      "code_stream_GBps": round(OUT_F * IN_F / 4 / us / 1e3, 1)})

@@ -386,12 +386,26 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             asm volatile("bar.sync 1, 512;" ::: "memory");
             if (*last_flag_ptr) {                                        // last CTA of this tile: fixed-order sum of the partials
                 __threadfence();
+                // 8 batch columns at a time: their loads are in flight together (one column per round trip -- the output stores keep the
+                // compiler from hoisting the next column's loads -- cost 64 L2 latencies at 256 rows: 48 us for a 4096 x 4096 layer).
+                // Per element the partials are still added in split order: same bits.
+                constexpr int UB = 8;
                 if (live)
-                    for (int b = hk; b < p.batch; b += 4) {
-                        float acc = 0.f;
-                        for (int zz = 0; zz < p.ksplit; ++zz)
-                            acc += __ldcg(p.partial + ((size_t)zz * p.n_pad + b) * p.O_pad + o);
-                        finish(acc, b);
+                    for (int b0 = hk; b0 < p.batch; b0 += 4 * UB) {
+                        float acc[UB];
+                        #pragma unroll
+                        for (int u = 0; u < UB; ++u) acc[u] = 0.f;
+                        for (int zz = 0; zz < p.ksplit; ++zz) {
+                            float v[UB];
+                            #pragma unroll
+                            for (int u = 0; u < UB; ++u)
+                                v[u] = b0 + 4 * u < p.batch ? __ldcg(p.partial + ((size_t)zz * p.n_pad + b0 + 4 * u) * p.O_pad + o) : 0.f;
+                            #pragma unroll
+                            for (int u = 0; u < UB; ++u) acc[u] += v[u];
+                        }
+                        #pragma unroll
+                        for (int u = 0; u < UB; ++u)
+                            if (b0 + 4 * u < p.batch) finish(acc[u], b0 + 4 * u);
                     }
                 if (tid == 0) p.counters[tile] = 0u;                     // hand the counter back
             }

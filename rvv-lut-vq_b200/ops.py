@@ -289,14 +289,25 @@ def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, co
 # two-step 38.4 / 38.0 / 38.4 / 35.9 / 41.9 us at 16 .. 256 rows, 58 at 512 and 157 us at 2048 (0.72 of the bf16 peak).  So: one
 # launch of the fused kernel while the rows fit one, the two-step route above.
 TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "257"))
+# Small layers (few row tiles: the fused kernel splits k and pays a fixed-order reduction of fp32 partials, while dequantize-once writes only
+# 32 MB): measured on the other Llama-2-7B shapes (tools/prefill_shapes.py, profiles/r02_prefill_shapes.jsonl) fused / two-step =
+# 9.5 / 18.6, 12.4 / 18.8, 29.7 / 21.1 us at 16 / 64 / 256 rows of 4096x4096 (11008x4096: 14.9 / 40.1, 18.1 / 41.0, 38.8 / 48.8; 4096x12288: 14.1 / 41.0,
+# 15.2 / 41.6, 28.3 / 47.4): up to 4096x4096 weights the two-step route takes over from 129 rows.
+TWO_STEP_MIN_ROWS_SMALL = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS_SMALL", "129"))
+SMALL_LAYER_WEIGHTS = 4096 * 4096
+
+
+def two_step_min_rows(out_features: int, in_features: int) -> int:
+    """rows from which ops.code2x8_matmat_dequant takes the dequantize-once + library GEMM route for this layer shape"""
+    return min(TWO_STEP_MIN_ROWS, TWO_STEP_MIN_ROWS_SMALL) if out_features * in_features <= SMALL_LAYER_WEIGHTS else TWO_STEP_MIN_ROWS
 
 
 def code2x8_matmat_dequant(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
                            bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """cuda_kernel.cpp:450-484, the prefill op: the fused tcgen05 kernel below TWO_STEP_MIN_ROWS rows, dequantize-once +
+    """cuda_kernel.cpp:450-484, the prefill op: the fused tcgen05 kernel below two_step_min_rows(out, in) rows, dequantize-once +
     library GEMM from there on (whichever is faster on B200; both within the north-star tolerance of the float64 result)."""
     rows = input.numel() // max(input.size(-1), 1)
-    if rows >= TWO_STEP_MIN_ROWS:
+    if rows >= two_step_min_rows(codes.size(0), input.size(-1)):
         return code2x8_matmat_dequant_two_step(input, codes, codebooks, scales, bias)
     return code2x8_matmat_dequant_fused(input, codes, codebooks, scales, bias)
 
