@@ -386,27 +386,52 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             asm volatile("bar.sync 1, 512;" ::: "memory");
             if (*last_flag_ptr) {                                        // last CTA of this tile: fixed-order sum of the partials
                 __threadfence();
-                // 8 batch columns at a time: their loads are in flight together (one column per round trip -- the output stores keep the
-                // compiler from hoisting the next column's loads -- cost 64 L2 latencies at 256 rows: 48 us for a 4096 x 4096 layer).
-                // Per element the partials are still added in split order: same bits.
-                constexpr int UB = 8;
-                if (live)
-                    for (int b0 = hk; b0 < p.batch; b0 += 4 * UB) {
-                        float acc[UB];
+                // The reduction is a read of ksplit x batch x rows fp32 partials by ONE CTA: bound by the bytes it keeps in flight.  Any
+                // thread may take any element here, so a thread takes 4 consecutive rows (one 16-byte load per partial) of 4 batch
+                // columns at a time: 512 threads x 4 x 16 B = 32 KiB in flight.  (One column of one row per round trip -- the first
+                // version, the output stores keeping the compiler from hoisting the next loads -- cost 48 us for 256 rows of a
+                // 4096 x 4096 layer; 8 scalar columns in flight 29.7.)  Per element the partials are still added in split order.
+                constexpr int UB = 4;
+                const int og = tid & 31, bq = tid >> 5;                  // rows row0 + 4 og .. + 3; batch columns bq, bq + 16, ...
+                const int o4 = row0 + og * 4;
+                if (og * 4 < p.rpc && o4 < p.O) {
+                    T sc4[4], bi4[4];
+                    #pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        sc4[e] = (p.scales && o4 + e < p.O) ? static_cast<const T*>(p.scales)[o4 + e] : D::from_f(1.f);
+                        bi4[e] = (p.bias && o4 + e < p.O) ? static_cast<const T*>(p.bias)[o4 + e] : D::from_f(0.f);
+                    }
+                    for (int b0 = bq; b0 < p.batch; b0 += 16 * UB) {
+                        float4 acc[UB];
                         #pragma unroll
-                        for (int u = 0; u < UB; ++u) acc[u] = 0.f;
+                        for (int u = 0; u < UB; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                         for (int zz = 0; zz < p.ksplit; ++zz) {
-                            float v[UB];
+                            float4 v[UB];
                             #pragma unroll
-                            for (int u = 0; u < UB; ++u)
-                                v[u] = b0 + 4 * u < p.batch ? __ldcg(p.partial + ((size_t)zz * p.n_pad + b0 + 4 * u) * p.O_pad + o) : 0.f;
+                            for (int u = 0; u < UB; ++u) {
+                                const int bb = b0 + 16 * u;
+                                v[u] = bb < p.batch ? __ldcg(reinterpret_cast<const float4*>(p.partial + ((size_t)zz * p.n_pad + bb) * p.O_pad + o4))
+                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+                            }
                             #pragma unroll
-                            for (int u = 0; u < UB; ++u) acc[u] += v[u];
+                            for (int u = 0; u < UB; ++u) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
                         }
                         #pragma unroll
-                        for (int u = 0; u < UB; ++u)
-                            if (b0 + 4 * u < p.batch) finish(acc[u], b0 + 4 * u);
+                        for (int u = 0; u < UB; ++u) {
+                            const int bb = b0 + 16 * u;
+                            if (bb >= p.batch) continue;
+                            const float f[4] = {acc[u].x, acc[u].y, acc[u].z, acc[u].w};
+                            #pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                if (o4 + e >= p.O) continue;
+                                T rr = D::from_f(f[e]);                  // the reference epilogue, as in finish()
+                                if (p.scales) rr = D::mul(rr, sc4[e]);
+                                if (p.bias)   rr = D::add(rr, bi4[e]);
+                                static_cast<T*>(p.y)[(size_t)bb * p.O + o4 + e] = rr;
+                            }
+                        }
                     }
+                }
                 if (tid == 0) p.counters[tile] = 0u;                     // hand the counter back
             }
         }

@@ -291,8 +291,8 @@ def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, co
 TWO_STEP_MIN_ROWS = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS", "257"))
 # Small layers (few row tiles: the fused kernel splits k and pays a fixed-order reduction of fp32 partials, while dequantize-once writes only
 # 32 MB): measured on the other Llama-2-7B shapes (tools/prefill_shapes.py, profiles/r02_prefill_shapes.jsonl) fused / two-step =
-# 9.5 / 18.6, 12.4 / 18.8, 29.7 / 21.1 us at 16 / 64 / 256 rows of 4096x4096 (11008x4096: 14.9 / 40.1, 18.1 / 41.0, 38.8 / 48.8; 4096x12288: 14.1 / 41.0,
-# 15.2 / 41.6, 28.3 / 47.4): up to 4096x4096 weights the two-step route takes over from 129 rows.
+# 9.6 / 18.7, 11.2 / 18.9, 23.2 / 21.1 us at 16 / 64 / 256 rows of 4096x4096 (11008x4096: 14.9 / 40.5, 16.9 / 41.2, 31.9 / 48.3; 4096x12288: 14.1 / 41.2,
+# 15.2 / 41.8, 28.8 / 47.7): up to 4096x4096 weights the two-step route takes over from 129 rows.
 TWO_STEP_MIN_ROWS_SMALL = int(os.environ.get("LUTVQ_TWO_STEP_MIN_ROWS_SMALL", "129"))
 SMALL_LAYER_WEIGHTS = 4096 * 4096
 
