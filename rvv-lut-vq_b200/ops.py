@@ -266,7 +266,7 @@ def _fn_matmat_packed():
 
 def code2x8_matmat_dequant_fused(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
                                  bias: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """cuda_kernel.cpp:450-484 as ONE kernel: dequantize into shared memory + tcgen05 GEMM (W never exists in HBM), the
+    """cuda_kernel.cpp:450-484 as ONE kernel: dequantize into tensor memory + tcgen05 GEMM (W never exists in HBM), the
     reference's epilogue order (round(acc) * scale + bias).  Batches above 256 rows are chunked (the codes are re-read per chunk)."""
     return _matmat("lutvq_code2x8_matmat_dequant", input, codes, codebooks, scales, bias)
 
