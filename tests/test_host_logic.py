@@ -192,3 +192,14 @@ def test_hf_checkpoint_layout_round_trip(tmp_path):
     hf_loader.save_checkpoint(str(tmp_path / "noq"), cfg_bad, state)
     with pytest.raises(ValueError):
         hf_loader.load_checkpoint(str(tmp_path / "noq"))
+
+
+def test_prefill_route_thresholds():
+    """ops.two_step_min_rows: the fused tcgen05 kernel while the rows fit one launch (<= 256), the dequantize-once + library GEMM route above;
+    small layers (<= 4096 x 4096 weights: the fused kernel splits k) switch from 129 rows (profiles/r02_prefill_shapes.jsonl)."""
+    from rvv_lut_vq_b200 import ops
+    assert ops.two_step_min_rows(11008, 4096) == ops.TWO_STEP_MIN_ROWS == 257
+    assert ops.two_step_min_rows(4096, 11008) == 257 and ops.two_step_min_rows(12288, 4096) == 257
+    assert ops.two_step_min_rows(4096, 4096) == ops.TWO_STEP_MIN_ROWS_SMALL == 129
+    assert ops.two_step_min_rows(1024, 1024) == 129
+    assert ops.TWO_STEP_MIN_ROWS_SMALL <= ops.TWO_STEP_MIN_ROWS
