@@ -87,22 +87,23 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
 }
-// D (tensor memory) (+)= A (TENSOR MEMORY: lane = row, 8 columns = 16 K-major 16-bit elements) * B (shared memory descriptor)
-__device__ __forceinline__ void tc_mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+// D (tensor memory) (+)= A (TENSOR MEMORY: lane = row, 8 columns = 16 K-major 16-bit elements) * B (shared memory descriptor):
+// the four K=16 steps of one k block, executed by a CONVERGED warp behind ONE election (one lane issues); A advances by 8 columns,
+// B's descriptor low word by 2 (32 bytes) per step
+__device__ __forceinline__ void tc_mma4_f16_ts_elect(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate_first) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
-}
-// the same, executed by a CONVERGED warp: one elected lane issues
-__device__ __forceinline__ void tc_mma_f16_ts_elect(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p, e;\n\t"
+        "{\n\t.reg .pred p, e, t;\n\t.reg .b64 d0, d1, d2, d3;\n\t.reg .b32 a1, a2, a3, l1, l2, l3;\n\t"
         "elect.sync _|e, 0xffffffff;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-        :: "r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "setp.eq.b32 t, 0, 0;\n\t"
+        "add.u32 a1, %1, 8;\n\tadd.u32 a2, %1, 16;\n\tadd.u32 a3, %1, 24;\n\t"
+        "add.u32 l1, %2, 2;\n\tadd.u32 l2, %2, 4;\n\tadd.u32 l3, %2, 6;\n\t"
+        "mov.b64 d0, {%2, %3};\n\tmov.b64 d1, {l1, %3};\n\tmov.b64 d2, {l2, %3};\n\tmov.b64 d3, {l3, %3};\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], d0, %4, p;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], d1, %4, t;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], d2, %4, t;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], d3, %4, t;\n\t}"
+        :: "r"(tmem_d), "r"(tmem_a), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate_first) : "memory");
 }
 __device__ __forceinline__ void tc_commit_elect(uint32_t bar) {
     asm volatile(
@@ -476,7 +477,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
         // the compiler wraps every tcgen05 instruction in an ELECT / vote / branch loop, and with the descriptors rebuilt per MMA
         // (shift, mask, or: a chain of dependent uniform-datapath ops) one MMA took ~96 cycles to ISSUE -- 256 of them were the
         // whole loop time at <= 64 columns.  The descriptors' low words now advance by adds: B by 2 per k step (32 bytes), by
-        // bblock/16 per k block; A by 8 columns per k step.
+        // bblock/16 per k block; A by 8 columns per k step; the 4 k steps of a k block share one election (14.1 -> 13.9 us at 16 rows).
         const uint32_t idesc = umma_idesc(DT == LUTVQ_BF16 ? 1 : 0, kBM, p.n_pad);
         const uint64_t bdesc0 = umma_desc_sw128(sB);
         const uint32_t bdesc_hi = (uint32_t)(bdesc0 >> 32), bstage16 = bstage >> 4, bblock16 = bblock >> 4;
@@ -495,11 +496,7 @@ gemm_dequant_tc_kernel(const GemmParams p, const __grid_constant__ CUtensorMap x
             #pragma unroll
             for (int sb = 0; sb < BPS; ++sb) {
                 if (kb + sb >= kb1) break;
-                #pragma unroll
-                for (int k = 0; k < kBK / 16; ++k) {
-                    const uint64_t bdesc = ((uint64_t)bdesc_hi << 32) | (uint64_t)(b_lo + (uint32_t)sb * bblock16 + (uint32_t)k * 2u);
-                    if (do_mma) tc_mma_f16_ts_elect(tmem_base, a_t + (uint32_t)(sb * kATmemCols + k * 8), bdesc, idesc, (kb + sb > kb0 || k > 0) ? 1u : 0u);
-                }
+                if (do_mma) tc_mma4_f16_ts_elect(tmem_base, a_t + (uint32_t)(sb * kATmemCols), b_lo + (uint32_t)sb * bblock16, bdesc_hi, idesc, kb + sb > kb0 ? 1u : 0u);
             }
             tc_commit_elect(empty_bar(s));                               // smem stage free once these MMAs have read it
             b_lo += bstage16;
