@@ -284,7 +284,7 @@ def code2x8_matmat_dequant_two_step(input: torch.Tensor, codes: torch.Tensor, co
 
 
 # rows from which dequantize-once + library GEMM beats the fused kernel.  Measured on B200, 4096x11008, a ring of 24 L2-cold
-# layers, scales applied (bench.py `prefill`, profiles/r02_bench_line.json): fused 14.1 / 14.5 / 15.3 / 18.4 / 28.5 us at
+# layers, scales applied (bench.py `prefill`, profiles/r02_bench_line.json): fused 14.0 / 14.4 / 15.0 / 18.0 / 27.9 us at
 # 16 / 32 / 64 / 128 / 256 rows, then 58 us at 512 and ~250 us at 2048 (one launch takes <= 256 rows: chunks re-read the codes);
 # two-step 38.4 / 38.0 / 38.4 / 35.9 / 41.9 us at 16 .. 256 rows, 58 at 512 and 157 us at 2048 (0.72 of the bf16 peak).  So: one
 # launch of the fused kernel while the rows fit one, the two-step route above.
